@@ -1,0 +1,183 @@
+/* sba.h — C-ABI of the B200-native stereo bundle adjuster (libsba.so).
+ *
+ * Drop-in boundary for the reference's BundleAdjuster (reference: src/bundle_adjuster.h:13-25):
+ * everything that BundleAdjuster::Optimize hands to Ceres (src/bundle_adjuster.cpp:59-117) goes
+ * through sba_solve() instead; the pack / unpack around it (src/bundle_adjuster.cpp:41-110,121-132)
+ * is sba_pack_window() / sba_unpack_window().  Plain pointers and sizes only; no C++/torch types.
+ *
+ * Conventions (identical to the reference):
+ *   poses   f64 [Nc*6]  = [angle-axis w (3), translation t (3)] of T_cw (camera-from-world)
+ *                          (src/math_utils.h:12-25, src/bundle_adjuster.cpp:66-69)
+ *   points  f64 [Np*3]
+ *   obs_uv  f32 [Nobs*4] = (u_l, v_l, u_r, v_r)          (src/observation.h:11-15)
+ *   p_l,p_r f64 [12] row-major 3x4 projection matrices    (src/reprojection_error.h:65-66)
+ *   objective  1/2 sum_k huber(|| r_k ||^2), r_k the 4-vector of src/reprojection_error.h:35-38
+ */
+#ifndef SBA_H_
+#define SBA_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sba_handle_s* sba_handle;
+
+typedef enum {
+  SBA_OK = 0,
+  SBA_NO_CONVERGENCE = 1,   /* iteration / time limit hit (results still written, like the reference) */
+  SBA_NUMERICAL_FAILURE = 2,
+  SBA_INVALID_ARGUMENT = 3,
+  SBA_CUDA_ERROR = 4,
+  SBA_NCCL_ERROR = 5
+} sba_status;
+
+/* termination reason per window */
+enum {
+  SBA_RUNNING = 0,
+  SBA_TERM_PARAMETER_TOLERANCE = 1,
+  SBA_TERM_FUNCTION_TOLERANCE = 2,
+  SBA_TERM_GRADIENT_TOLERANCE = 3,
+  SBA_TERM_MAX_ITERATIONS = 4,
+  SBA_TERM_MAX_TIME = 5,
+  SBA_TERM_MIN_RADIUS = 6,
+  SBA_TERM_INVALID_STEPS = 7
+};
+
+/* replaces the ceres::Solver::Options the reference fills in its ctor
+ * (src/bundle_adjuster.cpp:14-36) + the constants of src/params.h:34-47. */
+typedef struct sba_options {
+  int32_t max_iterations;        /* 50    src/params.h:34 */
+  double  max_time_s;            /* 1.0   src/params.h:41 ; <= 0: unlimited (the :40 alternative) */
+  double  huber_delta;           /* 1.0   src/bundle_adjuster.cpp:100 */
+  double  point_lower_bound;     /* -1e4  src/params.h:44 */
+  double  point_upper_bound;     /* +1e4  src/params.h:47 */
+  double  parameter_tolerance;   /* 1e-8  Ceres default */
+  double  function_tolerance;    /* 1e-16 src/bundle_adjuster.cpp:36 */
+  double  gradient_tolerance;    /* 1e-16 src/bundle_adjuster.cpp:35 */
+  int32_t residual_dim;          /* 4 = reference (src/reprojection_error.h:58); 3 = (u_l,v_l,u_r) only */
+  double  initial_radius;        /* 1e4   Ceres default initial_trust_region_radius */
+  int32_t max_pcg_iterations;    /* 500   PCG on the reduced camera system (replaces CHOLMOD, :26-29) */
+  double  pcg_tolerance;         /* 1e-10 relative preconditioned-residual tolerance */
+  int32_t verbose;               /* 0     (reference prints progress + FullReport, :15,:118) */
+} sba_options;
+
+typedef struct sba_summary {
+  double  initial_cost;          /* summed over windows */
+  double  final_cost;
+  int32_t iterations;            /* LM iterations run (max over windows), excluding iteration 0 */
+  int32_t successful_steps;      /* summed over windows */
+  int32_t linearizations;
+  int32_t pcg_iterations;        /* total */
+  int32_t termination;           /* reason of window 0 (SBA_TERM_*) */
+  int32_t num_windows_converged;
+  double  time_total_s;          /* wall, whole call */
+  double  time_structure_s;      /* one-off index / pattern build (host) */
+  double  time_h2d_s, time_d2h_s;
+  double  time_solve_s;          /* LM loop, wall */
+  double  ms_linearize;          /* device time (CUDA events), summed over the solve */
+  double  ms_schur;
+  double  ms_pcg;
+  double  ms_update;
+} sba_summary;
+
+void sba_default_options(sba_options* opt);
+const char* sba_status_string(int status);
+const char* sba_last_error(void);
+
+/* ---- handle ------------------------------------------------------------------------------- */
+/* One handle = one CUDA device = one host thread at a time.  No global state. */
+int sba_create(int device, sba_handle* out);
+void sba_destroy(sba_handle h);
+
+/* Problem structure (constant across LM iterations and across repeated solves of one window).
+ *   obs_cam[k], obs_pt[k]  : camera / point index of residual block k, in the reference's scan order
+ *                            (src/bundle_adjuster.cpp:62-102); duplicated (cam,pt) pairs allowed.
+ *   cam_fixed[c]           : 1 = held constant.  NULL => first camera of every window
+ *                            (src/bundle_adjuster.cpp:113).
+ *   num_windows / win_*    : independent problems solved in one call, each with its own LM state.
+ *                            win_cam_off / win_pt_off [num_windows+1]: cameras and points of window w
+ *                            are the contiguous index ranges [off[w], off[w+1]).  NULL => one window.
+ * Builds: observations sorted by point and by camera, pair list + block pattern of the reduced
+ * camera matrix.  Returns SBA_INVALID_ARGUMENT on out-of-range indices. */
+int sba_set_structure(sba_handle h, int32_t num_cameras, int32_t num_points, int64_t num_observations,
+                      const int32_t* obs_cam, const int32_t* obs_pt, const uint8_t* cam_fixed,
+                      int32_t num_windows, const int32_t* win_cam_off, const int32_t* win_pt_off);
+
+/* Multi-GPU: this rank owns points [pt_begin, pt_end) (and all their observations); cameras are
+ * replicated.  Must be called before sba_set_structure; needs sba_comm_init. */
+int sba_set_point_shard(sba_handle h, int32_t pt_begin, int32_t pt_end);
+
+/* Upload state + measurements (host pointers). */
+int sba_set_state(sba_handle h, const double* poses, const double* points);
+int sba_set_measurements(sba_handle h, const float* obs_uv, const double* p_l, const double* p_r);
+int sba_get_state(sba_handle h, double* poses, double* points);
+
+/* Run the LM loop on device-resident state. */
+int sba_run(sba_handle h, const sba_options* opt, sba_summary* summary);
+
+/* One-shot: structure + upload + LM + download.  poses / points are updated in place (also when
+ * the result is SBA_NO_CONVERGENCE, as the reference always writes back, :121-132); untouched on
+ * SBA_INVALID_ARGUMENT / SBA_CUDA_ERROR / SBA_NUMERICAL_FAILURE. */
+int sba_solve(sba_handle h, int32_t num_cameras, int32_t num_points, int64_t num_observations,
+              double* poses, double* points, const int32_t* obs_cam, const int32_t* obs_pt,
+              const float* obs_uv, const double* p_l, const double* p_r, const uint8_t* cam_fixed,
+              int32_t num_windows, const int32_t* win_cam_off, const int32_t* win_pt_off,
+              const sba_options* opt, sba_summary* summary);
+
+/* ---- stage-level entry points (parity tests + bench) ------------------------------------------ */
+/* K0+K1+K2: residuals, analytic Jacobians, Huber, U/V/W/g accumulation at the current state. */
+int sba_linearize(sba_handle h, const sba_options* opt);
+/* K3: damped Schur complement for trust-region radius `radius` (all windows). */
+int sba_schur(sba_handle h, const sba_options* opt, double radius);
+/* K4: PCG on the reduced system; returns iterations used. */
+int sba_pcg(sba_handle h, const sba_options* opt, int32_t* iterations);
+/* repeat (linearize + schur) `repeats` times; device ms per stage averaged (CUDA events). */
+int sba_time_linearize_schur(sba_handle h, const sba_options* opt, double radius, int32_t repeats,
+                             double* ms_linearize, double* ms_schur);
+
+/* Introspection, all host output buffers, any may be NULL.  Orders are the caller's own:
+ *   r [Nobs*4] corrected residuals in input observation order; W [Nobs*18] (6x3 row-major) likewise;
+ *   U [Nc*36] full symmetric 6x6; V [Np*9]; gc [Nc*6]; gp [Np*3]; cost [num_windows]. */
+int sba_get_linearization(sba_handle h, double* r, double* U, double* V, double* W, double* gc,
+                          double* gp, double* cost);
+/* Block pattern of the reduced camera matrix over FREE cameras (full: both triangles), sorted by
+ * (row, col).  Returns the block count; fills rows/cols up to `capacity`. */
+int64_t sba_get_schur_pattern(sba_handle h, int32_t* rows, int32_t* cols, int64_t capacity);
+/* Values of those blocks (36 doubles each, row-major), rhs [6*Nfree], and PCG solution [6*Nfree]. */
+int sba_get_schur_values(sba_handle h, double* blocks, double* rhs, double* solution);
+/* sorted views: obs index (input order) at each position of the point-sorted / camera-sorted lists */
+int sba_get_sorted_views(sba_handle h, int32_t* by_point, int32_t* by_camera);
+int32_t sba_num_free_cameras(sba_handle h);
+/* number of kernels launched by this handle so far (bench.py's gpu_launches) */
+int64_t sba_launch_count(sba_handle h);
+
+/* ---- multi-GPU (NCCL over NVLink) -------------------------------------------------------------- */
+/* id: 128-byte ncclUniqueId made by rank 0 with sba_comm_unique_id and broadcast by the caller. */
+int sba_comm_unique_id(uint8_t id[128]);
+int sba_comm_init(sba_handle h, int32_t rank, int32_t world_size, const uint8_t id[128]);
+
+/* ---- host side of BundleAdjuster::Optimize ------------------------------------------------------ */
+/* Pack window [start,end) of a map (reference: src/bundle_adjuster.cpp:41-110).
+ *   T_wc [N*16] f32 row-major world-from-camera (Frame::GlobalPose), map_points [M*3] f32,
+ *   frame_off [N+1] offsets into obs_point_id / obs_uv_in (per-frame observation lists, stored flat).
+ * Outputs (caller-allocated; capacities: poses 6*(end-start), the rest sized by the window's
+ * observation count): point numbering = order of first appearance, bit-exact with the reference.
+ * Returns number of points via *num_points. */
+int sba_pack_window(const float* T_wc, const float* map_points, const int64_t* frame_off,
+                    const uint32_t* obs_point_id, const float* obs_uv_in, int32_t start, int32_t end,
+                    double* poses, double* points, uint32_t* point_ids, int32_t* obs_cam,
+                    int32_t* obs_pt, float* obs_uv, int32_t* num_points);
+/* Write back (reference: src/bundle_adjuster.cpp:121-132 + Frame::GlobalPose setter,
+ * src/camera_frame.h:32-49): T_wc rows [start,end) and the window's map points are overwritten. */
+int sba_unpack_window(float* T_wc, float* map_points, int32_t start, int32_t end, const double* poses,
+                      const double* points, const uint32_t* point_ids, int32_t num_points);
+/* MatrixToPose / PoseToMatrix (src/math_utils.h:12-41), float arithmetic like the reference. */
+void sba_matrix_to_pose(const float* T16, double* pose6);
+void sba_pose_to_matrix(const double* pose6, float* T16);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SBA_H_ */

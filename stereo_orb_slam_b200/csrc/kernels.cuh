@@ -1,0 +1,671 @@
+// kernels.cuh — hand-written sm_100a kernels of the stereo BA hot path (fp64, HBM-bound).
+//
+// Stage map:  K0 cam_precompute · K1/K2 lin_points + lin_cameras (residual, analytic
+// Jacobian algebra, Huber, U/V/W/g accumulation; Jacobians never reach HBM, W is written once)
+// · K3 schur_pairs / schur_assemble / rhs · K4 pcg_* · K5 backsub · K6 cost_points · lm_control.
+// No global data-path atomics anywhere: every reduction is a fixed-order tree over statically
+// assigned chunks, so results are bit-reproducible run to run.
+#pragma once
+#include <cuda_runtime.h>
+#include "sba_device.cuh"
+#include "sba_internal.h"
+
+namespace sba {
+
+// Sum N per-thread values over a 128-thread CTA.  Thread t < N returns the total of element t
+// (fixed order: xor-butterfly inside each warp, then warps 0..3 in order).
+template <int N>
+__device__ __forceinline__ double block_sum(double (&v)[N], double* sm /* [4*N] */) {
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    double x = v[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    v[i] = x;
+  }
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  __syncthreads();   // protect sm against a previous use
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) sm[w * N + i] = v[i];
+  }
+  __syncthreads();
+  double out = 0.0;
+  if (threadIdx.x < N) out = ((sm[threadIdx.x] + sm[N + threadIdx.x]) + sm[2 * N + threadIdx.x]) + sm[3 * N + threadIdx.x];
+  return out;
+}
+
+__device__ __forceinline__ double block_max1(double v, double* sm /* [4] */) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane == 0) sm[w] = v;
+  __syncthreads();
+  return fmax(fmax(sm[0], sm[1]), fmax(sm[2], sm[3]));
+}
+
+__device__ __forceinline__ void load_campre(const CamPre* __restrict__ base, int c, CamPre& out) {
+  const double* s = reinterpret_cast<const double*>(base + c);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) out.R[i] = __ldg(s + i);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) out.Jl[i] = __ldg(s + 9 + i);
+#pragma unroll
+  for (int i = 0; i < 3; ++i) out.t[i] = __ldg(s + 18 + i);
+}
+// R and t only (cost evaluation)
+__device__ __forceinline__ void load_campre_Rt(const CamPre* __restrict__ base, int c, CamPre& out) {
+  const double* s = reinterpret_cast<const double*>(base + c);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) out.R[i] = __ldg(s + i);
+#pragma unroll
+  for (int i = 0; i < 3; ++i) out.t[i] = __ldg(s + 18 + i);
+}
+
+// ------------------------------------------------------------------------------------------ K0
+__global__ void k_cam_precompute(int Nc, const double* __restrict__ poses, CamPre* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= Nc) return;
+  CamPre cp;
+  cam_precompute(poses + 6 * c, cp);
+  out[c] = cp;
+}
+
+// clamp points into the box (Ceres projects x onto the bounds at iteration 0; reference bounds:
+// src/bundle_adjuster.cpp:104-108)
+__global__ void k_project_points(int64_t n, double* __restrict__ pts, double lo, double hi) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) pts[i] = clampd(pts[i], lo, hi);
+}
+
+// ------------------------------------------------------------------------------- K1/K2 by point
+// One thread per point, one CTA per point chunk.  Reads idx 4 + uv 16 B per observation and
+// 24 B per point; writes W 144 B per observation, V+gp 72 B per point.
+__global__ void __launch_bounds__(kThreads) k_lin_points(Dev d, DevParams P) {
+  __shared__ double sm[4 * 1];
+  __shared__ double smx[4];
+  const int chunk = blockIdx.x;
+  const int p = d.pchunk_begin[chunk] + threadIdx.x;
+  double cost[1] = {0.0};
+  double gmax = 0.0;
+  if (p < d.pchunk_end[chunk]) {
+    const double X[3] = {d.pts[3 * p], d.pts[3 * p + 1], d.pts[3 * p + 2]};
+    double V[6] = {0, 0, 0, 0, 0, 0}, gp[3] = {0, 0, 0};
+    const int e1 = d.pt_off[p + 1];
+    for (int e = d.pt_off[p]; e < e1; ++e) {
+      CamPre cp;
+      load_campre(d.campre, __ldg(d.pcam + e), cp);
+      const float4 m = __ldg(d.uv_p + e);
+      const float uv[4] = {m.x, m.y, m.z, m.w};
+      double q[3], r[4], D[12];
+      const double s = project(P.pl, P.pr, cp, X, uv, P.rdim, q, r, D);
+      double rho, w;
+      huber(P.huber_delta, s, rho, w);
+      cost[0] += 0.5 * rho;
+      double A[6], h[3], G[9], W[18];
+      form_A_h(D, r, w, A, h);
+      form_G(cp, q, G);
+      accum_point(cp, A, h, G, V, gp, W);
+      double2* Wo = reinterpret_cast<double2*>(d.W + (size_t)e * 18);
+#pragma unroll
+      for (int i = 0; i < 9; ++i) Wo[i] = make_double2(W[2 * i], W[2 * i + 1]);
+      if (d.r_dbg) {
+        const double sq = sqrt(w);
+        double* ro = d.r_dbg + (size_t)d.perm_p[e] * 4;
+        ro[0] = sq * r[0]; ro[1] = sq * r[1]; ro[2] = sq * r[2]; ro[3] = sq * r[3];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 6; ++i) d.V[(size_t)p * 6 + i] = V[i];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      d.gp[(size_t)p * 3 + i] = gp[i];
+      gmax = fmax(gmax, fabs(X[i] - clampd(X[i] - gp[i], P.lo, P.hi)));   // projected-gradient norm
+    }
+  }
+  const double tot = block_sum<1>(cost, sm);
+  const double mx = block_max1(gmax, smx);
+  if (threadIdx.x == 0) { d.lin_part[2 * chunk] = tot; d.lin_part[2 * chunk + 1] = mx; }
+}
+
+// ------------------------------------------------------------------------------ K1/K2 by camera
+// One CTA per camera chunk (<= kCamChunk observations of ONE free camera, camera order).
+// Recomputes the residual algebra (cheaper than storing per-observation Jacobians: 40 B read
+// instead of 216 B written + read) and reduces U (21) + gc (6) over the chunk.
+__global__ void __launch_bounds__(kThreads) k_lin_cameras(Dev d, DevParams P) {
+  __shared__ double sm[4 * 27];
+  const int ch = blockIdx.x;
+  const int c = d.cchunk_cam[ch];
+  CamPre cp;
+  load_campre(d.campre, c, cp);
+  double acc[27];
+#pragma unroll
+  for (int i = 0; i < 27; ++i) acc[i] = 0.0;
+  const int end = d.cchunk_end[ch];
+  for (int i = d.cchunk_begin[ch] + threadIdx.x; i < end; i += kThreads) {
+    const int p = __ldg(d.cpt + i);
+    const float4 m = __ldg(d.uv_c + i);
+    const float uv[4] = {m.x, m.y, m.z, m.w};
+    const double X[3] = {d.pts[3 * (size_t)p], d.pts[3 * (size_t)p + 1], d.pts[3 * (size_t)p + 2]};
+    double q[3], r[4], D[12];
+    const double s = project(P.pl, P.pr, cp, X, uv, P.rdim, q, r, D);
+    double rho, w;
+    huber(P.huber_delta, s, rho, w);
+    double A[6], h[3], G[9];
+    form_A_h(D, r, w, A, h);
+    form_G(cp, q, G);
+    accum_camera(A, h, G, acc, acc + 21);
+  }
+  const double tot = block_sum<27>(acc, sm);
+  if (threadIdx.x < 27) d.cpart[(size_t)ch * 27 + threadIdx.x] = tot;
+}
+
+// sum the chunk partials of every camera in chunk order -> U [Nc*21], gc [Nc*6]
+__global__ void k_cam_finish(Dev d) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= d.Nc * 27) return;
+  const int c = t / 27, e = t - c * 27;
+  double s = 0.0;
+  for (int ch = d.cam_chunk_off[c]; ch < d.cam_chunk_off[c + 1]; ++ch) s += d.cpart[(size_t)ch * 27 + e];
+  if (e < 21) d.U[(size_t)c * 21 + e] = s;
+  else d.gc[(size_t)c * 6 + (e - 21)] = s;
+}
+
+// Jacobi column scaling, fixed at iteration 0 (Ceres jacobi_scaling): s = 1/(1+sqrt(H_jj)), stored squared
+__global__ void k_jacobi_scale(Dev d) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nc = (int64_t)d.Nc * 6, np = (int64_t)d.Np * 3;
+  if (t < nc) {
+    const int c = (int)(t / 6), i = (int)(t - 6 * (int64_t)c);
+    const double s = 1.0 / (1.0 + sqrt(d.U[(size_t)c * 21 + up6(i, i)]));
+    d.sc2c[t] = s * s;
+  } else if (t < nc + np) {
+    const int64_t u = t - nc;
+    const int64_t p = u / 3; const int i = (int)(u - 3 * p);
+    const int di = (i == 0) ? 0 : (i == 1 ? 3 : 5);
+    const double s = 1.0 / (1.0 + sqrt(d.V[(size_t)p * 6 + di]));
+    d.sc2p[u] = s * s;
+  }
+}
+
+// per window: cost = sum of chunk costs, gmax = max(chunk gmax, |gc| of free cameras);
+// gradient-tolerance test (Ceres: after every accepted step and at iteration 0).
+__global__ void __launch_bounds__(kThreads) k_lin_finish(Dev d, DevParams P) {
+  __shared__ double sm[4];
+  __shared__ double smx[4];
+  const int w = blockIdx.x;
+  double cost[1] = {0.0};
+  double gmax = 0.0;
+  for (int ch = d.win_pchunk_off[w] + threadIdx.x; ch < d.win_pchunk_off[w + 1]; ch += kThreads) {
+    cost[0] += d.lin_part[2 * ch];
+    gmax = fmax(gmax, d.lin_part[2 * ch + 1]);
+  }
+  for (int f = d.win_fc_off[w] + threadIdx.x; f < d.win_fc_off[w + 1]; f += kThreads) {
+    const int c = d.free2cam[f];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) gmax = fmax(gmax, fabs(d.gc[(size_t)c * 6 + i]));
+  }
+  const double tot = block_sum<1>(cost, sm);
+  const double mx = block_max1(gmax, smx);
+  if (threadIdx.x == 0) {
+    d.w_cost[w] = tot;
+    d.w_gmax[w] = mx;
+  }
+}
+
+// --------------------------------------------------------------------------- K3: Schur complement
+// LM damping in Ceres's Jacobi-scaled space mapped back to the unscaled one:
+//   D_j = clamp(s_j^2 H_jj, 1e-6, 1e32) / (s_j^2 radius)        (levenberg_marquardt_strategy)
+__device__ __forceinline__ double lm_damp(double sc2, double hjj, double radius) {
+  return clampd(sc2 * hjj, 1e-6, 1e32) / (sc2 * radius);
+}
+
+// thread per point: Vinv = (V + Dp)^-1 (6 sym), tp = Vinv gp
+__global__ void __launch_bounds__(kThreads) k_point_damp(Dev d) {
+  const int chunk = blockIdx.x;
+  const int p = d.pchunk_begin[chunk] + threadIdx.x;
+  if (p >= d.pchunk_end[chunk]) return;
+  const int w = d.pchunk_win[chunk];
+  const double radius = d.w_radius[w];
+  double V[6];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) V[i] = d.V[(size_t)p * 6 + i];
+  V[0] += lm_damp(d.sc2p[(size_t)p * 3 + 0], V[0], radius);
+  V[3] += lm_damp(d.sc2p[(size_t)p * 3 + 1], V[3], radius);
+  V[5] += lm_damp(d.sc2p[(size_t)p * 3 + 2], V[5], radius);
+  double Vi[6];
+  if (!inv_sym3(V, Vi)) d.w_fail[w] = 1;   // benign race: every writer stores 1
+  const double g0 = d.gp[(size_t)p * 3], g1 = d.gp[(size_t)p * 3 + 1], g2 = d.gp[(size_t)p * 3 + 2];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) d.Vinv[(size_t)p * 6 + i] = Vi[i];
+  d.tp[(size_t)p * 3 + 0] = Vi[0] * g0 + Vi[1] * g1 + Vi[2] * g2;
+  d.tp[(size_t)p * 3 + 1] = Vi[1] * g0 + Vi[3] * g1 + Vi[4] * g2;
+  d.tp[(size_t)p * 3 + 2] = Vi[2] * g0 + Vi[4] * g1 + Vi[5] * g2;
+}
+
+__device__ __forceinline__ void load_W(const double* __restrict__ W, size_t pos, double out[18]) {
+  const double2* s = reinterpret_cast<const double2*>(W + pos * 18);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) { const double2 v = __ldg(s + i); out[2 * i] = v.x; out[2 * i + 1] = v.y; }
+}
+
+// One CTA per pair chunk (<= kPairChunk entries of ONE upper block (i,j), sorted by point):
+//   partial = sum_entries  W_a Vinv_p W_b^T          (6x6)
+__global__ void __launch_bounds__(kThreads) k_schur_pairs(Dev d) {
+  __shared__ double sm[4 * 36];
+  const int ch = blockIdx.x;
+  double acc[36];
+#pragma unroll
+  for (int i = 0; i < 36; ++i) acc[i] = 0.0;
+  const int64_t end = d.schunk_end[ch];
+  for (int64_t it = d.schunk_begin[ch] + threadIdx.x; it < end; it += kThreads) {
+    const int a = __ldg(d.ent_a + it), b = __ldg(d.ent_b + it);
+    const int p = __ldg(d.ppt + a);
+    double Wa[18], Wb[18], Vi[6];
+    load_W(d.W, (size_t)a, Wa);
+    load_W(d.W, (size_t)b, Wb);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) Vi[i] = __ldg(d.Vinv + (size_t)p * 6 + i);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      const double w0 = Wa[3 * i], w1 = Wa[3 * i + 1], w2 = Wa[3 * i + 2];
+      const double y0 = w0 * Vi[0] + w1 * Vi[1] + w2 * Vi[2];
+      const double y1 = w0 * Vi[1] + w1 * Vi[3] + w2 * Vi[4];
+      const double y2 = w0 * Vi[2] + w1 * Vi[4] + w2 * Vi[5];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) acc[6 * i + j] += y0 * Wb[3 * j] + y1 * Wb[3 * j + 1] + y2 * Wb[3 * j + 2];
+    }
+  }
+  const double tot = block_sum<36>(acc, sm);
+  if (threadIdx.x < 36) d.spart[(size_t)ch * 36 + threadIdx.x] = tot;
+}
+
+// thread per (upper block, element): Su = - sum of its chunk partials (U + D added in k_cam_prepare,
+// after the multi-GPU all-reduce of Su)
+__global__ void k_schur_assemble(Dev d) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (int64_t)d.nbu * 36) return;
+  const int b = (int)(t / 36), e = (int)(t - 36 * (int64_t)b);
+  double s = 0.0;
+  for (int ch = d.blk_chunk_off[b]; ch < d.blk_chunk_off[b + 1]; ++ch) s += d.spart[(size_t)ch * 36 + e];
+  d.Su[t] = -s;
+}
+
+// rhs partials, one CTA per camera chunk:  sum_obs W_e tp[point(e)]   (6)
+__global__ void __launch_bounds__(kThreads) k_rhs_cameras(Dev d) {
+  __shared__ double sm[4 * 6];
+  const int ch = blockIdx.x;
+  double acc[6] = {0, 0, 0, 0, 0, 0};
+  const int end = d.cchunk_end[ch];
+  for (int i = d.cchunk_begin[ch] + threadIdx.x; i < end; i += kThreads) {
+    const int pos = __ldg(d.cpos + i), p = __ldg(d.cpt + i);
+    double W[18];
+    load_W(d.W, (size_t)pos, W);
+    const double t0 = __ldg(d.tp + (size_t)p * 3), t1 = __ldg(d.tp + (size_t)p * 3 + 1), t2 = __ldg(d.tp + (size_t)p * 3 + 2);
+#pragma unroll
+    for (int r = 0; r < 6; ++r) acc[r] += W[3 * r] * t0 + W[3 * r + 1] * t1 + W[3 * r + 2] * t2;
+  }
+  const double tot = block_sum<6>(acc, sm);
+  if (threadIdx.x < 6) d.rpart[(size_t)ch * 6 + threadIdx.x] = tot;
+}
+
+// thread per (camera, 6): rsum[c*6+i] = sum of chunk partials (kept separate from gc so that a
+// multi-GPU run can all-reduce it together with Su)
+__global__ void k_rhs_finish(Dev d, double* __restrict__ rsum) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= d.Nf * 6) return;
+  const int f = t / 6, i = t - 6 * f;
+  const int c = d.free2cam[f];
+  double s = 0.0;
+  for (int ch = d.cam_chunk_off[c]; ch < d.cam_chunk_off[c + 1]; ++ch) s += d.rpart[(size_t)ch * 6 + i];
+  rsum[t] = s;
+}
+
+// thread per free camera: add U + D to the diagonal block, rhs = -gc + rsum, Minv = (S_ii)^-1
+__global__ void k_cam_prepare(Dev d, const double* __restrict__ rsum) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= d.Nf) return;
+  const int c = d.free2cam[f];
+  const int w = d.fcam_win[f];
+  const double radius = d.w_radius[w];
+  double* S = d.Su + (size_t)d.diag_blk[f] * 36;
+  double M[36];
+  const double* U = d.U + (size_t)c * 21;
+#pragma unroll
+  for (int i = 0; i < 6; ++i)
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      const double u = (i <= j) ? U[up6(i, j)] : U[up6(j, i)];
+      double v = S[6 * i + j] + u;
+      if (i == j) v += lm_damp(d.sc2c[(size_t)c * 6 + i], u, radius);
+      M[6 * i + j] = v;
+    }
+#pragma unroll
+  for (int i = 0; i < 36; ++i) S[i] = M[i];
+  if (!inv_spd6(M)) {
+    d.w_fail[w] = 1;
+#pragma unroll
+    for (int i = 0; i < 36; ++i) M[i] = (i % 7 == 0) ? 1.0 : 0.0;
+  }
+#pragma unroll
+  for (int i = 0; i < 36; ++i) d.Minv[(size_t)f * 36 + i] = M[i];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) d.rhs[(size_t)f * 6 + i] = rsum[(size_t)f * 6 + i] - d.gc[(size_t)c * 6 + i];
+}
+
+// ------------------------------------------------------------------------------------- K4: PCG
+// Block-Jacobi preconditioned CG on the reduced camera system, one independent solve per window,
+// all windows advanced by the same launches; scalars (alpha, beta, done flags) live on the device.
+
+// thread per free camera: x = 0, r = rhs, z = Minv r, p = z
+__global__ void k_pcg_init(Dev d) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= d.Nf) return;
+  double r[6];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) r[i] = d.rhs[(size_t)f * 6 + i];
+  const double* M = d.Minv + (size_t)f * 36;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    double z = 0.0;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) z += M[6 * i + j] * r[j];
+    d.x[(size_t)f * 6 + i] = 0.0;
+    d.r[(size_t)f * 6 + i] = r[i];
+    d.z[(size_t)f * 6 + i] = z;
+    d.p[(size_t)f * 6 + i] = z;
+  }
+}
+
+// one CTA per window: out = a . b over the window's free-camera rows (fixed order), then the
+// scalar recurrences.  mode 0: rz0 (init)   mode 1: pAp -> alpha   mode 2: rz_new -> beta, done test
+__global__ void __launch_bounds__(kThreads) k_pcg_dot(Dev d, DevParams P, const double* __restrict__ a,
+                                                      const double* __restrict__ b, int mode, int max_it) {
+  __shared__ double sm[4];
+  const int w = blockIdx.x;
+  double s[1] = {0.0};
+  const int i1 = d.win_fc_off[w + 1] * 6;
+  for (int i = d.win_fc_off[w] * 6 + threadIdx.x; i < i1; i += kThreads) s[0] += a[i] * b[i];
+  const double tot = block_sum<1>(s, sm);
+  if (threadIdx.x != 0) return;
+  if (mode == 0) {
+    d.w_rz[w] = tot; d.w_rz0[w] = tot; d.w_pcg_it[w] = 0; d.w_alpha[w] = 0.0; d.w_beta[w] = 0.0;
+    int done = 0;
+    if (d.w_status[w] != 0 || d.w_fail[w] != 0) done = 1;
+    else if (!(tot > 0.0)) { done = 1; if (!(tot == 0.0)) d.w_fail[w] = 1; }   // rhs == 0: x = 0 is the solution; NaN: fail
+    d.w_pcg_done[w] = done;
+    if (!done) atomicAdd(d.counters + 1, 1);
+  } else if (mode == 1) {
+    if (d.w_pcg_done[w]) { d.w_alpha[w] = 0.0; return; }
+    if (!(tot > 0.0)) { d.w_fail[w] = 1; d.w_pcg_done[w] = 1; d.w_alpha[w] = 0.0; return; }   // S not SPD
+    d.w_pAp[w] = tot;
+    d.w_alpha[w] = d.w_rz[w] / tot;
+  } else {
+    if (d.w_pcg_done[w]) { d.w_beta[w] = 0.0; d.w_alpha[w] = 0.0; return; }
+    const double rz_old = d.w_rz[w];
+    d.w_beta[w] = tot / rz_old;
+    d.w_rz[w] = tot;
+    const int it = ++d.w_pcg_it[w];
+    if (!isfinite(tot)) { d.w_fail[w] = 1; d.w_pcg_done[w] = 1; }
+    else if (tot <= P.pcg_tol2 * d.w_rz0[w] || it >= max_it) d.w_pcg_done[w] = 1;
+    else atomicAdd(d.counters + 1, 1);     // control-plane counter only (windows still iterating)
+  }
+}
+
+// thread per scalar row: Ap = S p  (block-CSR over the full pattern; upper blocks stored once)
+__global__ void k_pcg_matvec(Dev d) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= d.Nf * 6) return;
+  const int f = t / 6, r = t - 6 * f;
+  double s = 0.0;
+  const int j1 = d.row_ptr[f + 1];
+  for (int j = d.row_ptr[f]; j < j1; ++j) {
+    const int col = __ldg(d.bsr_col + j);
+    const int bi = __ldg(d.bsr_blk + j);
+    const double* x = d.p + (size_t)col * 6;
+    if (bi >= 0) {
+      const double* B = d.Su + (size_t)bi * 36 + 6 * r;
+#pragma unroll
+      for (int c = 0; c < 6; ++c) s += B[c] * x[c];
+    } else {
+      const double* B = d.Su + (size_t)(~bi) * 36 + r;   // transposed
+#pragma unroll
+      for (int c = 0; c < 6; ++c) s += B[6 * c] * x[c];
+    }
+  }
+  d.Ap[t] = s;
+}
+
+// thread per free camera: x += alpha p ; r -= alpha Ap ; z = Minv r
+__global__ void k_pcg_update_xr(Dev d) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= d.Nf) return;
+  const int w = d.fcam_win[f];
+  if (d.w_pcg_done[w]) return;
+  const double alpha = d.w_alpha[w];
+  double r[6];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    const size_t k = (size_t)f * 6 + i;
+    d.x[k] += alpha * d.p[k];
+    r[i] = d.r[k] - alpha * d.Ap[k];
+    d.r[k] = r[i];
+  }
+  const double* M = d.Minv + (size_t)f * 36;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    double z = 0.0;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) z += M[6 * i + j] * r[j];
+    d.z[(size_t)f * 6 + i] = z;
+  }
+}
+
+// thread per scalar row: p = z + beta p
+__global__ void k_pcg_update_p(Dev d) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= d.Nf * 6) return;
+  const int w = d.fcam_win[t / 6];
+  if (d.w_pcg_done[w]) return;
+  d.p[t] = d.z[t] + d.w_beta[w] * d.p[t];
+}
+
+// ------------------------------------------------------------------------- K5: back-substitution
+// thread per point: dp = -Vinv (gp + sum_obs W_e^T dc[cam(e)]),  candidate = clamp(x + dp)
+// chunk partials: g.dp, dp^T D dp, |candidate - x|^2, |x|^2
+__global__ void __launch_bounds__(kThreads) k_backsub(Dev d, DevParams P) {
+  __shared__ double sm[4 * 4];
+  const int chunk = blockIdx.x;
+  const int p = d.pchunk_begin[chunk] + threadIdx.x;
+  const int w = d.pchunk_win[chunk];
+  double part[4] = {0, 0, 0, 0};
+  if (p < d.pchunk_end[chunk]) {
+    const double g0 = d.gp[(size_t)p * 3], g1 = d.gp[(size_t)p * 3 + 1], g2 = d.gp[(size_t)p * 3 + 2];
+    double t0 = g0, t1 = g1, t2 = g2;
+    const int e1 = d.pt_off[p + 1];
+    for (int e = d.pt_off[p]; e < e1; ++e) {
+      const int f = __ldg(d.fc + __ldg(d.pcam + e));
+      if (f < 0) continue;
+      double W[18];
+      load_W(d.W, (size_t)e, W);
+#pragma unroll
+      for (int i = 0; i < 6; ++i) {
+        const double dc = d.x[(size_t)f * 6 + i];
+        t0 += W[3 * i] * dc; t1 += W[3 * i + 1] * dc; t2 += W[3 * i + 2] * dc;
+      }
+    }
+    double Vi[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) Vi[i] = d.Vinv[(size_t)p * 6 + i];
+    const double dp[3] = {-(Vi[0] * t0 + Vi[1] * t1 + Vi[2] * t2), -(Vi[1] * t0 + Vi[3] * t1 + Vi[4] * t2),
+                          -(Vi[2] * t0 + Vi[4] * t1 + Vi[5] * t2)};
+    const double radius = d.w_radius[w];
+    const double Vd[3] = {d.V[(size_t)p * 6], d.V[(size_t)p * 6 + 3], d.V[(size_t)p * 6 + 5]};
+    const double g[3] = {g0, g1, g2};
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const double x = d.pts[(size_t)p * 3 + i];
+      const double xn = clampd(x + dp[i], P.lo, P.hi);
+      d.pts_new[(size_t)p * 3 + i] = xn;
+      part[0] += g[i] * dp[i];
+      part[1] += lm_damp(d.sc2p[(size_t)p * 3 + i], Vd[i], radius) * dp[i] * dp[i];
+      part[2] += (xn - x) * (xn - x);
+      part[3] += x * x;
+    }
+  }
+  const double tot = block_sum<4>(part, sm);
+  if (threadIdx.x < 4) d.step_part[(size_t)chunk * 4 + threadIdx.x] = tot;
+}
+
+// one CTA per window: candidate poses, and the window's step scalars (cameras + point chunk partials)
+__global__ void __launch_bounds__(kThreads) k_cam_step(Dev d) {
+  __shared__ double sm[4 * 5];
+  const int w = blockIdx.x;
+  double part[5] = {0, 0, 0, 0, 0};   // g.d, d D d, |step|^2, |x|^2, dc . r_pcg
+  const double radius = d.w_radius[w];
+  for (int c = d.win_cam_off[w] + threadIdx.x; c < d.win_cam_off[w + 1]; c += kThreads) {
+    const int f = d.fc[c];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      const double x = d.poses[(size_t)c * 6 + i];
+      double dc = 0.0;
+      if (f >= 0) {
+        dc = d.x[(size_t)f * 6 + i];
+        part[0] += d.gc[(size_t)c * 6 + i] * dc;
+        part[1] += lm_damp(d.sc2c[(size_t)c * 6 + i], d.U[(size_t)c * 21 + up6(i, i)], radius) * dc * dc;
+        part[2] += dc * dc;
+        part[3] += x * x;
+        part[4] += dc * d.r[(size_t)f * 6 + i];
+      }
+      d.poses_new[(size_t)c * 6 + i] = x + dc;
+    }
+  }
+  for (int ch = d.win_pchunk_off[w] + threadIdx.x; ch < d.win_pchunk_off[w + 1]; ch += kThreads) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) part[i] += d.step_part[(size_t)ch * 4 + i];
+  }
+  const double tot = block_sum<5>(part, sm);
+  if (threadIdx.x == 0) d.w_gd[w] = tot;
+  if (threadIdx.x == 1) d.w_dDd[w] = tot;
+  if (threadIdx.x == 2) d.w_step2[w] = tot;
+  if (threadIdx.x == 3) d.w_x2[w] = tot;
+  if (threadIdx.x == 4) d.w_dr[w] = tot;
+}
+
+// -------------------------------------------------------------------------- K6: candidate cost
+__global__ void __launch_bounds__(kThreads) k_cost_points(Dev d, DevParams P) {
+  __shared__ double sm[4];
+  const int chunk = blockIdx.x;
+  const int p = d.pchunk_begin[chunk] + threadIdx.x;
+  double cost[1] = {0.0};
+  if (p < d.pchunk_end[chunk]) {
+    const double X[3] = {d.pts_new[3 * (size_t)p], d.pts_new[3 * (size_t)p + 1], d.pts_new[3 * (size_t)p + 2]};
+    const int e1 = d.pt_off[p + 1];
+    for (int e = d.pt_off[p]; e < e1; ++e) {
+      CamPre cp;
+      load_campre_Rt(d.campre_new, __ldg(d.pcam + e), cp);
+      const float4 m = __ldg(d.uv_p + e);
+      const float uv[4] = {m.x, m.y, m.z, m.w};
+      cost[0] += obs_cost(P.pl, P.pr, cp, X, uv, P.rdim, P.huber_delta);
+    }
+  }
+  const double tot = block_sum<1>(cost, sm);
+  if (threadIdx.x == 0) d.cost_part[chunk] = tot;
+}
+
+// one CTA per window: candidate cost = sum of chunk partials
+__global__ void __launch_bounds__(kThreads) k_cost_finish(Dev d) {
+  __shared__ double sm[4];
+  const int w = blockIdx.x;
+  double s[1] = {0.0};
+  for (int ch = d.win_pchunk_off[w] + threadIdx.x; ch < d.win_pchunk_off[w + 1]; ch += kThreads) s[0] += d.cost_part[ch];
+  const double tot = block_sum<1>(s, sm);
+  if (threadIdx.x == 0) d.w_cand[w] = tot;
+}
+
+// -------------------------------------------------------------------------------- LM control
+// Ceres trust-region rules (trust_region_minimizer.cc / levenberg_marquardt_strategy.cc restated;
+// options from the reference: src/bundle_adjuster.cpp:14-36).  Thread per window.
+
+// after a linearisation: gradient-tolerance test; `first` also initialises the LM state
+__global__ void k_lm_begin(Dev d, DevParams P, double initial_radius, int first) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= d.nwin) return;
+  if (first) {
+    d.w_radius[w] = initial_radius; d.w_decf[w] = 2.0; d.w_status[w] = 0; d.w_iter[w] = 0; d.w_succ[w] = 0;
+    d.w_invalid[w] = 0; d.w_accept[w] = 0;
+  }
+  d.w_fail[w] = 0;
+  if (d.w_status[w] == 0) {
+    if (!isfinite(d.w_cost[w])) d.w_status[w] = -2;                       // numerical failure
+    else if (d.w_gmax[w] <= P.gtol) d.w_status[w] = 3;                    // gradient tolerance
+  }
+}
+
+__global__ void k_lm_control(Dev d, DevParams P) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= d.nwin) return;
+  d.w_accept[w] = 0;
+  if (d.w_status[w] != 0) return;
+  const int iter = ++d.w_iter[w];
+  const double cost = d.w_cost[w], cand = d.w_cand[w];
+  const double model = -0.5 * d.w_gd[w] + 0.5 * d.w_dDd[w] + 0.5 * d.w_dr[w];
+  bool stop = false;
+  if (d.w_fail[w] != 0 || !(model > 0.0) || !isfinite(model)) {
+    // invalid step: Ceres halves the radius; 5 in a row is a failure
+    if (++d.w_invalid[w] >= 5) { d.w_status[w] = 7; stop = true; }
+    else d.w_radius[w] *= 0.5;
+  } else {
+    d.w_invalid[w] = 0;
+    const double step_norm = sqrt(d.w_step2[w]), x_norm = sqrt(d.w_x2[w]);
+    if (step_norm <= P.ptol * (x_norm + P.ptol)) { d.w_status[w] = 1; stop = true; }
+    else {
+      const double cost_change = cost - cand;
+      if (fabs(cost_change) <= P.ftol * cost) { d.w_status[w] = 2; stop = true; }
+      else {
+        const double rho = cost_change / model;
+        if (isfinite(cand) && rho > 1e-3) {
+          d.w_accept[w] = 1; d.w_succ[w]++;
+          d.w_cost[w] = cand;
+          const double t = 2.0 * rho - 1.0;
+          d.w_radius[w] = fmin(1e16, d.w_radius[w] / fmax(1.0 / 3.0, 1.0 - t * t * t));
+          d.w_decf[w] = 2.0;
+        } else {
+          d.w_radius[w] = d.w_radius[w] / d.w_decf[w];
+          d.w_decf[w] *= 2.0;
+        }
+      }
+    }
+  }
+  if (!stop) {
+    if (iter >= P.max_iterations) d.w_status[w] = 4;
+    else if (d.w_radius[w] < 1e-32) d.w_status[w] = 6;
+    else atomicAdd(d.counters, 1);     // control-plane counter: windows still running
+  }
+}
+
+// accepted windows: candidate -> current
+__global__ void __launch_bounds__(kThreads) k_apply_points(Dev d) {
+  const int chunk = blockIdx.x;
+  if (!d.w_accept[d.pchunk_win[chunk]]) return;
+  const int p = d.pchunk_begin[chunk] + threadIdx.x;
+  if (p >= d.pchunk_end[chunk]) return;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) d.pts[(size_t)p * 3 + i] = d.pts_new[(size_t)p * 3 + i];
+}
+__global__ void k_apply_cams(Dev d) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= d.Nc * 6) return;
+  if (d.w_accept[d.cam_win[t / 6]]) d.poses[t] = d.poses_new[t];
+}
+
+// permute the caller's observations into the point-sorted and camera-sorted views
+__global__ void k_permute_uv(Dev d, const float4* __restrict__ uv_in, float4* __restrict__ uv_p, float4* __restrict__ uv_c) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= d.Nobs) return;
+  uv_p[e] = uv_in[d.perm_p[e]];
+  uv_c[e] = uv_in[d.perm_p[d.cpos[e]]];
+}
+
+}  // namespace sba

@@ -1,0 +1,63 @@
+// sba_device.cuh — device-resident tables and state of one handle; passed by value to kernels.
+#pragma once
+#include <cstdint>
+#include "sba_math.cuh"
+
+namespace sba {
+
+struct DevParams {   // solver constants, by value
+  double pl[12], pr[12];
+  double huber_delta, lo, hi;
+  double ptol, ftol, gtol;
+  double pcg_tol2;     // pcg_tolerance^2
+  int32_t rdim, max_iterations;
+};
+
+struct Dev {
+  int32_t Nc, Np, Nf, nwin, nbu, npchunk, ncchunk, nschunk;
+  int64_t Nobs;
+  // ---- structure (const)
+  const int32_t *fc, *free2cam, *cam_win, *fcam_win, *win_cam_off, *win_fc_off, *win_pchunk_off;
+  const int32_t *pt_off, *perm_p, *pcam, *ppt, *cam_off, *cpos, *cpt;
+  const int32_t *pchunk_begin, *pchunk_end, *pchunk_win;
+  const int32_t *cchunk_cam, *cchunk_begin, *cchunk_end, *cam_chunk_off;
+  const int32_t *blk_row, *blk_col, *blk_chunk_off, *schunk_blk, *diag_blk;
+  const int64_t *schunk_begin, *schunk_end;
+  const int32_t *ent_a, *ent_b;
+  const int32_t *row_ptr, *bsr_col, *bsr_blk;
+  // ---- measurements (const during a solve)
+  const float4 *uv_p;   // [Nobs] point order
+  const float4 *uv_c;   // [Nobs] camera order
+  // ---- state
+  double *poses, *poses_new;     // [Nc*6]
+  double *pts, *pts_new;         // [Np*3]
+  CamPre *campre, *campre_new;   // [Nc]
+  // ---- linearisation
+  double *W;                     // [Nobs*18] point order
+  double *V, *gp;                // [Np*6], [Np*3]
+  double *Vinv, *tp;             // [Np*6], [Np*3]
+  double *U, *gc;                // [Nc*21], [Nc*6]
+  double *cpart;                 // [ncchunk*27]
+  double *sc2c, *sc2p;           // Jacobi scale^2 [Nc*6], [Np*3]
+  double *lin_part;              // [npchunk*2] cost, gmax
+  double *r_dbg;                 // [Nobs*4] or null
+  // ---- Schur
+  double *spart;                 // [nschunk*36]
+  double *Su;                    // [nbu*36]
+  double *rpart;                 // [ncchunk*6]
+  double *rhs;                   // [Nf*6]
+  double *Minv;                  // [Nf*36]
+  // ---- PCG vectors [Nf*6]
+  double *x, *r, *z, *p, *Ap;
+  // ---- step
+  double *step_part;             // [npchunk*4]  g.dp, dp D dp, |step|^2, |x|^2
+  double *cost_part;             // [npchunk]
+  // ---- per-window scalars [nwin]
+  double *w_radius, *w_decf, *w_cost, *w_cand, *w_gmax;
+  double *w_gd, *w_dDd, *w_dr, *w_step2, *w_x2;
+  double *w_rz, *w_rz0, *w_pAp, *w_alpha, *w_beta;
+  int32_t *w_status, *w_iter, *w_succ, *w_invalid, *w_accept, *w_fail, *w_pcg_done, *w_pcg_it;
+  int32_t *counters;             // [0] windows still running, [1] pcg windows not done
+};
+
+}  // namespace sba

@@ -519,7 +519,8 @@ __global__ void __launch_bounds__(kThreads) k_backsub(Dev d, DevParams P) {
 }
 
 // one CTA per window: candidate poses, and the window's step scalars (cameras + point chunk partials)
-__global__ void __launch_bounds__(kThreads) k_cam_step(Dev d) {
+// (multi-GPU: camera terms are counted on rank 0 only; the scalars are all-reduced afterwards)
+__global__ void __launch_bounds__(kThreads) k_cam_step(Dev d, int rank) {
   __shared__ double sm[4 * 5];
   const int w = blockIdx.x;
   double part[5] = {0, 0, 0, 0, 0};   // g.d, d D d, |step|^2, |x|^2, dc . r_pcg
@@ -530,8 +531,8 @@ __global__ void __launch_bounds__(kThreads) k_cam_step(Dev d) {
     for (int i = 0; i < 6; ++i) {
       const double x = d.poses[(size_t)c * 6 + i];
       double dc = 0.0;
-      if (f >= 0) {
-        dc = d.x[(size_t)f * 6 + i];
+      if (f >= 0) dc = d.x[(size_t)f * 6 + i];
+      if (f >= 0 && rank == 0) {
         part[0] += d.gc[(size_t)c * 6 + i] * dc;
         part[1] += lm_damp(d.sc2c[(size_t)c * 6 + i], d.U[(size_t)c * 21 + up6(i, i)], radius) * dc * dc;
         part[2] += dc * dc;
@@ -545,7 +546,8 @@ __global__ void __launch_bounds__(kThreads) k_cam_step(Dev d) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) part[i] += d.step_part[(size_t)ch * 4 + i];
   }
-  const double tot = block_sum<5>(part, sm);
+  double tot = block_sum<5>(part, sm);
+  if (threadIdx.x == 0 && d.w_fail[w] != 0) tot = nan("");   // poison the model change: invalid step on every rank
   if (threadIdx.x == 0) d.w_gd[w] = tot;
   if (threadIdx.x == 1) d.w_dDd[w] = tot;
   if (threadIdx.x == 2) d.w_step2[w] = tot;
@@ -627,6 +629,7 @@ __global__ void k_lm_control(Dev d, DevParams P) {
         const double rho = cost_change / model;
         if (isfinite(cand) && rho > 1e-3) {
           d.w_accept[w] = 1; d.w_succ[w]++;
+          atomicAdd(d.counters + 2, 1);     // control-plane counter: windows that moved
           d.w_cost[w] = cand;
           const double t = 2.0 * rho - 1.0;
           d.w_radius[w] = fmin(1e16, d.w_radius[w] / fmax(1.0 / 3.0, 1.0 - t * t * t));
@@ -643,6 +646,12 @@ __global__ void k_lm_control(Dev d, DevParams P) {
     else if (d.w_radius[w] < 1e-32) d.w_status[w] = 6;
     else atomicAdd(d.counters, 1);     // control-plane counter: windows still running
   }
+}
+
+// wall-clock limit hit on the host (reference: max_solver_time_in_seconds, src/bundle_adjuster.cpp:18)
+__global__ void k_lm_timeout(Dev d) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w < d.nwin && d.w_status[w] == 0) d.w_status[w] = 5;
 }
 
 // accepted windows: candidate -> current

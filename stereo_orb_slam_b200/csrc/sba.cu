@@ -203,8 +203,10 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   AL(d.rhs, nf * 6) AL(h->rsum, nf * 6) AL(d.Minv, nf * 36)
   AL(d.x, nf * 6) AL(d.r, nf * 6) AL(d.z, nf * 6) AL(d.p, nf * 6) AL(d.Ap, nf * 6)
   AL(d.step_part, (size_t)d.npchunk * 4) AL(d.cost_part, (size_t)d.npchunk)
-  AL(d.w_radius, nw) AL(d.w_decf, nw) AL(d.w_cost, nw) AL(d.w_cand, nw) AL(d.w_gmax, nw)
-  AL(d.w_gd, nw) AL(d.w_dDd, nw) AL(d.w_dr, nw) AL(d.w_step2, nw) AL(d.w_x2, nw)
+  AL(d.w_radius, nw) AL(d.w_decf, nw) AL(d.w_cost, nw) AL(d.w_gmax, nw)
+  AL(d.w_gd, nw * 6)   // one block: a multi-GPU solve all-reduces the six step scalars in one call
+  d.w_dDd = d.w_gd + nw; d.w_step2 = d.w_gd + 2 * nw; d.w_x2 = d.w_gd + 3 * nw; d.w_dr = d.w_gd + 4 * nw;
+  d.w_cand = d.w_gd + 5 * nw;
   AL(d.w_rz, nw) AL(d.w_rz0, nw) AL(d.w_pAp, nw) AL(d.w_alpha, nw) AL(d.w_beta, nw)
   AL(d.w_status, nw) AL(d.w_iter, nw) AL(d.w_succ, nw) AL(d.w_invalid, nw) AL(d.w_accept, nw)
   AL(d.w_fail, nw) AL(d.w_pcg_done, nw) AL(d.w_pcg_it, nw) AL(d.counters, 4)
@@ -224,3 +226,515 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   h->time_structure_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   return SBA_OK;
 }
+
+// ---- helpers (still inside extern "C": static, not exported) ------------------------------------
+static void fill_params(sba_handle h, const sba_options* o) {
+  DevParams& P = h->P;
+  P.huber_delta = o->huber_delta; P.lo = o->point_lower_bound; P.hi = o->point_upper_bound;
+  P.ptol = o->parameter_tolerance; P.ftol = o->function_tolerance; P.gtol = o->gradient_tolerance;
+  P.pcg_tol2 = o->pcg_tolerance * o->pcg_tolerance;
+  P.rdim = (o->residual_dim == 3) ? 3 : 4;
+  P.max_iterations = o->max_iterations;
+}
+
+static int check_ready(sba_handle h, bool need_state) {
+  if (!h) { set_error("null handle"); return SBA_INVALID_ARGUMENT; }
+  if (h->device < 0) { set_error("host-only handle: no CUDA device bound (there is no CPU fallback)"); return SBA_CUDA_ERROR; }
+  if (!h->has_structure) { set_error("sba_set_structure has not been called"); return SBA_INVALID_ARGUMENT; }
+  if (need_state && (!h->has_state || !h->has_meas)) { set_error("state / measurements not uploaded"); return SBA_INVALID_ARGUMENT; }
+  return SBA_OK;
+}
+
+int sba_set_state(sba_handle h, const double* poses, const double* points) {
+  int rc = check_ready(h, false);
+  if (rc) return rc;
+  const Dev& d = h->d;
+  if ((d.Nc > 0 && !poses) || (d.Np > 0 && !points)) { set_error("null state"); return SBA_INVALID_ARGUMENT; }
+  CUDA_TRY(cudaSetDevice(h->device));
+  if (d.Nc > 0) CUDA_TRY(cudaMemcpyAsync(d.poses, poses, (size_t)d.Nc * 48, cudaMemcpyHostToDevice, h->stream));
+  if (d.Np > 0) CUDA_TRY(cudaMemcpyAsync(d.pts, points, (size_t)d.Np * 24, cudaMemcpyHostToDevice, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  h->has_state = true; h->jacobi_done = false;
+  return SBA_OK;
+}
+
+int sba_set_measurements(sba_handle h, const float* obs_uv, const double* p_l, const double* p_r) {
+  int rc = check_ready(h, false);
+  if (rc) return rc;
+  if ((h->nobs_all > 0 && !obs_uv) || !p_l || !p_r) { set_error("null measurements"); return SBA_INVALID_ARGUMENT; }
+  CUDA_TRY(cudaSetDevice(h->device));
+  const Dev& d = h->d;
+  if (h->nobs_all > 0)
+    CUDA_TRY(cudaMemcpyAsync(h->uv_in, obs_uv, (size_t)h->nobs_all * 16, cudaMemcpyHostToDevice, h->stream));
+  LAUNCH(h, k_permute_uv, cdiv(d.Nobs, 256), 256, d, h->uv_in, const_cast<float4*>(d.uv_p), const_cast<float4*>(d.uv_c));
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  std::memcpy(h->P.pl, p_l, 96); std::memcpy(h->P.pr, p_r, 96);
+  h->has_meas = true; h->jacobi_done = false;
+  return SBA_OK;
+}
+
+int sba_get_state(sba_handle h, double* poses, double* points) {
+  int rc = check_ready(h, false);
+  if (rc) return rc;
+  if (!h->has_state) { set_error("no state"); return SBA_INVALID_ARGUMENT; }
+  const Dev& d = h->d;
+  CUDA_TRY(cudaSetDevice(h->device));
+  if (h->comm.active() && d.Np > 0) {
+    // every rank holds the updated values of its own points only: zero the rest and sum over ranks
+    const size_t b = (size_t)h->H.pt_begin * 3, e = (size_t)h->H.pt_end * 3, n = (size_t)d.Np * 3;
+    if (b > 0) CUDA_TRY(cudaMemsetAsync(d.pts, 0, b * 8, h->stream));
+    if (e < n) CUDA_TRY(cudaMemsetAsync(d.pts + e, 0, (n - e) * 8, h->stream));
+    std::string err;
+    if (!h->comm.allreduce(d.pts, n, false, h->stream, &err)) { set_error(err); return SBA_NCCL_ERROR; }
+  }
+  if (poses && d.Nc > 0) CUDA_TRY(cudaMemcpyAsync(poses, d.poses, (size_t)d.Nc * 48, cudaMemcpyDeviceToHost, h->stream));
+  if (points && d.Np > 0) CUDA_TRY(cudaMemcpyAsync(points, d.pts, (size_t)d.Np * 24, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return SBA_OK;
+}
+
+#define NCCL_TRY(call)                                           \
+  do {                                                           \
+    std::string _err;                                            \
+    if (!(call)) { set_error(_err); return SBA_NCCL_ERROR; }     \
+  } while (0)
+
+// K0 + K1 + K2 at the current state (d.poses / d.pts).
+static int do_linearize(sba_handle h) {
+  Dev& d = h->d;
+  const DevParams& P = h->P;
+  LAUNCH(h, k_cam_precompute, cdiv(d.Nc, 128), 128, d.Nc, d.poses, d.campre);
+  LAUNCH(h, k_lin_points, d.npchunk, kThreads, d, P);
+  LAUNCH(h, k_lin_cameras, d.ncchunk, kThreads, d, P);
+  LAUNCH(h, k_cam_finish, cdiv((int64_t)d.Nc * 27, 256), 256, d);
+  if (h->comm.active()) {
+    std::string _err;
+    if (!h->comm.allreduce(d.U, (size_t)d.Nc * 21, false, h->stream, &_err) ||
+        !h->comm.allreduce(d.gc, (size_t)d.Nc * 6, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+  }
+  LAUNCH(h, k_lin_finish, d.nwin, kThreads, d, P);
+  if (h->comm.active()) {
+    std::string _err;
+    if (!h->comm.allreduce(d.w_cost, (size_t)d.nwin, false, h->stream, &_err) ||
+        !h->comm.allreduce(d.w_gmax, (size_t)d.nwin, true, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+  }
+  if (!h->jacobi_done) {
+    LAUNCH(h, k_jacobi_scale, cdiv((int64_t)d.Nc * 6 + (int64_t)d.Np * 3, 256), 256, d);
+    h->jacobi_done = true;
+  }
+  CUDA_TRY(cudaGetLastError());
+  return SBA_OK;
+}
+
+// K3: damped Schur complement at the per-window radii in d.w_radius.
+static int do_schur(sba_handle h) {
+  Dev& d = h->d;
+  LAUNCH(h, k_point_damp, d.npchunk, kThreads, d);
+  LAUNCH(h, k_schur_pairs, d.nschunk, kThreads, d);
+  LAUNCH(h, k_schur_assemble, cdiv((int64_t)d.nbu * 36, 256), 256, d);
+  LAUNCH(h, k_rhs_cameras, d.ncchunk, kThreads, d);
+  LAUNCH(h, k_rhs_finish, cdiv((int64_t)d.Nf * 6, 128), 128, d, h->rsum);
+  if (h->comm.active()) {
+    std::string _err;
+    if (!h->comm.allreduce(d.Su, (size_t)d.nbu * 36, false, h->stream, &_err) ||
+        !h->comm.allreduce(h->rsum, (size_t)d.Nf * 6, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+  }
+  LAUNCH(h, k_cam_prepare, cdiv(d.Nf, 64), 64, d, h->rsum);
+  CUDA_TRY(cudaGetLastError());
+  return SBA_OK;
+}
+
+// K4: block-Jacobi PCG on the reduced camera system of every window (replicated on all ranks after
+// the all-reduce of S).  The host reads one control counter every `kPcgCheck` iterations.
+static constexpr int kPcgCheck = 4;
+static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
+  Dev& d = h->d;
+  const DevParams& P = h->P;
+  int it = 0;
+  if (d.Nf > 0) {
+    const int gf = cdiv(d.Nf, 128), gs = cdiv((int64_t)d.Nf * 6, 128);
+    CUDA_TRY(cudaMemsetAsync(d.counters + 1, 0, 4, h->stream));
+    LAUNCH(h, k_pcg_init, gf, 128, d);
+    LAUNCH(h, k_pcg_dot, d.nwin, kThreads, d, P, d.r, d.z, 0, opt->max_pcg_iterations);
+    CUDA_TRY(cudaMemcpyAsync(h->h_counters + 1, d.counters + 1, 4, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    int active = h->h_counters[1];
+    while (active > 0 && it < opt->max_pcg_iterations) {
+      const int n = std::min(kPcgCheck, opt->max_pcg_iterations - it);
+      for (int k = 0; k < n; ++k) {
+        LAUNCH(h, k_pcg_matvec, gs, 128, d);
+        LAUNCH(h, k_pcg_dot, d.nwin, kThreads, d, P, d.p, d.Ap, 1, opt->max_pcg_iterations);
+        LAUNCH(h, k_pcg_update_xr, gf, 128, d);
+        if (k == n - 1) CUDA_TRY(cudaMemsetAsync(d.counters + 1, 0, 4, h->stream));
+        LAUNCH(h, k_pcg_dot, d.nwin, kThreads, d, P, d.r, d.z, 2, opt->max_pcg_iterations);
+        LAUNCH(h, k_pcg_update_p, gs, 128, d);
+      }
+      it += n;
+      CUDA_TRY(cudaMemcpyAsync(h->h_counters + 1, d.counters + 1, 4, cudaMemcpyDeviceToHost, h->stream));
+      CUDA_TRY(cudaStreamSynchronize(h->stream));
+      active = h->h_counters[1];
+    }
+  }
+  CUDA_TRY(cudaGetLastError());
+  if (iters_out) *iters_out = it;
+  return SBA_OK;
+}
+
+// K5 + K6 + trust-region control: candidate state, its cost, accept / reject per window.
+static int do_step(sba_handle h) {
+  Dev& d = h->d;
+  const DevParams& P = h->P;
+  LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P);
+  LAUNCH(h, k_cam_step, d.nwin, kThreads, d, (int)(h->comm.active() ? h->comm.rank : 0));
+  LAUNCH(h, k_cam_precompute, cdiv(d.Nc, 128), 128, d.Nc, d.poses_new, d.campre_new);
+  LAUNCH(h, k_cost_points, d.npchunk, kThreads, d, P);
+  LAUNCH(h, k_cost_finish, d.nwin, kThreads, d);
+  if (h->comm.active()) {
+    std::string _err;   // w_gd, w_dDd, w_step2, w_x2, w_dr, w_cand are one contiguous block
+    if (!h->comm.allreduce(d.w_gd, (size_t)d.nwin * 6, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+  }
+  CUDA_TRY(cudaMemsetAsync(d.counters, 0, 4, h->stream));
+  CUDA_TRY(cudaMemsetAsync(d.counters + 2, 0, 4, h->stream));
+  LAUNCH(h, k_lm_control, cdiv(d.nwin, 128), 128, d, P);
+  LAUNCH(h, k_apply_points, d.npchunk, kThreads, d);
+  LAUNCH(h, k_apply_cams, cdiv((int64_t)d.Nc * 6, 256), 256, d);
+  CUDA_TRY(cudaGetLastError());
+  return SBA_OK;
+}
+
+int sba_linearize(sba_handle h, const sba_options* opt) {
+  int rc = check_ready(h, true);
+  if (rc) return rc;
+  sba_options o; if (opt) o = *opt; else sba_default_options(&o);
+  CUDA_TRY(cudaSetDevice(h->device));
+  fill_params(h, &o);
+  if ((rc = do_linearize(h))) return rc;
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return SBA_OK;
+}
+
+static int set_radius(sba_handle h, double radius) {
+  std::vector<double> r((size_t)h->d.nwin, radius);
+  CUDA_TRY(cudaMemcpyAsync(h->d.w_radius, r.data(), r.size() * 8, cudaMemcpyHostToDevice, h->stream));
+  CUDA_TRY(cudaMemsetAsync(h->d.w_status, 0, (size_t)h->d.nwin * 4, h->stream));
+  CUDA_TRY(cudaMemsetAsync(h->d.w_fail, 0, (size_t)h->d.nwin * 4, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));   // r is a host temporary
+  h->last_radius = radius;
+  return SBA_OK;
+}
+
+int sba_schur(sba_handle h, const sba_options* opt, double radius) {
+  int rc = check_ready(h, true);
+  if (rc) return rc;
+  if (!h->jacobi_done) { set_error("sba_schur needs a linearisation (sba_linearize)"); return SBA_INVALID_ARGUMENT; }
+  if (!(radius > 0.0)) { set_error("radius must be positive"); return SBA_INVALID_ARGUMENT; }
+  sba_options o; if (opt) o = *opt; else sba_default_options(&o);
+  CUDA_TRY(cudaSetDevice(h->device));
+  fill_params(h, &o);
+  if ((rc = set_radius(h, radius))) return rc;
+  if ((rc = do_schur(h))) return rc;
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return SBA_OK;
+}
+
+int sba_pcg(sba_handle h, const sba_options* opt, int32_t* iterations) {
+  int rc = check_ready(h, true);
+  if (rc) return rc;
+  sba_options o; if (opt) o = *opt; else sba_default_options(&o);
+  CUDA_TRY(cudaSetDevice(h->device));
+  fill_params(h, &o);
+  if ((rc = do_pcg(h, &o, iterations))) return rc;
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return SBA_OK;
+}
+
+int sba_time_linearize_schur(sba_handle h, const sba_options* opt, double radius, int32_t repeats,
+                             double* ms_linearize, double* ms_schur) {
+  int rc = check_ready(h, true);
+  if (rc) return rc;
+  if (repeats < 1) repeats = 1;
+  sba_options o; if (opt) o = *opt; else sba_default_options(&o);
+  CUDA_TRY(cudaSetDevice(h->device));
+  fill_params(h, &o);
+  if ((rc = do_linearize(h))) return rc;           // makes sure the Jacobi scaling exists
+  if ((rc = set_radius(h, radius))) return rc;
+  float ml = 0.f, ms = 0.f;
+  for (int i = 0; i < repeats; ++i) {
+    CUDA_TRY(cudaEventRecord(h->ev[0], h->stream));
+    if ((rc = do_linearize(h))) return rc;
+    CUDA_TRY(cudaEventRecord(h->ev[1], h->stream));
+    if ((rc = do_schur(h))) return rc;
+    CUDA_TRY(cudaEventRecord(h->ev[2], h->stream));
+    CUDA_TRY(cudaEventSynchronize(h->ev[2]));
+    float a = 0.f, b = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&a, h->ev[0], h->ev[1]));
+    CUDA_TRY(cudaEventElapsedTime(&b, h->ev[1], h->ev[2]));
+    ml += a; ms += b;
+  }
+  if (ms_linearize) *ms_linearize = ml / repeats;
+  if (ms_schur) *ms_schur = ms / repeats;
+  return SBA_OK;
+}
+
+int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
+  int rc = check_ready(h, true);
+  if (rc) return rc;
+  sba_options o; if (opt) o = *opt; else sba_default_options(&o);
+  if (o.max_iterations < 0 || !(o.huber_delta > 0.0) || !(o.initial_radius > 0.0) ||
+      !(o.point_lower_bound <= o.point_upper_bound)) { set_error("bad options"); return SBA_INVALID_ARGUMENT; }
+  using clk = std::chrono::steady_clock;
+  const auto t0 = clk::now();
+  auto secs = [&](clk::time_point a) { return std::chrono::duration<double>(clk::now() - a).count(); };
+  CUDA_TRY(cudaSetDevice(h->device));
+  fill_params(h, &o);
+  Dev& d = h->d;
+  const DevParams& P = h->P;
+  sba_summary S; std::memset(&S, 0, sizeof(S));
+  const int64_t launches0 = h->launches;
+
+  // iteration 0 (Ceres): project onto the bounds, evaluate, fix the Jacobi scaling, gradient test
+  LAUNCH(h, k_project_points, cdiv((int64_t)d.Np * 3, 256), 256, (int64_t)d.Np * 3, d.pts, P.lo, P.hi);
+  h->jacobi_done = false;
+  CUDA_TRY(cudaEventRecord(h->ev[4], h->stream));
+  if ((rc = do_linearize(h))) return rc;
+  LAUNCH(h, k_lm_begin, cdiv(d.nwin, 128), 128, d, P, o.initial_radius, 1);
+  CUDA_TRY(cudaEventRecord(h->ev[5], h->stream));
+  S.linearizations = 1;
+  std::vector<double> wcost((size_t)d.nwin);
+  CUDA_TRY(cudaMemcpyAsync(wcost.data(), d.w_cost, wcost.size() * 8, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  for (double c : wcost) S.initial_cost += c;
+  bool lin_pending = true;
+  auto take_lin_time = [&]() {
+    if (!lin_pending) return;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, h->ev[4], h->ev[5]) == cudaSuccess) S.ms_linearize += ms;
+    lin_pending = false;
+  };
+  take_lin_time();
+
+  int running = d.nwin;
+  for (int iter = 0; running > 0 && iter < o.max_iterations; ++iter) {
+    if (o.max_time_s > 0.0 && secs(t0) >= o.max_time_s) {
+      LAUNCH(h, k_lm_timeout, cdiv(d.nwin, 128), 128, d);
+      break;
+    }
+    CUDA_TRY(cudaEventRecord(h->ev[0], h->stream));
+    if ((rc = do_schur(h))) return rc;
+    CUDA_TRY(cudaEventRecord(h->ev[1], h->stream));
+    int32_t pit = 0;
+    if ((rc = do_pcg(h, &o, &pit))) return rc;
+    S.pcg_iterations += pit;
+    CUDA_TRY(cudaEventRecord(h->ev[2], h->stream));
+    if ((rc = do_step(h))) return rc;
+    CUDA_TRY(cudaEventRecord(h->ev[3], h->stream));
+    CUDA_TRY(cudaMemcpyAsync(h->h_counters, d.counters, 16, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    take_lin_time();
+    float a = 0.f, b = 0.f, c = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&a, h->ev[0], h->ev[1]));
+    CUDA_TRY(cudaEventElapsedTime(&b, h->ev[1], h->ev[2]));
+    CUDA_TRY(cudaEventElapsedTime(&c, h->ev[2], h->ev[3]));
+    S.ms_schur += a; S.ms_pcg += b; S.ms_update += c;
+    running = h->h_counters[0];
+    const int accepted = h->h_counters[2];
+    if (accepted > 0) {
+      CUDA_TRY(cudaEventRecord(h->ev[4], h->stream));
+      if ((rc = do_linearize(h))) return rc;
+      LAUNCH(h, k_lm_begin, cdiv(d.nwin, 128), 128, d, P, o.initial_radius, 0);
+      CUDA_TRY(cudaEventRecord(h->ev[5], h->stream));
+      lin_pending = true;
+      S.linearizations++;
+    } else {
+      CUDA_TRY(cudaMemsetAsync(d.w_fail, 0, (size_t)d.nwin * 4, h->stream));
+    }
+    if (o.verbose) {
+      CUDA_TRY(cudaMemcpyAsync(wcost.data(), d.w_cost, 8, cudaMemcpyDeviceToHost, h->stream));
+      CUDA_TRY(cudaStreamSynchronize(h->stream));
+      std::printf("[sba] it %d  cost(w0) %.12e  running %d  accepted %d  pcg %d\n", iter + 1, wcost[0], running, accepted, pit);
+    }
+  }
+  // windows still running here hit the iteration limit
+  std::vector<int32_t> st((size_t)d.nwin), its((size_t)d.nwin), succ((size_t)d.nwin);
+  CUDA_TRY(cudaMemcpyAsync(st.data(), d.w_status, st.size() * 4, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaMemcpyAsync(its.data(), d.w_iter, its.size() * 4, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaMemcpyAsync(succ.data(), d.w_succ, succ.size() * 4, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaMemcpyAsync(wcost.data(), d.w_cost, wcost.size() * 8, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  take_lin_time();
+  bool any_fail = false, any_limit = false;
+  for (int w = 0; w < d.nwin; ++w) {
+    int s = st[w];
+    if (s == 0) s = SBA_TERM_MAX_ITERATIONS;
+    if (w == 0) S.termination = s;
+    S.final_cost += wcost[w];
+    S.iterations = std::max(S.iterations, its[w]);
+    S.successful_steps += succ[w];
+    if (s == SBA_TERM_INVALID_STEPS || s < 0) any_fail = true;
+    else if (s == SBA_TERM_MAX_ITERATIONS || s == SBA_TERM_MAX_TIME) any_limit = true;
+    else S.num_windows_converged++;
+  }
+  S.time_structure_s = h->time_structure_s;
+  S.time_solve_s = secs(t0);
+  S.time_total_s = S.time_solve_s;
+  (void)launches0;
+  if (sum) *sum = S;
+  if (any_fail) { set_error("numerical failure (invalid steps / non-finite cost) in at least one window"); return SBA_NUMERICAL_FAILURE; }
+  return any_limit ? SBA_NO_CONVERGENCE : SBA_OK;
+}
+
+int sba_solve(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, double* poses, double* points,
+              const int32_t* obs_cam, const int32_t* obs_pt, const float* obs_uv, const double* p_l,
+              const double* p_r, const uint8_t* cam_fixed, int32_t nwin, const int32_t* win_cam_off,
+              const int32_t* win_pt_off, const sba_options* opt, sba_summary* sum) {
+  if (!h) { set_error("null handle"); return SBA_INVALID_ARGUMENT; }
+  if (h->device < 0) { set_error("host-only handle: no CUDA device bound (there is no CPU fallback)"); return SBA_CUDA_ERROR; }
+  using clk = std::chrono::steady_clock;
+  const auto t0 = clk::now();
+  auto secs = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double>(b - a).count(); };
+  int rc = sba_set_structure(h, Nc, Np, Nobs, obs_cam, obs_pt, cam_fixed, nwin, win_cam_off, win_pt_off);
+  if (rc) return rc;
+  const auto t1 = clk::now();
+  if ((rc = sba_set_state(h, poses, points))) return rc;
+  if ((rc = sba_set_measurements(h, obs_uv, p_l, p_r))) return rc;
+  const auto t2 = clk::now();
+  sba_summary S;
+  const int run_rc = sba_run(h, opt, &S);
+  if (run_rc != SBA_OK && run_rc != SBA_NO_CONVERGENCE) return run_rc;   // inputs untouched
+  const auto t3 = clk::now();
+  if ((rc = sba_get_state(h, poses, points))) return rc;
+  const auto t4 = clk::now();
+  S.time_structure_s = secs(t0, t1); S.time_h2d_s = secs(t1, t2); S.time_d2h_s = secs(t3, t4);
+  S.time_total_s = secs(t0, t4);
+  if (sum) *sum = S;
+  return run_rc;
+}
+
+// ---- introspection --------------------------------------------------------------------------------
+extern "C++" {
+template <typename T>
+static int d2h(sba_handle h, std::vector<T>& dst, const T* src, size_t n) {
+  dst.resize(n);
+  if (n) CUDA_TRY(cudaMemcpyAsync(dst.data(), src, n * sizeof(T), cudaMemcpyDeviceToHost, h->stream));
+  return SBA_OK;
+}
+}
+
+int sba_get_linearization(sba_handle h, double* r, double* U, double* V, double* W, double* gc,
+                          double* gp, double* cost) {
+  int rc = check_ready(h, true);
+  if (rc) return rc;
+  CUDA_TRY(cudaSetDevice(h->device));
+  Dev& d = h->d;
+  const HostStructure& H = h->H;
+  if (r) {   // corrected residuals are not kept by the hot path: re-run the linearisation with the debug sink
+    if (!h->r_dbg) { if ((rc = h->alloc(&h->r_dbg, (size_t)h->nobs_all * 4))) return rc; }
+    CUDA_TRY(cudaMemsetAsync(h->r_dbg, 0, std::max<size_t>(1, (size_t)h->nobs_all * 4) * 8, h->stream));
+    d.r_dbg = h->r_dbg;
+    rc = do_linearize(h);
+    d.r_dbg = nullptr;
+    if (rc) return rc;
+    if (h->nobs_all) CUDA_TRY(cudaMemcpyAsync(r, h->r_dbg, (size_t)h->nobs_all * 32, cudaMemcpyDeviceToHost, h->stream));
+  }
+  std::vector<double> hU, hV, hW;
+  if (U) { if ((rc = d2h(h, hU, d.U, (size_t)d.Nc * 21))) return rc; }
+  if (V) { if ((rc = d2h(h, hV, d.V, (size_t)d.Np * 6))) return rc; }
+  if (W) { if ((rc = d2h(h, hW, d.W, (size_t)d.Nobs * 18))) return rc; }
+  if (gc && d.Nc) CUDA_TRY(cudaMemcpyAsync(gc, d.gc, (size_t)d.Nc * 48, cudaMemcpyDeviceToHost, h->stream));
+  if (gp && d.Np) CUDA_TRY(cudaMemcpyAsync(gp, d.gp, (size_t)d.Np * 24, cudaMemcpyDeviceToHost, h->stream));
+  if (cost) CUDA_TRY(cudaMemcpyAsync(cost, d.w_cost, (size_t)d.nwin * 8, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  if (U)
+    for (int c = 0; c < d.Nc; ++c)
+      for (int i = 0; i < 6; ++i)
+        for (int j = 0; j < 6; ++j) U[(size_t)c * 36 + 6 * i + j] = hU[(size_t)c * 21 + (i <= j ? up6(i, j) : up6(j, i))];
+  if (V)
+    for (int p = 0; p < d.Np; ++p) {
+      const double* s = &hV[(size_t)p * 6];
+      double* o = V + (size_t)p * 9;
+      o[0] = s[0]; o[1] = s[1]; o[2] = s[2]; o[3] = s[1]; o[4] = s[3]; o[5] = s[4]; o[6] = s[2]; o[7] = s[4]; o[8] = s[5];
+    }
+  if (W) {
+    std::memset(W, 0, (size_t)h->nobs_all * 18 * 8);   // observations of unowned points (multi-GPU) stay zero
+    for (int64_t e = 0; e < d.Nobs; ++e) std::memcpy(W + (size_t)H.perm_p[e] * 18, &hW[(size_t)e * 18], 18 * 8);
+  }
+  return SBA_OK;
+}
+
+int64_t sba_get_schur_pattern(sba_handle h, int32_t* rows, int32_t* cols, int64_t capacity) {
+  if (!h || !h->has_structure) return -1;
+  const HostStructure& H = h->H;
+  const int64_t n = H.row_ptr.empty() ? 0 : H.row_ptr[H.Nf];
+  if (rows && cols) {
+    // row entries are stored lower part first then upper part, each ascending in column: already sorted
+    int64_t k = 0;
+    for (int f = 0; f < H.Nf; ++f)
+      for (int j = H.row_ptr[f]; j < H.row_ptr[f + 1] && k < capacity; ++j, ++k) { rows[k] = f; cols[k] = H.bsr_col[j]; }
+  }
+  return n;
+}
+
+int sba_get_schur_values(sba_handle h, double* blocks, double* rhs, double* solution) {
+  int rc = check_ready(h, true);
+  if (rc) return rc;
+  CUDA_TRY(cudaSetDevice(h->device));
+  const Dev& d = h->d;
+  const HostStructure& H = h->H;
+  std::vector<double> Su;
+  if (blocks) { if ((rc = d2h(h, Su, d.Su, (size_t)d.nbu * 36))) return rc; }
+  if (rhs && d.Nf) CUDA_TRY(cudaMemcpyAsync(rhs, d.rhs, (size_t)d.Nf * 48, cudaMemcpyDeviceToHost, h->stream));
+  if (solution && d.Nf) CUDA_TRY(cudaMemcpyAsync(solution, d.x, (size_t)d.Nf * 48, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  if (blocks) {
+    const int64_t n = H.row_ptr[H.Nf];
+    for (int64_t k = 0; k < n; ++k) {
+      const int32_t bi = H.bsr_blk[k];
+      double* o = blocks + (size_t)k * 36;
+      if (bi >= 0) std::memcpy(o, &Su[(size_t)bi * 36], 36 * 8);
+      else {
+        const double* s = &Su[(size_t)(~bi) * 36];
+        for (int i = 0; i < 6; ++i) for (int j = 0; j < 6; ++j) o[6 * i + j] = s[6 * j + i];
+      }
+    }
+  }
+  return SBA_OK;
+}
+
+int sba_get_sorted_views(sba_handle h, int32_t* by_point, int32_t* by_camera) {
+  if (!h || !h->has_structure) { set_error("no structure"); return SBA_INVALID_ARGUMENT; }
+  const HostStructure& H = h->H;
+  if (by_point) std::memcpy(by_point, H.perm_p.data(), (size_t)H.Nobs * 4);
+  if (by_camera) for (int64_t i = 0; i < H.Nobs; ++i) by_camera[i] = H.perm_p[H.cpos[i]];
+  return SBA_OK;
+}
+
+int32_t sba_num_free_cameras(sba_handle h) { return (h && h->has_structure) ? h->H.Nf : -1; }
+int64_t sba_launch_count(sba_handle h) { return h ? h->launches : -1; }
+
+// ---- multi-GPU --------------------------------------------------------------------------------------
+int sba_comm_unique_id(uint8_t id[128]) {
+  std::string err;
+  if (!nccl_api().load(&err)) { set_error(err); return SBA_NCCL_ERROR; }
+  ncclUniqueId uid;
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+  if (nccl_api().GetUniqueId(&uid) != ncclSuccess) { set_error("ncclGetUniqueId failed"); return SBA_NCCL_ERROR; }
+  std::memcpy(id, &uid, 128);
+  return SBA_OK;
+}
+
+int sba_comm_init(sba_handle h, int32_t rank, int32_t world_size, const uint8_t id[128]) {
+  if (!h || h->device < 0 || world_size < 1 || rank < 0 || rank >= world_size) { set_error("bad comm arguments"); return SBA_INVALID_ARGUMENT; }
+  std::string err;
+  if (!nccl_api().load(&err)) { set_error(err); return SBA_NCCL_ERROR; }
+  CUDA_TRY(cudaSetDevice(h->device));
+  h->comm.destroy();
+  ncclUniqueId uid; std::memcpy(&uid, id, 128);
+  ncclComm_t c = nullptr;
+  const ncclResult_t r = nccl_api().CommInitRank(&c, world_size, uid, rank);
+  if (r != ncclSuccess) { set_error(std::string("ncclCommInitRank: ") + (nccl_api().GetErrorString ? nccl_api().GetErrorString(r) : "error")); return SBA_NCCL_ERROR; }
+  h->comm.comm = c; h->comm.rank = rank; h->comm.world = world_size;
+  return SBA_OK;
+}
+
+}  // extern "C"

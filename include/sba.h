@@ -137,6 +137,15 @@ int sba_pcg(sba_handle h, const sba_options* opt, int32_t* iterations);
 int sba_time_linearize_schur(sba_handle h, const sba_options* opt, double radius, int32_t repeats,
                              double* ms_linearize, double* ms_schur);
 
+/* Time one stage in isolation (bench.py's roofline leg): `repeats` launches, each timed with CUDA
+ * events on the handle's stream; flush_l2 != 0 overwrites a 256 MiB scratch buffer between launches
+ * so every launch starts from a cold L2.  Stages: 0 k_lin_points (K1/K2 by point, the dominant
+ * kernel) 1 k_lin_cameras 2 k_schur_pairs 3 whole linearisation 4 whole Schur step
+ * 5 k_backsub 6 k_cost_points 7 one PCG iteration.  Needs a prior sba_linearize (and sba_schur for
+ * stages 5-7).  *ms = mean device milliseconds per launch. */
+int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t stage, int32_t repeats,
+                   int32_t flush_l2, double* ms);
+
 /* Introspection, all host output buffers, any may be NULL.  Orders are the caller's own:
  *   r [Nobs*4] corrected residuals in input observation order; W [Nobs*18] (6x3 row-major) likewise;
  *   U [Nc*36] full symmetric 6x6; V [Np*9]; gc [Nc*6]; gp [Np*3]; cost [num_windows]. */
@@ -176,6 +185,11 @@ int sba_unpack_window(float* T_wc, float* map_points, int32_t start, int32_t end
 /* MatrixToPose / PoseToMatrix (src/math_utils.h:12-41), float arithmetic like the reference. */
 void sba_matrix_to_pose(const float* T16, double* pose6);
 void sba_pose_to_matrix(const double* pose6, float* T16);
+/* float 4x4 helpers the Frame::GlobalPose setter needs (src/camera_frame.h:32-49): general inverse
+ * (Matrix4f::inverse), Normalize (src/math_utils.h:6-10), product out = A*B.  Row-major. */
+int sba_invert_pose(const float* T16, float* out16);
+void sba_normalize_pose(float* T16);
+void sba_compose_pose(const float* A16, const float* B16, float* out16);
 
 #ifdef __cplusplus
 }

@@ -142,6 +142,19 @@ void sba_pose_to_matrix(const double* pose, float* T) {
   T[3] = (float)pose[3]; T[7] = (float)pose[4]; T[11] = (float)pose[5];
 }
 
+int sba_invert_pose(const float* T, float* out) { return inverse4(T, out) ? SBA_OK : SBA_NUMERICAL_FAILURE; }
+void sba_normalize_pose(float* T) { normalize_pose(T); }
+void sba_compose_pose(const float* A, const float* B, float* out) {
+  float tmp[16];
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) {
+      float s = 0.0f;
+      for (int k = 0; k < 4; ++k) s += A[4 * i + k] * B[4 * k + j];
+      tmp[4 * i + j] = s;
+    }
+  std::memcpy(out, tmp, 64);
+}
+
 int sba_pack_window(const float* T_wc, const float* map_points, const int64_t* frame_off,
                     const uint32_t* obs_point_id, const float* obs_uv_in, int32_t start, int32_t end,
                     double* poses, double* points, uint32_t* point_ids, int32_t* obs_cam,

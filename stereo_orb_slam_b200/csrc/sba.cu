@@ -49,6 +49,7 @@ struct sba_handle_s {
   float4* uv_in = nullptr;            // staging for the caller-ordered observations
   double* rsum = nullptr;
   double* r_dbg = nullptr;
+  unsigned char* flush = nullptr;     // 256 MiB L2-flush scratch (sba_time_stage)
   int32_t* h_counters = nullptr;      // pinned
   int64_t launches = 0;
   int64_t nobs_all = 0;
@@ -82,7 +83,7 @@ struct sba_handle_s {
   void free_all() {
     for (void* p : allocs) cudaFree(p);
     allocs.clear();
-    uv_in = nullptr; rsum = nullptr; r_dbg = nullptr;
+    uv_in = nullptr; rsum = nullptr; r_dbg = nullptr; flush = nullptr;
     d = Dev{};
   }
 };
@@ -474,6 +475,59 @@ int sba_time_linearize_schur(sba_handle h, const sba_options* opt, double radius
   }
   if (ms_linearize) *ms_linearize = ml / repeats;
   if (ms_schur) *ms_schur = ms / repeats;
+  return SBA_OK;
+}
+
+int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t stage, int32_t repeats,
+                   int32_t flush_l2, double* ms_out) {
+  int rc = check_ready(h, true);
+  if (rc) return rc;
+  if (!h->jacobi_done) { set_error("sba_time_stage needs a linearisation (sba_linearize)"); return SBA_INVALID_ARGUMENT; }
+  if (stage < 0 || stage > 7) { set_error("unknown stage"); return SBA_INVALID_ARGUMENT; }
+  if (repeats < 1) repeats = 1;
+  sba_options o; if (opt) o = *opt; else sba_default_options(&o);
+  CUDA_TRY(cudaSetDevice(h->device));
+  fill_params(h, &o);
+  if (radius > 0.0 && (rc = set_radius(h, radius))) return rc;
+  Dev& d = h->d;
+  const DevParams& P = h->P;
+  const size_t flush_bytes = (size_t)256 << 20;
+  if (flush_l2 && !h->flush) { if ((rc = h->alloc(&h->flush, flush_bytes))) return rc; }
+  double total = 0.0;
+  for (int i = 0; i < repeats; ++i) {
+    if (flush_l2) CUDA_TRY(cudaMemsetAsync(h->flush, i & 0xff, flush_bytes, h->stream));
+    CUDA_TRY(cudaEventRecord(h->ev[6], h->stream));
+    switch (stage) {
+      case 0: LAUNCH(h, k_lin_points, d.npchunk, kThreads, d, P); break;
+      case 1: LAUNCH(h, k_lin_cameras, d.ncchunk, kThreads, d, P); break;
+      case 2: LAUNCH(h, k_schur_pairs, d.nschunk, kThreads, d); break;
+      case 3: if ((rc = do_linearize(h))) return rc; break;
+      case 4: if ((rc = do_schur(h))) return rc; break;
+      case 5: LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P); break;
+      case 6:
+        LAUNCH(h, k_cam_precompute, cdiv(d.Nc, 128), 128, d.Nc, d.poses, d.campre_new);
+        CUDA_TRY(cudaMemcpyAsync(d.pts_new, d.pts, std::max<size_t>(1, (size_t)d.Np * 3) * 8, cudaMemcpyDeviceToDevice, h->stream));
+        CUDA_TRY(cudaEventRecord(h->ev[6], h->stream));   // time the cost kernel alone
+        LAUNCH(h, k_cost_points, d.npchunk, kThreads, d, P);
+        break;
+      case 7: {
+        const int gf = cdiv(d.Nf, 128), gs = cdiv((int64_t)d.Nf * 6, 128);
+        LAUNCH(h, k_pcg_matvec, gs, 128, d);
+        LAUNCH(h, k_pcg_dot, d.nwin, kThreads, d, P, d.p, d.Ap, 1, 1 << 30);
+        LAUNCH(h, k_pcg_update_xr, gf, 128, d);
+        LAUNCH(h, k_pcg_dot, d.nwin, kThreads, d, P, d.r, d.z, 2, 1 << 30);
+        LAUNCH(h, k_pcg_update_p, gs, 128, d);
+        break;
+      }
+    }
+    CUDA_TRY(cudaEventRecord(h->ev[7], h->stream));
+    CUDA_TRY(cudaEventSynchronize(h->ev[7]));
+    float a = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&a, h->ev[6], h->ev[7]));
+    total += a;
+  }
+  CUDA_TRY(cudaGetLastError());
+  if (ms_out) *ms_out = total / repeats;
   return SBA_OK;
 }
 

@@ -81,6 +81,9 @@ def lib():
         L.sba_compose_pose.restype = None
         L.sba_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
         L.sba_destroy.argtypes = [C.c_void_p]
+        L.sba_get_schur_pattern.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int64]
+        L.sba_num_free_cameras.argtypes = [C.c_void_p]
+        L.sba_launch_count.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 

@@ -483,7 +483,7 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
   int rc = check_ready(h, true);
   if (rc) return rc;
   if (!h->jacobi_done) { set_error("sba_time_stage needs a linearisation (sba_linearize)"); return SBA_INVALID_ARGUMENT; }
-  if (stage < 0 || stage > 7) { set_error("unknown stage"); return SBA_INVALID_ARGUMENT; }
+  if (stage < 0 || stage > 8) { set_error("unknown stage"); return SBA_INVALID_ARGUMENT; }
   if (repeats < 1) repeats = 1;
   sba_options o; if (opt) o = *opt; else sba_default_options(&o);
   CUDA_TRY(cudaSetDevice(h->device));
@@ -503,6 +503,7 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
       case 2: LAUNCH(h, k_schur_pairs, d.nschunk, kThreads, d); break;
       case 3: if ((rc = do_linearize(h))) return rc; break;
       case 4: if ((rc = do_schur(h))) return rc; break;
+      case 8: if ((rc = do_linearize(h))) return rc; if ((rc = do_schur(h))) return rc; break;
       case 5: LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P); break;
       case 6:
         LAUNCH(h, k_cam_precompute, cdiv(d.Nc, 128), 128, d.Nc, d.poses, d.campre_new);

@@ -1,0 +1,58 @@
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    # build the oracle (checker) and the emulation helper when missing; libsba.so is built by
+    # __graft_entry__.build() and travels prebuilt to the GPU box.
+    lib = os.path.join(ROOT, "stereo_orb_slam_b200", "lib", "libsba.so")
+    orc = os.path.join(ROOT, "oracle", "_build", "libsba_oracle.so")
+    if not os.path.exists(lib) or not os.path.exists(orc):
+        import __graft_entry__ as g
+        g.build()
+
+
+@pytest.fixture(scope="session")
+def kitti():
+    from stereo_orb_slam_b200 import synthetic
+    return synthetic.projection_matrices()
+
+
+def make_window(num_frames, num_points, track_len, seed, **kw):
+    """Synthetic map packed as one BA window over all its frames (C-ABI pack)."""
+    from stereo_orb_slam_b200 import pack_window, synthetic
+    smap = synthetic.make_map(num_frames=num_frames, num_points=num_points, track_len=track_len, seed=seed, **kw)
+    w = pack_window(smap, 0, num_frames)
+    w["p_l"], w["p_r"], w["map"] = smap.p_l, smap.p_r, smap
+    fixed = np.zeros(num_frames, np.uint8); fixed[0] = 1
+    w["cam_fixed"] = fixed
+    return w
+
+
+@pytest.fixture(scope="session")
+def small_window():
+    return make_window(8, 600, 5, seed=7)
+
+
+@pytest.fixture(scope="session")
+def emu():
+    """tests/emu: the device formulas of csrc/sba_math.cuh compiled for the host (test-only)."""
+    import ctypes as C
+    out = os.path.join(ROOT, "tests", "emu", "_build", "libemu.so")
+    src = os.path.join(ROOT, "tests", "emu", "emu_math.cpp")
+    if not os.path.exists(out) or os.path.getmtime(out) < os.path.getmtime(src):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.check_call(["/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++", "-O2", "-std=c++17",
+                               "-fPIC", "-shared", "-Wno-unknown-pragmas", "-o", out, src])
+    L = C.CDLL(out)
+    L.emu_obs_cost.restype = C.c_double
+    return L

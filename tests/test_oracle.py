@@ -1,0 +1,127 @@
+"""The oracle against the golden vectors (tests/golden, mpmath 50 digits) and against itself.
+
+Parity is UNPINNED by the reference (it has no tests; Ceres is absent) — these KATs pin the
+residual / Jacobian / Huber arithmetic of reference: src/reprojection_error.h:12-41,
+src/bundle_adjuster.cpp:100 independently of both oracle/ and csrc/.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle
+from conftest import make_window
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+KATS = json.load(open(os.path.join(HERE, "golden", "reprojection_kats.json")))
+
+
+@pytest.mark.parametrize("case", KATS["cases"], ids=[c["name"] for c in KATS["cases"]])
+@pytest.mark.parametrize("mode", [0, 1], ids=["jet", "analytic"])
+def test_residual_jacobian_kat(case, mode):
+    r, Jc, Jp = oracle.residual(case["cam"], case["point"], case["uv"], case["p_l"], case["p_r"], mode)
+    assert np.abs(r - np.array(case["r"])).max() < 1e-11          # pixels
+    # Jet autodiff differentiates Ceres's first-order small-angle branch: exact to O(theta) only
+    tol = 1e-8 if mode == 0 else 1e-12
+    Jc_ref, Jp_ref = np.array(case["Jc"]), np.array(case["Jp"])
+    assert np.abs(Jc - Jc_ref).max() <= tol * np.abs(Jc_ref).max()
+    assert np.abs(Jp - Jp_ref).max() <= 1e-12 * np.abs(Jp_ref).max()
+
+
+@pytest.mark.parametrize("h", KATS["huber"], ids=[str(h["s"]) for h in KATS["huber"]])
+def test_huber_kat(h):
+    rho, sq = oracle.huber(1.0, h["s"])
+    assert abs(rho - h["rho"]) <= 1e-15 * max(1.0, abs(h["rho"]))
+    assert abs(sq - h["sqrt_rho1"]) <= 1e-15
+
+
+def test_device_formulas_match_oracle_blocks(emu, small_window):
+    """csrc/sba_math.cuh (compiled for the host) reproduces the oracle's per-observation blocks."""
+    import ctypes as C
+    w = small_window
+    lin = oracle.linearize(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
+    d = C.c_double
+    P = lambda a, t=d: a.ctypes.data_as(C.POINTER(t))
+    Nc, Np = w["poses"].shape[0], w["points"].shape[0]
+    U = np.zeros((Nc, 6, 6)); V = np.zeros((Np, 3, 3)); gc = np.zeros((Nc, 6)); gp = np.zeros((Np, 3)); cost = 0.0
+    iu = np.triu_indices(6)
+    for k in range(w["obs_cam"].size):
+        c, p = int(w["obs_cam"][k]), int(w["obs_pt"][k])
+        r = np.zeros(4); U21 = np.zeros(21); g6 = np.zeros(6); V6 = np.zeros(6); g3 = np.zeros(3); W = np.zeros(18); co = d(0)
+        pose = np.ascontiguousarray(w["poses"][c]); X = np.ascontiguousarray(w["points"][p]); uv = np.ascontiguousarray(w["obs_uv"][k])
+        emu.emu_observation(P(pose), P(X), P(uv, C.c_float), P(w["p_l"]), P(w["p_r"]), 4, d(1.0), P(r), P(U21), P(g6), P(V6),
+                            P(g3), P(W), C.byref(co))
+        assert np.abs(r - lin["r"][k]).max() < 1e-9
+        assert np.abs(W.reshape(6, 3) - lin["W"][k]).max() <= 1e-9 * max(1.0, np.abs(lin["W"][k]).max())
+        Uf = np.zeros((6, 6)); Uf[iu] = U21; Uf = Uf + np.triu(Uf, 1).T
+        Vf = np.array([[V6[0], V6[1], V6[2]], [V6[1], V6[3], V6[4]], [V6[2], V6[4], V6[5]]])
+        U[c] += Uf; V[p] += Vf; gc[c] += g6; gp[p] += g3; cost += co.value
+    for a, b in ((U, lin["U"]), (V, lin["V"]), (gc, lin["gc"]), (gp, lin["gp"])):
+        assert np.abs(a - b).max() <= 1e-9 * np.abs(b).max()
+    assert abs(cost - lin["cost"]) <= 1e-12 * lin["cost"]
+
+
+def test_oracle_noise_free_recovers_ground_truth():
+    """Known-answer case: exact measurements => the minimum is the ground truth, cost -> ~0
+    (limited by the f32 storage of the pixels)."""
+    w = make_window(6, 300, 4, seed=11, noise_free=True)
+    smap = w["map"]
+    po, xo, s = oracle.solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"],
+                             options=oracle.default_options(max_time_s=0.0, num_threads=2))
+    assert s["termination"] == 0
+    assert s["final_cost"] < 1e-4 * s["initial_cost"] and s["final_cost"] / w["obs_cam"].size < 1e-6
+    # gauge: camera 0 is held at its (exact) initial pose, so the solution is the ground truth itself
+    gt_pts = smap.gt_points[w["point_ids"]]
+    assert np.abs(xo - gt_pts).max() < 2e-2   # metres; far points are weakly constrained by 1e-4 px f32 rounding
+    assert np.median(np.abs(xo - gt_pts)) < 1e-3
+
+
+def test_oracle_minimum_is_solver_independent(small_window):
+    """autodiff and analytic Jacobians, with and without the line search, reach the same minimum."""
+    w = small_window
+    res = []
+    for kw in (dict(), dict(analytic_jacobian=1), dict(line_search=0)):
+        po, xo, s = oracle.solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"],
+                                 options=oracle.default_options(max_time_s=0.0, num_threads=2, **kw))
+        res.append((po, xo, s))
+    for po, xo, s in res[1:]:
+        assert abs(s["final_cost"] - res[0][2]["final_cost"]) <= 1e-7 * res[0][2]["final_cost"]
+        assert np.abs(po - res[0][0]).max() < 1e-5 and np.abs(xo - res[0][1]).max() < 1e-4
+
+
+def test_oracle_vs_numpy_gradient(small_window):
+    """The oracle's gradient (J^T r with the Huber corrector) equals the numerical gradient of
+    E = 1/2 sum rho(||r||^2) evaluated by an independent numpy restatement of the objective."""
+    w = small_window
+    pl, pr = w["p_l"].reshape(3, 4), w["p_r"].reshape(3, 4)
+
+    def objective(poses, pts):
+        th = np.maximum(np.linalg.norm(poses[:, :3], axis=1), 1e-150)[:, None, None]
+        K = np.zeros((poses.shape[0], 3, 3))
+        K[:, 0, 1] = -poses[:, 2]; K[:, 0, 2] = poses[:, 1]; K[:, 1, 0] = poses[:, 2]
+        K[:, 1, 2] = -poses[:, 0]; K[:, 2, 0] = -poses[:, 1]; K[:, 2, 1] = poses[:, 0]
+        R = np.eye(3) + np.sin(th) / th * K + (1 - np.cos(th)) / th ** 2 * (K @ K)
+        c, p = w["obs_cam"], w["obs_pt"]
+        q = np.einsum("kij,kj->ki", R[c], pts[p]) + poses[c, 3:]
+        qh = np.concatenate([q, np.ones((q.shape[0], 1))], axis=1)
+        a, b = qh @ pl.T, qh @ pr.T
+        pred = np.stack([a[:, 0] / a[:, 2], a[:, 1] / a[:, 2], b[:, 0] / b[:, 2], b[:, 1] / b[:, 2]], axis=1)
+        s = ((pred - w["obs_uv"].astype(np.float64)) ** 2).sum(axis=1)
+        return 0.5 * np.where(s <= 1.0, s, 2 * np.sqrt(s) - 1).sum()
+
+    lin = oracle.linearize(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
+    assert abs(objective(w["poses"], w["points"]) - lin["cost"]) <= 1e-10 * lin["cost"]
+    rng = np.random.default_rng(3)
+    for _ in range(6):
+        c, i = int(rng.integers(1, w["poses"].shape[0])), int(rng.integers(0, 6))
+        h = 1e-6
+        pp = w["poses"].copy(); pp[c, i] += h; pm = w["poses"].copy(); pm[c, i] -= h
+        num = (objective(pp, w["points"]) - objective(pm, w["points"])) / (2 * h)
+        assert abs(num - lin["gc"][c, i]) <= 1e-5 * max(1.0, abs(num))
+    for _ in range(6):
+        p, i = int(rng.integers(0, w["points"].shape[0])), int(rng.integers(0, 3))
+        h = 1e-6
+        xp = w["points"].copy(); xp[p, i] += h; xm = w["points"].copy(); xm[p, i] -= h
+        num = (objective(w["poses"], xp) - objective(w["poses"], xm)) / (2 * h)
+        assert abs(num - lin["gp"][p, i]) <= 1e-5 * max(1.0, abs(num))

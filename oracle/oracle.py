@@ -74,6 +74,7 @@ def lib():
         L.oracle_cost.restype = C.c_double
         L.oracle_time_linearize_schur.restype = C.c_double
         L.oracle_num_procs.restype = C.c_int
+        L.oracle_ls_minimize.restype = C.c_double
         _lib = L
     return _lib
 
@@ -120,6 +121,13 @@ def huber(delta, s):
     rho = C.c_double(); sq = C.c_double()
     lib().oracle_huber(C.c_double(delta), C.c_double(s), C.byref(rho), C.byref(sq))
     return rho.value, sq.value
+
+
+def ls_minimize(x, f, g, has_g, xmin, xmax):
+    x, f, g = _f64(x), _f64(f), _f64(g)
+    hg = _i32(has_g)
+    d = C.c_double
+    return lib().oracle_ls_minimize(x.size, _p(x, d), _p(f, d), _p(g, d), _p(hg, C.c_int32), d(xmin), d(xmax))
 
 
 def linearize(poses, points, obs_cam, obs_pt, obs_uv, p_l, p_r, huber_delta=1.0, rdim=4, analytic=0):

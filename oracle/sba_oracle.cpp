@@ -31,6 +31,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <complex>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -484,11 +485,12 @@ bool schur(const Problem& P, const Adjacency& A, const Blocks& B, const std::vec
 
 inline double clampd(double x, double lo, double hi) { return x < lo ? lo : (x > hi ? hi : x); }
 
-// ---- polynomial interpolation for the Armijo line search (ceres/polynomial.cc restated) -------
-// Fit the lowest-degree polynomial through the samples (value at x, optional gradient at x),
-// minimise it on [xmin, xmax].
+// ---- polynomial interpolation for the Armijo line search (ceres/polynomial.cc + line_search.cc restated) ----
+// FunctionSample: value always valid here; gradient = directional derivative along the search direction.
 struct Sample { double x, f, g; bool has_g; };
-double minimize_interpolating(const std::vector<Sample>& s, double xmin, double xmax) {
+
+// FindInterpolatingPolynomial: lowest-degree polynomial through all values / gradients, highest power first.
+bool fit_polynomial(const std::vector<Sample>& s, std::vector<double>* coef) {
   int neq = 0;
   for (auto& a : s) neq += a.has_g ? 2 : 1;
   const int deg = neq - 1;
@@ -502,33 +504,99 @@ double minimize_interpolating(const std::vector<Sample>& s, double xmin, double 
       rhs[row++] = a.g;
     }
   }
-  // Gaussian elimination with partial pivoting
-  std::vector<double> c(rhs);
-  for (int i = 0; i < neq; ++i) {
-    int piv = i;
-    for (int r2 = i + 1; r2 < neq; ++r2) if (std::fabs(M[(size_t)r2 * neq + i]) > std::fabs(M[(size_t)piv * neq + i])) piv = r2;
-    if (piv != i) { for (int j = 0; j < neq; ++j) std::swap(M[(size_t)i * neq + j], M[(size_t)piv * neq + j]); std::swap(c[i], c[piv]); }
-    const double d = M[(size_t)i * neq + i];
-    if (d == 0.0) return 0.5 * (xmin + xmax);
-    for (int r2 = i + 1; r2 < neq; ++r2) {
-      const double f = M[(size_t)r2 * neq + i] / d;
-      for (int j = i; j < neq; ++j) M[(size_t)r2 * neq + j] -= f * M[(size_t)i * neq + j];
-      c[r2] -= f * c[i];
+  // LU with full pivoting (Ceres: lhs.fullPivLu().solve(rhs))
+  std::vector<int> colperm(neq);
+  for (int i = 0; i < neq; ++i) colperm[i] = i;
+  for (int k = 0; k < neq; ++k) {
+    int pr = k, pc = k; double best = -1.0;
+    for (int i = k; i < neq; ++i) for (int j2 = k; j2 < neq; ++j2) { const double v = std::fabs(M[(size_t)i * neq + j2]); if (v > best) { best = v; pr = i; pc = j2; } }
+    if (!(best > 0.0)) return false;
+    if (pr != k) { for (int j2 = 0; j2 < neq; ++j2) std::swap(M[(size_t)k * neq + j2], M[(size_t)pr * neq + j2]); std::swap(rhs[k], rhs[pr]); }
+    if (pc != k) { for (int i = 0; i < neq; ++i) std::swap(M[(size_t)i * neq + k], M[(size_t)i * neq + pc]); std::swap(colperm[k], colperm[pc]); }
+    for (int i = k + 1; i < neq; ++i) {
+      const double f = M[(size_t)i * neq + k] / M[(size_t)k * neq + k];
+      for (int j2 = k; j2 < neq; ++j2) M[(size_t)i * neq + j2] -= f * M[(size_t)k * neq + j2];
+      rhs[i] -= f * rhs[k];
     }
   }
-  for (int i = neq - 1; i >= 0; --i) { double sacc = c[i]; for (int j = i + 1; j < neq; ++j) sacc -= M[(size_t)i * neq + j] * c[j]; c[i] = sacc / M[(size_t)i * neq + i]; }
-  auto eval = [&](double x) { double v = 0; for (int j = 0; j <= deg; ++j) v = v * x + c[j]; return v; };
-  double best_x = xmin, best_v = eval(xmin);
-  if (eval(xmax) < best_v) { best_v = eval(xmax); best_x = xmax; }
-  // stationary points of degree-2 / degree-3 polynomials
-  std::vector<double> roots;
-  if (deg == 2) { if (c[0] != 0) roots.push_back(-c[1] / (2 * c[0])); }
-  else if (deg == 3) {
-    const double a = 3 * c[0], b = 2 * c[1], cc = c[2];
-    if (a == 0) { if (b != 0) roots.push_back(-cc / b); }
-    else { const double disc = b * b - 4 * a * cc; if (disc >= 0) { const double sq = std::sqrt(disc); roots.push_back((-b + sq) / (2 * a)); roots.push_back((-b - sq) / (2 * a)); } }
+  std::vector<double> y(neq);
+  for (int i = neq - 1; i >= 0; --i) { double acc = rhs[i]; for (int j2 = i + 1; j2 < neq; ++j2) acc -= M[(size_t)i * neq + j2] * y[j2]; y[i] = acc / M[(size_t)i * neq + i]; }
+  coef->assign(neq, 0.0);
+  for (int i = 0; i < neq; ++i) (*coef)[colperm[i]] = y[i];
+  return true;
+}
+inline double poly_eval(const std::vector<double>& c, double x) { double v = 0; for (double a : c) v = v * x + a; return v; }
+
+// FindPolynomialRoots: REAL PARTS of all roots (Ceres keeps the real part of every companion-matrix eigenvalue).
+// Degrees 1-2 closed form as in polynomial.cc; higher degrees by Laguerre iteration with deflation (complex).
+void polynomial_root_real_parts(std::vector<double> c, std::vector<double>* out) {
+  out->clear();
+  while (c.size() > 1 && c[0] == 0.0) c.erase(c.begin());
+  const int deg = (int)c.size() - 1;
+  if (deg <= 0) return;
+  if (deg == 1) { out->push_back(-c[1] / c[0]); return; }
+  if (deg == 2) {
+    const double a = c[0], b = c[1], cc = c[2];
+    const double D = b * b - 4 * a * cc, sD = std::sqrt(std::fabs(D));
+    if (D >= 0) {
+      if (b >= 0) { out->push_back((-b - sD) / (2 * a)); out->push_back((2 * cc) / (-b - sD)); }
+      else { out->push_back((2 * cc) / (-b + sD)); out->push_back((-b + sD) / (2 * a)); }
+    } else { out->push_back(-b / (2 * a)); out->push_back(-b / (2 * a)); }
+    return;
   }
-  for (double r0 : roots) if (r0 > xmin && r0 < xmax) { const double v = eval(r0); if (v < best_v) { best_v = v; best_x = r0; } }
+  typedef std::complex<double> cd;
+  std::vector<cd> a(c.begin(), c.end());           // highest power first
+  std::vector<cd> work = a;
+  std::vector<cd> roots;
+  for (int m = deg; m >= 1; --m) {
+    cd x(0.0, 0.0);
+    for (int it = 0; it < 200; ++it) {
+      cd b = work[0], d(0, 0), f(0, 0);
+      for (int j = 1; j <= m; ++j) { f = x * f + d; d = x * d + b; b = x * b + work[j]; }
+      if (std::abs(b) == 0.0) break;
+      const cd g = d / b, g2 = g * g, h = g2 - 2.0 * f / b;
+      const cd sq = std::sqrt(double(m - 1) * (double(m) * h - g2));
+      cd gp = g + sq, gm = g - sq;
+      if (std::abs(gp) < std::abs(gm)) gp = gm;
+      const cd dx = (std::abs(gp) > 0.0) ? double(m) / gp : std::polar(1.0 + std::abs(x), (double)it);
+      const cd x1 = x - dx;
+      if (x == x1) break;
+      x = x1;
+    }
+    // polish on the undeflated polynomial (two Newton steps)
+    for (int it = 0; it < 2; ++it) {
+      cd b = a[0], d(0, 0);
+      for (int j = 1; j <= deg; ++j) { d = x * d + b; b = x * b + a[j]; }
+      if (std::abs(d) > 0.0) x -= b / d;
+    }
+    roots.push_back(x);
+    std::vector<cd> q(m);                             // deflate: synthetic division by (z - x)
+    q[0] = work[0];
+    for (int j = 1; j < m; ++j) q[j] = work[j] + x * q[j - 1];
+    work = q;
+  }
+  for (auto& r : roots) out->push_back(r.real());
+}
+
+// MinimizeInterpolatingPolynomial (MinimizePolynomial): midpoint, both ends, real parts of the derivative's roots.
+double minimize_interpolating(const std::vector<Sample>& s, double xmin, double xmax) {
+  std::vector<double> c;
+  double best_x = 0.5 * (xmin + xmax);
+  if (!fit_polynomial(s, &c)) return best_x;
+  double best_v = poly_eval(c, best_x);
+  const double vmin = poly_eval(c, xmin), vmax = poly_eval(c, xmax);
+  if (vmin < best_v) { best_v = vmin; best_x = xmin; }
+  if (vmax < best_v) { best_v = vmax; best_x = xmax; }
+  const int deg = (int)c.size() - 1;
+  if (deg < 2) return best_x;
+  std::vector<double> dc(deg), roots;
+  for (int j = 0; j < deg; ++j) dc[j] = (deg - j) * c[j];
+  polynomial_root_real_parts(dc, &roots);
+  for (double r0 : roots) {
+    if (!(r0 >= xmin) || !(r0 <= xmax)) continue;
+    const double v = poly_eval(c, r0);
+    if (v < best_v) { best_v = v; best_x = r0; }
+  }
   return best_x;
 }
 
@@ -588,6 +656,13 @@ void oracle_residual(const double* cam, const double* pt, const double* uv, cons
 }
 
 void oracle_huber(double delta, double s, double* rho, double* sqrt_rho1) { huber(delta, s, rho, sqrt_rho1); }
+
+// line-search step selection on explicit samples (tests): returns argmin of the interpolating polynomial
+double oracle_ls_minimize(int n, const double* x, const double* f, const double* g, const int32_t* has_g, double xmin, double xmax) {
+  std::vector<Sample> s;
+  for (int i = 0; i < n; ++i) s.push_back(Sample{x[i], f[i], g[i], has_g[i] != 0});
+  return minimize_interpolating(s, xmin, xmax);
+}
 
 // Linearise: corrected residuals and normal-equation blocks.
 int oracle_linearize(int Nc, int Np, int Nobs, const double* poses, const double* points,
@@ -767,30 +842,59 @@ int oracle_solve(int Nc, int Np, int Nobs, double* poses, double* points, const 
     double step_size = 1.0;
     double ccost = candidate(1.0);
     if (opt->line_search) {
-      // projected Armijo line search along delta (Ceres does this whenever bounds are set;
-      // sufficient decrease 1e-4, contraction in [1e-3, 0.6], <= 20 step-size iterations)
-      double gd = 0.0;
-      for (int c = 0; c < Nc; ++c) if (fc[c] >= 0) for (int i = 0; i < 6; ++i) gd += B.gc[6 * c + i] * dc[6 * c + i];
-      for (size_t i = 0; i < np3; ++i) gd += B.gp[i] * dp[i];
-      std::vector<Sample> hist;
-      Sample s0{0.0, cost, gd, true};
+      // Projected Armijo line search along delta — Ceres runs it after every trust-region step when any
+      // parameter is bounded (TrustRegionMinimizer::DoLineSearch; the reference bounds every point,
+      // src/bundle_adjuster.cpp:104-108).  ArmijoLineSearch, CUBIC interpolation => value AND directional
+      // derivative at every trial point; sufficient_decrease 1e-4, contraction in [1e-3, 0.6],
+      // <= 20 iterations, min step 1e-9 (against the direction's max-norm).  On failure delta is kept whole.
+      double gd = 0.0, dmax = 0.0;
+      for (int c = 0; c < Nc; ++c) if (fc[c] >= 0) for (int i = 0; i < 6; ++i) { gd += B.gc[6 * c + i] * dc[6 * c + i]; dmax = std::max(dmax, std::fabs(dc[6 * c + i])); }
+      for (size_t i = 0; i < np3; ++i) { gd += B.gp[i] * dp[i]; dmax = std::max(dmax, std::fabs(dp[i])); }
+      // cost and directional derivative  d/ds cost(x + s delta)  at the (projected) trial point
+      auto candidate_grad = [&](double step, double* g_out) {
+        for (size_t i = 0; i < nc6; ++i) cposes[i] = poses[i] + step * dc[i];
+        for (size_t i = 0; i < np3; ++i) cpoints[i] = clampd(points[i] + step * dp[i], lo, hi);
+        double f = 0.0, g = 0.0;
+#pragma omp parallel for reduction(+ : f, g) schedule(static)
+        for (int k = 0; k < Nobs; ++k) {
+          double r[4], Jc[24], Jp[12];
+          f += eval_obs(P, cposes.data(), cpoints.data(), k, r, Jc, Jp);
+          const double* a = &dc[6 * (size_t)obs_cam[k]]; const double* b = &dp[3 * (size_t)obs_pt[k]];
+          for (int m = 0; m < 4; ++m) {
+            double jd = 0; for (int i = 0; i < 6; ++i) jd += Jc[m * 6 + i] * a[i]; for (int i = 0; i < 3; ++i) jd += Jp[m * 3 + i] * b[i];
+            g += r[m] * jd;
+          }
+        }
+        *g_out = g;
+        return f;
+      };
+      const Sample s0{0.0, cost, gd, true};
       Sample prev{0.0, 0.0, 0.0, false}; bool have_prev = false;
       Sample cur{1.0, ccost, 0.0, false};
+      bool cur_valid = std::isfinite(ccost);
+      bool success = true;
       int it_ls = 0;
-      while (!(cur.f <= cost + 1e-4 * gd * cur.x) && it_ls < 20) {
-        std::vector<Sample> s; s.push_back(s0);
-        if (have_prev) s.push_back(prev);
-        s.push_back(cur);
+      bool have_grad = false;
+      while (!cur_valid || cur.f > cost + 1e-4 * gd * cur.x) {
+        if (++it_ls >= 20) { success = false; break; }
+        if (cur_valid && !have_grad) { double g; candidate_grad(cur.x, &g); cur.g = g; cur.has_g = std::isfinite(g); have_grad = true; }
+        double nx;
         const double lo_x = cur.x * 1e-3, hi_x = cur.x * 0.6;
-        double nx = std::isfinite(cur.f) ? minimize_interpolating(s, lo_x, hi_x) : cur.x * 0.5;
-        prev = cur; have_prev = true;
-        cur.x = nx; cur.f = candidate(nx);
-        ++it_ls;
-        if (nx < 1e-9) break;
+        if (!cur_valid) nx = std::min(std::max(cur.x * 0.5, lo_x), hi_x);
+        else {
+          std::vector<Sample> sm; sm.push_back(s0); sm.push_back(cur);
+          if (have_prev) sm.push_back(prev);
+          nx = minimize_interpolating(sm, lo_x, hi_x);
+        }
+        if (nx * dmax < 1e-9) { success = false; break; }
+        prev = cur; have_prev = cur_valid;
+        double g;
+        cur.x = nx; cur.f = candidate_grad(nx, &g); cur.g = g;
+        cur_valid = std::isfinite(cur.f) && std::isfinite(g); cur.has_g = cur_valid; have_grad = true;
       }
-      if (cur.f <= cost + 1e-4 * gd * cur.x) { step_size = cur.x; ccost = cur.f; }
-      else { step_size = 1.0; ccost = candidate(1.0); }
-      if (step_size != 1.0) ccost = candidate(step_size);
+      if (success) { step_size = cur.x; ccost = cur.f; }
+      else { step_size = 1.0; }
+      ccost = candidate(step_size);     // leaves cposes / cpoints at the chosen step
     }
     double step_norm2 = 0.0;
     for (int c = 0; c < Nc; ++c) if (fc[c] >= 0) for (int i = 0; i < 6; ++i) { const double d = cposes[6 * c + i] - poses[6 * c + i]; step_norm2 += d * d; }

@@ -8,6 +8,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include "sba_device.cuh"
+#include "sba_linesearch.cuh"
 #include "sba_internal.h"
 
 namespace sba {
@@ -472,14 +473,16 @@ __global__ void k_pcg_update_p(Dev d) {
 }
 
 // ------------------------------------------------------------------------- K5: back-substitution
-// thread per point: dp = -Vinv (gp + sum_obs W_e^T dc[cam(e)]),  candidate = clamp(x + dp)
-// chunk partials: g.dp, dp^T D dp, |candidate - x|^2, |x|^2
+// thread per point: dp = -Vinv (gp + sum_obs W_e^T dc[cam(e)])   (stored; the candidate is formed by the
+// line-search kernels).  chunk partials: g.dp, dp^T D dp, |x|^2, max|dp|
 __global__ void __launch_bounds__(kThreads) k_backsub(Dev d, DevParams P) {
-  __shared__ double sm[4 * 4];
+  __shared__ double sm[4 * 3];
+  __shared__ double smx[4];
   const int chunk = blockIdx.x;
   const int p = d.pchunk_begin[chunk] + threadIdx.x;
   const int w = d.pchunk_win[chunk];
-  double part[4] = {0, 0, 0, 0};
+  double part[3] = {0, 0, 0};
+  double dmax = 0.0;
   if (p < d.pchunk_end[chunk]) {
     const double g0 = d.gp[(size_t)p * 3], g1 = d.gp[(size_t)p * 3 + 1], g2 = d.gp[(size_t)p * 3 + 2];
     double t0 = g0, t1 = g1, t2 = g2;
@@ -506,84 +509,164 @@ __global__ void __launch_bounds__(kThreads) k_backsub(Dev d, DevParams P) {
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
       const double x = d.pts[(size_t)p * 3 + i];
-      const double xn = clampd(x + dp[i], P.lo, P.hi);
-      d.pts_new[(size_t)p * 3 + i] = xn;
+      d.dp[(size_t)p * 3 + i] = dp[i];
       part[0] += g[i] * dp[i];
       part[1] += lm_damp(d.sc2p[(size_t)p * 3 + i], Vd[i], radius) * dp[i] * dp[i];
-      part[2] += (xn - x) * (xn - x);
-      part[3] += x * x;
+      part[2] += x * x;
+      dmax = fmax(dmax, fabs(dp[i]));
     }
   }
-  const double tot = block_sum<4>(part, sm);
-  if (threadIdx.x < 4) d.step_part[(size_t)chunk * 4 + threadIdx.x] = tot;
+  const double tot = block_sum<3>(part, sm);
+  const double mx = block_max1(dmax, smx);
+  if (threadIdx.x < 3) d.step_part[(size_t)chunk * 4 + threadIdx.x] = tot;
+  if (threadIdx.x == 3) d.step_part[(size_t)chunk * 4 + 3] = mx;
 }
 
-// one CTA per window: candidate poses, and the window's step scalars (cameras + point chunk partials)
+// one CTA per window: the step scalars (cameras + point chunk partials) and the line-search start state.
 // (multi-GPU: camera terms are counted on rank 0 only; the scalars are all-reduced afterwards)
 __global__ void __launch_bounds__(kThreads) k_cam_step(Dev d, int rank) {
-  __shared__ double sm[4 * 5];
+  __shared__ double sm[4 * 4];
+  __shared__ double smx[4];
   const int w = blockIdx.x;
-  double part[5] = {0, 0, 0, 0, 0};   // g.d, d D d, |step|^2, |x|^2, dc . r_pcg
+  double part[4] = {0, 0, 0, 0};   // g.d, d D d, |x|^2, dc . r_pcg
+  double dmax = 0.0;
   const double radius = d.w_radius[w];
   for (int c = d.win_cam_off[w] + threadIdx.x; c < d.win_cam_off[w + 1]; c += kThreads) {
     const int f = d.fc[c];
+    if (f < 0) continue;
 #pragma unroll
     for (int i = 0; i < 6; ++i) {
       const double x = d.poses[(size_t)c * 6 + i];
-      double dc = 0.0;
-      if (f >= 0) dc = d.x[(size_t)f * 6 + i];
-      if (f >= 0 && rank == 0) {
+      const double dc = d.x[(size_t)f * 6 + i];
+      dmax = fmax(dmax, fabs(dc));
+      if (rank == 0) {
         part[0] += d.gc[(size_t)c * 6 + i] * dc;
         part[1] += lm_damp(d.sc2c[(size_t)c * 6 + i], d.U[(size_t)c * 21 + up6(i, i)], radius) * dc * dc;
-        part[2] += dc * dc;
-        part[3] += x * x;
-        part[4] += dc * d.r[(size_t)f * 6 + i];
+        part[2] += x * x;
+        part[3] += dc * d.r[(size_t)f * 6 + i];
       }
-      d.poses_new[(size_t)c * 6 + i] = x + dc;
     }
   }
   for (int ch = d.win_pchunk_off[w] + threadIdx.x; ch < d.win_pchunk_off[w + 1]; ch += kThreads) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) part[i] += d.step_part[(size_t)ch * 4 + i];
+    for (int i = 0; i < 3; ++i) part[i] += d.step_part[(size_t)ch * 4 + i];
+    dmax = fmax(dmax, d.step_part[(size_t)ch * 4 + 3]);
   }
-  double tot = block_sum<5>(part, sm);
+  double tot = block_sum<4>(part, sm);
+  const double mx = block_max1(dmax, smx);
   if (threadIdx.x == 0 && d.w_fail[w] != 0) tot = nan("");   // poison the model change: invalid step on every rank
-  if (threadIdx.x == 0) d.w_gd[w] = tot;
+  if (threadIdx.x == 0) {
+    d.w_gd[w] = tot;
+    d.w_dmax[w] = mx;
+    d.w_accept[w] = 0;
+    d.w_ls_state[w] = (d.w_status[w] == 0) ? 1 : 0;     // 1: evaluate the full step (cost only)
+    d.w_ls_x[w] = 1.0; d.w_ls_it[w] = 0; d.w_ls_pvalid[w] = 0;
+  }
   if (threadIdx.x == 1) d.w_dDd[w] = tot;
-  if (threadIdx.x == 2) d.w_step2[w] = tot;
-  if (threadIdx.x == 3) d.w_x2[w] = tot;
-  if (threadIdx.x == 4) d.w_dr[w] = tot;
+  if (threadIdx.x == 2) d.w_x2[w] = tot;
+  if (threadIdx.x == 3) d.w_dr[w] = tot;
 }
 
-// -------------------------------------------------------------------------- K6: candidate cost
-__global__ void __launch_bounds__(kThreads) k_cost_points(Dev d, DevParams P) {
-  __shared__ double sm[4];
+// ----------------------------------------------- K6: trial point of the projected line search + its cost
+// Ceres evaluates x (+) s*delta with the bounds projection inside Plus (parameter_block.h), first at s = 1.
+// thread per camera of a searching window: trial pose and its precompute
+__global__ void k_trial_cams(Dev d) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= d.Nc) return;
+  const int w = d.cam_win[c];
+  const int st = d.w_ls_state[w];
+  if (st < 1 || st > 3) return;
+  const double step = d.w_ls_x[w];
+  const int f = d.fc[c];
+  double pose[6];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    pose[i] = d.poses[(size_t)c * 6 + i];
+    if (f >= 0) pose[i] += step * d.x[(size_t)f * 6 + i];
+    d.poses_new[(size_t)c * 6 + i] = pose[i];
+  }
+  CamPre cp;
+  cam_precompute(pose, cp);
+  d.campre_new[c] = cp;
+}
+
+// thread per point: trial point, cost, |x_trial - x|^2 and (state 2) the directional derivative
+//   d/ds cost = sum_obs  rho' (D^T r) . (G dw + dt + R dp)     evaluated at the trial point
+__global__ void __launch_bounds__(kThreads) k_trial_points(Dev d, DevParams P) {
+  __shared__ double sm[4 * 3];
   const int chunk = blockIdx.x;
+  const int w = d.pchunk_win[chunk];
+  const int st = d.w_ls_state[w];
+  if (st < 1 || st > 3) return;
+  const bool grad = (st == 2);
+  const double step = d.w_ls_x[w];
   const int p = d.pchunk_begin[chunk] + threadIdx.x;
-  double cost[1] = {0.0};
+  double part[3] = {0, 0, 0};
   if (p < d.pchunk_end[chunk]) {
-    const double X[3] = {d.pts_new[3 * (size_t)p], d.pts_new[3 * (size_t)p + 1], d.pts_new[3 * (size_t)p + 2]};
+    double X[3], dpv[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const double x = d.pts[3 * (size_t)p + i];
+      dpv[i] = d.dp[3 * (size_t)p + i];
+      X[i] = clampd(x + step * dpv[i], P.lo, P.hi);
+      d.pts_new[3 * (size_t)p + i] = X[i];
+      part[2] += (X[i] - x) * (X[i] - x);
+    }
     const int e1 = d.pt_off[p + 1];
     for (int e = d.pt_off[p]; e < e1; ++e) {
-      CamPre cp;
-      load_campre_Rt(d.campre_new, __ldg(d.pcam + e), cp);
+      const int c = __ldg(d.pcam + e);
       const float4 m = __ldg(d.uv_p + e);
       const float uv[4] = {m.x, m.y, m.z, m.w};
-      cost[0] += obs_cost(P.pl, P.pr, cp, X, uv, P.rdim, P.huber_delta);
+      if (!grad) {
+        CamPre cp;
+        load_campre_Rt(d.campre_new, c, cp);
+        part[0] += obs_cost(P.pl, P.pr, cp, X, uv, P.rdim, P.huber_delta);
+      } else {
+        CamPre cp;
+        load_campre(d.campre_new, c, cp);
+        double q[3], r[4], D[12];
+        const double s = project(P.pl, P.pr, cp, X, uv, P.rdim, q, r, D);
+        double rho, wt;
+        huber(P.huber_delta, s, rho, wt);
+        part[0] += 0.5 * rho;
+        double A[6], h[3], G[9];
+        form_A_h(D, r, wt, A, h);
+        form_G(cp, q, G);
+        double v[3] = {cp.R[0] * dpv[0] + cp.R[1] * dpv[1] + cp.R[2] * dpv[2],
+                       cp.R[3] * dpv[0] + cp.R[4] * dpv[1] + cp.R[5] * dpv[2],
+                       cp.R[6] * dpv[0] + cp.R[7] * dpv[1] + cp.R[8] * dpv[2]};
+        const int f = __ldg(d.fc + c);
+        if (f >= 0) {
+          const double* dc = d.x + (size_t)f * 6;
+#pragma unroll
+          for (int i = 0; i < 3; ++i) v[i] += G[3 * i] * dc[0] + G[3 * i + 1] * dc[1] + G[3 * i + 2] * dc[2] + dc[3 + i];
+        }
+        part[1] += h[0] * v[0] + h[1] * v[1] + h[2] * v[2];
+      }
     }
   }
-  const double tot = block_sum<1>(cost, sm);
-  if (threadIdx.x == 0) d.cost_part[chunk] = tot;
+  const double tot = block_sum<3>(part, sm);
+  if (threadIdx.x < 3) d.ls_part[(size_t)chunk * 3 + threadIdx.x] = tot;
 }
 
-// one CTA per window: candidate cost = sum of chunk partials
-__global__ void __launch_bounds__(kThreads) k_cost_finish(Dev d) {
-  __shared__ double sm[4];
+// one CTA per searching window: raw sums (cost, directional derivative, |step|^2 incl. the cameras on rank 0)
+__global__ void __launch_bounds__(kThreads) k_ls_reduce(Dev d, int rank) {
+  __shared__ double sm[4 * 3];
   const int w = blockIdx.x;
-  double s[1] = {0.0};
-  for (int ch = d.win_pchunk_off[w] + threadIdx.x; ch < d.win_pchunk_off[w + 1]; ch += kThreads) s[0] += d.cost_part[ch];
-  const double tot = block_sum<1>(s, sm);
-  if (threadIdx.x == 0) d.w_cand[w] = tot;
+  const int st = d.w_ls_state[w];
+  if (st < 1 || st > 3) return;
+  double part[3] = {0, 0, 0};
+  for (int ch = d.win_pchunk_off[w] + threadIdx.x; ch < d.win_pchunk_off[w + 1]; ch += kThreads) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) part[i] += d.ls_part[(size_t)ch * 3 + i];
+  }
+  if (rank == 0)
+    for (int c = d.win_cam_off[w] + threadIdx.x; c < d.win_cam_off[w + 1]; c += kThreads) {
+#pragma unroll
+      for (int i = 0; i < 6; ++i) { const double dd = d.poses_new[(size_t)c * 6 + i] - d.poses[(size_t)c * 6 + i]; part[2] += dd * dd; }
+    }
+  const double tot = block_sum<3>(part, sm);
+  if (threadIdx.x < 3) d.w_ls_red[(size_t)threadIdx.x * d.nwin + w] = tot;
 }
 
 // -------------------------------------------------------------------------------- LM control
@@ -605,10 +688,54 @@ __global__ void k_lm_begin(Dev d, DevParams P, double initial_radius, int first)
   }
 }
 
+// Projected Armijo line search, one thread per window (ArmijoLineSearch::DoSearch restated; see
+// sba_linesearch.cuh).  States: 1 full step evaluated (cost only) · 2 trial evaluated with its directional
+// derivative · 3 full step re-evaluated after a failed search · 4 candidate ready for k_lm_control · 0 idle.
+__global__ void k_ls_control(Dev d, DevParams P) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= d.nwin) return;
+  const int st = d.w_ls_state[w];
+  if (st < 1 || st > 3) return;
+  const double f = d.w_ls_red[w], g = d.w_ls_red[(size_t)d.nwin + w], step2 = d.w_ls_red[2 * (size_t)d.nwin + w];
+  const double x = d.w_ls_x[w];
+  const double cost0 = d.w_cost[w], gd = d.w_gd[w];
+  if (st == 3) { d.w_cand[w] = f; d.w_step2[w] = step2; d.w_ls_state[w] = 4; return; }
+  if (st == 1) {
+    // an invalid trust-region step never reaches the line search (k_lm_control treats it)
+    const double model = -0.5 * gd + 0.5 * d.w_dDd[w] + 0.5 * d.w_dr[w];
+    if (d.w_fail[w] != 0 || !(model > 0.0) || !isfinite(model)) { d.w_cand[w] = f; d.w_step2[w] = step2; d.w_ls_state[w] = 4; return; }
+  }
+  const bool valid = isfinite(f) && (st == 1 || isfinite(g));
+  if (valid && f <= cost0 + 1e-4 * gd * x) { d.w_cand[w] = f; d.w_step2[w] = step2; d.w_ls_state[w] = 4; return; }
+  if (st == 1 && valid) {          // sufficient decrease failed: the same step again, now with the derivative
+    d.w_ls_state[w] = 2;
+    atomicAdd(d.counters + 3, 1);
+    return;
+  }
+  bool failed = false;
+  double nx = x;
+  const int it = ++d.w_ls_it[w];
+  if (it >= 20) failed = true;      // max_num_line_search_step_size_iterations
+  else {
+    LsSample cur; cur.x = x; cur.f = f; cur.g = g; cur.has_g = 1;
+    LsSample prev; prev.x = d.w_ls_px[w]; prev.f = d.w_ls_pf[w]; prev.g = d.w_ls_pg[w]; prev.has_g = 1;
+    nx = ls_next_step(cost0, gd, prev, d.w_ls_pvalid[w], cur, valid ? 1 : 0);
+    if (nx * d.w_dmax[w] < 1e-9) failed = true;     // min_line_search_step_size
+  }
+  if (failed) {                     // Ceres keeps the whole step when the search fails
+    d.w_ls_x[w] = 1.0; d.w_ls_state[w] = 3;
+  } else {
+    d.w_ls_px[w] = x; d.w_ls_pf[w] = f; d.w_ls_pg[w] = g; d.w_ls_pvalid[w] = valid ? 1 : 0;
+    d.w_ls_x[w] = nx; d.w_ls_state[w] = 2;
+  }
+  atomicAdd(d.counters + 3, 1);
+}
+
 __global__ void k_lm_control(Dev d, DevParams P) {
   const int w = blockIdx.x * blockDim.x + threadIdx.x;
   if (w >= d.nwin) return;
-  d.w_accept[w] = 0;
+  if (d.w_ls_state[w] != 4) return;      // idle, or its line search is still running
+  d.w_ls_state[w] = 0;
   if (d.w_status[w] != 0) return;
   const int iter = ++d.w_iter[w];
   const double cost = d.w_cost[w], cand = d.w_cand[w];

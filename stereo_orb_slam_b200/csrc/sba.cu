@@ -203,11 +203,13 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   AL(d.spart, (size_t)d.nschunk * 36) AL(d.Su, (size_t)d.nbu * 36) AL(d.rpart, (size_t)d.ncchunk * 6)
   AL(d.rhs, nf * 6) AL(h->rsum, nf * 6) AL(d.Minv, nf * 36)
   AL(d.x, nf * 6) AL(d.r, nf * 6) AL(d.z, nf * 6) AL(d.p, nf * 6) AL(d.Ap, nf * 6)
-  AL(d.step_part, (size_t)d.npchunk * 4) AL(d.cost_part, (size_t)d.npchunk)
+  AL(d.dp, np * 3) AL(d.step_part, (size_t)d.npchunk * 4) AL(d.ls_part, (size_t)d.npchunk * 3)
   AL(d.w_radius, nw) AL(d.w_decf, nw) AL(d.w_cost, nw) AL(d.w_gmax, nw)
-  AL(d.w_gd, nw * 6)   // one block: a multi-GPU solve all-reduces the six step scalars in one call
-  d.w_dDd = d.w_gd + nw; d.w_step2 = d.w_gd + 2 * nw; d.w_x2 = d.w_gd + 3 * nw; d.w_dr = d.w_gd + 4 * nw;
-  d.w_cand = d.w_gd + 5 * nw;
+  AL(d.w_gd, nw * 4)   // one block: a multi-GPU solve all-reduces the four step scalars in one call
+  d.w_dDd = d.w_gd + nw; d.w_x2 = d.w_gd + 2 * nw; d.w_dr = d.w_gd + 3 * nw;
+  AL(d.w_dmax, nw) AL(d.w_ls_red, nw * 3) AL(d.w_step2, nw) AL(d.w_cand, nw)
+  AL(d.w_ls_x, nw) AL(d.w_ls_px, nw) AL(d.w_ls_pf, nw) AL(d.w_ls_pg, nw)
+  AL(d.w_ls_state, nw) AL(d.w_ls_it, nw) AL(d.w_ls_pvalid, nw)
   AL(d.w_rz, nw) AL(d.w_rz0, nw) AL(d.w_pAp, nw) AL(d.w_alpha, nw) AL(d.w_beta, nw)
   AL(d.w_status, nw) AL(d.w_iter, nw) AL(d.w_succ, nw) AL(d.w_invalid, nw) AL(d.w_accept, nw)
   AL(d.w_fail, nw) AL(d.w_pcg_done, nw) AL(d.w_pcg_it, nw) AL(d.counters, 4)
@@ -218,6 +220,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   CUDA_TRY(cudaMemsetAsync(d.w_status, 0, nw * 4, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.w_fail, 0, nw * 4, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.w_accept, 0, nw * 4, h->stream));
+  CUDA_TRY(cudaMemsetAsync(d.w_ls_state, 0, nw * 4, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.counters, 0, 16, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.pts, 0, std::max<size_t>(1, np * 3) * 8, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.pts_new, 0, std::max<size_t>(1, np * 3) * 8, h->stream));
@@ -382,22 +385,50 @@ static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
   return SBA_OK;
 }
 
-// K5 + K6 + trust-region control: candidate state, its cost, accept / reject per window.
-static int do_step(sba_handle h) {
+// One round of the projected line search: trial poses / points at every searching window's current step
+// size, cost (+ directional derivative), then the per-window Armijo decision.
+static int do_ls_round(sba_handle h) {
   Dev& d = h->d;
   const DevParams& P = h->P;
-  LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P);
-  LAUNCH(h, k_cam_step, d.nwin, kThreads, d, (int)(h->comm.active() ? h->comm.rank : 0));
-  LAUNCH(h, k_cam_precompute, cdiv(d.Nc, 128), 128, d.Nc, d.poses_new, d.campre_new);
-  LAUNCH(h, k_cost_points, d.npchunk, kThreads, d, P);
-  LAUNCH(h, k_cost_finish, d.nwin, kThreads, d);
+  const int rank = (int)(h->comm.active() ? h->comm.rank : 0);
+  CUDA_TRY(cudaMemsetAsync(d.counters + 3, 0, 4, h->stream));
+  LAUNCH(h, k_trial_cams, cdiv(d.Nc, 128), 128, d);
+  LAUNCH(h, k_trial_points, d.npchunk, kThreads, d, P);
+  LAUNCH(h, k_ls_reduce, d.nwin, kThreads, d, rank);
   if (h->comm.active()) {
-    std::string _err;   // w_gd, w_dDd, w_step2, w_x2, w_dr, w_cand are one contiguous block
-    if (!h->comm.allreduce(d.w_gd, (size_t)d.nwin * 6, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+    std::string _err;
+    if (!h->comm.allreduce(d.w_ls_red, (size_t)d.nwin * 3, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
   }
+  LAUNCH(h, k_ls_control, cdiv(d.nwin, 128), 128, d, P);
+  return SBA_OK;
+}
+
+// K5 + K6 + trust-region control: step, line search (Ceres: bounds => projected Armijo search after every
+// trust-region step), accept / reject per window.  Leaves counters [0] running [2] accepted on the host.
+static int do_step(sba_handle h, int* ls_rounds) {
+  Dev& d = h->d;
+  const DevParams& P = h->P;
+  const int rank = (int)(h->comm.active() ? h->comm.rank : 0);
+  int rc;
   CUDA_TRY(cudaMemsetAsync(d.counters, 0, 4, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.counters + 2, 0, 4, h->stream));
-  LAUNCH(h, k_lm_control, cdiv(d.nwin, 128), 128, d, P);
+  LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P);
+  LAUNCH(h, k_cam_step, d.nwin, kThreads, d, rank);
+  if (h->comm.active()) {
+    std::string _err;   // w_gd, w_dDd, w_x2, w_dr are one contiguous block
+    if (!h->comm.allreduce(d.w_gd, (size_t)d.nwin * 4, false, h->stream, &_err) ||
+        !h->comm.allreduce(d.w_dmax, (size_t)d.nwin, true, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+  }
+  int rounds = 0;
+  for (;;) {
+    if ((rc = do_ls_round(h))) return rc;
+    ++rounds;
+    LAUNCH(h, k_lm_control, cdiv(d.nwin, 128), 128, d, P);
+    CUDA_TRY(cudaMemcpyAsync(h->h_counters, d.counters, 16, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (h->h_counters[3] <= 0 || rounds > 64) break;
+  }
+  if (ls_rounds) *ls_rounds += rounds;
   LAUNCH(h, k_apply_points, d.npchunk, kThreads, d);
   LAUNCH(h, k_apply_cams, cdiv((int64_t)d.Nc * 6, 256), 256, d);
   CUDA_TRY(cudaGetLastError());
@@ -505,11 +536,12 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
       case 4: if ((rc = do_schur(h))) return rc; break;
       case 8: if ((rc = do_linearize(h))) return rc; if ((rc = do_schur(h))) return rc; break;
       case 5: LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P); break;
-      case 6:
-        LAUNCH(h, k_cam_precompute, cdiv(d.Nc, 128), 128, d.Nc, d.poses, d.campre_new);
-        CUDA_TRY(cudaMemcpyAsync(d.pts_new, d.pts, std::max<size_t>(1, (size_t)d.Np * 3) * 8, cudaMemcpyDeviceToDevice, h->stream));
+      case 6:      // one line-search evaluation of the full step (needs sba_schur + sba_pcg for a meaningful step)
+        LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P);
+        LAUNCH(h, k_cam_step, d.nwin, kThreads, d, 0);
+        LAUNCH(h, k_trial_cams, cdiv(d.Nc, 128), 128, d);
         CUDA_TRY(cudaEventRecord(h->ev[6], h->stream));   // time the cost kernel alone
-        LAUNCH(h, k_cost_points, d.npchunk, kThreads, d, P);
+        LAUNCH(h, k_trial_points, d.npchunk, kThreads, d, P);
         break;
       case 7: {
         const int gf = cdiv(d.Nf, 128), gs = cdiv((int64_t)d.Nf * 6, 128);
@@ -570,6 +602,7 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
   take_lin_time();
 
   int running = d.nwin;
+  int ls_rounds = 0;
   for (int iter = 0; running > 0 && iter < o.max_iterations; ++iter) {
     if (o.max_time_s > 0.0 && secs(t0) >= o.max_time_s) {
       LAUNCH(h, k_lm_timeout, cdiv(d.nwin, 128), 128, d);
@@ -582,10 +615,9 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
     if ((rc = do_pcg(h, &o, &pit))) return rc;
     S.pcg_iterations += pit;
     CUDA_TRY(cudaEventRecord(h->ev[2], h->stream));
-    if ((rc = do_step(h))) return rc;
+    if ((rc = do_step(h, &ls_rounds))) return rc;      // syncs; h_counters holds [running, -, accepted, -]
     CUDA_TRY(cudaEventRecord(h->ev[3], h->stream));
-    CUDA_TRY(cudaMemcpyAsync(h->h_counters, d.counters, 16, cudaMemcpyDeviceToHost, h->stream));
-    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    CUDA_TRY(cudaEventSynchronize(h->ev[3]));
     take_lin_time();
     float a = 0.f, b = 0.f, c = 0.f;
     CUDA_TRY(cudaEventElapsedTime(&a, h->ev[0], h->ev[1]));

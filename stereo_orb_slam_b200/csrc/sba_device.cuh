@@ -50,14 +50,21 @@ struct Dev {
   // ---- PCG vectors [Nf*6]
   double *x, *r, *z, *p, *Ap;
   // ---- step
-  double *step_part;             // [npchunk*4]  g.dp, dp D dp, |step|^2, |x|^2
-  double *cost_part;             // [npchunk]
+  double *dp;                    // [Np*3] point step (back-substitution)
+  double *step_part;             // [npchunk*4]  g.dp, dp D dp, |x|^2, max|dp|
+  double *ls_part;               // [npchunk*3]  trial cost, directional derivative, |x_trial - x|^2
   // ---- per-window scalars [nwin]
   double *w_radius, *w_decf, *w_cost, *w_cand, *w_gmax;
-  double *w_gd, *w_dDd, *w_dr, *w_step2, *w_x2;
+  double *w_gd, *w_dDd, *w_dr, *w_x2;     // one block [4*nwin] (all-reduced together on multi-GPU)
+  double *w_dmax;                          // max-norm of the step (all-reduced with max)
+  double *w_ls_red;                        // [3*nwin] trial cost, directional derivative, |step|^2 (raw sums)
+  double *w_step2;
+  // projected Armijo line search state (sba_linesearch.cuh)
+  double *w_ls_x, *w_ls_px, *w_ls_pf, *w_ls_pg;
+  int32_t *w_ls_state, *w_ls_it, *w_ls_pvalid;
   double *w_rz, *w_rz0, *w_pAp, *w_alpha, *w_beta;
   int32_t *w_status, *w_iter, *w_succ, *w_invalid, *w_accept, *w_fail, *w_pcg_done, *w_pcg_it;
-  int32_t *counters;             // [0] windows still running, [1] pcg windows not done
+  int32_t *counters;             // [0] windows still running, [1] pcg windows not done, [2] accepted, [3] line searches pending
 };
 
 }  // namespace sba

@@ -49,10 +49,11 @@ def emu():
     import ctypes as C
     out = os.path.join(ROOT, "tests", "emu", "_build", "libemu.so")
     src = os.path.join(ROOT, "tests", "emu", "emu_math.cpp")
-    if not os.path.exists(out) or os.path.getmtime(out) < os.path.getmtime(src):
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(src), *[os.path.getmtime(os.path.join(ROOT, 'stereo_orb_slam_b200', 'csrc', f)) for f in ('sba_math.cuh', 'sba_linesearch.cuh')]):
         os.makedirs(os.path.dirname(out), exist_ok=True)
         subprocess.check_call(["/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++", "-O2", "-std=c++17",
                                "-fPIC", "-shared", "-Wno-unknown-pragmas", "-o", out, src])
     L = C.CDLL(out)
     L.emu_obs_cost.restype = C.c_double
+    L.emu_ls_minimize.restype = C.c_double
     return L

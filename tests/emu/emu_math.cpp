@@ -2,6 +2,7 @@
 // the CUDA kernels are built from can be checked against the oracle without a GPU.  NOT a product
 // path (libsba.so has no CPU fallback).
 #include "../../stereo_orb_slam_b200/csrc/sba_math.cuh"
+#include "../../stereo_orb_slam_b200/csrc/sba_linesearch.cuh"
 extern "C" {
 void emu_observation(const double* pose, const double* X, const float* uv, const double* pl, const double* pr,
                      int rdim, double delta, double* r_corrected, double* U21, double* gc, double* V6, double* gp,
@@ -24,4 +25,9 @@ double emu_obs_cost(const double* pose, const double* X, const float* uv, const 
 }
 int emu_inv_spd6(double* M) { return sba::inv_spd6(M) ? 1 : 0; }
 int emu_inv_sym3(const double* M, double* Mi) { return sba::inv_sym3(M, Mi) ? 1 : 0; }
+double emu_ls_minimize(int n, const double* x, const double* f, const double* g, const int* has_g, double xmin, double xmax) {
+  sba::LsSample s[3];
+  for (int i = 0; i < n && i < 3; ++i) { s[i].x = x[i]; s[i].f = f[i]; s[i].g = g[i]; s[i].has_g = has_g[i]; }
+  return sba::ls_minimize_interpolating(s, n, xmin, xmax);
+}
 }

@@ -125,3 +125,39 @@ def test_oracle_vs_numpy_gradient(small_window):
         xp = w["points"].copy(); xp[p, i] += h; xm = w["points"].copy(); xm[p, i] -= h
         num = (objective(w["poses"], xp) - objective(w["poses"], xm)) / (2 * h)
         assert abs(num - lin["gp"][p, i]) <= 1e-5 * max(1.0, abs(num))
+
+
+def test_line_search_step_selection_three_ways(emu):
+    """Ceres's MinimizeInterpolatingPolynomial restated three times — oracle (C++, Laguerre roots), the device
+    header csrc/sba_linesearch.cuh (Durand-Kerner roots, compiled for the host) and numpy (polyfit-free
+    Vandermonde solve + np.roots) — must pick the same step, incl. the real parts of complex roots."""
+    import ctypes as C
+    rng = np.random.default_rng(8)
+    d = C.c_double
+    P = lambda a, t=d: a.ctypes.data_as(C.POINTER(t))
+    for trial in range(200):
+        n = 2 if trial % 2 == 0 else 3
+        x = np.zeros(n); f = np.zeros(n); g = np.zeros(n)
+        f[0] = rng.uniform(1, 100); g[0] = -rng.uniform(0.1, 50)
+        x[1] = rng.uniform(1e-3, 1.0); f[1] = f[0] + rng.normal(0, 5); g[1] = rng.normal(0, 50)
+        if n == 3:
+            x[2] = x[1] / rng.uniform(0.05, 0.6); f[2] = f[0] + abs(rng.normal(0, 20)); g[2] = rng.normal(0, 80)
+        hg = np.ones(n, np.int32)
+        lo, hi = 1e-3 * x[1], 0.6 * x[1]
+        a = oracle.ls_minimize(x, f, g, hg, lo, hi)
+        b = emu.emu_ls_minimize(n, P(x), P(f), P(g), P(hg, C.c_int), d(lo), d(hi))
+        # numpy restatement
+        deg = 2 * n - 1
+        rows, rhs = [], []
+        for i in range(n):
+            rows.append([x[i] ** (deg - j) for j in range(deg + 1)]); rhs.append(f[i])
+            rows.append([(deg - j) * x[i] ** (deg - j - 1) if j < deg else 0.0 for j in range(deg + 1)]); rhs.append(g[i])
+        c = np.linalg.solve(np.array(rows), np.array(rhs))
+        cand = [0.5 * (lo + hi), lo, hi] + [float(np.real(r)) for r in np.roots(np.polyder(c))]
+        cand = [v for v in cand if lo <= v <= hi]
+        vals = [np.polyval(c, v) for v in cand]
+        ref = cand[int(np.argmin(vals))]
+        pa, pb, pr = np.polyval(c, a), np.polyval(c, b), min(vals)
+        scale = max(1.0, abs(pr))
+        assert abs(pa - pr) <= 1e-9 * scale and abs(pb - pr) <= 1e-9 * scale, (trial, a, b, ref)
+        assert abs(a - b) <= 1e-7 * hi, (trial, a, b, ref)

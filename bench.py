@@ -208,10 +208,11 @@ def run_ours(args):
         sv2.solve(hb["poses"], hb["points"], hb["obs_cam"], hb["obs_pt"], hb["obs_uv"], w["p_l"], w["p_r"], options=opt)
     e_steps = max(3, min(args.steps, 10))
     barrier()
-    t0 = time.perf_counter(); lin = 0; its = 0; solve_s = 0.0; summ = None
+    t0 = time.perf_counter(); lin = 0; its = 0; solve_s = 0.0; summ = None; brk = {}
     for _ in range(e_steps):
         _, _, summ = sv2.solve(hb["poses"], hb["points"], hb["obs_cam"], hb["obs_pt"], hb["obs_uv"], w["p_l"], w["p_r"], options=opt)
         lin += summ["linearizations"]; its += summ["iterations"]; solve_s += summ["time_solve_s"]
+        brk = {k: brk.get(k, 0.0) + 1e3 * summ[k] / e_steps for k in ("time_structure_s", "time_h2d_s", "time_solve_s", "time_d2h_s")}
     barrier()
     e_wall = time.perf_counter() - t0
     te = torch.tensor([e_wall], dtype=torch.float64, device="cuda"); tl = torch.tensor([float(Nobs * lin)], dtype=torch.float64, device="cuda")
@@ -231,7 +232,9 @@ def run_ours(args):
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "what": "sba_solve on pinned host buffers: structure build + H2D + full LM solve + D2H; obs x linearisations / wall",
                     "ms_per_solve": 1e3 * e_wall / e_steps, "lm_iterations": its // e_steps, "final_cost": summ["final_cost"],
-                    "termination": summ["termination_name"]},
+                    "termination": summ["termination_name"],
+                    "ms_breakdown": {k.replace("time_", "").replace("_s", ""): v for k, v in brk.items()},
+                    "device_ms": {k: summ[k] for k in ("ms_linearize", "ms_schur", "ms_pcg", "ms_update")}},
             "lm_iters_per_s": its / solve_s,
             "roofline": {"bound": "hbm", "kernel": "k_lin_points", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                          "traffic": None, "peak_source": peak_src, "algorithmic_bytes": B_lp, "us_per_launch": 1e3 * t_lp},

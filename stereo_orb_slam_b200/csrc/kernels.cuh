@@ -472,6 +472,115 @@ __global__ void k_pcg_update_p(Dev d) {
   d.p[t] = d.z[t] + d.w_beta[w] * d.p[t];
 }
 
+// Whole PCG solve in ONE launch: one CTA per window, vectors (and, when it fits, the window's blocks of S and
+// the block-Jacobi inverses) in shared memory, fixed-order CTA reductions for the fp64 dot products.  Used when
+// every window's reduced system is small enough (local / sliding windows, batched windows); the multi-launch
+// kernels above remain for global problems.  Same recurrences and stopping rule as k_pcg_dot.
+constexpr int kPcgThreads = 512;
+
+__device__ __forceinline__ double cta_sum512(double v, double* red /* [16] */) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = 0.0;
+#pragma unroll
+  for (int i = 0; i < kPcgThreads / 32; ++i) t += red[i];
+  return t;
+}
+
+__global__ void __launch_bounds__(kPcgThreads) k_pcg_window(Dev d, DevParams P, int max_it, int s_in_smem) {
+  extern __shared__ double smem[];
+  const int w = blockIdx.x;
+  const int f0 = d.win_fc_off[w], f1 = d.win_fc_off[w + 1];
+  const int nf = f1 - f0, n = 6 * nf;
+  if (threadIdx.x == 0) d.w_pcg_it[w] = 0;
+  if (nf <= 0) return;
+  if (d.w_status[w] != 0 || d.w_fail[w] != 0) return;     // uniform per CTA; leaves x untouched (unused)
+  double* x = smem; double* r = x + n; double* z = r + n; double* pv = z + n; double* Ap = pv + n;
+  double* red = Ap + n;                    // [16]
+  const int b0 = d.diag_blk[f0];
+  const int b1 = (f1 < d.Nf) ? d.diag_blk[f1] : d.nbu;
+  const double* Sg = d.Su + (size_t)b0 * 36;
+  const double* Mg = d.Minv + (size_t)f0 * 36;
+  const double* S = Sg; const double* M = Mg;
+  if (s_in_smem) {
+    double* Ms = red + 16; double* Ss = Ms + (size_t)nf * 36;
+    for (int i = threadIdx.x; i < nf * 36; i += kPcgThreads) Ms[i] = Mg[i];
+    for (int i = threadIdx.x; i < (b1 - b0) * 36; i += kPcgThreads) Ss[i] = Sg[i];
+    S = Ss; M = Ms;
+  }
+  for (int i = threadIdx.x; i < n; i += kPcgThreads) { x[i] = 0.0; r[i] = d.rhs[(size_t)f0 * 6 + i]; }
+  __syncthreads();
+  double part = 0.0;
+  for (int i = threadIdx.x; i < n; i += kPcgThreads) {
+    const int f = i / 6, k = i - 6 * f;
+    double acc = 0.0;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) acc += M[(size_t)f * 36 + 6 * k + j] * r[6 * f + j];
+    z[i] = acc; pv[i] = acc;
+    part += r[i] * acc;
+  }
+  double rz = cta_sum512(part, red);
+  const double rz0 = rz;
+  int it = 0;
+  bool fail = false;
+  if (!(rz > 0.0)) { if (!(rz == 0.0)) fail = true; }      // rhs == 0: x = 0 is the solution; NaN: fail
+  else {
+    for (;;) {
+      // Ap = S p  (block-CSR over the full pattern; upper blocks stored once)
+      part = 0.0;
+      for (int i = threadIdx.x; i < n; i += kPcgThreads) {
+        const int f = i / 6, k = i - 6 * f;
+        double acc = 0.0;
+        const int j1 = d.row_ptr[f0 + f + 1];
+        for (int j = d.row_ptr[f0 + f]; j < j1; ++j) {
+          const int col = __ldg(d.bsr_col + j) - f0;
+          const int bi = __ldg(d.bsr_blk + j);
+          const double* xv = pv + 6 * col;
+          if (bi >= 0) {
+            const double* B = S + (size_t)(bi - b0) * 36 + 6 * k;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) acc += B[c] * xv[c];
+          } else {
+            const double* B = S + (size_t)(~bi - b0) * 36 + k;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) acc += B[6 * c] * xv[c];
+          }
+        }
+        Ap[i] = acc;
+        part += pv[i] * acc;
+      }
+      const double pAp = cta_sum512(part, red);
+      if (!(pAp > 0.0)) { fail = true; break; }             // S not SPD
+      const double alpha = rz / pAp;
+      for (int i = threadIdx.x; i < n; i += kPcgThreads) { x[i] += alpha * pv[i]; r[i] -= alpha * Ap[i]; }
+      __syncthreads();
+      part = 0.0;
+      for (int i = threadIdx.x; i < n; i += kPcgThreads) {
+        const int f = i / 6, k = i - 6 * f;
+        double acc = 0.0;
+#pragma unroll
+        for (int j = 0; j < 6; ++j) acc += M[(size_t)f * 36 + 6 * k + j] * r[6 * f + j];
+        z[i] = acc;
+        part += r[i] * acc;
+      }
+      const double rz_new = cta_sum512(part, red);
+      ++it;
+      if (!isfinite(rz_new)) { fail = true; break; }
+      if (rz_new <= P.pcg_tol2 * rz0 || it >= max_it) { rz = rz_new; break; }
+      const double beta = rz_new / rz;
+      rz = rz_new;
+      for (int i = threadIdx.x; i < n; i += kPcgThreads) pv[i] = z[i] + beta * pv[i];
+      __syncthreads();
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += kPcgThreads) { d.x[(size_t)f0 * 6 + i] = x[i]; d.r[(size_t)f0 * 6 + i] = r[i]; }
+  if (threadIdx.x == 0) { d.w_pcg_it[w] = it; if (fail) d.w_fail[w] = 1; atomicMax(d.counters + 4, it); }   // control-plane counter
+}
+
 // ------------------------------------------------------------------------- K5: back-substitution
 // thread per point: dp = -Vinv (gp + sum_obs W_e^T dc[cam(e)])   (stored; the candidate is formed by the
 // line-search kernels).  chunk partials: g.dp, dp^T D dp, |x|^2, max|dp|

@@ -56,6 +56,8 @@ struct sba_handle_s {
   sba::Comm comm;                     // NCCL (multi-GPU), inactive on 1 GPU
   double time_structure_s = 0.0;
   double last_radius = 1e4;
+  // single-launch PCG (k_pcg_window): usable when every window's system fits one CTA
+  bool pcg_window_ok = false; int pcg_s_in_smem = 0; size_t pcg_smem = 0;
 
   template <typename T>
   int alloc(T** p, size_t n) {
@@ -129,7 +131,7 @@ int sba_create(int device, sba_handle* out) {
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
-    if (e == cudaSuccess) e = cudaMallocHost((void**)&h->h_counters, 4 * sizeof(int32_t));
+    if (e == cudaSuccess) e = cudaMallocHost((void**)&h->h_counters, 8 * sizeof(int32_t));
     if (e != cudaSuccess) {
       set_error(std::string("sba_create: no usable CUDA device: ") + cudaGetErrorString(e));
       delete h;
@@ -212,7 +214,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   AL(d.w_ls_state, nw) AL(d.w_ls_it, nw) AL(d.w_ls_pvalid, nw)
   AL(d.w_rz, nw) AL(d.w_rz0, nw) AL(d.w_pAp, nw) AL(d.w_alpha, nw) AL(d.w_beta, nw)
   AL(d.w_status, nw) AL(d.w_iter, nw) AL(d.w_succ, nw) AL(d.w_invalid, nw) AL(d.w_accept, nw)
-  AL(d.w_fail, nw) AL(d.w_pcg_done, nw) AL(d.w_pcg_it, nw) AL(d.counters, 4)
+  AL(d.w_fail, nw) AL(d.w_pcg_done, nw) AL(d.w_pcg_it, nw) AL(d.counters, 8)
 #undef AL
   // everything the kernels may read before it is first written starts at zero
   CUDA_TRY(cudaMemsetAsync(d.x, 0, std::max<size_t>(1, nf * 6) * 8, h->stream));
@@ -221,12 +223,30 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   CUDA_TRY(cudaMemsetAsync(d.w_fail, 0, nw * 4, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.w_accept, 0, nw * 4, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.w_ls_state, 0, nw * 4, h->stream));
-  CUDA_TRY(cudaMemsetAsync(d.counters, 0, 16, h->stream));
+  CUDA_TRY(cudaMemsetAsync(d.counters, 0, 32, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.pts, 0, std::max<size_t>(1, np * 3) * 8, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.pts_new, 0, std::max<size_t>(1, np * 3) * 8, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.V, 0, std::max<size_t>(1, np * 6) * 8, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.gp, 0, std::max<size_t>(1, np * 3) * 8, h->stream));
   CUDA_TRY(cudaStreamSynchronize(h->stream));
+  {
+    // per-window size of the reduced system -> can one CTA hold it?
+    int nf_max = 0; int64_t nb_max = 0;
+    for (int w = 0; w < H.nwin; ++w) {
+      const int f0 = H.win_fc_off[w], f1 = H.win_fc_off[w + 1];
+      if (f1 <= f0) continue;
+      nf_max = std::max(nf_max, f1 - f0);
+      const int64_t b0 = H.diag_blk[f0], b1 = (f1 < H.Nf) ? H.diag_blk[f1] : (int64_t)H.blk_row.size();
+      nb_max = std::max(nb_max, b1 - b0);
+    }
+    const size_t vec = ((size_t)5 * 6 * nf_max + 16) * 8;
+    const size_t full = vec + ((size_t)nf_max * 36 + (size_t)nb_max * 36) * 8;
+    h->pcg_window_ok = (nf_max > 0 && nf_max <= 512);   // multi-GPU: S is all-reduced, so every rank runs the same replicated solve
+    h->pcg_s_in_smem = (full <= (size_t)220 * 1024) ? 1 : 0;
+    h->pcg_smem = h->pcg_s_in_smem ? full : vec;
+    if (h->pcg_window_ok)
+      CUDA_TRY(cudaFuncSetAttribute(k_pcg_window, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->pcg_smem));
+  }
   h->time_structure_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   return SBA_OK;
 }
@@ -356,7 +376,13 @@ static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
   Dev& d = h->d;
   const DevParams& P = h->P;
   int it = 0;
-  if (d.Nf > 0) {
+  if (d.Nf > 0 && h->pcg_window_ok) {
+    // one launch, no host round trip; the iteration count comes back with the LM counters (counters[4])
+    CUDA_TRY(cudaMemsetAsync(d.counters + 4, 0, 4, h->stream));
+    k_pcg_window<<<d.nwin, kPcgThreads, h->pcg_smem, h->stream>>>(d, P, opt->max_pcg_iterations, h->pcg_s_in_smem);
+    h->launches++;
+    it = -1;
+  } else if (d.Nf > 0) {
     const int gf = cdiv(d.Nf, 128), gs = cdiv((int64_t)d.Nf * 6, 128);
     CUDA_TRY(cudaMemsetAsync(d.counters + 1, 0, 4, h->stream));
     LAUNCH(h, k_pcg_init, gf, 128, d);
@@ -424,7 +450,7 @@ static int do_step(sba_handle h, int* ls_rounds) {
     if ((rc = do_ls_round(h))) return rc;
     ++rounds;
     LAUNCH(h, k_lm_control, cdiv(d.nwin, 128), 128, d, P);
-    CUDA_TRY(cudaMemcpyAsync(h->h_counters, d.counters, 16, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaMemcpyAsync(h->h_counters, d.counters, 32, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
     if (h->h_counters[3] <= 0 || rounds > 64) break;
   }
@@ -478,6 +504,9 @@ int sba_pcg(sba_handle h, const sba_options* opt, int32_t* iterations) {
   fill_params(h, &o);
   if ((rc = do_pcg(h, &o, iterations))) return rc;
   CUDA_TRY(cudaStreamSynchronize(h->stream));
+  if (iterations && *iterations < 0) {     // single-launch path: the count lives on the device
+    CUDA_TRY(cudaMemcpy(iterations, h->d.counters + 4, 4, cudaMemcpyDeviceToHost));
+  }
   return SBA_OK;
 }
 
@@ -613,9 +642,9 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
     CUDA_TRY(cudaEventRecord(h->ev[1], h->stream));
     int32_t pit = 0;
     if ((rc = do_pcg(h, &o, &pit))) return rc;
-    S.pcg_iterations += pit;
     CUDA_TRY(cudaEventRecord(h->ev[2], h->stream));
-    if ((rc = do_step(h, &ls_rounds))) return rc;      // syncs; h_counters holds [running, -, accepted, -]
+    if ((rc = do_step(h, &ls_rounds))) return rc;      // syncs; h_counters holds [running, -, accepted, -, pcg its]
+    S.pcg_iterations += (pit >= 0) ? pit : h->h_counters[4];
     CUDA_TRY(cudaEventRecord(h->ev[3], h->stream));
     CUDA_TRY(cudaEventSynchronize(h->ev[3]));
     take_lin_time();

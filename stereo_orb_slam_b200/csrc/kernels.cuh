@@ -80,95 +80,147 @@ __global__ void k_project_points(int64_t n, double* __restrict__ pts, double lo,
   if (i < n) pts[i] = clampd(pts[i], lo, hi);
 }
 
-// ------------------------------------------------------------------------------- K1/K2 by point
-// One thread per point, one CTA per point chunk.  Reads idx 4 + uv 16 B per observation and
-// 24 B per point; writes W 144 B per observation, V+gp 72 B per point.
-__global__ void __launch_bounds__(kThreads) k_lin_points(Dev d, DevParams P) {
-  __shared__ double sm[4 * 1];
-  __shared__ double smx[4];
-  const int chunk = blockIdx.x;
-  const int p = d.pchunk_begin[chunk] + threadIdx.x;
-  double cost[1] = {0.0};
-  double gmax = 0.0;
-  if (p < d.pchunk_end[chunk]) {
-    const double X[3] = {d.pts[3 * p], d.pts[3 * p + 1], d.pts[3 * p + 2]};
-    double V[6] = {0, 0, 0, 0, 0, 0}, gp[3] = {0, 0, 0};
-    const int e1 = d.pt_off[p + 1];
-    for (int e = d.pt_off[p]; e < e1; ++e) {
-      CamPre cp;
-      load_campre(d.campre, __ldg(d.pcam + e), cp);
-      const float4 m = __ldg(d.uv_p + e);
-      const float uv[4] = {m.x, m.y, m.z, m.w};
-      double q[3], r[4], D[12];
-      const double s = project(P.pl, P.pr, cp, X, uv, P.rdim, q, r, D);
-      double rho, w;
-      huber(P.huber_delta, s, rho, w);
-      cost[0] += 0.5 * rho;
-      double A[6], h[3], G[9], W[18];
-      form_A_h(D, r, w, A, h);
-      form_G(cp, q, G);
-      accum_point(cp, A, h, G, V, gp, W);
-      double2* Wo = reinterpret_cast<double2*>(d.W + (size_t)e * 18);
+// ------------------------------------------------------------------------------- K1/K2 per chunk
+// One CTA per chunk (<= kObsChunk observations of <= kPointChunk consecutive points), one THREAD PER
+// OBSERVATION: residual, Huber weight, the analytic block algebra of sba_math.cuh.  W (144 B) goes straight to
+// HBM; the point-side sums (V, gp: 9 doubles) and the camera-side operands (A, h, G: 18 doubles) are staged in
+// shared memory and reduced inside the CTA — per point by its thread, per camera slot by one warp — so each
+// observation is read exactly once (idx 4 B + uv 16 B) and nothing is recomputed.  The per-(chunk, slot)
+// camera partials are summed over chunks by k_cam_assemble through a static list (fixed order, no atomics).
+constexpr int kLinThreads = 256;
+constexpr int kCamStride = 19;     // doubles per observation in the camera staging area (odd: no bank conflicts)
+
+__device__ __forceinline__ void point_contrib(const CamPre& c, const double A[6], const double h[3], const double G[9],
+                                              double Vc[9], double W[18]) {
+  double Af[9]; sym3_full(A, Af);
+  double AR[9]; mul33(Af, c.R, AR);
+  Vc[0] = c.R[0] * AR[0] + c.R[3] * AR[3] + c.R[6] * AR[6];
+  Vc[1] = c.R[0] * AR[1] + c.R[3] * AR[4] + c.R[6] * AR[7];
+  Vc[2] = c.R[0] * AR[2] + c.R[3] * AR[5] + c.R[6] * AR[8];
+  Vc[3] = c.R[1] * AR[1] + c.R[4] * AR[4] + c.R[7] * AR[7];
+  Vc[4] = c.R[1] * AR[2] + c.R[4] * AR[5] + c.R[7] * AR[8];
+  Vc[5] = c.R[2] * AR[2] + c.R[5] * AR[5] + c.R[8] * AR[8];
 #pragma unroll
-      for (int i = 0; i < 9; ++i) Wo[i] = make_double2(W[2 * i], W[2 * i + 1]);
-      if (d.r_dbg) {
-        const double sq = sqrt(w);
-        double* ro = d.r_dbg + (size_t)d.perm_p[e] * 4;
-        ro[0] = sq * r[0]; ro[1] = sq * r[1]; ro[2] = sq * r[2]; ro[3] = sq * r[3];
-      }
-    }
+  for (int i = 0; i < 3; ++i) Vc[6 + i] = c.R[i] * h[0] + c.R[3 + i] * h[1] + c.R[6 + i] * h[2];
+  mulT33(G, AR, W);
 #pragma unroll
-    for (int i = 0; i < 6; ++i) d.V[(size_t)p * 6 + i] = V[i];
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      d.gp[(size_t)p * 3 + i] = gp[i];
-      gmax = fmax(gmax, fabs(X[i] - clampd(X[i] - gp[i], P.lo, P.hi)));   // projected-gradient norm
-    }
-  }
-  const double tot = block_sum<1>(cost, sm);
-  const double mx = block_max1(gmax, smx);
-  if (threadIdx.x == 0) { d.lin_part[2 * chunk] = tot; d.lin_part[2 * chunk + 1] = mx; }
+  for (int i = 0; i < 9; ++i) W[9 + i] = AR[i];
 }
 
-// ------------------------------------------------------------------------------ K1/K2 by camera
-// One CTA per camera chunk (<= kCamChunk observations of ONE free camera, camera order).
-// Recomputes the residual algebra (cheaper than storing per-observation Jacobians: 40 B read
-// instead of 216 B written + read) and reduces U (21) + gc (6) over the chunk.
-__global__ void __launch_bounds__(kThreads) k_lin_cameras(Dev d, DevParams P) {
-  __shared__ double sm[4 * 27];
-  const int ch = blockIdx.x;
-  const int c = d.cchunk_cam[ch];
-  CamPre cp;
-  load_campre(d.campre, c, cp);
-  double acc[27];
-#pragma unroll
-  for (int i = 0; i < 27; ++i) acc[i] = 0.0;
-  const int end = d.cchunk_end[ch];
-  for (int i = d.cchunk_begin[ch] + threadIdx.x; i < end; i += kThreads) {
-    const int p = __ldg(d.cpt + i);
-    const float4 m = __ldg(d.uv_c + i);
+__global__ void __launch_bounds__(kLinThreads) k_lin_chunk(Dev d, DevParams P) {
+  extern __shared__ double smem[];
+  __shared__ double sm1[kLinThreads / 32];
+  __shared__ double smx[kLinThreads / 32];
+  const int chunk = blockIdx.x;
+  const int p0 = d.pchunk_begin[chunk], p1 = d.pchunk_end[chunk];
+  const int e0 = d.pt_off[p0], n = d.pt_off[p1] - e0;
+  double* cam_st = smem;                                   // [n * kCamStride]  A(6) h(3) G(9)
+  double* pt_st = smem + (size_t)n * kCamStride;           // [n * 9]           V(6) gp(3)
+  double cost = 0.0;
+  for (int i = threadIdx.x; i < n; i += kLinThreads) {
+    const int e = e0 + i;
+    const int p = __ldg(d.ppt + e);
+    CamPre cp;
+    load_campre(d.campre, __ldg(d.pcam + e), cp);
+    const float4 m = __ldg(d.uv_p + e);
     const float uv[4] = {m.x, m.y, m.z, m.w};
     const double X[3] = {d.pts[3 * (size_t)p], d.pts[3 * (size_t)p + 1], d.pts[3 * (size_t)p + 2]};
     double q[3], r[4], D[12];
     const double s = project(P.pl, P.pr, cp, X, uv, P.rdim, q, r, D);
     double rho, w;
     huber(P.huber_delta, s, rho, w);
+    cost += 0.5 * rho;
     double A[6], h[3], G[9];
     form_A_h(D, r, w, A, h);
     form_G(cp, q, G);
-    accum_camera(A, h, G, acc, acc + 21);
+    double* cs = cam_st + (size_t)i * kCamStride;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) cs[k] = A[k];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) cs[6 + k] = h[k];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) cs[9 + k] = G[k];
+    double Vc[9], W[18];
+    point_contrib(cp, A, h, G, Vc, W);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) pt_st[(size_t)i * 9 + k] = Vc[k];
+    double2* Wo = reinterpret_cast<double2*>(d.W + (size_t)e * 18);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) Wo[k] = make_double2(W[2 * k], W[2 * k + 1]);
+    if (d.r_dbg) {
+      const double sq = sqrt(w);
+      double* ro = d.r_dbg + (size_t)d.perm_p[e] * 4;
+      ro[0] = sq * r[0]; ro[1] = sq * r[1]; ro[2] = sq * r[2]; ro[3] = sq * r[3];
+    }
   }
-  const double tot = block_sum<27>(acc, sm);
-  if (threadIdx.x < 27) d.cpart[(size_t)ch * 27 + threadIdx.x] = tot;
+  __syncthreads();
+  // per point: V, gp (thread per point, observations of a point are consecutive)
+  double gmax = 0.0;
+  for (int p = p0 + threadIdx.x; p < p1; p += kLinThreads) {
+    double acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const int i1 = d.pt_off[p + 1] - e0;
+    for (int i = d.pt_off[p] - e0; i < i1; ++i) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) acc[k] += pt_st[(size_t)i * 9 + k];
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) d.V[(size_t)p * 6 + k] = acc[k];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      d.gp[(size_t)p * 3 + k] = acc[6 + k];
+      const double x = d.pts[(size_t)p * 3 + k];
+      gmax = fmax(gmax, fabs(x - clampd(x - acc[6 + k], P.lo, P.hi)));   // projected-gradient norm
+    }
+  }
+  // per camera slot: U (21) + gc (6), one warp per slot over the slot's observations
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cs0 = d.slot_off[chunk], cs1 = d.slot_off[chunk + 1];
+  for (int cs = cs0 + warp; cs < cs1; cs += kLinThreads / 32) {
+    if (d.fc[d.cs_cam[cs]] < 0) continue;        // a fixed camera is not an unknown (src/bundle_adjuster.cpp:113)
+    double acc[27];
+#pragma unroll
+    for (int k = 0; k < 27; ++k) acc[k] = 0.0;
+    const int j1 = d.cs_obs_off[cs + 1];
+    for (int j = d.cs_obs_off[cs] + lane; j < j1; j += 32) {
+      const double* c = cam_st + (size_t)d.sobs[j] * kCamStride;
+      double A[6], h[3], G[9];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) A[k] = c[k];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) h[k] = c[6 + k];
+#pragma unroll
+      for (int k = 0; k < 9; ++k) G[k] = c[9 + k];
+      accum_camera(A, h, G, acc, acc + 21);
+    }
+#pragma unroll
+    for (int k = 0; k < 27; ++k) {
+      double x = acc[k];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+      if (lane == 0) d.cspart[(size_t)cs * 27 + k] = x;
+    }
+  }
+  // chunk cost and projected-gradient max
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { cost += __shfl_xor_sync(0xffffffffu, cost, o); gmax = fmax(gmax, __shfl_xor_sync(0xffffffffu, gmax, o)); }
+  if (lane == 0) { sm1[warp] = cost; smx[warp] = gmax; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0, mx = 0.0;
+#pragma unroll
+    for (int k = 0; k < kLinThreads / 32; ++k) { t += sm1[k]; mx = fmax(mx, smx[k]); }
+    d.lin_part[2 * chunk] = t; d.lin_part[2 * chunk + 1] = mx;
+  }
 }
 
-// sum the chunk partials of every camera in chunk order -> U [Nc*21], gc [Nc*6]
-__global__ void k_cam_finish(Dev d) {
+// thread per (camera, element): U (21) and gc (6) = sum of the camera's chunk-slot partials in list order
+__global__ void k_cam_assemble(Dev d) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= d.Nc * 27) return;
   const int c = t / 27, e = t - c * 27;
   double s = 0.0;
-  for (int ch = d.cam_chunk_off[c]; ch < d.cam_chunk_off[c + 1]; ++ch) s += d.cpart[(size_t)ch * 27 + e];
+  if (d.fc[c] >= 0)
+    for (int j = d.cam_part_off[c]; j < d.cam_part_off[c + 1]; ++j) s += d.cspart[(size_t)d.cam_part[j] * 27 + e];
   if (e < 21) d.U[(size_t)c * 21 + e] = s;
   else d.gc[(size_t)c * 6 + (e - 21)] = s;
 }
@@ -222,96 +274,146 @@ __device__ __forceinline__ double lm_damp(double sc2, double hjj, double radius)
   return clampd(sc2 * hjj, 1e-6, 1e32) / (sc2 * radius);
 }
 
-// thread per point: Vinv = (V + Dp)^-1 (6 sym), tp = Vinv gp
-__global__ void __launch_bounds__(kThreads) k_point_damp(Dev d) {
-  const int chunk = blockIdx.x;
-  const int p = d.pchunk_begin[chunk] + threadIdx.x;
-  if (p >= d.pchunk_end[chunk]) return;
-  const int w = d.pchunk_win[chunk];
-  const double radius = d.w_radius[w];
-  double V[6];
-#pragma unroll
-  for (int i = 0; i < 6; ++i) V[i] = d.V[(size_t)p * 6 + i];
-  V[0] += lm_damp(d.sc2p[(size_t)p * 3 + 0], V[0], radius);
-  V[3] += lm_damp(d.sc2p[(size_t)p * 3 + 1], V[3], radius);
-  V[5] += lm_damp(d.sc2p[(size_t)p * 3 + 2], V[5], radius);
-  double Vi[6];
-  if (!inv_sym3(V, Vi)) d.w_fail[w] = 1;   // benign race: every writer stores 1
-  const double g0 = d.gp[(size_t)p * 3], g1 = d.gp[(size_t)p * 3 + 1], g2 = d.gp[(size_t)p * 3 + 2];
-#pragma unroll
-  for (int i = 0; i < 6; ++i) d.Vinv[(size_t)p * 6 + i] = Vi[i];
-  d.tp[(size_t)p * 3 + 0] = Vi[0] * g0 + Vi[1] * g1 + Vi[2] * g2;
-  d.tp[(size_t)p * 3 + 1] = Vi[1] * g0 + Vi[3] * g1 + Vi[4] * g2;
-  d.tp[(size_t)p * 3 + 2] = Vi[2] * g0 + Vi[4] * g1 + Vi[5] * g2;
-}
-
 __device__ __forceinline__ void load_W(const double* __restrict__ W, size_t pos, double out[18]) {
   const double2* s = reinterpret_cast<const double2*>(W + pos * 18);
 #pragma unroll
   for (int i = 0; i < 9; ++i) { const double2 v = __ldg(s + i); out[2 * i] = v.x; out[2 * i + 1] = v.y; }
 }
 
-// One CTA per pair chunk (<= kPairChunk entries of ONE upper block (i,j), sorted by point):
-//   partial = sum_entries  W_a Vinv_p W_b^T          (6x6)
-__global__ void __launch_bounds__(kThreads) k_schur_pairs(Dev d) {
-  __shared__ double sm[4 * 36];
-  const int ch = blockIdx.x;
-  double acc[36];
-#pragma unroll
-  for (int i = 0; i < 36; ++i) acc[i] = 0.0;
-  const int64_t end = d.schunk_end[ch];
-  for (int64_t it = d.schunk_begin[ch] + threadIdx.x; it < end; it += kThreads) {
-    const int a = __ldg(d.ent_a + it), b = __ldg(d.ent_b + it);
-    const int p = __ldg(d.ppt + a);
-    double Wa[18], Wb[18], Vi[6];
-    load_W(d.W, (size_t)a, Wa);
-    load_W(d.W, (size_t)b, Wb);
-#pragma unroll
-    for (int i = 0; i < 6; ++i) Vi[i] = __ldg(d.Vinv + (size_t)p * 6 + i);
-#pragma unroll
-    for (int i = 0; i < 6; ++i) {
-      const double w0 = Wa[3 * i], w1 = Wa[3 * i + 1], w2 = Wa[3 * i + 2];
-      const double y0 = w0 * Vi[0] + w1 * Vi[1] + w2 * Vi[2];
-      const double y1 = w0 * Vi[1] + w1 * Vi[3] + w2 * Vi[4];
-      const double y2 = w0 * Vi[2] + w1 * Vi[4] + w2 * Vi[5];
-#pragma unroll
-      for (int j = 0; j < 6; ++j) acc[6 * i + j] += y0 * Wb[3 * j] + y1 * Wb[3 * j + 1] + y2 * Wb[3 * j + 2];
-    }
-  }
-  const double tot = block_sum<36>(acc, sm);
-  if (threadIdx.x < 36) d.spart[(size_t)ch * 36 + threadIdx.x] = tot;
+// One CTA per chunk, the whole of K3 for the chunk's points in one pass over W:
+//   1. thread per point: Vinv = (V + D)^-1, tp = Vinv gp                    (kept in shared memory + HBM)
+//   2. the chunk's W (contiguous in point order) staged ONCE into shared memory
+//   3. one warp per local block (slot pair sa, sb): sum over the chunk's points of  W_a Vinv W_b^T  for the
+//      point's observations a in slot sa, b in slot sb (every ordered pair on the diagonal, duplicates
+//      included) -> spart[lb];  one warp per free slot: sum of W tp -> rpart[cs]
+// S and the right-hand side are assembled from the partials in list order by k_schur_assemble / k_rhs_finish.
+constexpr int kSchurThreads = 256;
+constexpr int kWStride = 19;       // doubles per observation in the W staging area
+
+__host__ __device__ __forceinline__ size_t schur_smem_bytes(int n, int np) {
+  return ((size_t)n * kWStride + (size_t)np * 9) * 8 + (size_t)(np + 1) * 4 + (size_t)n;
 }
 
-// thread per (upper block, element): Su = - sum of its chunk partials (U + D added in k_cam_prepare,
-// after the multi-GPU all-reduce of Su)
+__global__ void __launch_bounds__(kSchurThreads) k_schur_chunk(Dev d) {
+  extern __shared__ double smem[];
+  const int chunk = blockIdx.x;
+  const int p0 = d.pchunk_begin[chunk], p1 = d.pchunk_end[chunk], np = p1 - p0;
+  const int e0 = d.pt_off[p0], n = d.pt_off[p1] - e0;
+  const int w = d.pchunk_win[chunk];
+  double* Wst = smem;                                   // [n * kWStride]
+  double* Vi = Wst + (size_t)n * kWStride;              // [np * 6]
+  double* tp = Vi + (size_t)np * 6;                     // [np * 3]
+  int* pofs = reinterpret_cast<int*>(tp + (size_t)np * 3);      // [np + 1] chunk-local observation offsets
+  uint8_t* osl = reinterpret_cast<uint8_t*>(pofs + np + 1);     // [n]
+  const double radius = d.w_radius[w];
+  for (int pl = threadIdx.x; pl <= np; pl += kSchurThreads) pofs[pl] = d.pt_off[p0 + pl] - e0;
+  for (int i = threadIdx.x; i < n; i += kSchurThreads) osl[i] = d.oslot[e0 + i];
+  for (int pl = threadIdx.x; pl < np; pl += kSchurThreads) {
+    const int p = p0 + pl;
+    double V[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) V[i] = d.V[(size_t)p * 6 + i];
+    V[0] += lm_damp(d.sc2p[(size_t)p * 3 + 0], V[0], radius);
+    V[3] += lm_damp(d.sc2p[(size_t)p * 3 + 1], V[3], radius);
+    V[5] += lm_damp(d.sc2p[(size_t)p * 3 + 2], V[5], radius);
+    double inv[6];
+    if (!inv_sym3(V, inv)) d.w_fail[w] = 1;   // benign race: every writer stores 1
+    const double g0 = d.gp[(size_t)p * 3], g1 = d.gp[(size_t)p * 3 + 1], g2 = d.gp[(size_t)p * 3 + 2];
+    const double t0 = inv[0] * g0 + inv[1] * g1 + inv[2] * g2;
+    const double t1 = inv[1] * g0 + inv[3] * g1 + inv[4] * g2;
+    const double t2 = inv[2] * g0 + inv[4] * g1 + inv[5] * g2;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) { Vi[pl * 6 + i] = inv[i]; d.Vinv[(size_t)p * 6 + i] = inv[i]; }
+    tp[pl * 3] = t0; tp[pl * 3 + 1] = t1; tp[pl * 3 + 2] = t2;
+    d.tp[(size_t)p * 3] = t0; d.tp[(size_t)p * 3 + 1] = t1; d.tp[(size_t)p * 3 + 2] = t2;
+  }
+  {
+    const double* Wg = d.W + (size_t)e0 * 18;
+    for (int i = threadIdx.x; i < n * 18; i += kSchurThreads) {
+      const int o = i / 18, k = i - 18 * o;
+      Wst[(size_t)o * kWStride + k] = __ldg(Wg + i);
+    }
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int NW = kSchurThreads / 32;
+  // ---- local blocks
+  const int lb0 = d.lb_off[chunk], lb1 = d.lb_off[chunk + 1];
+  for (int lb = lb0 + warp; lb < lb1; lb += NW) {
+    const int sa = d.lb_sa[lb], sb = d.lb_sb[lb];
+    double acc[36];
+#pragma unroll
+    for (int i = 0; i < 36; ++i) acc[i] = 0.0;
+    for (int pl = lane; pl < np; pl += 32) {
+      const int o0 = pofs[pl], o1 = pofs[pl + 1];
+      for (int a = o0; a < o1; ++a) {
+        if (osl[a] != sa) continue;
+        const double* Wa = Wst + (size_t)a * kWStride;
+        const double* vi = Vi + pl * 6;
+        double Y[18];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+          const double w0 = Wa[3 * i], w1 = Wa[3 * i + 1], w2 = Wa[3 * i + 2];
+          Y[3 * i] = w0 * vi[0] + w1 * vi[1] + w2 * vi[2];
+          Y[3 * i + 1] = w0 * vi[1] + w1 * vi[3] + w2 * vi[4];
+          Y[3 * i + 2] = w0 * vi[2] + w1 * vi[4] + w2 * vi[5];
+        }
+        for (int b = o0; b < o1; ++b) {
+          if (osl[b] != sb) continue;
+          const double* Wb = Wst + (size_t)b * kWStride;
+#pragma unroll
+          for (int j = 0; j < 6; ++j) {
+            const double b0 = Wb[3 * j], b1 = Wb[3 * j + 1], b2 = Wb[3 * j + 2];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) acc[6 * i + j] += Y[3 * i] * b0 + Y[3 * i + 1] * b1 + Y[3 * i + 2] * b2;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 36; ++i) {
+      double x = acc[i];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+      if (lane == 0) d.spart[(size_t)lb * 36 + i] = x;
+    }
+  }
+  // ---- right-hand side partials: sum over the slot's observations of W_e tp[point(e)]
+  const int cs0 = d.slot_off[chunk], cs1 = d.slot_off[chunk + 1];
+  for (int cs = cs0 + warp; cs < cs1; cs += NW) {
+    if (d.fc[d.cs_cam[cs]] < 0) continue;
+    double acc[6] = {0, 0, 0, 0, 0, 0};
+    const int j1 = d.cs_obs_off[cs + 1];
+    for (int j = d.cs_obs_off[cs] + lane; j < j1; j += 32) {
+      const int o = d.sobs[j];
+      const int pl = __ldg(d.ppt + e0 + o) - p0;
+      const double* W = Wst + (size_t)o * kWStride;
+      const double t0 = tp[pl * 3], t1 = tp[pl * 3 + 1], t2 = tp[pl * 3 + 2];
+#pragma unroll
+      for (int r = 0; r < 6; ++r) acc[r] += W[3 * r] * t0 + W[3 * r + 1] * t1 + W[3 * r + 2] * t2;
+    }
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+      double x = acc[r];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+      if (lane == 0) d.rpart[(size_t)cs * 6 + r] = x;
+    }
+  }
+}
+
+// thread per (upper block, element): Su = - sum of its local-block partials in list order (U + D are added in
+// k_cam_prepare, after the multi-GPU all-reduce of Su)
 __global__ void k_schur_assemble(Dev d) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= (int64_t)d.nbu * 36) return;
   const int b = (int)(t / 36), e = (int)(t - 36 * (int64_t)b);
   double s = 0.0;
-  for (int ch = d.blk_chunk_off[b]; ch < d.blk_chunk_off[b + 1]; ++ch) s += d.spart[(size_t)ch * 36 + e];
+  for (int j = d.blk_part_off[b]; j < d.blk_part_off[b + 1]; ++j) s += d.spart[(size_t)d.blk_part[j] * 36 + e];
   d.Su[t] = -s;
 }
 
-// rhs partials, one CTA per camera chunk:  sum_obs W_e tp[point(e)]   (6)
-__global__ void __launch_bounds__(kThreads) k_rhs_cameras(Dev d) {
-  __shared__ double sm[4 * 6];
-  const int ch = blockIdx.x;
-  double acc[6] = {0, 0, 0, 0, 0, 0};
-  const int end = d.cchunk_end[ch];
-  for (int i = d.cchunk_begin[ch] + threadIdx.x; i < end; i += kThreads) {
-    const int pos = __ldg(d.cpos + i), p = __ldg(d.cpt + i);
-    double W[18];
-    load_W(d.W, (size_t)pos, W);
-    const double t0 = __ldg(d.tp + (size_t)p * 3), t1 = __ldg(d.tp + (size_t)p * 3 + 1), t2 = __ldg(d.tp + (size_t)p * 3 + 2);
-#pragma unroll
-    for (int r = 0; r < 6; ++r) acc[r] += W[3 * r] * t0 + W[3 * r + 1] * t1 + W[3 * r + 2] * t2;
-  }
-  const double tot = block_sum<6>(acc, sm);
-  if (threadIdx.x < 6) d.rpart[(size_t)ch * 6 + threadIdx.x] = tot;
-}
-
-// thread per (camera, 6): rsum[c*6+i] = sum of chunk partials (kept separate from gc so that a
+// thread per (free camera, 6): rsum = sum of the camera's chunk-slot partials (kept separate from gc so that a
 // multi-GPU run can all-reduce it together with Su)
 __global__ void k_rhs_finish(Dev d, double* __restrict__ rsum) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -319,7 +421,7 @@ __global__ void k_rhs_finish(Dev d, double* __restrict__ rsum) {
   const int f = t / 6, i = t - 6 * f;
   const int c = d.free2cam[f];
   double s = 0.0;
-  for (int ch = d.cam_chunk_off[c]; ch < d.cam_chunk_off[c + 1]; ++ch) s += d.rpart[(size_t)ch * 6 + i];
+  for (int j = d.cam_part_off[c]; j < d.cam_part_off[c + 1]; ++j) s += d.rpart[(size_t)d.cam_part[j] * 6 + i];
   rsum[t] = s;
 }
 
@@ -905,12 +1007,11 @@ __global__ void k_apply_cams(Dev d) {
   if (d.w_accept[d.cam_win[t / 6]]) d.poses[t] = d.poses_new[t];
 }
 
-// permute the caller's observations into the point-sorted and camera-sorted views
-__global__ void k_permute_uv(Dev d, const float4* __restrict__ uv_in, float4* __restrict__ uv_p, float4* __restrict__ uv_c) {
+// permute the caller's observations into the point-sorted view
+__global__ void k_permute_uv(Dev d, const float4* __restrict__ uv_in, float4* __restrict__ uv_p) {
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= d.Nobs) return;
   uv_p[e] = uv_in[d.perm_p[e]];
-  uv_c[e] = uv_in[d.perm_p[d.cpos[e]]];
 }
 
 }  // namespace sba

@@ -58,6 +58,7 @@ struct sba_handle_s {
   double last_radius = 1e4;
   // single-launch PCG (k_pcg_window): usable when every window's system fits one CTA
   bool pcg_window_ok = false; int pcg_s_in_smem = 0; size_t pcg_smem = 0;
+  size_t lin_smem = 0, schur_smem = 0;   // dynamic shared memory of the per-chunk kernels (largest chunk)
 
   template <typename T>
   int alloc(T** p, size_t n) {
@@ -182,27 +183,27 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   Dev& d = h->d;
   d.Nc = H.Nc; d.Np = H.Np; d.Nf = H.Nf; d.nwin = H.nwin; d.Nobs = H.Nobs;
   d.nbu = (int32_t)H.blk_row.size(); d.npchunk = (int32_t)H.pchunk_begin.size();
-  d.ncchunk = (int32_t)H.cchunk_cam.size(); d.nschunk = (int32_t)H.schunk_blk.size();
+  d.ncs = (int32_t)H.cs_cam.size(); d.nlb = (int32_t)H.lb_blk.size();
   int rc = 0;
 #define UP(field) if ((rc = h->upload(&d.field, H.field))) return rc;
   UP(fc) UP(free2cam) UP(cam_win) UP(fcam_win) UP(win_cam_off) UP(win_fc_off) UP(win_pchunk_off)
-  UP(pt_off) UP(perm_p) UP(pcam) UP(ppt) UP(cam_off) UP(cpos) UP(cpt)
+  UP(pt_off) UP(perm_p) UP(pcam) UP(ppt)
   UP(pchunk_begin) UP(pchunk_end) UP(pchunk_win)
-  UP(cchunk_cam) UP(cchunk_begin) UP(cchunk_end) UP(cam_chunk_off)
-  UP(blk_row) UP(blk_col) UP(blk_chunk_off) UP(schunk_blk) UP(diag_blk)
-  UP(schunk_begin) UP(schunk_end) UP(ent_a) UP(ent_b) UP(row_ptr) UP(bsr_col) UP(bsr_blk)
+  UP(slot_off) UP(cs_cam) UP(cs_obs_off) UP(lb_off) UP(lb_blk) UP(oslot) UP(lb_sa) UP(lb_sb) UP(sobs)
+  UP(blk_row) UP(blk_col) UP(diag_blk) UP(blk_part_off) UP(blk_part) UP(cam_part_off) UP(cam_part)
+  UP(row_ptr) UP(bsr_col) UP(bsr_blk)
 #undef UP
   const size_t nobs = (size_t)H.Nobs, nc = (size_t)H.Nc, np = (size_t)H.Np, nf = (size_t)H.Nf, nw = (size_t)H.nwin;
 #define AL(ptr, n) if ((rc = h->alloc(&ptr, (n)))) return rc;
-  float4 *uvp, *uvc;
-  AL(uvp, nobs) AL(uvc, nobs) d.uv_p = uvp; d.uv_c = uvc;
+  float4* uvp;
+  AL(uvp, nobs) d.uv_p = uvp;
   AL(h->uv_in, (size_t)Nobs)
   AL(d.poses, nc * 6) AL(d.poses_new, nc * 6) AL(d.pts, np * 3) AL(d.pts_new, np * 3)
   AL(d.campre, nc) AL(d.campre_new, nc)
   AL(d.W, nobs * 18) AL(d.V, np * 6) AL(d.gp, np * 3) AL(d.Vinv, np * 6) AL(d.tp, np * 3)
-  AL(d.U, nc * 21) AL(d.gc, nc * 6) AL(d.cpart, (size_t)d.ncchunk * 27)
+  AL(d.U, nc * 21) AL(d.gc, nc * 6) AL(d.cspart, (size_t)d.ncs * 27)
   AL(d.sc2c, nc * 6) AL(d.sc2p, np * 3) AL(d.lin_part, (size_t)d.npchunk * 2)
-  AL(d.spart, (size_t)d.nschunk * 36) AL(d.Su, (size_t)d.nbu * 36) AL(d.rpart, (size_t)d.ncchunk * 6)
+  AL(d.spart, (size_t)d.nlb * 36) AL(d.Su, (size_t)d.nbu * 36) AL(d.rpart, (size_t)d.ncs * 6)
   AL(d.rhs, nf * 6) AL(h->rsum, nf * 6) AL(d.Minv, nf * 36)
   AL(d.x, nf * 6) AL(d.r, nf * 6) AL(d.z, nf * 6) AL(d.p, nf * 6) AL(d.Ap, nf * 6)
   AL(d.dp, np * 3) AL(d.step_part, (size_t)d.npchunk * 4) AL(d.ls_part, (size_t)d.npchunk * 3)
@@ -229,6 +230,17 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   CUDA_TRY(cudaMemsetAsync(d.V, 0, std::max<size_t>(1, np * 6) * 8, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.gp, 0, std::max<size_t>(1, np * 3) * 8, h->stream));
   CUDA_TRY(cudaStreamSynchronize(h->stream));
+  {
+    int nmax = 0, npmax = 0;
+    for (size_t c = 0; c < H.pchunk_begin.size(); ++c) {
+      nmax = std::max(nmax, H.pt_off[H.pchunk_end[c]] - H.pt_off[H.pchunk_begin[c]]);
+      npmax = std::max(npmax, H.pchunk_end[c] - H.pchunk_begin[c]);
+    }
+    h->lin_smem = (size_t)nmax * (kCamStride + 9) * 8;
+    h->schur_smem = schur_smem_bytes(nmax, npmax);
+    CUDA_TRY(cudaFuncSetAttribute(k_lin_chunk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->lin_smem, 1024)));
+    CUDA_TRY(cudaFuncSetAttribute(k_schur_chunk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->schur_smem, 1024)));
+  }
   {
     // per-window size of the reduced system -> can one CTA hold it?
     int nf_max = 0; int64_t nb_max = 0;
@@ -290,7 +302,7 @@ int sba_set_measurements(sba_handle h, const float* obs_uv, const double* p_l, c
   const Dev& d = h->d;
   if (h->nobs_all > 0)
     CUDA_TRY(cudaMemcpyAsync(h->uv_in, obs_uv, (size_t)h->nobs_all * 16, cudaMemcpyHostToDevice, h->stream));
-  LAUNCH(h, k_permute_uv, cdiv(d.Nobs, 256), 256, d, h->uv_in, const_cast<float4*>(d.uv_p), const_cast<float4*>(d.uv_c));
+  LAUNCH(h, k_permute_uv, cdiv(d.Nobs, 256), 256, d, h->uv_in, const_cast<float4*>(d.uv_p));
   CUDA_TRY(cudaGetLastError());
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   std::memcpy(h->P.pl, p_l, 96); std::memcpy(h->P.pr, p_r, 96);
@@ -329,9 +341,8 @@ static int do_linearize(sba_handle h) {
   Dev& d = h->d;
   const DevParams& P = h->P;
   LAUNCH(h, k_cam_precompute, cdiv(d.Nc, 128), 128, d.Nc, d.poses, d.campre);
-  LAUNCH(h, k_lin_points, d.npchunk, kThreads, d, P);
-  LAUNCH(h, k_lin_cameras, d.ncchunk, kThreads, d, P);
-  LAUNCH(h, k_cam_finish, cdiv((int64_t)d.Nc * 27, 256), 256, d);
+  if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P); h->launches++; }
+  LAUNCH(h, k_cam_assemble, cdiv((int64_t)d.Nc * 27, 256), 256, d);
   if (h->comm.active()) {
     std::string _err;
     if (!h->comm.allreduce(d.U, (size_t)d.Nc * 21, false, h->stream, &_err) ||
@@ -354,10 +365,8 @@ static int do_linearize(sba_handle h) {
 // K3: damped Schur complement at the per-window radii in d.w_radius.
 static int do_schur(sba_handle h) {
   Dev& d = h->d;
-  LAUNCH(h, k_point_damp, d.npchunk, kThreads, d);
-  LAUNCH(h, k_schur_pairs, d.nschunk, kThreads, d);
+  if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d); h->launches++; }
   LAUNCH(h, k_schur_assemble, cdiv((int64_t)d.nbu * 36, 256), 256, d);
-  LAUNCH(h, k_rhs_cameras, d.ncchunk, kThreads, d);
   LAUNCH(h, k_rhs_finish, cdiv((int64_t)d.Nf * 6, 128), 128, d, h->rsum);
   if (h->comm.active()) {
     std::string _err;
@@ -558,9 +567,9 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
     if (flush_l2) CUDA_TRY(cudaMemsetAsync(h->flush, i & 0xff, flush_bytes, h->stream));
     CUDA_TRY(cudaEventRecord(h->ev[6], h->stream));
     switch (stage) {
-      case 0: LAUNCH(h, k_lin_points, d.npchunk, kThreads, d, P); break;
-      case 1: LAUNCH(h, k_lin_cameras, d.ncchunk, kThreads, d, P); break;
-      case 2: LAUNCH(h, k_schur_pairs, d.nschunk, kThreads, d); break;
+      case 0: if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P); h->launches++; } break;
+      case 1: LAUNCH(h, k_cam_assemble, cdiv((int64_t)d.Nc * 27, 256), 256, d); break;
+      case 2: if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d); h->launches++; } break;
       case 3: if ((rc = do_linearize(h))) return rc; break;
       case 4: if ((rc = do_schur(h))) return rc; break;
       case 8: if ((rc = do_linearize(h))) return rc; if ((rc = do_schur(h))) return rc; break;
@@ -821,7 +830,12 @@ int sba_get_sorted_views(sba_handle h, int32_t* by_point, int32_t* by_camera) {
   if (!h || !h->has_structure) { set_error("no structure"); return SBA_INVALID_ARGUMENT; }
   const HostStructure& H = h->H;
   if (by_point) std::memcpy(by_point, H.perm_p.data(), (size_t)H.Nobs * 4);
-  if (by_camera) for (int64_t i = 0; i < H.Nobs; ++i) by_camera[i] = H.perm_p[H.cpos[i]];
+  if (by_camera) {   // camera order: grouped by camera, ascending point-order position inside a camera
+    std::vector<int64_t> off((size_t)H.Nc + 1, 0);
+    for (int64_t e = 0; e < H.Nobs; ++e) off[H.pcam[e] + 1]++;
+    for (int c = 0; c < H.Nc; ++c) off[c + 1] += off[c];
+    for (int64_t e = 0; e < H.Nobs; ++e) by_camera[off[H.pcam[e]]++] = H.perm_p[e];
+  }
   return SBA_OK;
 }
 

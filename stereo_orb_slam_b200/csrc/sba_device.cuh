@@ -14,20 +14,19 @@ struct DevParams {   // solver constants, by value
 };
 
 struct Dev {
-  int32_t Nc, Np, Nf, nwin, nbu, npchunk, ncchunk, nschunk;
+  int32_t Nc, Np, Nf, nwin, nbu, npchunk, ncs, nlb;
   int64_t Nobs;
-  // ---- structure (const)
+  // ---- structure (const): see sba_internal.h
   const int32_t *fc, *free2cam, *cam_win, *fcam_win, *win_cam_off, *win_fc_off, *win_pchunk_off;
-  const int32_t *pt_off, *perm_p, *pcam, *ppt, *cam_off, *cpos, *cpt;
+  const int32_t *pt_off, *perm_p, *pcam, *ppt;
   const int32_t *pchunk_begin, *pchunk_end, *pchunk_win;
-  const int32_t *cchunk_cam, *cchunk_begin, *cchunk_end, *cam_chunk_off;
-  const int32_t *blk_row, *blk_col, *blk_chunk_off, *schunk_blk, *diag_blk;
-  const int64_t *schunk_begin, *schunk_end;
-  const int32_t *ent_a, *ent_b;
+  const int32_t *slot_off, *cs_cam, *cs_obs_off, *lb_off, *lb_blk;
+  const uint8_t *oslot, *lb_sa, *lb_sb;
+  const uint16_t *sobs;
+  const int32_t *blk_row, *blk_col, *diag_blk, *blk_part_off, *blk_part, *cam_part_off, *cam_part;
   const int32_t *row_ptr, *bsr_col, *bsr_blk;
   // ---- measurements (const during a solve)
   const float4 *uv_p;   // [Nobs] point order
-  const float4 *uv_c;   // [Nobs] camera order
   // ---- state
   double *poses, *poses_new;     // [Nc*6]
   double *pts, *pts_new;         // [Np*3]
@@ -37,14 +36,14 @@ struct Dev {
   double *V, *gp;                // [Np*6], [Np*3]
   double *Vinv, *tp;             // [Np*6], [Np*3]
   double *U, *gc;                // [Nc*21], [Nc*6]
-  double *cpart;                 // [ncchunk*27]
+  double *cspart;                // [ncs*27] per chunk-slot partial of U (21) and gc (6)
   double *sc2c, *sc2p;           // Jacobi scale^2 [Nc*6], [Np*3]
   double *lin_part;              // [npchunk*2] cost, gmax
   double *r_dbg;                 // [Nobs*4] or null
   // ---- Schur
-  double *spart;                 // [nschunk*36]
+  double *spart;                 // [nlb*36] per local-block partial of sum W Vinv W^T
   double *Su;                    // [nbu*36]
-  double *rpart;                 // [ncchunk*6]
+  double *rpart;                 // [ncs*6] per chunk-slot partial of sum W tp
   double *rhs;                   // [Nf*6]
   double *Minv;                  // [Nf*36]
   // ---- PCG vectors [Nf*6]

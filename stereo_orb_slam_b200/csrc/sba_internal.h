@@ -6,17 +6,24 @@
 
 namespace sba {
 
-constexpr int kThreads = 128;        // CTA size of every chunked kernel
-constexpr int kPointChunk = 128;     // points per CTA (thread per point)
-constexpr int kCamChunk = 1024;      // camera-ordered observations per CTA
-constexpr int kPairChunk = 1024;     // pair entries per CTA
+constexpr int kThreads = 128;        // CTA size of the thread-per-point kernels
+constexpr int kPointChunk = 128;     // max points per chunk
+constexpr int kObsChunk = 512;       // max observations per chunk (= CTA size of the thread-per-observation kernels)
+constexpr int kMaxSlots = 255;       // distinct cameras per chunk (slot index is a byte)
 
 // Everything that depends only on (obs_cam, obs_pt, cam_fixed, windows): built once on the host
 // (reference: the index build of src/bundle_adjuster.cpp:57-110 fixes obs->cam/pt; the rest is new).
+//
+// Unit of work = CHUNK: a run of consecutive points (<= kPointChunk points, <= kObsChunk observations, one
+// window, one rank).  In the reference's first-appearance point numbering neighbouring points are seen by the
+// same few cameras, so a chunk touches a handful of cameras ("slots") and a handful of blocks of the reduced
+// camera matrix ("local blocks"); every cross-observation reduction (per point, per camera, per block) is first
+// done inside the chunk's CTA and then summed over chunks through static lists, in a fixed order, without atomics.
 struct HostStructure {
   int32_t Nc = 0, Np = 0, Nf = 0, nwin = 0;
   int64_t Nobs = 0;          // observations held by this rank (all of them on 1 GPU)
   int32_t pt_begin = 0, pt_end = 0;   // owned point range (multi-GPU shard); [0,Np) on 1 GPU
+  int32_t obs_cap = kObsChunk;
 
   std::vector<int32_t> fc;            // [Nc] free-camera index or -1
   std::vector<int32_t> free2cam;      // [Nf]
@@ -29,22 +36,25 @@ struct HostStructure {
   std::vector<int32_t> perm_p;        // [Nobs]   input observation index at position e
   std::vector<int32_t> pcam;          // [Nobs]   camera at position e
   std::vector<int32_t> ppt;           // [Nobs]   point at position e
-  // camera order (positions i, grouped by camera, stable)
-  std::vector<int32_t> cam_off;       // [Nc+1]
-  std::vector<int32_t> cpos;          // [Nobs]   point-order position of camera-order position i
-  std::vector<int32_t> cpt;           // [Nobs]   point at camera-order position i
-  // CTA work tables
-  std::vector<int32_t> pchunk_begin, pchunk_end, pchunk_win;   // point chunks (never span windows)
+  // chunks (owned points only)
+  std::vector<int32_t> pchunk_begin, pchunk_end, pchunk_win;   // point range and window of chunk c
   std::vector<int32_t> win_pchunk_off;                          // [nwin+1]
-  std::vector<int32_t> cchunk_cam, cchunk_begin, cchunk_end;    // camera chunks (free cameras only)
-  std::vector<int32_t> cam_chunk_off;                           // [Nc+1]
-  // reduced camera matrix: upper blocks (row <= col, free indices), sorted (row, col)
+  // camera slots: chunk c owns slots cs in [slot_off[c], slot_off[c+1])
+  std::vector<int32_t> slot_off;                                // [nchunk+1]
+  std::vector<int32_t> cs_cam;                                  // [ncs] camera of chunk-slot cs
+  std::vector<int32_t> cs_obs_off;                              // [ncs+1] range of sobs (absolute positions)
+  std::vector<uint8_t> oslot;                                   // [Nobs] slot (local to its chunk) of position e
+  std::vector<uint16_t> sobs;                                   // [Nobs] chunk-local obs index, grouped by slot
+  // local blocks: chunk c owns lb in [lb_off[c], lb_off[c+1]); slots sa, sb with fc[sa] <= fc[sb], both free
+  std::vector<int32_t> lb_off;                                  // [nchunk+1]
+  std::vector<uint8_t> lb_sa, lb_sb;                            // [nlb]
+  std::vector<int32_t> lb_blk;                                  // [nlb] upper block id
+  // reduced camera matrix: upper blocks (row <= col, free indices), sorted (row, col); partial lists
   std::vector<int32_t> blk_row, blk_col;                        // [nbu]
-  std::vector<int64_t> blk_ent_off;                             // [nbu+1]
-  std::vector<int32_t> ent_a, ent_b;                            // [E] point-order positions
-  std::vector<int32_t> schunk_blk;                              // [nsch]
-  std::vector<int64_t> schunk_begin, schunk_end;
-  std::vector<int32_t> blk_chunk_off;                           // [nbu+1]
+  std::vector<int32_t> blk_part_off;                            // [nbu+1]
+  std::vector<int32_t> blk_part;                                // [nlb] lb indices, ascending
+  std::vector<int32_t> cam_part_off;                            // [Nc+1]
+  std::vector<int32_t> cam_part;                                // [ncs] chunk-slot indices, ascending
   std::vector<int32_t> diag_blk;                                // [Nf] upper-block index of (i,i)
   // full pattern in block-CSR for the PCG mat-vec: entry -> (col, upper block, transposed?)
   std::vector<int32_t> row_ptr;                                 // [Nf+1]

@@ -1,6 +1,6 @@
-// structure.cpp — one-off host build of the index tables the kernels run on:
-// point-sorted and camera-sorted observation views, CTA work chunks, the pair list and the block
-// pattern of the reduced camera matrix.
+// structure.cpp — one-off host build of the index tables the kernels run on: the point-sorted observation
+// view, the chunks with their camera slots and local blocks, and the block pattern of the reduced camera
+// matrix with the static partial lists that make every reduction fixed-order and atomic-free.
 //
 // reference: the observation -> (camera, point) indexing comes from the pack loop
 // (src/bundle_adjuster.cpp:57-110); the gauge (first camera constant, :113) decides which cameras
@@ -16,9 +16,37 @@
 namespace sba {
 
 namespace {
-struct Ent {
-  int32_t col, a, b;  // a,b: local point-order positions, or -1 when the point is not owned (pattern only)
-};
+
+struct ChunkRange { int32_t p0, p1, win; bool owned; };
+
+// chunk boundaries over ALL points (unowned ones only feed the block pattern): never across a window, never
+// across the owned range, <= kPointChunk points, <= obs_cap observations
+bool make_chunks(const HostStructure& H, const std::vector<int32_t>& gpt_off, int obs_cap, std::vector<ChunkRange>* out,
+                 std::string* err) {
+  out->clear();
+  for (int w = 0; w < H.nwin; ++w) {
+    int p = H.win_pt_off[w];
+    const int pend = H.win_pt_off[w + 1];
+    while (p < pend) {
+      const bool owned = (p >= H.pt_begin && p < H.pt_end);
+      int limit = pend;
+      if (owned) limit = std::min(limit, H.pt_end);
+      else if (p < H.pt_begin) limit = std::min(limit, H.pt_begin);
+      int q = p;
+      int nobs = 0;
+      while (q < limit && q - p < kPointChunk) {
+        const int k = gpt_off[q + 1] - gpt_off[q];
+        if (k > kMaxSlots) { *err = "a point has more than 255 observations (unsupported track length)"; return false; }
+        if (nobs + k > obs_cap) break;
+        nobs += k; ++q;
+      }
+      out->push_back(ChunkRange{p, q, w, owned});
+      p = q;
+    }
+  }
+  return true;
+}
+
 }  // namespace
 
 std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32_t* obs_cam, const int32_t* obs_pt,
@@ -96,103 +124,151 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     const int32_t k = gperm[base + e];
     H.perm_p[e] = k; H.pcam[e] = obs_cam[k]; H.ppt[e] = obs_pt[k];
   }
-  // ---- camera order over local positions (inside a camera: ascending point-order position)
-  H.cam_off.assign(Nc + 1, 0);
-  for (int64_t e = 0; e < Nobs; ++e) H.cam_off[H.pcam[e] + 1]++;
-  for (int c = 0; c < Nc; ++c) H.cam_off[c + 1] += H.cam_off[c];
-  H.cpos.resize(Nobs); H.cpt.resize(Nobs);
-  {
-    std::vector<int32_t> cur(H.cam_off.begin(), H.cam_off.end() - 1);
-    for (int64_t e = 0; e < Nobs; ++e) { const int32_t i = cur[H.pcam[e]]++; H.cpos[i] = (int32_t)e; H.cpt[i] = H.ppt[e]; }
-  }
-  // ---- CTA chunks
-  H.win_pchunk_off.assign(nwin + 1, 0);
-  for (int w = 0; w < nwin; ++w) {
-    H.win_pchunk_off[w] = (int32_t)H.pchunk_begin.size();
-    const int lo = std::max(H.win_pt_off[w], pt_begin), hi = std::min(H.win_pt_off[w + 1], pt_end);
-    for (int b = lo; b < hi; b += kPointChunk) {
-      H.pchunk_begin.push_back(b); H.pchunk_end.push_back(std::min(b + kPointChunk, hi)); H.pchunk_win.push_back(w);
-    }
-  }
-  H.win_pchunk_off[nwin] = (int32_t)H.pchunk_begin.size();
-  H.cam_chunk_off.assign(Nc + 1, 0);
-  for (int c = 0; c < Nc; ++c) {
-    H.cam_chunk_off[c] = (int32_t)H.cchunk_cam.size();
-    if (H.fc[c] < 0) continue;
-    for (int b = H.cam_off[c]; b < H.cam_off[c + 1]; b += kCamChunk) {
-      H.cchunk_cam.push_back(c); H.cchunk_begin.push_back(b); H.cchunk_end.push_back(std::min(b + kCamChunk, H.cam_off[c + 1]));
-    }
-  }
-  H.cam_chunk_off[Nc] = (int32_t)H.cchunk_cam.size();
 
-  // ---- pair entries, bucketed by block row (free camera), then sorted by column inside a row
-  // ordered pairs (a,b) of one point's observations with fc[a] < fc[b], or fc[a] == fc[b] (the
-  // diagonal takes every ordered pair, incl. a == b and both orders of duplicated (cam,pt) pairs).
-  std::vector<int64_t> row_cnt(Nf + 1, 0);
-  for (int p = 0; p < Np; ++p) {
-    const int32_t g0 = gpt_off[p], g1 = gpt_off[p + 1];
-    for (int32_t ga = g0; ga < g1; ++ga) {
-      const int32_t fa = H.fc[obs_cam[gperm[ga]]];
-      if (fa < 0) continue;
-      int64_t n = 0;
-      for (int32_t gb = g0; gb < g1; ++gb) { const int32_t fb = H.fc[obs_cam[gperm[gb]]]; if (fb >= fa) ++n; }
-      row_cnt[fa + 1] += n;
-    }
-  }
-  for (int f = 0; f < Nf; ++f) row_cnt[f + 1] += row_cnt[f];
-  const int64_t Etot = row_cnt[Nf];
-  std::vector<Ent> ents((size_t)Etot);
-  {
-    std::vector<int64_t> cur(row_cnt.begin(), row_cnt.end() - 1);
-    for (int p = 0; p < Np; ++p) {
-      const int32_t g0 = gpt_off[p], g1 = gpt_off[p + 1];
-      const bool owned = (p >= pt_begin && p < pt_end);
-      for (int32_t ga = g0; ga < g1; ++ga) {
-        const int32_t fa = H.fc[obs_cam[gperm[ga]]];
-        if (fa < 0) continue;
-        for (int32_t gb = g0; gb < g1; ++gb) {
-          const int32_t fb = H.fc[obs_cam[gperm[gb]]];
-          if (fb < fa) continue;
-          Ent& e = ents[(size_t)cur[fa]++];
-          e.col = fb; e.a = owned ? ga - base : -1; e.b = owned ? gb - base : -1;
+  // ---- chunks, camera slots, local blocks
+  struct LB { uint8_t sa, sb; int64_t key; };
+  struct ChunkTab {
+    std::vector<int32_t> cams, slot_obs_off;
+    std::vector<uint8_t> oslot;
+    std::vector<uint16_t> sobs;
+    std::vector<LB> lbs;
+  };
+  std::vector<ChunkRange> cr;
+  std::vector<ChunkTab> tab;
+  int obs_cap = kObsChunk;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    std::string err;
+    if (!make_chunks(H, gpt_off, obs_cap, &cr, &err)) return err;
+    const int nch = (int)cr.size();
+    tab.assign(nch, ChunkTab());
+    bool overflow = false;
+#pragma omp parallel
+    {
+      std::vector<int32_t> slot_of_cam(Nc, -1);
+      std::vector<uint8_t> bits;
+      std::vector<int32_t> cnt;
+#pragma omp for schedule(dynamic, 16)
+      for (int ch = 0; ch < nch; ++ch) {
+        const ChunkRange& R = cr[ch];
+        ChunkTab& T = tab[ch];
+        const int32_t g0 = gpt_off[R.p0], g1 = gpt_off[R.p1];
+        const int n = g1 - g0;
+        T.oslot.resize(n);
+        bool bad = false;
+        for (int i = 0; i < n; ++i) {
+          const int32_t cam = obs_cam[gperm[g0 + i]];
+          int32_t s = slot_of_cam[cam];
+          if (s < 0) {
+            s = (int32_t)T.cams.size();
+            if (s >= kMaxSlots) { bad = true; break; }
+            slot_of_cam[cam] = s; T.cams.push_back(cam);
+          }
+          T.oslot[i] = (uint8_t)s;
         }
+        for (int32_t cam : T.cams) slot_of_cam[cam] = -1;
+        if (bad) {
+#pragma omp atomic write
+          overflow = true;
+          continue;
+        }
+        const int ns = (int)T.cams.size();
+        // co-visibility inside the chunk: pairs of free slots sharing a point
+        bits.assign((size_t)ns * ns, 0);
+        for (int p = R.p0; p < R.p1; ++p) {
+          const int a0 = gpt_off[p] - g0, a1 = gpt_off[p + 1] - g0;
+          for (int a = a0; a < a1; ++a) {
+            const int sa = T.oslot[a]; const int32_t fa = H.fc[T.cams[sa]];
+            if (fa < 0) continue;
+            for (int b = a0; b < a1; ++b) {
+              const int sb = T.oslot[b]; const int32_t fb = H.fc[T.cams[sb]];
+              if (fb < fa) continue;
+              bits[(size_t)sa * ns + sb] = 1;
+            }
+          }
+        }
+        for (int sa = 0; sa < ns; ++sa)
+          for (int sb = 0; sb < ns; ++sb)
+            if (bits[(size_t)sa * ns + sb]) {
+              const int64_t fa = H.fc[T.cams[sa]], fb = H.fc[T.cams[sb]];
+              if (sa != sb && fa == fb) continue;   // cannot happen (slot <-> camera is 1:1); keep the diagonal once
+              T.lbs.push_back(LB{(uint8_t)sa, (uint8_t)sb, fa * (int64_t)Nf + fb});
+            }
+        std::sort(T.lbs.begin(), T.lbs.end(), [](const LB& x, const LB& y) { return x.key < y.key; });
+        if (!R.owned) { T.oslot.clear(); T.oslot.shrink_to_fit(); continue; }
+        // observations grouped by slot (stable)
+        cnt.assign(ns + 1, 0);
+        for (int i = 0; i < n; ++i) cnt[T.oslot[i] + 1]++;
+        for (int s = 0; s < ns; ++s) cnt[s + 1] += cnt[s];
+        T.slot_obs_off.assign(cnt.begin(), cnt.end());
+        T.sobs.resize(n);
+        for (int i = 0; i < n; ++i) T.sobs[cnt[T.oslot[i]]++] = (uint16_t)i;
       }
     }
+    if (!overflow) break;
+    if (attempt == 1) return "chunk with more than 255 distinct cameras";
+    obs_cap = kMaxSlots;          // <= 255 observations per chunk guarantees <= 255 slots
   }
-#pragma omp parallel for schedule(dynamic, 16)
-  for (int f = 0; f < Nf; ++f)
-    std::stable_sort(ents.begin() + row_cnt[f], ents.begin() + row_cnt[f + 1],
-                     [](const Ent& x, const Ent& y) { return x.col < y.col; });
-  // blocks (the diagonal block of every free camera always exists, first in its row)
-  H.diag_blk.assign(Nf, -1);
-  H.blk_ent_off.push_back(0);
-  H.ent_a.reserve((size_t)Etot); H.ent_b.reserve((size_t)Etot);
-  for (int f = 0; f < Nf; ++f) {
-    int64_t i = row_cnt[f];
-    const int64_t end = row_cnt[f + 1];
-    if (i == end || ents[(size_t)i].col != f) {   // camera without (owned or unowned) observations
-      H.diag_blk[f] = (int32_t)H.blk_row.size();
-      H.blk_row.push_back(f); H.blk_col.push_back(f); H.blk_ent_off.push_back((int64_t)H.ent_a.size());
-    }
-    while (i < end) {
-      const int32_t col = ents[(size_t)i].col;
-      if (col == f) H.diag_blk[f] = (int32_t)H.blk_row.size();
-      H.blk_row.push_back(f); H.blk_col.push_back(col);
-      for (; i < end && ents[(size_t)i].col == col; ++i)
-        if (ents[(size_t)i].a >= 0) { H.ent_a.push_back(ents[(size_t)i].a); H.ent_b.push_back(ents[(size_t)i].b); }
-      H.blk_ent_off.push_back((int64_t)H.ent_a.size());
-    }
+  H.obs_cap = obs_cap;
+  const int nch_all = (int)cr.size();
+
+  // ---- block pattern: union of all chunks' local blocks + the diagonal of every free camera
+  std::vector<int64_t> keys;
+  {
+    size_t tot = (size_t)Nf;
+    for (int ch = 0; ch < nch_all; ++ch) tot += tab[ch].lbs.size();
+    keys.reserve(tot);
+    for (int f = 0; f < Nf; ++f) keys.push_back((int64_t)f * Nf + f);
+    for (int ch = 0; ch < nch_all; ++ch) for (const LB& b : tab[ch].lbs) keys.push_back(b.key);
+    std::sort(keys.begin(), keys.end());
+    keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
   }
-  std::vector<Ent>().swap(ents);
-  const int32_t nbu = (int32_t)H.blk_row.size();
-  H.blk_chunk_off.assign(nbu + 1, 0);
+  const int32_t nbu = (int32_t)keys.size();
+  H.blk_row.resize(nbu); H.blk_col.resize(nbu); H.diag_blk.assign(Nf, -1);
   for (int b = 0; b < nbu; ++b) {
-    H.blk_chunk_off[b] = (int32_t)H.schunk_blk.size();
-    for (int64_t s = H.blk_ent_off[b]; s < H.blk_ent_off[b + 1]; s += kPairChunk) {
-      H.schunk_blk.push_back(b); H.schunk_begin.push_back(s); H.schunk_end.push_back(std::min<int64_t>(s + kPairChunk, H.blk_ent_off[b + 1]));
-    }
+    H.blk_row[b] = (int32_t)(keys[b] / std::max(Nf, 1)); H.blk_col[b] = (int32_t)(keys[b] % std::max(Nf, 1));
+    if (H.blk_row[b] == H.blk_col[b]) H.diag_blk[H.blk_row[b]] = b;
   }
-  H.blk_chunk_off[nbu] = (int32_t)H.schunk_blk.size();
+
+  // ---- flatten the owned chunks
+  H.win_pchunk_off.assign(nwin + 1, 0);
+  H.slot_off.push_back(0); H.lb_off.push_back(0); H.cs_obs_off.push_back(0);
+  H.oslot.resize(Nobs); H.sobs.resize(Nobs);
+  {
+    int w_next = 0;
+    for (int ch = 0; ch < nch_all; ++ch) {
+      const ChunkRange& R = cr[ch];
+      if (!R.owned) continue;
+      while (w_next <= R.win) H.win_pchunk_off[w_next++] = (int32_t)H.pchunk_begin.size();
+      const ChunkTab& T = tab[ch];
+      H.pchunk_begin.push_back(R.p0); H.pchunk_end.push_back(R.p1); H.pchunk_win.push_back(R.win);
+      const int32_t e0 = H.pt_off[R.p0];
+      const int n = (int)T.oslot.size();
+      std::memcpy(H.oslot.data() + e0, T.oslot.data(), (size_t)n);
+      std::memcpy(H.sobs.data() + e0, T.sobs.data(), (size_t)n * sizeof(uint16_t));
+      for (size_t s = 0; s < T.cams.size(); ++s) { H.cs_cam.push_back(T.cams[s]); H.cs_obs_off.push_back(e0 + T.slot_obs_off[s + 1]); }
+      H.slot_off.push_back((int32_t)H.cs_cam.size());
+      for (const LB& b : T.lbs) {
+        H.lb_sa.push_back(b.sa); H.lb_sb.push_back(b.sb);
+        H.lb_blk.push_back((int32_t)(std::lower_bound(keys.begin(), keys.end(), b.key) - keys.begin()));
+      }
+      H.lb_off.push_back((int32_t)H.lb_sa.size());
+    }
+    while (w_next <= nwin) H.win_pchunk_off[w_next++] = (int32_t)H.pchunk_begin.size();
+  }
+  std::vector<ChunkTab>().swap(tab);
+
+  // ---- static partial lists (ascending => fixed summation order)
+  const int32_t nlb = (int32_t)H.lb_blk.size(), ncs = (int32_t)H.cs_cam.size();
+  H.blk_part_off.assign(nbu + 1, 0);
+  for (int i = 0; i < nlb; ++i) H.blk_part_off[H.lb_blk[i] + 1]++;
+  for (int b = 0; b < nbu; ++b) H.blk_part_off[b + 1] += H.blk_part_off[b];
+  H.blk_part.resize(nlb);
+  { std::vector<int32_t> cur(H.blk_part_off.begin(), H.blk_part_off.end() - 1); for (int i = 0; i < nlb; ++i) H.blk_part[cur[H.lb_blk[i]]++] = i; }
+  H.cam_part_off.assign(Nc + 1, 0);
+  for (int i = 0; i < ncs; ++i) H.cam_part_off[H.cs_cam[i] + 1]++;
+  for (int c = 0; c < Nc; ++c) H.cam_part_off[c + 1] += H.cam_part_off[c];
+  H.cam_part.resize(ncs);
+  { std::vector<int32_t> cur(H.cam_part_off.begin(), H.cam_part_off.end() - 1); for (int i = 0; i < ncs; ++i) H.cam_part[cur[H.cs_cam[i]]++] = i; }
 
   // ---- full block-CSR pattern (both triangles) for the mat-vec
   H.row_ptr.assign(Nf + 1, 0);

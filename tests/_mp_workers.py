@@ -1,0 +1,107 @@
+"""Worker functions for the multi-process tests (spawned by torch.multiprocessing; must be importable)."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def _init(rank, world, port, backend):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group(backend, rank=rank, world_size=world)
+    return dist
+
+
+def make_problem(num_frames=14, num_points=900, track_len=5, seed=31, loop=False):
+    from stereo_orb_slam_b200 import pack_window, synthetic
+    smap = synthetic.make_map(num_frames=num_frames, num_points=num_points, track_len=track_len, seed=seed, loop=loop,
+                              loop_frames=3 if loop else 0)
+    w = pack_window(smap, 0, num_frames)
+    w["p_l"], w["p_r"] = smap.p_l, smap.p_r
+    return w
+
+
+def host_shard_worker(rank, world, port, out_dir):
+    """gloo, no GPU: every rank builds the structure tables of its point shard on a host-only handle; the
+    shards must tile the observations exactly once and agree on the (global) reduced-camera block pattern."""
+    dist = _init(rank, world, port, "gloo")
+    from stereo_orb_slam_b200 import Solver
+    from stereo_orb_slam_b200.parallel import shard_points
+    w = make_problem(loop=True)
+    Nc, Np = w["poses"].shape[0], w["points"].shape[0]
+    b = shard_points(w["obs_pt"], Np, world)
+    sv = Solver(-1)
+    sv.set_point_shard(int(b[rank]), int(b[rank + 1]))
+    sv.set_structure(Nc, Np, w["obs_cam"], w["obs_pt"])
+    n_local = int(np.count_nonzero((w["obs_pt"] >= b[rank]) & (w["obs_pt"] < b[rank + 1])))
+    by_point, _ = sv.sorted_views()
+    rows, cols = sv.schur_pattern()
+    mine = dict(rank=rank, bounds=b.tolist(), n_local=n_local, obs=by_point[:n_local].tolist(),
+                pattern=(rows.tolist(), cols.tolist()))
+    got = [None] * world
+    dist.all_gather_object(got, mine)
+    if rank == 0:
+        ref = Solver(-1).set_structure(Nc, Np, w["obs_cam"], w["obs_pt"])
+        r0, c0 = ref.schur_pattern()
+        allobs = np.concatenate([np.asarray(g["obs"], np.int64) for g in got])
+        ok = (sorted(allobs.tolist()) == list(range(w["obs_cam"].size)))
+        for g in got:
+            ok = ok and g["bounds"] == got[0]["bounds"]
+            ok = ok and g["pattern"][0] == r0.tolist() and g["pattern"][1] == c0.tolist()
+            lo, hi = g["bounds"][g["rank"]], g["bounds"][g["rank"] + 1]
+            pts = w["obs_pt"][np.asarray(g["obs"], np.int64)]
+            ok = ok and bool(np.all((pts >= lo) & (pts < hi))) and bool(np.all(np.diff(pts) >= 0))
+        counts = [g["n_local"] for g in got]
+        with open(os.path.join(out_dir, "result.txt"), "w") as f:
+            f.write("%d %d %d\n" % (int(ok), min(counts), max(counts)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def window_shard_worker(rank, world, port, out_dir):
+    """gloo, no GPU: batched windows split over ranks; every rank's sub-problem is self-contained."""
+    dist = _init(rank, world, port, "gloo")
+    from stereo_orb_slam_b200 import Solver
+    from stereo_orb_slam_b200.parallel import shard_windows, slice_windows
+    ws = [make_problem(num_frames=5, num_points=60 + 7 * i, track_len=3, seed=100 + i) for i in range(5)]
+    cam_off = np.cumsum([0] + [x["poses"].shape[0] for x in ws]); pt_off = np.cumsum([0] + [x["points"].shape[0] for x in ws])
+    obs_cam = np.concatenate([x["obs_cam"] + cam_off[i] for i, x in enumerate(ws)])
+    obs_pt = np.concatenate([x["obs_pt"] + pt_off[i] for i, x in enumerate(ws)])
+    lo, hi = shard_windows(len(ws), world)[rank]
+    (c0, c1), (p0, p1), mask, wc, wp = slice_windows(lo, hi, cam_off, pt_off, obs_cam, obs_pt)
+    sv = Solver(-1).set_structure(c1 - c0, p1 - p0, obs_cam[mask] - c0, obs_pt[mask] - p0, win_cam_off=wc, win_pt_off=wp)
+    mine = dict(windows=(lo, hi), nobs=int(mask.sum()), nfree=sv.num_free_cameras)
+    got = [None] * world
+    dist.all_gather_object(got, mine)
+    if rank == 0:
+        ok = sum(g["nobs"] for g in got) == obs_cam.size and sum(g["nfree"] for g in got) == int(cam_off[-1]) - len(ws)
+        ok = ok and [g["windows"] for g in got] == shard_windows(len(ws), world)
+        with open(os.path.join(out_dir, "result.txt"), "w") as f:
+            f.write("%d\n" % int(ok))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def gpu_sharded_worker(rank, world, port, out_dir):
+    """NCCL, one GPU per rank: point-sharded solve of one problem == the single-GPU solve."""
+    import torch
+    dist = _init(rank, world, port, "gloo")     # the group only carries the 128-byte NCCL id; libsba runs its own communicator
+    torch.cuda.set_device(rank)
+    from stereo_orb_slam_b200 import Solver, default_options
+    from stereo_orb_slam_b200.parallel import ShardedSolver
+    w = make_problem(num_frames=24, num_points=4000, track_len=6, seed=77, loop=True)
+    opt = default_options(max_time_s=0.0)
+    ss = ShardedSolver(rank)
+    poses, points, s = ss.solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"], options=opt)
+    if rank == 0:
+        p1, x1, s1 = Solver(0).solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"], options=opt)
+        np.savez(os.path.join(out_dir, "result.npz"), poses=poses, points=points, cost=s["final_cost"], it=s["iterations"],
+                 poses1=p1, points1=x1, cost1=s1["final_cost"], it1=s1["iterations"], init=s["initial_cost"], init1=s1["initial_cost"])
+    dist.barrier()
+    ss.solver.close()
+    dist.destroy_process_group()

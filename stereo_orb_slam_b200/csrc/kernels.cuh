@@ -81,14 +81,20 @@ __global__ void k_project_points(int64_t n, double* __restrict__ pts, double lo,
 }
 
 // ------------------------------------------------------------------------------- K1/K2 per chunk
-// One CTA per chunk (<= kObsChunk observations of <= kPointChunk consecutive points), one THREAD PER
-// OBSERVATION: residual, Huber weight, the analytic block algebra of sba_math.cuh.  W (144 B) goes straight to
-// HBM; the point-side sums (V, gp: 9 doubles) and the camera-side operands (A, h, G: 18 doubles) are staged in
-// shared memory and reduced inside the CTA — per point by its thread, per camera slot by one warp — so each
-// observation is read exactly once (idx 4 B + uv 16 B) and nothing is recomputed.  The per-(chunk, slot)
-// camera partials are summed over chunks by k_cam_assemble through a static list (fixed order, no atomics).
+// One CTA per chunk (<= kObsChunk = 256 observations of <= kPointChunk consecutive points), one THREAD PER
+// OBSERVATION.  Everything an observation needs is staged in shared memory first with independent, coalesced
+// loads — the chunk's points, and R / J_l / t of the chunk's few cameras ("slots"), computed here from the poses
+// (K0 folded in) — so the only per-thread global reads are idx (1 + 4 B) and uv (16 B).  W (144 B) goes straight
+// to HBM; the point-side sums (V, gp: 9 doubles) and the camera-side operands (A, h, G: 18 doubles) are reduced
+// inside the CTA — per point by its thread, per camera slot by one warp.  The per-(chunk, slot) camera partials
+// are summed over chunks in list order (fixed, no data atomics) by whichever chunk arrives LAST at the camera's
+// counter, so U and gc are complete when the kernel ends and no assemble launch is needed.
 constexpr int kLinThreads = 256;
 constexpr int kCamStride = 19;     // doubles per observation in the camera staging area (odd: no bank conflicts)
+
+__host__ __device__ __forceinline__ size_t lin_smem_bytes(int n, int np, int ns) {
+  return ((size_t)n * (kCamStride + 9) + (size_t)ns * 21 + (size_t)np * 3) * 8;
+}
 
 __device__ __forceinline__ void point_contrib(const CamPre& c, const double A[6], const double h[3], const double G[9],
                                               double Vc[9], double W[18]) {
@@ -107,29 +113,59 @@ __device__ __forceinline__ void point_contrib(const CamPre& c, const double A[6]
   for (int i = 0; i < 9; ++i) W[9 + i] = AR[i];
 }
 
-__global__ void __launch_bounds__(kLinThreads) k_lin_chunk(Dev d, DevParams P) {
+// Arrival at a static partial list: every lane has published its partial; returns true (warp-uniform) for the
+// warp that arrives last, which may then read everybody's partials (with .cg loads).  The counter is reset by
+// the caller once the sum is done, so it is zero again when the kernel ends.
+__device__ __forceinline__ bool arrive_last(int32_t* counter, int expected) {
+  __threadfence();
+  __syncwarp();
+  int last = 0;
+  if ((threadIdx.x & 31) == 0) last = (atomicAdd(counter, 1) + 1 == expected) ? 1 : 0;   // control-plane counter
+  last = __shfl_sync(0xffffffffu, last, 0);
+  if (last) __threadfence();
+  return last != 0;
+}
+
+__global__ void __launch_bounds__(kLinThreads, 2) k_lin_chunk(Dev d, DevParams P) {
   extern __shared__ double smem[];
   __shared__ double sm1[kLinThreads / 32];
   __shared__ double smx[kLinThreads / 32];
   const int chunk = blockIdx.x;
-  const int p0 = d.pchunk_begin[chunk], p1 = d.pchunk_end[chunk];
+  const int p0 = d.pchunk_begin[chunk], p1 = d.pchunk_end[chunk], np = p1 - p0;
   const int e0 = d.pt_off[p0], n = d.pt_off[p1] - e0;
+  const int cs0 = d.slot_off[chunk], cs1 = d.slot_off[chunk + 1], ns = cs1 - cs0;
   double* cam_st = smem;                                   // [n * kCamStride]  A(6) h(3) G(9)
-  double* pt_st = smem + (size_t)n * kCamStride;           // [n * 9]           V(6) gp(3)
-  double cost = 0.0;
-  for (int i = threadIdx.x; i < n; i += kLinThreads) {
-    const int e = e0 + i;
-    const int p = __ldg(d.ppt + e);
+  double* pt_st = cam_st + (size_t)n * kCamStride;         // [n * 9]           V(6) gp(3)
+  double* cpre = pt_st + (size_t)n * 9;                    // [ns * 21]         R Jl t of the chunk's cameras
+  double* xs = cpre + (size_t)ns * 21;                     // [np * 3]          the chunk's points
+  // ---- stage: independent loads only
+  const int i = threadIdx.x;
+  const bool act = i < n;
+  int sl = 0, pl = 0;
+  float4 m = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (act) {
+    sl = d.oslot[e0 + i];
+    pl = __ldg(d.ppt + e0 + i) - p0;
+    m = __ldg(d.uv_p + e0 + i);
+  }
+  for (int k = threadIdx.x; k < np * 3; k += kLinThreads) xs[k] = d.pts[(size_t)p0 * 3 + k];
+  for (int s = threadIdx.x; s < ns; s += kLinThreads) {
     CamPre cp;
-    load_campre(d.campre, __ldg(d.pcam + e), cp);
-    const float4 m = __ldg(d.uv_p + e);
+    cam_precompute(d.poses + 6 * (size_t)d.cs_cam[cs0 + s], cp);
+    *reinterpret_cast<CamPre*>(cpre + 21 * s) = cp;
+  }
+  __syncthreads();
+  double cost = 0.0;
+  if (act) {
+    const int e = e0 + i;
+    const CamPre& cp = *reinterpret_cast<const CamPre*>(cpre + 21 * sl);
     const float uv[4] = {m.x, m.y, m.z, m.w};
-    const double X[3] = {d.pts[3 * (size_t)p], d.pts[3 * (size_t)p + 1], d.pts[3 * (size_t)p + 2]};
+    const double X[3] = {xs[3 * pl], xs[3 * pl + 1], xs[3 * pl + 2]};
     double q[3], r[4], D[12];
     const double s = project(P.pl, P.pr, cp, X, uv, P.rdim, q, r, D);
     double rho, w;
     huber(P.huber_delta, s, rho, w);
-    cost += 0.5 * rho;
+    cost = 0.5 * rho;
     double A[6], h[3], G[9];
     form_A_h(D, r, w, A, h);
     form_G(cp, q, G);
@@ -154,53 +190,71 @@ __global__ void __launch_bounds__(kLinThreads) k_lin_chunk(Dev d, DevParams P) {
     }
   }
   __syncthreads();
-  // per point: V, gp (thread per point, observations of a point are consecutive)
+  // ---- per point: V, gp (thread per point, observations of a point are consecutive)
   double gmax = 0.0;
-  for (int p = p0 + threadIdx.x; p < p1; p += kLinThreads) {
+  for (int q = threadIdx.x; q < np; q += kLinThreads) {
+    const int p = p0 + q;
     double acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     const int i1 = d.pt_off[p + 1] - e0;
-    for (int i = d.pt_off[p] - e0; i < i1; ++i) {
+    for (int o = d.pt_off[p] - e0; o < i1; ++o) {
 #pragma unroll
-      for (int k = 0; k < 9; ++k) acc[k] += pt_st[(size_t)i * 9 + k];
+      for (int k = 0; k < 9; ++k) acc[k] += pt_st[(size_t)o * 9 + k];
     }
 #pragma unroll
     for (int k = 0; k < 6; ++k) d.V[(size_t)p * 6 + k] = acc[k];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
       d.gp[(size_t)p * 3 + k] = acc[6 + k];
-      const double x = d.pts[(size_t)p * 3 + k];
+      const double x = xs[3 * q + k];
       gmax = fmax(gmax, fabs(x - clampd(x - acc[6 + k], P.lo, P.hi)));   // projected-gradient norm
     }
   }
-  // per camera slot: U (21) + gc (6), one warp per slot over the slot's observations
+  // ---- per camera slot: U (21) + gc (6), one warp per slot over the slot's observations
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int cs0 = d.slot_off[chunk], cs1 = d.slot_off[chunk + 1];
   for (int cs = cs0 + warp; cs < cs1; cs += kLinThreads / 32) {
-    if (d.fc[d.cs_cam[cs]] < 0) continue;        // a fixed camera is not an unknown (src/bundle_adjuster.cpp:113)
+    const int c = d.cs_cam[cs];
+    if (d.fc[c] < 0) continue;        // a fixed camera is not an unknown (src/bundle_adjuster.cpp:113)
     double acc[27];
 #pragma unroll
     for (int k = 0; k < 27; ++k) acc[k] = 0.0;
     const int j1 = d.cs_obs_off[cs + 1];
     for (int j = d.cs_obs_off[cs] + lane; j < j1; j += 32) {
-      const double* c = cam_st + (size_t)d.sobs[j] * kCamStride;
+      const double* cc = cam_st + (size_t)d.sobs[j] * kCamStride;
       double A[6], h[3], G[9];
 #pragma unroll
-      for (int k = 0; k < 6; ++k) A[k] = c[k];
+      for (int k = 0; k < 6; ++k) A[k] = cc[k];
 #pragma unroll
-      for (int k = 0; k < 3; ++k) h[k] = c[6 + k];
+      for (int k = 0; k < 3; ++k) h[k] = cc[6 + k];
 #pragma unroll
-      for (int k = 0; k < 9; ++k) G[k] = c[9 + k];
+      for (int k = 0; k < 9; ++k) G[k] = cc[9 + k];
       accum_camera(A, h, G, acc, acc + 21);
     }
+    double mine = 0.0;
 #pragma unroll
     for (int k = 0; k < 27; ++k) {
       double x = acc[k];
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-      if (lane == 0) d.cspart[(size_t)cs * 27 + k] = x;
+      if (lane == k) mine = x;
+    }
+    const int l0 = d.cam_part_off[c], l1 = d.cam_part_off[c + 1];
+    if (l1 - l0 == 1) {               // the only partial of this camera: it is the sum
+      if (lane < 21) d.U[(size_t)c * 21 + lane] = mine;
+      else if (lane < 27) d.gc[(size_t)c * 6 + (lane - 21)] = mine;
+      continue;
+    }
+    if (lane < 27) d.cspart[(size_t)cs * 27 + lane] = mine;
+    if (arrive_last(d.cam_cnt + c, l1 - l0)) {
+      if (lane < 27) {
+        double s = 0.0;
+        for (int j = l0; j < l1; ++j) s += __ldcg(d.cspart + (size_t)d.cam_part[j] * 27 + lane);
+        if (lane < 21) d.U[(size_t)c * 21 + lane] = s;
+        else d.gc[(size_t)c * 6 + (lane - 21)] = s;
+      }
+      if (lane == 0) d.cam_cnt[c] = 0;
     }
   }
-  // chunk cost and projected-gradient max
+  // ---- chunk cost and projected-gradient max
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) { cost += __shfl_xor_sync(0xffffffffu, cost, o); gmax = fmax(gmax, __shfl_xor_sync(0xffffffffu, gmax, o)); }
   if (lane == 0) { sm1[warp] = cost; smx[warp] = gmax; }
@@ -211,18 +265,6 @@ __global__ void __launch_bounds__(kLinThreads) k_lin_chunk(Dev d, DevParams P) {
     for (int k = 0; k < kLinThreads / 32; ++k) { t += sm1[k]; mx = fmax(mx, smx[k]); }
     d.lin_part[2 * chunk] = t; d.lin_part[2 * chunk + 1] = mx;
   }
-}
-
-// thread per (camera, element): U (21) and gc (6) = sum of the camera's chunk-slot partials in list order
-__global__ void k_cam_assemble(Dev d) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= d.Nc * 27) return;
-  const int c = t / 27, e = t - c * 27;
-  double s = 0.0;
-  if (d.fc[c] >= 0)
-    for (int j = d.cam_part_off[c]; j < d.cam_part_off[c + 1]; ++j) s += d.cspart[(size_t)d.cam_part[j] * 27 + e];
-  if (e < 21) d.U[(size_t)c * 21 + e] = s;
-  else d.gc[(size_t)c * 6 + (e - 21)] = s;
 }
 
 // Jacobi column scaling, fixed at iteration 0 (Ceres jacobi_scaling): s = 1/(1+sqrt(H_jj)), stored squared
@@ -281,57 +323,98 @@ __device__ __forceinline__ void load_W(const double* __restrict__ W, size_t pos,
 }
 
 // One CTA per chunk, the whole of K3 for the chunk's points in one pass over W:
-//   1. thread per point: Vinv = (V + D)^-1, tp = Vinv gp                    (kept in shared memory + HBM)
-//   2. the chunk's W (contiguous in point order) staged ONCE into shared memory
-//   3. one warp per local block (slot pair sa, sb): sum over the chunk's points of  W_a Vinv W_b^T  for the
-//      point's observations a in slot sa, b in slot sb (every ordered pair on the diagonal, duplicates
-//      included) -> spart[lb];  one warp per free slot: sum of W tp -> rpart[cs]
-// S and the right-hand side are assembled from the partials in list order by k_schur_assemble / k_rhs_finish.
+//   1. thread per point: Cholesky of V + D (3x3): Linv, Vinv = Linv^T Linv, tp = Vinv gp (Vinv, tp -> HBM for K5),
+//      u = Linv gp
+//   2. the chunk's W (contiguous in point order) staged ONCE into shared memory with coalesced loads, then each
+//      observation's thread turns its row into Z = W Linv^T in place, so that  W_a Vinv W_b^T = Z_a Z_b^T
+//   3. one warp per local block (slot pair sa, sb): lane e owns ELEMENT e of the 6x6 partial and walks the block's
+//      static pair list (a, b): acc += Z_a[row] . Z_b[col] — 3 FMAs per pair and lane, no cross-lane reduction,
+//      no divergence (elements 32..35 are done 8 pairs at a time by the same warp);  one warp per free slot:
+//      sum of Z_e u[point(e)] = W_e tp -> rpart
+//   4. whichever chunk arrives LAST at a block's / camera's counter sums that block's / camera's partials in
+//      list order (fixed order, no data atomics): Su and rsum are complete when the kernel ends.
 constexpr int kSchurThreads = 256;
-constexpr int kWStride = 19;       // doubles per observation in the W staging area
+constexpr int kZStride = 19;       // doubles per observation in the Z staging area (odd: conflict-free row access)
 
 __host__ __device__ __forceinline__ size_t schur_smem_bytes(int n, int np) {
-  return ((size_t)n * kWStride + (size_t)np * 9) * 8 + (size_t)(np + 1) * 4 + (size_t)n;
+  return ((size_t)n * kZStride + (size_t)np * 9) * 8 + (size_t)((n + 7) & ~7);
 }
 
-__global__ void __launch_bounds__(kSchurThreads) k_schur_chunk(Dev d) {
+__global__ void __launch_bounds__(kSchurThreads, 3) k_schur_chunk(Dev d) {
   extern __shared__ double smem[];
   const int chunk = blockIdx.x;
   const int p0 = d.pchunk_begin[chunk], p1 = d.pchunk_end[chunk], np = p1 - p0;
   const int e0 = d.pt_off[p0], n = d.pt_off[p1] - e0;
   const int w = d.pchunk_win[chunk];
-  double* Wst = smem;                                   // [n * kWStride]
-  double* Vi = Wst + (size_t)n * kWStride;              // [np * 6]
-  double* tp = Vi + (size_t)np * 6;                     // [np * 3]
-  int* pofs = reinterpret_cast<int*>(tp + (size_t)np * 3);      // [np + 1] chunk-local observation offsets
-  uint8_t* osl = reinterpret_cast<uint8_t*>(pofs + np + 1);     // [n]
+  double* Z = smem;                                     // [n * kZStride]
+  double* Li = Z + (size_t)n * kZStride;                // [np * 6]  Linv: 00 10 11 20 21 22
+  double* us = Li + (size_t)np * 6;                     // [np * 3]  u = Linv gp
+  uint8_t* opl = reinterpret_cast<uint8_t*>(us + (size_t)np * 3);   // [n] chunk-local point of each observation
   const double radius = d.w_radius[w];
-  for (int pl = threadIdx.x; pl <= np; pl += kSchurThreads) pofs[pl] = d.pt_off[p0 + pl] - e0;
-  for (int i = threadIdx.x; i < n; i += kSchurThreads) osl[i] = d.oslot[e0 + i];
-  for (int pl = threadIdx.x; pl < np; pl += kSchurThreads) {
-    const int p = p0 + pl;
-    double V[6];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) V[i] = d.V[(size_t)p * 6 + i];
-    V[0] += lm_damp(d.sc2p[(size_t)p * 3 + 0], V[0], radius);
-    V[3] += lm_damp(d.sc2p[(size_t)p * 3 + 1], V[3], radius);
-    V[5] += lm_damp(d.sc2p[(size_t)p * 3 + 2], V[5], radius);
-    double inv[6];
-    if (!inv_sym3(V, inv)) d.w_fail[w] = 1;   // benign race: every writer stores 1
-    const double g0 = d.gp[(size_t)p * 3], g1 = d.gp[(size_t)p * 3 + 1], g2 = d.gp[(size_t)p * 3 + 2];
-    const double t0 = inv[0] * g0 + inv[1] * g1 + inv[2] * g2;
-    const double t1 = inv[1] * g0 + inv[3] * g1 + inv[4] * g2;
-    const double t2 = inv[2] * g0 + inv[4] * g1 + inv[5] * g2;
-#pragma unroll
-    for (int i = 0; i < 6; ++i) { Vi[pl * 6 + i] = inv[i]; d.Vinv[(size_t)p * 6 + i] = inv[i]; }
-    tp[pl * 3] = t0; tp[pl * 3 + 1] = t1; tp[pl * 3 + 2] = t2;
-    d.tp[(size_t)p * 3] = t0; d.tp[(size_t)p * 3 + 1] = t1; d.tp[(size_t)p * 3 + 2] = t2;
-  }
   {
     const double* Wg = d.W + (size_t)e0 * 18;
     for (int i = threadIdx.x; i < n * 18; i += kSchurThreads) {
       const int o = i / 18, k = i - 18 * o;
-      Wst[(size_t)o * kWStride + k] = __ldg(Wg + i);
+      Z[(size_t)o * kZStride + k] = __ldg(Wg + i);
+    }
+  }
+  for (int i = threadIdx.x; i < n; i += kSchurThreads) opl[i] = (uint8_t)(__ldg(d.ppt + e0 + i) - p0);
+  for (int q = threadIdx.x; q < np; q += kSchurThreads) {
+    const int p = p0 + q;
+    double V[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) V[i] = d.V[(size_t)p * 6 + i];
+    const double a = V[0] + lm_damp(d.sc2p[(size_t)p * 3 + 0], V[0], radius);
+    const double dd = V[3] + lm_damp(d.sc2p[(size_t)p * 3 + 1], V[3], radius);
+    const double f = V[5] + lm_damp(d.sc2p[(size_t)p * 3 + 2], V[5], radius);
+    const double b = V[1], c = V[2], e = V[4];
+    // lower Cholesky factor and its inverse
+    double i00 = 0, i10 = 0, i11 = 0, i20 = 0, i21 = 0, i22 = 0;
+    bool ok = a > 0.0;
+    if (ok) {
+      const double l00 = sqrt(a);
+      i00 = 1.0 / l00;
+      const double l10 = b * i00, l20 = c * i00;
+      const double r1 = dd - l10 * l10;
+      ok = r1 > 0.0;
+      if (ok) {
+        const double l11 = sqrt(r1);
+        i11 = 1.0 / l11;
+        const double l21 = (e - l20 * l10) * i11;
+        const double r2 = f - l20 * l20 - l21 * l21;
+        ok = r2 > 0.0 && isfinite(r2);
+        if (ok) {
+          i22 = 1.0 / sqrt(r2);
+          i10 = -l10 * i00 * i11;
+          i21 = -l21 * i11 * i22;
+          i20 = -(l20 * i00 + l21 * i10) * i22;
+        }
+      }
+    }
+    if (!ok) { d.w_fail[w] = 1; i00 = i10 = i11 = i20 = i21 = i22 = 0.0; }   // benign race: every writer stores 1
+    const double g0 = d.gp[(size_t)p * 3], g1 = d.gp[(size_t)p * 3 + 1], g2 = d.gp[(size_t)p * 3 + 2];
+    const double u0 = i00 * g0, u1 = i10 * g0 + i11 * g1, u2 = i20 * g0 + i21 * g1 + i22 * g2;
+    double* vo = d.Vinv + (size_t)p * 6;
+    vo[0] = i00 * i00 + i10 * i10 + i20 * i20; vo[1] = i10 * i11 + i20 * i21; vo[2] = i20 * i22;
+    vo[3] = i11 * i11 + i21 * i21; vo[4] = i21 * i22; vo[5] = i22 * i22;
+    d.tp[(size_t)p * 3] = i00 * u0 + i10 * u1 + i20 * u2;
+    d.tp[(size_t)p * 3 + 1] = i11 * u1 + i21 * u2;
+    d.tp[(size_t)p * 3 + 2] = i22 * u2;
+    Li[q * 6] = i00; Li[q * 6 + 1] = i10; Li[q * 6 + 2] = i11; Li[q * 6 + 3] = i20; Li[q * 6 + 4] = i21; Li[q * 6 + 5] = i22;
+    us[q * 3] = u0; us[q * 3 + 1] = u1; us[q * 3 + 2] = u2;
+  }
+  __syncthreads();
+  // ---- Z = W Linv^T, each observation's thread on its own row
+  for (int i = threadIdx.x; i < n; i += kSchurThreads) {
+    const double* L = Li + (int)opl[i] * 6;
+    const double i00 = L[0], i10 = L[1], i11 = L[2], i20 = L[3], i21 = L[4], i22 = L[5];
+    double* z = Z + (size_t)i * kZStride;
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+      const double w0 = z[3 * r], w1 = z[3 * r + 1], w2 = z[3 * r + 2];
+      z[3 * r] = w0 * i00;
+      z[3 * r + 1] = w0 * i10 + w1 * i11;
+      z[3 * r + 2] = w0 * i20 + w1 * i21 + w2 * i22;
     }
   }
   __syncthreads();
@@ -339,100 +422,112 @@ __global__ void __launch_bounds__(kSchurThreads) k_schur_chunk(Dev d) {
   constexpr int NW = kSchurThreads / 32;
   // ---- local blocks
   const int lb0 = d.lb_off[chunk], lb1 = d.lb_off[chunk + 1];
+  const double* za = Z + 3 * (lane / 6);          // row i of Z_a
+  const double* zb = Z + 3 * (lane % 6);          // row j of Z_b
+  const double* zb5 = Z + 3 * (2 + (lane & 3));   // leftover elements (5, 2..5): row j of Z_b
   for (int lb = lb0 + warp; lb < lb1; lb += NW) {
-    const int sa = d.lb_sa[lb], sb = d.lb_sb[lb];
-    double acc[36];
-#pragma unroll
-    for (int i = 0; i < 36; ++i) acc[i] = 0.0;
-    for (int pl = lane; pl < np; pl += 32) {
-      const int o0 = pofs[pl], o1 = pofs[pl + 1];
-      for (int a = o0; a < o1; ++a) {
-        if (osl[a] != sa) continue;
-        const double* Wa = Wst + (size_t)a * kWStride;
-        const double* vi = Vi + pl * 6;
-        double Y[18];
-#pragma unroll
-        for (int i = 0; i < 6; ++i) {
-          const double w0 = Wa[3 * i], w1 = Wa[3 * i + 1], w2 = Wa[3 * i + 2];
-          Y[3 * i] = w0 * vi[0] + w1 * vi[1] + w2 * vi[2];
-          Y[3 * i + 1] = w0 * vi[1] + w1 * vi[3] + w2 * vi[4];
-          Y[3 * i + 2] = w0 * vi[2] + w1 * vi[4] + w2 * vi[5];
-        }
-        for (int b = o0; b < o1; ++b) {
-          if (osl[b] != sb) continue;
-          const double* Wb = Wst + (size_t)b * kWStride;
-#pragma unroll
-          for (int j = 0; j < 6; ++j) {
-            const double b0 = Wb[3 * j], b1 = Wb[3 * j + 1], b2 = Wb[3 * j + 2];
-#pragma unroll
-            for (int i = 0; i < 6; ++i) acc[6 * i + j] += Y[3 * i] * b0 + Y[3 * i + 1] * b1 + Y[3 * i + 2] * b2;
-          }
-        }
+    const int q0 = d.lb_pair_off[lb], q1 = d.lb_pair_off[lb + 1];
+    double acc0 = 0.0, acc1 = 0.0;
+    for (int base = q0; base < q1; base += 32) {
+      const unsigned mine = (base + lane < q1) ? (unsigned)__ldg(d.pairs + base + lane) : 0u;
+      const int cnt = min(32, q1 - base);
+      int t = 0;
+      for (; t + 1 < cnt; t += 2) {
+        const unsigned pa = __shfl_sync(0xffffffffu, mine, t), pb = __shfl_sync(0xffffffffu, mine, t + 1);
+        const double* A0 = za + (pa & 255u) * kZStride; const double* B0 = zb + (pa >> 8) * kZStride;
+        const double* A1 = za + (pb & 255u) * kZStride; const double* B1 = zb + (pb >> 8) * kZStride;
+        acc0 += A0[0] * B0[0] + A0[1] * B0[1] + A0[2] * B0[2];
+        acc1 += A1[0] * B1[0] + A1[1] * B1[1] + A1[2] * B1[2];
+      }
+      if (t < cnt) {
+        const unsigned pa = __shfl_sync(0xffffffffu, mine, t);
+        const double* A0 = za + (pa & 255u) * kZStride; const double* B0 = zb + (pa >> 8) * kZStride;
+        acc0 += A0[0] * B0[0] + A0[1] * B0[1] + A0[2] * B0[2];
       }
     }
-#pragma unroll
-    for (int i = 0; i < 36; ++i) {
-      double x = acc[i];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-      if (lane == 0) d.spart[(size_t)lb * 36 + i] = x;
+    const double acc = acc0 + acc1;
+    double accL = 0.0;                              // elements 32..35, eight pairs per step
+    for (int q = q0 + (lane >> 2); q < q1; q += 8) {
+      const unsigned pa = (unsigned)__ldg(d.pairs + q);
+      const double* A0 = Z + (pa & 255u) * kZStride + 15; const double* B0 = zb5 + (pa >> 8) * kZStride;
+      accL += A0[0] * B0[0] + A0[1] * B0[1] + A0[2] * B0[2];
+    }
+    accL += __shfl_xor_sync(0xffffffffu, accL, 4);
+    accL += __shfl_xor_sync(0xffffffffu, accL, 8);
+    accL += __shfl_xor_sync(0xffffffffu, accL, 16);
+    const int blk = d.lb_blk[lb];
+    const int l0 = d.blk_part_off[blk], l1 = d.blk_part_off[blk + 1];
+    if (l1 - l0 == 1) {                             // the only partial of this block: Su = -partial
+      d.Su[(size_t)blk * 36 + lane] = -acc;
+      if (lane < 4) d.Su[(size_t)blk * 36 + 32 + lane] = -accL;
+      continue;
+    }
+    d.spart[(size_t)lb * 36 + lane] = acc;
+    if (lane < 4) d.spart[(size_t)lb * 36 + 32 + lane] = accL;
+    if (arrive_last(d.blk_cnt + blk, l1 - l0)) {
+      double s0 = 0.0, s1 = 0.0;
+      for (int j = l0; j < l1; ++j) {
+        const double* sp = d.spart + (size_t)d.blk_part[j] * 36;
+        s0 += __ldcg(sp + lane);
+        if (lane < 4) s1 += __ldcg(sp + 32 + lane);
+      }
+      d.Su[(size_t)blk * 36 + lane] = -s0;
+      if (lane < 4) d.Su[(size_t)blk * 36 + 32 + lane] = -s1;
+      if (lane == 0) d.blk_cnt[blk] = 0;
     }
   }
-  // ---- right-hand side partials: sum over the slot's observations of W_e tp[point(e)]
+  // ---- right-hand side partials: sum over the slot's observations of W_e tp[point(e)] = Z_e u[point(e)]
   const int cs0 = d.slot_off[chunk], cs1 = d.slot_off[chunk + 1];
   for (int cs = cs0 + warp; cs < cs1; cs += NW) {
-    if (d.fc[d.cs_cam[cs]] < 0) continue;
+    const int c = d.cs_cam[cs];
+    const int f = d.fc[c];
+    if (f < 0) continue;
     double acc[6] = {0, 0, 0, 0, 0, 0};
     const int j1 = d.cs_obs_off[cs + 1];
     for (int j = d.cs_obs_off[cs] + lane; j < j1; j += 32) {
       const int o = d.sobs[j];
-      const int pl = __ldg(d.ppt + e0 + o) - p0;
-      const double* W = Wst + (size_t)o * kWStride;
-      const double t0 = tp[pl * 3], t1 = tp[pl * 3 + 1], t2 = tp[pl * 3 + 2];
+      const double* zz = Z + (size_t)o * kZStride;
+      const double* u = us + (int)opl[o] * 3;
+      const double t0 = u[0], t1 = u[1], t2 = u[2];
 #pragma unroll
-      for (int r = 0; r < 6; ++r) acc[r] += W[3 * r] * t0 + W[3 * r + 1] * t1 + W[3 * r + 2] * t2;
+      for (int r = 0; r < 6; ++r) acc[r] += zz[3 * r] * t0 + zz[3 * r + 1] * t1 + zz[3 * r + 2] * t2;
     }
+    double mine = 0.0;
 #pragma unroll
     for (int r = 0; r < 6; ++r) {
       double x = acc[r];
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-      if (lane == 0) d.rpart[(size_t)cs * 6 + r] = x;
+      if (lane == r) mine = x;
+    }
+    const int l0 = d.cam_part_off[c], l1 = d.cam_part_off[c + 1];
+    if (l1 - l0 == 1) {
+      if (lane < 6) d.rsum[(size_t)f * 6 + lane] = mine;
+      continue;
+    }
+    if (lane < 6) d.rpart[(size_t)cs * 6 + lane] = mine;
+    if (arrive_last(d.cam_cnt + d.Nc + c, l1 - l0)) {
+      if (lane < 6) {
+        double s = 0.0;
+        for (int j = l0; j < l1; ++j) s += __ldcg(d.rpart + (size_t)d.cam_part[j] * 6 + lane);
+        d.rsum[(size_t)f * 6 + lane] = s;
+      }
+      if (lane == 0) d.cam_cnt[d.Nc + c] = 0;
     }
   }
 }
 
-// thread per (upper block, element): Su = - sum of its local-block partials in list order (U + D are added in
-// k_cam_prepare, after the multi-GPU all-reduce of Su)
-__global__ void k_schur_assemble(Dev d) {
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= (int64_t)d.nbu * 36) return;
-  const int b = (int)(t / 36), e = (int)(t - 36 * (int64_t)b);
-  double s = 0.0;
-  for (int j = d.blk_part_off[b]; j < d.blk_part_off[b + 1]; ++j) s += d.spart[(size_t)d.blk_part[j] * 36 + e];
-  d.Su[t] = -s;
-}
-
-// thread per (free camera, 6): rsum = sum of the camera's chunk-slot partials (kept separate from gc so that a
-// multi-GPU run can all-reduce it together with Su)
-__global__ void k_rhs_finish(Dev d, double* __restrict__ rsum) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= d.Nf * 6) return;
-  const int f = t / 6, i = t - 6 * f;
-  const int c = d.free2cam[f];
-  double s = 0.0;
-  for (int j = d.cam_part_off[c]; j < d.cam_part_off[c + 1]; ++j) s += d.rpart[(size_t)d.cam_part[j] * 6 + i];
-  rsum[t] = s;
-}
-
 // thread per free camera: add U + D to the diagonal block, rhs = -gc + rsum, Minv = (S_ii)^-1
-__global__ void k_cam_prepare(Dev d, const double* __restrict__ rsum) {
+__global__ void k_cam_prepare(Dev d) {
+  const double* __restrict__ rsum = d.rsum;
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= d.Nf) return;
   const int c = d.free2cam[f];
   const int w = d.fcam_win[f];
   const double radius = d.w_radius[w];
-  double* S = d.Su + (size_t)d.diag_blk[f] * 36;
+  const int db = d.diag_blk[f];
+  double* S = d.Su + (size_t)db * 36;
+  const bool seen = d.multi_gpu || d.blk_part_off[db + 1] > d.blk_part_off[db];   // a free camera without observations has S_ff = 0
   double M[36];
   const double* U = d.U + (size_t)c * 21;
 #pragma unroll
@@ -440,7 +535,7 @@ __global__ void k_cam_prepare(Dev d, const double* __restrict__ rsum) {
 #pragma unroll
     for (int j = 0; j < 6; ++j) {
       const double u = (i <= j) ? U[up6(i, j)] : U[up6(j, i)];
-      double v = S[6 * i + j] + u;
+      double v = (seen ? S[6 * i + j] : 0.0) + u;
       if (i == j) v += lm_damp(d.sc2c[(size_t)c * 6 + i], u, radius);
       M[6 * i + j] = v;
     }
@@ -574,25 +669,36 @@ __global__ void k_pcg_update_p(Dev d) {
   d.p[t] = d.z[t] + d.w_beta[w] * d.p[t];
 }
 
-// Whole PCG solve in ONE launch: one CTA per window, vectors (and, when it fits, the window's blocks of S and
-// the block-Jacobi inverses) in shared memory, fixed-order CTA reductions for the fp64 dot products.  Used when
-// every window's reduced system is small enough (local / sliding windows, batched windows); the multi-launch
-// kernels above remain for global problems.  Same recurrences and stopping rule as k_pcg_dot.
-constexpr int kPcgThreads = 512;
+// Whole PCG solve in ONE launch: one CTA per window, vectors, block pattern and (when it fits) the window's
+// blocks of S and the block-Jacobi inverses in shared memory.  Used when every window's reduced system is small
+// enough (local / sliding windows, batched windows); the multi-launch kernels above remain for global problems.
+// Same recurrences and stopping rule as k_pcg_dot.  Per iteration: three CTA barriers.
+//   mat-vec   one warp per block-row; lane (ps, i) = (lane / 6, lane % 6) owns scalar row i of every fifth entry
+//             of the block-row (6 FMAs per entry), the five partial rows are summed in lane order
+//   dots      fp64, fixed order: warp butterfly -> one partial per warp in shared memory -> every warp re-reduces
+//             the 32 partials with the same butterfly (all threads hold the same bits)
+//   r         ping-pong buffers, so z = Minv r_new needs no barrier between the r update and its use
+constexpr int kPcgThreads = 1024;
+constexpr int kPcgWarps = kPcgThreads / 32;
 
-__device__ __forceinline__ double cta_sum512(double v, double* red /* [16] */) {
+__host__ __device__ __forceinline__ size_t pcg_smem_bytes(int nf, int nb_upper, int nb_full, bool s_in_smem) {
+  size_t dbl = (size_t)6 * 6 * nf + 2 * kPcgWarps;                      // x r0 r1 z p Ap + two reduction buffers
+  if (s_in_smem) dbl += (size_t)36 * nf + (size_t)36 * nb_upper;
+  return dbl * 8 + ((size_t)(nf + 1) + 2 * (size_t)nb_full) * 4;
+}
+
+__device__ __forceinline__ double pcg_reduce(double part, double* red, int lane, int warp) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  if (lane == 0) red[warp] = part;
   __syncthreads();
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-  __syncthreads();
-  double t = 0.0;
+  double t = red[lane];
 #pragma unroll
-  for (int i = 0; i < kPcgThreads / 32; ++i) t += red[i];
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
   return t;
 }
 
-__global__ void __launch_bounds__(kPcgThreads) k_pcg_window(Dev d, DevParams P, int max_it, int s_in_smem) {
+__global__ void __launch_bounds__(kPcgThreads, 1) k_pcg_window(Dev d, DevParams P, int max_it, int s_in_smem) {
   extern __shared__ double smem[];
   const int w = blockIdx.x;
   const int f0 = d.win_fc_off[w], f1 = d.win_fc_off[w + 1];
@@ -600,21 +706,35 @@ __global__ void __launch_bounds__(kPcgThreads) k_pcg_window(Dev d, DevParams P, 
   if (threadIdx.x == 0) d.w_pcg_it[w] = 0;
   if (nf <= 0) return;
   if (d.w_status[w] != 0 || d.w_fail[w] != 0) return;     // uniform per CTA; leaves x untouched (unused)
-  double* x = smem; double* r = x + n; double* z = r + n; double* pv = z + n; double* Ap = pv + n;
-  double* red = Ap + n;                    // [16]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double* x = smem; double* ra = x + n; double* rb = ra + n; double* z = rb + n; double* pv = z + n; double* Ap = pv + n;
+  double* redA = Ap + n; double* redB = redA + kPcgWarps;
   const int b0 = d.diag_blk[f0];
   const int b1 = (f1 < d.Nf) ? d.diag_blk[f1] : d.nbu;
-  const double* Sg = d.Su + (size_t)b0 * 36;
-  const double* Mg = d.Minv + (size_t)f0 * 36;
-  const double* S = Sg; const double* M = Mg;
+  const int e0 = d.row_ptr[f0], ne = d.row_ptr[f1] - e0;
+  const double* S = d.Su + (size_t)b0 * 36;
+  const double* M = d.Minv + (size_t)f0 * 36;
+  double* next = redB + kPcgWarps;
   if (s_in_smem) {
-    double* Ms = red + 16; double* Ss = Ms + (size_t)nf * 36;
-    for (int i = threadIdx.x; i < nf * 36; i += kPcgThreads) Ms[i] = Mg[i];
-    for (int i = threadIdx.x; i < (b1 - b0) * 36; i += kPcgThreads) Ss[i] = Sg[i];
+    double* Ms = next; double* Ss = Ms + (size_t)nf * 36;
+    for (int i = threadIdx.x; i < nf * 36; i += kPcgThreads) Ms[i] = M[i];
+    for (int i = threadIdx.x; i < (b1 - b0) * 36; i += kPcgThreads) Ss[i] = S[i];
     S = Ss; M = Ms;
+    next = Ss + (size_t)(b1 - b0) * 36;
   }
-  for (int i = threadIdx.x; i < n; i += kPcgThreads) { x[i] = 0.0; r[i] = d.rhs[(size_t)f0 * 6 + i]; }
+  int* rp = reinterpret_cast<int*>(next);                  // [nf + 1] entry offsets, window-local
+  int* ecol = rp + nf + 1;                                 // [ne] 6 * local block-column
+  int* eblk = ecol + ne;                                   // [ne] element offset of the block in S; < 0: ~offset, transposed
+  for (int i = threadIdx.x; i <= nf; i += kPcgThreads) rp[i] = d.row_ptr[f0 + i] - e0;
+  for (int i = threadIdx.x; i < ne; i += kPcgThreads) {
+    ecol[i] = 6 * (d.bsr_col[e0 + i] - f0);
+    const int bi = d.bsr_blk[e0 + i];
+    eblk[i] = (bi >= 0) ? (bi - b0) * 36 : ~((~bi - b0) * 36);
+  }
+  for (int i = threadIdx.x; i < n; i += kPcgThreads) { x[i] = 0.0; ra[i] = d.rhs[(size_t)f0 * 6 + i]; }
   __syncthreads();
+  double* r = ra; double* rn = rb;
+  // z = Minv r, p = z, rz
   double part = 0.0;
   for (int i = threadIdx.x; i < n; i += kPcgThreads) {
     const int f = i / 6, k = i - 6 * f;
@@ -624,51 +744,57 @@ __global__ void __launch_bounds__(kPcgThreads) k_pcg_window(Dev d, DevParams P, 
     z[i] = acc; pv[i] = acc;
     part += r[i] * acc;
   }
-  double rz = cta_sum512(part, red);
+  double rz = pcg_reduce(part, redB, lane, warp);
   const double rz0 = rz;
   int it = 0;
   bool fail = false;
+  const int ps = lane / 6, ri = lane - 6 * ps;
   if (!(rz > 0.0)) { if (!(rz == 0.0)) fail = true; }      // rhs == 0: x = 0 is the solution; NaN: fail
   else {
     for (;;) {
-      // Ap = S p  (block-CSR over the full pattern; upper blocks stored once)
+      // ---- Ap = S p  (block-CSR over the full pattern; upper blocks stored once), pAp
       part = 0.0;
-      for (int i = threadIdx.x; i < n; i += kPcgThreads) {
-        const int f = i / 6, k = i - 6 * f;
+      for (int f = warp; f < nf; f += kPcgWarps) {
         double acc = 0.0;
-        const int j1 = d.row_ptr[f0 + f + 1];
-        for (int j = d.row_ptr[f0 + f]; j < j1; ++j) {
-          const int col = __ldg(d.bsr_col + j) - f0;
-          const int bi = __ldg(d.bsr_blk + j);
-          const double* xv = pv + 6 * col;
-          if (bi >= 0) {
-            const double* B = S + (size_t)(bi - b0) * 36 + 6 * k;
-#pragma unroll
-            for (int c = 0; c < 6; ++c) acc += B[c] * xv[c];
-          } else {
-            const double* B = S + (size_t)(~bi - b0) * 36 + k;
-#pragma unroll
-            for (int c = 0; c < 6; ++c) acc += B[6 * c] * xv[c];
+        if (lane < 30) {
+          const int j1 = rp[f + 1];
+          for (int j = rp[f] + ps; j < j1; j += 5) {
+            const double* xv = pv + ecol[j];
+            const int off = eblk[j];
+            if (off >= 0) {
+              const double* B = S + off + 6 * ri;
+              acc += (B[0] * xv[0] + B[1] * xv[1] + B[2] * xv[2]) + (B[3] * xv[3] + B[4] * xv[4] + B[5] * xv[5]);
+            } else {
+              const double* B = S + (~off) + ri;
+              acc += (B[0] * xv[0] + B[6] * xv[1] + B[12] * xv[2]) + (B[18] * xv[3] + B[24] * xv[4] + B[30] * xv[5]);
+            }
           }
         }
-        Ap[i] = acc;
-        part += pv[i] * acc;
+        double tot = acc;                                  // rows of the five entry groups, in lane order
+#pragma unroll
+        for (int g = 1; g < 5; ++g) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * g) & 31);
+        if (lane < 6) { Ap[6 * f + lane] = tot; part += pv[6 * f + lane] * tot; }
       }
-      const double pAp = cta_sum512(part, red);
+      const double pAp = pcg_reduce(part, redA, lane, warp);
       if (!(pAp > 0.0)) { fail = true; break; }             // S not SPD
       const double alpha = rz / pAp;
-      for (int i = threadIdx.x; i < n; i += kPcgThreads) { x[i] += alpha * pv[i]; r[i] -= alpha * Ap[i]; }
-      __syncthreads();
+      // ---- x += alpha p ; r_new = r - alpha Ap ; z = Minv r_new ; rz_new
       part = 0.0;
       for (int i = threadIdx.x; i < n; i += kPcgThreads) {
         const int f = i / 6, k = i - 6 * f;
-        double acc = 0.0;
+        x[i] += alpha * pv[i];
+        double acc = 0.0, mine = 0.0;
 #pragma unroll
-        for (int j = 0; j < 6; ++j) acc += M[(size_t)f * 36 + 6 * k + j] * r[6 * f + j];
-        z[i] = acc;
-        part += r[i] * acc;
+        for (int j = 0; j < 6; ++j) {
+          const double rj = r[6 * f + j] - alpha * Ap[6 * f + j];
+          if (j == k) mine = rj;
+          acc += M[(size_t)f * 36 + 6 * k + j] * rj;
+        }
+        rn[i] = mine; z[i] = acc;
+        part += mine * acc;
       }
-      const double rz_new = cta_sum512(part, red);
+      const double rz_new = pcg_reduce(part, redB, lane, warp);
+      { double* t = r; r = rn; rn = t; }
       ++it;
       if (!isfinite(rz_new)) { fail = true; break; }
       if (rz_new <= P.pcg_tol2 * rz0 || it >= max_it) { rz = rz_new; break; }

@@ -9,6 +9,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -47,7 +48,6 @@ struct sba_handle_s {
   DevParams P{};
   std::vector<void*> allocs;          // structure + work buffers (freed on re-structure)
   float4* uv_in = nullptr;            // staging for the caller-ordered observations
-  double* rsum = nullptr;
   double* r_dbg = nullptr;
   unsigned char* flush = nullptr;     // 256 MiB L2-flush scratch (sba_time_stage)
   int32_t* h_counters = nullptr;      // pinned
@@ -86,7 +86,7 @@ struct sba_handle_s {
   void free_all() {
     for (void* p : allocs) cudaFree(p);
     allocs.clear();
-    uv_in = nullptr; rsum = nullptr; r_dbg = nullptr; flush = nullptr;
+    uv_in = nullptr; r_dbg = nullptr; flush = nullptr;
     d = Dev{};
   }
 };
@@ -176,6 +176,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   h->has_structure = true;
   h->time_structure_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   if (h->device < 0) return SBA_OK;
+  const double t_host = h->time_structure_s;
 
   CUDA_TRY(cudaSetDevice(h->device));
   h->free_all();
@@ -189,7 +190,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   UP(fc) UP(free2cam) UP(cam_win) UP(fcam_win) UP(win_cam_off) UP(win_fc_off) UP(win_pchunk_off)
   UP(pt_off) UP(perm_p) UP(pcam) UP(ppt)
   UP(pchunk_begin) UP(pchunk_end) UP(pchunk_win)
-  UP(slot_off) UP(cs_cam) UP(cs_obs_off) UP(lb_off) UP(lb_blk) UP(oslot) UP(lb_sa) UP(lb_sb) UP(sobs)
+  UP(slot_off) UP(cs_cam) UP(cs_obs_off) UP(lb_off) UP(lb_blk) UP(lb_pair_off) UP(pairs) UP(oslot) UP(lb_sa) UP(lb_sb) UP(sobs)
   UP(blk_row) UP(blk_col) UP(diag_blk) UP(blk_part_off) UP(blk_part) UP(cam_part_off) UP(cam_part)
   UP(row_ptr) UP(bsr_col) UP(bsr_blk)
 #undef UP
@@ -198,13 +199,14 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   float4* uvp;
   AL(uvp, nobs) d.uv_p = uvp;
   AL(h->uv_in, (size_t)Nobs)
+  AL(d.cam_cnt, nc * 2) AL(d.blk_cnt, (size_t)d.nbu)
   AL(d.poses, nc * 6) AL(d.poses_new, nc * 6) AL(d.pts, np * 3) AL(d.pts_new, np * 3)
   AL(d.campre, nc) AL(d.campre_new, nc)
   AL(d.W, nobs * 18) AL(d.V, np * 6) AL(d.gp, np * 3) AL(d.Vinv, np * 6) AL(d.tp, np * 3)
   AL(d.U, nc * 21) AL(d.gc, nc * 6) AL(d.cspart, (size_t)d.ncs * 27)
   AL(d.sc2c, nc * 6) AL(d.sc2p, np * 3) AL(d.lin_part, (size_t)d.npchunk * 2)
   AL(d.spart, (size_t)d.nlb * 36) AL(d.Su, (size_t)d.nbu * 36) AL(d.rpart, (size_t)d.ncs * 6)
-  AL(d.rhs, nf * 6) AL(h->rsum, nf * 6) AL(d.Minv, nf * 36)
+  AL(d.rhs, nf * 6) AL(d.rsum, nf * 6) AL(d.Minv, nf * 36)
   AL(d.x, nf * 6) AL(d.r, nf * 6) AL(d.z, nf * 6) AL(d.p, nf * 6) AL(d.Ap, nf * 6)
   AL(d.dp, np * 3) AL(d.step_part, (size_t)d.npchunk * 4) AL(d.ls_part, (size_t)d.npchunk * 3)
   AL(d.w_radius, nw) AL(d.w_decf, nw) AL(d.w_cost, nw) AL(d.w_gmax, nw)
@@ -229,15 +231,18 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   CUDA_TRY(cudaMemsetAsync(d.pts_new, 0, std::max<size_t>(1, np * 3) * 8, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.V, 0, std::max<size_t>(1, np * 6) * 8, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.gp, 0, std::max<size_t>(1, np * 3) * 8, h->stream));
+  // camera-side sums are only written where a chunk contributes: the rest stays zero for good
+  CUDA_TRY(cudaMemsetAsync(d.U, 0, std::max<size_t>(1, nc * 21) * 8, h->stream));
+  CUDA_TRY(cudaMemsetAsync(d.gc, 0, std::max<size_t>(1, nc * 6) * 8, h->stream));
+  CUDA_TRY(cudaMemsetAsync(d.Su, 0, std::max<size_t>(1, (size_t)d.nbu * 36) * 8, h->stream));
+  CUDA_TRY(cudaMemsetAsync(d.rsum, 0, std::max<size_t>(1, nf * 6) * 8, h->stream));
+  CUDA_TRY(cudaMemsetAsync(d.cam_cnt, 0, std::max<size_t>(1, nc * 2) * 4, h->stream));
+  CUDA_TRY(cudaMemsetAsync(d.blk_cnt, 0, std::max<size_t>(1, (size_t)d.nbu) * 4, h->stream));
+  d.multi_gpu = h->comm.active() ? 1 : 0;
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   {
-    int nmax = 0, npmax = 0;
-    for (size_t c = 0; c < H.pchunk_begin.size(); ++c) {
-      nmax = std::max(nmax, H.pt_off[H.pchunk_end[c]] - H.pt_off[H.pchunk_begin[c]]);
-      npmax = std::max(npmax, H.pchunk_end[c] - H.pchunk_begin[c]);
-    }
-    h->lin_smem = (size_t)nmax * (kCamStride + 9) * 8;
-    h->schur_smem = schur_smem_bytes(nmax, npmax);
+    h->lin_smem = lin_smem_bytes(H.max_chunk_obs, H.max_chunk_pts, H.max_slots);
+    h->schur_smem = schur_smem_bytes(H.max_chunk_obs, H.max_chunk_pts);
     CUDA_TRY(cudaFuncSetAttribute(k_lin_chunk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->lin_smem, 1024)));
     CUDA_TRY(cudaFuncSetAttribute(k_schur_chunk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->schur_smem, 1024)));
   }
@@ -251,15 +256,20 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
       const int64_t b0 = H.diag_blk[f0], b1 = (f1 < H.Nf) ? H.diag_blk[f1] : (int64_t)H.blk_row.size();
       nb_max = std::max(nb_max, b1 - b0);
     }
-    const size_t vec = ((size_t)5 * 6 * nf_max + 16) * 8;
-    const size_t full = vec + ((size_t)nf_max * 36 + (size_t)nb_max * 36) * 8;
-    h->pcg_window_ok = (nf_max > 0 && nf_max <= 512);   // multi-GPU: S is all-reduced, so every rank runs the same replicated solve
+    int64_t ne_max = 0;
+    for (int w = 0; w < H.nwin; ++w) ne_max = std::max<int64_t>(ne_max, H.row_ptr[H.win_fc_off[w + 1]] - H.row_ptr[H.win_fc_off[w]]);
+    const size_t lean = pcg_smem_bytes(nf_max, (int)nb_max, (int)ne_max, false);
+    const size_t full = pcg_smem_bytes(nf_max, (int)nb_max, (int)ne_max, true);
+    h->pcg_window_ok = (nf_max > 0 && lean <= (size_t)220 * 1024);   // multi-GPU: S is all-reduced, so every rank runs the same replicated solve
     h->pcg_s_in_smem = (full <= (size_t)220 * 1024) ? 1 : 0;
-    h->pcg_smem = h->pcg_s_in_smem ? full : vec;
+    h->pcg_smem = h->pcg_s_in_smem ? full : lean;
     if (h->pcg_window_ok)
       CUDA_TRY(cudaFuncSetAttribute(k_pcg_window, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->pcg_smem));
   }
   h->time_structure_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  if (std::getenv("SBA_TIMING"))
+    std::fprintf(stderr, "[sba] structure: host build %.3f ms, device alloc + upload %.3f ms (%zu allocations)\n", 1e3 * t_host,
+                 1e3 * (h->time_structure_s - t_host), h->allocs.size());
   return SBA_OK;
 }
 
@@ -340,9 +350,11 @@ int sba_get_state(sba_handle h, double* poses, double* points) {
 static int do_linearize(sba_handle h) {
   Dev& d = h->d;
   const DevParams& P = h->P;
-  LAUNCH(h, k_cam_precompute, cdiv(d.Nc, 128), 128, d.Nc, d.poses, d.campre);
+  if (h->comm.active()) {      // ranks without a local contribution to a camera must add zero, not last iteration's sum
+    CUDA_TRY(cudaMemsetAsync(d.U, 0, (size_t)d.Nc * 21 * 8, h->stream));
+    CUDA_TRY(cudaMemsetAsync(d.gc, 0, (size_t)d.Nc * 6 * 8, h->stream));
+  }
   if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P); h->launches++; }
-  LAUNCH(h, k_cam_assemble, cdiv((int64_t)d.Nc * 27, 256), 256, d);
   if (h->comm.active()) {
     std::string _err;
     if (!h->comm.allreduce(d.U, (size_t)d.Nc * 21, false, h->stream, &_err) ||
@@ -365,15 +377,17 @@ static int do_linearize(sba_handle h) {
 // K3: damped Schur complement at the per-window radii in d.w_radius.
 static int do_schur(sba_handle h) {
   Dev& d = h->d;
+  if (h->comm.active()) {
+    CUDA_TRY(cudaMemsetAsync(d.Su, 0, (size_t)d.nbu * 36 * 8, h->stream));
+    CUDA_TRY(cudaMemsetAsync(d.rsum, 0, (size_t)d.Nf * 6 * 8, h->stream));
+  }
   if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d); h->launches++; }
-  LAUNCH(h, k_schur_assemble, cdiv((int64_t)d.nbu * 36, 256), 256, d);
-  LAUNCH(h, k_rhs_finish, cdiv((int64_t)d.Nf * 6, 128), 128, d, h->rsum);
   if (h->comm.active()) {
     std::string _err;
     if (!h->comm.allreduce(d.Su, (size_t)d.nbu * 36, false, h->stream, &_err) ||
-        !h->comm.allreduce(h->rsum, (size_t)d.Nf * 6, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+        !h->comm.allreduce(d.rsum, (size_t)d.Nf * 6, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
   }
-  LAUNCH(h, k_cam_prepare, cdiv(d.Nf, 64), 64, d, h->rsum);
+  LAUNCH(h, k_cam_prepare, cdiv(d.Nf, 64), 64, d);
   CUDA_TRY(cudaGetLastError());
   return SBA_OK;
 }
@@ -568,7 +582,7 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
     CUDA_TRY(cudaEventRecord(h->ev[6], h->stream));
     switch (stage) {
       case 0: if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P); h->launches++; } break;
-      case 1: LAUNCH(h, k_cam_assemble, cdiv((int64_t)d.Nc * 27, 256), 256, d); break;
+      case 1: LAUNCH(h, k_cam_prepare, cdiv(d.Nf, 64), 64, d); break;
       case 2: if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d); h->launches++; } break;
       case 3: if ((rc = do_linearize(h))) return rc; break;
       case 4: if ((rc = do_schur(h))) return rc; break;

@@ -20,9 +20,9 @@ struct Dev {
   const int32_t *fc, *free2cam, *cam_win, *fcam_win, *win_cam_off, *win_fc_off, *win_pchunk_off;
   const int32_t *pt_off, *perm_p, *pcam, *ppt;
   const int32_t *pchunk_begin, *pchunk_end, *pchunk_win;
-  const int32_t *slot_off, *cs_cam, *cs_obs_off, *lb_off, *lb_blk;
+  const int32_t *slot_off, *cs_cam, *cs_obs_off, *lb_off, *lb_blk, *lb_pair_off;
   const uint8_t *oslot, *lb_sa, *lb_sb;
-  const uint16_t *sobs;
+  const uint16_t *sobs, *pairs;
   const int32_t *blk_row, *blk_col, *diag_blk, *blk_part_off, *blk_part, *cam_part_off, *cam_part;
   const int32_t *row_ptr, *bsr_col, *bsr_blk;
   // ---- measurements (const during a solve)
@@ -40,10 +40,13 @@ struct Dev {
   double *sc2c, *sc2p;           // Jacobi scale^2 [Nc*6], [Np*3]
   double *lin_part;              // [npchunk*2] cost, gmax
   double *r_dbg;                 // [Nobs*4] or null
+  int32_t *cam_cnt, *blk_cnt;    // [2*Nc], [nbu] arrival counters of the in-kernel assembly (zero between launches)
+  int32_t multi_gpu;             // 1: point-sharded run (camera-side sums are zeroed before and all-reduced after the chunk kernels)
   // ---- Schur
   double *spart;                 // [nlb*36] per local-block partial of sum W Vinv W^T
   double *Su;                    // [nbu*36]
   double *rpart;                 // [ncs*6] per chunk-slot partial of sum W tp
+  double *rsum;                  // [Nf*6] sum over observations of W tp per free camera
   double *rhs;                   // [Nf*6]
   double *Minv;                  // [Nf*36]
   // ---- PCG vectors [Nf*6]

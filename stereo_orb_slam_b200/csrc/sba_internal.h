@@ -8,7 +8,8 @@ namespace sba {
 
 constexpr int kThreads = 128;        // CTA size of the thread-per-point kernels
 constexpr int kPointChunk = 128;     // max points per chunk
-constexpr int kObsChunk = 512;       // max observations per chunk (= CTA size of the thread-per-observation kernels)
+constexpr int kObsChunk = 256;       // max observations per chunk (= CTA size of the thread-per-observation kernels;
+                                     // chunk-local observation indices fit a byte)
 constexpr int kMaxSlots = 255;       // distinct cameras per chunk (slot index is a byte)
 
 // Everything that depends only on (obs_cam, obs_pt, cam_fixed, windows): built once on the host
@@ -49,6 +50,11 @@ struct HostStructure {
   std::vector<int32_t> lb_off;                                  // [nchunk+1]
   std::vector<uint8_t> lb_sa, lb_sb;                            // [nlb]
   std::vector<int32_t> lb_blk;                                  // [nlb] upper block id
+  // products of local block lb: pairs [lb_pair_off[lb], lb_pair_off[lb+1]) of chunk-local observations (a | b << 8)
+  // of one point with slot(a) = sa, slot(b) = sb, points ascending; its partial is sum_pairs W_a Vinv W_b^T
+  std::vector<int32_t> lb_pair_off;                             // [nlb+1]
+  std::vector<uint16_t> pairs;                                  // [npairs]
+  int32_t max_slots = 0, max_chunk_obs = 0, max_chunk_pts = 0;  // over owned chunks (shared-memory sizing)
   // reduced camera matrix: upper blocks (row <= col, free indices), sorted (row, col); partial lists
   std::vector<int32_t> blk_row, blk_col;                        // [nbu]
   std::vector<int32_t> blk_part_off;                            // [nbu+1]

@@ -132,6 +132,8 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     std::vector<uint8_t> oslot;
     std::vector<uint16_t> sobs;
     std::vector<LB> lbs;
+    std::vector<int32_t> lb_pair_cnt;     // [nlb]
+    std::vector<uint16_t> pairs;          // grouped by lb
   };
   std::vector<ChunkRange> cr;
   std::vector<ChunkTab> tab;
@@ -146,7 +148,7 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     {
       std::vector<int32_t> slot_of_cam(Nc, -1);
       std::vector<uint8_t> bits;
-      std::vector<int32_t> cnt;
+      std::vector<int32_t> cnt, lb_of, cur;
 #pragma omp for schedule(dynamic, 16)
       for (int ch = 0; ch < nch; ++ch) {
         const ChunkRange& R = cr[ch];
@@ -202,6 +204,31 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
         T.slot_obs_off.assign(cnt.begin(), cnt.end());
         T.sobs.resize(n);
         for (int i = 0; i < n; ++i) T.sobs[cnt[T.oslot[i]]++] = (uint16_t)i;
+        // pair lists: for every local block the (a, b) observation pairs of one point, points ascending
+        const int nl = (int)T.lbs.size();
+        lb_of.assign((size_t)ns * ns, -1);
+        for (int l = 0; l < nl; ++l) lb_of[(size_t)T.lbs[l].sa * ns + T.lbs[l].sb] = l;
+        T.lb_pair_cnt.assign(nl, 0);
+        for (int pass = 0; pass < 2; ++pass) {
+          if (pass == 1) {
+            cur.assign(nl + 1, 0);
+            for (int l = 0; l < nl; ++l) cur[l + 1] = cur[l] + T.lb_pair_cnt[l];
+            T.pairs.resize(cur[nl]);
+          }
+          for (int p = R.p0; p < R.p1; ++p) {
+            const int a0 = gpt_off[p] - g0, a1 = gpt_off[p + 1] - g0;
+            for (int a = a0; a < a1; ++a) {
+              const int sa = T.oslot[a];
+              if (H.fc[T.cams[sa]] < 0) continue;
+              for (int b = a0; b < a1; ++b) {
+                const int l = lb_of[(size_t)sa * ns + T.oslot[b]];
+                if (l < 0) continue;
+                if (pass == 0) T.lb_pair_cnt[l]++;
+                else T.pairs[cur[l]++] = (uint16_t)(a | (b << 8));
+              }
+            }
+          }
+        }
       }
     }
     if (!overflow) break;
@@ -233,6 +260,13 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
   H.win_pchunk_off.assign(nwin + 1, 0);
   H.slot_off.push_back(0); H.lb_off.push_back(0); H.cs_obs_off.push_back(0);
   H.oslot.resize(Nobs); H.sobs.resize(Nobs);
+  H.lb_pair_off.push_back(0);
+  {
+    size_t npairs = 0;
+    for (int ch = 0; ch < nch_all; ++ch) if (cr[ch].owned) npairs += tab[ch].pairs.size();
+    if (npairs > 2000000000ULL) return "too many block products for 32-bit offsets";
+    H.pairs.reserve(npairs);
+  }
   {
     int w_next = 0;
     for (int ch = 0; ch < nch_all; ++ch) {
@@ -247,10 +281,16 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
       std::memcpy(H.sobs.data() + e0, T.sobs.data(), (size_t)n * sizeof(uint16_t));
       for (size_t s = 0; s < T.cams.size(); ++s) { H.cs_cam.push_back(T.cams[s]); H.cs_obs_off.push_back(e0 + T.slot_obs_off[s + 1]); }
       H.slot_off.push_back((int32_t)H.cs_cam.size());
-      for (const LB& b : T.lbs) {
+      for (size_t l = 0; l < T.lbs.size(); ++l) {
+        const LB& b = T.lbs[l];
         H.lb_sa.push_back(b.sa); H.lb_sb.push_back(b.sb);
         H.lb_blk.push_back((int32_t)(std::lower_bound(keys.begin(), keys.end(), b.key) - keys.begin()));
+        H.lb_pair_off.push_back(H.lb_pair_off.back() + T.lb_pair_cnt[l]);
       }
+      H.pairs.insert(H.pairs.end(), T.pairs.begin(), T.pairs.end());
+      H.max_slots = std::max(H.max_slots, (int32_t)T.cams.size());
+      H.max_chunk_obs = std::max(H.max_chunk_obs, (int32_t)n);
+      H.max_chunk_pts = std::max(H.max_chunk_pts, R.p1 - R.p0);
       H.lb_off.push_back((int32_t)H.lb_sa.size());
     }
     while (w_next <= nwin) H.win_pchunk_off[w_next++] = (int32_t)H.pchunk_begin.size();

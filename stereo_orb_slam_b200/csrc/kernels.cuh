@@ -7,6 +7,7 @@
 // assigned chunks, so results are bit-reproducible run to run.
 #pragma once
 #include <cuda_runtime.h>
+#include <cooperative_groups.h>
 #include "sba_device.cuh"
 #include "sba_linesearch.cuh"
 #include "sba_internal.h"
@@ -286,7 +287,7 @@ __global__ void k_jacobi_scale(Dev d) {
 
 // per window: cost = sum of chunk costs, gmax = max(chunk gmax, |gc| of free cameras);
 // gradient-tolerance test (Ceres: after every accepted step and at iteration 0).
-__global__ void __launch_bounds__(kThreads) k_lin_finish(Dev d, DevParams P) {
+__global__ void __launch_bounds__(kThreads) k_lin_finish(Dev d, DevParams P, int keep_cost) {
   __shared__ double sm[4];
   __shared__ double smx[4];
   const int w = blockIdx.x;
@@ -304,7 +305,10 @@ __global__ void __launch_bounds__(kThreads) k_lin_finish(Dev d, DevParams P) {
   const double tot = block_sum<1>(cost, sm);
   const double mx = block_max1(gmax, smx);
   if (threadIdx.x == 0) {
-    d.w_cost[w] = tot;
+    // After an accepted step the window's cost stays the accepted candidate's (Ceres: x_cost = candidate_cost, and
+    // its re-evaluation returns the same bits).  The line search compares trial costs against it at step sizes
+    // where the decrease is a few ulps, so both must come from the same summation (k_trial_points), not this one.
+    if (!keep_cost) d.w_cost[w] = tot;
     d.w_gmax[w] = mx;
   }
 }
@@ -692,7 +696,7 @@ __device__ __forceinline__ double pcg_reduce(double part, double* red, int lane,
   for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
   if (lane == 0) red[warp] = part;
   __syncthreads();
-  double t = red[lane];
+  double t = (lane < (int)(blockDim.x >> 5)) ? red[lane] : 0.0;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
   return t;
@@ -707,6 +711,7 @@ __global__ void __launch_bounds__(kPcgThreads, 1) k_pcg_window(Dev d, DevParams 
   if (nf <= 0) return;
   if (d.w_status[w] != 0 || d.w_fail[w] != 0) return;     // uniform per CTA; leaves x untouched (unused)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nthr = blockDim.x, nwarps = blockDim.x >> 5;     // 64..1024 threads, sized to the window by the host
   double* x = smem; double* ra = x + n; double* rb = ra + n; double* z = rb + n; double* pv = z + n; double* Ap = pv + n;
   double* redA = Ap + n; double* redB = redA + kPcgWarps;
   const int b0 = d.diag_blk[f0];
@@ -717,26 +722,26 @@ __global__ void __launch_bounds__(kPcgThreads, 1) k_pcg_window(Dev d, DevParams 
   double* next = redB + kPcgWarps;
   if (s_in_smem) {
     double* Ms = next; double* Ss = Ms + (size_t)nf * 36;
-    for (int i = threadIdx.x; i < nf * 36; i += kPcgThreads) Ms[i] = M[i];
-    for (int i = threadIdx.x; i < (b1 - b0) * 36; i += kPcgThreads) Ss[i] = S[i];
+    for (int i = threadIdx.x; i < nf * 36; i += nthr) Ms[i] = M[i];
+    for (int i = threadIdx.x; i < (b1 - b0) * 36; i += nthr) Ss[i] = S[i];
     S = Ss; M = Ms;
     next = Ss + (size_t)(b1 - b0) * 36;
   }
   int* rp = reinterpret_cast<int*>(next);                  // [nf + 1] entry offsets, window-local
   int* ecol = rp + nf + 1;                                 // [ne] 6 * local block-column
   int* eblk = ecol + ne;                                   // [ne] element offset of the block in S; < 0: ~offset, transposed
-  for (int i = threadIdx.x; i <= nf; i += kPcgThreads) rp[i] = d.row_ptr[f0 + i] - e0;
-  for (int i = threadIdx.x; i < ne; i += kPcgThreads) {
+  for (int i = threadIdx.x; i <= nf; i += nthr) rp[i] = d.row_ptr[f0 + i] - e0;
+  for (int i = threadIdx.x; i < ne; i += nthr) {
     ecol[i] = 6 * (d.bsr_col[e0 + i] - f0);
     const int bi = d.bsr_blk[e0 + i];
     eblk[i] = (bi >= 0) ? (bi - b0) * 36 : ~((~bi - b0) * 36);
   }
-  for (int i = threadIdx.x; i < n; i += kPcgThreads) { x[i] = 0.0; ra[i] = d.rhs[(size_t)f0 * 6 + i]; }
+  for (int i = threadIdx.x; i < n; i += nthr) { x[i] = 0.0; ra[i] = d.rhs[(size_t)f0 * 6 + i]; }
   __syncthreads();
   double* r = ra; double* rn = rb;
   // z = Minv r, p = z, rz
   double part = 0.0;
-  for (int i = threadIdx.x; i < n; i += kPcgThreads) {
+  for (int i = threadIdx.x; i < n; i += nthr) {
     const int f = i / 6, k = i - 6 * f;
     double acc = 0.0;
 #pragma unroll
@@ -754,7 +759,7 @@ __global__ void __launch_bounds__(kPcgThreads, 1) k_pcg_window(Dev d, DevParams 
     for (;;) {
       // ---- Ap = S p  (block-CSR over the full pattern; upper blocks stored once), pAp
       part = 0.0;
-      for (int f = warp; f < nf; f += kPcgWarps) {
+      for (int f = warp; f < nf; f += nwarps) {
         double acc = 0.0;
         if (lane < 30) {
           const int j1 = rp[f + 1];
@@ -780,7 +785,7 @@ __global__ void __launch_bounds__(kPcgThreads, 1) k_pcg_window(Dev d, DevParams 
       const double alpha = rz / pAp;
       // ---- x += alpha p ; r_new = r - alpha Ap ; z = Minv r_new ; rz_new
       part = 0.0;
-      for (int i = threadIdx.x; i < n; i += kPcgThreads) {
+      for (int i = threadIdx.x; i < n; i += nthr) {
         const int f = i / 6, k = i - 6 * f;
         x[i] += alpha * pv[i];
         double acc = 0.0, mine = 0.0;
@@ -800,13 +805,198 @@ __global__ void __launch_bounds__(kPcgThreads, 1) k_pcg_window(Dev d, DevParams 
       if (rz_new <= P.pcg_tol2 * rz0 || it >= max_it) { rz = rz_new; break; }
       const double beta = rz_new / rz;
       rz = rz_new;
-      for (int i = threadIdx.x; i < n; i += kPcgThreads) pv[i] = z[i] + beta * pv[i];
+      for (int i = threadIdx.x; i < n; i += nthr) pv[i] = z[i] + beta * pv[i];
       __syncthreads();
     }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < n; i += kPcgThreads) { d.x[(size_t)f0 * 6 + i] = x[i]; d.r[(size_t)f0 * 6 + i] = r[i]; }
+  for (int i = threadIdx.x; i < n; i += nthr) { d.x[(size_t)f0 * 6 + i] = x[i]; d.r[(size_t)f0 * 6 + i] = r[i]; }
   if (threadIdx.x == 0) { d.w_pcg_it[w] = it; if (fail) d.w_fail[w] = 1; atomicMax(d.counters + 4, it); }   // control-plane counter
+}
+
+// The same solve for windows whose reduced system is too big for one SM's shared-memory bandwidth and issue
+// rate (a 50-keyframe sliding window: ~600 blocks of S re-read every iteration): one thread-block CLUSTER of
+// kPcgCluster CTAs per window.  Block-rows are dealt round-robin to the CTAs; S, Minv and the pattern are read
+// through L1 (each CTA's slice stays resident), the vectors live in shared memory.  Per iteration there are two
+// cluster barriers and one CTA barrier:
+//   A  Ap = S p on the CTA's rows; every warp leader stores its p.Ap partial into ALL CTAs' reduction buffers
+//      through distributed shared memory                                            -> cluster barrier
+//   B  alpha; x, r, z = Minv r on the CTA's rows; z and the r.z partials are stored into all CTAs  -> cluster barrier
+//   C  beta; every CTA forms the whole p = z + beta p locally                       -> CTA barrier
+// Partials are summed in (CTA, warp) order by every thread: all CTAs hold bit-identical scalars.
+constexpr int kPcgCluster = 8;
+constexpr int kPcgClThreads = 256;
+constexpr int kPcgClSlots = kPcgCluster * (kPcgClThreads / 32);   // 64 partials per reduction
+
+// rows_cap / ent_cap: most block-rows / block entries any CTA owns (0, 0: S and Minv stay in global memory)
+__host__ __device__ __forceinline__ size_t pcg_cluster_smem_bytes(int nf, int rows_cap, int ent_cap) {
+  return ((size_t)6 * 6 * nf + 2 * kPcgClSlots + (size_t)36 * rows_cap + (size_t)36 * ent_cap) * 8 +   // x r0 r1 z p Ap, red, Minv, S
+         ((size_t)rows_cap + 1 + (size_t)ent_cap) * 4;
+}
+
+__device__ __forceinline__ double pcg_cluster_sum(const double* red, int lane) {
+  double t = red[lane] + red[lane + 32];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  return t;
+}
+
+__global__ void __launch_bounds__(kPcgClThreads, 1) k_pcg_cluster(Dev d, DevParams P, int max_it, int rows_cap, int ent_cap) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  extern __shared__ double smem[];
+  const int rank = (int)cluster.block_rank();
+  const int w = blockIdx.x / kPcgCluster;
+  const int f0 = d.win_fc_off[w], f1 = d.win_fc_off[w + 1];
+  const int nf = f1 - f0, n = 6 * nf;
+  if (rank == 0 && threadIdx.x == 0) d.w_pcg_it[w] = 0;
+  if (nf <= 0) return;                                      // uniform over the cluster
+  if (d.w_status[w] != 0 || d.w_fail[w] != 0) return;       // idem; leaves x untouched (unused)
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int NW = kPcgClThreads / 32;
+  double* x = smem; double* ra = x + n; double* rb = ra + n; double* z = rb + n; double* pv = z + n; double* Ap = pv + n;
+  double* redA = Ap + n; double* redB = redA + kPcgClSlots;
+  const double* __restrict__ S = d.Su;
+  const double* __restrict__ M = d.Minv + (size_t)f0 * 36;
+  // rows of this CTA: local block-rows lf = rank, rank + CL, ...; its scalar rows are dealt to threads
+  const int my_rows = (nf > rank) ? (nf - rank + kPcgCluster - 1) / kPcgCluster : 0;
+  for (int i = threadIdx.x; i < n; i += kPcgClThreads) { x[i] = 0.0; ra[i] = d.rhs[(size_t)f0 * 6 + i]; }
+  // The CTA's slice of S, one 6x6 copy per pattern entry of its rows (transposed blocks already turned), and of
+  // Minv: cluster.sync invalidates L1, so what is re-read every iteration has to sit in shared memory.
+  const bool staged = ent_cap > 0;
+  double* Ms = redB + kPcgClSlots;                           // [rows_cap * 36]
+  double* Ss = Ms + (size_t)rows_cap * 36;                   // [ent_cap * 36]
+  int* lrp = reinterpret_cast<int*>(Ss + (size_t)ent_cap * 36);   // [rows_cap + 1]
+  int* lcol = lrp + rows_cap + 1;                            // [ent_cap] 6 * local block-column
+  if (staged) {
+    if (threadIdx.x == 0) {
+      int acc = 0;
+      for (int m = 0; m < my_rows; ++m) {
+        const int f = f0 + rank + m * kPcgCluster;
+        lrp[m] = acc;
+        acc += d.row_ptr[f + 1] - d.row_ptr[f];
+      }
+      lrp[my_rows] = acc;
+    }
+    __syncthreads();
+    for (int m = 0; m < my_rows; ++m) {
+      const int f = f0 + rank + m * kPcgCluster;
+      const int g0 = d.row_ptr[f], cnt = d.row_ptr[f + 1] - g0, l0 = lrp[m];
+      for (int i = threadIdx.x; i < cnt; i += kPcgClThreads) lcol[l0 + i] = 6 * (d.bsr_col[g0 + i] - f0);
+      for (int i = threadIdx.x; i < cnt * 36; i += kPcgClThreads) {
+        const int e = i / 36, k = i - 36 * e, rr = k / 6, cc = k - 6 * rr;
+        const int bi = d.bsr_blk[g0 + e];
+        Ss[(size_t)(l0 + e) * 36 + k] = (bi >= 0) ? S[(size_t)bi * 36 + k] : S[(size_t)(~bi) * 36 + 6 * cc + rr];
+      }
+      for (int i = threadIdx.x; i < 36; i += kPcgClThreads) Ms[m * 36 + i] = M[(size_t)(rank + m * kPcgCluster) * 36 + i];
+    }
+  }
+  cluster.sync();          // every CTA of the cluster is running before anybody writes into a peer's shared memory
+  double* r = ra; double* rn = rb;
+  // z = Minv r, p = z over the WHOLE vector in every CTA (cheap, saves a broadcast); rz from the own rows only
+  double part = 0.0;
+  for (int i = threadIdx.x; i < n; i += kPcgClThreads) {
+    const int f = i / 6, k = i - 6 * f;
+    double acc = 0.0;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) acc += __ldg(M + (size_t)f * 36 + 6 * k + j) * r[6 * f + j];
+    z[i] = acc; pv[i] = acc;
+    if (f % kPcgCluster == rank) part += r[i] * acc;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  if (lane < kPcgCluster) cluster.map_shared_rank(redB, lane)[rank * NW + warp] = part;
+  cluster.sync();
+  double rz = pcg_cluster_sum(redB, lane);
+  const double rz0 = rz;
+  int it = 0;
+  bool fail = false;
+  const int ps = lane / 6, ri = lane - 6 * ps;
+  if (!(rz > 0.0)) { if (!(rz == 0.0)) fail = true; }      // rhs == 0: x = 0 is the solution; NaN: fail
+  else {
+    for (;;) {
+      // ---- A: Ap = S p on the own block-rows, p.Ap partials to everybody
+      part = 0.0;
+      for (int m = warp; m < my_rows; m += NW) {
+        const int lf = rank + m * kPcgCluster;
+        double acc = 0.0;
+        if (staged && lane < 30) {
+          const int j1 = lrp[m + 1];
+          for (int j = lrp[m] + ps; j < j1; j += 5) {
+            const double* xv = pv + lcol[j];
+            const double* B = Ss + (size_t)j * 36 + 6 * ri;
+            acc += (B[0] * xv[0] + B[1] * xv[1] + B[2] * xv[2]) + (B[3] * xv[3] + B[4] * xv[4] + B[5] * xv[5]);
+          }
+        } else if (lane < 30) {
+          const int j1 = __ldg(d.row_ptr + f0 + lf + 1);
+          for (int j = __ldg(d.row_ptr + f0 + lf) + ps; j < j1; j += 5) {
+            const double* xv = pv + 6 * (__ldg(d.bsr_col + j) - f0);
+            const int bi = __ldg(d.bsr_blk + j);
+            if (bi >= 0) {
+              const double* B = S + (size_t)bi * 36 + 6 * ri;
+              acc += (__ldg(B) * xv[0] + __ldg(B + 1) * xv[1] + __ldg(B + 2) * xv[2]) +
+                     (__ldg(B + 3) * xv[3] + __ldg(B + 4) * xv[4] + __ldg(B + 5) * xv[5]);
+            } else {
+              const double* B = S + (size_t)(~bi) * 36 + ri;
+              acc += (__ldg(B) * xv[0] + __ldg(B + 6) * xv[1] + __ldg(B + 12) * xv[2]) +
+                     (__ldg(B + 18) * xv[3] + __ldg(B + 24) * xv[4] + __ldg(B + 30) * xv[5]);
+            }
+          }
+        }
+        double tot = acc;                                  // rows of the five entry groups, in lane order
+#pragma unroll
+        for (int g = 1; g < 5; ++g) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * g) & 31);
+        if (lane < 6) { Ap[6 * lf + lane] = tot; part += pv[6 * lf + lane] * tot; }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+      if (lane < kPcgCluster) cluster.map_shared_rank(redA, lane)[rank * NW + warp] = part;
+      cluster.sync();
+      const double pAp = pcg_cluster_sum(redA, lane);
+      if (!(pAp > 0.0)) { fail = true; break; }             // S not SPD
+      const double alpha = rz / pAp;
+      // ---- B: x, r, z on the own rows (the warp that wrote Ap[row] is not the thread that reads it: CTA barrier
+      //         is implied by cluster.sync above); z and the r.z partials to everybody
+      part = 0.0;
+      for (int t = threadIdx.x; t < my_rows * 6; t += kPcgClThreads) {
+        const int m = t / 6, k = t - 6 * m;
+        const int f = rank + m * kPcgCluster, i = 6 * f + k;
+        x[i] += alpha * pv[i];
+        double acc = 0.0, mine = 0.0;
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+          const double rj = r[6 * f + j] - alpha * Ap[6 * f + j];
+          if (j == k) mine = rj;
+          acc += (staged ? Ms[m * 36 + 6 * k + j] : __ldg(M + (size_t)f * 36 + 6 * k + j)) * rj;
+        }
+        rn[i] = mine;
+        part += mine * acc;
+#pragma unroll
+        for (int c = 0; c < kPcgCluster; ++c) cluster.map_shared_rank(z, c)[i] = acc;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+      if (lane < kPcgCluster) cluster.map_shared_rank(redB, lane)[rank * NW + warp] = part;
+      cluster.sync();
+      const double rz_new = pcg_cluster_sum(redB, lane);
+      { double* t = r; r = rn; rn = t; }
+      ++it;
+      if (!isfinite(rz_new)) { fail = true; break; }
+      if (rz_new <= P.pcg_tol2 * rz0 || it >= max_it) { rz = rz_new; break; }
+      const double beta = rz_new / rz;
+      rz = rz_new;
+      // ---- C: the whole p in every CTA
+      for (int i = threadIdx.x; i < n; i += kPcgClThreads) pv[i] = z[i] + beta * pv[i];
+      __syncthreads();
+    }
+  }
+  cluster.sync();          // nobody leaves while a peer may still write into its shared memory
+  for (int t = threadIdx.x; t < my_rows * 6; t += kPcgClThreads) {
+    const int m = t / 6, k = t - 6 * m;
+    const int i = 6 * (rank + m * kPcgCluster) + k;
+    d.x[(size_t)f0 * 6 + i] = x[i]; d.r[(size_t)f0 * 6 + i] = r[i];
+  }
+  if (rank == 0 && threadIdx.x == 0) { d.w_pcg_it[w] = it; if (fail) d.w_fail[w] = 1; atomicMax(d.counters + 4, it); }   // control-plane counter
 }
 
 // ------------------------------------------------------------------------- K5: back-substitution

@@ -57,7 +57,8 @@ struct sba_handle_s {
   double time_structure_s = 0.0;
   double last_radius = 1e4;
   // single-launch PCG (k_pcg_window): usable when every window's system fits one CTA
-  bool pcg_window_ok = false; int pcg_s_in_smem = 0; size_t pcg_smem = 0;
+  bool pcg_window_ok = false; int pcg_s_in_smem = 0; size_t pcg_smem = 0; int pcg_threads = 1024;
+  bool pcg_cluster_ok = false; size_t pcg_cluster_smem = 0; int pcg_rows_cap = 0, pcg_ent_cap = 0;   // one 8-CTA cluster per window (k_pcg_cluster)
   size_t lin_smem = 0, schur_smem = 0;   // dynamic shared memory of the per-chunk kernels (largest chunk)
 
   template <typename T>
@@ -105,7 +106,7 @@ void sba_default_options(sba_options* o) {
   o->max_iterations = 50; o->max_time_s = 1.0; o->huber_delta = 1.0;
   o->point_lower_bound = -10000.0; o->point_upper_bound = 10000.0;
   o->parameter_tolerance = 1e-8; o->function_tolerance = 1e-16; o->gradient_tolerance = 1e-16;
-  o->residual_dim = 4; o->initial_radius = 1e4; o->max_pcg_iterations = 500; o->pcg_tolerance = 1e-10;
+  o->residual_dim = 4; o->initial_radius = 1e4; o->max_pcg_iterations = 500; o->pcg_tolerance = 1e-12;
   o->verbose = 0;
 }
 
@@ -263,6 +264,25 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
     h->pcg_window_ok = (nf_max > 0 && lean <= (size_t)220 * 1024);   // multi-GPU: S is all-reduced, so every rank runs the same replicated solve
     h->pcg_s_in_smem = (full <= (size_t)220 * 1024) ? 1 : 0;
     h->pcg_smem = h->pcg_s_in_smem ? full : lean;
+    h->pcg_threads = 32 * std::min(32, std::max(2, nf_max));
+    // mid-size windows: a cluster per window (8 SMs' issue rate and L1 for the mat-vec)
+    {
+      int rows_cap = 0; int64_t ent_cap = 0;
+      for (int w = 0; w < H.nwin; ++w) {
+        const int g0 = H.win_fc_off[w], g1 = H.win_fc_off[w + 1];
+        for (int r = 0; r < kPcgCluster; ++r) {
+          int rows = 0; int64_t ent = 0;
+          for (int f = g0 + r; f < g1; f += kPcgCluster) { ++rows; ent += H.row_ptr[f + 1] - H.row_ptr[f]; }
+          rows_cap = std::max(rows_cap, rows); ent_cap = std::max(ent_cap, ent);
+        }
+      }
+      h->pcg_rows_cap = rows_cap; h->pcg_ent_cap = (int)std::min<int64_t>(ent_cap, 1 << 30);
+      if (pcg_cluster_smem_bytes(nf_max, rows_cap, h->pcg_ent_cap) > (size_t)200 * 1024) { h->pcg_rows_cap = 0; h->pcg_ent_cap = 0; }
+    }
+    h->pcg_cluster_smem = pcg_cluster_smem_bytes(nf_max, h->pcg_rows_cap, h->pcg_ent_cap);
+    h->pcg_cluster_ok = (nf_max >= (std::getenv("SBA_FORCE_CLUSTER") ? 1 : 24) && H.nwin <= 64 && h->pcg_cluster_smem <= (size_t)200 * 1024 && !std::getenv("SBA_NO_CLUSTER"));
+    if (h->pcg_cluster_ok)
+      CUDA_TRY(cudaFuncSetAttribute(k_pcg_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->pcg_cluster_smem, 1024)));
     if (h->pcg_window_ok)
       CUDA_TRY(cudaFuncSetAttribute(k_pcg_window, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->pcg_smem));
   }
@@ -347,7 +367,7 @@ int sba_get_state(sba_handle h, double* poses, double* points) {
   } while (0)
 
 // K0 + K1 + K2 at the current state (d.poses / d.pts).
-static int do_linearize(sba_handle h) {
+static int do_linearize(sba_handle h, bool keep_cost = false) {
   Dev& d = h->d;
   const DevParams& P = h->P;
   if (h->comm.active()) {      // ranks without a local contribution to a camera must add zero, not last iteration's sum
@@ -360,10 +380,10 @@ static int do_linearize(sba_handle h) {
     if (!h->comm.allreduce(d.U, (size_t)d.Nc * 21, false, h->stream, &_err) ||
         !h->comm.allreduce(d.gc, (size_t)d.Nc * 6, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
   }
-  LAUNCH(h, k_lin_finish, d.nwin, kThreads, d, P);
+  LAUNCH(h, k_lin_finish, d.nwin, kThreads, d, P, keep_cost ? 1 : 0);
   if (h->comm.active()) {
     std::string _err;
-    if (!h->comm.allreduce(d.w_cost, (size_t)d.nwin, false, h->stream, &_err) ||
+    if ((!keep_cost && !h->comm.allreduce(d.w_cost, (size_t)d.nwin, false, h->stream, &_err)) ||
         !h->comm.allreduce(d.w_gmax, (size_t)d.nwin, true, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
   }
   if (!h->jacobi_done) {
@@ -399,10 +419,22 @@ static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
   Dev& d = h->d;
   const DevParams& P = h->P;
   int it = 0;
-  if (d.Nf > 0 && h->pcg_window_ok) {
+  if (d.Nf > 0 && h->pcg_cluster_ok) {
+    CUDA_TRY(cudaMemsetAsync(d.counters + 4, 0, 4, h->stream));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)d.nwin * kPcgCluster); cfg.blockDim = dim3(kPcgClThreads);
+    cfg.dynamicSmemBytes = h->pcg_cluster_smem; cfg.stream = h->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = kPcgCluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    CUDA_TRY(cudaLaunchKernelEx(&cfg, k_pcg_cluster, d, P, (int)opt->max_pcg_iterations, h->pcg_rows_cap, h->pcg_ent_cap));
+    h->launches++;
+    it = -1;
+  } else if (d.Nf > 0 && h->pcg_window_ok) {
     // one launch, no host round trip; the iteration count comes back with the LM counters (counters[4])
     CUDA_TRY(cudaMemsetAsync(d.counters + 4, 0, 4, h->stream));
-    k_pcg_window<<<d.nwin, kPcgThreads, h->pcg_smem, h->stream>>>(d, P, opt->max_pcg_iterations, h->pcg_s_in_smem);
+    k_pcg_window<<<d.nwin, h->pcg_threads, h->pcg_smem, h->stream>>>(d, P, opt->max_pcg_iterations, h->pcg_s_in_smem);
     h->launches++;
     it = -1;
   } else if (d.Nf > 0) {
@@ -680,7 +712,7 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
     const int accepted = h->h_counters[2];
     if (accepted > 0) {
       CUDA_TRY(cudaEventRecord(h->ev[4], h->stream));
-      if ((rc = do_linearize(h))) return rc;
+      if ((rc = do_linearize(h, true))) return rc;
       LAUNCH(h, k_lm_begin, cdiv(d.nwin, 128), 128, d, P, o.initial_radius, 0);
       CUDA_TRY(cudaEventRecord(h->ev[5], h->stream));
       lin_pending = true;
@@ -691,7 +723,12 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
     if (o.verbose) {
       CUDA_TRY(cudaMemcpyAsync(wcost.data(), d.w_cost, 8, cudaMemcpyDeviceToHost, h->stream));
       CUDA_TRY(cudaStreamSynchronize(h->stream));
-      std::printf("[sba] it %d  cost(w0) %.12e  running %d  accepted %d  pcg %d\n", iter + 1, wcost[0], running, accepted, pit);
+      double dbg[6] = {0, 0, 0, 0, 0, 0};
+      cudaMemcpy(&dbg[0], d.w_radius, 8, cudaMemcpyDeviceToHost); cudaMemcpy(&dbg[1], d.w_step2, 8, cudaMemcpyDeviceToHost);
+      cudaMemcpy(&dbg[2], d.w_x2, 8, cudaMemcpyDeviceToHost); cudaMemcpy(&dbg[3], d.w_ls_x, 8, cudaMemcpyDeviceToHost);
+      cudaMemcpy(&dbg[4], d.w_cand, 8, cudaMemcpyDeviceToHost); cudaMemcpy(&dbg[5], d.w_gd, 8, cudaMemcpyDeviceToHost);
+      std::printf("[sba] it %d  cost(w0) %.12e  running %d  accepted %d  pcg %d  ls_rounds %d | radius %.3e |step| %.3e |x| %.3e ls_x %.3e cand %.12e gd %.3e\n",
+                  iter + 1, wcost[0], running, accepted, (pit >= 0) ? pit : h->h_counters[4], ls_rounds, dbg[0], std::sqrt(dbg[1]), std::sqrt(dbg[2]), dbg[3], dbg[4], dbg[5]);
     }
   }
   // windows still running here hit the iteration limit

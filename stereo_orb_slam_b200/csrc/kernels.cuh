@@ -127,7 +127,41 @@ __device__ __forceinline__ bool arrive_last(int32_t* counter, int expected) {
   return last != 0;
 }
 
-__global__ void __launch_bounds__(kLinThreads, 2) k_lin_chunk(Dev d, DevParams P) {
+// Sum of the contiguous partial rows [l0, l1) of one block / camera (E doubles each), spread over the warp so
+// that many loads are in flight: lane (pg, eg) = (lane / 4, lane % 4) adds elements [eg * EG, eg * EG + EG) of
+// rows pg, pg + 8, ... in order, four rows per batch with the loads issued before the adds, then the eight row
+// groups are folded with a fixed xor butterfly.  Every lane returns the totals of its element group (valid
+// where eg * EG + k < E).  Fixed order: bit-reproducible.
+template <int E, int EG>
+__device__ __forceinline__ void gather_partials(const double* part, int l0, int l1, int lane, double (&acc)[EG]) {
+  const int pg = lane >> 2, e0 = (lane & 3) * EG;
+#pragma unroll
+  for (int k = 0; k < EG; ++k) acc[k] = 0.0;
+  for (int j = l0 + pg; j < l1; j += 32) {
+    double v[4][EG];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const bool in = j + 8 * u < l1;
+      const double* row = part + (size_t)(in ? j + 8 * u : l0) * E + e0;
+#pragma unroll
+      for (int k = 0; k < EG; ++k) v[u][k] = (in && e0 + k < E) ? __ldcg(row + k) : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int k = 0; k < EG; ++k) acc[k] += v[u][k];
+  }
+#pragma unroll
+  for (int k = 0; k < EG; ++k) {
+    double x = acc[k];
+    x += __shfl_xor_sync(0xffffffffu, x, 4);
+    x += __shfl_xor_sync(0xffffffffu, x, 8);
+    x += __shfl_xor_sync(0xffffffffu, x, 16);
+    acc[k] = x;
+  }
+}
+
+__global__ void __launch_bounds__(kLinThreads, 2) k_lin_chunk(Dev d, DevParams P, int dbg) {
   extern __shared__ double smem[];
   __shared__ double sm1[kLinThreads / 32];
   __shared__ double smx[kLinThreads / 32];
@@ -193,7 +227,7 @@ __global__ void __launch_bounds__(kLinThreads, 2) k_lin_chunk(Dev d, DevParams P
   __syncthreads();
   // ---- per point: V, gp (thread per point, observations of a point are consecutive)
   double gmax = 0.0;
-  for (int q = threadIdx.x; q < np; q += kLinThreads) {
+  for (int q = threadIdx.x; q < np && !(dbg & 4); q += kLinThreads) {
     const int p = p0 + q;
     double acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     const int i1 = d.pt_off[p + 1] - e0;
@@ -212,7 +246,7 @@ __global__ void __launch_bounds__(kLinThreads, 2) k_lin_chunk(Dev d, DevParams P
   }
   // ---- per camera slot: U (21) + gc (6), one warp per slot over the slot's observations
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int cs = cs0 + warp; cs < cs1; cs += kLinThreads / 32) {
+  for (int cs = cs0 + warp; cs < cs1 && !(dbg & 1); cs += kLinThreads / 32) {
     const int c = d.cs_cam[cs];
     if (d.fc[c] < 0) continue;        // a fixed camera is not an unknown (src/bundle_adjuster.cpp:113)
     double acc[27];
@@ -238,22 +272,7 @@ __global__ void __launch_bounds__(kLinThreads, 2) k_lin_chunk(Dev d, DevParams P
       for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
       if (lane == k) mine = x;
     }
-    const int l0 = d.cam_part_off[c], l1 = d.cam_part_off[c + 1];
-    if (l1 - l0 == 1) {               // the only partial of this camera: it is the sum
-      if (lane < 21) d.U[(size_t)c * 21 + lane] = mine;
-      else if (lane < 27) d.gc[(size_t)c * 6 + (lane - 21)] = mine;
-      continue;
-    }
-    if (lane < 27) d.cspart[(size_t)cs * 27 + lane] = mine;
-    if (arrive_last(d.cam_cnt + c, l1 - l0)) {
-      if (lane < 27) {
-        double s = 0.0;
-        for (int j = l0; j < l1; ++j) s += __ldcg(d.cspart + (size_t)d.cam_part[j] * 27 + lane);
-        if (lane < 21) d.U[(size_t)c * 21 + lane] = s;
-        else d.gc[(size_t)c * 6 + (lane - 21)] = s;
-      }
-      if (lane == 0) d.cam_cnt[c] = 0;
-    }
+    if (lane < 27) d.cspart[(size_t)d.cs_pos[cs] * 27 + lane] = mine;
   }
   // ---- chunk cost and projected-gradient max
 #pragma unroll
@@ -338,13 +357,14 @@ __device__ __forceinline__ void load_W(const double* __restrict__ W, size_t pos,
 //   4. whichever chunk arrives LAST at a block's / camera's counter sums that block's / camera's partials in
 //      list order (fixed order, no data atomics): Su and rsum are complete when the kernel ends.
 constexpr int kSchurThreads = 256;
-constexpr int kZStride = 19;       // doubles per observation in the Z staging area (odd: conflict-free row access)
+constexpr int kZStride = 18;       // doubles per observation in the Z staging area (rows stay 16-byte aligned: LDS.128)
+constexpr int kSchurPairCap = 8192;  // block products of one chunk staged in shared memory (16 KB); larger lists are read through L1
 
-__host__ __device__ __forceinline__ size_t schur_smem_bytes(int n, int np) {
-  return ((size_t)n * kZStride + (size_t)np * 9) * 8 + (size_t)((n + 7) & ~7);
+__host__ __device__ __forceinline__ size_t schur_smem_bytes(int n, int np, int npairs) {
+  return ((size_t)n * kZStride + (size_t)np * 9) * 8 + (size_t)((n + 15) & ~15) + (size_t)(npairs <= kSchurPairCap ? npairs : 0) * 2;
 }
 
-__global__ void __launch_bounds__(kSchurThreads, 3) k_schur_chunk(Dev d) {
+__global__ void __launch_bounds__(kSchurThreads, 3) k_schur_chunk(Dev d, int max_pairs, int dbg) {
   extern __shared__ double smem[];
   const int chunk = blockIdx.x;
   const int p0 = d.pchunk_begin[chunk], p1 = d.pchunk_end[chunk], np = p1 - p0;
@@ -354,6 +374,12 @@ __global__ void __launch_bounds__(kSchurThreads, 3) k_schur_chunk(Dev d) {
   double* Li = Z + (size_t)n * kZStride;                // [np * 6]  Linv: 00 10 11 20 21 22
   double* us = Li + (size_t)np * 6;                     // [np * 3]  u = Linv gp
   uint8_t* opl = reinterpret_cast<uint8_t*>(us + (size_t)np * 3);   // [n] chunk-local point of each observation
+  uint16_t* prs = reinterpret_cast<uint16_t*>(opl + ((n + 15) & ~15));   // the chunk's pair lists, when they fit
+  const int pq0 = d.lb_pair_off[d.lb_off[chunk]], npq = d.lb_pair_off[d.lb_off[chunk + 1]] - pq0;
+  const bool pairs_staged = npq <= kSchurPairCap && max_pairs <= kSchurPairCap;
+  if (pairs_staged)
+    for (int i = threadIdx.x; i < npq; i += kSchurThreads) prs[i] = __ldg(d.pairs + pq0 + i);
+  auto pair_at = [&](int q) -> unsigned { return pairs_staged ? (unsigned)prs[q] : (unsigned)__ldg(d.pairs + pq0 + q); };
   const double radius = d.w_radius[w];
   {
     const double* Wg = d.W + (size_t)e0 * 18;
@@ -422,67 +448,44 @@ __global__ void __launch_bounds__(kSchurThreads, 3) k_schur_chunk(Dev d) {
     }
   }
   __syncthreads();
+  if (dbg & 8) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int NW = kSchurThreads / 32;
-  // ---- local blocks
+  // ---- local blocks: lane (ps, i) = (lane / 6, lane % 6) owns ROW i of the 6x6 partial for every fifth pair
   const int lb0 = d.lb_off[chunk], lb1 = d.lb_off[chunk + 1];
-  const double* za = Z + 3 * (lane / 6);          // row i of Z_a
-  const double* zb = Z + 3 * (lane % 6);          // row j of Z_b
-  const double* zb5 = Z + 3 * (2 + (lane & 3));   // leftover elements (5, 2..5): row j of Z_b
+  const int ps = lane / 6, ri = lane - 6 * ps;
   for (int lb = lb0 + warp; lb < lb1; lb += NW) {
-    const int q0 = d.lb_pair_off[lb], q1 = d.lb_pair_off[lb + 1];
-    double acc0 = 0.0, acc1 = 0.0;
-    for (int base = q0; base < q1; base += 32) {
-      const unsigned mine = (base + lane < q1) ? (unsigned)__ldg(d.pairs + base + lane) : 0u;
-      const int cnt = min(32, q1 - base);
-      int t = 0;
-      for (; t + 1 < cnt; t += 2) {
-        const unsigned pa = __shfl_sync(0xffffffffu, mine, t), pb = __shfl_sync(0xffffffffu, mine, t + 1);
-        const double* A0 = za + (pa & 255u) * kZStride; const double* B0 = zb + (pa >> 8) * kZStride;
-        const double* A1 = za + (pb & 255u) * kZStride; const double* B1 = zb + (pb >> 8) * kZStride;
-        acc0 += A0[0] * B0[0] + A0[1] * B0[1] + A0[2] * B0[2];
-        acc1 += A1[0] * B1[0] + A1[1] * B1[1] + A1[2] * B1[2];
-      }
-      if (t < cnt) {
-        const unsigned pa = __shfl_sync(0xffffffffu, mine, t);
-        const double* A0 = za + (pa & 255u) * kZStride; const double* B0 = zb + (pa >> 8) * kZStride;
-        acc0 += A0[0] * B0[0] + A0[1] * B0[1] + A0[2] * B0[2];
+    const int q0 = d.lb_pair_off[lb] - pq0, q1 = d.lb_pair_off[lb + 1] - pq0;
+    double acc[6] = {0, 0, 0, 0, 0, 0};
+    if (lane < 30 && !(dbg & 1)) {
+      for (int q = q0 + ps; q < q1; q += 5) {
+        const unsigned pr = pair_at(q);
+        const double* A = Z + (pr & 255u) * kZStride + 3 * ri;
+        const double2* B = reinterpret_cast<const double2*>(Z + (pr >> 8) * kZStride);
+        const double a0 = A[0], a1 = A[1], a2 = A[2];
+        double bb[18];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) { const double2 v = B[k]; bb[2 * k] = v.x; bb[2 * k + 1] = v.y; }
+#pragma unroll
+        for (int j = 0; j < 6; ++j) acc[j] += a0 * bb[3 * j] + a1 * bb[3 * j + 1] + a2 * bb[3 * j + 2];
       }
     }
-    const double acc = acc0 + acc1;
-    double accL = 0.0;                              // elements 32..35, eight pairs per step
-    for (int q = q0 + (lane >> 2); q < q1; q += 8) {
-      const unsigned pa = (unsigned)__ldg(d.pairs + q);
-      const double* A0 = Z + (pa & 255u) * kZStride + 15; const double* B0 = zb5 + (pa >> 8) * kZStride;
-      accL += A0[0] * B0[0] + A0[1] * B0[1] + A0[2] * B0[2];
+    // rows of the five pair groups summed in lane order: lanes 0..5 end up with row ri of the partial
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      double t = acc[j];
+#pragma unroll
+      for (int g = 1; g < 5; ++g) t += __shfl_sync(0xffffffffu, acc[j], (lane + 6 * g) & 31);
+      acc[j] = t;
     }
-    accL += __shfl_xor_sync(0xffffffffu, accL, 4);
-    accL += __shfl_xor_sync(0xffffffffu, accL, 8);
-    accL += __shfl_xor_sync(0xffffffffu, accL, 16);
-    const int blk = d.lb_blk[lb];
-    const int l0 = d.blk_part_off[blk], l1 = d.blk_part_off[blk + 1];
-    if (l1 - l0 == 1) {                             // the only partial of this block: Su = -partial
-      d.Su[(size_t)blk * 36 + lane] = -acc;
-      if (lane < 4) d.Su[(size_t)blk * 36 + 32 + lane] = -accL;
-      continue;
-    }
-    d.spart[(size_t)lb * 36 + lane] = acc;
-    if (lane < 4) d.spart[(size_t)lb * 36 + 32 + lane] = accL;
-    if (arrive_last(d.blk_cnt + blk, l1 - l0)) {
-      double s0 = 0.0, s1 = 0.0;
-      for (int j = l0; j < l1; ++j) {
-        const double* sp = d.spart + (size_t)d.blk_part[j] * 36;
-        s0 += __ldcg(sp + lane);
-        if (lane < 4) s1 += __ldcg(sp + 32 + lane);
-      }
-      d.Su[(size_t)blk * 36 + lane] = -s0;
-      if (lane < 4) d.Su[(size_t)blk * 36 + 32 + lane] = -s1;
-      if (lane == 0) d.blk_cnt[blk] = 0;
+    if (lane < 6) {
+      double2* o = reinterpret_cast<double2*>(d.spart + (size_t)d.lb_pos[lb] * 36 + 6 * lane);
+      o[0] = make_double2(acc[0], acc[1]); o[1] = make_double2(acc[2], acc[3]); o[2] = make_double2(acc[4], acc[5]);
     }
   }
   // ---- right-hand side partials: sum over the slot's observations of W_e tp[point(e)] = Z_e u[point(e)]
   const int cs0 = d.slot_off[chunk], cs1 = d.slot_off[chunk + 1];
-  for (int cs = cs0 + warp; cs < cs1; cs += NW) {
+  for (int cs = cs0 + warp; cs < cs1 && !(dbg & 4); cs += NW) {
     const int c = d.cs_cam[cs];
     const int f = d.fc[c];
     if (f < 0) continue;
@@ -504,21 +507,89 @@ __global__ void __launch_bounds__(kSchurThreads, 3) k_schur_chunk(Dev d) {
       for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
       if (lane == r) mine = x;
     }
-    const int l0 = d.cam_part_off[c], l1 = d.cam_part_off[c + 1];
-    if (l1 - l0 == 1) {
-      if (lane < 6) d.rsum[(size_t)f * 6 + lane] = mine;
-      continue;
-    }
-    if (lane < 6) d.rpart[(size_t)cs * 6 + lane] = mine;
-    if (arrive_last(d.cam_cnt + d.Nc + c, l1 - l0)) {
-      if (lane < 6) {
-        double s = 0.0;
-        for (int j = l0; j < l1; ++j) s += __ldcg(d.rpart + (size_t)d.cam_part[j] * 6 + lane);
-        d.rsum[(size_t)f * 6 + lane] = s;
-      }
-      if (lane == 0) d.cam_cnt[d.Nc + c] = 0;
+    if (lane < 6) d.rpart[(size_t)d.cs_pos[cs] * 6 + lane] = mine;
+  }
+}
+
+// One warp per free camera: U (21) and gc (6) = sum of the camera's chunk-slot partials in list order.
+__global__ void __launch_bounds__(256) k_assemble_cams(Dev d) {
+  const int f = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (f >= d.Nf) return;
+  const int c = d.free2cam[f];
+  double tot[7];
+  gather_partials<27, 7>(d.cspart, d.cam_part_off[c], d.cam_part_off[c + 1], lane, tot);
+  if (lane < 4) {
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+      const int e = lane * 7 + k;
+      if (e < 21) d.U[(size_t)c * 21 + e] = tot[k];
+      else if (e < 27) d.gc[(size_t)c * 6 + (e - 21)] = tot[k];
     }
   }
+}
+
+// One warp per upper block of S and one per free camera:
+//   block warp   Su[b] = - sum of the block's local partials in list order
+//   camera warp  rsum[f] = sum of the camera's W tp partials; with `prepare` (single GPU: no all-reduce in
+//                between) it also assembles its own diagonal block and does the work of k_cam_prepare:
+//                S_ff += U + D, Minv = S_ff^-1, rhs = rsum - gc
+__global__ void __launch_bounds__(256) k_assemble_schur(Dev d, int prepare) {
+  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (wid < d.nbu) {
+    const int b = wid;
+    if (prepare && d.blk_row[b] == d.blk_col[b]) return;     // diagonal blocks belong to the camera warps
+    double tot[9];
+    gather_partials<36, 9>(d.spart, d.blk_part_off[b], d.blk_part_off[b + 1], lane, tot);
+    if (lane < 4) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) d.Su[(size_t)b * 36 + lane * 9 + k] = -tot[k];
+    }
+    return;
+  }
+  const int f = wid - d.nbu;
+  if (f >= d.Nf) return;
+  const int c = d.free2cam[f];
+  double rs[2];
+  gather_partials<6, 2>(d.rpart, d.cam_part_off[c], d.cam_part_off[c + 1], lane, rs);
+  if (lane < 3) { d.rsum[(size_t)f * 6 + 2 * lane] = rs[0]; d.rsum[(size_t)f * 6 + 2 * lane + 1] = rs[1]; }
+  if (!prepare) return;
+  const int db = d.diag_blk[f];
+  double tot[9];
+  gather_partials<36, 9>(d.spart, d.blk_part_off[db], d.blk_part_off[db + 1], lane, tot);
+  // lane 0 collects the 6x6 and the right-hand side, then factorises (one thread per camera, all cameras in parallel)
+  double M[36];
+#pragma unroll
+  for (int g = 0; g < 4; ++g)
+#pragma unroll
+    for (int k = 0; k < 9; ++k) M[g * 9 + k] = -__shfl_sync(0xffffffffu, tot[k], g);
+  double r6[6];
+#pragma unroll
+  for (int g = 0; g < 3; ++g) { r6[2 * g] = __shfl_sync(0xffffffffu, rs[0], g); r6[2 * g + 1] = __shfl_sync(0xffffffffu, rs[1], g); }
+  if (lane != 0) return;
+  const int w = d.fcam_win[f];
+  const double radius = d.w_radius[w];
+  const double* U = d.U + (size_t)c * 21;
+  double* S = d.Su + (size_t)db * 36;
+#pragma unroll
+  for (int i = 0; i < 6; ++i)
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      const double u = (i <= j) ? U[up6(i, j)] : U[up6(j, i)];
+      double v = M[6 * i + j] + u;
+      if (i == j) v += lm_damp(d.sc2c[(size_t)c * 6 + i], u, radius);
+      M[6 * i + j] = v;
+    }
+#pragma unroll
+  for (int i = 0; i < 36; ++i) S[i] = M[i];
+  if (!inv_spd6(M)) {
+    d.w_fail[w] = 1;
+#pragma unroll
+    for (int i = 0; i < 36; ++i) M[i] = (i % 7 == 0) ? 1.0 : 0.0;
+  }
+#pragma unroll
+  for (int i = 0; i < 36; ++i) d.Minv[(size_t)f * 36 + i] = M[i];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) d.rhs[(size_t)f * 6 + i] = r6[i] - d.gc[(size_t)c * 6 + i];
 }
 
 // thread per free camera: add U + D to the diagonal block, rhs = -gc + rsum, Minv = (S_ii)^-1
@@ -531,7 +602,6 @@ __global__ void k_cam_prepare(Dev d) {
   const double radius = d.w_radius[w];
   const int db = d.diag_blk[f];
   double* S = d.Su + (size_t)db * 36;
-  const bool seen = d.multi_gpu || d.blk_part_off[db + 1] > d.blk_part_off[db];   // a free camera without observations has S_ff = 0
   double M[36];
   const double* U = d.U + (size_t)c * 21;
 #pragma unroll
@@ -539,7 +609,7 @@ __global__ void k_cam_prepare(Dev d) {
 #pragma unroll
     for (int j = 0; j < 6; ++j) {
       const double u = (i <= j) ? U[up6(i, j)] : U[up6(j, i)];
-      double v = (seen ? S[6 * i + j] : 0.0) + u;
+      double v = S[6 * i + j] + u;
       if (i == j) v += lm_damp(d.sc2c[(size_t)c * 6 + i], u, radius);
       M[6 * i + j] = v;
     }

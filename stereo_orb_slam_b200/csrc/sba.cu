@@ -35,6 +35,8 @@ void set_error(const std::string& s) { g_last_error = s; }
   } while (0)
 
 inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+// SBA_DEBUG_MASK: phase knock-outs for timing experiments (results are then wrong); 0 in any real run
+inline int dbg_mask() { const char* e = std::getenv("SBA_DEBUG_MASK"); return e ? std::atoi(e) : 0; }
 }  // namespace
 
 struct sba_handle_s {
@@ -66,8 +68,10 @@ struct sba_handle_s {
     *p = nullptr;
     if (n == 0) n = 1;
     void* q = nullptr;
-    cudaError_t e = cudaMalloc(&q, n * sizeof(T));
-    if (e != cudaSuccess) { set_error(std::string("cudaMalloc: ") + cudaGetErrorString(e)); return SBA_CUDA_ERROR; }
+    // stream-ordered pool: after the first solve a re-structure (every BundleAdjuster::Optimize call) reuses the
+    // pool's cached blocks instead of paying ~100 cudaMalloc/cudaFree round trips
+    cudaError_t e = cudaMallocAsync(&q, n * sizeof(T), stream);
+    if (e != cudaSuccess) { set_error(std::string("cudaMallocAsync: ") + cudaGetErrorString(e)); return SBA_CUDA_ERROR; }
     allocs.push_back(q);
     *p = static_cast<T*>(q);
     return SBA_OK;
@@ -85,7 +89,7 @@ struct sba_handle_s {
     return SBA_OK;
   }
   void free_all() {
-    for (void* p : allocs) cudaFree(p);
+    for (void* p : allocs) cudaFreeAsync(p, stream);
     allocs.clear();
     uv_in = nullptr; r_dbg = nullptr; flush = nullptr;
     d = Dev{};
@@ -133,6 +137,13 @@ int sba_create(int device, sba_handle* out) {
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
+    if (e == cudaSuccess) {      // keep freed blocks in the device's default pool (no trim at synchronisation points)
+      cudaMemPool_t pool = nullptr;
+      if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+        unsigned long long keep = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+      }
+    }
     if (e == cudaSuccess) e = cudaMallocHost((void**)&h->h_counters, 8 * sizeof(int32_t));
     if (e != cudaSuccess) {
       set_error(std::string("sba_create: no usable CUDA device: ") + cudaGetErrorString(e));
@@ -150,6 +161,7 @@ void sba_destroy(sba_handle h) {
     cudaSetDevice(h->device);
     h->comm.destroy();
     h->free_all();
+    if (h->stream) cudaStreamSynchronize(h->stream);     // the frees above are stream-ordered
     for (int i = 0; i < 8; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     if (h->h_counters) cudaFreeHost(h->h_counters);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -193,7 +205,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   UP(pchunk_begin) UP(pchunk_end) UP(pchunk_win)
   UP(slot_off) UP(cs_cam) UP(cs_obs_off) UP(lb_off) UP(lb_blk) UP(lb_pair_off) UP(pairs) UP(oslot) UP(lb_sa) UP(lb_sb) UP(sobs)
   UP(blk_row) UP(blk_col) UP(diag_blk) UP(blk_part_off) UP(blk_part) UP(cam_part_off) UP(cam_part)
-  UP(row_ptr) UP(bsr_col) UP(bsr_blk)
+  UP(row_ptr) UP(bsr_col) UP(bsr_blk) UP(lb_pos) UP(cs_pos)
 #undef UP
   const size_t nobs = (size_t)H.Nobs, nc = (size_t)H.Nc, np = (size_t)H.Np, nf = (size_t)H.Nf, nw = (size_t)H.nwin;
 #define AL(ptr, n) if ((rc = h->alloc(&ptr, (n)))) return rc;
@@ -243,7 +255,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   {
     h->lin_smem = lin_smem_bytes(H.max_chunk_obs, H.max_chunk_pts, H.max_slots);
-    h->schur_smem = schur_smem_bytes(H.max_chunk_obs, H.max_chunk_pts);
+    h->schur_smem = schur_smem_bytes(H.max_chunk_obs, H.max_chunk_pts, H.max_chunk_pairs);
     CUDA_TRY(cudaFuncSetAttribute(k_lin_chunk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->lin_smem, 1024)));
     CUDA_TRY(cudaFuncSetAttribute(k_schur_chunk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->schur_smem, 1024)));
   }
@@ -374,7 +386,8 @@ static int do_linearize(sba_handle h, bool keep_cost = false) {
     CUDA_TRY(cudaMemsetAsync(d.U, 0, (size_t)d.Nc * 21 * 8, h->stream));
     CUDA_TRY(cudaMemsetAsync(d.gc, 0, (size_t)d.Nc * 6 * 8, h->stream));
   }
-  if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P); h->launches++; }
+  if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; }
+  LAUNCH(h, k_assemble_cams, cdiv((int64_t)d.Nf * 32, 256), 256, d);
   if (h->comm.active()) {
     std::string _err;
     if (!h->comm.allreduce(d.U, (size_t)d.Nc * 21, false, h->stream, &_err) ||
@@ -401,7 +414,10 @@ static int do_schur(sba_handle h) {
     CUDA_TRY(cudaMemsetAsync(d.Su, 0, (size_t)d.nbu * 36 * 8, h->stream));
     CUDA_TRY(cudaMemsetAsync(d.rsum, 0, (size_t)d.Nf * 6 * 8, h->stream));
   }
-  if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d); h->launches++; }
+  if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++; }
+  const int fused = h->comm.active() ? 0 : 1;     // multi-GPU: the partial sums are all-reduced before the cameras are prepared
+  LAUNCH(h, k_assemble_schur, cdiv(((int64_t)d.nbu + d.Nf) * 32, 256), 256, d, fused);
+  if (fused) { CUDA_TRY(cudaGetLastError()); return SBA_OK; }
   if (h->comm.active()) {
     std::string _err;
     if (!h->comm.allreduce(d.Su, (size_t)d.nbu * 36, false, h->stream, &_err) ||
@@ -598,7 +614,7 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
   int rc = check_ready(h, true);
   if (rc) return rc;
   if (!h->jacobi_done) { set_error("sba_time_stage needs a linearisation (sba_linearize)"); return SBA_INVALID_ARGUMENT; }
-  if (stage < 0 || stage > 8) { set_error("unknown stage"); return SBA_INVALID_ARGUMENT; }
+  if (stage < 0 || stage > 10) { set_error("unknown stage"); return SBA_INVALID_ARGUMENT; }
   if (repeats < 1) repeats = 1;
   sba_options o; if (opt) o = *opt; else sba_default_options(&o);
   CUDA_TRY(cudaSetDevice(h->device));
@@ -613,13 +629,15 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
     if (flush_l2) CUDA_TRY(cudaMemsetAsync(h->flush, i & 0xff, flush_bytes, h->stream));
     CUDA_TRY(cudaEventRecord(h->ev[6], h->stream));
     switch (stage) {
-      case 0: if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P); h->launches++; } break;
-      case 1: LAUNCH(h, k_cam_prepare, cdiv(d.Nf, 64), 64, d); break;
-      case 2: if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d); h->launches++; } break;
+      case 0: if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; } break;
+      case 1: LAUNCH(h, k_assemble_schur, cdiv(((int64_t)d.nbu + d.Nf) * 32, 256), 256, d, 1); break;
+      case 2: if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++; } break;
       case 3: if ((rc = do_linearize(h))) return rc; break;
       case 4: if ((rc = do_schur(h))) return rc; break;
       case 8: if ((rc = do_linearize(h))) return rc; if ((rc = do_schur(h))) return rc; break;
       case 5: LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P); break;
+      case 9: LAUNCH(h, k_assemble_cams, cdiv((int64_t)d.Nf * 32, 256), 256, d); break;
+      case 10: LAUNCH(h, k_lin_finish, d.nwin, kThreads, d, P, 0); break;
       case 6:      // one line-search evaluation of the full step (needs sba_schur + sba_pcg for a meaningful step)
         LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P);
         LAUNCH(h, k_cam_step, d.nwin, kThreads, d, 0);

@@ -25,6 +25,7 @@ struct Dev {
   const uint16_t *sobs, *pairs;
   const int32_t *blk_row, *blk_col, *diag_blk, *blk_part_off, *blk_part, *cam_part_off, *cam_part;
   const int32_t *row_ptr, *bsr_col, *bsr_blk;
+  const int32_t *lb_pos, *cs_pos;
   // ---- measurements (const during a solve)
   const float4 *uv_p;   // [Nobs] point order
   // ---- state

@@ -54,13 +54,17 @@ struct HostStructure {
   // of one point with slot(a) = sa, slot(b) = sb, points ascending; its partial is sum_pairs W_a Vinv W_b^T
   std::vector<int32_t> lb_pair_off;                             // [nlb+1]
   std::vector<uint16_t> pairs;                                  // [npairs]
-  int32_t max_slots = 0, max_chunk_obs = 0, max_chunk_pts = 0;  // over owned chunks (shared-memory sizing)
+  int32_t max_slots = 0, max_chunk_obs = 0, max_chunk_pts = 0, max_chunk_pairs = 0;  // over owned chunks (shared-memory sizing)
   // reduced camera matrix: upper blocks (row <= col, free indices), sorted (row, col); partial lists
   std::vector<int32_t> blk_row, blk_col;                        // [nbu]
   std::vector<int32_t> blk_part_off;                            // [nbu+1]
   std::vector<int32_t> blk_part;                                // [nlb] lb indices, ascending
   std::vector<int32_t> cam_part_off;                            // [Nc+1]
   std::vector<int32_t> cam_part;                                // [ncs] chunk-slot indices, ascending
+  // where the kernels store their partials: position in the block's / camera's list, so that the partials of one
+  // block / camera are CONTIGUOUS rows for the assemble kernels
+  std::vector<int32_t> lb_pos;                                  // [nlb] inverse of blk_part
+  std::vector<int32_t> cs_pos;                                  // [ncs] inverse of cam_part
   std::vector<int32_t> diag_blk;                                // [Nf] upper-block index of (i,i)
   // full pattern in block-CSR for the PCG mat-vec: entry -> (col, upper block, transposed?)
   std::vector<int32_t> row_ptr;                                 // [Nf+1]

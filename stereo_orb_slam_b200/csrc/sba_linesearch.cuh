@@ -38,10 +38,13 @@ SBA_HD int ls_fit_polynomial(const LsSample* s, int n, double* c /* [6] */) {
   for (int i = 0; i < 36; ++i) M[i] = 0.0;
   int row = 0;
   for (int i = 0; i < n; ++i) {
-    for (int j = 0; j <= deg; ++j) M[row * 6 + j] = pow(s[i].x, (double)(deg - j));
+    double pw[6];                      // x^0 .. x^5 by repeated multiplication (one thread runs this: no pow())
+    pw[0] = 1.0;
+    for (int j = 1; j < 6; ++j) pw[j] = pw[j - 1] * s[i].x;
+    for (int j = 0; j <= deg; ++j) M[row * 6 + j] = pw[deg - j];
     b[row++] = s[i].f;
     if (s[i].has_g) {
-      for (int j = 0; j < deg; ++j) M[row * 6 + j] = (double)(deg - j) * pow(s[i].x, (double)(deg - j - 1));
+      for (int j = 0; j < deg; ++j) M[row * 6 + j] = (double)(deg - j) * pw[deg - j - 1];
       b[row++] = s[i].g;
     }
   }
@@ -131,7 +134,27 @@ SBA_HD int ls_roots_real_parts(const double* cin, int deg, double* out /* [4] */
       zr[k] -= wr; zi[k] -= wi;
       change = fmax(change, fabs(wr) + fabs(wi));
     }
-    if (change <= 1e-15 * bound) break;
+    if (change <= 1e-9 * bound) break;
+  }
+  // polish: Newton on p(z) in complex arithmetic from the separated Durand-Kerner estimates (quadratic
+  // convergence: three steps take 1e-9 to rounding level; the slow linear tail of the simultaneous iteration
+  // is what made this routine cost > 100 us in its single thread)
+  for (int k = 0; k < deg; ++k) {
+    for (int it = 0; it < 4; ++it) {
+      double pr = 1.0, pi = 0.0, dr = 0.0, di = 0.0;   // p and p' by Horner
+      for (int i = 0; i < deg; ++i) {
+        const double ndr = dr * zr[k] - di * zi[k] + pr, ndi = dr * zi[k] + di * zr[k] + pi;
+        dr = ndr; di = ndi;
+        const double tr = pr * zr[k] - pi * zi[k] + m[i], ti = pr * zi[k] + pi * zr[k];
+        pr = tr; pi = ti;
+      }
+      const double den = dr * dr + di * di;
+      if (!(den > 0.0) || !isfinite(den)) break;
+      const double wr = (pr * dr + pi * di) / den, wi = (pi * dr - pr * di) / den;
+      if (!isfinite(wr) || !isfinite(wi)) break;
+      zr[k] -= wr; zi[k] -= wi;
+      if (fabs(wr) + fabs(wi) <= 1e-16 * bound) break;
+    }
   }
   for (int k = 0; k < deg; ++k) out[k] = zr[k];
   return deg;

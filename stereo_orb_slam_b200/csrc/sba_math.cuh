@@ -233,44 +233,62 @@ SBA_HD void accum_point(const CamPre& c, const double A[6], const double h[3], c
   for (int i = 0; i < 9; ++i) W[9 + i] = AR[i];  // rows 3..5 : A R
 }
 
-// in-place inverse of an SPD 6x6 (full, row-major) by Cholesky; returns false if not SPD
+// in-place inverse of an SPD 6x6 (full, row-major) by Cholesky; returns false if not SPD.
+// Every loop is unrolled so that L and its inverse live in registers (rolled, they sit in local memory and the
+// single thread that runs this per camera takes > 10 us).
 SBA_HD bool inv_spd6(double* M) {
+  // all loops run 0..5 with the triangular ranges as (compile-time after unrolling) predicates
   double L[36];
+  bool ok = true;
 #pragma unroll
-  for (int i = 0; i < 36; ++i) L[i] = 0.0;
   for (int j = 0; j < 6; ++j) {
     double d = M[7 * j];
-    for (int k = 0; k < j; ++k) d -= L[6 * j + k] * L[6 * j + k];
-    if (!(d > 0.0) || !isfinite(d)) return false;
+#pragma unroll
+    for (int k = 0; k < 6; ++k)
+      if (k < j) d -= L[6 * j + k] * L[6 * j + k];
+    if (!(d > 0.0) || !isfinite(d)) { ok = false; d = 1.0; }
     d = sqrt(d);
     L[7 * j] = d;
     const double id = 1.0 / d;
-    for (int i = j + 1; i < 6; ++i) {
-      double s = M[6 * i + j];
-      for (int k = 0; k < j; ++k) s -= L[6 * i + k] * L[6 * j + k];
-      L[6 * i + j] = s * id;
-    }
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+      if (i > j) {
+        double s = M[6 * i + j];
+#pragma unroll
+        for (int k = 0; k < 6; ++k)
+          if (k < j) s -= L[6 * i + k] * L[6 * j + k];
+        L[6 * i + j] = s * id;
+      }
   }
-  // invert L (lower) in place -> Li
+  if (!ok) return false;
+  // invert L (lower) -> Li
   double Li[36];
 #pragma unroll
-  for (int i = 0; i < 36; ++i) Li[i] = 0.0;
   for (int j = 0; j < 6; ++j) {
     Li[7 * j] = 1.0 / L[7 * j];
-    for (int i = j + 1; i < 6; ++i) {
-      double s = 0.0;
-      for (int k = j; k < i; ++k) s -= L[6 * i + k] * Li[6 * k + j];
-      Li[6 * i + j] = s / L[7 * i];
-    }
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+      if (i > j) {
+        double s = 0.0;
+#pragma unroll
+        for (int k = 0; k < 6; ++k)
+          if (k >= j && k < i) s -= L[6 * i + k] * Li[6 * k + j];
+        Li[6 * i + j] = s / L[7 * i];
+      }
   }
   // M^-1 = Li^T Li
+#pragma unroll
   for (int i = 0; i < 6; ++i)
-    for (int j = 0; j <= i; ++j) {
-      double s = 0.0;
-      for (int k = i; k < 6; ++k) s += Li[6 * k + i] * Li[6 * k + j];
-      M[6 * i + j] = s;
-      M[6 * j + i] = s;
-    }
+#pragma unroll
+    for (int j = 0; j < 6; ++j)
+      if (j <= i) {
+        double s = 0.0;
+#pragma unroll
+        for (int k = 0; k < 6; ++k)
+          if (k >= i) s += Li[6 * k + i] * Li[6 * k + j];
+        M[6 * i + j] = s;
+        M[6 * j + i] = s;
+      }
   return true;
 }
 

@@ -291,6 +291,7 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
       H.max_slots = std::max(H.max_slots, (int32_t)T.cams.size());
       H.max_chunk_obs = std::max(H.max_chunk_obs, (int32_t)n);
       H.max_chunk_pts = std::max(H.max_chunk_pts, R.p1 - R.p0);
+      H.max_chunk_pairs = std::max(H.max_chunk_pairs, (int32_t)std::min<size_t>(T.pairs.size(), 1u << 30));
       H.lb_off.push_back((int32_t)H.lb_sa.size());
     }
     while (w_next <= nwin) H.win_pchunk_off[w_next++] = (int32_t)H.pchunk_begin.size();
@@ -309,6 +310,10 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
   for (int c = 0; c < Nc; ++c) H.cam_part_off[c + 1] += H.cam_part_off[c];
   H.cam_part.resize(ncs);
   { std::vector<int32_t> cur(H.cam_part_off.begin(), H.cam_part_off.end() - 1); for (int i = 0; i < ncs; ++i) H.cam_part[cur[H.cs_cam[i]]++] = i; }
+
+  H.lb_pos.resize(nlb); H.cs_pos.resize(ncs);
+  for (int i = 0; i < nlb; ++i) H.lb_pos[H.blk_part[i]] = i;
+  for (int i = 0; i < ncs; ++i) H.cs_pos[H.cam_part[i]] = i;
 
   // ---- full block-CSR pattern (both triangles) for the mat-vec
   H.row_ptr.assign(Nf + 1, 0);

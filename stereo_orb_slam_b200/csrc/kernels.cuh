@@ -91,7 +91,7 @@ __global__ void k_project_points(int64_t n, double* __restrict__ pts, double lo,
 // are summed over chunks in list order (fixed, no data atomics) by whichever chunk arrives LAST at the camera's
 // counter, so U and gc are complete when the kernel ends and no assemble launch is needed.
 constexpr int kLinThreads = 256;
-constexpr int kCamStride = 19;     // doubles per observation in the camera staging area (odd: no bank conflicts)
+constexpr int kCamStride = 27;     // doubles per observation in the camera staging area: its U (21) and gc (6) terms
 
 __host__ __device__ __forceinline__ size_t lin_smem_bytes(int n, int np, int ns) {
   return ((size_t)n * (kCamStride + 9) + (size_t)ns * 21 + (size_t)np * 3) * 8;
@@ -204,13 +204,15 @@ __global__ void __launch_bounds__(kLinThreads, 2) k_lin_chunk(Dev d, DevParams P
     double A[6], h[3], G[9];
     form_A_h(D, r, w, A, h);
     form_G(cp, q, G);
-    double* cs = cam_st + (size_t)i * kCamStride;
+    {
+      double cu[27];
 #pragma unroll
-    for (int k = 0; k < 6; ++k) cs[k] = A[k];
+      for (int k = 0; k < 27; ++k) cu[k] = 0.0;
+      accum_camera(A, h, G, cu, cu + 21);
+      double* cs = cam_st + (size_t)i * kCamStride;
 #pragma unroll
-    for (int k = 0; k < 3; ++k) cs[6 + k] = h[k];
-#pragma unroll
-    for (int k = 0; k < 9; ++k) cs[9 + k] = G[k];
+      for (int k = 0; k < 27; ++k) cs[k] = cu[k];
+    }
     double Vc[9], W[18];
     point_contrib(cp, A, h, G, Vc, W);
 #pragma unroll
@@ -249,29 +251,11 @@ __global__ void __launch_bounds__(kLinThreads, 2) k_lin_chunk(Dev d, DevParams P
   for (int cs = cs0 + warp; cs < cs1 && !(dbg & 1); cs += kLinThreads / 32) {
     const int c = d.cs_cam[cs];
     if (d.fc[c] < 0) continue;        // a fixed camera is not an unknown (src/bundle_adjuster.cpp:113)
-    double acc[27];
-#pragma unroll
-    for (int k = 0; k < 27; ++k) acc[k] = 0.0;
-    const int j1 = d.cs_obs_off[cs + 1];
-    for (int j = d.cs_obs_off[cs] + lane; j < j1; j += 32) {
-      const double* cc = cam_st + (size_t)d.sobs[j] * kCamStride;
-      double A[6], h[3], G[9];
-#pragma unroll
-      for (int k = 0; k < 6; ++k) A[k] = cc[k];
-#pragma unroll
-      for (int k = 0; k < 3; ++k) h[k] = cc[6 + k];
-#pragma unroll
-      for (int k = 0; k < 9; ++k) G[k] = cc[9 + k];
-      accum_camera(A, h, G, acc, acc + 21);
-    }
+    // lane e sums element e of the slot's observations in list order (no cross-lane reduction)
     double mine = 0.0;
-#pragma unroll
-    for (int k = 0; k < 27; ++k) {
-      double x = acc[k];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-      if (lane == k) mine = x;
-    }
+    const int j1 = d.cs_obs_off[cs + 1];
+    if (lane < 27)
+      for (int j = d.cs_obs_off[cs]; j < j1; ++j) mine += cam_st[(size_t)__ldg(d.sobs + j) * kCamStride + lane];
     if (lane < 27) d.cspart[(size_t)d.cs_pos[cs] * 27 + lane] = mine;
   }
   // ---- chunk cost and projected-gradient max

@@ -273,7 +273,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
     for (int w = 0; w < H.nwin; ++w) ne_max = std::max<int64_t>(ne_max, H.row_ptr[H.win_fc_off[w + 1]] - H.row_ptr[H.win_fc_off[w]]);
     const size_t lean = pcg_smem_bytes(nf_max, (int)nb_max, (int)ne_max, false);
     const size_t full = pcg_smem_bytes(nf_max, (int)nb_max, (int)ne_max, true);
-    h->pcg_window_ok = (nf_max > 0 && lean <= (size_t)220 * 1024);   // multi-GPU: S is all-reduced, so every rank runs the same replicated solve
+    h->pcg_window_ok = (nf_max > 0 && lean <= (size_t)220 * 1024 && !std::getenv("SBA_FORCE_MULTILAUNCH"));   // multi-GPU: S is all-reduced, so every rank runs the same replicated solve
     h->pcg_s_in_smem = (full <= (size_t)220 * 1024) ? 1 : 0;
     h->pcg_smem = h->pcg_s_in_smem ? full : lean;
     h->pcg_threads = 32 * std::min(32, std::max(2, nf_max));
@@ -292,7 +292,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
       if (pcg_cluster_smem_bytes(nf_max, rows_cap, h->pcg_ent_cap) > (size_t)200 * 1024) { h->pcg_rows_cap = 0; h->pcg_ent_cap = 0; }
     }
     h->pcg_cluster_smem = pcg_cluster_smem_bytes(nf_max, h->pcg_rows_cap, h->pcg_ent_cap);
-    h->pcg_cluster_ok = (nf_max >= (std::getenv("SBA_FORCE_CLUSTER") ? 1 : 24) && H.nwin <= 64 && h->pcg_cluster_smem <= (size_t)200 * 1024 && !std::getenv("SBA_NO_CLUSTER"));
+    h->pcg_cluster_ok = (nf_max >= (std::getenv("SBA_FORCE_CLUSTER") ? 1 : 24) && H.nwin <= 64 && h->pcg_cluster_smem <= (size_t)200 * 1024 && !std::getenv("SBA_NO_CLUSTER") && !std::getenv("SBA_FORCE_MULTILAUNCH"));
     if (h->pcg_cluster_ok)
       CUDA_TRY(cudaFuncSetAttribute(k_pcg_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->pcg_cluster_smem, 1024)));
     if (h->pcg_window_ok)

@@ -97,6 +97,31 @@ def test_pcg_solves_the_reduced_system(small_window):
     assert np.abs(x - xs).max() <= 1e-8 * np.abs(xs).max()
 
 
+@pytest.mark.parametrize("path", ["window", "cluster", "multilaunch"])
+def test_every_pcg_path_solves_the_same_system(small_window, path, monkeypatch):
+    """The reduced system goes through one of three PCG kernels depending on its size (one CTA per window, one
+    8-CTA cluster per window, or the multi-launch global path); force each on the same small window."""
+    for k in ("SBA_NO_CLUSTER", "SBA_FORCE_CLUSTER", "SBA_FORCE_MULTILAUNCH"):
+        monkeypatch.delenv(k, raising=False)
+    if path == "cluster":
+        monkeypatch.setenv("SBA_FORCE_CLUSTER", "1")
+    elif path == "multilaunch":
+        monkeypatch.setenv("SBA_FORCE_MULTILAUNCH", "1")
+    else:
+        monkeypatch.setenv("SBA_NO_CLUSTER", "1")
+    w = small_window
+    s = load(w)
+    s.linearize(); s.schur(1e4)
+    it = s.pcg(default_options(pcg_tolerance=1e-12, max_pcg_iterations=500))
+    S, rhs, x = s.schur_dense()
+    xs = np.linalg.solve(S, rhs)
+    assert 0 < it <= 500
+    assert np.abs(x - xs).max() <= 1e-8 * np.abs(xs).max()
+    po, xo, so = oracle.solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"], options=oracle_opts())
+    poses, points, summ = Solver(0).solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"], options=PARITY)
+    check_solution(w, summ, poses, points, so, po, xo)
+
+
 def check_solution(w, summary, poses, points, so, po, xo):
     assert abs(summary["final_cost"] - so["final_cost"]) <= 1e-5 * so["final_cost"]
     assert np.abs(poses[:, :3] - po[:, :3]).max() < 1e-5          # rad

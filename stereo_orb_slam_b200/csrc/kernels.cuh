@@ -47,22 +47,23 @@ __device__ __forceinline__ double block_max1(double v, double* sm /* [4] */) {
   return fmax(fmax(sm[0], sm[1]), fmax(sm[2], sm[3]));
 }
 
-__device__ __forceinline__ void load_campre(const CamPre* __restrict__ base, int c, CamPre& out) {
+// (.cg loads: the trial camera table is rewritten every line-search round inside one cooperative kernel)
+__device__ __forceinline__ void load_campre(const CamPre* base, int c, CamPre& out) {
   const double* s = reinterpret_cast<const double*>(base + c);
 #pragma unroll
-  for (int i = 0; i < 9; ++i) out.R[i] = __ldg(s + i);
+  for (int i = 0; i < 9; ++i) out.R[i] = __ldcg(s + i);
 #pragma unroll
-  for (int i = 0; i < 9; ++i) out.Jl[i] = __ldg(s + 9 + i);
+  for (int i = 0; i < 9; ++i) out.Jl[i] = __ldcg(s + 9 + i);
 #pragma unroll
-  for (int i = 0; i < 3; ++i) out.t[i] = __ldg(s + 18 + i);
+  for (int i = 0; i < 3; ++i) out.t[i] = __ldcg(s + 18 + i);
 }
 // R and t only (cost evaluation)
-__device__ __forceinline__ void load_campre_Rt(const CamPre* __restrict__ base, int c, CamPre& out) {
+__device__ __forceinline__ void load_campre_Rt(const CamPre* base, int c, CamPre& out) {
   const double* s = reinterpret_cast<const double*>(base + c);
 #pragma unroll
-  for (int i = 0; i < 9; ++i) out.R[i] = __ldg(s + i);
+  for (int i = 0; i < 9; ++i) out.R[i] = __ldcg(s + i);
 #pragma unroll
-  for (int i = 0; i < 3; ++i) out.t[i] = __ldg(s + 18 + i);
+  for (int i = 0; i < 3; ++i) out.t[i] = __ldcg(s + 18 + i);
 }
 
 // ------------------------------------------------------------------------------------------ K0
@@ -1056,10 +1057,9 @@ __global__ void __launch_bounds__(kPcgClThreads, 1) k_pcg_cluster(Dev d, DevPara
 // ------------------------------------------------------------------------- K5: back-substitution
 // thread per point: dp = -Vinv (gp + sum_obs W_e^T dc[cam(e)])   (stored; the candidate is formed by the
 // line-search kernels).  chunk partials: g.dp, dp^T D dp, |x|^2, max|dp|
-__global__ void __launch_bounds__(kThreads) k_backsub(Dev d, DevParams P) {
+__device__ __forceinline__ void dev_backsub(const Dev& d, const DevParams& P, int chunk) {
   __shared__ double sm[4 * 3];
   __shared__ double smx[4];
-  const int chunk = blockIdx.x;
   const int p = d.pchunk_begin[chunk] + threadIdx.x;
   const int w = d.pchunk_win[chunk];
   double part[3] = {0, 0, 0};
@@ -1103,12 +1103,13 @@ __global__ void __launch_bounds__(kThreads) k_backsub(Dev d, DevParams P) {
   if (threadIdx.x == 3) d.step_part[(size_t)chunk * 4 + 3] = mx;
 }
 
+__global__ void __launch_bounds__(kThreads) k_backsub(Dev d, DevParams P) { dev_backsub(d, P, blockIdx.x); }
+
 // one CTA per window: the step scalars (cameras + point chunk partials) and the line-search start state.
 // (multi-GPU: camera terms are counted on rank 0 only; the scalars are all-reduced afterwards)
-__global__ void __launch_bounds__(kThreads) k_cam_step(Dev d, int rank) {
+__device__ __forceinline__ void dev_cam_step(const Dev& d, int w, int rank) {
   __shared__ double sm[4 * 4];
   __shared__ double smx[4];
-  const int w = blockIdx.x;
   double part[4] = {0, 0, 0, 0};   // g.d, d D d, |x|^2, dc . r_pcg
   double dmax = 0.0;
   const double radius = d.w_radius[w];
@@ -1148,16 +1149,17 @@ __global__ void __launch_bounds__(kThreads) k_cam_step(Dev d, int rank) {
   if (threadIdx.x == 3) d.w_dr[w] = tot;
 }
 
+__global__ void __launch_bounds__(kThreads) k_cam_step(Dev d, int rank) { dev_cam_step(d, blockIdx.x, rank); }
+
 // ----------------------------------------------- K6: trial point of the projected line search + its cost
 // Ceres evaluates x (+) s*delta with the bounds projection inside Plus (parameter_block.h), first at s = 1.
 // thread per camera of a searching window: trial pose and its precompute
-__global__ void k_trial_cams(Dev d) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void dev_trial_cam(const Dev& d, int c) {
   if (c >= d.Nc) return;
   const int w = d.cam_win[c];
-  const int st = d.w_ls_state[w];
+  const int st = __ldcg(d.w_ls_state + w);
   if (st < 1 || st > 3) return;
-  const double step = d.w_ls_x[w];
+  const double step = __ldcg(d.w_ls_x + w);
   const int f = d.fc[c];
   double pose[6];
 #pragma unroll
@@ -1171,16 +1173,17 @@ __global__ void k_trial_cams(Dev d) {
   d.campre_new[c] = cp;
 }
 
+__global__ void k_trial_cams(Dev d) { dev_trial_cam(d, blockIdx.x * blockDim.x + threadIdx.x); }
+
 // thread per point: trial point, cost, |x_trial - x|^2 and (state 2) the directional derivative
 //   d/ds cost = sum_obs  rho' (D^T r) . (G dw + dt + R dp)     evaluated at the trial point
-__global__ void __launch_bounds__(kThreads) k_trial_points(Dev d, DevParams P) {
+__device__ __forceinline__ void dev_trial_points(const Dev& d, const DevParams& P, int chunk) {
   __shared__ double sm[4 * 3];
-  const int chunk = blockIdx.x;
   const int w = d.pchunk_win[chunk];
-  const int st = d.w_ls_state[w];
+  const int st = __ldcg(d.w_ls_state + w);
   if (st < 1 || st > 3) return;
   const bool grad = (st == 2);
-  const double step = d.w_ls_x[w];
+  const double step = __ldcg(d.w_ls_x + w);
   const int p = d.pchunk_begin[chunk] + threadIdx.x;
   double part[3] = {0, 0, 0};
   if (p < d.pchunk_end[chunk]) {
@@ -1230,25 +1233,28 @@ __global__ void __launch_bounds__(kThreads) k_trial_points(Dev d, DevParams P) {
   if (threadIdx.x < 3) d.ls_part[(size_t)chunk * 3 + threadIdx.x] = tot;
 }
 
+__global__ void __launch_bounds__(kThreads) k_trial_points(Dev d, DevParams P) { dev_trial_points(d, P, blockIdx.x); }
+
 // one CTA per searching window: raw sums (cost, directional derivative, |step|^2 incl. the cameras on rank 0)
-__global__ void __launch_bounds__(kThreads) k_ls_reduce(Dev d, int rank) {
+__device__ __forceinline__ void dev_ls_reduce(const Dev& d, int w, int rank) {
   __shared__ double sm[4 * 3];
-  const int w = blockIdx.x;
-  const int st = d.w_ls_state[w];
+  const int st = __ldcg(d.w_ls_state + w);
   if (st < 1 || st > 3) return;
   double part[3] = {0, 0, 0};
   for (int ch = d.win_pchunk_off[w] + threadIdx.x; ch < d.win_pchunk_off[w + 1]; ch += kThreads) {
 #pragma unroll
-    for (int i = 0; i < 3; ++i) part[i] += d.ls_part[(size_t)ch * 3 + i];
+    for (int i = 0; i < 3; ++i) part[i] += __ldcg(d.ls_part + (size_t)ch * 3 + i);
   }
   if (rank == 0)
     for (int c = d.win_cam_off[w] + threadIdx.x; c < d.win_cam_off[w + 1]; c += kThreads) {
 #pragma unroll
-      for (int i = 0; i < 6; ++i) { const double dd = d.poses_new[(size_t)c * 6 + i] - d.poses[(size_t)c * 6 + i]; part[2] += dd * dd; }
+      for (int i = 0; i < 6; ++i) { const double dd = __ldcg(d.poses_new + (size_t)c * 6 + i) - d.poses[(size_t)c * 6 + i]; part[2] += dd * dd; }
     }
   const double tot = block_sum<3>(part, sm);
   if (threadIdx.x < 3) d.w_ls_red[(size_t)threadIdx.x * d.nwin + w] = tot;
 }
+
+__global__ void __launch_bounds__(kThreads) k_ls_reduce(Dev d, int rank) { dev_ls_reduce(d, blockIdx.x, rank); }
 
 // -------------------------------------------------------------------------------- LM control
 // Ceres trust-region rules (trust_region_minimizer.cc / levenberg_marquardt_strategy.cc restated;
@@ -1272,8 +1278,7 @@ __global__ void k_lm_begin(Dev d, DevParams P, double initial_radius, int first)
 // Projected Armijo line search, one thread per window (ArmijoLineSearch::DoSearch restated; see
 // sba_linesearch.cuh).  States: 1 full step evaluated (cost only) · 2 trial evaluated with its directional
 // derivative · 3 full step re-evaluated after a failed search · 4 candidate ready for k_lm_control · 0 idle.
-__global__ void k_ls_control(Dev d, DevParams P) {
-  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void dev_ls_control(const Dev& d, const DevParams& P, int w, int32_t* searching) {
   if (w >= d.nwin) return;
   const int st = d.w_ls_state[w];
   if (st < 1 || st > 3) return;
@@ -1290,7 +1295,7 @@ __global__ void k_ls_control(Dev d, DevParams P) {
   if (valid && f <= cost0 + 1e-4 * gd * x) { d.w_cand[w] = f; d.w_step2[w] = step2; d.w_ls_state[w] = 4; return; }
   if (st == 1 && valid) {          // sufficient decrease failed: the same step again, now with the derivative
     d.w_ls_state[w] = 2;
-    atomicAdd(d.counters + 3, 1);
+    atomicAdd(searching, 1);
     return;
   }
   bool failed = false;
@@ -1309,11 +1314,11 @@ __global__ void k_ls_control(Dev d, DevParams P) {
     d.w_ls_px[w] = x; d.w_ls_pf[w] = f; d.w_ls_pg[w] = g; d.w_ls_pvalid[w] = valid ? 1 : 0;
     d.w_ls_x[w] = nx; d.w_ls_state[w] = 2;
   }
-  atomicAdd(d.counters + 3, 1);
+  atomicAdd(searching, 1);
 }
+__global__ void k_ls_control(Dev d, DevParams P) { dev_ls_control(d, P, blockIdx.x * blockDim.x + threadIdx.x, d.counters + 3); }
 
-__global__ void k_lm_control(Dev d, DevParams P) {
-  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void dev_lm_control(const Dev& d, const DevParams& P, int w) {
   if (w >= d.nwin) return;
   if (d.w_ls_state[w] != 4) return;      // idle, or its line search is still running
   d.w_ls_state[w] = 0;
@@ -1356,6 +1361,8 @@ __global__ void k_lm_control(Dev d, DevParams P) {
   }
 }
 
+__global__ void k_lm_control(Dev d, DevParams P) { dev_lm_control(d, P, blockIdx.x * blockDim.x + threadIdx.x); }
+
 // wall-clock limit hit on the host (reference: max_solver_time_in_seconds, src/bundle_adjuster.cpp:18)
 __global__ void k_lm_timeout(Dev d) {
   const int w = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1363,18 +1370,56 @@ __global__ void k_lm_timeout(Dev d) {
 }
 
 // accepted windows: candidate -> current
-__global__ void __launch_bounds__(kThreads) k_apply_points(Dev d) {
-  const int chunk = blockIdx.x;
-  if (!d.w_accept[d.pchunk_win[chunk]]) return;
+__device__ __forceinline__ void dev_apply_points(const Dev& d, int chunk) {
+  if (!__ldcg(d.w_accept + d.pchunk_win[chunk])) return;
   const int p = d.pchunk_begin[chunk] + threadIdx.x;
   if (p >= d.pchunk_end[chunk]) return;
 #pragma unroll
   for (int i = 0; i < 3; ++i) d.pts[(size_t)p * 3 + i] = d.pts_new[(size_t)p * 3 + i];
 }
-__global__ void k_apply_cams(Dev d) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(kThreads) k_apply_points(Dev d) { dev_apply_points(d, blockIdx.x); }
+__device__ __forceinline__ void dev_apply_cam(const Dev& d, int t) {
   if (t >= d.Nc * 6) return;
-  if (d.w_accept[d.cam_win[t / 6]]) d.poses[t] = d.poses_new[t];
+  if (__ldcg(d.w_accept + d.cam_win[t / 6])) d.poses[t] = __ldcg(d.poses_new + t);
+}
+__global__ void k_apply_cams(Dev d) { dev_apply_cam(d, blockIdx.x * blockDim.x + threadIdx.x); }
+
+// K5 + K6 + the trust-region decision of every window in ONE cooperative launch (single GPU): back-substitution,
+// step scalars, then the projected line search round by round — trial cameras | grid barrier | trial points and
+// their costs | grid barrier | per-window reduction and the Armijo / LM decision | grid barrier — until no window
+// is still searching, then accepted candidates become the state.  Replaces 5 launches, a memset and a host round
+// trip per line-search round.  The searching counter alternates between counters[3] and [5] so that resetting
+// one never races with reading the other; counters[6] returns the number of rounds.
+__global__ void __launch_bounds__(kThreads) k_step_loop(Dev d, DevParams P) {
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  const int nb = gridDim.x;
+  for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) { dev_backsub(d, P, ch); __syncthreads(); }
+  if (blockIdx.x == 0 && threadIdx.x == 0) { d.counters[0] = 0; d.counters[2] = 0; d.counters[3] = 0; d.counters[5] = 0; }
+  grid.sync();
+  for (int w = blockIdx.x; w < d.nwin; w += nb) { dev_cam_step(d, w, 0); __syncthreads(); }
+  grid.sync();
+  int round = 0;
+  for (;;) {
+    int32_t* cnt = d.counters + ((round & 1) ? 5 : 3);
+    int32_t* other = d.counters + ((round & 1) ? 3 : 5);
+    for (int c = blockIdx.x * kThreads + threadIdx.x; c < d.Nc; c += nb * kThreads) dev_trial_cam(d, c);
+    grid.sync();
+    for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) { dev_trial_points(d, P, ch); __syncthreads(); }
+    grid.sync();
+    if (blockIdx.x == 0 && threadIdx.x == 0) *other = 0;
+    for (int w = blockIdx.x; w < d.nwin; w += nb) {
+      dev_ls_reduce(d, w, 0);
+      __syncthreads();
+      if (threadIdx.x == 0) { dev_ls_control(d, P, w, cnt); dev_lm_control(d, P, w); }
+      __syncthreads();
+    }
+    grid.sync();
+    ++round;
+    if (__ldcg(cnt) <= 0 || round > 64) break;
+  }
+  for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) dev_apply_points(d, ch);
+  for (int t = blockIdx.x * kThreads + threadIdx.x; t < d.Nc * 6; t += nb * kThreads) dev_apply_cam(d, t);
+  if (blockIdx.x == 0 && threadIdx.x == 0) d.counters[6] = round;
 }
 
 // permute the caller's observations into the point-sorted view

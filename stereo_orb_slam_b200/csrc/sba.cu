@@ -60,6 +60,7 @@ struct sba_handle_s {
   double last_radius = 1e4;
   // single-launch PCG (k_pcg_window): usable when every window's system fits one CTA
   bool pcg_window_ok = false; int pcg_s_in_smem = 0; size_t pcg_smem = 0; int pcg_threads = 1024;
+  int coop_blocks = 0;        // co-resident CTAs of k_step_loop (0: cooperative launch unavailable)
   bool pcg_cluster_ok = false; size_t pcg_cluster_smem = 0; int pcg_rows_cap = 0, pcg_ent_cap = 0;   // one 8-CTA cluster per window (k_pcg_cluster)
   size_t lin_smem = 0, schur_smem = 0;   // dynamic shared memory of the per-chunk kernels (largest chunk)
 
@@ -137,6 +138,13 @@ int sba_create(int device, sba_handle* out) {
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
+    if (e == cudaSuccess && !std::getenv("SBA_NO_COOP")) {
+      int coop = 0, per_sm = 0, sms = 0;
+      cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+      if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_step_loop, kThreads, 0) == cudaSuccess)
+        h->coop_blocks = per_sm * sms;
+    }
     if (e == cudaSuccess) {      // keep freed blocks in the device's default pool (no trim at synchronisation points)
       cudaMemPool_t pool = nullptr;
       if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
@@ -506,6 +514,19 @@ static int do_step(sba_handle h, int* ls_rounds) {
   Dev& d = h->d;
   const DevParams& P = h->P;
   const int rank = (int)(h->comm.active() ? h->comm.rank : 0);
+  if (!h->comm.active() && h->coop_blocks > 0) {
+    // single GPU: the whole step in one cooperative launch (k_step_loop), one host read at the end
+    const int want = std::max(std::max(d.npchunk, d.nwin), cdiv(d.Nc, kThreads));
+    const int grid = std::max(1, std::min(h->coop_blocks, want));
+    Dev dd = d; DevParams pp = P;
+    void* args[] = {&dd, &pp};
+    CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_step_loop, dim3(grid), dim3(kThreads), args, 0, h->stream));
+    h->launches++;
+    CUDA_TRY(cudaMemcpyAsync(h->h_counters, d.counters, 32, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (ls_rounds) *ls_rounds += h->h_counters[6];
+    return SBA_OK;
+  }
   int rc;
   CUDA_TRY(cudaMemsetAsync(d.counters, 0, 4, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.counters + 2, 0, 4, h->stream));

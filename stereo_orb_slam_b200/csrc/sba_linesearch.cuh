@@ -78,10 +78,52 @@ SBA_HD int ls_fit_polynomial(const LsSample* s, int n, double* c /* [6] */) {
   return deg;
 }
 
+// One root of the complex polynomial sum_k (ar[k] + i ai[k]) x^k of degree m by Laguerre's iteration, started
+// from (and returned in) xr + i xi.  Textbook algorithm (p, p', p'' by Horner; step m / (G +- sqrt((m-1)(m H - G^2)))
+// with the larger denominator; an occasional fractional step breaks limit cycles).
+SBA_HD void sba_ls_laguerre(const double* ar, const double* ai, int m, double& xr, double& xi) {
+  const double frac[8] = {0.5, 0.25, 0.75, 0.13, 0.38, 0.62, 0.88, 1.0};
+  for (int it = 1; it <= 80; ++it) {
+    double br = ar[m], bi = ai[m], dr = 0.0, di = 0.0, fr = 0.0, fi = 0.0;
+    double err = sqrt(br * br + bi * bi);
+    const double abx = sqrt(xr * xr + xi * xi);
+    for (int j = m - 1; j >= 0; --j) {
+      double tr = xr * fr - xi * fi + dr, ti = xr * fi + xi * fr + di; fr = tr; fi = ti;
+      tr = xr * dr - xi * di + br; ti = xr * di + xi * dr + bi; dr = tr; di = ti;
+      tr = xr * br - xi * bi + ar[j]; ti = xr * bi + xi * br + ai[j]; br = tr; bi = ti;
+      err = sqrt(br * br + bi * bi) + abx * err;
+    }
+    const double babs2 = br * br + bi * bi;
+    if (!(babs2 > 0.0) || sqrt(babs2) <= 1e-15 * err) return;          // at a root (to rounding)
+    // G = p'/p, H = G^2 - 2 (p''/2)/p
+    const double gr = (dr * br + di * bi) / babs2, gi = (di * br - dr * bi) / babs2;
+    const double g2r = gr * gr - gi * gi, g2i = 2.0 * gr * gi;
+    const double qr = (fr * br + fi * bi) / babs2, qi = (fi * br - fr * bi) / babs2;
+    const double hr = g2r - 2.0 * qr, hi = g2i - 2.0 * qi;
+    // sq = sqrt((m-1) (m H - G^2))
+    const double sr0 = (double)(m - 1) * ((double)m * hr - g2r), si0 = (double)(m - 1) * ((double)m * hi - g2i);
+    const double sabs = sqrt(sr0 * sr0 + si0 * si0);
+    double sqr = sqrt(0.5 * fmax(sabs + sr0, 0.0)), sqi = sqrt(0.5 * fmax(sabs - sr0, 0.0));
+    if (si0 < 0.0) sqi = -sqi;
+    double pr = gr + sqr, pi = gi + sqi;
+    const double mr = gr - sqr, mi = gi - sqi;
+    if (pr * pr + pi * pi < mr * mr + mi * mi) { pr = mr; pi = mi; }
+    const double pabs2 = pr * pr + pi * pi;
+    double dxr, dxi;
+    if (pabs2 > 0.0) { dxr = (double)m * pr / pabs2; dxi = -(double)m * pi / pabs2; }
+    else { dxr = (1.0 + abx) * cos((double)it); dxi = (1.0 + abx) * sin((double)it); }
+    const double nr = xr - dxr, ni = xi - dxi;
+    if (nr == xr && ni == xi) return;                                   // converged
+    if (!isfinite(nr) || !isfinite(ni)) return;
+    if (it % 10) { xr = nr; xi = ni; }
+    else { const double f = frac[(it / 10) & 7]; xr -= f * dxr; xi -= f * dxi; }
+  }
+}
+
 // Real parts of ALL roots (complex ones included — Ceres's MinimizePolynomial looks at the real part of
 // every eigenvalue of the companion matrix) of p(x) = c[0] x^deg + ... + c[deg].  deg <= 4.
 // Returns the number of values written.  Degrees 1 and 2 are closed form (FindLinear/QuadraticPolynomialRoots);
-// 3 and 4 by simultaneous (Durand-Kerner) iteration in complex arithmetic.
+// 3 and 4 by Laguerre's iteration with deflation and polishing, in complex arithmetic.
 SBA_HD int ls_roots_real_parts(const double* cin, int deg, double* out /* [4] */) {
   int lead = 0;
   while (lead < deg && cin[lead] == 0.0) ++lead;     // RemoveLeadingZeros
@@ -101,61 +143,31 @@ SBA_HD int ls_roots_real_parts(const double* cin, int deg, double* out /* [4] */
     }
     return 2;
   }
-  // monic coefficients m[0..deg-1]: x^deg + m[0] x^(deg-1) + ... + m[deg-1]
-  double m[4];
-  double bound = 0.0;
-  for (int i = 0; i < deg; ++i) { m[i] = c[i + 1] / c[0]; bound = fmax(bound, fabs(m[i])); }
-  bound = 1.0 + bound;                                // Cauchy bound on |root|
+  // Degrees 3 and 4: Laguerre's iteration in complex arithmetic with deflation, every root polished on the
+  // undeflated polynomial.  (A simultaneous Durand-Kerner iteration started on the Cauchy circle needs hundreds
+  // of sweeps when the leading coefficient is tiny — the usual case here, a quintic fitted through data that is
+  // almost cubic — and its single thread then costs > 100 us per line-search round.)
+  // a[k] = coefficient of x^k, complex, of the current (deflated) polynomial
+  double ar[5], ai[5];
+  for (int k = 0; k <= deg; ++k) { ar[k] = c[deg - k]; ai[k] = 0.0; }
   double zr[4], zi[4];
-  for (int k = 0; k < deg; ++k) {                     // spread starting points on a circle, off the real axis
-    const double ang = 0.4 + 6.283185307179586 * k / deg;
-    zr[k] = 0.5 * bound * cos(ang); zi[k] = 0.5 * bound * sin(ang);
-  }
-  for (int it = 0; it < 500; ++it) {
-    double change = 0.0;
-    for (int k = 0; k < deg; ++k) {
-      // p(z_k), Horner in complex arithmetic
-      double pr = 1.0, pi = 0.0;
-      for (int i = 0; i < deg; ++i) {
-        const double tr = pr * zr[k] - pi * zi[k] + m[i];
-        const double ti = pr * zi[k] + pi * zr[k];
-        pr = tr; pi = ti;
-      }
-      double qr = 1.0, qi = 0.0;                      // prod_{j != k} (z_k - z_j)
-      for (int j = 0; j < deg; ++j) {
-        if (j == k) continue;
-        const double dr = zr[k] - zr[j], di = zi[k] - zi[j];
-        const double tr = qr * dr - qi * di, ti = qr * di + qi * dr;
-        qr = tr; qi = ti;
-      }
-      const double den = qr * qr + qi * qi;
-      if (!(den > 0.0)) continue;
-      const double wr = (pr * qr + pi * qi) / den, wi = (pi * qr - pr * qi) / den;
-      zr[k] -= wr; zi[k] -= wi;
-      change = fmax(change, fabs(wr) + fabs(wi));
-    }
-    if (change <= 1e-9 * bound) break;
-  }
-  // polish: Newton on p(z) in complex arithmetic from the separated Durand-Kerner estimates (quadratic
-  // convergence: three steps take 1e-9 to rounding level; the slow linear tail of the simultaneous iteration
-  // is what made this routine cost > 100 us in its single thread)
-  for (int k = 0; k < deg; ++k) {
-    for (int it = 0; it < 4; ++it) {
-      double pr = 1.0, pi = 0.0, dr = 0.0, di = 0.0;   // p and p' by Horner
-      for (int i = 0; i < deg; ++i) {
-        const double ndr = dr * zr[k] - di * zi[k] + pr, ndi = dr * zi[k] + di * zr[k] + pi;
-        dr = ndr; di = ndi;
-        const double tr = pr * zr[k] - pi * zi[k] + m[i], ti = pr * zi[k] + pi * zr[k];
-        pr = tr; pi = ti;
-      }
-      const double den = dr * dr + di * di;
-      if (!(den > 0.0) || !isfinite(den)) break;
-      const double wr = (pr * dr + pi * di) / den, wi = (pi * dr - pr * di) / den;
-      if (!isfinite(wr) || !isfinite(wi)) break;
-      zr[k] -= wr; zi[k] -= wi;
-      if (fabs(wr) + fabs(wi) <= 1e-16 * bound) break;
+  int m = deg;
+  for (int found = 0; found < deg; ++found, --m) {
+    double xr = 0.0, xi = 0.0;
+    sba_ls_laguerre(ar, ai, m, xr, xi);
+    zr[found] = xr; zi[found] = xi;
+    // deflate: synthetic division by (x - root)
+    double br = ar[m], bi = ai[m];
+    for (int k = m - 1; k >= 0; --k) {
+      const double tr = ar[k], ti = ai[k];
+      ar[k] = br; ai[k] = bi;
+      const double nr = xr * br - xi * bi + tr, ni = xr * bi + xi * br + ti;
+      br = nr; bi = ni;
     }
   }
+  // polish on the original polynomial
+  for (int k = 0; k <= deg; ++k) { ar[k] = c[deg - k]; ai[k] = 0.0; }
+  for (int k = 0; k < deg; ++k) sba_ls_laguerre(ar, ai, deg, zr[k], zi[k]);
   for (int k = 0; k < deg; ++k) out[k] = zr[k];
   return deg;
 }
@@ -171,12 +183,19 @@ SBA_HD double ls_minimize_interpolating(const LsSample* s, int n, double xmin, d
   if (vmin < best_v) { best_v = vmin; best_x = xmin; }
   if (vmax < best_v) { best_v = vmax; best_x = xmax; }
   if (deg < 2) return best_x;
+  // derivative in the scaled variable y = x / xmax: the search interval becomes [xmin / xmax, 1], the roots that
+  // matter are O(1) and the simultaneous iteration converges in a few tens of steps instead of running to its
+  // cap when the step sizes are ~1e-11 (coefficients spanning 50 orders of magnitude)
+  const double sc = (xmax > 0.0 && isfinite(xmax)) ? xmax : 1.0;
   double dcoef[5];
-  for (int j = 0; j < deg; ++j) dcoef[j] = (double)(deg - j) * c[j];
+  {
+    double pw = 1.0;                                  // sc^(deg-1-j), built from the constant term upwards
+    for (int j = deg - 1; j >= 0; --j) { dcoef[j] = (double)(deg - j) * c[j] * pw; pw *= sc; }
+  }
   double roots[4];
   const int nr = ls_roots_real_parts(dcoef, deg - 1, roots);
   for (int i = 0; i < nr; ++i) {
-    const double r = roots[i];
+    const double r = roots[i] * sc;
     if (!(r >= xmin) || !(r <= xmax)) continue;       // also drops NaN
     const double v = ls_poly_eval(c, deg, r);
     if (v < best_v) { best_v = v; best_x = r; }

@@ -31,3 +31,4 @@ double emu_ls_minimize(int n, const double* x, const double* f, const double* g,
   return sba::ls_minimize_interpolating(s, n, xmin, xmax);
 }
 }
+extern "C" int emu_ls_roots(const double* c, int deg, double* out) { return sba::ls_roots_real_parts(c, deg, out); }

@@ -161,3 +161,22 @@ def test_line_search_step_selection_three_ways(emu):
         scale = max(1.0, abs(pr))
         assert abs(pa - pr) <= 1e-9 * scale and abs(pb - pr) <= 1e-9 * scale, (trial, a, b, ref)
         assert abs(a - b) <= 1e-7 * hi, (trial, a, b, ref)
+
+
+def test_polynomial_root_real_parts_match_numpy(emu):
+    """sba_linesearch.cuh's root finder (closed form up to degree 2, Laguerre + deflation above) against
+    numpy.roots, including the badly scaled case the line search produces (tiny leading coefficient)."""
+    import ctypes as C
+    rng = np.random.default_rng(11)
+    cases = [rng.normal(size=d + 1) for d in (1, 2, 3, 4) for _ in range(20)]
+    cases += [np.array([1e-14, 2.0, -3.0, 0.5, 1.0]), np.array([1e-9, 1e-3, 1.0, -2.0]), np.array([1.0, -4.0, 6.0, -4.0, 1.0 - 1e-8]),
+              np.array([1.0, 0.0, 2.0, 0.0, 1.0 + 1e-6])]
+    for c in cases:
+        c = np.ascontiguousarray(c, np.float64)
+        out = np.zeros(4)
+        n = emu.emu_ls_roots(c.ctypes.data_as(C.POINTER(C.c_double)), C.c_int(c.size - 1), out.ctypes.data_as(C.POINTER(C.c_double)))
+        assert n == c.size - 1
+        ref = np.sort(np.roots(c).real)
+        got = np.sort(out[:n])
+        scale = np.maximum(1.0, np.abs(np.roots(c)).max())
+        assert np.abs(got - ref).max() <= 1e-6 * scale, (c, got, ref)

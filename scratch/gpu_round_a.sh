@@ -10,5 +10,5 @@ cat gpurun_out/bench.json
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
 cat gpurun_out/bench_ref.json
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_launch.log 2>&1; echo "ncu1 rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_lin_chunk|k_schur_chunk' -s 4 -c 2 -o gpurun_out/full_chunks python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_full.log 2>&1; echo "ncu2 rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_lin_chunk|k_schur_chunk|k_assemble_schur|k_assemble_cams' -s 8 -c 4 -f -o gpurun_out/full_chunks python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_full.log 2>&1; echo "ncu2 rc=$?"
 ls -la gpurun_out

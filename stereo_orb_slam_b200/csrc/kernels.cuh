@@ -496,76 +496,103 @@ __global__ void __launch_bounds__(kSchurThreads, 3) k_schur_chunk(Dev d, int max
   }
 }
 
-// One warp per free camera: U (21) and gc (6) = sum of the camera's chunk-slot partials in list order.
-__global__ void __launch_bounds__(256) k_assemble_cams(Dev d) {
-  const int f = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (f >= d.Nf) return;
-  const int c = d.free2cam[f];
-  double tot[7];
-  gather_partials<27, 7>(d.cspart, d.cam_part_off[c], d.cam_part_off[c + 1], lane, tot);
-  if (lane < 4) {
+// Sum of the contiguous partial rows [l0, l1) of one block / camera by a whole CTA of kAsmThreads: warp w takes
+// rows w*8 + pg, + 8*kAsmWarps, ... (gather_partials with a stride), so that even a camera seen by > 100 chunks
+// needs one or two batches of independent loads; the warps' totals are then added in warp order through shared
+// memory.  Thread e < E returns element e (all threads pass the barrier).  Fixed order: bit-reproducible.
+constexpr int kAsmThreads = 128;
+constexpr int kAsmWarps = kAsmThreads / 32;
+
+template <int E, int EG>
+__device__ __forceinline__ double cta_gather(const double* part, int l0, int l1, double* sm /* [kAsmWarps * 4 * EG] */) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int pg = lane >> 2, e0 = (lane & 3) * EG;
+  double acc[EG];
 #pragma unroll
-    for (int k = 0; k < 7; ++k) {
-      const int e = lane * 7 + k;
-      if (e < 21) d.U[(size_t)c * 21 + e] = tot[k];
-      else if (e < 27) d.gc[(size_t)c * 6 + (e - 21)] = tot[k];
+  for (int k = 0; k < EG; ++k) acc[k] = 0.0;
+  constexpr int RS = 8 * kAsmWarps;                 // row groups over the CTA
+  for (int j = l0 + warp * 8 + pg; j < l1; j += 4 * RS) {
+    double v[4][EG];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const bool in = j + RS * u < l1;
+      const double* row = part + (size_t)(in ? j + RS * u : l0) * E + e0;
+#pragma unroll
+      for (int k = 0; k < EG; ++k) v[u][k] = (in && e0 + k < E) ? __ldcg(row + k) : 0.0;
     }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int k = 0; k < EG; ++k) acc[k] += v[u][k];
   }
+#pragma unroll
+  for (int k = 0; k < EG; ++k) {
+    double x = acc[k];
+    x += __shfl_xor_sync(0xffffffffu, x, 4);
+    x += __shfl_xor_sync(0xffffffffu, x, 8);
+    x += __shfl_xor_sync(0xffffffffu, x, 16);
+    if (lane < 4) sm[warp * 4 * EG + e0 + k] = x;
+  }
+  __syncthreads();
+  double tot = 0.0;
+  if (threadIdx.x < E) {
+#pragma unroll
+    for (int w = 0; w < kAsmWarps; ++w) tot += sm[w * 4 * EG + threadIdx.x];
+  }
+  return tot;
 }
 
-// One warp per upper block of S and one per free camera:
-//   block warp   Su[b] = - sum of the block's local partials in list order
-//   camera warp  rsum[f] = sum of the camera's W tp partials; with `prepare` (single GPU: no all-reduce in
+// One CTA per free camera: U (21) and gc (6) = sum of the camera's chunk-slot partials in list order.
+__global__ void __launch_bounds__(kAsmThreads) k_assemble_cams(Dev d) {
+  __shared__ double sm[kAsmWarps * 28];
+  const int f = blockIdx.x;
+  const int c = d.free2cam[f];
+  const double tot = cta_gather<27, 7>(d.cspart, d.cam_part_off[c], d.cam_part_off[c + 1], sm);
+  const int e = threadIdx.x;
+  if (e < 21) d.U[(size_t)c * 21 + e] = tot;
+  else if (e < 27) d.gc[(size_t)c * 6 + (e - 21)] = tot;
+}
+
+// One CTA per upper block of S and one per free camera:
+//   block CTA    Su[b] = - sum of the block's local partials in list order
+//   camera CTA   rsum[f] = sum of the camera's W tp partials; with `prepare` (single GPU: no all-reduce in
 //                between) it also assembles its own diagonal block and does the work of k_cam_prepare:
 //                S_ff += U + D, Minv = S_ff^-1, rhs = rsum - gc
-__global__ void __launch_bounds__(256) k_assemble_schur(Dev d, int prepare) {
-  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (wid < d.nbu) {
-    const int b = wid;
-    if (prepare && d.blk_row[b] == d.blk_col[b]) return;     // diagonal blocks belong to the camera warps
-    double tot[9];
-    gather_partials<36, 9>(d.spart, d.blk_part_off[b], d.blk_part_off[b + 1], lane, tot);
-    if (lane < 4) {
-#pragma unroll
-      for (int k = 0; k < 9; ++k) d.Su[(size_t)b * 36 + lane * 9 + k] = -tot[k];
-    }
+__global__ void __launch_bounds__(kAsmThreads) k_assemble_schur(Dev d, int prepare) {
+  __shared__ double sm[kAsmWarps * 36];
+  __shared__ double sM[36];
+  __shared__ double sr[6];
+  if ((int)blockIdx.x < d.nbu) {
+    const int b = blockIdx.x;
+    if (prepare && d.blk_row[b] == d.blk_col[b]) return;     // diagonal blocks belong to the camera CTAs
+    const double tot = cta_gather<36, 9>(d.spart, d.blk_part_off[b], d.blk_part_off[b + 1], sm);
+    if (threadIdx.x < 36) d.Su[(size_t)b * 36 + threadIdx.x] = -tot;
     return;
   }
-  const int f = wid - d.nbu;
+  const int f = blockIdx.x - d.nbu;
   if (f >= d.Nf) return;
   const int c = d.free2cam[f];
-  double rs[2];
-  gather_partials<6, 2>(d.rpart, d.cam_part_off[c], d.cam_part_off[c + 1], lane, rs);
-  if (lane < 3) { d.rsum[(size_t)f * 6 + 2 * lane] = rs[0]; d.rsum[(size_t)f * 6 + 2 * lane + 1] = rs[1]; }
+  const double rs = cta_gather<6, 2>(d.rpart, d.cam_part_off[c], d.cam_part_off[c + 1], sm);
+  if (threadIdx.x < 6) { d.rsum[(size_t)f * 6 + threadIdx.x] = rs; sr[threadIdx.x] = rs; }
   if (!prepare) return;
+  __syncthreads();                                           // sm is reused
   const int db = d.diag_blk[f];
-  double tot[9];
-  gather_partials<36, 9>(d.spart, d.blk_part_off[db], d.blk_part_off[db + 1], lane, tot);
-  // lane 0 collects the 6x6 and the right-hand side, then factorises (one thread per camera, all cameras in parallel)
+  const double tot = cta_gather<36, 9>(d.spart, d.blk_part_off[db], d.blk_part_off[db + 1], sm);
+  const int w = d.fcam_win[f];
+  if (threadIdx.x < 36) {
+    const int i = threadIdx.x / 6, j = threadIdx.x - 6 * i;
+    const double u = d.U[(size_t)c * 21 + ((i <= j) ? up6(i, j) : up6(j, i))];
+    double v = -tot + u;
+    if (i == j) v += lm_damp(d.sc2c[(size_t)c * 6 + i], u, d.w_radius[w]);
+    sM[threadIdx.x] = v;
+    d.Su[(size_t)db * 36 + threadIdx.x] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  // one thread per camera factorises (all cameras in parallel, registers only)
   double M[36];
 #pragma unroll
-  for (int g = 0; g < 4; ++g)
-#pragma unroll
-    for (int k = 0; k < 9; ++k) M[g * 9 + k] = -__shfl_sync(0xffffffffu, tot[k], g);
-  double r6[6];
-#pragma unroll
-  for (int g = 0; g < 3; ++g) { r6[2 * g] = __shfl_sync(0xffffffffu, rs[0], g); r6[2 * g + 1] = __shfl_sync(0xffffffffu, rs[1], g); }
-  if (lane != 0) return;
-  const int w = d.fcam_win[f];
-  const double radius = d.w_radius[w];
-  const double* U = d.U + (size_t)c * 21;
-  double* S = d.Su + (size_t)db * 36;
-#pragma unroll
-  for (int i = 0; i < 6; ++i)
-#pragma unroll
-    for (int j = 0; j < 6; ++j) {
-      const double u = (i <= j) ? U[up6(i, j)] : U[up6(j, i)];
-      double v = M[6 * i + j] + u;
-      if (i == j) v += lm_damp(d.sc2c[(size_t)c * 6 + i], u, radius);
-      M[6 * i + j] = v;
-    }
-#pragma unroll
-  for (int i = 0; i < 36; ++i) S[i] = M[i];
+  for (int i = 0; i < 36; ++i) M[i] = sM[i];
   if (!inv_spd6(M)) {
     d.w_fail[w] = 1;
 #pragma unroll
@@ -574,7 +601,7 @@ __global__ void __launch_bounds__(256) k_assemble_schur(Dev d, int prepare) {
 #pragma unroll
   for (int i = 0; i < 36; ++i) d.Minv[(size_t)f * 36 + i] = M[i];
 #pragma unroll
-  for (int i = 0; i < 6; ++i) d.rhs[(size_t)f * 6 + i] = r6[i] - d.gc[(size_t)c * 6 + i];
+  for (int i = 0; i < 6; ++i) d.rhs[(size_t)f * 6 + i] = sr[i] - d.gc[(size_t)c * 6 + i];
 }
 
 // thread per free camera: add U + D to the diagonal block, rhs = -gc + rsum, Minv = (S_ii)^-1
@@ -1285,6 +1312,7 @@ __device__ __forceinline__ void dev_ls_control(const Dev& d, const DevParams& P,
   const double f = d.w_ls_red[w], g = d.w_ls_red[(size_t)d.nwin + w], step2 = d.w_ls_red[2 * (size_t)d.nwin + w];
   const double x = d.w_ls_x[w];
   const double cost0 = d.w_cost[w], gd = d.w_gd[w];
+  if (P.debug && w == 0) printf("[ls] it %d st %d x %.6e f-cost0 %.6e armijo_rhs %.6e g %.6e gd %.6e\n", d.w_iter[w] + 1, st, x, f - cost0, 1e-4 * gd * x, g, gd);
   if (st == 3) { d.w_cand[w] = f; d.w_step2[w] = step2; d.w_ls_state[w] = 4; return; }
   if (st == 1) {
     // an invalid trust-region step never reaches the line search (k_lm_control treats it)

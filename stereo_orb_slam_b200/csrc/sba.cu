@@ -321,6 +321,7 @@ static void fill_params(sba_handle h, const sba_options* o) {
   P.pcg_tol2 = o->pcg_tolerance * o->pcg_tolerance;
   P.rdim = (o->residual_dim == 3) ? 3 : 4;
   P.max_iterations = o->max_iterations;
+  P.debug = std::getenv("SBA_DEBUG_LS") ? 1 : 0;
 }
 
 static int check_ready(sba_handle h, bool need_state) {
@@ -395,7 +396,7 @@ static int do_linearize(sba_handle h, bool keep_cost = false) {
     CUDA_TRY(cudaMemsetAsync(d.gc, 0, (size_t)d.Nc * 6 * 8, h->stream));
   }
   if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; }
-  LAUNCH(h, k_assemble_cams, cdiv((int64_t)d.Nf * 32, 256), 256, d);
+  LAUNCH(h, k_assemble_cams, d.Nf, kAsmThreads, d);
   if (h->comm.active()) {
     std::string _err;
     if (!h->comm.allreduce(d.U, (size_t)d.Nc * 21, false, h->stream, &_err) ||
@@ -424,7 +425,7 @@ static int do_schur(sba_handle h) {
   }
   if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++; }
   const int fused = h->comm.active() ? 0 : 1;     // multi-GPU: the partial sums are all-reduced before the cameras are prepared
-  LAUNCH(h, k_assemble_schur, cdiv(((int64_t)d.nbu + d.Nf) * 32, 256), 256, d, fused);
+  LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, fused);
   if (fused) { CUDA_TRY(cudaGetLastError()); return SBA_OK; }
   if (h->comm.active()) {
     std::string _err;
@@ -651,13 +652,13 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
     CUDA_TRY(cudaEventRecord(h->ev[6], h->stream));
     switch (stage) {
       case 0: if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; } break;
-      case 1: LAUNCH(h, k_assemble_schur, cdiv(((int64_t)d.nbu + d.Nf) * 32, 256), 256, d, 1); break;
+      case 1: LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 1); break;
       case 2: if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++; } break;
       case 3: if ((rc = do_linearize(h))) return rc; break;
       case 4: if ((rc = do_schur(h))) return rc; break;
       case 8: if ((rc = do_linearize(h))) return rc; if ((rc = do_schur(h))) return rc; break;
       case 5: LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P); break;
-      case 9: LAUNCH(h, k_assemble_cams, cdiv((int64_t)d.Nf * 32, 256), 256, d); break;
+      case 9: LAUNCH(h, k_assemble_cams, d.Nf, kAsmThreads, d); break;
       case 10: LAUNCH(h, k_lin_finish, d.nwin, kThreads, d, P, 0); break;
       case 6:      // one line-search evaluation of the full step (needs sba_schur + sba_pcg for a meaningful step)
         LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P);

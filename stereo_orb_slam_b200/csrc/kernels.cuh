@@ -162,7 +162,7 @@ __device__ __forceinline__ void gather_partials(const double* part, int l0, int 
   }
 }
 
-__global__ void __launch_bounds__(kLinThreads, 2) k_lin_chunk(Dev d, DevParams P, int dbg) {
+__global__ void __launch_bounds__(kLinThreads, 3) k_lin_chunk(Dev d, DevParams P, int dbg) {
   extern __shared__ double smem[];
   __shared__ double sm1[kLinThreads / 32];
   __shared__ double smx[kLinThreads / 32];
@@ -372,7 +372,7 @@ __host__ __device__ __forceinline__ size_t schur_smem_bytes(int n, int np, int n
   return ((size_t)n * kZStride + (size_t)np * 9) * 8 + (size_t)((n + 15) & ~15) + (size_t)(npairs <= kSchurPairCap ? npairs : 0) * 2;
 }
 
-__global__ void __launch_bounds__(kSchurThreads, 3) k_schur_chunk(Dev d, int max_pairs, int dbg) {
+__global__ void __launch_bounds__(kSchurThreads, 4) k_schur_chunk(Dev d, int max_pairs, int dbg) {
   extern __shared__ __align__(16) double smem[];
   const int chunk = blockIdx.x;
   const int p0 = d.pchunk_begin[chunk], p1 = d.pchunk_end[chunk], np = p1 - p0;
@@ -1101,6 +1101,130 @@ __global__ void __launch_bounds__(kPcgClThreads, 1) k_pcg_cluster(Dev d, DevPara
     d.x[(size_t)f0 * 6 + i] = x[i]; d.r[(size_t)f0 * 6 + i] = r[i];
   }
   if (rank == 0 && threadIdx.x == 0) { d.w_pcg_it[w] = it; if (fail) d.w_fail[w] = 1; atomicMax(d.counters + 4, it); }   // control-plane counter
+}
+
+// Global problems (one window, thousands of free cameras): the whole PCG solve in ONE cooperative launch over
+// the block-CSR in global memory, two grid barriers per iteration.
+//   A  warp per block-row: Ap = S p with p = z + beta p_old formed on the fly from the previous iteration's
+//      vectors (the row's own p goes to the other p buffer: no barrier between "update p" and "use p");
+//      per-row p.Ap                                                                  -> grid barrier
+//      every CTA sums the per-row dots in the same fixed order -> the same alpha everywhere, no broadcast
+//   B  warp per block-row: x += alpha p, r -= alpha Ap, z = Minv r, per-row r.z     -> grid barrier
+// counters[4] returns the iteration count.  Vectors: d.x, d.r, d.z, d.Ap, p ping-pong in d.p / pbuf.
+__device__ __forceinline__ double coop_sum(const double* v, int n, double* sm /* [4] */) {
+  double s[1] = {0.0};
+  for (int i = threadIdx.x; i < n; i += kThreads) s[0] += __ldcg(v + i);
+  const double t = block_sum<1>(s, sm);
+  __shared__ double bc;
+  if (threadIdx.x == 0) bc = t;
+  __syncthreads();
+  return bc;
+}
+
+__global__ void __launch_bounds__(kThreads) k_pcg_coop(Dev d, DevParams P, int max_it, double* pbuf, double* rowdot) {
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  __shared__ double sm[4];
+  const int lane = threadIdx.x & 31;
+  const int gw = (blockIdx.x * kThreads + threadIdx.x) >> 5, nw = (gridDim.x * kThreads) >> 5;
+  const int nf = d.Nf;
+  if (d.w_status[0] != 0 || d.w_fail[0] != 0) { if (blockIdx.x == 0 && threadIdx.x == 0) d.w_pcg_it[0] = 0; return; }
+  const int ps = lane / 6, ri = lane - 6 * ps;
+  // init: x = 0, r = rhs, z = Minv r, p_old = 0 (so that p = z + beta * 0 in the first mat-vec), per-row r.z
+  for (int f = gw; f < nf; f += nw) {
+    double rj[6], z = 0.0;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) rj[j] = d.rhs[(size_t)f * 6 + j];
+    if (lane < 6) {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) z += d.Minv[(size_t)f * 36 + 6 * lane + j] * rj[j];
+      d.x[(size_t)f * 6 + lane] = 0.0; d.r[(size_t)f * 6 + lane] = rj[lane]; d.z[(size_t)f * 6 + lane] = z;
+      d.p[(size_t)f * 6 + lane] = 0.0; pbuf[(size_t)f * 6 + lane] = 0.0;
+    }
+    double dot = (lane < 6) ? rj[lane < 6 ? lane : 0] * z : 0.0;
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);   // lanes 0..7 (6, 7 hold zero)
+    if (lane == 0) rowdot[f] = dot;
+  }
+  grid.sync();
+  double rz = coop_sum(rowdot, nf, sm);
+  const double rz0 = rz;
+  int it = 0;
+  bool fail = false;
+  double beta = 0.0;
+  double* pold = d.p; double* pnew = pbuf;
+  if (!(rz > 0.0)) { if (!(rz == 0.0)) fail = true; }
+  else {
+    for (;;) {
+      // ---- A
+      for (int f = gw; f < nf; f += nw) {
+        double acc = 0.0;
+        if (lane < 30) {
+          const int j1 = d.row_ptr[f + 1];
+          for (int j = d.row_ptr[f] + ps; j < j1; j += 5) {
+            const int col = __ldg(d.bsr_col + j), bi = __ldg(d.bsr_blk + j);
+            double xv[6];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) xv[c] = __ldcg(d.z + (size_t)col * 6 + c) + beta * __ldcg(pold + (size_t)col * 6 + c);
+            if (bi >= 0) {
+              const double* B = d.Su + (size_t)bi * 36 + 6 * ri;
+              acc += (__ldg(B) * xv[0] + __ldg(B + 1) * xv[1] + __ldg(B + 2) * xv[2]) + (__ldg(B + 3) * xv[3] + __ldg(B + 4) * xv[4] + __ldg(B + 5) * xv[5]);
+            } else {
+              const double* B = d.Su + (size_t)(~bi) * 36 + ri;
+              acc += (__ldg(B) * xv[0] + __ldg(B + 6) * xv[1] + __ldg(B + 12) * xv[2]) + (__ldg(B + 18) * xv[3] + __ldg(B + 24) * xv[4] + __ldg(B + 30) * xv[5]);
+            }
+          }
+        }
+        double tot = acc;
+#pragma unroll
+        for (int g = 1; g < 5; ++g) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * g) & 31);
+        double dot = 0.0;
+        if (lane < 6) {
+          const double pv = __ldcg(d.z + (size_t)f * 6 + lane) + beta * __ldcg(pold + (size_t)f * 6 + lane);
+          pnew[(size_t)f * 6 + lane] = pv;
+          d.Ap[(size_t)f * 6 + lane] = tot;
+          dot = pv * tot;
+        }
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+        if (lane == 0) rowdot[f] = dot;
+      }
+      grid.sync();
+      const double pAp = coop_sum(rowdot, nf, sm);
+      if (!(pAp > 0.0)) { fail = true; break; }
+      const double alpha = rz / pAp;
+      // ---- B (the warp that owns a row in A owns it here too: its own pnew / Ap writes are visible to it)
+      for (int f = gw; f < nf; f += nw) {
+        double rj[6];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) rj[j] = __ldcg(d.r + (size_t)f * 6 + j) - alpha * __ldcg(d.Ap + (size_t)f * 6 + j);
+        double dot = 0.0;
+        __syncwarp();                      // every lane has read the old r before lanes 0..5 overwrite it
+        if (lane < 6) {
+          double z = 0.0;
+#pragma unroll
+          for (int j = 0; j < 6; ++j) z += d.Minv[(size_t)f * 36 + 6 * lane + j] * rj[j];
+          d.x[(size_t)f * 6 + lane] += alpha * __ldcg(pnew + (size_t)f * 6 + lane);
+          double mine = 0.0;
+#pragma unroll
+          for (int j = 0; j < 6; ++j) if (j == lane) mine = rj[j];
+          d.r[(size_t)f * 6 + lane] = mine; d.z[(size_t)f * 6 + lane] = z;
+          dot = mine * z;
+        }
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+        if (lane == 0) rowdot[f] = dot;
+      }
+      grid.sync();
+      const double rz_new = coop_sum(rowdot, nf, sm);
+      { double* t = pold; pold = pnew; pnew = t; }
+      ++it;
+      if (!isfinite(rz_new)) { fail = true; break; }
+      if (rz_new <= P.pcg_tol2 * rz0 || it >= max_it) { rz = rz_new; break; }
+      beta = rz_new / rz;
+      rz = rz_new;
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) { d.w_pcg_it[0] = it; if (fail) d.w_fail[0] = 1; d.counters[4] = it; }
 }
 
 // ------------------------------------------------------------------------- K5: back-substitution

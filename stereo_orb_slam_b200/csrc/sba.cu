@@ -61,6 +61,8 @@ struct sba_handle_s {
   // single-launch PCG (k_pcg_window): usable when every window's system fits one CTA
   bool pcg_window_ok = false; int pcg_s_in_smem = 0; size_t pcg_smem = 0; int pcg_threads = 1024;
   int coop_blocks = 0;        // co-resident CTAs of k_step_loop (0: cooperative launch unavailable)
+  int coop_pcg_blocks = 0;    // idem for k_pcg_coop
+  double* pcg_pbuf = nullptr; double* pcg_rowdot = nullptr;
   bool pcg_cluster_ok = false; size_t pcg_cluster_smem = 0; int pcg_rows_cap = 0, pcg_ent_cap = 0;   // one 8-CTA cluster per window (k_pcg_cluster)
   size_t lin_smem = 0, schur_smem = 0;   // dynamic shared memory of the per-chunk kernels (largest chunk)
 
@@ -92,7 +94,7 @@ struct sba_handle_s {
   void free_all() {
     for (void* p : allocs) cudaFreeAsync(p, stream);
     allocs.clear();
-    uv_in = nullptr; r_dbg = nullptr; flush = nullptr;
+    uv_in = nullptr; r_dbg = nullptr; pcg_pbuf = nullptr; pcg_rowdot = nullptr; flush = nullptr;
     d = Dev{};
   }
 };
@@ -144,6 +146,8 @@ int sba_create(int device, sba_handle* out) {
       cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
       if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_step_loop, kThreads, 0) == cudaSuccess)
         h->coop_blocks = per_sm * sms;
+      if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_coop, kThreads, 0) == cudaSuccess)
+        h->coop_pcg_blocks = per_sm * sms;
     }
     if (e == cudaSuccess) {      // keep freed blocks in the device's default pool (no trim at synchronisation points)
       cudaMemPool_t pool = nullptr;
@@ -228,7 +232,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   AL(d.sc2c, nc * 6) AL(d.sc2p, np * 3) AL(d.lin_part, (size_t)d.npchunk * 2)
   AL(d.spart, (size_t)d.nlb * 36) AL(d.Su, (size_t)d.nbu * 36) AL(d.rpart, (size_t)d.ncs * 6)
   AL(d.rhs, nf * 6) AL(d.rsum, nf * 6) AL(d.Minv, nf * 36)
-  AL(d.x, nf * 6) AL(d.r, nf * 6) AL(d.z, nf * 6) AL(d.p, nf * 6) AL(d.Ap, nf * 6)
+  AL(d.x, nf * 6) AL(d.r, nf * 6) AL(d.z, nf * 6) AL(d.p, nf * 6) AL(d.Ap, nf * 6) AL(h->pcg_pbuf, nf * 6) AL(h->pcg_rowdot, nf)
   AL(d.dp, np * 3) AL(d.step_part, (size_t)d.npchunk * 4) AL(d.ls_part, (size_t)d.npchunk * 3)
   AL(d.w_radius, nw) AL(d.w_decf, nw) AL(d.w_cost, nw) AL(d.w_gmax, nw)
   AL(d.w_gd, nw * 4)   // one block: a multi-GPU solve all-reduces the four step scalars in one call
@@ -444,7 +448,8 @@ static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
   Dev& d = h->d;
   const DevParams& P = h->P;
   int it = 0;
-  if (d.Nf > 0 && h->pcg_cluster_ok) {
+  const bool force_coop = std::getenv("SBA_FORCE_COOP_PCG") != nullptr && d.nwin == 1 && h->coop_pcg_blocks > 0;
+  if (d.Nf > 0 && h->pcg_cluster_ok && !force_coop) {
     CUDA_TRY(cudaMemsetAsync(d.counters + 4, 0, 4, h->stream));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)d.nwin * kPcgCluster); cfg.blockDim = dim3(kPcgClThreads);
@@ -456,10 +461,18 @@ static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
     CUDA_TRY(cudaLaunchKernelEx(&cfg, k_pcg_cluster, d, P, (int)opt->max_pcg_iterations, h->pcg_rows_cap, h->pcg_ent_cap));
     h->launches++;
     it = -1;
-  } else if (d.Nf > 0 && h->pcg_window_ok) {
+  } else if (d.Nf > 0 && h->pcg_window_ok && !force_coop) {
     // one launch, no host round trip; the iteration count comes back with the LM counters (counters[4])
     CUDA_TRY(cudaMemsetAsync(d.counters + 4, 0, 4, h->stream));
     k_pcg_window<<<d.nwin, h->pcg_threads, h->pcg_smem, h->stream>>>(d, P, opt->max_pcg_iterations, h->pcg_s_in_smem);
+    h->launches++;
+    it = -1;
+  } else if (d.Nf > 0 && d.nwin == 1 && h->coop_pcg_blocks > 0 && !std::getenv("SBA_FORCE_MULTILAUNCH")) {
+    // one big window: cooperative single-launch PCG over the block-CSR in global memory
+    const int grid = std::max(1, std::min(h->coop_pcg_blocks, cdiv((int64_t)d.Nf * 32, kThreads)));
+    Dev dd = d; DevParams pp = P; int mi = opt->max_pcg_iterations; double* pb = h->pcg_pbuf; double* rd = h->pcg_rowdot;
+    void* args[] = {&dd, &pp, &mi, &pb, &rd};
+    CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_pcg_coop, dim3(grid), dim3(kThreads), args, 0, h->stream));
     h->launches++;
     it = -1;
   } else if (d.Nf > 0) {

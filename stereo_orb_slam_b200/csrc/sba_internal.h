@@ -8,7 +8,7 @@ namespace sba {
 
 constexpr int kThreads = 128;        // CTA size of the thread-per-point kernels
 constexpr int kPointChunk = 128;     // max points per chunk
-constexpr int kObsChunk = 256;       // max observations per chunk (= CTA size of the thread-per-observation kernels;
+constexpr int kObsChunk = 240;       // max observations per chunk (= CTA size of the thread-per-observation kernels;
                                      // chunk-local observation indices fit a byte)
 constexpr int kMaxSlots = 255;       // distinct cameras per chunk (slot index is a byte)
 

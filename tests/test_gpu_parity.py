@@ -97,16 +97,19 @@ def test_pcg_solves_the_reduced_system(small_window):
     assert np.abs(x - xs).max() <= 1e-8 * np.abs(xs).max()
 
 
-@pytest.mark.parametrize("path", ["window", "cluster", "multilaunch"])
+@pytest.mark.parametrize("path", ["window", "cluster", "multilaunch", "cooperative"])
 def test_every_pcg_path_solves_the_same_system(small_window, path, monkeypatch):
-    """The reduced system goes through one of three PCG kernels depending on its size (one CTA per window, one
-    8-CTA cluster per window, or the multi-launch global path); force each on the same small window."""
-    for k in ("SBA_NO_CLUSTER", "SBA_FORCE_CLUSTER", "SBA_FORCE_MULTILAUNCH"):
+    """The reduced system goes through one of four PCG paths depending on its size (one CTA per window, one
+    8-CTA cluster per window, one cooperative launch over the global block-CSR, or the multi-launch path); force each
+    on the same small window."""
+    for k in ("SBA_NO_CLUSTER", "SBA_FORCE_CLUSTER", "SBA_FORCE_MULTILAUNCH", "SBA_FORCE_COOP_PCG"):
         monkeypatch.delenv(k, raising=False)
     if path == "cluster":
         monkeypatch.setenv("SBA_FORCE_CLUSTER", "1")
     elif path == "multilaunch":
         monkeypatch.setenv("SBA_FORCE_MULTILAUNCH", "1")
+    elif path == "cooperative":
+        monkeypatch.setenv("SBA_FORCE_COOP_PCG", "1")
     else:
         monkeypatch.setenv("SBA_NO_CLUSTER", "1")
     w = small_window

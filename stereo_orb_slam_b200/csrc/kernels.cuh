@@ -66,15 +66,6 @@ __device__ __forceinline__ void load_campre_Rt(const CamPre* base, int c, CamPre
   for (int i = 0; i < 3; ++i) out.t[i] = __ldcg(s + 18 + i);
 }
 
-// ------------------------------------------------------------------------------------------ K0
-__global__ void k_cam_precompute(int Nc, const double* __restrict__ poses, CamPre* __restrict__ out) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= Nc) return;
-  CamPre cp;
-  cam_precompute(poses + 6 * c, cp);
-  out[c] = cp;
-}
-
 // clamp points into the box (Ceres projects x onto the bounds at iteration 0; reference bounds:
 // src/bundle_adjuster.cpp:104-108)
 __global__ void k_project_points(int64_t n, double* __restrict__ pts, double lo, double hi) {
@@ -113,53 +104,6 @@ __device__ __forceinline__ void point_contrib(const CamPre& c, const double A[6]
   mulT33(G, AR, W);
 #pragma unroll
   for (int i = 0; i < 9; ++i) W[9 + i] = AR[i];
-}
-
-// Arrival at a static partial list: every lane has published its partial; returns true (warp-uniform) for the
-// warp that arrives last, which may then read everybody's partials (with .cg loads).  The counter is reset by
-// the caller once the sum is done, so it is zero again when the kernel ends.
-__device__ __forceinline__ bool arrive_last(int32_t* counter, int expected) {
-  __threadfence();
-  __syncwarp();
-  int last = 0;
-  if ((threadIdx.x & 31) == 0) last = (atomicAdd(counter, 1) + 1 == expected) ? 1 : 0;   // control-plane counter
-  last = __shfl_sync(0xffffffffu, last, 0);
-  if (last) __threadfence();
-  return last != 0;
-}
-
-// Sum of the contiguous partial rows [l0, l1) of one block / camera (E doubles each), spread over the warp so
-// that many loads are in flight: lane (pg, eg) = (lane / 4, lane % 4) adds elements [eg * EG, eg * EG + EG) of
-// rows pg, pg + 8, ... in order, four rows per batch with the loads issued before the adds, then the eight row
-// groups are folded with a fixed xor butterfly.  Every lane returns the totals of its element group (valid
-// where eg * EG + k < E).  Fixed order: bit-reproducible.
-template <int E, int EG>
-__device__ __forceinline__ void gather_partials(const double* part, int l0, int l1, int lane, double (&acc)[EG]) {
-  const int pg = lane >> 2, e0 = (lane & 3) * EG;
-#pragma unroll
-  for (int k = 0; k < EG; ++k) acc[k] = 0.0;
-  for (int j = l0 + pg; j < l1; j += 32) {
-    double v[4][EG];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const bool in = j + 8 * u < l1;
-      const double* row = part + (size_t)(in ? j + 8 * u : l0) * E + e0;
-#pragma unroll
-      for (int k = 0; k < EG; ++k) v[u][k] = (in && e0 + k < E) ? __ldcg(row + k) : 0.0;
-    }
-#pragma unroll
-    for (int u = 0; u < 4; ++u)
-#pragma unroll
-      for (int k = 0; k < EG; ++k) acc[k] += v[u][k];
-  }
-#pragma unroll
-  for (int k = 0; k < EG; ++k) {
-    double x = acc[k];
-    x += __shfl_xor_sync(0xffffffffu, x, 4);
-    x += __shfl_xor_sync(0xffffffffu, x, 8);
-    x += __shfl_xor_sync(0xffffffffu, x, 16);
-    acc[k] = x;
-  }
 }
 
 __global__ void __launch_bounds__(kLinThreads, 3) k_lin_chunk(Dev d, DevParams P, int dbg) {
@@ -519,7 +463,7 @@ __global__ void __launch_bounds__(kSchurThreads, 4) k_schur_chunk(Dev d, int max
 }
 
 // Sum of the contiguous partial rows [l0, l1) of one block / camera by a whole CTA of kAsmThreads: warp w takes
-// rows w*8 + pg, + 8*kAsmWarps, ... (gather_partials with a stride), so that even a camera seen by > 100 chunks
+// rows w*8 + pg, + 8*kAsmWarps, ..., so that even a camera seen by > 100 chunks
 // needs one or two batches of independent loads; the warps' totals are then added in warp order through shared
 // memory.  Thread e < E returns element e (all threads pass the barrier).  Fixed order: bit-reproducible.
 constexpr int kAsmThreads = 128;

@@ -224,9 +224,8 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   float4* uvp;
   AL(uvp, nobs) d.uv_p = uvp;
   AL(h->uv_in, (size_t)Nobs)
-  AL(d.cam_cnt, nc * 2) AL(d.blk_cnt, (size_t)d.nbu)
   AL(d.poses, nc * 6) AL(d.poses_new, nc * 6) AL(d.pts, np * 3) AL(d.pts_new, np * 3)
-  AL(d.campre, nc) AL(d.campre_new, nc)
+  AL(d.campre_new, nc)
   AL(d.W, nobs * 18) AL(d.V, np * 6) AL(d.gp, np * 3) AL(d.Vinv, np * 6) AL(d.tp, np * 3)
   AL(d.U, nc * 21) AL(d.gc, nc * 6) AL(d.cspart, (size_t)d.ncs * 27)
   AL(d.sc2c, nc * 6) AL(d.sc2p, np * 3) AL(d.lin_part, (size_t)d.npchunk * 2)
@@ -261,9 +260,6 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   CUDA_TRY(cudaMemsetAsync(d.gc, 0, std::max<size_t>(1, nc * 6) * 8, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.Su, 0, std::max<size_t>(1, (size_t)d.nbu * 36) * 8, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.rsum, 0, std::max<size_t>(1, nf * 6) * 8, h->stream));
-  CUDA_TRY(cudaMemsetAsync(d.cam_cnt, 0, std::max<size_t>(1, nc * 2) * 4, h->stream));
-  CUDA_TRY(cudaMemsetAsync(d.blk_cnt, 0, std::max<size_t>(1, (size_t)d.nbu) * 4, h->stream));
-  d.multi_gpu = h->comm.active() ? 1 : 0;
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   {
     h->lin_smem = lin_smem_bytes(H.max_chunk_obs, H.max_chunk_pts, H.max_slots);
@@ -395,10 +391,6 @@ int sba_get_state(sba_handle h, double* poses, double* points) {
 static int do_linearize(sba_handle h, bool keep_cost = false) {
   Dev& d = h->d;
   const DevParams& P = h->P;
-  if (h->comm.active()) {      // ranks without a local contribution to a camera must add zero, not last iteration's sum
-    CUDA_TRY(cudaMemsetAsync(d.U, 0, (size_t)d.Nc * 21 * 8, h->stream));
-    CUDA_TRY(cudaMemsetAsync(d.gc, 0, (size_t)d.Nc * 6 * 8, h->stream));
-  }
   if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; }
   LAUNCH(h, k_assemble_cams, d.Nf, kAsmThreads, d);
   if (h->comm.active()) {
@@ -423,10 +415,6 @@ static int do_linearize(sba_handle h, bool keep_cost = false) {
 // K3: damped Schur complement at the per-window radii in d.w_radius.
 static int do_schur(sba_handle h) {
   Dev& d = h->d;
-  if (h->comm.active()) {
-    CUDA_TRY(cudaMemsetAsync(d.Su, 0, (size_t)d.nbu * 36 * 8, h->stream));
-    CUDA_TRY(cudaMemsetAsync(d.rsum, 0, (size_t)d.Nf * 6 * 8, h->stream));
-  }
   if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++; }
   const int fused = h->comm.active() ? 0 : 1;     // multi-GPU: the partial sums are all-reduced before the cameras are prepared
   LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, fused);

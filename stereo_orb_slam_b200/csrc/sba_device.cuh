@@ -32,7 +32,7 @@ struct Dev {
   // ---- state
   double *poses, *poses_new;     // [Nc*6]
   double *pts, *pts_new;         // [Np*3]
-  CamPre *campre, *campre_new;   // [Nc]
+  CamPre *campre_new;            // [Nc] trial cameras of the line search (the linearisation computes its own per chunk)
   // ---- linearisation
   double *W;                     // [Nobs*18] point order
   double *V, *gp;                // [Np*6], [Np*3]
@@ -42,8 +42,6 @@ struct Dev {
   double *sc2c, *sc2p;           // Jacobi scale^2 [Nc*6], [Np*3]
   double *lin_part;              // [npchunk*2] cost, gmax
   double *r_dbg;                 // [Nobs*4] or null
-  int32_t *cam_cnt, *blk_cnt;    // [2*Nc], [nbu] arrival counters of the in-kernel assembly (zero between launches)
-  int32_t multi_gpu;             // 1: point-sharded run (camera-side sums are zeroed before and all-reduced after the chunk kernels)
   // ---- Schur
   double *spart;                 // [nlb*36] per local-block partial of sum W Vinv W^T
   double *Su;                    // [nbu*36]

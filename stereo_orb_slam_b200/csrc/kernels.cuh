@@ -1378,14 +1378,14 @@ __global__ void __launch_bounds__(kThreads) k_ls_reduce(Dev d, int rank) { dev_l
 // options from the reference: src/bundle_adjuster.cpp:14-36).  Thread per window.
 
 // after a linearisation: gradient-tolerance test; `first` also initialises the LM state
-__global__ void k_lm_begin(Dev d, DevParams P, double initial_radius, int first) {
+__global__ void k_lm_begin(Dev d, DevParams P, double initial_radius, int first, int clear_fail) {
   const int w = blockIdx.x * blockDim.x + threadIdx.x;
   if (w >= d.nwin) return;
   if (first) {
     d.w_radius[w] = initial_radius; d.w_decf[w] = 2.0; d.w_status[w] = 0; d.w_iter[w] = 0; d.w_succ[w] = 0;
     d.w_invalid[w] = 0; d.w_accept[w] = 0;
   }
-  d.w_fail[w] = 0;
+  if (clear_fail) d.w_fail[w] = 0;
   if (d.w_status[w] == 0) {
     if (!isfinite(d.w_cost[w])) d.w_status[w] = -2;                       // numerical failure
     else if (d.w_gmax[w] <= P.gtol) d.w_status[w] = 3;                    // gradient tolerance

@@ -43,6 +43,12 @@ struct sba_handle_s {
   int device = -1;            // -1: host-only handle (structure build / introspection only)
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[8] = {};
+  // The camera-side tail of a linearisation (k_assemble_cams, k_lin_finish, k_lm_begin: a few dozen small CTAs)
+  // runs on `side`, forked after k_lin_chunk, while the next k_schur_chunk fills the SMs on `stream`;
+  // join_tail() makes `stream` wait for it before the first consumer of U / gc / the window scalars.
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  bool tail_pending = false;
   HostStructure H;
   bool has_structure = false, has_state = false, has_meas = false, jacobi_done = false;
   int32_t shard_begin = -1, shard_end = -1;
@@ -140,6 +146,9 @@ int sba_create(int device, sba_handle* out) {
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
     if (e == cudaSuccess && !std::getenv("SBA_NO_COOP")) {
       int coop = 0, per_sm = 0, sms = 0;
       cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
@@ -171,11 +180,15 @@ void sba_destroy(sba_handle h) {
   if (!h) return;
   if (h->device >= 0) {
     cudaSetDevice(h->device);
+    if (h->side) cudaStreamSynchronize(h->side);
     h->comm.destroy();
     h->free_all();
     if (h->stream) cudaStreamSynchronize(h->stream);     // the frees above are stream-ordered
     for (int i = 0; i < 8; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     if (h->h_counters) cudaFreeHost(h->h_counters);
+    if (h->side) cudaStreamDestroy(h->side);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
     if (h->stream) cudaStreamDestroy(h->stream);
   }
   delete h;
@@ -388,10 +401,39 @@ int sba_get_state(sba_handle h, double* poses, double* points) {
   } while (0)
 
 // K0 + K1 + K2 at the current state (d.poses / d.pts).
-static int do_linearize(sba_handle h, bool keep_cost = false) {
+// `stream` waits for the forked tail of the last linearisation (no-op when none is pending)
+static int join_tail(sba_handle h) {
+  if (!h->tail_pending) return SBA_OK;
+  CUDA_TRY(cudaEventRecord(h->ev_join, h->side));
+  CUDA_TRY(cudaStreamWaitEvent(h->stream, h->ev_join, 0));
+  h->tail_pending = false;
+  return SBA_OK;
+}
+
+// `fork_tail`: single GPU, Jacobi scaling already fixed: the camera-side tail goes to the side stream and the caller
+// (the LM loop, the K1-K3 timing stage) joins after launching k_schur_chunk, which needs none of its results.
+// `lm_begin` >= 0 appends k_lm_begin(first = lm_begin) to the tail.
+static int do_linearize(sba_handle h, bool keep_cost = false, bool fork_tail = false, int lm_begin = -1,
+                        double initial_radius = 0.0) {
   Dev& d = h->d;
   const DevParams& P = h->P;
+  int rc = join_tail(h);
+  if (rc) return rc;
   if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; }
+  if (fork_tail && !h->comm.active() && h->jacobi_done && !std::getenv("SBA_NO_FORK")) {
+    CUDA_TRY(cudaEventRecord(h->ev_fork, h->stream));
+    CUDA_TRY(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+    if (d.Nf > 0) { k_assemble_cams<<<d.Nf, kAsmThreads, 0, h->side>>>(d); h->launches++; }
+    if (d.nwin > 0) { k_lin_finish<<<d.nwin, kThreads, 0, h->side>>>(d, P, keep_cost ? 1 : 0); h->launches++; }
+    if (lm_begin >= 0) {
+      // w_fail is cleared on `stream` (k_schur_chunk may set it concurrently with the tail)
+      CUDA_TRY(cudaMemsetAsync(d.w_fail, 0, (size_t)d.nwin * 4, h->stream));
+      k_lm_begin<<<cdiv(d.nwin, 128), 128, 0, h->side>>>(d, P, initial_radius, lm_begin, 0); h->launches++;
+    }
+    h->tail_pending = true;
+    CUDA_TRY(cudaGetLastError());
+    return SBA_OK;
+  }
   LAUNCH(h, k_assemble_cams, d.Nf, kAsmThreads, d);
   if (h->comm.active()) {
     std::string _err;
@@ -408,6 +450,7 @@ static int do_linearize(sba_handle h, bool keep_cost = false) {
     LAUNCH(h, k_jacobi_scale, cdiv((int64_t)d.Nc * 6 + (int64_t)d.Np * 3, 256), 256, d);
     h->jacobi_done = true;
   }
+  if (lm_begin >= 0) LAUNCH(h, k_lm_begin, cdiv(d.nwin, 128), 128, d, P, initial_radius, lm_begin, 1);
   CUDA_TRY(cudaGetLastError());
   return SBA_OK;
 }
@@ -416,6 +459,7 @@ static int do_linearize(sba_handle h, bool keep_cost = false) {
 static int do_schur(sba_handle h) {
   Dev& d = h->d;
   if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++; }
+  { const int jrc = join_tail(h); if (jrc) return jrc; }
   const int fused = h->comm.active() ? 0 : 1;     // multi-GPU: the partial sums are all-reduced before the cameras are prepared
   LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, fused);
   if (fused) { CUDA_TRY(cudaGetLastError()); return SBA_OK; }
@@ -657,7 +701,7 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
       case 2: if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++; } break;
       case 3: if ((rc = do_linearize(h))) return rc; break;
       case 4: if ((rc = do_schur(h))) return rc; break;
-      case 8: if ((rc = do_linearize(h))) return rc; if ((rc = do_schur(h))) return rc; break;
+      case 8: if ((rc = do_linearize(h, false, true))) return rc; if ((rc = do_schur(h))) return rc; break;
       case 5: LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P); break;
       case 9: LAUNCH(h, k_assemble_cams, d.Nf, kAsmThreads, d); break;
       case 10: LAUNCH(h, k_lin_finish, d.nwin, kThreads, d, P, 0); break;
@@ -709,8 +753,7 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
   LAUNCH(h, k_project_points, cdiv((int64_t)d.Np * 3, 256), 256, (int64_t)d.Np * 3, d.pts, P.lo, P.hi);
   h->jacobi_done = false;
   CUDA_TRY(cudaEventRecord(h->ev[4], h->stream));
-  if ((rc = do_linearize(h))) return rc;
-  LAUNCH(h, k_lm_begin, cdiv(d.nwin, 128), 128, d, P, o.initial_radius, 1);
+  if ((rc = do_linearize(h, false, false, 1, o.initial_radius))) return rc;
   CUDA_TRY(cudaEventRecord(h->ev[5], h->stream));
   S.linearizations = 1;
   std::vector<double> wcost((size_t)d.nwin);
@@ -730,6 +773,7 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
   int ls_rounds = 0;
   for (int iter = 0; running > 0 && iter < o.max_iterations; ++iter) {
     if (o.max_time_s > 0.0 && secs(t0) >= o.max_time_s) {
+      if ((rc = join_tail(h))) return rc;
       LAUNCH(h, k_lm_timeout, cdiv(d.nwin, 128), 128, d);
       break;
     }
@@ -753,8 +797,7 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
     const int accepted = h->h_counters[2];
     if (accepted > 0) {
       CUDA_TRY(cudaEventRecord(h->ev[4], h->stream));
-      if ((rc = do_linearize(h, true))) return rc;
-      LAUNCH(h, k_lm_begin, cdiv(d.nwin, 128), 128, d, P, o.initial_radius, 0);
+      if ((rc = do_linearize(h, true, true, 0, o.initial_radius))) return rc;
       CUDA_TRY(cudaEventRecord(h->ev[5], h->stream));
       lin_pending = true;
       S.linearizations++;
@@ -762,6 +805,7 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
       CUDA_TRY(cudaMemsetAsync(d.w_fail, 0, (size_t)d.nwin * 4, h->stream));
     }
     if (o.verbose) {
+      if ((rc = join_tail(h))) return rc;
       CUDA_TRY(cudaMemcpyAsync(wcost.data(), d.w_cost, 8, cudaMemcpyDeviceToHost, h->stream));
       CUDA_TRY(cudaStreamSynchronize(h->stream));
       double dbg[6] = {0, 0, 0, 0, 0, 0};
@@ -773,6 +817,7 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
     }
   }
   // windows still running here hit the iteration limit
+  if ((rc = join_tail(h))) return rc;
   std::vector<int32_t> st((size_t)d.nwin), its((size_t)d.nwin), succ((size_t)d.nwin);
   CUDA_TRY(cudaMemcpyAsync(st.data(), d.w_status, st.size() * 4, cudaMemcpyDeviceToHost, h->stream));
   CUDA_TRY(cudaMemcpyAsync(its.data(), d.w_iter, its.size() * 4, cudaMemcpyDeviceToHost, h->stream));

@@ -191,17 +191,36 @@ __global__ void __launch_bounds__(kLinThreads, 3) k_lin_chunk(Dev d, DevParams P
       gmax = fmax(gmax, fabs(x - clampd(x - acc[6 + k], P.lo, P.hi)));   // projected-gradient norm
     }
   }
-  // ---- per camera slot: U (21) + gc (6), one warp per slot over the slot's observations
+  // ---- per camera slot: U (21) + gc (6), one warp per slot over the slot's observations.  The point sums above
+  // keep the first warps busy, so the slots are dealt from the last warp down.
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int cs = cs0 + warp; cs < cs1 && !(dbg & 1); cs += kLinThreads / 32) {
+  constexpr int NW = kLinThreads / 32;
+  for (int cs = cs0 + (NW - 1 - warp); cs < cs1 && !(dbg & 1); cs += NW) {
     const int c = d.cs_cam[cs];
     if (d.fc[c] < 0) continue;        // a fixed camera is not an unknown (src/bundle_adjuster.cpp:113)
-    // lane e sums element e of the slot's observations in list order (no cross-lane reduction)
-    double mine = 0.0;
-    const int j1 = d.cs_obs_off[cs + 1];
-    if (lane < 27)
-      for (int j = d.cs_obs_off[cs]; j < j1; ++j) mine += cam_st[(size_t)__ldg(d.sobs + j) * kCamStride + lane];
-    if (lane < 27) d.cspart[(size_t)d.cs_pos[cs] * 27 + lane] = mine;
+    // lane e sums element e of the slot's observations in list order, even and odd list positions apart (two
+    // independent add chains, joined at the end: a fixed order); the observation indices come 32 at a time by one
+    // coalesced load and are handed round by shuffles, so nothing in the loop waits on global memory
+    double s0 = 0.0, s1 = 0.0;
+    const int j0 = d.cs_obs_off[cs], j1 = d.cs_obs_off[cs + 1];
+    const double* col = cam_st + (lane < 27 ? lane : 0);
+    for (int jb = j0; jb < j1; jb += 32) {
+      const int mine_o = (jb + lane < j1) ? (int)__ldg(d.sobs + jb + lane) : 0;
+      const int m = min(32, j1 - jb);
+      int t = 0;
+      for (; t + 3 < m; t += 4) {
+        const int o0 = __shfl_sync(0xffffffffu, mine_o, t), o1 = __shfl_sync(0xffffffffu, mine_o, t + 1);
+        const int o2 = __shfl_sync(0xffffffffu, mine_o, t + 2), o3 = __shfl_sync(0xffffffffu, mine_o, t + 3);
+        const double v0 = col[o0 * kCamStride], v1 = col[o1 * kCamStride], v2 = col[o2 * kCamStride], v3 = col[o3 * kCamStride];
+        s0 += v0; s1 += v1; s0 += v2; s1 += v3;
+      }
+      for (; t < m; ++t) {
+        const int o = __shfl_sync(0xffffffffu, mine_o, t);
+        const double v = col[o * kCamStride];
+        if (t & 1) s1 += v; else s0 += v;
+      }
+    }
+    if (lane < 27) d.cspart[(size_t)d.cs_pos[cs] * 27 + lane] = s0 + s1;
   }
   // ---- chunk cost and projected-gradient max
 #pragma unroll
@@ -527,7 +546,6 @@ __global__ void __launch_bounds__(kAsmThreads) k_assemble_cams(Dev d) {
 __global__ void __launch_bounds__(kAsmThreads) k_assemble_schur(Dev d, int prepare) {
   __shared__ double sm[kAsmWarps * 36];
   __shared__ double sM[36];
-  __shared__ double sr[6];
   if ((int)blockIdx.x < d.nbu) {
     const int b = blockIdx.x;
     if (prepare && d.blk_row[b] == d.blk_col[b]) return;     // diagonal blocks belong to the camera CTAs
@@ -537,19 +555,29 @@ __global__ void __launch_bounds__(kAsmThreads) k_assemble_schur(Dev d, int prepa
   }
   const int f = blockIdx.x - d.nbu;
   if (f >= d.Nf) return;
+  // every index and scalar the two gathers and the prepare step need is requested up front, so that their
+  // latencies overlap instead of chaining behind the barriers of cta_gather
   const int c = d.free2cam[f];
-  const double rs = cta_gather<6, 2>(d.rpart, d.cam_part_off[c], d.cam_part_off[c + 1], sm);
-  if (threadIdx.x < 6) { d.rsum[(size_t)f * 6 + threadIdx.x] = rs; sr[threadIdx.x] = rs; }
+  const int db = d.diag_blk[f], w = d.fcam_win[f];
+  const int r0 = d.cam_part_off[c], r1 = d.cam_part_off[c + 1];
+  int b0 = 0, b1 = 0;
+  double u = 0.0, damp = 0.0, gcv = 0.0;
+  const int ti = threadIdx.x / 6, tj = threadIdx.x - 6 * ti;
+  if (prepare) {
+    b0 = d.blk_part_off[db]; b1 = d.blk_part_off[db + 1];
+    if (threadIdx.x < 36) {
+      u = d.U[(size_t)c * 21 + ((ti <= tj) ? up6(ti, tj) : up6(tj, ti))];
+      if (ti == tj) damp = lm_damp(d.sc2c[(size_t)c * 6 + ti], u, d.w_radius[w]);
+    }
+    if (threadIdx.x < 6) gcv = d.gc[(size_t)c * 6 + threadIdx.x];
+  }
+  const double rs = cta_gather<6, 2>(d.rpart, r0, r1, sm);
+  if (threadIdx.x < 6) { d.rsum[(size_t)f * 6 + threadIdx.x] = rs; if (prepare) d.rhs[(size_t)f * 6 + threadIdx.x] = rs - gcv; }
   if (!prepare) return;
   __syncthreads();                                           // sm is reused
-  const int db = d.diag_blk[f];
-  const double tot = cta_gather<36, 9>(d.spart, d.blk_part_off[db], d.blk_part_off[db + 1], sm);
-  const int w = d.fcam_win[f];
+  const double tot = cta_gather<36, 9>(d.spart, b0, b1, sm);
   if (threadIdx.x < 36) {
-    const int i = threadIdx.x / 6, j = threadIdx.x - 6 * i;
-    const double u = d.U[(size_t)c * 21 + ((i <= j) ? up6(i, j) : up6(j, i))];
-    double v = -tot + u;
-    if (i == j) v += lm_damp(d.sc2c[(size_t)c * 6 + i], u, d.w_radius[w]);
+    const double v = -tot + u + damp;
     sM[threadIdx.x] = v;
     d.Su[(size_t)db * 36 + threadIdx.x] = v;
   }
@@ -566,8 +594,6 @@ __global__ void __launch_bounds__(kAsmThreads) k_assemble_schur(Dev d, int prepa
   }
 #pragma unroll
   for (int i = 0; i < 36; ++i) d.Minv[(size_t)f * 36 + i] = M[i];
-#pragma unroll
-  for (int i = 0; i < 6; ++i) d.rhs[(size_t)f * 6 + i] = sr[i] - d.gc[(size_t)c * 6 + i];
 }
 
 // thread per free camera: add U + D to the diagonal block, rhs = -gc + rsum, Minv = (S_ii)^-1

@@ -317,6 +317,14 @@ __device__ __forceinline__ void bulk_load(void* dst_smem, const void* src_global
                "l"(src_global), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
+// D = A B + D on the FP64 tensor cores: A 8x4 (lane holds A[lane/4][lane%4]), B 4x8 (lane holds B[lane%4][lane/4]),
+// D 8x8 (lane holds D[lane/4][2 (lane%4)], D[lane/4][2 (lane%4) + 1])
+__device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+               : "+d"(d0), "+d"(d1)
+               : "d"(a), "d"(b));
+}
+
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t done;
   do {
@@ -421,37 +429,38 @@ __global__ void __launch_bounds__(kSchurThreads, 4) k_schur_chunk(Dev d, int max
   if (dbg & 8) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int NW = kSchurThreads / 32;
-  // ---- local blocks: lane (ps, i) = (lane / 6, lane % 6) owns ROW i of the 6x6 partial for every fifth pair
+  // ---- local blocks: one warp per block, one FP64 tensor-core MMA (m8n8k4) per pair: D(8x8) += A(8x4) B(4x8)
+  // with A[i][k] = Z_a[i][k], B[k][j] = Z_b[j][k] (rows/cols 6-7 and k = 3 are zero padding), so lane
+  // (g, t) = (lane / 4, lane % 4) feeds element 3 g + t of BOTH rows and ends up holding S[g][2t], S[g][2t+1]:
+  // two 8-byte shared loads per pair and lane, no cross-lane reduction, partial rows written straight from the
+  // accumulator fragment.  Even and odd pairs go to two accumulators (independent MMA chains, fixed order).
   const int lb0 = d.lb_off[chunk], lb1 = d.lb_off[chunk + 1];
-  const int ps = lane / 6, ri = lane - 6 * ps;
+  const int g = lane >> 2, t = lane & 3;
+  const bool feeds = g < 6 && t < 3;
+  const double* Zl = Z + (feeds ? 3 * g + t : 0);
   for (int lb = lb0 + warp; lb < lb1; lb += NW) {
     const int q0 = d.lb_pair_off[lb] - pq0, q1 = d.lb_pair_off[lb + 1] - pq0;
-    double acc[6] = {0, 0, 0, 0, 0, 0};
-    if (lane < 30 && !(dbg & 1)) {
-      for (int q = q0 + ps; q < q1; q += 5) {
-        const unsigned pr = pair_at(q);
-        const double* A = Z + (pr & 255u) * kZStride + 3 * ri;
-        const double2* B = reinterpret_cast<const double2*>(Z + (pr >> 8) * kZStride);
-        const double a0 = A[0], a1 = A[1], a2 = A[2];
-        double bb[18];
-#pragma unroll
-        for (int k = 0; k < 9; ++k) { const double2 v = B[k]; bb[2 * k] = v.x; bb[2 * k + 1] = v.y; }
-#pragma unroll
-        for (int j = 0; j < 6; ++j) acc[j] += a0 * bb[3 * j] + a1 * bb[3 * j + 1] + a2 * bb[3 * j + 2];
+    double c0 = 0.0, c1 = 0.0, e0_ = 0.0, e1_ = 0.0;
+    if (!(dbg & 1)) {
+      int q = q0;
+      for (; q + 1 < q1; q += 2) {
+        const unsigned pa = pair_at(q), pb = pair_at(q + 1);
+        double a0 = 0.0, b0 = 0.0, a1 = 0.0, b1 = 0.0;
+        if (feeds) {
+          a0 = Zl[(pa & 255u) * kZStride]; b0 = Zl[(pa >> 8) * kZStride];
+          a1 = Zl[(pb & 255u) * kZStride]; b1 = Zl[(pb >> 8) * kZStride];
+        }
+        dmma884(c0, c1, a0, b0);
+        dmma884(e0_, e1_, a1, b1);
+      }
+      if (q < q1) {
+        const unsigned pa = pair_at(q);
+        double a0 = 0.0, b0 = 0.0;
+        if (feeds) { a0 = Zl[(pa & 255u) * kZStride]; b0 = Zl[(pa >> 8) * kZStride]; }
+        dmma884(c0, c1, a0, b0);
       }
     }
-    // rows of the five pair groups summed in lane order: lanes 0..5 end up with row ri of the partial
-#pragma unroll
-    for (int j = 0; j < 6; ++j) {
-      double t = acc[j];
-#pragma unroll
-      for (int g = 1; g < 5; ++g) t += __shfl_sync(0xffffffffu, acc[j], (lane + 6 * g) & 31);
-      acc[j] = t;
-    }
-    if (lane < 6) {
-      double2* o = reinterpret_cast<double2*>(d.spart + (size_t)d.lb_pos[lb] * 36 + 6 * lane);
-      o[0] = make_double2(acc[0], acc[1]); o[1] = make_double2(acc[2], acc[3]); o[2] = make_double2(acc[4], acc[5]);
-    }
+    if (feeds) *reinterpret_cast<double2*>(d.spart + (size_t)d.lb_pos[lb] * 36 + 6 * g + 2 * t) = make_double2(c0 + e0_, c1 + e1_);
   }
   // ---- right-hand side partials: sum over the slot's observations of W_e tp[point(e)] = Z_e u[point(e)]
   const int cs0 = d.slot_off[chunk], cs1 = d.slot_off[chunk + 1];

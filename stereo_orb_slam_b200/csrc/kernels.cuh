@@ -358,7 +358,6 @@ __global__ void __launch_bounds__(kSchurThreads, 4) k_schur_chunk(Dev d, int max
   const bool pairs_staged = npq <= kSchurPairCap && max_pairs <= kSchurPairCap;
   if (pairs_staged)
     for (int i = threadIdx.x; i < npq; i += kSchurThreads) prs[i] = __ldg(d.pairs + pq0 + i);
-  auto pair_at = [&](int q) -> unsigned { return pairs_staged ? (unsigned)prs[q] : (unsigned)__ldg(d.pairs + pq0 + q); };
   const double radius = d.w_radius[w];
   // the chunk's W tile (n x 144 B, contiguous in point order, 16-byte aligned) straight into Z by one bulk copy
   __shared__ __align__(8) uint64_t wbar;
@@ -441,24 +440,28 @@ __global__ void __launch_bounds__(kSchurThreads, 4) k_schur_chunk(Dev d, int max
   for (int lb = lb0 + warp; lb < lb1; lb += NW) {
     const int q0 = d.lb_pair_off[lb] - pq0, q1 = d.lb_pair_off[lb + 1] - pq0;
     double c0 = 0.0, c1 = 0.0, e0_ = 0.0, e1_ = 0.0;
-    if (!(dbg & 1)) {
+    auto mma_pair = [&](unsigned pr, double& x0, double& x1) {
+      double a = 0.0, b = 0.0;
+      if (feeds) { a = Zl[(pr & 255u) * kZStride]; b = Zl[(pr >> 8) * kZStride]; }
+      dmma884(x0, x1, a, b);
+    };
+    if (dbg & 1) {
+    } else if (pairs_staged) {
+      // staged list: an odd first entry alone, then two entries per 4-byte shared load (prs is 16-byte aligned)
       int q = q0;
+      if ((q & 1) && q < q1) { mma_pair(prs[q], e0_, e1_); ++q; }
+      const uint32_t* pp = reinterpret_cast<const uint32_t*>(prs);
       for (; q + 1 < q1; q += 2) {
-        const unsigned pa = pair_at(q), pb = pair_at(q + 1);
-        double a0 = 0.0, b0 = 0.0, a1 = 0.0, b1 = 0.0;
-        if (feeds) {
-          a0 = Zl[(pa & 255u) * kZStride]; b0 = Zl[(pa >> 8) * kZStride];
-          a1 = Zl[(pb & 255u) * kZStride]; b1 = Zl[(pb >> 8) * kZStride];
-        }
-        dmma884(c0, c1, a0, b0);
-        dmma884(e0_, e1_, a1, b1);
+        const uint32_t two = pp[q >> 1];
+        mma_pair(two & 0xffffu, c0, c1);
+        mma_pair(two >> 16, e0_, e1_);
       }
-      if (q < q1) {
-        const unsigned pa = pair_at(q);
-        double a0 = 0.0, b0 = 0.0;
-        if (feeds) { a0 = Zl[(pa & 255u) * kZStride]; b0 = Zl[(pa >> 8) * kZStride]; }
-        dmma884(c0, c1, a0, b0);
-      }
+      if (q < q1) mma_pair(prs[q], c0, c1);
+    } else {
+      const uint16_t* gp = d.pairs + pq0;
+      int q = q0;
+      for (; q + 1 < q1; q += 2) { mma_pair(__ldg(gp + q), c0, c1); mma_pair(__ldg(gp + q + 1), e0_, e1_); }
+      if (q < q1) mma_pair(__ldg(gp + q), c0, c1);
     }
     if (feeds) *reinterpret_cast<double2*>(d.spart + (size_t)d.lb_pos[lb] * 36 + 6 * g + 2 * t) = make_double2(c0 + e0_, c1 + e1_);
   }

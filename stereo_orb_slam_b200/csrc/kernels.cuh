@@ -111,9 +111,9 @@ __global__ void __launch_bounds__(kLinThreads, 3) k_lin_chunk(Dev d, DevParams P
   __shared__ double sm1[kLinThreads / 32];
   __shared__ double smx[kLinThreads / 32];
   const int chunk = blockIdx.x;
-  const int p0 = d.pchunk_begin[chunk], p1 = d.pchunk_end[chunk], np = p1 - p0;
-  const int e0 = d.pt_off[p0], n = d.pt_off[p1] - e0;
-  const int cs0 = d.slot_off[chunk], cs1 = d.slot_off[chunk + 1], ns = cs1 - cs0;
+  const int4 c0 = __ldg(d.cdesc + 4 * (size_t)chunk), c1 = __ldg(d.cdesc + 4 * (size_t)chunk + 1);   // one record, one round trip
+  const int p0 = c0.x, np = c0.y, e0 = c0.z, n = c0.w;
+  const int cs0 = c1.y, ns = c1.z, cs1 = cs0 + ns;
   double* cam_st = smem;                                   // [n * kCamStride]  A(6) h(3) G(9)
   double* pt_st = cam_st + (size_t)n * kCamStride;         // [n * 9]           V(6) gp(3)
   double* cpre = pt_st + (size_t)n * 9;                    // [ns * 21]         R Jl t of the chunk's cameras
@@ -346,33 +346,43 @@ __host__ __device__ __forceinline__ size_t schur_smem_bytes(int n, int np, int n
 __global__ void __launch_bounds__(kSchurThreads, 4) k_schur_chunk(Dev d, int max_pairs, int dbg) {
   extern __shared__ __align__(16) double smem[];
   const int chunk = blockIdx.x;
-  const int p0 = d.pchunk_begin[chunk], p1 = d.pchunk_end[chunk], np = p1 - p0;
-  const int e0 = d.pt_off[p0], n = d.pt_off[p1] - e0;
-  const int w = d.pchunk_win[chunk];
+  const int4 c0 = __ldg(d.cdesc + 4 * (size_t)chunk), c1 = __ldg(d.cdesc + 4 * (size_t)chunk + 1), c2 = __ldg(d.cdesc + 4 * (size_t)chunk + 2);
+  const int p0 = c0.x, np = c0.y, e0 = c0.z, n = c0.w;
+  const int w = c1.x, cs0 = c1.y, cs1 = c1.y + c1.z, lb0 = c1.w, lb1 = c1.w + c2.x;
+  const int pq0 = c2.y, npq = c2.z;
   double* Z = smem;                                     // [n * kZStride]
   double* Li = Z + (size_t)n * kZStride;                // [np * 6]  Linv: 00 10 11 20 21 22
   double* us = Li + (size_t)np * 6;                     // [np * 3]  u = Linv gp
   uint8_t* opl = reinterpret_cast<uint8_t*>(us + (size_t)np * 3);   // [n] chunk-local point of each observation
   uint16_t* prs = reinterpret_cast<uint16_t*>(opl + ((n + 15) & ~15));   // the chunk's pair lists, when they fit
-  const int pq0 = d.lb_pair_off[d.lb_off[chunk]], npq = d.lb_pair_off[d.lb_off[chunk + 1]] - pq0;
   const bool pairs_staged = npq <= kSchurPairCap && max_pairs <= kSchurPairCap;
-  if (pairs_staged)
-    for (int i = threadIdx.x; i < npq; i += kSchurThreads) prs[i] = __ldg(d.pairs + pq0 + i);
-  const double radius = d.w_radius[w];
-  // the chunk's W tile (n x 144 B, contiguous in point order, 16-byte aligned) straight into Z by one bulk copy
-  __shared__ __align__(8) uint64_t wbar;
-  if (threadIdx.x == 0) mbar_init(&wbar, 1);
-  __syncthreads();
-  if (threadIdx.x == 0 && n > 0) bulk_load(Z, d.W + (size_t)e0 * 18, (uint32_t)n * 144u, &wbar);
-  for (int i = threadIdx.x; i < n; i += kSchurThreads) opl[i] = (uint8_t)(__ldg(d.ppt + e0 + i) - p0);
-  for (int q = threadIdx.x; q < np; q += kSchurThreads) {
-    const int p = p0 + q;
-    double V[6];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int NW = kSchurThreads / 32;
+  // one point per thread (np <= kPointChunk <= kSchurThreads): its V, scaling and gradient are requested first ...
+  static_assert(kPointChunk <= kSchurThreads, "one point per thread");
+  const int q = threadIdx.x;
+  const bool has_pt = q < np && !(dbg & 16);
+  const int p = p0 + q;
+  double V[6] = {0, 0, 0, 0, 0, 0}, s2[3] = {1, 1, 1}, gv[3] = {0, 0, 0};
+  if (has_pt) {
 #pragma unroll
     for (int i = 0; i < 6; ++i) V[i] = d.V[(size_t)p * 6 + i];
-    const double a = V[0] + lm_damp(d.sc2p[(size_t)p * 3 + 0], V[0], radius);
-    const double dd = V[3] + lm_damp(d.sc2p[(size_t)p * 3 + 1], V[3], radius);
-    const double f = V[5] + lm_damp(d.sc2p[(size_t)p * 3 + 2], V[5], radius);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { s2[i] = d.sc2p[(size_t)p * 3 + i]; gv[i] = d.gp[(size_t)p * 3 + i]; }
+  }
+  const double radius = d.w_radius[w];
+  // ... then the chunk's W tile (n x 144 B, contiguous in point order, 16-byte aligned) straight into Z by one bulk
+  // copy: 34 KB per CTA, queued behind the small latency-critical loads above instead of in front of them.  The
+  // other threads meet the barrier only after the __syncthreads below.
+  __shared__ __align__(8) uint64_t wbar;
+  if (threadIdx.x == 0) {
+    mbar_init(&wbar, 1);
+    if (n > 0 && !(dbg & 32)) bulk_load(Z, d.W + (size_t)e0 * 18, (uint32_t)n * 144u, &wbar);
+  }
+  if (has_pt) {
+    const double a = V[0] + lm_damp(s2[0], V[0], radius);
+    const double dd = V[3] + lm_damp(s2[1], V[3], radius);
+    const double f = V[5] + lm_damp(s2[2], V[5], radius);
     const double b = V[1], c = V[2], e = V[4];
     // lower Cholesky factor and its inverse
     double i00 = 0, i10 = 0, i11 = 0, i20 = 0, i21 = 0, i22 = 0;
@@ -398,7 +408,7 @@ __global__ void __launch_bounds__(kSchurThreads, 4) k_schur_chunk(Dev d, int max
       }
     }
     if (!ok) { d.w_fail[w] = 1; i00 = i10 = i11 = i20 = i21 = i22 = 0.0; }   // benign race: every writer stores 1
-    const double g0 = d.gp[(size_t)p * 3], g1 = d.gp[(size_t)p * 3 + 1], g2 = d.gp[(size_t)p * 3 + 2];
+    const double g0 = gv[0], g1 = gv[1], g2 = gv[2];
     const double u0 = i00 * g0, u1 = i10 * g0 + i11 * g1, u2 = i20 * g0 + i21 * g1 + i22 * g2;
     double* vo = d.Vinv + (size_t)p * 6;
     vo[0] = i00 * i00 + i10 * i10 + i20 * i20; vo[1] = i10 * i11 + i20 * i21; vo[2] = i20 * i22;
@@ -409,10 +419,13 @@ __global__ void __launch_bounds__(kSchurThreads, 4) k_schur_chunk(Dev d, int max
     Li[q * 6] = i00; Li[q * 6 + 1] = i10; Li[q * 6 + 2] = i11; Li[q * 6 + 3] = i20; Li[q * 6 + 4] = i21; Li[q * 6 + 5] = i22;
     us[q * 3] = u0; us[q * 3 + 1] = u1; us[q * 3 + 2] = u2;
   }
+  if (pairs_staged)
+    for (int i = threadIdx.x; i < npq; i += kSchurThreads) prs[i] = __ldg(d.pairs + pq0 + i);
+  for (int i = threadIdx.x; i < n; i += kSchurThreads) opl[i] = (uint8_t)(__ldg(d.ppt + e0 + i) - p0);
   __syncthreads();
-  if (n > 0) mbar_wait(&wbar, 0);
+  if (n > 0 && !(dbg & 32)) mbar_wait(&wbar, 0);
   // ---- Z = W Linv^T, each observation's thread on its own row
-  for (int i = threadIdx.x; i < n; i += kSchurThreads) {
+  for (int i = threadIdx.x; i < n && !(dbg & 64); i += kSchurThreads) {
     const double* L = Li + (int)opl[i] * 6;
     const double i00 = L[0], i10 = L[1], i11 = L[2], i20 = L[3], i21 = L[4], i22 = L[5];
     double* z = Z + (size_t)i * kZStride;
@@ -426,14 +439,11 @@ __global__ void __launch_bounds__(kSchurThreads, 4) k_schur_chunk(Dev d, int max
   }
   __syncthreads();
   if (dbg & 8) return;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  constexpr int NW = kSchurThreads / 32;
   // ---- local blocks: one warp per block, one FP64 tensor-core MMA (m8n8k4) per pair: D(8x8) += A(8x4) B(4x8)
   // with A[i][k] = Z_a[i][k], B[k][j] = Z_b[j][k] (rows/cols 6-7 and k = 3 are zero padding), so lane
   // (g, t) = (lane / 4, lane % 4) feeds element 3 g + t of BOTH rows and ends up holding S[g][2t], S[g][2t+1]:
   // two 8-byte shared loads per pair and lane, no cross-lane reduction, partial rows written straight from the
   // accumulator fragment.  Even and odd pairs go to two accumulators (independent MMA chains, fixed order).
-  const int lb0 = d.lb_off[chunk], lb1 = d.lb_off[chunk + 1];
   const int g = lane >> 2, t = lane & 3;
   const bool feeds = g < 6 && t < 3;
   const double* Zl = Z + (feeds ? 3 * g + t : 0);
@@ -466,7 +476,6 @@ __global__ void __launch_bounds__(kSchurThreads, 4) k_schur_chunk(Dev d, int max
     if (feeds) *reinterpret_cast<double2*>(d.spart + (size_t)d.lb_pos[lb] * 36 + 6 * g + 2 * t) = make_double2(c0 + e0_, c1 + e1_);
   }
   // ---- right-hand side partials: sum over the slot's observations of W_e tp[point(e)] = Z_e u[point(e)]
-  const int cs0 = d.slot_off[chunk], cs1 = d.slot_off[chunk + 1];
   for (int cs = cs0 + warp; cs < cs1 && !(dbg & 4); cs += NW) {
     const int c = d.cs_cam[cs];
     const int f = d.fc[c];

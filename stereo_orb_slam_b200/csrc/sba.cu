@@ -228,6 +228,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   UP(fc) UP(free2cam) UP(cam_win) UP(fcam_win) UP(win_cam_off) UP(win_fc_off) UP(win_pchunk_off)
   UP(pt_off) UP(perm_p) UP(pcam) UP(ppt)
   UP(pchunk_begin) UP(pchunk_end) UP(pchunk_win)
+  { const int32_t* cd = nullptr; if ((rc = h->upload(&cd, H.cdesc))) return rc; d.cdesc = reinterpret_cast<const int4*>(cd); }   // cudaMalloc'ed: 256-byte aligned
   UP(slot_off) UP(cs_cam) UP(cs_obs_off) UP(lb_off) UP(lb_blk) UP(lb_pair_off) UP(pairs) UP(oslot) UP(lb_sa) UP(lb_sb) UP(sobs)
   UP(blk_row) UP(blk_col) UP(diag_blk) UP(blk_part_off) UP(blk_part) UP(cam_part_off) UP(cam_part)
   UP(row_ptr) UP(bsr_col) UP(bsr_blk) UP(lb_pos) UP(cs_pos)

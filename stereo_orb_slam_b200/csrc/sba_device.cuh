@@ -21,6 +21,7 @@ struct Dev {
   const int32_t *fc, *free2cam, *cam_win, *fcam_win, *win_cam_off, *win_fc_off, *win_pchunk_off;
   const int32_t *pt_off, *perm_p, *pcam, *ppt;
   const int32_t *pchunk_begin, *pchunk_end, *pchunk_win;
+  const int4* cdesc;            // [npchunk * 4]  chunk records (HostStructure::cdesc)
   const int32_t *slot_off, *cs_cam, *cs_obs_off, *lb_off, *lb_blk, *lb_pair_off;
   const uint8_t *oslot, *lb_sa, *lb_sb;
   const uint16_t *sobs, *pairs;

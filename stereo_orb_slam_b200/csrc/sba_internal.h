@@ -39,6 +39,9 @@ struct HostStructure {
   std::vector<int32_t> ppt;           // [Nobs]   point at position e
   // chunks (owned points only)
   std::vector<int32_t> pchunk_begin, pchunk_end, pchunk_win;   // point range and window of chunk c
+  // one 64-byte record per chunk, everything the per-chunk kernels need to start (one load instead of a chain):
+  // [0] p0 [1] np [2] e0 [3] n  [4] win [5] cs0 [6] ns [7] lb0  [8] nlb [9] pq0 [10] npq [11..15] 0
+  std::vector<int32_t> cdesc;                                   // [nchunk * 16]
   std::vector<int32_t> win_pchunk_off;                          // [nwin+1]
   // camera slots: chunk c owns slots cs in [slot_off[c], slot_off[c+1])
   std::vector<int32_t> slot_off;                                // [nchunk+1]

@@ -318,6 +318,18 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
                  H.lb_blk.size(), H.pairs.size(), cur_it, new_it, cur_warp_max, new_warp_max);
   }
   std::vector<ChunkTab>().swap(tab);
+  {
+    const int nch = (int)H.pchunk_begin.size();
+    H.cdesc.assign((size_t)nch * 16, 0);
+    for (int ch = 0; ch < nch; ++ch) {
+      int32_t* D = H.cdesc.data() + (size_t)ch * 16;
+      const int32_t p0 = H.pchunk_begin[ch], p1 = H.pchunk_end[ch];
+      D[0] = p0; D[1] = p1 - p0; D[2] = H.pt_off[p0]; D[3] = H.pt_off[p1] - H.pt_off[p0];
+      D[4] = H.pchunk_win[ch]; D[5] = H.slot_off[ch]; D[6] = H.slot_off[ch + 1] - H.slot_off[ch]; D[7] = H.lb_off[ch];
+      D[8] = H.lb_off[ch + 1] - H.lb_off[ch]; D[9] = H.lb_pair_off[H.lb_off[ch]];
+      D[10] = H.lb_pair_off[H.lb_off[ch + 1]] - H.lb_pair_off[H.lb_off[ch]];
+    }
+  }
 
   // ---- static partial lists (ascending => fixed summation order)
   const int32_t nlb = (int32_t)H.lb_blk.size(), ncs = (int32_t)H.cs_cam.size();

@@ -61,6 +61,8 @@ typedef struct sba_options {
   int32_t max_pcg_iterations;    /* 500   PCG on the reduced camera system (replaces CHOLMOD, :26-29) */
   double  pcg_tolerance;         /* 1e-10 relative preconditioned-residual tolerance */
   int32_t verbose;               /* 0     (reference prints progress + FullReport, :15,:118) */
+  int32_t linear_solver;         /* 0     reduced camera system: 0 auto (block Cholesky when every window has <= 64 free
+                                  *       cameras, the reference's exact factorisation, :26-29; else PCG), 1 PCG, 2 Cholesky */
 } sba_options;
 
 typedef struct sba_summary {

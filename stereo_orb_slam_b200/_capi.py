@@ -33,7 +33,7 @@ class Options(C.Structure):
         ("point_lower_bound", C.c_double), ("point_upper_bound", C.c_double),
         ("parameter_tolerance", C.c_double), ("function_tolerance", C.c_double),
         ("gradient_tolerance", C.c_double), ("residual_dim", C.c_int32), ("initial_radius", C.c_double),
-        ("max_pcg_iterations", C.c_int32), ("pcg_tolerance", C.c_double), ("verbose", C.c_int32),
+        ("max_pcg_iterations", C.c_int32), ("pcg_tolerance", C.c_double), ("verbose", C.c_int32), ("linear_solver", C.c_int32),
     ]
 
 

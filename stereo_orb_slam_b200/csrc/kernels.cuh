@@ -909,6 +909,377 @@ __global__ void __launch_bounds__(kPcgThreads, 1) k_pcg_window(Dev d, DevParams 
   if (threadIdx.x == 0) { d.w_pcg_it[w] = it; if (fail) d.w_fail[w] = 1; atomicMax(d.counters + 4, it); }   // control-plane counter
 }
 
+// ------------------------------------------------------------------ K4 (small windows): direct solve
+// The reference factors the reduced camera matrix exactly (Ceres SPARSE_SCHUR + CHOLMOD, src/bundle_adjuster.cpp:
+// 26-29).  For a local-BA window (<= kCholMaxCams free cameras, a dense-ish S of a few hundred unknowns) the same
+// is cheaper on the GPU than 100+ CG iterations: one CTA per window runs a right-looking BLOCK Cholesky (6x6
+// blocks) on the dense lower block-triangle of S, kept in an L2-resident workspace; the panel column of each step
+// and the inverses of the diagonal factors live in shared memory.  The right-hand side rides along as an extra
+// block row (forward substitution for free); the back substitution walks the rows of L upwards.  Everything is
+// done in a fixed order by one CTA: bit-reproducible.  Three CTA barriers per block column.
+constexpr int kCholThreads = 512;
+constexpr int kCholMaxCams = 64;
+
+__host__ __device__ __forceinline__ size_t chol_smem_bytes(int nf) { return ((size_t)nf * (36 + 36 + 6) + 36 + 16) * 8; }
+__host__ __device__ __forceinline__ int64_t chol_ws_elems(int nf) { return (int64_t)nf * (nf + 1) / 2 * 36; }
+
+// In: a = SPD 6x6 (row-major, lower triangle read).  Out: li = inverse of its lower Cholesky factor (row-major, lower).
+// 1/L_jj comes from rsqrt (one dependent step per column instead of sqrt + divide); L_jj = s * rsqrt(s).
+__device__ __forceinline__ bool chol6_inverse_factor(const double* a, double* li) {
+  double L[6][6], inv[6];
+  bool ok = true;
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    double s = a[6 * j + j];
+#pragma unroll
+    for (int t = 0; t < 6; ++t) if (t < j) s -= L[j][t] * L[j][t];
+    ok = ok && (s > 0.0) && isfinite(s);
+    inv[j] = rsqrt(ok ? s : 1.0);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) if (i > j) {
+      double v = a[6 * i + j];
+#pragma unroll
+      for (int t = 0; t < 6; ++t) if (t < j) v -= L[i][t] * L[j][t];
+      L[i][j] = v * inv[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      double v = 0.0;
+      if (i == j) v = inv[j];
+      else if (i > j) {
+        double acc = 0.0;
+#pragma unroll
+        for (int t = 0; t < 6; ++t) if (t >= j && t < i) acc += L[i][t] * li[6 * t + j];
+        v = -acc * inv[i];
+      }
+      li[6 * i + j] = v;
+    }
+  }
+  return ok;
+}
+
+__global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
+  extern __shared__ double smem[];
+  const int w = blockIdx.x;
+  const int f0 = d.win_fc_off[w], f1 = d.win_fc_off[w + 1];
+  const int nf = f1 - f0, n = 6 * nf;
+  if (threadIdx.x == 0) d.w_pcg_it[w] = 0;
+  if (nf <= 0) return;
+  if (d.w_status[w] != 0 || d.w_fail[w] != 0) return;     // uniform per CTA; leaves x untouched (unused)
+  const int tid = threadIdx.x;
+  double* P = smem;                         // [nf * 36] panel: L_ik of the current column k (rows i > k)
+  double* LI = P + (size_t)nf * 36;         // [nf * 36] inverse diagonal factors
+  double* y = LI + (size_t)nf * 36;         // [n]       right-hand side -> forward-substituted -> solution
+  double* akk = y + n;                      // [36]
+  double* xk = akk + 36;                    // [6]
+  __shared__ int bad;
+  double* A = d.chol_ws + d.chol_off[w];    // lower block (i, j), i >= j, at (i (i + 1) / 2 + j) * 36, row-major
+  const int nblk = nf * (nf + 1) / 2;
+  const int b0 = d.diag_blk[f0];
+  const int b1 = (f1 < d.Nf) ? d.diag_blk[f1] : d.nbu;
+  if (tid == 0) bad = 0;
+  for (int i = tid; i < nblk * 36; i += kCholThreads) A[i] = 0.0;
+  for (int i = tid; i < n; i += kCholThreads) y[i] = d.rhs[(size_t)f0 * 6 + i];
+  __syncthreads();
+  // upper block (r, c), r <= c, of S  ->  lower block (c, r) = its transpose
+  for (int i = tid; i < (b1 - b0) * 36; i += kCholThreads) {
+    const int b = b0 + i / 36, e = i % 36, er = e / 6, ec = e - 6 * er;
+    const int r = d.blk_row[b] - f0, c = d.blk_col[b] - f0;
+    A[(size_t)(c * (c + 1) / 2 + r) * 36 + 6 * ec + er] = d.Su[(size_t)b * 36 + e];
+  }
+  __syncthreads();
+  for (int k = 0; k < nf; ++k) {
+    const int m = nf - 1 - k;               // rows below the diagonal
+    // (a) diagonal block: factor, keep the inverse of the factor
+    if (tid < 36) akk[tid] = __ldcg(A + (size_t)(k * (k + 1) / 2 + k) * 36 + tid);
+    __syncthreads();
+    if (tid == 0) {
+      double li[36];
+      if (!chol6_inverse_factor(akk, li)) bad = 1;
+#pragma unroll
+      for (int i = 0; i < 36; ++i) LI[(size_t)k * 36 + i] = li[i];
+    }
+    __syncthreads();
+    // (b) panel L_ik = A_ik Linv^T for i > k (kept in shared memory and written back for the back substitution);
+    //     right-hand side block: y_k <- Linv y_k
+    const double* li = LI + (size_t)k * 36;
+    for (int idx = tid; idx < m * 36; idx += kCholThreads) {
+      const int i = k + 1 + idx / 36, e = idx % 36, r = e / 6, c = e - 6 * r;
+      double* blk = A + (size_t)(i * (i + 1) / 2 + k) * 36;
+      double acc = 0.0;
+#pragma unroll
+      for (int t = 0; t < 6; ++t) if (t <= c) acc += __ldcg(blk + 6 * r + t) * li[6 * c + t];
+      P[(size_t)i * 36 + e] = acc;
+    }
+    if (tid >= kCholThreads - 6) {
+      const int c = tid - (kCholThreads - 6);
+      double acc = 0.0;
+#pragma unroll
+      for (int t = 0; t < 6; ++t) if (t <= c) acc += li[6 * c + t] * y[6 * k + t];
+      xk[c] = acc;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < m * 36; idx += kCholThreads) {
+      const int i = k + 1 + idx / 36, e = idx % 36;
+      A[(size_t)(i * (i + 1) / 2 + k) * 36 + e] = P[(size_t)i * 36 + e];
+    }
+    if (tid < 6) y[6 * k + tid] = xk[tid];
+    // (c) trailing update A_ij -= L_ik L_jk^T (i >= j > k) and y_j -= L_jk y_k
+    //     one thread per (block, row): its row of L_ik in registers, L_jk streamed with 16-byte shared loads
+    const int nupd = m * (m + 1) / 2;
+    for (int idx = tid; idx < nupd * 6; idx += kCholThreads) {
+      const int bi = idx / 6, r = idx - 6 * bi;
+      int ii = (int)((sqrtf(8.f * (float)bi + 1.f) - 1.f) * 0.5f);
+      while ((ii + 1) * (ii + 2) / 2 <= bi) ++ii;
+      while (ii * (ii + 1) / 2 > bi) --ii;
+      const int jj = bi - ii * (ii + 1) / 2;
+      const int i = k + 1 + ii, j = k + 1 + jj;
+      const double2* Li = reinterpret_cast<const double2*>(P + (size_t)i * 36 + 6 * r);
+      const double2 l0 = Li[0], l1 = Li[1], l2 = Li[2];
+      const double2* Lj = reinterpret_cast<const double2*>(P + (size_t)j * 36);
+      double acc[6];
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
+        const double2 m0 = Lj[3 * c], m1 = Lj[3 * c + 1], m2 = Lj[3 * c + 2];
+        acc[c] = (l0.x * m0.x + l0.y * m0.y + l1.x * m1.x) + (l1.y * m1.y + l2.x * m2.x + l2.y * m2.y);
+      }
+      double2* dst = reinterpret_cast<double2*>(A + (size_t)(i * (i + 1) / 2 + j) * 36 + 6 * r);
+#pragma unroll
+      for (int h = 0; h < 3; ++h) {
+        double2 v = __ldcg(dst + h);
+        v.x -= acc[2 * h]; v.y -= acc[2 * h + 1];
+        __stcg(dst + h, v);
+      }
+    }
+    for (int idx = tid; idx < m * 6; idx += kCholThreads) {
+      const int j = k + 1 + idx / 6, r = idx % 6;
+      const double* Lj = P + (size_t)j * 36 + 6 * r;
+      double acc = 0.0;
+#pragma unroll
+      for (int t = 0; t < 6; ++t) acc += Lj[t] * xk[t];
+      y[6 * j + r] -= acc;
+    }
+    __syncthreads();
+  }
+  // back substitution L^T x = y, rows of L upwards: x_k = Linv_kk^T y_k, then y_j -= L_kj^T x_k for j < k
+  for (int k = nf - 1; k >= 0; --k) {
+    const double* li = LI + (size_t)k * 36;
+    if (tid < 6) {
+      double acc = 0.0;
+#pragma unroll
+      for (int t = 0; t < 6; ++t) if (t >= tid) acc += li[6 * t + tid] * y[6 * k + t];
+      xk[tid] = acc;
+    }
+    __syncthreads();
+    if (tid < 6) y[6 * k + tid] = xk[tid];
+    for (int idx = tid; idx < k * 6; idx += kCholThreads) {
+      const int j = idx / 6, c = idx - 6 * j;
+      const double* blk = A + (size_t)(k * (k + 1) / 2 + j) * 36;
+      double acc = 0.0;
+#pragma unroll
+      for (int r = 0; r < 6; ++r) acc += __ldcg(blk + 6 * r + c) * xk[r];
+      y[6 * j + c] -= acc;
+    }
+    __syncthreads();
+  }
+  const bool fail = bad != 0;
+  for (int i = tid; i < n; i += kCholThreads) {
+    const double v = y[i];
+    d.x[(size_t)f0 * 6 + i] = (fail || !isfinite(v)) ? 0.0 : v;
+    d.r[(size_t)f0 * 6 + i] = 0.0;                         // exact solve: no linear residual in the model change
+    if (!isfinite(v)) bad = 1;                             // benign race: every writer stores 1
+  }
+  __syncthreads();
+  if (tid == 0 && bad != 0) d.w_fail[w] = 1;
+}
+
+// The same factorisation for a mid-size window (a 50-keyframe sliding window: 294 unknowns, 1225 lower blocks =
+// 353 KB) on one thread-block CLUSTER of kCholCluster CTAs: block column j lives in the shared memory of CTA
+// j % kCholCluster, so every trailing update is a local shared-memory update.  Per block column k:
+//   owner        factors the diagonal block, forms the panel L_ik (i > k) and y_k in its `pan` buffer
+//   cluster barrier (ONE per column; `pan` is double-buffered, the owner rotates)
+//   every CTA    pulls the panel through distributed shared memory into its local copy and updates its own
+//                columns j > k (A_ij -= L_ik L_jk^T, y_j -= L_jk y_k)
+// Back substitution: the owner of column k holds all L_ik (i > k): x_k = Linv_kk^T (y_k - sum L_ik^T x_i), pushed
+// to every CTA's copy of x, one cluster barrier per column.  Fixed order throughout: bit-reproducible.
+constexpr int kCholCluster = 8;
+constexpr int kCholClThreads = 256;
+
+__host__ __device__ __forceinline__ int chol_cl_cols(int nf, int rank) { return (nf > rank) ? (nf - rank + kCholCluster - 1) / kCholCluster : 0; }
+// blocks of the first lj local columns of CTA `rank` (column j = rank + kCholCluster * l holds rows j..nf-1)
+__host__ __device__ __forceinline__ int chol_cl_coloff(int nf, int rank, int lj) {
+  return lj * (nf - rank) - kCholCluster * (lj * (lj - 1) / 2);
+}
+__host__ __device__ __forceinline__ size_t chol_cluster_smem_bytes(int nf) {
+  const int maxcols = chol_cl_cols(nf, 0);
+  const size_t blocks = (size_t)chol_cl_coloff(nf, 0, maxcols);
+  // own columns, pan[2] (panel + y_k), local panel copy (+ y_k), own inverse factors, own y, x, reduction scratch
+  return (blocks * 36 + 2 * ((size_t)nf * 36 + 8) + ((size_t)nf * 36 + 8) + (size_t)maxcols * 36 + (size_t)maxcols * 6 +
+          (size_t)nf * 6 + 64 + kCholClThreads) * 8;
+}
+
+__global__ void __launch_bounds__(kCholClThreads, 1) k_chol_cluster(Dev d) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  extern __shared__ double smem[];
+  constexpr int CL = kCholCluster, T = kCholClThreads;
+  const int rank = (int)cluster.block_rank();
+  const int w = blockIdx.x / CL;
+  const int f0 = d.win_fc_off[w], f1 = d.win_fc_off[w + 1];
+  const int nf = f1 - f0, n = 6 * nf;
+  if (rank == 0 && threadIdx.x == 0) d.w_pcg_it[w] = 0;
+  if (nf <= 0) return;                                      // uniform over the cluster
+  if (d.w_status[w] != 0 || d.w_fail[w] != 0) return;       // idem; leaves x untouched (unused)
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int my_cols = chol_cl_cols(nf, rank), maxcols = chol_cl_cols(nf, 0);
+  const int pstride = nf * 36 + 8;                          // panel rows (indexed by i) + y_k at [nf * 36 .. + 6)
+  double* Acol = smem;                                                       // own columns
+  double* pan = Acol + (size_t)chol_cl_coloff(nf, 0, maxcols) * 36;         // [2][pstride] written by the owner, pulled by all
+  double* lp = pan + 2 * (size_t)pstride;                                    // [pstride] local copy of the current panel
+  double* LIm = lp + pstride;                                                // [maxcols * 36] inverse diagonal factors (own columns)
+  double* ym = LIm + (size_t)maxcols * 36;                                   // [maxcols * 6]  right-hand side of the own columns
+  double* xall = ym + (size_t)maxcols * 6;                                   // [n]            solution, every CTA has all of it
+  double* red = xall + n;                                                    // [64 + T]
+  __shared__ int bad;
+  if (tid == 0) bad = 0;
+  const int myblocks = chol_cl_coloff(nf, rank, my_cols);
+  for (int i = tid; i < myblocks * 36; i += T) Acol[i] = 0.0;
+  for (int i = tid; i < my_cols * 6; i += T) { const int lj = i / 6; ym[i] = d.rhs[(size_t)(f0 + rank + CL * lj) * 6 + (i - 6 * lj)]; }
+  __syncthreads();
+  {
+    // upper block (r, c), r <= c, of S -> lower block (c, r) = its transpose, kept by the owner of column r
+    const int b0 = d.diag_blk[f0];
+    const int b1 = (f1 < d.Nf) ? d.diag_blk[f1] : d.nbu;
+    for (int i = tid; i < (b1 - b0) * 36; i += T) {
+      const int b = b0 + i / 36, e = i % 36, er = e / 6, ec = e - 6 * er;
+      const int r = d.blk_row[b] - f0, c = d.blk_col[b] - f0;
+      if (r % CL != rank) continue;
+      Acol[(size_t)(chol_cl_coloff(nf, rank, r / CL) + (c - r)) * 36 + 6 * ec + er] = d.Su[(size_t)b * 36 + e];
+    }
+  }
+  cluster.sync();          // every CTA of the cluster is running (and initialised) before anybody reads a peer's shared memory
+  for (int k = 0; k < nf; ++k) {
+    const int owner = k % CL, lk = k / CL, m = nf - 1 - k;
+    double* pb = pan + (size_t)(k & 1) * pstride;
+    if (rank == owner) {
+      double* colk = Acol + (size_t)chol_cl_coloff(nf, rank, lk) * 36;       // rows k..nf-1 of column k
+      if (tid == 0) {
+        double li[36];
+        if (!chol6_inverse_factor(colk, li)) bad = 1;
+#pragma unroll
+        for (int i = 0; i < 36; ++i) LIm[(size_t)lk * 36 + i] = li[i];
+      }
+      __syncthreads();
+      const double* li = LIm + (size_t)lk * 36;
+      for (int idx = tid; idx < m * 36; idx += T) {
+        const int ii = 1 + idx / 36, e = idx % 36, r = e / 6, c = e - 6 * r;
+        const double* blk = colk + (size_t)ii * 36 + 6 * r;
+        double acc = 0.0;
+#pragma unroll
+        for (int t = 0; t < 6; ++t) if (t <= c) acc += blk[t] * li[6 * c + t];
+        pb[(size_t)(k + ii) * 36 + e] = acc;
+      }
+      if (tid >= T - 6) {
+        const int c = tid - (T - 6);
+        double acc = 0.0;
+#pragma unroll
+        for (int t = 0; t < 6; ++t) if (t <= c) acc += li[6 * c + t] * ym[6 * lk + t];
+        pb[(size_t)nf * 36 + c] = acc;
+      }
+    }
+    cluster.sync();
+    // pull the panel (rows k+1..nf-1) and y_k from the owner
+    {
+      const double2* src = reinterpret_cast<const double2*>(cluster.map_shared_rank(pb, owner) + (size_t)(k + 1) * 36);
+      double2* dst = reinterpret_cast<double2*>(lp + (size_t)(k + 1) * 36);
+      for (int i = tid; i < m * 18; i += T) dst[i] = src[i];
+      if (tid < 6) lp[(size_t)nf * 36 + tid] = cluster.map_shared_rank(pb, owner)[(size_t)nf * 36 + tid];
+    }
+    __syncthreads();
+    if (rank == owner) {
+      // keep L_ik (for the back substitution) and y_k in the own column
+      double* colk = Acol + (size_t)chol_cl_coloff(nf, rank, lk) * 36;
+      for (int i = tid; i < m * 36; i += T) colk[36 + i] = lp[(size_t)(k + 1) * 36 + i];
+      if (tid < 6) ym[6 * lk + tid] = lp[(size_t)nf * 36 + tid];
+    }
+    // trailing update of the own columns j > k: one thread per (block, row)
+    const double* yk = lp + (size_t)nf * 36;
+    for (int lj = (k + 1 > rank) ? (k + 1 - rank + CL - 1) / CL : 0; lj < my_cols; ++lj) {
+      const int j = rank + CL * lj;
+      double* colj = Acol + (size_t)chol_cl_coloff(nf, rank, lj) * 36;
+      const double2* Lj = reinterpret_cast<const double2*>(lp + (size_t)j * 36);
+      for (int it = tid; it < (nf - j) * 6; it += T) {
+        const int ii = it / 6, r = it - 6 * ii;
+        const double2* Li = reinterpret_cast<const double2*>(lp + (size_t)(j + ii) * 36 + 6 * r);
+        const double2 l0 = Li[0], l1 = Li[1], l2 = Li[2];
+        double2* dst = reinterpret_cast<double2*>(colj + (size_t)ii * 36 + 6 * r);
+#pragma unroll
+        for (int h = 0; h < 3; ++h) {
+          const double2 a0 = Lj[6 * h], a1 = Lj[6 * h + 1], a2 = Lj[6 * h + 2];
+          const double2 b0 = Lj[6 * h + 3], b1 = Lj[6 * h + 4], b2 = Lj[6 * h + 5];
+          double2 v = dst[h];
+          v.x -= (l0.x * a0.x + l0.y * a0.y + l1.x * a1.x) + (l1.y * a1.y + l2.x * a2.x + l2.y * a2.y);
+          v.y -= (l0.x * b0.x + l0.y * b0.y + l1.x * b1.x) + (l1.y * b1.y + l2.x * b2.x + l2.y * b2.y);
+          dst[h] = v;
+        }
+      }
+      if (tid >= T - 6) {
+        const int r = tid - (T - 6);
+        const double* Lr = lp + (size_t)j * 36 + 6 * r;
+        double acc = 0.0;
+#pragma unroll
+        for (int t = 0; t < 6; ++t) acc += Lr[t] * yk[t];
+        ym[6 * lj + r] -= acc;
+      }
+    }
+    __syncthreads();
+  }
+  // back substitution, columns downwards
+  for (int k = nf - 1; k >= 0; --k) {
+    const int owner = k % CL, lk = k / CL, m = nf - 1 - k;
+    if (rank == owner) {
+      const double* colk = Acol + (size_t)chol_cl_coloff(nf, rank, lk) * 36;
+      // s[c] = sum over i > k, r of L_ik[r][c] x_i[r]: lane c of each group of 6 over the (i, r) pairs
+      double acc = 0.0;
+      const int c = tid % 6, g = tid / 6;                   // 42 groups of 6 threads (the last 4 threads idle)
+      if (g < 42)
+        for (int q = g; q < m * 6; q += 42) {
+          const int ii = 1 + q / 6, r = q % 6;
+          acc += colk[(size_t)ii * 36 + 6 * r + c] * xall[6 * (k + ii) + r];
+        }
+      if (g < 42) red[64 + tid] = acc;
+      __syncthreads();
+      if (tid < 6) {
+        double s_ = 0.0;
+        for (int gg = 0; gg < 42; ++gg) s_ += red[64 + 6 * gg + tid];
+        red[tid] = ym[6 * lk + tid] - s_;
+      }
+      __syncthreads();
+      if (tid < 6) {
+        const double* li = LIm + (size_t)lk * 36;
+        double v = 0.0;
+#pragma unroll
+        for (int t = 0; t < 6; ++t) if (t >= tid) v += li[6 * t + tid] * red[t];
+#pragma unroll
+        for (int rr = 0; rr < CL; ++rr) cluster.map_shared_rank(xall, rr)[6 * k + tid] = v;
+      }
+    }
+    cluster.sync();
+  }
+  if (bad != 0) d.w_fail[w] = 1;                             // benign race: every writer stores 1
+  if (rank == 0) {
+    for (int i = tid; i < n; i += T) {
+      const double v = xall[i];
+      d.x[(size_t)f0 * 6 + i] = isfinite(v) ? v : 0.0;
+      d.r[(size_t)f0 * 6 + i] = 0.0;                         // exact solve: no linear residual in the model change
+      if (!isfinite(v)) d.w_fail[w] = 1;
+    }
+  }
+}
+
 // The same solve for windows whose reduced system is too big for one SM's shared-memory bandwidth and issue
 // rate (a 50-keyframe sliding window: ~600 blocks of S re-read every iteration): one thread-block CLUSTER of
 // kPcgCluster CTAs per window.  Block-rows are dealt round-robin to the CTAs; S, Minv and the pattern are read

@@ -70,6 +70,8 @@ struct sba_handle_s {
   int coop_pcg_blocks = 0;    // idem for k_pcg_coop
   double* pcg_pbuf = nullptr; double* pcg_rowdot = nullptr;
   bool pcg_cluster_ok = false; size_t pcg_cluster_smem = 0; int pcg_rows_cap = 0, pcg_ent_cap = 0;   // one 8-CTA cluster per window (k_pcg_cluster)
+  bool chol_ok = false; size_t chol_smem = 0;   // one CTA per window factors S exactly (k_chol_window)
+  bool chol_cluster_ok = false; size_t chol_cluster_smem = 0;   // mid-size windows: one 8-CTA cluster per window (k_chol_cluster)
   size_t lin_smem = 0, schur_smem = 0;   // dynamic shared memory of the per-chunk kernels (largest chunk)
 
   template <typename T>
@@ -119,7 +121,7 @@ void sba_default_options(sba_options* o) {
   o->max_iterations = 50; o->max_time_s = 1.0; o->huber_delta = 1.0;
   o->point_lower_bound = -10000.0; o->point_upper_bound = 10000.0;
   o->parameter_tolerance = 1e-8; o->function_tolerance = 1e-16; o->gradient_tolerance = 1e-16;
-  o->residual_dim = 4; o->initial_radius = 1e4; o->max_pcg_iterations = 500; o->pcg_tolerance = 1e-12;
+  o->residual_dim = 4; o->initial_radius = 1e4; o->max_pcg_iterations = 500; o->pcg_tolerance = 1e-12; o->linear_solver = 0;
   o->verbose = 0;
 }
 
@@ -320,6 +322,31 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
     if (h->pcg_window_ok)
       CUDA_TRY(cudaFuncSetAttribute(k_pcg_window, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->pcg_smem));
   }
+  {
+    // direct solve: every window small enough for the dense lower block-triangle workspace
+    int nf_max = 0;
+    std::vector<int64_t> off((size_t)H.nwin, 0);
+    int64_t tot = 0;
+    for (int w = 0; w < H.nwin; ++w) {
+      const int nfw = H.win_fc_off[w + 1] - H.win_fc_off[w];
+      nf_max = std::max(nf_max, nfw);
+      off[w] = tot; tot += chol_ws_elems(nfw);
+    }
+    h->chol_ok = nf_max > 0 && nf_max <= kCholMaxCams && tot <= ((int64_t)1 << 31) && !std::getenv("SBA_NO_DIRECT");
+    d.chol_ws = nullptr; d.chol_off = nullptr;
+    if (h->chol_ok) {
+      if ((rc = h->upload(&d.chol_off, off))) return rc;
+      if ((rc = h->alloc(&d.chol_ws, (size_t)std::max<int64_t>(tot, 1)))) return rc;
+      h->chol_smem = chol_smem_bytes(nf_max);
+      CUDA_TRY(cudaFuncSetAttribute(k_chol_window, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->chol_smem, 1024)));
+      CUDA_TRY(cudaStreamSynchronize(h->stream));      // `off` is a local
+    }
+    h->chol_cluster_smem = chol_cluster_smem_bytes(std::max(nf_max, 1));
+    h->chol_cluster_ok = h->chol_ok && nf_max >= (std::getenv("SBA_FORCE_CLUSTER") ? 1 : 16) && H.nwin <= 64 &&
+                         h->chol_cluster_smem <= (size_t)200 * 1024 && !std::getenv("SBA_NO_CLUSTER");
+    if (h->chol_cluster_ok)
+      CUDA_TRY(cudaFuncSetAttribute(k_chol_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->chol_cluster_smem, 1024)));
+  }
   h->time_structure_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   if (std::getenv("SBA_TIMING"))
     std::fprintf(stderr, "[sba] structure: host build %.3f ms, device alloc + upload %.3f ms (%zu allocations)\n", 1e3 * t_host,
@@ -482,7 +509,24 @@ static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
   const DevParams& P = h->P;
   int it = 0;
   const bool force_coop = std::getenv("SBA_FORCE_COOP_PCG") != nullptr && d.nwin == 1 && h->coop_pcg_blocks > 0;
-  if (d.Nf > 0 && h->pcg_cluster_ok && !force_coop) {
+  if (opt->linear_solver == 2 && !h->chol_ok) { set_error("linear_solver = Cholesky needs windows of at most 64 free cameras"); return SBA_INVALID_ARGUMENT; }
+  if (d.Nf > 0 && h->chol_ok && opt->linear_solver != 1) {
+    CUDA_TRY(cudaMemsetAsync(d.counters + 4, 0, 4, h->stream));
+    if (h->chol_cluster_ok) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3((unsigned)d.nwin * kCholCluster); cfg.blockDim = dim3(kCholClThreads);
+      cfg.dynamicSmemBytes = h->chol_cluster_smem; cfg.stream = h->stream;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = kCholCluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      cfg.attrs = at; cfg.numAttrs = 1;
+      CUDA_TRY(cudaLaunchKernelEx(&cfg, k_chol_cluster, d));
+    } else {
+      k_chol_window<<<d.nwin, kCholThreads, h->chol_smem, h->stream>>>(d);
+    }
+    h->launches++;
+    it = -1;
+  } else if (d.Nf > 0 && h->pcg_cluster_ok && !force_coop) {
     CUDA_TRY(cudaMemsetAsync(d.counters + 4, 0, 4, h->stream));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)d.nwin * kPcgCluster); cfg.blockDim = dim3(kPcgClThreads);

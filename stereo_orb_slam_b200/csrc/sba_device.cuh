@@ -52,6 +52,9 @@ struct Dev {
   double *Minv;                  // [Nf*36]
   // ---- PCG vectors [Nf*6]
   double *x, *r, *z, *p, *Ap;
+  // ---- direct solve of small windows (k_chol_window): dense lower block-triangle of each window's S
+  double *chol_ws;               // [sum over windows of nf (nf + 1) / 2 * 36]
+  const int64_t *chol_off;       // [nwin] element offset of window w in chol_ws
   // ---- step
   double *dp;                    // [Np*3] point step (back-substitution)
   double *step_part;             // [npchunk*4]  g.dp, dp D dp, |x|^2, max|dp|

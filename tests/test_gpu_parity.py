@@ -90,39 +90,61 @@ def test_pcg_solves_the_reduced_system(small_window):
     w = small_window
     s = load(w)
     s.linearize(); s.schur(1e4)
-    it = s.pcg(default_options(pcg_tolerance=1e-12, max_pcg_iterations=500))
+    it = s.pcg(default_options(pcg_tolerance=1e-12, max_pcg_iterations=500, linear_solver=1))
     S, rhs, x = s.schur_dense()
     xs = np.linalg.solve(S, rhs)
     assert 0 < it <= 500
     assert np.abs(x - xs).max() <= 1e-8 * np.abs(xs).max()
 
 
-@pytest.mark.parametrize("path", ["window", "cluster", "multilaunch", "cooperative"])
-def test_every_pcg_path_solves_the_same_system(small_window, path, monkeypatch):
-    """The reduced system goes through one of four PCG paths depending on its size (one CTA per window, one
-    8-CTA cluster per window, one cooperative launch over the global block-CSR, or the multi-launch path); force each
-    on the same small window."""
-    for k in ("SBA_NO_CLUSTER", "SBA_FORCE_CLUSTER", "SBA_FORCE_MULTILAUNCH", "SBA_FORCE_COOP_PCG"):
+@pytest.mark.parametrize("path", ["cholesky", "cholesky_cluster", "window", "cluster", "multilaunch", "cooperative"])
+def test_every_linear_solver_path_solves_the_same_system(small_window, path, monkeypatch):
+    """The reduced system goes through the block Cholesky (windows of <= 64 free cameras, the default there: one CTA
+    per window, or one 8-CTA cluster per window from 16 cameras up) or one of four PCG
+    paths depending on its size (one CTA per window, one 8-CTA cluster per window, one cooperative launch over the
+    global block-CSR, or the multi-launch path); force each on the same small window."""
+    for k in ("SBA_NO_CLUSTER", "SBA_FORCE_CLUSTER", "SBA_FORCE_MULTILAUNCH", "SBA_FORCE_COOP_PCG", "SBA_NO_DIRECT"):
         monkeypatch.delenv(k, raising=False)
-    if path == "cluster":
+    if path in ("cluster", "cholesky_cluster"):
         monkeypatch.setenv("SBA_FORCE_CLUSTER", "1")
     elif path == "multilaunch":
         monkeypatch.setenv("SBA_FORCE_MULTILAUNCH", "1")
     elif path == "cooperative":
         monkeypatch.setenv("SBA_FORCE_COOP_PCG", "1")
-    else:
+    elif path == "window":
         monkeypatch.setenv("SBA_NO_CLUSTER", "1")
+    chol = path.startswith("cholesky")
+    solver = 2 if chol else 1
     w = small_window
     s = load(w)
     s.linearize(); s.schur(1e4)
-    it = s.pcg(default_options(pcg_tolerance=1e-12, max_pcg_iterations=500))
+    it = s.pcg(default_options(pcg_tolerance=1e-12, max_pcg_iterations=500, linear_solver=solver))
     S, rhs, x = s.schur_dense()
     xs = np.linalg.solve(S, rhs)
-    assert 0 < it <= 500
-    assert np.abs(x - xs).max() <= 1e-8 * np.abs(xs).max()
+    assert (it == 0) if chol else (0 < it <= 500)
+    assert np.abs(x - xs).max() <= (1e-11 if chol else 1e-8) * np.abs(xs).max()
     po, xo, so = oracle.solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"], options=oracle_opts())
-    poses, points, summ = Solver(0).solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"], options=PARITY)
+    opt = default_options(max_time_s=0.0, linear_solver=solver)
+    poses, points, summ = Solver(0).solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"], options=opt)
     check_solution(w, summ, poses, points, so, po, xo)
+
+
+def test_cholesky_of_a_batch_of_windows_equals_pcg(monkeypatch):
+    """Config-3 shape: several independent windows in one call, one CTA per window in k_chol_window."""
+    ws = [make_window(5 + i, 300 + 50 * i, 4, 40 + i) for i in range(4)]
+    cam_off = np.cumsum([0] + [x["poses"].shape[0] for x in ws]).astype(np.int32)
+    pt_off = np.cumsum([0] + [x["points"].shape[0] for x in ws]).astype(np.int32)
+    poses = np.concatenate([x["poses"] for x in ws]); points = np.concatenate([x["points"] for x in ws])
+    cam = np.concatenate([x["obs_cam"] + cam_off[i] for i, x in enumerate(ws)]).astype(np.int32)
+    pt = np.concatenate([x["obs_pt"] + pt_off[i] for i, x in enumerate(ws)]).astype(np.int32)
+    uv = np.concatenate([x["obs_uv"] for x in ws])
+    out = {}
+    for name, solver in (("chol", 2), ("pcg", 1)):
+        s = Solver(0).set_structure(poses.shape[0], points.shape[0], cam, pt, win_cam_off=cam_off, win_pt_off=pt_off)
+        s.set_state(poses, points); s.set_measurements(uv, ws[0]["p_l"], ws[0]["p_r"])
+        s.linearize(); s.schur(1e4); s.pcg(default_options(pcg_tolerance=1e-13, max_pcg_iterations=500, linear_solver=solver))
+        out[name] = s.schur_values()[2].copy()
+    assert np.abs(out["chol"] - out["pcg"]).max() <= 1e-8 * np.abs(out["pcg"]).max()
 
 
 def check_solution(w, summary, poses, points, so, po, xo):

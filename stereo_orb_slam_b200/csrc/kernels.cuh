@@ -1237,38 +1237,63 @@ __global__ void __launch_bounds__(kCholClThreads, 1) k_chol_cluster(Dev d) {
     }
     __syncthreads();
   }
-  // back substitution, columns downwards
-  for (int k = nf - 1; k >= 0; --k) {
-    const int owner = k % CL, lk = k / CL, m = nf - 1 - k;
-    if (rank == owner) {
-      const double* colk = Acol + (size_t)chol_cl_coloff(nf, rank, lk) * 36;
-      // s[c] = sum over i > k, r of L_ik[r][c] x_i[r]: lane c of each group of 6 over the (i, r) pairs
+  // Back substitution by CTA 0 alone, columns downwards: x_k = Linv_kk^T (y_k - sum over i > k of L_ik^T x_i).  Column
+  // k, its inverse factor and y_k are read straight out of their owner's shared memory; none of that depends on x,
+  // so the loads of column k - 1 are issued before the reduction of column k finishes (registers `nxt`): the
+  // critical path per column is two CTA barriers, no cluster barrier.
+  cluster.sync();                                            // all columns final
+  if (rank == 0) {
+    constexpr int G = 42, PER = (kCholMaxCams * 6 + G - 1) / G;   // 42 groups of 6 threads over the (i, r) pairs of a column
+    const int c = tid % 6, g = tid / 6;
+    double cur[PER], nxt[PER], li_c[6], li_n[6], y_c = 0.0, y_n = 0.0;
+    auto fetch = [&](int k, double* col, double* li, double& yv) {
+      const int owner = k % CL, lk = k / CL, m = nf - 1 - k;
+      const double* colk = cluster.map_shared_rank(Acol, owner) + (size_t)chol_cl_coloff(nf, owner, lk) * 36;
+#pragma unroll
+      for (int u = 0; u < PER; ++u) {
+        const int q = g + G * u;
+        col[u] = (g < G && q < m * 6) ? colk[(size_t)(1 + q / 6) * 36 + 6 * (q % 6) + c] : 0.0;
+      }
+      if (tid < 6) {
+        const double* lik = cluster.map_shared_rank(LIm, owner) + (size_t)lk * 36;
+#pragma unroll
+        for (int t = 0; t < 6; ++t) li[t] = lik[6 * t + tid];          // column tid of Linv = row tid of Linv^T
+        yv = cluster.map_shared_rank(ym, owner)[6 * lk + tid];
+      }
+    };
+    fetch(nf - 1, cur, li_c, y_c);
+    for (int k = nf - 1; k >= 0; --k) {
+      if (k > 0) fetch(k - 1, nxt, li_n, y_n);
+      const int m = nf - 1 - k;
       double acc = 0.0;
-      const int c = tid % 6, g = tid / 6;                   // 42 groups of 6 threads (the last 4 threads idle)
-      if (g < 42)
-        for (int q = g; q < m * 6; q += 42) {
-          const int ii = 1 + q / 6, r = q % 6;
-          acc += colk[(size_t)ii * 36 + 6 * r + c] * xall[6 * (k + ii) + r];
-        }
-      if (g < 42) red[64 + tid] = acc;
+#pragma unroll
+      for (int u = 0; u < PER; ++u) {
+        const int q = g + G * u;
+        if (g < G && q < m * 6) acc += cur[u] * xall[6 * (k + 1 + q / 6) + (q % 6)];
+      }
+      if (g < G) red[64 + tid] = acc;
       __syncthreads();
       if (tid < 6) {
         double s_ = 0.0;
-        for (int gg = 0; gg < 42; ++gg) s_ += red[64 + 6 * gg + tid];
-        red[tid] = ym[6 * lk + tid] - s_;
+        for (int gg = 0; gg < G; ++gg) s_ += red[64 + 6 * gg + tid];
+        red[tid] = y_c - s_;
       }
       __syncthreads();
       if (tid < 6) {
-        const double* li = LIm + (size_t)lk * 36;
         double v = 0.0;
 #pragma unroll
-        for (int t = 0; t < 6; ++t) if (t >= tid) v += li[6 * t + tid] * red[t];
-#pragma unroll
-        for (int rr = 0; rr < CL; ++rr) cluster.map_shared_rank(xall, rr)[6 * k + tid] = v;
+        for (int t = 0; t < 6; ++t) if (t >= tid) v += li_c[t] * red[t];
+        xall[6 * k + tid] = v;
       }
+      __syncthreads();
+#pragma unroll
+      for (int u = 0; u < PER; ++u) cur[u] = nxt[u];
+#pragma unroll
+      for (int t = 0; t < 6; ++t) li_c[t] = li_n[t];
+      y_c = y_n;
     }
-    cluster.sync();
   }
+  cluster.sync();                                            // peers keep their shared memory alive until CTA 0 is done
   if (bad != 0) d.w_fail[w] = 1;                             // benign race: every writer stores 1
   if (rank == 0) {
     for (int i = tid; i < n; i += T) {

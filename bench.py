@@ -29,7 +29,7 @@ METRIC = "BA observations/sec through residual+Jacobian+Hessian accumulation+Sch
 UNIT = "obs/s"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of the same
 # workload (profiles/, see the summary there); None for a kernel without a capture
-TRAFFIC = {"k_schur_chunk": 36270080, "k_lin_chunk": 5943040}   # profiles/r01_c_ncu_full_summary.txt (C2; W written by k_lin_chunk stays in L2)
+TRAFFIC = {"k_schur_chunk": 36198656, "k_lin_chunk": 6119168}   # profiles/r01_f_ncu_full_summary.txt (C2; W written by k_lin_chunk stays in L2)
 
 
 def make_workload(name, rank=0):

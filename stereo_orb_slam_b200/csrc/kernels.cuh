@@ -962,6 +962,7 @@ __device__ __forceinline__ bool chol6_inverse_factor(const double* a, double* li
 }
 
 __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
+  const int T = blockDim.x;                // 128 .. kCholThreads, sized to the window by the host
   extern __shared__ double smem[];
   const int w = blockIdx.x;
   const int f0 = d.win_fc_off[w], f1 = d.win_fc_off[w + 1];
@@ -981,11 +982,11 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
   const int b0 = d.diag_blk[f0];
   const int b1 = (f1 < d.Nf) ? d.diag_blk[f1] : d.nbu;
   if (tid == 0) bad = 0;
-  for (int i = tid; i < nblk * 36; i += kCholThreads) A[i] = 0.0;
-  for (int i = tid; i < n; i += kCholThreads) y[i] = d.rhs[(size_t)f0 * 6 + i];
+  for (int i = tid; i < nblk * 36; i += T) A[i] = 0.0;
+  for (int i = tid; i < n; i += T) y[i] = d.rhs[(size_t)f0 * 6 + i];
   __syncthreads();
   // upper block (r, c), r <= c, of S  ->  lower block (c, r) = its transpose
-  for (int i = tid; i < (b1 - b0) * 36; i += kCholThreads) {
+  for (int i = tid; i < (b1 - b0) * 36; i += T) {
     const int b = b0 + i / 36, e = i % 36, er = e / 6, ec = e - 6 * er;
     const int r = d.blk_row[b] - f0, c = d.blk_col[b] - f0;
     A[(size_t)(c * (c + 1) / 2 + r) * 36 + 6 * ec + er] = d.Su[(size_t)b * 36 + e];
@@ -1006,7 +1007,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
     // (b) panel L_ik = A_ik Linv^T for i > k (kept in shared memory and written back for the back substitution);
     //     right-hand side block: y_k <- Linv y_k
     const double* li = LI + (size_t)k * 36;
-    for (int idx = tid; idx < m * 36; idx += kCholThreads) {
+    for (int idx = tid; idx < m * 36; idx += T) {
       const int i = k + 1 + idx / 36, e = idx % 36, r = e / 6, c = e - 6 * r;
       double* blk = A + (size_t)(i * (i + 1) / 2 + k) * 36;
       double acc = 0.0;
@@ -1014,15 +1015,15 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
       for (int t = 0; t < 6; ++t) if (t <= c) acc += __ldcg(blk + 6 * r + t) * li[6 * c + t];
       P[(size_t)i * 36 + e] = acc;
     }
-    if (tid >= kCholThreads - 6) {
-      const int c = tid - (kCholThreads - 6);
+    if (tid >= T - 6) {
+      const int c = tid - (T - 6);
       double acc = 0.0;
 #pragma unroll
       for (int t = 0; t < 6; ++t) if (t <= c) acc += li[6 * c + t] * y[6 * k + t];
       xk[c] = acc;
     }
     __syncthreads();
-    for (int idx = tid; idx < m * 36; idx += kCholThreads) {
+    for (int idx = tid; idx < m * 36; idx += T) {
       const int i = k + 1 + idx / 36, e = idx % 36;
       A[(size_t)(i * (i + 1) / 2 + k) * 36 + e] = P[(size_t)i * 36 + e];
     }
@@ -1030,7 +1031,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
     // (c) trailing update A_ij -= L_ik L_jk^T (i >= j > k) and y_j -= L_jk y_k
     //     one thread per (block, row): its row of L_ik in registers, L_jk streamed with 16-byte shared loads
     const int nupd = m * (m + 1) / 2;
-    for (int idx = tid; idx < nupd * 6; idx += kCholThreads) {
+    for (int idx = tid; idx < nupd * 6; idx += T) {
       const int bi = idx / 6, r = idx - 6 * bi;
       int ii = (int)((sqrtf(8.f * (float)bi + 1.f) - 1.f) * 0.5f);
       while ((ii + 1) * (ii + 2) / 2 <= bi) ++ii;
@@ -1054,7 +1055,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
         __stcg(dst + h, v);
       }
     }
-    for (int idx = tid; idx < m * 6; idx += kCholThreads) {
+    for (int idx = tid; idx < m * 6; idx += T) {
       const int j = k + 1 + idx / 6, r = idx % 6;
       const double* Lj = P + (size_t)j * 36 + 6 * r;
       double acc = 0.0;
@@ -1075,7 +1076,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
     }
     __syncthreads();
     if (tid < 6) y[6 * k + tid] = xk[tid];
-    for (int idx = tid; idx < k * 6; idx += kCholThreads) {
+    for (int idx = tid; idx < k * 6; idx += T) {
       const int j = idx / 6, c = idx - 6 * j;
       const double* blk = A + (size_t)(k * (k + 1) / 2 + j) * 36;
       double acc = 0.0;
@@ -1086,7 +1087,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
     __syncthreads();
   }
   const bool fail = bad != 0;
-  for (int i = tid; i < n; i += kCholThreads) {
+  for (int i = tid; i < n; i += T) {
     const double v = y[i];
     d.x[(size_t)f0 * 6 + i] = (fail || !isfinite(v)) ? 0.0 : v;
     d.r[(size_t)f0 * 6 + i] = 0.0;                         // exact solve: no linear residual in the model change

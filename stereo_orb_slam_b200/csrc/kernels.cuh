@@ -1846,7 +1846,7 @@ __device__ __forceinline__ void dev_ls_control(const Dev& d, const DevParams& P,
   const double f = d.w_ls_red[w], g = d.w_ls_red[(size_t)d.nwin + w], step2 = d.w_ls_red[2 * (size_t)d.nwin + w];
   const double x = d.w_ls_x[w];
   const double cost0 = d.w_cost[w], gd = d.w_gd[w];
-  if (P.debug && w == 0) printf("[ls] it %d st %d x %.6e f-cost0 %.6e armijo_rhs %.6e g %.6e gd %.6e\n", d.w_iter[w] + 1, st, x, f - cost0, 1e-4 * gd * x, g, gd);
+  if (P.debug == 1 && w == 0) printf("[ls] it %d st %d x %.6e f-cost0 %.6e armijo_rhs %.6e g %.6e gd %.6e\n", d.w_iter[w] + 1, st, x, f - cost0, 1e-4 * gd * x, g, gd);
   if (st == 3) { d.w_cand[w] = f; d.w_step2[w] = step2; d.w_ls_state[w] = 4; return; }
   if (st == 1) {
     // an invalid trust-region step never reaches the line search (k_lm_control treats it)
@@ -1952,22 +1952,32 @@ __global__ void k_apply_cams(Dev d) { dev_apply_cam(d, blockIdx.x * blockDim.x +
 // is still searching, then accepted candidates become the state.  Replaces 5 launches, a memset and a host round
 // trip per line-search round.  The searching counter alternates between counters[3] and [5] so that resetting
 // one never races with reading the other; counters[6] returns the number of rounds.
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+
 __global__ void __launch_bounds__(kThreads) k_step_loop(Dev d, DevParams P) {
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
   const int nb = gridDim.x;
+  // P.debug == 2 (SBA_DEBUG_LS=2): block 0 prints the nanoseconds spent in each phase (tuning aid)
+  const bool prof = P.debug == 2 && blockIdx.x == 0 && threadIdx.x == 0;
+  unsigned long long t0 = prof ? gtimer() : 0, tp[6] = {0, 0, 0, 0, 0, 0};
+  auto lap = [&](int k) { if (prof) { const unsigned long long t = gtimer(); tp[k] += t - t0; t0 = t; } };
   for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) { dev_backsub(d, P, ch); __syncthreads(); }
   if (blockIdx.x == 0 && threadIdx.x == 0) { d.counters[0] = 0; d.counters[2] = 0; d.counters[3] = 0; d.counters[5] = 0; }
   grid.sync();
+  lap(0);
   for (int w = blockIdx.x; w < d.nwin; w += nb) { dev_cam_step(d, w, 0); __syncthreads(); }
   grid.sync();
+  lap(1);
   int round = 0;
   for (;;) {
     int32_t* cnt = d.counters + ((round & 1) ? 5 : 3);
     int32_t* other = d.counters + ((round & 1) ? 3 : 5);
     for (int c = blockIdx.x * kThreads + threadIdx.x; c < d.Nc; c += nb * kThreads) dev_trial_cam(d, c);
     grid.sync();
+    lap(2);
     for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) { dev_trial_points(d, P, ch); __syncthreads(); }
     grid.sync();
+    lap(3);
     if (blockIdx.x == 0 && threadIdx.x == 0) *other = 0;
     for (int w = blockIdx.x; w < d.nwin; w += nb) {
       dev_ls_reduce(d, w, 0);
@@ -1976,12 +1986,15 @@ __global__ void __launch_bounds__(kThreads) k_step_loop(Dev d, DevParams P) {
       __syncthreads();
     }
     grid.sync();
+    lap(4);
     ++round;
     if (__ldcg(cnt) <= 0 || round > 64) break;
   }
   for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) dev_apply_points(d, ch);
   for (int t = blockIdx.x * kThreads + threadIdx.x; t < d.Nc * 6; t += nb * kThreads) dev_apply_cam(d, t);
   if (blockIdx.x == 0 && threadIdx.x == 0) d.counters[6] = round;
+  lap(5);
+  if (prof) printf("[step] rounds %d  backsub %llu  cam_step %llu  trial_cam %llu  trial_points %llu  reduce+control %llu  apply %llu ns\n", round, tp[0], tp[1], tp[2], tp[3], tp[4], tp[5]);
 }
 
 // permute the caller's observations into the point-sorted view

@@ -363,7 +363,7 @@ static void fill_params(sba_handle h, const sba_options* o) {
   P.pcg_tol2 = o->pcg_tolerance * o->pcg_tolerance;
   P.rdim = (o->residual_dim == 3) ? 3 : 4;
   P.max_iterations = o->max_iterations;
-  P.debug = std::getenv("SBA_DEBUG_LS") ? 1 : 0;
+  P.debug = std::getenv("SBA_DEBUG_LS") ? std::max(1, std::atoi(std::getenv("SBA_DEBUG_LS"))) : 0;
 }
 
 static int check_ready(sba_handle h, bool need_state) {

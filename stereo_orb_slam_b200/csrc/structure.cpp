@@ -8,7 +8,6 @@
 // structurally non-zero iff some point is observed by both free cameras i and j.
 #include <cstdio>
 #include <cstdlib>
-#include <functional>
 #include <algorithm>
 #include <cstring>
 #ifdef _OPENMP
@@ -299,23 +298,6 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
       H.lb_off.push_back((int32_t)H.lb_sa.size());
     }
     while (w_next <= nwin) H.win_pchunk_off[w_next++] = (int32_t)H.pchunk_begin.size();
-  }
-  if (std::getenv("SBA_STRUCT_STATS")) {
-    const int nch = (int)H.pchunk_begin.size();
-    long cur_it = 0, new_it = 0, cur_warp_max = 0, new_warp_max = 0;
-    for (int ch = 0; ch < nch; ++ch) {
-      std::vector<int> c;
-      for (int l = H.lb_off[ch]; l < H.lb_off[ch + 1]; ++l) c.push_back(H.lb_pair_off[l + 1] - H.lb_pair_off[l]);
-      long w[8] = {0};
-      for (size_t i = 0; i < c.size(); ++i) { cur_it += (c[i] + 4) / 5; w[i % 8] += (c[i] + 4) / 5 + 3; }
-      cur_warp_max += *std::max_element(w, w + 8);
-      std::sort(c.begin(), c.end(), std::greater<int>());
-      long v[8] = {0};
-      for (size_t i = 0, b = 0; i < c.size(); i += 5, ++b) { new_it += c[i]; v[b % 8] += c[i] + 1; }
-      new_warp_max += *std::max_element(v, v + 8);
-    }
-    std::fprintf(stderr, "[sba] chunks %d lbs %zu pairs %zu  warp-iterations now %ld -> grouped %ld ; critical path now %ld -> %ld\n", nch,
-                 H.lb_blk.size(), H.pairs.size(), cur_it, new_it, cur_warp_max, new_warp_max);
   }
   std::vector<ChunkTab>().swap(tab);
   {

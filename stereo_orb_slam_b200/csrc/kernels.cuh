@@ -1106,6 +1106,8 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
 //                columns j > k (A_ij -= L_ik L_jk^T, y_j -= L_jk y_k)
 // Back substitution: the owner of column k holds all L_ik (i > k): x_k = Linv_kk^T (y_k - sum L_ik^T x_i), pushed
 // to every CTA's copy of x, one cluster barrier per column.  Fixed order throughout: bit-reproducible.
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+
 constexpr int kCholCluster = 8;
 constexpr int kCholClThreads = 256;
 
@@ -1118,11 +1120,11 @@ __host__ __device__ __forceinline__ size_t chol_cluster_smem_bytes(int nf) {
   const int maxcols = chol_cl_cols(nf, 0);
   const size_t blocks = (size_t)chol_cl_coloff(nf, 0, maxcols);
   // own columns, pan[2] (panel + y_k), local panel copy (+ y_k), own inverse factors, own y, x, reduction scratch
-  return (blocks * 36 + 2 * ((size_t)nf * 36 + 8) + ((size_t)nf * 36 + 8) + (size_t)maxcols * 36 + (size_t)maxcols * 6 +
+  return (blocks * 36 + 2 * ((size_t)nf * 36 + 8) + 2 * ((size_t)nf * 36 + 8) + (size_t)maxcols * 36 + (size_t)maxcols * 6 +
           (size_t)nf * 6 + 64 + kCholClThreads) * 8;
 }
 
-__global__ void __launch_bounds__(kCholClThreads, 1) k_chol_cluster(Dev d) {
+__global__ void __launch_bounds__(kCholClThreads, 1) k_chol_cluster(Dev d, int profile) {
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
   extern __shared__ double smem[];
@@ -1139,8 +1141,8 @@ __global__ void __launch_bounds__(kCholClThreads, 1) k_chol_cluster(Dev d) {
   const int pstride = nf * 36 + 8;                          // panel rows (indexed by i) + y_k at [nf * 36 .. + 6)
   double* Acol = smem;                                                       // own columns
   double* pan = Acol + (size_t)chol_cl_coloff(nf, 0, maxcols) * 36;         // [2][pstride] written by the owner, pulled by all
-  double* lp = pan + 2 * (size_t)pstride;                                    // [pstride] local copy of the current panel
-  double* LIm = lp + pstride;                                                // [maxcols * 36] inverse diagonal factors (own columns)
+  double* lpb = pan + 2 * (size_t)pstride;                                   // [2][pstride] local copies of the panels (k & 1)
+  double* LIm = lpb + 2 * (size_t)pstride;                                                // [maxcols * 36] inverse diagonal factors (own columns)
   double* ym = LIm + (size_t)maxcols * 36;                                   // [maxcols * 6]  right-hand side of the own columns
   double* xall = ym + (size_t)maxcols * 6;                                   // [n]            solution, every CTA has all of it
   double* red = xall + n;                                                    // [64 + T]
@@ -1162,81 +1164,118 @@ __global__ void __launch_bounds__(kCholClThreads, 1) k_chol_cluster(Dev d) {
     }
   }
   cluster.sync();          // every CTA of the cluster is running (and initialised) before anybody reads a peer's shared memory
+  // profile != 0 (SBA_DEBUG_LS=2): thread 0 of CTA 1 prints the nanoseconds per phase, summed over the columns (tuning aid)
+  const bool prof = profile != 0 && rank == 1 && tid == 0 && w == 0;
+  unsigned long long t0 = prof ? gtimer() : 0, tp[6] = {0, 0, 0, 0, 0, 0};
+  auto lap = [&](int i) { if (prof) { const unsigned long long t = gtimer(); tp[i] += t - t0; t0 = t; } };
+  // factor the diagonal block of the own column k and form its panel + y_k in pan[k & 1] (whole CTA, owner only)
+  auto factor_and_panel = [&](int k) {
+    const int lk = k / CL, m = nf - 1 - k;
+    double* pb = pan + (size_t)(k & 1) * pstride;
+    // the owner of column k + 1 is on the critical path: it gets the panel pushed into its local copy, the others pull
+    double* nx = (k + 1 < nf) ? cluster.map_shared_rank(lpb + (size_t)(k & 1) * pstride, (k + 1) % CL) : pb;
+    double* colk = Acol + (size_t)chol_cl_coloff(nf, rank, lk) * 36;       // rows k..nf-1 of column k
+    if (tid == 0) {
+      double li[36];
+      if (!chol6_inverse_factor(colk, li)) bad = 1;
+#pragma unroll
+      for (int i = 0; i < 36; ++i) LIm[(size_t)lk * 36 + i] = li[i];
+    }
+    __syncthreads();
+    const double* li = LIm + (size_t)lk * 36;
+    for (int idx = tid; idx < m * 36; idx += T) {
+      const int ii = 1 + idx / 36, e = idx % 36, r = e / 6, c = e - 6 * r;
+      const double* blk = colk + (size_t)ii * 36 + 6 * r;
+      double acc = 0.0;
+#pragma unroll
+      for (int t = 0; t < 6; ++t) if (t <= c) acc += blk[t] * li[6 * c + t];
+      pb[(size_t)(k + ii) * 36 + e] = acc;
+      nx[(size_t)(k + ii) * 36 + e] = acc;
+    }
+    if (tid >= T - 6) {
+      const int c = tid - (T - 6);
+      double acc = 0.0;
+#pragma unroll
+      for (int t = 0; t < 6; ++t) if (t <= c) acc += li[6 * c + t] * ym[6 * lk + t];
+      pb[(size_t)nf * 36 + c] = acc;
+      nx[(size_t)nf * 36 + c] = acc;
+    }
+  };
+  // A_ij -= L_ik L_jk^T (i >= j) and y_j -= L_jk y_k for the own local column lj, from the local panel copy:
+  // one thread per (block, row)
+  auto update_column = [&](int lj, const double* lp) {
+    const int j = rank + CL * lj;
+    const double* yk = lp + (size_t)nf * 36;
+    double* colj = Acol + (size_t)chol_cl_coloff(nf, rank, lj) * 36;
+    const double2* Lj = reinterpret_cast<const double2*>(lp + (size_t)j * 36);
+    for (int it = tid; it < (nf - j) * 6; it += T) {
+      const int ii = it / 6, r = it - 6 * ii;
+      const double2* Li = reinterpret_cast<const double2*>(lp + (size_t)(j + ii) * 36 + 6 * r);
+      const double2 l0 = Li[0], l1 = Li[1], l2 = Li[2];
+      double2* dst = reinterpret_cast<double2*>(colj + (size_t)ii * 36 + 6 * r);
+#pragma unroll
+      for (int h = 0; h < 3; ++h) {
+        const double2 a0 = Lj[6 * h], a1 = Lj[6 * h + 1], a2 = Lj[6 * h + 2];
+        const double2 b0 = Lj[6 * h + 3], b1 = Lj[6 * h + 4], b2 = Lj[6 * h + 5];
+        double2 v = dst[h];
+        v.x -= (l0.x * a0.x + l0.y * a0.y + l1.x * a1.x) + (l1.y * a1.y + l2.x * a2.x + l2.y * a2.y);
+        v.y -= (l0.x * b0.x + l0.y * b0.y + l1.x * b1.x) + (l1.y * b1.y + l2.x * b2.x + l2.y * b2.y);
+        dst[h] = v;
+      }
+    }
+    if (tid >= T - 6) {
+      const int r = tid - (T - 6);
+      const double* Lr = lp + (size_t)j * 36 + 6 * r;
+      double acc = 0.0;
+#pragma unroll
+      for (int t = 0; t < 6; ++t) acc += Lr[t] * yk[t];
+      ym[6 * lj + r] -= acc;
+    }
+  };
+  if (rank == 0) factor_and_panel(0);
+  lap(0);
+  cluster.sync();
+  lap(1);
   for (int k = 0; k < nf; ++k) {
     const int owner = k % CL, lk = k / CL, m = nf - 1 - k;
     double* pb = pan + (size_t)(k & 1) * pstride;
-    if (rank == owner) {
-      double* colk = Acol + (size_t)chol_cl_coloff(nf, rank, lk) * 36;       // rows k..nf-1 of column k
-      if (tid == 0) {
-        double li[36];
-        if (!chol6_inverse_factor(colk, li)) bad = 1;
-#pragma unroll
-        for (int i = 0; i < 36; ++i) LIm[(size_t)lk * 36 + i] = li[i];
-      }
-      __syncthreads();
-      const double* li = LIm + (size_t)lk * 36;
-      for (int idx = tid; idx < m * 36; idx += T) {
-        const int ii = 1 + idx / 36, e = idx % 36, r = e / 6, c = e - 6 * r;
-        const double* blk = colk + (size_t)ii * 36 + 6 * r;
-        double acc = 0.0;
-#pragma unroll
-        for (int t = 0; t < 6; ++t) if (t <= c) acc += blk[t] * li[6 * c + t];
-        pb[(size_t)(k + ii) * 36 + e] = acc;
-      }
-      if (tid >= T - 6) {
-        const int c = tid - (T - 6);
-        double acc = 0.0;
-#pragma unroll
-        for (int t = 0; t < 6; ++t) if (t <= c) acc += li[6 * c + t] * ym[6 * lk + t];
-        pb[(size_t)nf * 36 + c] = acc;
-      }
-    }
-    cluster.sync();
-    // pull the panel (rows k+1..nf-1) and y_k from the owner
-    {
+    double* lp = lpb + (size_t)(k & 1) * pstride;
+    const bool next_owner = (k + 1 < nf) && ((k + 1) % CL == rank);
+    // pull the panel (rows k+1..nf-1) and y_k from the owner (the next owner already has them)
+    if (!next_owner) {
       const double2* src = reinterpret_cast<const double2*>(cluster.map_shared_rank(pb, owner) + (size_t)(k + 1) * 36);
       double2* dst = reinterpret_cast<double2*>(lp + (size_t)(k + 1) * 36);
-      for (int i = tid; i < m * 18; i += T) dst[i] = src[i];
+      // all remote loads first (independent round trips through the cluster network), then the local stores
+      constexpr int NP = ((kCholMaxCams - 1) * 18 + T - 1) / T;
+      double2 v[NP];
+#pragma unroll
+      for (int u = 0; u < NP; ++u) { const int i = tid + u * T; if (i < m * 18) v[u] = src[i]; }
+#pragma unroll
+      for (int u = 0; u < NP; ++u) { const int i = tid + u * T; if (i < m * 18) dst[i] = v[u]; }
       if (tid < 6) lp[(size_t)nf * 36 + tid] = cluster.map_shared_rank(pb, owner)[(size_t)nf * 36 + tid];
     }
     __syncthreads();
+    lap(2);
+    // look-ahead: the owner of column k + 1 brings that column up to date first, factors it and forms the next
+    // panel while the other CTAs (and then itself) do the rest of the trailing update
+    const int first = (k + 1 > rank) ? (k + 1 - rank + CL - 1) / CL : 0;    // first own local column with j > k
+    if (next_owner) {
+      update_column(first, lp);           // rank + CL * first == k + 1
+      __syncthreads();
+      factor_and_panel(k + 1);
+    }
+    lap(0);
     if (rank == owner) {
       // keep L_ik (for the back substitution) and y_k in the own column
       double* colk = Acol + (size_t)chol_cl_coloff(nf, rank, lk) * 36;
       for (int i = tid; i < m * 36; i += T) colk[36 + i] = lp[(size_t)(k + 1) * 36 + i];
       if (tid < 6) ym[6 * lk + tid] = lp[(size_t)nf * 36 + tid];
     }
-    // trailing update of the own columns j > k: one thread per (block, row)
-    const double* yk = lp + (size_t)nf * 36;
-    for (int lj = (k + 1 > rank) ? (k + 1 - rank + CL - 1) / CL : 0; lj < my_cols; ++lj) {
-      const int j = rank + CL * lj;
-      double* colj = Acol + (size_t)chol_cl_coloff(nf, rank, lj) * 36;
-      const double2* Lj = reinterpret_cast<const double2*>(lp + (size_t)j * 36);
-      for (int it = tid; it < (nf - j) * 6; it += T) {
-        const int ii = it / 6, r = it - 6 * ii;
-        const double2* Li = reinterpret_cast<const double2*>(lp + (size_t)(j + ii) * 36 + 6 * r);
-        const double2 l0 = Li[0], l1 = Li[1], l2 = Li[2];
-        double2* dst = reinterpret_cast<double2*>(colj + (size_t)ii * 36 + 6 * r);
-#pragma unroll
-        for (int h = 0; h < 3; ++h) {
-          const double2 a0 = Lj[6 * h], a1 = Lj[6 * h + 1], a2 = Lj[6 * h + 2];
-          const double2 b0 = Lj[6 * h + 3], b1 = Lj[6 * h + 4], b2 = Lj[6 * h + 5];
-          double2 v = dst[h];
-          v.x -= (l0.x * a0.x + l0.y * a0.y + l1.x * a1.x) + (l1.y * a1.y + l2.x * a2.x + l2.y * a2.y);
-          v.y -= (l0.x * b0.x + l0.y * b0.y + l1.x * b1.x) + (l1.y * b1.y + l2.x * b2.x + l2.y * b2.y);
-          dst[h] = v;
-        }
-      }
-      if (tid >= T - 6) {
-        const int r = tid - (T - 6);
-        const double* Lr = lp + (size_t)j * 36 + 6 * r;
-        double acc = 0.0;
-#pragma unroll
-        for (int t = 0; t < 6; ++t) acc += Lr[t] * yk[t];
-        ym[6 * lj + r] -= acc;
-      }
-    }
+    for (int lj = first + (next_owner ? 1 : 0); lj < my_cols; ++lj) update_column(lj, lp);
     __syncthreads();
+    lap(3);
+    cluster.sync();                       // panel k + 1 is in its owner's pan; every CTA is done with lp
+    lap(1);
   }
   // Back substitution by CTA 0 alone, columns downwards: x_k = Linv_kk^T (y_k - sum over i > k of L_ik^T x_i).  Column
   // k, its inverse factor and y_k are read straight out of their owner's shared memory; none of that depends on x,
@@ -1295,6 +1334,8 @@ __global__ void __launch_bounds__(kCholClThreads, 1) k_chol_cluster(Dev d) {
     }
   }
   cluster.sync();                                            // peers keep their shared memory alive until CTA 0 is done
+  lap(4);
+  if (prof) printf("[chol] nf %d  own factor+panel %llu  barrier %llu  pull %llu  trailing %llu  back substitution (CTA 0) %llu ns\n", nf, tp[0], tp[1], tp[2], tp[3], tp[4]);
   if (bad != 0) d.w_fail[w] = 1;                             // benign race: every writer stores 1
   if (rank == 0) {
     for (int i = tid; i < n; i += T) {
@@ -1952,8 +1993,6 @@ __global__ void k_apply_cams(Dev d) { dev_apply_cam(d, blockIdx.x * blockDim.x +
 // is still searching, then accepted candidates become the state.  Replaces 5 launches, a memset and a host round
 // trip per line-search round.  The searching counter alternates between counters[3] and [5] so that resetting
 // one never races with reading the other; counters[6] returns the number of rounds.
-__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
-
 __global__ void __launch_bounds__(kThreads) k_step_loop(Dev d, DevParams P) {
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
   const int nb = gridDim.x;

@@ -344,7 +344,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
     }
     h->chol_cluster_smem = chol_cluster_smem_bytes(std::max(nf_max, 1));
     h->chol_cluster_ok = h->chol_ok && nf_max >= (std::getenv("SBA_FORCE_CLUSTER") ? 1 : 16) && H.nwin <= 64 &&
-                         h->chol_cluster_smem <= (size_t)200 * 1024 && !std::getenv("SBA_NO_CLUSTER");
+                         h->chol_cluster_smem <= (size_t)220 * 1024 && !std::getenv("SBA_NO_CLUSTER");
     if (h->chol_cluster_ok)
       CUDA_TRY(cudaFuncSetAttribute(k_chol_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->chol_cluster_smem, 1024)));
   }
@@ -521,7 +521,7 @@ static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
       at[0].id = cudaLaunchAttributeClusterDimension;
       at[0].val.clusterDim.x = kCholCluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
       cfg.attrs = at; cfg.numAttrs = 1;
-      CUDA_TRY(cudaLaunchKernelEx(&cfg, k_chol_cluster, d));
+      CUDA_TRY(cudaLaunchKernelEx(&cfg, k_chol_cluster, d, (int)(h->P.debug == 2)));
     } else {
       k_chol_window<<<d.nwin, h->chol_threads, h->chol_smem, h->stream>>>(d);
     }

@@ -920,7 +920,10 @@ __global__ void __launch_bounds__(kPcgThreads, 1) k_pcg_window(Dev d, DevParams 
 constexpr int kCholThreads = 512;
 constexpr int kCholMaxCams = 64;
 
-__host__ __device__ __forceinline__ size_t chol_smem_bytes(int nf) { return ((size_t)nf * (36 + 36 + 6) + 36 + 16) * 8; }
+constexpr int kCholSmemCams = 20;    // 210 lower blocks = 60 KB
+__host__ __device__ __forceinline__ size_t chol_smem_bytes(int nf) {
+  return ((size_t)nf * (36 + 36 + 6) + 36 + 16 + (nf <= kCholSmemCams ? (size_t)nf * (nf + 1) / 2 * 36 : 0)) * 8;
+}
 __host__ __device__ __forceinline__ int64_t chol_ws_elems(int nf) { return (int64_t)nf * (nf + 1) / 2 * 36; }
 
 // In: a = SPD 6x6 (row-major, lower triangle read).  Out: li = inverse of its lower Cholesky factor (row-major, lower).
@@ -961,6 +964,9 @@ __device__ __forceinline__ bool chol6_inverse_factor(const double* a, double* li
   return ok;
 }
 
+// WS_SMEM: the lower block-triangle itself sits in shared memory (windows of <= kCholSmemCams free cameras: no L2
+// round trip anywhere in the factorisation); otherwise in the L2-resident workspace.
+template <bool WS_SMEM>
 __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
   const int T = blockDim.x;                // 128 .. kCholThreads, sized to the window by the host
   extern __shared__ double smem[];
@@ -977,8 +983,11 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
   double* akk = y + n;                      // [36]
   double* xk = akk + 36;                    // [6]
   __shared__ int bad;
-  double* A = d.chol_ws + d.chol_off[w];    // lower block (i, j), i >= j, at (i (i + 1) / 2 + j) * 36, row-major
+  double* A = WS_SMEM ? (xk + 8) : (d.chol_ws + d.chol_off[w]);    // lower block (i, j), i >= j, at (i (i + 1) / 2 + j) * 36, row-major
   const int nblk = nf * (nf + 1) / 2;
+  auto ld = [](const double* p) { return WS_SMEM ? *p : __ldcg(p); };
+  auto ld2 = [](const double2* p) { return WS_SMEM ? *p : __ldcg(p); };
+  auto st2 = [](double2* p, double2 v) { if (WS_SMEM) *p = v; else __stcg(p, v); };
   const int b0 = d.diag_blk[f0];
   const int b1 = (f1 < d.Nf) ? d.diag_blk[f1] : d.nbu;
   if (tid == 0) bad = 0;
@@ -995,7 +1004,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
   for (int k = 0; k < nf; ++k) {
     const int m = nf - 1 - k;               // rows below the diagonal
     // (a) diagonal block: factor, keep the inverse of the factor
-    if (tid < 36) akk[tid] = __ldcg(A + (size_t)(k * (k + 1) / 2 + k) * 36 + tid);
+    if (tid < 36) akk[tid] = ld(A + (size_t)(k * (k + 1) / 2 + k) * 36 + tid);
     __syncthreads();
     if (tid == 0) {
       double li[36];
@@ -1012,7 +1021,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
       double* blk = A + (size_t)(i * (i + 1) / 2 + k) * 36;
       double acc = 0.0;
 #pragma unroll
-      for (int t = 0; t < 6; ++t) if (t <= c) acc += __ldcg(blk + 6 * r + t) * li[6 * c + t];
+      for (int t = 0; t < 6; ++t) if (t <= c) acc += ld(blk + 6 * r + t) * li[6 * c + t];
       P[(size_t)i * 36 + e] = acc;
     }
     if (tid >= T - 6) {
@@ -1050,9 +1059,9 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
       double2* dst = reinterpret_cast<double2*>(A + (size_t)(i * (i + 1) / 2 + j) * 36 + 6 * r);
 #pragma unroll
       for (int h = 0; h < 3; ++h) {
-        double2 v = __ldcg(dst + h);
+        double2 v = ld2(dst + h);
         v.x -= acc[2 * h]; v.y -= acc[2 * h + 1];
-        __stcg(dst + h, v);
+        st2(dst + h, v);
       }
     }
     for (int idx = tid; idx < m * 6; idx += T) {
@@ -1081,7 +1090,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
       const double* blk = A + (size_t)(k * (k + 1) / 2 + j) * 36;
       double acc = 0.0;
 #pragma unroll
-      for (int r = 0; r < 6; ++r) acc += __ldcg(blk + 6 * r + c) * xk[r];
+      for (int r = 0; r < 6; ++r) acc += ld(blk + 6 * r + c) * xk[r];
       y[6 * j + c] -= acc;
     }
     __syncthreads();

@@ -70,7 +70,7 @@ struct sba_handle_s {
   int coop_pcg_blocks = 0;    // idem for k_pcg_coop
   double* pcg_pbuf = nullptr; double* pcg_rowdot = nullptr;
   bool pcg_cluster_ok = false; size_t pcg_cluster_smem = 0; int pcg_rows_cap = 0, pcg_ent_cap = 0;   // one 8-CTA cluster per window (k_pcg_cluster)
-  bool chol_ok = false; size_t chol_smem = 0; int chol_threads = kCholThreads;   // one CTA per window factors S exactly (k_chol_window)
+  bool chol_ok = false, chol_in_smem = false; size_t chol_smem = 0; int chol_threads = kCholThreads;   // one CTA per window factors S exactly (k_chol_window)
   bool chol_cluster_ok = false; size_t chol_cluster_smem = 0;   // mid-size windows: one 8-CTA cluster per window (k_chol_cluster)
   size_t lin_smem = 0, schur_smem = 0;   // dynamic shared memory of the per-chunk kernels (largest chunk)
 
@@ -339,7 +339,9 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
       if ((rc = h->alloc(&d.chol_ws, (size_t)std::max<int64_t>(tot, 1)))) return rc;
       h->chol_smem = chol_smem_bytes(nf_max);
       h->chol_threads = nf_max <= 12 ? 128 : (nf_max <= 24 ? 256 : kCholThreads);   // trailing update of the first column: nf (nf - 1) / 2 * 6 rows
-      CUDA_TRY(cudaFuncSetAttribute(k_chol_window, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->chol_smem, 1024)));
+      h->chol_in_smem = nf_max <= kCholSmemCams;
+      CUDA_TRY(cudaFuncSetAttribute(k_chol_window<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->chol_smem, 1024)));
+      CUDA_TRY(cudaFuncSetAttribute(k_chol_window<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->chol_smem, 1024)));
       CUDA_TRY(cudaStreamSynchronize(h->stream));      // `off` is a local
     }
     h->chol_cluster_smem = chol_cluster_smem_bytes(std::max(nf_max, 1));
@@ -523,7 +525,8 @@ static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
       cfg.attrs = at; cfg.numAttrs = 1;
       CUDA_TRY(cudaLaunchKernelEx(&cfg, k_chol_cluster, d, (int)(h->P.debug == 2)));
     } else {
-      k_chol_window<<<d.nwin, h->chol_threads, h->chol_smem, h->stream>>>(d);
+      if (h->chol_in_smem) k_chol_window<true><<<d.nwin, h->chol_threads, h->chol_smem, h->stream>>>(d);
+      else k_chol_window<false><<<d.nwin, h->chol_threads, h->chol_smem, h->stream>>>(d);
     }
     h->launches++;
     it = -1;

@@ -129,9 +129,13 @@ def test_every_linear_solver_path_solves_the_same_system(small_window, path, mon
     check_solution(w, summ, poses, points, so, po, xo)
 
 
-def test_cholesky_of_a_batch_of_windows_equals_pcg(monkeypatch):
-    """Config-3 shape: several independent windows in one call, one CTA per window in k_chol_window."""
-    ws = [make_window(5 + i, 300 + 50 * i, 4, 40 + i) for i in range(4)]
+@pytest.mark.parametrize("frames", [5, 24])
+def test_cholesky_of_a_batch_of_windows_equals_pcg(frames, monkeypatch):
+    """Config-3 shape: several independent windows in one call, one CTA per window in k_chol_window — with the
+    lower block-triangle in shared memory (<= 20 free cameras) or in the L2-resident workspace (more; the cluster
+    kernel is switched off to get there)."""
+    monkeypatch.setenv("SBA_NO_CLUSTER", "1")
+    ws = [make_window(frames + i, 300 + 50 * i, 4, 40 + i) for i in range(4)]
     cam_off = np.cumsum([0] + [x["poses"].shape[0] for x in ws]).astype(np.int32)
     pt_off = np.cumsum([0] + [x["points"].shape[0] for x in ws]).astype(np.int32)
     poses = np.concatenate([x["poses"] for x in ws]); points = np.concatenate([x["points"] for x in ws])

@@ -7,6 +7,8 @@
 // are free.  The pattern rule is SURVEY §8 R10: block (i,j) of the reduced camera matrix is
 // structurally non-zero iff some point is observed by both free cameras i and j.
 #include <cstdio>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <algorithm>
 #include <cstring>
@@ -60,6 +62,14 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
   if (pt_begin < 0 || pt_end > Np || pt_begin > pt_end) return "bad point shard";
   HostStructure& H = *S;
   H = HostStructure();
+  const bool timing = std::getenv("SBA_TIMING") != nullptr;
+  auto tprev = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (!timing) return;
+    const auto t = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[sba]   structure %-28s %.3f ms\n", what, 1e3 * std::chrono::duration<double>(t - tprev).count());
+    tprev = t;
+  };
   H.Nc = Nc; H.Np = Np; H.nwin = nwin; H.pt_begin = pt_begin; H.pt_end = pt_end;
 
   // ---- windows
@@ -109,6 +119,7 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     std::vector<int32_t> cur(gpt_off.begin(), gpt_off.end() - 1);
     for (int64_t k = 0; k < NobsAll; ++k) gperm[cur[obs_pt[k]]++] = (int32_t)k;
   }
+  lap("validate + counting sort");
   // ---- local (owned) slice of the point order
   const int32_t base = gpt_off[pt_begin];
   const int64_t Nobs = (int64_t)gpt_off[pt_end] - base;
@@ -127,6 +138,7 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     H.perm_p[e] = k; H.pcam[e] = obs_cam[k]; H.ppt[e] = obs_pt[k];
   }
 
+  lap("point-order views");
   // ---- chunks, camera slots, local blocks
   struct LB { uint8_t sa, sb; int64_t key; };
   struct ChunkTab {
@@ -241,9 +253,18 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
   H.obs_cap = obs_cap;
   const int nch_all = (int)cr.size();
 
+  lap("chunk tables (parallel)");
   // ---- block pattern: union of all chunks' local blocks + the diagonal of every free camera
   std::vector<int64_t> keys;
-  {
+  std::vector<int32_t> key_blk;        // small Nf: block id by key (dense Nf x Nf map)
+  const bool dense_map = (int64_t)Nf * Nf <= ((int64_t)1 << 22);
+  if (dense_map) {
+    std::vector<uint8_t> mark((size_t)Nf * Nf, 0);
+    for (int f = 0; f < Nf; ++f) mark[(size_t)f * Nf + f] = 1;
+    for (int ch = 0; ch < nch_all; ++ch) for (const LB& b : tab[ch].lbs) mark[(size_t)b.key] = 1;
+    key_blk.assign((size_t)Nf * Nf, -1);
+    for (size_t k = 0; k < mark.size(); ++k) if (mark[k]) { key_blk[k] = (int32_t)keys.size(); keys.push_back((int64_t)k); }
+  } else {
     size_t tot = (size_t)Nf;
     for (int ch = 0; ch < nch_all; ++ch) tot += tab[ch].lbs.size();
     keys.reserve(tot);
@@ -259,45 +280,58 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     if (H.blk_row[b] == H.blk_col[b]) H.diag_blk[H.blk_row[b]] = b;
   }
 
-  // ---- flatten the owned chunks
+  lap("block pattern");
+  // ---- flatten the owned chunks: offsets by one serial prefix pass, contents filled in parallel
   H.win_pchunk_off.assign(nwin + 1, 0);
-  H.slot_off.push_back(0); H.lb_off.push_back(0); H.cs_obs_off.push_back(0);
-  H.oslot.resize(Nobs); H.sobs.resize(Nobs);
-  H.lb_pair_off.push_back(0);
-  {
-    size_t npairs = 0;
-    for (int ch = 0; ch < nch_all; ++ch) if (cr[ch].owned) npairs += tab[ch].pairs.size();
-    if (npairs > 2000000000ULL) return "too many block products for 32-bit offsets";
-    H.pairs.reserve(npairs);
-  }
+  std::vector<int> own;                                   // owned chunks, in order
+  for (int ch = 0; ch < nch_all; ++ch) if (cr[ch].owned) own.push_back(ch);
+  const int nch = (int)own.size();
+  H.pchunk_begin.resize(nch); H.pchunk_end.resize(nch); H.pchunk_win.resize(nch);
+  H.slot_off.assign(nch + 1, 0); H.lb_off.assign(nch + 1, 0);
+  std::vector<int64_t> pair_off((size_t)nch + 1, 0);
   {
     int w_next = 0;
-    for (int ch = 0; ch < nch_all; ++ch) {
-      const ChunkRange& R = cr[ch];
-      if (!R.owned) continue;
-      while (w_next <= R.win) H.win_pchunk_off[w_next++] = (int32_t)H.pchunk_begin.size();
-      const ChunkTab& T = tab[ch];
-      H.pchunk_begin.push_back(R.p0); H.pchunk_end.push_back(R.p1); H.pchunk_win.push_back(R.win);
-      const int32_t e0 = H.pt_off[R.p0];
-      const int n = (int)T.oslot.size();
-      std::memcpy(H.oslot.data() + e0, T.oslot.data(), (size_t)n);
-      std::memcpy(H.sobs.data() + e0, T.sobs.data(), (size_t)n * sizeof(uint16_t));
-      for (size_t s = 0; s < T.cams.size(); ++s) { H.cs_cam.push_back(T.cams[s]); H.cs_obs_off.push_back(e0 + T.slot_obs_off[s + 1]); }
-      H.slot_off.push_back((int32_t)H.cs_cam.size());
-      for (size_t l = 0; l < T.lbs.size(); ++l) {
-        const LB& b = T.lbs[l];
-        H.lb_sa.push_back(b.sa); H.lb_sb.push_back(b.sb);
-        H.lb_blk.push_back((int32_t)(std::lower_bound(keys.begin(), keys.end(), b.key) - keys.begin()));
-        H.lb_pair_off.push_back(H.lb_pair_off.back() + T.lb_pair_cnt[l]);
-      }
-      H.pairs.insert(H.pairs.end(), T.pairs.begin(), T.pairs.end());
+    for (int i = 0; i < nch; ++i) {
+      const ChunkRange& R = cr[own[i]];
+      const ChunkTab& T = tab[own[i]];
+      while (w_next <= R.win) H.win_pchunk_off[w_next++] = i;
+      H.pchunk_begin[i] = R.p0; H.pchunk_end[i] = R.p1; H.pchunk_win[i] = R.win;
+      H.slot_off[i + 1] = H.slot_off[i] + (int32_t)T.cams.size();
+      H.lb_off[i + 1] = H.lb_off[i] + (int32_t)T.lbs.size();
+      pair_off[i + 1] = pair_off[i] + (int64_t)T.pairs.size();
       H.max_slots = std::max(H.max_slots, (int32_t)T.cams.size());
-      H.max_chunk_obs = std::max(H.max_chunk_obs, (int32_t)n);
+      H.max_chunk_obs = std::max(H.max_chunk_obs, (int32_t)T.oslot.size());
       H.max_chunk_pts = std::max(H.max_chunk_pts, R.p1 - R.p0);
       H.max_chunk_pairs = std::max(H.max_chunk_pairs, (int32_t)std::min<size_t>(T.pairs.size(), 1u << 30));
-      H.lb_off.push_back((int32_t)H.lb_sa.size());
     }
-    while (w_next <= nwin) H.win_pchunk_off[w_next++] = (int32_t)H.pchunk_begin.size();
+    while (w_next <= nwin) H.win_pchunk_off[w_next++] = nch;
+  }
+  if (pair_off[nch] > 2000000000LL) return "too many block products for 32-bit offsets";
+  const int32_t ncs_all = H.slot_off[nch], nlb_all = H.lb_off[nch];
+  H.oslot.resize(Nobs); H.sobs.resize(Nobs);
+  H.cs_cam.resize(ncs_all); H.cs_obs_off.assign((size_t)ncs_all + 1, 0);
+  H.lb_sa.resize(nlb_all); H.lb_sb.resize(nlb_all); H.lb_blk.resize(nlb_all); H.lb_pair_off.assign((size_t)nlb_all + 1, 0);
+  H.pairs.resize((size_t)pair_off[nch]);
+#pragma omp parallel for schedule(dynamic, 16)
+  for (int i = 0; i < nch; ++i) {
+    const ChunkRange& R = cr[own[i]];
+    const ChunkTab& T = tab[own[i]];
+    const int32_t e0 = H.pt_off[R.p0];
+    const int n = (int)T.oslot.size();
+    std::memcpy(H.oslot.data() + e0, T.oslot.data(), (size_t)n);
+    std::memcpy(H.sobs.data() + e0, T.sobs.data(), (size_t)n * sizeof(uint16_t));
+    const int32_t s0 = H.slot_off[i];
+    for (size_t sl = 0; sl < T.cams.size(); ++sl) { H.cs_cam[s0 + sl] = T.cams[sl]; H.cs_obs_off[s0 + sl + 1] = e0 + T.slot_obs_off[sl + 1]; }
+    const int32_t l0 = H.lb_off[i];
+    int64_t q = pair_off[i];
+    for (size_t l = 0; l < T.lbs.size(); ++l) {
+      const LB& b = T.lbs[l];
+      H.lb_sa[l0 + l] = b.sa; H.lb_sb[l0 + l] = b.sb;
+      H.lb_blk[l0 + l] = dense_map ? key_blk[(size_t)b.key] : (int32_t)(std::lower_bound(keys.begin(), keys.end(), b.key) - keys.begin());
+      q += T.lb_pair_cnt[l];
+      H.lb_pair_off[l0 + l + 1] = (int32_t)q;
+    }
+    if (!T.pairs.empty()) std::memcpy(H.pairs.data() + pair_off[i], T.pairs.data(), T.pairs.size() * sizeof(uint16_t));
   }
   std::vector<ChunkTab>().swap(tab);
   {
@@ -313,6 +347,7 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     }
   }
 
+  lap("flatten");
   // ---- static partial lists (ascending => fixed summation order)
   const int32_t nlb = (int32_t)H.lb_blk.size(), ncs = (int32_t)H.cs_cam.size();
   H.blk_part_off.assign(nbu + 1, 0);
@@ -347,6 +382,7 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
       if (H.blk_row[b] != H.blk_col[b]) { const int32_t r = H.blk_col[b]; const int32_t at = cur[r]++; H.bsr_col[at] = H.blk_row[b]; H.bsr_blk[at] = ~b; }
     for (int b = 0; b < nbu; ++b) { const int32_t r = H.blk_row[b]; const int32_t at = cur[r]++; H.bsr_col[at] = H.blk_col[b]; H.bsr_blk[at] = b; }
   }
+  lap("partial lists + block-CSR");
   return std::string();
 }
 

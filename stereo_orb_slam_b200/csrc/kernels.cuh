@@ -1788,56 +1788,102 @@ __global__ void k_trial_cams(Dev d) { dev_trial_cam(d, blockIdx.x * blockDim.x +
 
 // thread per point: trial point, cost, |x_trial - x|^2 and (state 2) the directional derivative
 //   d/ds cost = sum_obs  rho' (D^T r) . (G dw + dt + R dp)     evaluated at the trial point
+constexpr int kTrialSlots = 32;    // chunks with at most this many cameras compute their trial cameras in shared memory
+
 __device__ __forceinline__ void dev_trial_points(const Dev& d, const DevParams& P, int chunk) {
   __shared__ double sm[4 * 3];
-  const int w = d.pchunk_win[chunk];
+  __shared__ double cps[kTrialSlots * 21];    // trial R / J_l / t of the chunk's cameras
+  __shared__ double Xs[kPointChunk * 3];      // the chunk's trial points
+  __shared__ double dps[kPointChunk * 3];     // and their steps
+  __shared__ int cfs[kTrialSlots];            // their free-camera index (or -1)
+  const int4 cd0 = __ldg(d.cdesc + 4 * (size_t)chunk), cd1 = __ldg(d.cdesc + 4 * (size_t)chunk + 1);
+  const int p0 = cd0.x, np = cd0.y, e0 = cd0.z, n = cd0.w, w = cd1.x, cs0 = cd1.y, ns = cd1.z;
   const int st = __ldcg(d.w_ls_state + w);
   if (st < 1 || st > 3) return;
   const bool grad = (st == 2);
   const double step = __ldcg(d.w_ls_x + w);
-  const int p = d.pchunk_begin[chunk] + threadIdx.x;
+  // Trial cameras of the chunk, computed here exactly as dev_trial_cam does (same expression, same bits) instead of
+  // read back from campre_new: no L2 round trip per observation, and no dependence on the trial-camera phase.
+  const bool staged = ns <= kTrialSlots;
+  if (staged) {
+    for (int sl = threadIdx.x; sl < ns; sl += kThreads) {
+      const int c = d.cs_cam[cs0 + sl];
+      const int f = d.fc[c];
+      double pose[6];
+#pragma unroll
+      for (int i = 0; i < 6; ++i) {
+        pose[i] = d.poses[(size_t)c * 6 + i];
+        if (f >= 0) pose[i] += step * d.x[(size_t)f * 6 + i];
+      }
+      CamPre cp;
+      cam_precompute(pose, cp);
+      *reinterpret_cast<CamPre*>(cps + 21 * sl) = cp;
+      cfs[sl] = f;
+    }
+  }
   double part[3] = {0, 0, 0};
-  if (p < d.pchunk_end[chunk]) {
-    double X[3], dpv[3];
+  // thread per point: the projected trial point (kept in shared memory for the chunk's observations), |x_trial - x|^2
+  static_assert(kPointChunk <= kThreads, "one point per thread");
+  if ((int)threadIdx.x < np) {
+    const int p = p0 + threadIdx.x;
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
       const double x = d.pts[3 * (size_t)p + i];
-      dpv[i] = d.dp[3 * (size_t)p + i];
-      X[i] = clampd(x + step * dpv[i], P.lo, P.hi);
-      d.pts_new[3 * (size_t)p + i] = X[i];
-      part[2] += (X[i] - x) * (X[i] - x);
+      const double dv = d.dp[3 * (size_t)p + i];
+      const double X = clampd(x + step * dv, P.lo, P.hi);
+      d.pts_new[3 * (size_t)p + i] = X;
+      Xs[3 * threadIdx.x + i] = X; dps[3 * threadIdx.x + i] = dv;
+      part[2] += (X - x) * (X - x);
     }
-    const int e1 = d.pt_off[p + 1];
-    for (int e = d.pt_off[p]; e < e1; ++e) {
-      const int c = __ldg(d.pcam + e);
-      const float4 m = __ldg(d.uv_p + e);
-      const float uv[4] = {m.x, m.y, m.z, m.w};
-      if (!grad) {
-        CamPre cp;
-        load_campre_Rt(d.campre_new, c, cp);
-        part[0] += obs_cost(P.pl, P.pr, cp, X, uv, P.rdim, P.huber_delta);
-      } else {
-        CamPre cp;
-        load_campre(d.campre_new, c, cp);
-        double q[3], r[4], D[12];
-        const double s = project(P.pl, P.pr, cp, X, uv, P.rdim, q, r, D);
-        double rho, wt;
-        huber(P.huber_delta, s, rho, wt);
-        part[0] += 0.5 * rho;
-        double A[6], h[3], G[9];
-        form_A_h(D, r, wt, A, h);
-        form_G(cp, q, G);
-        double v[3] = {cp.R[0] * dpv[0] + cp.R[1] * dpv[1] + cp.R[2] * dpv[2],
-                       cp.R[3] * dpv[0] + cp.R[4] * dpv[1] + cp.R[5] * dpv[2],
-                       cp.R[6] * dpv[0] + cp.R[7] * dpv[1] + cp.R[8] * dpv[2]};
-        const int f = __ldg(d.fc + c);
-        if (f >= 0) {
-          const double* dc = d.x + (size_t)f * 6;
+  }
+  __syncthreads();
+  // thread per observation: its cost and (state 2) its share of the directional derivative
+  for (int i = threadIdx.x; i < n; i += kThreads) {
+    const int e = e0 + i;
+    const int pl = __ldg(d.ppt + e) - p0;
+    const float4 m = __ldg(d.uv_p + e);
+    const float uv[4] = {m.x, m.y, m.z, m.w};
+    const double X[3] = {Xs[3 * pl], Xs[3 * pl + 1], Xs[3 * pl + 2]};
+    CamPre cp;
+    int f;
+    if (staged) {
+      const int sl = d.oslot[e];
+      const double* src = cps + 21 * sl;
 #pragma unroll
-          for (int i = 0; i < 3; ++i) v[i] += G[3 * i] * dc[0] + G[3 * i + 1] * dc[1] + G[3 * i + 2] * dc[2] + dc[3 + i];
-        }
-        part[1] += h[0] * v[0] + h[1] * v[1] + h[2] * v[2];
+      for (int k = 0; k < 9; ++k) cp.R[k] = src[k];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) cp.t[k] = src[18 + k];
+      if (grad) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) cp.Jl[k] = src[9 + k];
       }
+      f = cfs[sl];
+    } else {
+      const int c = __ldg(d.pcam + e);
+      if (grad) load_campre(d.campre_new, c, cp); else load_campre_Rt(d.campre_new, c, cp);
+      f = __ldg(d.fc + c);
+    }
+    if (!grad) {
+      part[0] += obs_cost(P.pl, P.pr, cp, X, uv, P.rdim, P.huber_delta);
+    } else {
+      const double dpv[3] = {dps[3 * pl], dps[3 * pl + 1], dps[3 * pl + 2]};
+      double q[3], r[4], D[12];
+      const double s = project(P.pl, P.pr, cp, X, uv, P.rdim, q, r, D);
+      double rho, wt;
+      huber(P.huber_delta, s, rho, wt);
+      part[0] += 0.5 * rho;
+      double A[6], h[3], G[9];
+      form_A_h(D, r, wt, A, h);
+      form_G(cp, q, G);
+      double v[3] = {cp.R[0] * dpv[0] + cp.R[1] * dpv[1] + cp.R[2] * dpv[2],
+                     cp.R[3] * dpv[0] + cp.R[4] * dpv[1] + cp.R[5] * dpv[2],
+                     cp.R[6] * dpv[0] + cp.R[7] * dpv[1] + cp.R[8] * dpv[2]};
+      if (f >= 0) {
+        const double* dc = d.x + (size_t)f * 6;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) v[k] += G[3 * k] * dc[0] + G[3 * k + 1] * dc[1] + G[3 * k + 2] * dc[2] + dc[3 + k];
+      }
+      part[1] += h[0] * v[0] + h[1] * v[1] + h[2] * v[2];
     }
   }
   const double tot = block_sum<3>(part, sm);
@@ -2002,7 +2048,7 @@ __global__ void k_apply_cams(Dev d) { dev_apply_cam(d, blockIdx.x * blockDim.x +
 // is still searching, then accepted candidates become the state.  Replaces 5 launches, a memset and a host round
 // trip per line-search round.  The searching counter alternates between counters[3] and [5] so that resetting
 // one never races with reading the other; counters[6] returns the number of rounds.
-__global__ void __launch_bounds__(kThreads) k_step_loop(Dev d, DevParams P) {
+__global__ void __launch_bounds__(kThreads) k_step_loop(Dev d, DevParams P, int fused_cams) {
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
   const int nb = gridDim.x;
   // P.debug == 2 (SBA_DEBUG_LS=2): block 0 prints the nanoseconds spent in each phase (tuning aid)
@@ -2021,7 +2067,7 @@ __global__ void __launch_bounds__(kThreads) k_step_loop(Dev d, DevParams P) {
     int32_t* cnt = d.counters + ((round & 1) ? 5 : 3);
     int32_t* other = d.counters + ((round & 1) ? 3 : 5);
     for (int c = blockIdx.x * kThreads + threadIdx.x; c < d.Nc; c += nb * kThreads) dev_trial_cam(d, c);
-    grid.sync();
+    if (!fused_cams) grid.sync();         // the chunks read campre_new only when one of them has too many cameras to stage
     lap(2);
     for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) { dev_trial_points(d, P, ch); __syncthreads(); }
     grid.sync();

@@ -615,7 +615,8 @@ static int do_step(sba_handle h, int* ls_rounds) {
     int grid = std::max(1, std::min(h->coop_blocks, want));
     if (const char* e = std::getenv("SBA_STEP_GRID")) grid = std::max(1, std::min(grid, std::atoi(e)));   // tuning aid
     Dev dd = d; DevParams pp = P;
-    void* args[] = {&dd, &pp};
+    int fused_cams = h->H.max_slots <= kTrialSlots ? 1 : 0;
+    void* args[] = {&dd, &pp, &fused_cams};
     CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_step_loop, dim3(grid), dim3(kThreads), args, 0, h->stream));
     h->launches++;
     CUDA_TRY(cudaMemcpyAsync(h->h_counters, d.counters, 32, cudaMemcpyDeviceToHost, h->stream));

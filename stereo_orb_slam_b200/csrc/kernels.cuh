@@ -1565,6 +1565,9 @@ __global__ void __launch_bounds__(kThreads) k_pcg_coop(Dev d, DevParams P, int m
   const int lane = threadIdx.x & 31;
   const int gw = (blockIdx.x * kThreads + threadIdx.x) >> 5, nw = (gridDim.x * kThreads) >> 5;
   const int nf = d.Nf;
+  // Two per-row dot buffers: a CTA that is through with a reduction may start writing the NEXT phase's dots while a
+  // slower CTA is still summing this phase's, so consecutive phases must not share a buffer.
+  double* dotA = rowdot; double* dotB = rowdot + nf;
   if (d.w_status[0] != 0 || d.w_fail[0] != 0) { if (blockIdx.x == 0 && threadIdx.x == 0) d.w_pcg_it[0] = 0; return; }
   const int ps = lane / 6, ri = lane - 6 * ps;
   // init: x = 0, r = rhs, z = Minv r, p_old = 0 (so that p = z + beta * 0 in the first mat-vec), per-row r.z
@@ -1581,10 +1584,10 @@ __global__ void __launch_bounds__(kThreads) k_pcg_coop(Dev d, DevParams P, int m
     double dot = (lane < 6) ? rj[lane < 6 ? lane : 0] * z : 0.0;
 #pragma unroll
     for (int o = 4; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);   // lanes 0..7 (6, 7 hold zero)
-    if (lane == 0) rowdot[f] = dot;
+    if (lane == 0) dotB[f] = dot;
   }
   grid.sync();
-  double rz = coop_sum(rowdot, nf, sm);
+  double rz = coop_sum(dotB, nf, sm);
   const double rz0 = rz;
   int it = 0;
   bool fail = false;
@@ -1624,10 +1627,10 @@ __global__ void __launch_bounds__(kThreads) k_pcg_coop(Dev d, DevParams P, int m
         }
 #pragma unroll
         for (int o = 4; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
-        if (lane == 0) rowdot[f] = dot;
+        if (lane == 0) dotA[f] = dot;
       }
       grid.sync();
-      const double pAp = coop_sum(rowdot, nf, sm);
+      const double pAp = coop_sum(dotA, nf, sm);
       if (!(pAp > 0.0)) { fail = true; break; }
       const double alpha = rz / pAp;
       // ---- B (the warp that owns a row in A owns it here too: its own pnew / Ap writes are visible to it)
@@ -1650,10 +1653,10 @@ __global__ void __launch_bounds__(kThreads) k_pcg_coop(Dev d, DevParams P, int m
         }
 #pragma unroll
         for (int o = 4; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
-        if (lane == 0) rowdot[f] = dot;
+        if (lane == 0) dotB[f] = dot;
       }
       grid.sync();
-      const double rz_new = coop_sum(rowdot, nf, sm);
+      const double rz_new = coop_sum(dotB, nf, sm);
       { double* t = pold; pold = pnew; pnew = t; }
       ++it;
       if (!isfinite(rz_new)) { fail = true; break; }

@@ -247,7 +247,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   AL(d.sc2c, nc * 6) AL(d.sc2p, np * 3) AL(d.lin_part, (size_t)d.npchunk * 2)
   AL(d.spart, (size_t)d.nlb * 36) AL(d.Su, (size_t)d.nbu * 36) AL(d.rpart, (size_t)d.ncs * 6)
   AL(d.rhs, nf * 6) AL(d.rsum, nf * 6) AL(d.Minv, nf * 36)
-  AL(d.x, nf * 6) AL(d.r, nf * 6) AL(d.z, nf * 6) AL(d.p, nf * 6) AL(d.Ap, nf * 6) AL(h->pcg_pbuf, nf * 6) AL(h->pcg_rowdot, nf)
+  AL(d.x, nf * 6) AL(d.r, nf * 6) AL(d.z, nf * 6) AL(d.p, nf * 6) AL(d.Ap, nf * 6) AL(h->pcg_pbuf, nf * 6) AL(h->pcg_rowdot, 2 * nf)
   AL(d.dp, np * 3) AL(d.step_part, (size_t)d.npchunk * 4) AL(d.ls_part, (size_t)d.npchunk * 3)
   AL(d.w_radius, nw) AL(d.w_decf, nw) AL(d.w_cost, nw) AL(d.w_gmax, nw)
   AL(d.w_gd, nw * 4)   // one block: a multi-GPU solve all-reduces the four step scalars in one call

@@ -151,6 +151,23 @@ def test_cholesky_of_a_batch_of_windows_equals_pcg(frames, monkeypatch):
     assert np.abs(out["chol"] - out["pcg"]).max() <= 1e-8 * np.abs(out["pcg"]).max()
 
 
+def test_cooperative_pcg_is_bit_reproducible_on_a_global_problem():
+    """k_pcg_coop on thousands of block-rows: every CTA sums the per-row dots itself, so a fast CTA must not
+    overwrite them for the next phase while a slow one is still reading (the two phases use separate buffers).
+    Two solves of the same system must agree to the bit."""
+    smap = synthetic.make_config("C4", scale=0.5)
+    b = pack_window(smap, 0, smap.num_frames)
+    s = Solver(0).set_structure(b["poses"].shape[0], b["points"].shape[0], b["obs_cam"], b["obs_pt"])
+    s.set_state(b["poses"], b["points"]); s.set_measurements(b["obs_uv"], smap.p_l, smap.p_r)
+    s.linearize(); s.schur(1e4)
+    xs = []
+    for _ in range(3):
+        it = s.pcg(default_options(max_pcg_iterations=200))
+        xs.append(s.schur_values()[2].copy())
+        assert 0 < it <= 200
+    assert np.array_equal(xs[0], xs[1]) and np.array_equal(xs[0], xs[2])
+
+
 def check_solution(w, summary, poses, points, so, po, xo):
     assert abs(summary["final_cost"] - so["final_cost"]) <= 1e-5 * so["final_cost"]
     assert np.abs(poses[:, :3] - po[:, :3]).max() < 1e-5          # rad

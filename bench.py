@@ -148,6 +148,8 @@ def run_ours(args):
 
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and "SBA_HOST_THREADS" not in os.environ:       # torchrun pins OMP_NUM_THREADS=1; share the host cores instead
+        os.environ["SBA_HOST_THREADS"] = str(max(1, (os.cpu_count() or 1) // world))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
     torch.cuda.set_device(local)
@@ -241,7 +243,7 @@ def run_ours(args):
                 "schur_blocks": nblk},
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "what": "sba_solve on pinned host buffers: structure build + H2D + full LM solve + D2H; obs x linearisations / wall",
+                    "host_threads_per_rank": int(os.environ.get("SBA_HOST_THREADS", os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1))), "what": "sba_solve on pinned host buffers: structure build + H2D + full LM solve + D2H; obs x linearisations / wall",
                     "ms_per_solve": 1e3 * e_wall / e_steps, "lm_iterations": its // e_steps, "final_cost": summ["final_cost"],
                     "termination": summ["termination_name"],
                     "ms_breakdown": {k.replace("time_", "").replace("_s", ""): v for k, v in brk.items()},

@@ -63,6 +63,10 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
   HostStructure& H = *S;
   H = HostStructure();
   const bool timing = std::getenv("SBA_TIMING") != nullptr;
+  // host threads of the structure build: SBA_HOST_THREADS, else the OpenMP default (launchers such as torchrun set
+  // OMP_NUM_THREADS=1 for every rank, which is the wrong default for this short, embarrassingly parallel build)
+  int nthreads = omp_get_max_threads();
+  if (const char* e = std::getenv("SBA_HOST_THREADS")) nthreads = std::max(1, std::atoi(e));
   auto tprev = std::chrono::steady_clock::now();
   auto lap = [&](const char* what) {
     if (!timing) return;
@@ -132,7 +136,7 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     H.pt_off[p] = (int32_t)v;
   }
   H.perm_p.resize(Nobs); H.pcam.resize(Nobs); H.ppt.resize(Nobs);
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for schedule(static) num_threads(nthreads)
   for (int64_t e = 0; e < Nobs; ++e) {
     const int32_t k = gperm[base + e];
     H.perm_p[e] = k; H.pcam[e] = obs_cam[k]; H.ppt[e] = obs_pt[k];
@@ -159,7 +163,7 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     const int nch = (int)cr.size();
     tab.assign(nch, ChunkTab());
     bool overflow = false;
-#pragma omp parallel
+#pragma omp parallel num_threads(nthreads)
     {
       std::vector<int32_t> slot_of_cam(Nc, -1);
       std::vector<uint8_t> bits;
@@ -312,7 +316,7 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
   H.cs_cam.resize(ncs_all); H.cs_obs_off.assign((size_t)ncs_all + 1, 0);
   H.lb_sa.resize(nlb_all); H.lb_sb.resize(nlb_all); H.lb_blk.resize(nlb_all); H.lb_pair_off.assign((size_t)nlb_all + 1, 0);
   H.pairs.resize((size_t)pair_off[nch]);
-#pragma omp parallel for schedule(dynamic, 16)
+#pragma omp parallel for schedule(dynamic, 16) num_threads(nthreads)
   for (int i = 0; i < nch; ++i) {
     const ChunkRange& R = cr[own[i]];
     const ChunkTab& T = tab[own[i]];

@@ -138,7 +138,15 @@ def run_reference(args):
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "lm_iters_per_s": its / tot, "k1k3_obs_per_s": Nobs / k13,
             "note": "CPU restatement of the reference's Ceres path — Ceres itself unavailable on this box"}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_JSON_OUT = None
+
+
+def emit(line):
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n"); out.flush()
 
 
 def run_ours(args):
@@ -154,8 +162,9 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line
+        # keep stdout to the one JSON line: NCCL writes its banner ("NCCL version ...", printed from level VERSION
+        # up, WARN included) and anything else it logs to stderr instead
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -264,7 +273,7 @@ def run_ours(args):
         line["cpu_baseline"] = {"value": Nobs / sec, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": "%d passes of linearise (Jet autodiff) + block build + dense Schur over the same %s window" % (reps_cpu, args.workload)}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -278,6 +287,12 @@ def main():
     ap.add_argument("--workload", default="C2", choices=["C1", "C2", "C4s"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: file descriptor 1 is pointed at stderr for everything else (NCCL prints
+    # its version banner to stdout whatever NCCL_DEBUG_FILE says) and the line goes to the saved descriptor
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -47,6 +47,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--iters", type=int, default=10, help="LM iteration cap of the timed solve")
     args = ap.parse_args()
+    sys.stdout.flush(); json_out = os.fdopen(os.dup(1), "w"); os.dup2(2, 1)     # stdout carries the JSON line only (NCCL's banner goes to stderr)
     import torch
     import torch.distributed as dist
     from stereo_orb_slam_b200 import Solver, default_options, pack_window, synthetic
@@ -55,6 +56,8 @@ def main():
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # stdout carries the JSON line only
+        os.environ.setdefault("SBA_HOST_THREADS", str(max(1, (os.cpu_count() or 1) // world)))
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -101,10 +104,10 @@ def main():
     if rank == 0:
         nobs = float(c[0])
         final_cost = float(c[1]) if args.mode == "C3" else s["final_cost"]
-        print(json.dumps({"mode": args.mode, "workload": label, "n_gpus": world, "scaling": "strong",
+        json_out.write(json.dumps({"mode": args.mode, "workload": label, "n_gpus": world, "scaling": "strong",
                           "k1k3_obs_per_s": nobs * args.steps / (float(t[0]) * 1e-3), "ms_per_step": float(t[0]) / args.steps,
                           "lm_iterations": s["iterations"], "lm_iters_per_s": s["iterations"] / float(t[1]), "solve_s": float(t[1]),
-                          "pcg_iterations": s["pcg_iterations"], "final_cost": final_cost, "termination": s["termination_name"]}), flush=True)
+                          "pcg_iterations": s["pcg_iterations"], "final_cost": final_cost, "termination": s["termination_name"]}) + "\n"); json_out.flush()
     sv.close()
     if world > 1:
         dist.destroy_process_group()

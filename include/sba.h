@@ -59,7 +59,7 @@ typedef struct sba_options {
   int32_t residual_dim;          /* 4 = reference (src/reprojection_error.h:58); 3 = (u_l,v_l,u_r) only */
   double  initial_radius;        /* 1e4   Ceres default initial_trust_region_radius */
   int32_t max_pcg_iterations;    /* 500   PCG on the reduced camera system (replaces CHOLMOD, :26-29) */
-  double  pcg_tolerance;         /* 1e-10 relative preconditioned-residual tolerance */
+  double  pcg_tolerance;         /* 1e-12 relative preconditioned-residual tolerance (tight: stands in for the exact solve) */
   int32_t verbose;               /* 0     (reference prints progress + FullReport, :15,:118) */
   int32_t linear_solver;         /* 0     reduced camera system: 0 auto (block Cholesky when every window has <= 64 free
                                   *       cameras, the reference's exact factorisation, :26-29; else PCG), 1 PCG, 2 Cholesky */

@@ -29,6 +29,8 @@ def test_default_options_are_the_reference_configuration():
     assert (o.point_lower_bound, o.point_upper_bound) == (-1e4, 1e4)
     assert (o.function_tolerance, o.gradient_tolerance, o.parameter_tolerance) == (1e-16, 1e-16, 1e-8)
     assert o.residual_dim == 4 and o.initial_radius == 1e4
+    # the tail of the struct (layout check of the ctypes mirror against the C definition)
+    assert (o.max_pcg_iterations, o.pcg_tolerance, o.verbose, o.linear_solver) == (500, 1e-12, 0, 0)
 
 
 def test_no_cpu_fallback_compute_needs_a_device():

@@ -5,6 +5,7 @@
       windows dealt to the ranks (shard_windows), no data-path collective            -> strong scaling over N
   torchrun --nproc-per-node N scripts/scale_bench.py --mode C4 [--scale 1.0]      one global BA, points sharded
       (shard_points), camera-side sums all-reduced by NCCL inside libsba.so          -> strong scaling over N
+  ... --mode C5                                                                   the 20k-pose / 5M-point / 30M-observation stress config, same path as C4
 
 Each prints one JSON line on rank 0: K1-K3 observations/s (device time, max over ranks, L2 flushed between
 steps) and LM iterations/s of a capped solve (sba_run, state resident), plus the final cost for the parity table.
@@ -41,7 +42,7 @@ def batched_problem(nwin, base=16):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--mode", default="C3", choices=["C3", "C4"])
+    ap.add_argument("--mode", default="C3", choices=["C3", "C4", "C5"])
     ap.add_argument("--windows", type=int, default=4096)
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--steps", type=int, default=10)
@@ -74,7 +75,7 @@ def main():
                          win_pt_off=b["win_pt_off"])
         nobs_local, label = int(b["obs_cam"].size), "C3: %d independent windows of 10 keyframes / 5k points" % args.windows
     else:
-        smap = synthetic.make_config("C4", scale=args.scale)
+        smap = synthetic.make_config(args.mode, scale=args.scale)
         b = pack_window(smap, 0, smap.num_frames); b["p_l"], b["p_r"] = smap.p_l, smap.p_r
         if world > 1:
             uid = [Solver.comm_unique_id() if rank == 0 else None]
@@ -86,7 +87,7 @@ def main():
         else:
             nobs_local = int(b["obs_cam"].size)
         sv.set_structure(b["poses"].shape[0], b["points"].shape[0], b["obs_cam"], b["obs_pt"])
-        label = "C4 x%.2f: %d poses / %d points / %d observations, points sharded" % (args.scale, b["poses"].shape[0], b["points"].shape[0], b["obs_cam"].size)
+        label = "%s x%.2f: %d poses / %d points / %d observations, points sharded" % (args.mode, args.scale, b["poses"].shape[0], b["points"].shape[0], b["obs_cam"].size)
     sv.set_state(b["poses"], b["points"]); sv.set_measurements(b["obs_uv"], b["p_l"], b["p_r"])
     sv.linearize()
     for _ in range(3):

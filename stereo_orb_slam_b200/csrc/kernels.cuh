@@ -1145,7 +1145,7 @@ __global__ void __launch_bounds__(kCholClThreads, 1) k_chol_cluster(Dev d, int p
   if (rank == 0 && threadIdx.x == 0) d.w_pcg_it[w] = 0;
   if (nf <= 0) return;                                      // uniform over the cluster
   if (d.w_status[w] != 0 || d.w_fail[w] != 0) return;       // idem; leaves x untouched (unused)
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x;
   const int my_cols = chol_cl_cols(nf, rank), maxcols = chol_cl_cols(nf, 0);
   const int pstride = nf * 36 + 8;                          // panel rows (indexed by i) + y_k at [nf * 36 .. + 6)
   double* Acol = smem;                                                       // own columns

@@ -141,3 +141,24 @@ def test_batched_windows_pattern_is_block_diagonal():
     assert np.array_equal(fwin[rows], fwin[cols])
     with pytest.raises(_capi.SbaError):   # an observation may not link two windows
         Solver(-1).set_structure(cam_off[-1], pt_off[-1], oc, op[::-1].copy(), win_cam_off=cam_off, win_pt_off=pt_off)
+
+
+def test_structure_is_independent_of_the_host_thread_count(monkeypatch):
+    """The counting sort into point order (reference scan order kept inside a point, src/bundle_adjuster.cpp:77-102) is
+    must not depend on how the structure build is split over the host threads: same tables, and the earliest offending
+    observation decides the error message."""
+    smap = synthetic.make_config("C2")
+    w = pack_window(smap, 0, smap.num_frames)
+    Nc, Np = w["poses"].shape[0], w["points"].shape[0]
+    out = {}
+    for t in (1, 5):
+        monkeypatch.setenv("SBA_HOST_THREADS", str(t))
+        s = Solver(-1).set_structure(Nc, Np, w["obs_cam"], w["obs_pt"])
+        out[t] = s.sorted_views() + s.schur_pattern()
+    for a, b in zip(out[1], out[5]):
+        assert np.array_equal(a, b)
+    assert np.array_equal(out[5][0], np.argsort(w["obs_pt"], kind="stable"))
+    oc, op = w["obs_cam"].copy(), w["obs_pt"].copy()
+    oc[150000] = Nc + 7; op[100000] = -5          # the earlier observation decides the message
+    with pytest.raises(Exception, match="obs_pt out of range"):
+        Solver(-1).set_structure(Nc, Np, oc, op)

@@ -84,8 +84,10 @@ class BundleAdjusterT {
       m_off[(size_t)i + 1] = (int64_t)m_pid.size();
     }
     const size_t nobs = m_pid.size();
-    m_map.resize(m_ldm_points.size() * 3);
-    for (uint32_t id : m_pid) {                                                 // only the window's points are read (:81-87)
+    // id-indexed staging of the WINDOW's points: only they are read and written here (:81-87); the buffer persists
+    // across calls, so growing it costs O(points created since the last call), not O(map)
+    if (m_map.size() < m_ldm_points.size() * 3) m_map.resize(m_ldm_points.size() * 3);
+    for (uint32_t id : m_pid) {
       if (id >= m_ldm_points.size()) throw std::out_of_range("BundleAdjuster::Optimize: observation of an unknown map point");
       const std::array<float, 3> p = m_ldm_points[id]->Position();
       m_map[(size_t)id * 3] = p[0]; m_map[(size_t)id * 3 + 1] = p[1]; m_map[(size_t)id * 3 + 2] = p[2];
@@ -100,9 +102,9 @@ class BundleAdjusterT {
     return np;
   }
 
-  // src/bundle_adjuster.cpp:39-133.  The reference returns void and never looks at the termination type;
-  // results are written back whenever the solve produced any (SBA_OK / SBA_NO_CONVERGENCE).  Hard errors
-  // (no CUDA device, invalid indices, non-finite cost) throw: there is no CPU fallback.
+  // src/bundle_adjuster.cpp:39-133.  The reference returns void and never looks at the termination type: results
+  // are written back whatever the solver says — also after a numerical failure (the last accepted state; see
+  // Status() / Summary()).  Only hard errors (no CUDA device, NCCL, invalid indices) throw: there is no CPU fallback.
   void Optimize(unsigned int start_frame_id, unsigned int end_frame_id) {
     if (end_frame_id <= start_frame_id) return;
     const int32_t np = Pack(start_frame_id, end_frame_id);
@@ -113,7 +115,7 @@ class BundleAdjusterT {
     m_status = sba_solve(m_handle, nc, np, (int64_t)nobs, m_poses.data(), m_points.data(), m_cam.data(), m_pt.data(),
                          m_uvp.data(), ReprojectionError::p_l().data(), ReprojectionError::p_r().data(), nullptr, 1,
                          nullptr, nullptr, &m_options, &m_summary);
-    if (m_status != SBA_OK && m_status != SBA_NO_CONVERGENCE) check(m_status, "sba_solve");
+    if (m_status != SBA_OK && m_status != SBA_NO_CONVERGENCE && m_status != SBA_NUMERICAL_FAILURE) check(m_status, "sba_solve");
     if (m_options.verbose)
       std::printf("[sba] cost %.6e -> %.6e, %d iterations, termination %d, %.3f ms\n", m_summary.initial_cost,
                   m_summary.final_cost, m_summary.iterations, m_summary.termination, 1e3 * m_summary.time_total_s);

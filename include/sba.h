@@ -61,8 +61,9 @@ typedef struct sba_options {
   int32_t max_pcg_iterations;    /* 500   PCG on the reduced camera system (replaces CHOLMOD, :26-29) */
   double  pcg_tolerance;         /* 1e-12 relative preconditioned-residual tolerance (tight: stands in for the exact solve) */
   int32_t verbose;               /* 0     (reference prints progress + FullReport, :15,:118) */
-  int32_t linear_solver;         /* 0     reduced camera system: 0 auto (block Cholesky when every window has <= 64 free
-                                  *       cameras, the reference's exact factorisation, :26-29; else PCG), 1 PCG, 2 Cholesky */
+  int32_t linear_solver;         /* 0     reduced camera system: 0 auto = the reference's exact factorisation (:26-29): dense block
+                                  *       Cholesky for windows of <= 64 free cameras, block-sparse Cholesky (nested dissection)
+                                  *       above; PCG only if the pattern is too dense to factor.  1 PCG.  2 Cholesky or an error */
 } sba_options;
 
 typedef struct sba_summary {
@@ -89,7 +90,8 @@ const char* sba_status_string(int status);
 const char* sba_last_error(void);
 
 /* ---- handle ------------------------------------------------------------------------------- */
-/* One handle = one CUDA device = one host thread at a time.  No global state. */
+/* One handle = one CUDA device = one host thread at a time.  No global state: device memory comes from a
+ * stream-ordered pool owned by the handle. */
 int sba_create(int device, sba_handle* out);
 void sba_destroy(sba_handle h);
 
@@ -119,9 +121,10 @@ int sba_get_state(sba_handle h, double* poses, double* points);
 /* Run the LM loop on device-resident state. */
 int sba_run(sba_handle h, const sba_options* opt, sba_summary* summary);
 
-/* One-shot: structure + upload + LM + download.  poses / points are updated in place (also when
- * the result is SBA_NO_CONVERGENCE, as the reference always writes back, :121-132); untouched on
- * SBA_INVALID_ARGUMENT / SBA_CUDA_ERROR / SBA_NUMERICAL_FAILURE. */
+/* One-shot: structure + upload + LM + download.  poses / points are updated in place — also when the
+ * result is SBA_NO_CONVERGENCE or SBA_NUMERICAL_FAILURE (the last ACCEPTED state), because the reference
+ * never looks at Ceres' termination type and always writes back (:116-132); untouched on
+ * SBA_INVALID_ARGUMENT / SBA_CUDA_ERROR / SBA_NCCL_ERROR. */
 int sba_solve(sba_handle h, int32_t num_cameras, int32_t num_points, int64_t num_observations,
               double* poses, double* points, const int32_t* obs_cam, const int32_t* obs_pt,
               const float* obs_uv, const double* p_l, const double* p_r, const uint8_t* cam_fixed,
@@ -160,6 +163,16 @@ int64_t sba_get_schur_pattern(sba_handle h, int32_t* rows, int32_t* cols, int64_
 int sba_get_schur_values(sba_handle h, double* blocks, double* rhs, double* solution);
 /* sorted views: obs index (input order) at each position of the point-sorted / camera-sorted lists */
 int sba_get_sorted_views(sba_handle h, int32_t* by_point, int32_t* by_camera);
+/* Symbolic phase of the exact block-sparse Cholesky used when a window has more than 64 free cameras (the global BA
+ * calls, src/slam.cpp:156; stands in for CHOLMOD's analysis, src/bundle_adjuster.cpp:26-29).  info = {block columns n,
+ * blocks in L, block products, elimination-tree levels}; call once with NULL arrays for the sizes.  perm [n] new -> old
+ * free-camera index; col_ptr [n+1] / row_idx [nnzL] pattern of L (diagonal first); init_src [nnzL] block of
+ * sba_get_schur_pattern's UPPER blocks that lands there (b, ~b = transposed, INT32_MIN = fill); upd_ptr [nnzL+1] /
+ * upd_a, upd_b [nupd] products L_a L_b^T each block receives; lvl_ptr [levels+1] / lvl_cols [n] level sets.
+ * SBA_INVALID_ARGUMENT when the structure has no sparse factorisation. */
+int sba_get_factor_symbolic(sba_handle h, int64_t info[4], int32_t* perm, int32_t* col_ptr, int32_t* row_idx,
+                            int32_t* init_src, int64_t* upd_ptr, int32_t* upd_a, int32_t* upd_b, int32_t* lvl_ptr,
+                            int32_t* lvl_cols);
 int32_t sba_num_free_cameras(sba_handle h);
 /* number of kernels launched by this handle so far (bench.py's gpu_launches) */
 int64_t sba_launch_count(sba_handle h);

@@ -34,6 +34,7 @@
 #include <complex>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <set>
@@ -485,6 +486,134 @@ bool schur(const Problem& P, const Adjacency& A, const Blocks& B, const std::vec
 
 inline double clampd(double x, double lo, double hi) { return x < lo ? lo : (x > hi ? hi : x); }
 
+// ---- envelope (skyline) form of the reduced camera matrix, for global problems (thousands of cameras) -----------
+// Ceres factors the reduced camera matrix with a sparse Cholesky (CHOLMOD, src/bundle_adjuster.cpp:26-29); the dense
+// LLT above is the same solution but O(n^2) memory.  In the reference's frame order the matrix is banded
+// (co-visibility reaches a few frames back) plus loop-closure rows, so a row-wise envelope — row i stores columns
+// first[i]..i of the lower triangle — holds it exactly, fill-in included, and Jennings' row Cholesky factors it in
+// place.  Same arithmetic as the dense LLT up to summation order.
+struct Envelope {
+  int n = 0;
+  std::vector<int> first;        // [n] first stored column of row i
+  std::vector<size_t> off;       // [n+1]
+  std::vector<double> v;
+  double* row(int i) { return v.data() + off[i] - first[i]; }             // row(i)[j] for first[i] <= j <= i
+  const double* row(int i) const { return v.data() + off[i] - first[i]; }
+  void build(const Problem& P, const Adjacency& A, const std::vector<int>& fc, int Nf) {
+    n = 6 * Nf;
+    std::vector<int> fb(Nf);
+    for (int f = 0; f < Nf; ++f) fb[f] = f;
+    for (int p = 0; p < P.Np; ++p) {
+      int mn = Nf;
+      for (int e = A.pt_off[p]; e < A.pt_off[p + 1]; ++e) { const int f = fc[P.obs_cam[A.pt_obs[e]]]; if (f >= 0) mn = std::min(mn, f); }
+      for (int e = A.pt_off[p]; e < A.pt_off[p + 1]; ++e) { const int f = fc[P.obs_cam[A.pt_obs[e]]]; if (f >= 0) fb[f] = std::min(fb[f], mn); }
+    }
+    first.resize(n); off.assign(n + 1, 0);
+    for (int i = 0; i < n; ++i) { first[i] = 6 * fb[i / 6]; off[i + 1] = off[i] + (size_t)(i - first[i] + 1); }
+    v.assign(off[n], 0.0);
+  }
+};
+
+bool envelope_cholesky(Envelope& E) {
+  for (int i = 0; i < E.n; ++i) {
+    double* ri = E.row(i);
+    for (int j = E.first[i]; j <= i; ++j) {
+      const double* rj = E.row(j);
+      double s = ri[j];
+      for (int k = std::max(E.first[i], E.first[j]); k < j; ++k) s -= ri[k] * rj[k];
+      if (j < i) ri[j] = s / rj[j];
+      else { if (!(s > 0.0) || !std::isfinite(s)) return false; ri[i] = std::sqrt(s); }
+    }
+  }
+  return true;
+}
+void envelope_solve(const Envelope& E, double* b) {
+  for (int i = 0; i < E.n; ++i) { const double* ri = E.row(i); double s = b[i]; for (int k = E.first[i]; k < i; ++k) s -= ri[k] * b[k]; b[i] = s / ri[i]; }
+  for (int i = E.n - 1; i >= 0; --i) { const double* ri = E.row(i); const double x = b[i] / ri[i]; b[i] = x; for (int k = E.first[i]; k < i; ++k) b[k] -= ri[k] * x; }
+}
+
+// the same damped Schur complement as schur(), accumulated into the envelope (lower triangle only)
+bool schur_envelope(const Problem& P, const Adjacency& A, const Blocks& B, const std::vector<int>& fc, int Nf,
+                    const double* Dc, const double* Dp, Envelope* E, std::vector<double>* rhs, std::vector<double>* Vinv) {
+  const int n = 6 * Nf;
+  std::fill(E->v.begin(), E->v.end(), 0.0);
+  rhs->assign(n, 0.0); Vinv->assign((size_t)P.Np * 9, 0.0);
+  for (int c = 0; c < P.Nc; ++c) {
+    if (fc[c] < 0) continue;
+    const int o = 6 * fc[c];
+    for (int i = 0; i < 6; ++i) {
+      for (int j = 0; j <= i; ++j) E->row(o + i)[o + j] = B.U[(size_t)c * 36 + i * 6 + j];
+      E->row(o + i)[o + i] += Dc[6 * c + i];
+      (*rhs)[o + i] = -B.gc[6 * c + i];
+    }
+  }
+  bool ok = true;
+#pragma omp parallel for schedule(static)
+  for (int p = 0; p < P.Np; ++p) {
+    double M[9];
+    for (int i = 0; i < 9; ++i) M[i] = B.V[(size_t)p * 9 + i];
+    for (int i = 0; i < 3; ++i) M[i * 4] += Dp[3 * p + i];
+    if (!invert_spd3(M, &(*Vinv)[(size_t)p * 9])) {
+#pragma omp atomic write
+      ok = false;
+    }
+  }
+  if (!ok) return false;
+  int nthreads = 1;
+#ifdef _OPENMP
+  nthreads = omp_get_max_threads();
+#endif
+  if (E->v.size() * (size_t)nthreads > (size_t)1 << 27) nthreads = 1;
+  std::vector<Envelope> Ep(nthreads, *E);
+  std::vector<std::vector<double>> rp(nthreads);
+#pragma omp parallel num_threads(nthreads)
+  {
+    int t = 0;
+#ifdef _OPENMP
+    t = omp_get_thread_num();
+#endif
+    Envelope& El = Ep[t]; std::vector<double>& rl = rp[t];
+    std::fill(El.v.begin(), El.v.end(), 0.0); rl.assign(n, 0.0);
+#pragma omp for schedule(static)
+    for (int p = 0; p < P.Np; ++p) {
+      const double* Vi = &(*Vinv)[(size_t)p * 9];
+      const double* gp = &B.gp[(size_t)p * 3];
+      double tp[3];
+      for (int i = 0; i < 3; ++i) tp[i] = Vi[i * 3] * gp[0] + Vi[i * 3 + 1] * gp[1] + Vi[i * 3 + 2] * gp[2];
+      for (int ea = A.pt_off[p]; ea < A.pt_off[p + 1]; ++ea) {
+        const int ka = A.pt_obs[ea]; const int fa = fc[P.obs_cam[ka]];
+        if (fa < 0) continue;
+        const double* Wa = &B.W[(size_t)ka * 18];
+        double Y[18];
+        for (int i = 0; i < 6; ++i) for (int j = 0; j < 3; ++j)
+          Y[i * 3 + j] = Wa[i * 3] * Vi[j] + Wa[i * 3 + 1] * Vi[3 + j] + Wa[i * 3 + 2] * Vi[6 + j];
+        for (int i = 0; i < 6; ++i) rl[6 * fa + i] += Wa[i * 3] * tp[0] + Wa[i * 3 + 1] * tp[1] + Wa[i * 3 + 2] * tp[2];
+        for (int eb = A.pt_off[p]; eb < A.pt_off[p + 1]; ++eb) {
+          const int kb = A.pt_obs[eb]; const int fb = fc[P.obs_cam[kb]];
+          if (fb < 0 || fb > fa) continue;                      // lower triangle
+          const double* Wb = &B.W[(size_t)kb * 18];
+          for (int i = 0; i < 6; ++i) {
+            double* r = El.row(6 * fa + i);
+            const int jmax = (fb == fa) ? i : 5;
+            for (int j = 0; j <= jmax; ++j) r[6 * fb + j] -= Y[i * 3] * Wb[j * 3] + Y[i * 3 + 1] * Wb[j * 3 + 1] + Y[i * 3 + 2] * Wb[j * 3 + 2];
+          }
+        }
+      }
+    }
+  }
+  for (int t = 0; t < nthreads; ++t) {
+    for (size_t i = 0; i < E->v.size(); ++i) E->v[i] += Ep[t].v[i];
+    for (int i = 0; i < n; ++i) (*rhs)[i] += rp[t][i];
+  }
+  return true;
+}
+
+// reduced systems above this size go through the envelope (ORACLE_ENVELOPE=1 / 0 forces it on / off: tests)
+inline bool use_envelope(int n) {
+  if (const char* e = std::getenv("ORACLE_ENVELOPE")) return std::atoi(e) != 0;
+  return n > 1500;
+}
+
 // ---- polynomial interpolation for the Armijo line search (ceres/polynomial.cc + line_search.cc restated) ----
 // FunctionSample: value always valid here; gradient = directional derivative along the search direction.
 struct Sample { double x, f, g; bool has_g; };
@@ -778,6 +907,9 @@ int oracle_solve(int Nc, int Np, int Nobs, double* poses, double* points, const 
   double gmax = gradient_max_norm();
   if (gmax <= opt->gradient_tolerance) { term = 0; reason = 3; }
   std::vector<double> Dc(nc6), Dp(np3), S, rhs, Vinv, dc(nc6), dp(np3), cposes(nc6), cpoints(np3);
+  const bool envelope = use_envelope(6 * Nf);
+  Envelope E;
+  if (envelope) E.build(P, A, fc, Nf);
   int iter = 0;
   while (term == 1) {
     if (iter >= opt->max_iterations) { reason = 4; break; }
@@ -790,12 +922,21 @@ int oracle_solve(int Nc, int Np, int Nobs, double* poses, double* points, const 
     for (size_t p = 0; p < (size_t)Np; ++p) for (int i = 0; i < 3; ++i)
       Dp[3 * p + i] = clampd(sc2p[3 * p + i] * B.V[p * 9 + i * 4], 1e-6, 1e32) / (sc2p[3 * p + i] * radius);
     auto ts = clk::now();
-    bool ok = schur(P, A, B, fc, Nf, Dc.data(), Dp.data(), &S, &rhs, &Vinv);
-    sum->time_schur_s += secs(ts, clk::now());
-    auto tv = clk::now();
     const int n = 6 * Nf;
-    if (ok && n > 0) { ok = cholesky(S, n); if (ok) cholesky_solve(S, n, rhs.data()); }
-    sum->time_solve_s += secs(tv, clk::now());
+    bool ok;
+    if (envelope) {
+      ok = schur_envelope(P, A, B, fc, Nf, Dc.data(), Dp.data(), &E, &rhs, &Vinv);
+      sum->time_schur_s += secs(ts, clk::now());
+      auto tv = clk::now();
+      if (ok && n > 0) { ok = envelope_cholesky(E); if (ok) envelope_solve(E, rhs.data()); }
+      sum->time_solve_s += secs(tv, clk::now());
+    } else {
+      ok = schur(P, A, B, fc, Nf, Dc.data(), Dp.data(), &S, &rhs, &Vinv);
+      sum->time_schur_s += secs(ts, clk::now());
+      auto tv = clk::now();
+      if (ok && n > 0) { ok = cholesky(S, n); if (ok) cholesky_solve(S, n, rhs.data()); }
+      sum->time_solve_s += secs(tv, clk::now());
+    }
     double model_change = 0.0;
     if (ok) {
       std::fill(dc.begin(), dc.end(), 0.0);

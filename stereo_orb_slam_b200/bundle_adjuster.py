@@ -73,7 +73,8 @@ def pose_to_matrix(pose):
 class BundleAdjuster:
     """Drop-in for the reference class.  `options` defaults to the reference's solver configuration
     (src/bundle_adjuster.cpp:14-36); the reference ignores the solve status and always writes back —
-    so does Optimize(), except on hard errors (CUDA / invalid input / non-finite cost), which raise."""
+    so does Optimize(), numerical failures included (last accepted state; see last_summary["status"]); only
+    hard errors (CUDA / NCCL / invalid input) raise."""
 
     def __init__(self, smap, device=0, options=None):
         self.map = smap

@@ -18,6 +18,8 @@
 #include "kernels.cuh"
 #include "sba_comm.h"
 #include "sba_internal.h"
+#include "sparse_chol.cuh"
+#include "sparse_chol.h"
 
 using namespace sba;
 
@@ -54,6 +56,7 @@ struct sba_handle_s {
   int32_t shard_begin = -1, shard_end = -1;
   Dev d{};
   DevParams P{};
+  cudaMemPool_t pool = nullptr;       // the handle's own stream-ordered pool (no process-wide side effects)
   std::vector<void*> allocs;          // structure + work buffers (freed on re-structure)
   float4* uv_in = nullptr;            // staging for the caller-ordered observations
   double* r_dbg = nullptr;
@@ -73,6 +76,8 @@ struct sba_handle_s {
   bool chol_ok = false, chol_in_smem = false; size_t chol_smem = 0; int chol_threads = kCholThreads;   // one CTA per window factors S exactly (k_chol_window)
   bool chol_cluster_ok = false; size_t chol_cluster_smem = 0;   // mid-size windows: one 8-CTA cluster per window (k_chol_cluster)
   size_t lin_smem = 0, schur_smem = 0;   // dynamic shared memory of the per-chunk kernels (largest chunk)
+  // exact block-sparse Cholesky of the reduced system for windows of more than kCholMaxCams free cameras (k_spchol)
+  SparseCholSymbolic sym; bool sym_ok = false; SpCholDev sp{}; bool spchol_ok = false; int spchol_blocks = 0; double time_symbolic_s = 0.0;
 
   template <typename T>
   int alloc(T** p, size_t n) {
@@ -81,7 +86,7 @@ struct sba_handle_s {
     void* q = nullptr;
     // stream-ordered pool: after the first solve a re-structure (every BundleAdjuster::Optimize call) reuses the
     // pool's cached blocks instead of paying ~100 cudaMalloc/cudaFree round trips
-    cudaError_t e = cudaMallocAsync(&q, n * sizeof(T), stream);
+    cudaError_t e = pool ? cudaMallocFromPoolAsync(&q, n * sizeof(T), pool, stream) : cudaMallocAsync(&q, n * sizeof(T), stream);
     if (e != cudaSuccess) { set_error(std::string("cudaMallocAsync: ") + cudaGetErrorString(e)); return SBA_CUDA_ERROR; }
     allocs.push_back(q);
     *p = static_cast<T*>(q);
@@ -159,12 +164,22 @@ int sba_create(int device, sba_handle* out) {
         h->coop_blocks = per_sm * sms;
       if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_coop, kThreads, 0) == cudaSuccess)
         h->coop_pcg_blocks = per_sm * sms;
+      if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_spchol, kSpThreads, 0) == cudaSuccess)
+        h->spchol_blocks = std::min(per_sm, 2) * sms;
     }
-    if (e == cudaSuccess) {      // keep freed blocks in the device's default pool (no trim at synchronisation points)
-      cudaMemPool_t pool = nullptr;
-      if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+    if (e == cudaSuccess) {      // a private pool that keeps its freed blocks (no trim at synchronisation points): a
+                                 // re-structure on the next Optimize call reuses them; the device's default pool is untouched
+      cudaMemPoolProps props = {};
+      props.allocType = cudaMemAllocationTypePinned;
+      props.handleTypes = cudaMemHandleTypeNone;
+      props.location.type = cudaMemLocationTypeDevice;
+      props.location.id = device;
+      if (cudaMemPoolCreate(&h->pool, &props) == cudaSuccess) {
         unsigned long long keep = ~0ull;
-        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        cudaMemPoolSetAttribute(h->pool, cudaMemPoolAttrReleaseThreshold, &keep);
+      } else {
+        h->pool = nullptr;       // falls back to the default pool with its default (trimming) threshold
+        cudaGetLastError();
       }
     }
     if (e == cudaSuccess) e = cudaMallocHost((void**)&h->h_counters, 8 * sizeof(int32_t));
@@ -186,6 +201,7 @@ void sba_destroy(sba_handle h) {
     h->comm.destroy();
     h->free_all();
     if (h->stream) cudaStreamSynchronize(h->stream);     // the frees above are stream-ordered
+    if (h->pool) cudaMemPoolDestroy(h->pool);
     for (int i = 0; i < 8; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     if (h->h_counters) cudaFreeHost(h->h_counters);
     if (h->side) cudaStreamDestroy(h->side);
@@ -214,6 +230,20 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   if (!err.empty()) { set_error("sba_set_structure: " + err); return SBA_INVALID_ARGUMENT; }
   h->nobs_all = Nobs;
   h->has_structure = true;
+  h->sym_ok = false; h->sym = SparseCholSymbolic();
+  {
+    // windows of more than kCholMaxCams free cameras (global BA): symbolic phase of the exact block-sparse Cholesky —
+    // nested-dissection ordering, elimination-tree levels, static update lists — once per structure
+    int nf_max = 0;
+    for (int w = 0; w < h->H.nwin; ++w) nf_max = std::max(nf_max, h->H.win_fc_off[w + 1] - h->H.win_fc_off[w]);
+    if (h->H.Nf > 0 && (nf_max > kCholMaxCams || std::getenv("SBA_FORCE_SPARSE_CHOL")) && !std::getenv("SBA_NO_SPARSE_CHOL")) {
+      const auto ts = std::chrono::steady_clock::now();
+      const std::string serr = sparse_chol_symbolic(h->H.Nf, h->H.blk_row, h->H.blk_col, (int64_t)256 << 20, &h->sym);
+      h->time_symbolic_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - ts).count();
+      h->sym_ok = serr.empty();
+      if (!h->sym_ok && std::getenv("SBA_TIMING")) std::fprintf(stderr, "[sba] sparse Cholesky unavailable: %s\n", serr.c_str());
+    }
+  }
   h->time_structure_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   if (h->device < 0) return SBA_OK;
   const double t_host = h->time_structure_s;
@@ -252,7 +282,8 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   AL(d.w_radius, nw) AL(d.w_decf, nw) AL(d.w_cost, nw) AL(d.w_gmax, nw)
   AL(d.w_gd, nw * 4)   // one block: a multi-GPU solve all-reduces the four step scalars in one call
   d.w_dDd = d.w_gd + nw; d.w_x2 = d.w_gd + 2 * nw; d.w_dr = d.w_gd + 3 * nw;
-  AL(d.w_dmax, nw) AL(d.w_ls_red, nw * 3) AL(d.w_step2, nw) AL(d.w_cand, nw)
+  AL(d.w_dmax, nw + 1)   // + one slot: the ranks' agreed time-out flag
+  AL(d.w_ls_red, nw * 3) AL(d.w_step2, nw) AL(d.w_cand, nw)
   AL(d.w_ls_x, nw) AL(d.w_ls_px, nw) AL(d.w_ls_pf, nw) AL(d.w_ls_pg, nw)
   AL(d.w_ls_state, nw) AL(d.w_ls_it, nw) AL(d.w_ls_pvalid, nw)
   AL(d.w_rz, nw) AL(d.w_rz0, nw) AL(d.w_pAp, nw) AL(d.w_alpha, nw) AL(d.w_beta, nw)
@@ -349,6 +380,34 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
                          h->chol_cluster_smem <= (size_t)220 * 1024 && !std::getenv("SBA_NO_CLUSTER");
     if (h->chol_cluster_ok)
       CUDA_TRY(cudaFuncSetAttribute(k_chol_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->chol_cluster_smem, 1024)));
+  }
+  h->spchol_ok = false; h->sp = SpCholDev{};
+  if (h->sym_ok && h->spchol_blocks > 0 && (!h->chol_ok || std::getenv("SBA_FORCE_SPARSE_CHOL"))) {
+    {
+      const SparseCholSymbolic& Y = h->sym;
+      SpCholDev& sp = h->sp;
+      sp.n = Y.n; sp.nlev = Y.nlev; sp.nnzL = (int32_t)Y.nnzL();
+      if ((rc = h->upload(&sp.perm, Y.perm))) return rc;
+      if ((rc = h->upload(&sp.col_ptr, Y.col_ptr))) return rc;
+      if ((rc = h->upload(&sp.row_idx, Y.row_idx))) return rc;
+      if ((rc = h->upload(&sp.init_src, Y.init_src))) return rc;
+      if ((rc = h->upload(&sp.upd_ptr, Y.upd_ptr))) return rc;
+      if ((rc = h->upload(&sp.upd_a, Y.upd_a))) return rc;
+      if ((rc = h->upload(&sp.upd_b, Y.upd_b))) return rc;
+      if ((rc = h->upload(&sp.rowl_ptr, Y.rowl_ptr))) return rc;
+      if ((rc = h->upload(&sp.rowl_blk, Y.rowl_blk))) return rc;
+      if ((rc = h->upload(&sp.rowl_col, Y.rowl_col))) return rc;
+      if ((rc = h->upload(&sp.lvl_ptr, Y.lvl_ptr))) return rc;
+      if ((rc = h->upload(&sp.lvl_cols, Y.lvl_cols))) return rc;
+      if ((rc = h->alloc(&sp.Lv, (size_t)Y.nnzL() * 36))) return rc;
+      if ((rc = h->alloc(&sp.Li, (size_t)Y.n * 36))) return rc;
+      if ((rc = h->alloc(&sp.y, (size_t)Y.n * 6))) return rc;
+      CUDA_TRY(cudaStreamSynchronize(h->stream));
+      h->spchol_ok = true;
+      if (std::getenv("SBA_TIMING"))
+        std::fprintf(stderr, "[sba] sparse Cholesky symbolic: %.3f ms, %d block columns, %lld blocks in L (%lld in S), %lld products, %d levels\n",
+                     1e3 * h->time_symbolic_s, Y.n, (long long)Y.nnzL(), (long long)H.blk_row.size(), (long long)Y.nupd(), Y.nlev);
+    }
   }
   h->time_structure_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   if (std::getenv("SBA_TIMING"))
@@ -512,8 +571,19 @@ static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
   const DevParams& P = h->P;
   int it = 0;
   const bool force_coop = std::getenv("SBA_FORCE_COOP_PCG") != nullptr && d.nwin == 1 && h->coop_pcg_blocks > 0;
-  if (opt->linear_solver == 2 && !h->chol_ok) { set_error("linear_solver = Cholesky needs windows of at most 64 free cameras"); return SBA_INVALID_ARGUMENT; }
-  if (d.Nf > 0 && h->chol_ok && opt->linear_solver != 1) {
+  const bool force_sparse = std::getenv("SBA_FORCE_SPARSE_CHOL") != nullptr && h->spchol_ok;
+  if (opt->linear_solver == 2 && !h->chol_ok && !h->spchol_ok) { set_error("linear_solver = Cholesky: no exact factorisation available for this structure"); return SBA_INVALID_ARGUMENT; }
+  if (d.Nf > 0 && opt->linear_solver != 1 && h->spchol_ok && (force_sparse || !h->chol_ok)) {
+    // more than 64 free cameras in a window: the exact block-sparse Cholesky, one cooperative launch
+    CUDA_TRY(cudaMemsetAsync(d.counters + 4, 0, 4, h->stream));
+    int grid = std::max(1, h->spchol_blocks);
+    if (const char* e = std::getenv("SBA_SPCHOL_GRID")) grid = std::max(1, std::min(grid, std::atoi(e)));   // tuning aid
+    Dev dd = d; SpCholDev ss = h->sp;
+    void* args[] = {&dd, &ss};
+    CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_spchol, dim3(grid), dim3(kSpThreads), args, 0, h->stream));
+    h->launches++;
+    it = -1;
+  } else if (d.Nf > 0 && h->chol_ok && opt->linear_solver != 1) {
     CUDA_TRY(cudaMemsetAsync(d.counters + 4, 0, 4, h->stream));
     if (h->chol_cluster_ok) {
       cudaLaunchConfig_t cfg = {};
@@ -823,7 +893,18 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
   int running = d.nwin;
   int ls_rounds = 0;
   for (int iter = 0; running > 0 && iter < o.max_iterations; ++iter) {
-    if (o.max_time_s > 0.0 && secs(t0) >= o.max_time_s) {
+    bool timed_out = o.max_time_s > 0.0 && secs(t0) >= o.max_time_s;
+    if (o.max_time_s > 0.0 && h->comm.active()) {
+      // every other LM decision is bit-identical on all ranks; the wall clock is not, and a rank that stops alone
+      // would leave its peers inside an all-reduce: the ranks agree on the flag (max) before anybody acts on it
+      double flag = timed_out ? 1.0 : 0.0;
+      CUDA_TRY(cudaMemcpyAsync(d.w_dmax + d.nwin, &flag, 8, cudaMemcpyHostToDevice, h->stream));
+      { std::string _err; if (!h->comm.allreduce(d.w_dmax + d.nwin, 1, true, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; } }
+      CUDA_TRY(cudaMemcpyAsync(&flag, d.w_dmax + d.nwin, 8, cudaMemcpyDeviceToHost, h->stream));
+      CUDA_TRY(cudaStreamSynchronize(h->stream));
+      timed_out = flag != 0.0;
+    }
+    if (timed_out) {
       if ((rc = join_tail(h))) return rc;
       LAUNCH(h, k_lm_timeout, cdiv(d.nwin, 128), 128, d);
       break;
@@ -914,7 +995,10 @@ int sba_solve(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, double* poses,
   const auto t2 = clk::now();
   sba_summary S;
   const int run_rc = sba_run(h, opt, &S);
-  if (run_rc != SBA_OK && run_rc != SBA_NO_CONVERGENCE) return run_rc;   // inputs untouched
+  // The reference never looks at Ceres' termination type and always writes back the last accepted state, also after
+  // FAILURE (src/bundle_adjuster.cpp:116-132): a numerical failure (5 invalid steps in a row, non-finite cost) still
+  // returns the last accepted state (candidates are only applied on acceptance) together with its status.
+  if (run_rc != SBA_OK && run_rc != SBA_NO_CONVERGENCE && run_rc != SBA_NUMERICAL_FAILURE) return run_rc;   // inputs untouched
   const auto t3 = clk::now();
   if ((rc = sba_get_state(h, poses, points))) return rc;
   const auto t4 = clk::now();
@@ -1024,6 +1108,19 @@ int sba_get_sorted_views(sba_handle h, int32_t* by_point, int32_t* by_camera) {
     for (int c = 0; c < H.Nc; ++c) off[c + 1] += off[c];
     for (int64_t e = 0; e < H.Nobs; ++e) by_camera[off[H.pcam[e]]++] = H.perm_p[e];
   }
+  return SBA_OK;
+}
+
+int sba_get_factor_symbolic(sba_handle h, int64_t info[4], int32_t* perm, int32_t* col_ptr, int32_t* row_idx,
+                            int32_t* init_src, int64_t* upd_ptr, int32_t* upd_a, int32_t* upd_b, int32_t* lvl_ptr,
+                            int32_t* lvl_cols) {
+  if (!h || !h->has_structure) { set_error("no structure"); return SBA_INVALID_ARGUMENT; }
+  if (!h->sym_ok) { set_error("this structure has no sparse factorisation (every window has <= 64 free cameras, or the pattern is too dense)"); return SBA_INVALID_ARGUMENT; }
+  const SparseCholSymbolic& Y = h->sym;
+  if (info) { info[0] = Y.n; info[1] = Y.nnzL(); info[2] = Y.nupd(); info[3] = Y.nlev; }
+  auto cp = [](auto* dst, const auto& v) { if (dst && !v.empty()) std::memcpy(dst, v.data(), v.size() * sizeof(v[0])); };
+  cp(perm, Y.perm); cp(col_ptr, Y.col_ptr); cp(row_idx, Y.row_idx); cp(init_src, Y.init_src); cp(upd_ptr, Y.upd_ptr);
+  cp(upd_a, Y.upd_a); cp(upd_b, Y.upd_b); cp(lvl_ptr, Y.lvl_ptr); cp(lvl_cols, Y.lvl_cols);
   return SBA_OK;
 }
 

@@ -1,0 +1,212 @@
+// sparse_chol.cuh — numeric phase of the exact block-sparse Cholesky of the reduced camera matrix (sm_100a, fp64).
+//
+// The reference factors the reduced camera system exactly (Ceres SPARSE_SCHUR + CHOLMOD, src/bundle_adjuster.cpp:
+// 26-29).  For the global BA calls (src/slam.cpp:156, src/pose_graph_optimizer.cpp:95: thousands of free cameras,
+// banded co-visibility + loop-closure blocks) the whole solve S x = rhs is ONE cooperative launch:
+//   0  scatter the blocks of S into the (nested-dissection ordered) pattern of L
+//   1  elimination-tree levels, leaves first, one grid barrier per level; a CTA per block column j (left-looking):
+//        every block (i, j) gathers its static list of products  L_ik L_jk^T  on the FP64 tensor cores (two m8n8k4
+//        MMAs per product, operands straight from L2), the right-hand side gathers  sum_k L_jk y_k  alongside;
+//        then the 6x6 diagonal factor + its inverse, the panel  L_ij = A_ij Linv_jj^T  and  y_j = Linv_jj t_j
+//   2  the same levels downwards, a warp per column:  x_j = Linv_jj^T (y_j - sum_i L_ij^T x_i)
+// One writer per block, every sum in list order: bit-reproducible, no atomics.  Symbolic phase: sparse_chol.cpp.
+#pragma once
+#include <cooperative_groups.h>
+#include "kernels.cuh"
+
+namespace sba {
+
+struct SpCholDev {
+  int32_t n, nlev, nnzL;
+  const int32_t *perm, *col_ptr, *row_idx, *init_src;
+  const int64_t* upd_ptr;
+  const int32_t *upd_a, *upd_b;
+  const int32_t *rowl_ptr, *rowl_blk, *rowl_col, *lvl_ptr, *lvl_cols;
+  double* Lv;     // [nnzL * 36] blocks of L, row-major 6x6 (block (i, j): rows of i, columns of j)
+  double* Li;     // [n * 36]    inverse diagonal factors (lower)
+  double* y;      // [n * 6]     forward-substituted right-hand side, then the solution (new order)
+};
+
+constexpr int kSpThreads = 256;
+constexpr int kSpWarps = kSpThreads / 32;
+constexpr int kSpStage = 48;      // blocks of one column staged in shared memory between gather and panel (13.5 KB)
+
+__global__ void __launch_bounds__(kSpThreads) k_spchol(Dev d, SpCholDev sc) {
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  __shared__ double col_st[kSpStage * 36];
+  __shared__ double akk[36], li_s[36], tj[8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (d.nwin == 1 && (d.w_status[0] != 0 || d.w_fail[0] != 0)) {     // uniform over the grid; leaves x untouched (unused)
+    if (blockIdx.x == 0 && tid == 0) d.w_pcg_it[0] = 0;
+    return;
+  }
+  // ---- 0: scatter S into the pattern of L
+  {
+    const int64_t tot = (int64_t)sc.nnzL * 36;
+    for (int64_t idx = (int64_t)blockIdx.x * kSpThreads + tid; idx < tot; idx += (int64_t)gridDim.x * kSpThreads) {
+      const int b = (int)(idx / 36), e = (int)(idx - 36 * (int64_t)b);
+      const int src = __ldg(sc.init_src + b);
+      double v = 0.0;
+      if (src >= 0) v = d.Su[(size_t)src * 36 + e];
+      else if (src != INT32_MIN) { const int r = e / 6, c = e - 6 * r; v = d.Su[(size_t)(~src) * 36 + 6 * c + r]; }
+      __stcg(sc.Lv + idx, v);
+    }
+    for (int w = blockIdx.x * kSpThreads + tid; w < d.nwin; w += gridDim.x * kSpThreads) d.w_pcg_it[w] = 0;
+  }
+  grid.sync();
+  // ---- 1: factorisation + forward substitution, level by level
+  const int g = lane >> 2, t4 = lane & 3;
+  const bool f0 = g < 6, f1 = g < 6 && t4 < 2;
+  const int o0 = 6 * (f0 ? g : 0) + t4, o1 = 6 * (f1 ? g : 0) + (f1 ? t4 + 4 : 0);
+  const int ps = lane / 6, ri = lane - 6 * ps;
+  for (int lvl = 0; lvl < sc.nlev; ++lvl) {
+    const int c_begin = __ldg(sc.lvl_ptr + lvl), c_end = __ldg(sc.lvl_ptr + lvl + 1);
+    for (int ci = c_begin + blockIdx.x; ci < c_end; ci += gridDim.x) {
+      const int j = __ldg(sc.lvl_cols + ci);
+      const int b0 = __ldg(sc.col_ptr + j), nb = __ldg(sc.col_ptr + j + 1) - b0;
+      const bool staged = nb <= kSpStage;
+      // (a) gather: block = A_ij - sum_k L_ik L_jk^T, one warp per block, products in list order on two
+      //     accumulator chains; update indices come 32 at a time by one coalesced load and are handed round
+      for (int bi = warp; bi < nb; bi += kSpWarps) {
+        const int blk = b0 + bi;
+        const int64_t u0 = sc.upd_ptr[blk], u1 = sc.upd_ptr[blk + 1];
+        double c0 = 0.0, c1 = 0.0, e0 = 0.0, e1 = 0.0;
+        for (int64_t ub = u0; ub < u1; ub += 32) {
+          const int m = (int)min((int64_t)32, u1 - ub);
+          const int ia = (lane < m) ? __ldg(sc.upd_a + ub + lane) : 0;
+          const int ib = (lane < m) ? __ldg(sc.upd_b + ub + lane) : 0;
+          int u = 0;
+          for (; u + 1 < m; u += 2) {
+            const double* A0 = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ia, u) * 36;
+            const double* B0 = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ib, u) * 36;
+            const double* A1 = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ia, u + 1) * 36;
+            const double* B1 = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ib, u + 1) * 36;
+            const double a00 = f0 ? __ldcg(A0 + o0) : 0.0, b00 = f0 ? __ldcg(B0 + o0) : 0.0;
+            const double a01 = f1 ? __ldcg(A0 + o1) : 0.0, b01 = f1 ? __ldcg(B0 + o1) : 0.0;
+            const double a10 = f0 ? __ldcg(A1 + o0) : 0.0, b10 = f0 ? __ldcg(B1 + o0) : 0.0;
+            const double a11 = f1 ? __ldcg(A1 + o1) : 0.0, b11 = f1 ? __ldcg(B1 + o1) : 0.0;
+            dmma884(c0, c1, a00, b00); dmma884(c0, c1, a01, b01);
+            dmma884(e0, e1, a10, b10); dmma884(e0, e1, a11, b11);
+          }
+          if (u < m) {
+            const double* A0 = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ia, u) * 36;
+            const double* B0 = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ib, u) * 36;
+            const double a00 = f0 ? __ldcg(A0 + o0) : 0.0, b00 = f0 ? __ldcg(B0 + o0) : 0.0;
+            const double a01 = f1 ? __ldcg(A0 + o1) : 0.0, b01 = f1 ? __ldcg(B0 + o1) : 0.0;
+            dmma884(c0, c1, a00, b00); dmma884(c0, c1, a01, b01);
+          }
+        }
+        if (f0 && t4 < 3) {
+          const int e = 6 * g + 2 * t4;
+          const double2 a = __ldcg(reinterpret_cast<const double2*>(sc.Lv + (size_t)blk * 36 + e));
+          const double2 v = make_double2(a.x - (c0 + e0), a.y - (c1 + e1));
+          if (bi == 0) { akk[e] = v.x; akk[e + 1] = v.y; }
+          else if (staged) { col_st[bi * 36 + e] = v.x; col_st[bi * 36 + e + 1] = v.y; }
+          else __stcg(reinterpret_cast<double2*>(sc.Lv + (size_t)blk * 36 + e), v);
+        }
+      }
+      // (b) right-hand side: t_j = rhs_j - sum_k L_jk y_k  (last warp; five entry groups of six rows, summed in lane order)
+      if (warp == kSpWarps - 1) {
+        double acc = 0.0;
+        if (lane < 30) {
+          const int r1 = __ldg(sc.rowl_ptr + j + 1);
+          for (int e = __ldg(sc.rowl_ptr + j) + ps; e < r1; e += 5) {
+            const double* L = sc.Lv + (size_t)__ldg(sc.rowl_blk + e) * 36 + 6 * ri;
+            const double* yk = sc.y + (size_t)__ldg(sc.rowl_col + e) * 6;
+            acc += (__ldcg(L) * __ldcg(yk) + __ldcg(L + 1) * __ldcg(yk + 1) + __ldcg(L + 2) * __ldcg(yk + 2)) +
+                   (__ldcg(L + 3) * __ldcg(yk + 3) + __ldcg(L + 4) * __ldcg(yk + 4) + __ldcg(L + 5) * __ldcg(yk + 5));
+          }
+        }
+        double tot = acc;
+#pragma unroll
+        for (int q = 1; q < 5; ++q) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * q) & 31);
+        if (lane < 6) tj[lane] = d.rhs[(size_t)__ldg(sc.perm + j) * 6 + lane] - tot;
+      }
+      __syncthreads();
+      // (c) diagonal block: factor, keep the inverse of the factor
+      if (tid == 0) {
+        double li[36];
+        if (!chol6_inverse_factor(akk, li)) d.w_fail[d.fcam_win[__ldg(sc.perm + j)]] = 1;   // benign race: every writer stores 1
+#pragma unroll
+        for (int i = 0; i < 36; ++i) { li_s[i] = li[i]; __stcg(sc.Li + (size_t)j * 36 + i, li[i]); }
+      }
+      __syncthreads();
+      // (d) panel L_ij = A_ij Linv^T (i > j) and y_j = Linv t_j
+      if (staged) {
+        for (int idx = tid; idx < (nb - 1) * 36; idx += kSpThreads) {
+          const int bi = 1 + idx / 36, e = idx % 36, r = e / 6, c = e - 6 * r;
+          double acc = 0.0;
+#pragma unroll
+          for (int q = 0; q < 6; ++q) if (q <= c) acc += col_st[bi * 36 + 6 * r + q] * li_s[6 * c + q];
+          __stcg(sc.Lv + (size_t)(b0 + bi) * 36 + e, acc);
+        }
+      } else {
+        // long columns (dense patterns) stay in L2: a thread per block row, in place (it reads its row before it writes it)
+        for (int idx = tid; idx < (nb - 1) * 6; idx += kSpThreads) {
+          double* row = sc.Lv + (size_t)(b0 + 1 + idx / 6) * 36 + 6 * (idx % 6);
+          double a[6], o[6];
+#pragma unroll
+          for (int q = 0; q < 6; ++q) a[q] = __ldcg(row + q);
+#pragma unroll
+          for (int c = 0; c < 6; ++c) {
+            double acc = 0.0;
+#pragma unroll
+            for (int q = 0; q < 6; ++q) if (q <= c) acc += a[q] * li_s[6 * c + q];
+            o[c] = acc;
+          }
+#pragma unroll
+          for (int q = 0; q < 6; ++q) __stcg(row + q, o[q]);
+        }
+      }
+      if (tid >= kSpThreads - 6) {
+        const int c = tid - (kSpThreads - 6);
+        double acc = 0.0;
+#pragma unroll
+        for (int q = 0; q < 6; ++q) if (q <= c) acc += li_s[6 * c + q] * tj[q];
+        __stcg(sc.y + (size_t)j * 6 + c, acc);
+      }
+      __syncthreads();                          // shared buffers are reused by the CTA's next column
+    }
+    grid.sync();
+  }
+  // ---- 2: back substitution, levels downwards, a warp per column
+  const int gw = (blockIdx.x * kSpThreads + tid) >> 5, nw = (gridDim.x * kSpThreads) >> 5;
+  for (int lvl = sc.nlev - 1; lvl >= 0; --lvl) {
+    const int c_begin = __ldg(sc.lvl_ptr + lvl), c_end = __ldg(sc.lvl_ptr + lvl + 1);
+    for (int ci = c_begin + gw; ci < c_end; ci += nw) {
+      const int j = __ldg(sc.lvl_cols + ci);
+      const int b0 = __ldg(sc.col_ptr + j), b1 = __ldg(sc.col_ptr + j + 1);
+      double acc = 0.0;
+      if (lane < 30) {
+        for (int b = b0 + 1 + ps; b < b1; b += 5) {
+          const double* L = sc.Lv + (size_t)b * 36 + ri;                     // column ri of L_ij
+          const double* xi = sc.y + (size_t)__ldg(sc.row_idx + b) * 6;
+          acc += (__ldcg(L) * __ldcg(xi) + __ldcg(L + 6) * __ldcg(xi + 1) + __ldcg(L + 12) * __ldcg(xi + 2)) +
+                 (__ldcg(L + 18) * __ldcg(xi + 3) + __ldcg(L + 24) * __ldcg(xi + 4) + __ldcg(L + 30) * __ldcg(xi + 5));
+        }
+      }
+      double tot = acc;
+#pragma unroll
+      for (int q = 1; q < 5; ++q) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * q) & 31);
+      const double s = (lane < 6) ? __ldcg(sc.y + (size_t)j * 6 + lane) - tot : 0.0;
+      double v = 0.0;
+#pragma unroll
+      for (int q = 0; q < 6; ++q) {
+        const double sq = __shfl_sync(0xffffffffu, s, q);
+        if (lane < 6 && q >= lane) v += __ldcg(sc.Li + (size_t)j * 36 + 6 * q + lane) * sq;    // Linv^T
+      }
+      if (lane < 6) {
+        __stcg(sc.y + (size_t)j * 6 + lane, v);
+        const int f = __ldg(sc.perm + j);
+        const int w = d.fcam_win[f];
+        const bool ok = isfinite(v) && __ldcg(d.w_fail + w) == 0;
+        if (!isfinite(v)) d.w_fail[w] = 1;                                    // benign race: every writer stores 1
+        d.x[(size_t)f * 6 + lane] = ok ? v : 0.0;
+        d.r[(size_t)f * 6 + lane] = 0.0;                                      // exact solve: no linear residual in the model change
+      }
+    }
+    if (lvl > 0) grid.sync();
+  }
+}
+
+}  // namespace sba

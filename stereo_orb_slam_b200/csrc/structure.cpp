@@ -41,9 +41,12 @@ bool make_chunks(const HostStructure& H, const std::vector<int32_t>& gpt_off, in
       while (q < limit && q - p < kPointChunk) {
         const int k = gpt_off[q + 1] - gpt_off[q];
         if (k > kMaxSlots) { *err = "a point has more than 255 observations (unsupported track length)"; return false; }
-        if (nobs + k > obs_cap) break;
+        // a point never straddles chunks; one whose track alone exceeds the tuning cap (obs_cap < k <= 255) gets a
+        // chunk of its own — chunk-local indices are bytes and the per-observation kernels run 256 threads
+        if (nobs + k > obs_cap && q > p) break;
         nobs += k; ++q;
       }
+      if (q == p) { *err = "internal: empty chunk"; return false; }
       out->push_back(ChunkRange{p, q, w, owned});
       p = q;
     }

@@ -91,7 +91,7 @@ class Solver:
         s = capi.Summary()
         o = options if options is not None else capi.default_options()
         rc = self._L.sba_run(self._h, C.byref(o), C.byref(s))
-        capi.check(rc, ok=(capi.SBA_OK, capi.SBA_NO_CONVERGENCE))
+        capi.check(rc, ok=(capi.SBA_OK, capi.SBA_NO_CONVERGENCE, capi.SBA_NUMERICAL_FAILURE))
         out = s.as_dict(); out["status"] = rc
         return out
 
@@ -112,7 +112,8 @@ class Solver:
                                ptr(obs_cam, I32), ptr(obs_pt, I32), ptr(obs_uv, F), ptr(p_l, D), ptr(p_r, D),
                                ptr(cam_fixed, U8), I32(nwin), ptr(win_cam_off, I32), ptr(win_pt_off, I32),
                                C.byref(o), C.byref(s))
-        capi.check(rc, ok=(capi.SBA_OK, capi.SBA_NO_CONVERGENCE))
+        # like the reference, a numerical failure still returns the last accepted state (summary["status"] says so)
+        capi.check(rc, ok=(capi.SBA_OK, capi.SBA_NO_CONVERGENCE, capi.SBA_NUMERICAL_FAILURE))
         self.Nc, self.Np, self.Nobs, self.nwin = Nc, Np, int(obs_cam.size), nwin
         out = s.as_dict(); out["status"] = rc
         return poses.reshape(-1, 6), points.reshape(-1, 3), out
@@ -186,6 +187,21 @@ class Solver:
         bp = np.zeros(self.Nobs, np.int32); bc = np.zeros(self.Nobs, np.int32)
         capi.check(self._L.sba_get_sorted_views(self._h, ptr(bp, I32), ptr(bc, I32)))
         return bp, bc
+
+    def factor_symbolic(self):
+        """Symbolic phase of the block-sparse Cholesky (structures with a window of > 64 free cameras)."""
+        info = (C.c_int64 * 4)()
+        capi.check(self._L.sba_get_factor_symbolic(self._h, info, None, None, None, None, None, None, None, None, None))
+        n, nnz, nupd, nlev = (int(v) for v in info)
+        out = dict(n=n, nnzL=nnz, nupd=nupd, nlev=nlev, perm=np.zeros(n, np.int32), col_ptr=np.zeros(n + 1, np.int32),
+                   row_idx=np.zeros(nnz, np.int32), init_src=np.zeros(nnz, np.int32), upd_ptr=np.zeros(nnz + 1, np.int64),
+                   upd_a=np.zeros(nupd, np.int32), upd_b=np.zeros(nupd, np.int32), lvl_ptr=np.zeros(nlev + 1, np.int32),
+                   lvl_cols=np.zeros(n, np.int32))
+        capi.check(self._L.sba_get_factor_symbolic(
+            self._h, info, ptr(out["perm"], I32), ptr(out["col_ptr"], I32), ptr(out["row_idx"], I32), ptr(out["init_src"], I32),
+            ptr(out["upd_ptr"], I64), ptr(out["upd_a"], I32), ptr(out["upd_b"], I32), ptr(out["lvl_ptr"], I32),
+            ptr(out["lvl_cols"], I32)))
+        return out
 
     @property
     def num_free_cameras(self):

@@ -103,9 +103,20 @@ def _project(T_cw_R, T_cw_t, X, cam):
 
 def make_map(num_frames, num_points, track_len, seed, noise_px=0.5, outlier_frac=0.03,
              pose_sigma_t=0.05, pose_sigma_r=0.005, loop=False, loop_frames=0, cam=KITTI,
-             noise_free=False, depth_min=4.0, depth_max=80.0):
+             noise_free=False, depth_min=4.0, depth_max=80.0, vo_gates=True):
     """Generate a StereoMap.  `noise_free=True` gives the known-answer twin: exact measurements and a
-    perturbed start, so the optimum has cost ~ 0 (up to f32 storage of the pixels) at ground truth."""
+    perturbed start, so the optimum has cost ~ 0 (up to f32 storage of the pixels) at ground truth.
+
+    `vo_gates` (default): the map only holds what the reference's visual odometer lets through —
+      * a stereo keypoint pair enters a frame's container only if it triangulates to a depth in [0, 100] m (rectified
+        stereo: src/camera_model.cpp:219) and below fx*b (src/visual_odometer.cpp:137, MaxSensibleDistance :111-121);
+        that holds for the observation that creates a point and for every re-observation;
+      * a re-observation is a RANSAC inlier: 4-term stereo reprojection distance < 3 px
+        (ransac_solver/include/stereo_reprojection.h:96-133), so "outliers" are bounded: `outlier_frac` of the
+        re-observations get an extra error of 1.5-2.9 px (4-vector norm), well into Huber's linear range (delta = 1),
+        and anything at or beyond 3 px from the true projection is dropped.
+    `vo_gates=False` is the stress case the reference never sees: disparity clamped at 1 px (depth up to 386 m),
+    gross outliers of +-(10-50) px; weakly constrained points then run to the +-1e4 bound."""
     rng = np.random.default_rng(seed)
     gt = trajectory(num_frames, rng, loop=loop)
     R_wc, t_wc = gt[:, :3, :3], gt[:, :3, 3]
@@ -136,10 +147,22 @@ def make_map(num_frames, num_points, track_len, seed, noise_px=0.5, outlier_frac
     vis = (z > 0.5) & (z < cam["fx"] * cam["b"]) & (uv[:, 0] >= 0) & (uv[:, 0] < cam["width"]) & \
           (uv[:, 2] >= 0) & (uv[:, 2] < cam["width"]) & (uv[:, 1] >= 0) & (uv[:, 1] < cam["height"])
     fr, pid, uv = fr[vis], pid[vis], uv[vis]
-    # dense ids in order of first observation (frame, then candidate id), as VO::Update assigns them
-    seen = np.unique(pid)
     first_fr = np.full(over, num_frames, np.int64)
     np.minimum.at(first_fr, pid, fr)
+    # the measurement noise of every candidate's FIRST observation is drawn up front: that observation creates the
+    # point (reference 3.3), and whether the point exists at all depends on the depth it triangulates to
+    first_noise = np.zeros((over, 4)) if noise_free else rng.normal(0, noise_px, (over, 4))
+    if vo_gates:
+        is_first = fr == first_fr[pid]
+        m0 = (uv[is_first] + first_noise[pid[is_first]]).astype(np.float32).astype(np.float64)
+        disp = m0[:, 0] - m0[:, 2]
+        z0 = np.where(disp > 0, cam["fx"] * cam["b"] / np.where(disp > 0, disp, 1.0), np.inf)
+        created = np.zeros(over, bool)
+        created[pid[is_first]] = (z0 >= 0.0) & (z0 <= 100.0) & (z0 < cam["fx"] * cam["b"])
+        keep0 = created[pid]
+        fr, pid, uv = fr[keep0], pid[keep0], uv[keep0]
+    # dense ids in order of first observation (frame, then candidate id), as VO::Update assigns them
+    seen = np.unique(pid)
     if seen.size > num_points:   # uniform subsample (keeps every frame populated), then first-appearance order
         seen = np.sort(rng.choice(seen, num_points, replace=False))
     order = seen[np.lexsort((seen, first_fr[seen]))]
@@ -147,19 +170,39 @@ def make_map(num_frames, num_points, track_len, seed, noise_px=0.5, outlier_frac
     keep = new_id[pid] >= 0
     fr, pid, uv = fr[keep], new_id[pid[keep]], uv[keep]
     Xw = Xw[order]
+    first_noise = first_noise[order]
     # frame-major, point id ascending inside a frame
     o = np.lexsort((pid, fr))
     fr, pid, uv = fr[o], pid[o], uv[o]
     K = fr.size
     if not noise_free:
-        uv = uv + rng.normal(0, noise_px, (K, 4))
+        noise = rng.normal(0, noise_px, (K, 4))
         out = rng.random(K) < outlier_frac
         # a point's first observation creates it (reference §3.3: triangulated at creation), so it is
-        # never a gross outlier; later re-observations can be.
+        # never an outlier; later re-observations can be.
         fo = np.full(Xw.shape[0], K, np.int64); np.minimum.at(fo, pid, np.arange(K)); out[fo] = False
+        noise[fo] = first_noise
         nout = int(out.sum())
-        uv[out] += rng.uniform(10, 50, (nout, 4)) * rng.choice([-1.0, 1.0], (nout, 4))
+        if vo_gates:
+            # bounded outliers (RANSAC inliers by construction): error vector of norm 1.5 .. 2.9 px
+            dirs = rng.normal(0, 1, (nout, 4)); dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+            noise[out] = dirs * rng.uniform(1.5, 2.9, (nout, 1))
+        else:
+            noise[out] += rng.uniform(10, 50, (nout, 4)) * rng.choice([-1.0, 1.0], (nout, 4))
+        uv = uv + noise
+    else:
+        noise = np.zeros((K, 4))
     uv32 = uv.astype(np.float32)
+    if vo_gates:
+        # every observation is a stereo keypoint pair of the frame's container, which only holds pairs that triangulate
+        # inside the range (src/visual_odometer.cpp:137-143 after src/camera_model.cpp:219), and a re-observation is
+        # a RANSAC inlier (< 3 px, stereo_reprojection.h:96-133): anything else never reaches the map
+        dsp = uv32[:, 0].astype(np.float64) - uv32[:, 2].astype(np.float64)
+        okz = (dsp > 0) & (cam["fx"] * cam["b"] / np.where(dsp > 0, dsp, 1.0) <= 100.0)
+        okz &= (np.linalg.norm(noise, axis=1) < 3.0)
+        okz[fo if not noise_free else np.zeros(0, np.int64)] |= (dsp[fo] > 0) if not noise_free else False
+        fr, pid, uv, uv32 = fr[okz], pid[okz], uv[okz], uv32[okz]
+        K = fr.size
     frame_off = np.zeros(num_frames + 1, np.int64)
     np.add.at(frame_off, fr + 1, 1); frame_off = np.cumsum(frame_off)
 

@@ -38,6 +38,18 @@ def make_window(num_frames, num_points, track_len, seed, **kw):
     return w
 
 
+def batch_windows(ws):
+    """Independent windows concatenated into one batched problem (config 3 shape): dict with the flat arrays plus
+    win_cam_off / win_pt_off."""
+    cam_off = np.cumsum([0] + [w["poses"].shape[0] for w in ws]).astype(np.int32)
+    pt_off = np.cumsum([0] + [w["points"].shape[0] for w in ws]).astype(np.int32)
+    return dict(poses=np.concatenate([w["poses"] for w in ws]), points=np.concatenate([w["points"] for w in ws]),
+                obs_cam=np.concatenate([w["obs_cam"] + cam_off[i] for i, w in enumerate(ws)]).astype(np.int32),
+                obs_pt=np.concatenate([w["obs_pt"] + pt_off[i] for i, w in enumerate(ws)]).astype(np.int32),
+                obs_uv=np.concatenate([w["obs_uv"] for w in ws]), win_cam_off=cam_off, win_pt_off=pt_off,
+                p_l=ws[0]["p_l"], p_r=ws[0]["p_r"])
+
+
 @pytest.fixture(scope="session")
 def small_window():
     return make_window(8, 600, 5, seed=7)

@@ -8,7 +8,7 @@ import pytest
 
 from oracle import oracle
 from stereo_orb_slam_b200 import BundleAdjuster, Solver, _capi, default_options, pack_window, synthetic
-from conftest import make_window
+from conftest import batch_windows, make_window
 
 pytestmark = pytest.mark.gpu
 
@@ -97,15 +97,17 @@ def test_pcg_solves_the_reduced_system(small_window):
     assert np.abs(x - xs).max() <= 1e-8 * np.abs(xs).max()
 
 
-@pytest.mark.parametrize("path", ["cholesky", "cholesky_cluster", "window", "cluster", "multilaunch", "cooperative"])
+@pytest.mark.parametrize("path", ["cholesky", "cholesky_cluster", "cholesky_sparse", "window", "cluster", "multilaunch", "cooperative"])
 def test_every_linear_solver_path_solves_the_same_system(small_window, path, monkeypatch):
     """The reduced system goes through the block Cholesky (windows of <= 64 free cameras, the default there: one CTA
     per window, or one 8-CTA cluster per window from 16 cameras up) or one of four PCG
     paths depending on its size (one CTA per window, one 8-CTA cluster per window, one cooperative launch over the
     global block-CSR, or the multi-launch path); force each on the same small window."""
-    for k in ("SBA_NO_CLUSTER", "SBA_FORCE_CLUSTER", "SBA_FORCE_MULTILAUNCH", "SBA_FORCE_COOP_PCG", "SBA_NO_DIRECT"):
+    for k in ("SBA_NO_CLUSTER", "SBA_FORCE_CLUSTER", "SBA_FORCE_MULTILAUNCH", "SBA_FORCE_COOP_PCG", "SBA_NO_DIRECT", "SBA_FORCE_SPARSE_CHOL"):
         monkeypatch.delenv(k, raising=False)
-    if path in ("cluster", "cholesky_cluster"):
+    if path == "cholesky_sparse":       # the block-sparse factorisation of the global configs, forced on a small window
+        monkeypatch.setenv("SBA_FORCE_SPARSE_CHOL", "1")
+    elif path in ("cluster", "cholesky_cluster"):
         monkeypatch.setenv("SBA_FORCE_CLUSTER", "1")
     elif path == "multilaunch":
         monkeypatch.setenv("SBA_FORCE_MULTILAUNCH", "1")
@@ -162,7 +164,7 @@ def test_cooperative_pcg_is_bit_reproducible_on_a_global_problem():
     s.linearize(); s.schur(1e4)
     xs = []
     for _ in range(3):
-        it = s.pcg(default_options(max_pcg_iterations=200))
+        it = s.pcg(default_options(max_pcg_iterations=200, linear_solver=1))
         xs.append(s.schur_values()[2].copy())
         assert 0 < it <= 200
     assert np.array_equal(xs[0], xs[1]) and np.array_equal(xs[0], xs[2])
@@ -293,37 +295,146 @@ def test_bundle_adjuster_optimize_writes_back_like_the_reference():
     assert ba.Optimize(4, 4) is None                          # empty window: no-op
 
 
-def test_config2_full_size_properties():
-    """BASELINE.json configs[1] at full size (50 keyframes / 40k points / ~200k obs).
-
-    Up to iteration 16 the GPU and the oracle walk the same trajectory (costs agree to ~1e-12) and are compared at
-    the north_star tolerances.  After that this window sits in a flat valley with far points pinned at the +-1e4
-    bound (src/bundle_adjuster.cpp:104-108): every trust-region step is rejected, the projected line search
-    contracts to step sizes ~1e-11 where the cost change is below one ulp of the cost, and whether it then
-    "succeeds" (tiny step -> parameter tolerance -> stop at iteration 19, what the oracle happens to do) or "fails"
-    (full step kept, rejected, LM goes on) is decided by the last bit of a 200k-term sum — for any implementation,
-    Ceres included (trace in profiles/).  Past that point only size-independent properties are
-    asserted: the cost never increases, the reported cost is the oracle's cost function at the GPU's solution,
-    the gradient has collapsed, and a re-solve does not move uphill."""
-    smap = synthetic.make_config("C2")
+def c2_window(**kw):
+    smap = synthetic.make_config("C2", **kw)
     w = pack_window(smap, 0, smap.num_frames)
     w["p_l"], w["p_r"] = smap.p_l, smap.p_r
+    return w
+
+
+def test_config2_full_size_matches_oracle_at_termination():
+    """BASELINE.json configs[1] at full size (50 keyframes / 40k points / ~200k obs), generated under the reference's
+    own gates (points and observations its visual odometer would have dropped do not exist: src/camera_model.cpp:219,
+    src/visual_odometer.cpp:137, stereo_reprojection.h:96-133).  GPU and oracle are compared at the solver's own
+    termination — the reference's 50-iteration cap (src/params.h:34) or a tolerance, whichever comes first — at the
+    north_star tolerances, and the two must stop for the same reason after the same number of iterations."""
+    w = c2_window()
+    args = (w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
     sv = Solver(0)
-    args = (w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r)
+    pg, xg, sg = sv.solve(*args, options=PARITY)
+    po, xo, so = oracle.solve(*args, options=oracle_opts())
+    assert sg["iterations"] == so["iterations"] and sg["termination"] == so["reason"]
+    assert sg["successful_steps"] == so["successful_steps"]
+    check_solution(w, sg, pg, xg, so, po, xo)
+    # the reported cost is the oracle's cost function at the GPU's solution
+    c = oracle.cost(pg, xg, w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
+    assert abs(c - sg["final_cost"]) <= 1e-10 * c
+    assert sg["final_cost"] < 0.1 * sg["initial_cost"] and np.abs(xg).max() < 1e3      # nothing runs to the +-1e4 bound
+
+
+def test_config2_stress_without_the_reference_gates():
+    """The ungated variant (far points at 1 px disparity, gross +-10..50 px outliers — inputs the reference never
+    produces): weakly constrained points run to the +-1e4 bound (src/bundle_adjuster.cpp:104-108) and the end game is
+    decided by rounding, so GPU and oracle are compared at iteration 16, where both still walk the same
+    trajectory, and only size-independent properties are asserted at the 50-iteration cap."""
+    w = c2_window(vo_gates=False)
+    sv = Solver(0)
+    args = (w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
     p16, x16, s16 = sv.solve(*args, options=default_options(max_time_s=0.0, max_iterations=16))
     po, xo, so = oracle.solve(*args, options=oracle_opts(max_iterations=16))
     assert s16["iterations"] == 16 and so["iterations"] == 16
     check_solution(w, s16, p16, x16, so, po, xo)
-    # the reference's configuration (50-iteration cap, src/params.h:34)
     p50, x50, s50 = sv.solve(*args, options=PARITY)
     assert s50["status"] in (_capi.SBA_OK, _capi.SBA_NO_CONVERGENCE) and s50["iterations"] <= 50
     assert s50["final_cost"] <= s16["final_cost"] * (1 + 1e-12) and s50["final_cost"] < 0.5 * s50["initial_cost"]
-    c = oracle.cost(p50, x50, w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r)
+    c = oracle.cost(p50, x50, w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
     assert abs(c - s50["final_cost"]) <= 1e-10 * c
-    lin = oracle.linearize(p50, x50, w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r)
-    g0 = oracle.linearize(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r)
-    assert np.abs(lin["gc"][1:]).max() < 1e-2 * np.abs(g0["gc"][1:]).max()
-    p2, x2, s2 = sv.solve(p50, x50, w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r, options=PARITY)
-    # a re-solve restarts the trust region at radius 1e4 and may creep further down the flat valley, never up
-    assert s2["final_cost"] <= s50["final_cost"] * (1 + 1e-12)
-    assert abs(s2["final_cost"] - s50["final_cost"]) <= 1e-3 * s50["final_cost"]
+    assert np.abs(x50).max() <= 1e4                                                    # the bounds hold
+
+
+def test_config3_many_windows_match_the_oracle():
+    """BASELINE.json configs[2] shape: 256 DISTINCT 10-keyframe windows (seed + window id) in one batched call, every
+    window with its own trust region; 16 of them, spread over the batch, are checked against oracle.solve at the
+    north_star tolerances, and the batch total against the sum of its windows."""
+    nwin = 256
+    seed0 = synthetic.CONFIGS["C3"]["seed"]
+    ws = []
+    for i in range(nwin):
+        smap = synthetic.make_config("C3", seed=seed0 + i, num_points=1250)       # quarter-size windows keep the test short
+        w = pack_window(smap, 0, smap.num_frames)
+        w["p_l"], w["p_r"] = smap.p_l, smap.p_r
+        ws.append(w)
+    b = batch_windows(ws)
+    pb, xb, sb = Solver(0).solve(b["poses"], b["points"], b["obs_cam"], b["obs_pt"], b["obs_uv"], b["p_l"], b["p_r"],
+                                 win_cam_off=b["win_cam_off"], win_pt_off=b["win_pt_off"], options=PARITY)
+    assert sb["status"] in (_capi.SBA_OK, _capi.SBA_NO_CONVERGENCE)
+    co, po_ = b["win_cam_off"], b["win_pt_off"]
+    for i in range(0, nwin, nwin // 16):
+        w = ws[i]
+        po, xo, so = oracle.solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"],
+                                  options=oracle_opts())
+        pg, xg = pb[co[i]:co[i + 1]], xb[po_[i]:po_[i + 1]]
+        c = oracle.cost(pg, xg, w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
+        assert abs(c - so["final_cost"]) <= 1e-5 * so["final_cost"], i
+        assert np.abs(pg[:, :3] - po[:, :3]).max() < 1e-5 and np.abs(pg[:, 3:] - po[:, 3:]).max() < 1e-4, i
+        assert np.abs(xg - xo).max() < 1e-4, i
+        assert np.array_equal(pg[0], w["poses"][0])
+    tot = sum(oracle.cost(pb[co[i]:co[i + 1]], xb[po_[i]:po_[i + 1]], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
+              for i, w in enumerate(ws))
+    assert abs(tot - sb["final_cost"]) <= 1e-10 * tot
+
+
+def global_case(name, scale, **kw):
+    smap = synthetic.make_config(name, scale=scale, **kw)
+    w = pack_window(smap, 0, smap.num_frames)
+    w["p_l"], w["p_r"] = smap.p_l, smap.p_r
+    return w
+
+
+@pytest.mark.parametrize("name,scale", [("C4", 0.25), ("C5", 0.05)])
+def test_global_configs_scaled_match_the_oracle(name, scale):
+    """BASELINE.json configs[3] / [4] shapes — C4: 1135 poses / 250k points / 1.4M observations with the loop closed;
+    C5: a 1000-pose open chain / 250k points.  The reduced camera system (6 804 / 5 994 unknowns) is factored exactly
+    on both sides, as the reference does (SPARSE_SCHUR + CHOLMOD, src/bundle_adjuster.cpp:26-29): block-sparse Cholesky
+    in nested-dissection order on the GPU, row-envelope Cholesky in the oracle.  Compared at the solver's own
+    termination at the north_star tolerances."""
+    w = global_case(name, scale)
+    args = (w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
+    sv = Solver(0)
+    pg, xg, sg = sv.solve(*args, options=PARITY)
+    assert sg["pcg_iterations"] == 0                              # exact factorisation, no PCG
+    po, xo, so = oracle.solve(*args, options=oracle_opts())
+    assert sg["iterations"] == so["iterations"] and sg["termination"] == so["reason"]
+    check_solution(w, sg, pg, xg, so, po, xo)
+    # and the PCG path north_star names reaches the same minimum when it is given the iterations it needs
+    pp, xp, sp = sv.solve(*args, options=default_options(max_time_s=0.0, linear_solver=1, max_pcg_iterations=4000, max_iterations=8))
+    p8, x8, s8 = sv.solve(*args, options=default_options(max_time_s=0.0, max_iterations=8))
+    assert abs(sp["final_cost"] - s8["final_cost"]) <= 1e-6 * s8["final_cost"]
+
+
+def test_sparse_cholesky_solves_the_reduced_system_of_a_loop():
+    """k_spchol against numpy on a 227-pose loop (C4 at 1/20): S x = rhs to 1e-10, and bit-identical on a re-run."""
+    w = global_case("C4", 0.05)
+    s = load(w)
+    s.linearize(); s.schur(1e4)
+    assert s.pcg(default_options(linear_solver=2)) == 0
+    S, rhs, x = s.schur_dense()
+    xs = np.linalg.solve(S, rhs)
+    assert np.abs(x - xs).max() <= 1e-10 * np.abs(xs).max()
+    s.pcg(default_options(linear_solver=2))
+    assert np.array_equal(s.schur_values()[2], x)
+
+
+def test_wall_clock_limit_terminates_with_the_state_written_back():
+    """max_solver_time_in_seconds (src/params.h:41, src/bundle_adjuster.cpp:18): a tiny limit stops the loop with
+    SBA_TERM_MAX_TIME and the last accepted state comes back, like every other termination."""
+    w = c2_window()
+    args = (w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
+    sv = Solver(0)
+    sv.solve(*args, options=default_options(max_time_s=0.0, max_iterations=2))      # warm-up: module load, pool growth
+    pg, xg, sg = sv.solve(*args, options=default_options(max_time_s=2e-3))
+    assert sg["termination_name"] == "max_time" and sg["status"] == _capi.SBA_NO_CONVERGENCE
+    assert 0 < sg["iterations"] < 50 and sg["final_cost"] < sg["initial_cost"]
+    c = oracle.cost(pg, xg, w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
+    assert abs(c - sg["final_cost"]) <= 1e-10 * c
+
+
+def test_numerical_failure_still_writes_back_like_the_reference(small_window):
+    """The reference ignores Ceres' termination type and writes back whatever state it has (src/bundle_adjuster.cpp:
+    116-132).  A non-finite measurement makes the cost non-finite: SBA_NUMERICAL_FAILURE, the (projected) input state
+    is returned instead of an exception."""
+    w = small_window
+    uv = w["obs_uv"].copy(); uv[5, 0] = np.nan
+    pg, xg, sg = Solver(0).solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], uv, w["p_l"], w["p_r"], options=PARITY)
+    assert sg["status"] == _capi.SBA_NUMERICAL_FAILURE
+    assert np.array_equal(pg, w["poses"]) and np.array_equal(xg, w["points"])

@@ -162,3 +162,24 @@ def test_structure_is_independent_of_the_host_thread_count(monkeypatch):
     oc[150000] = Nc + 7; op[100000] = -5          # the earlier observation decides the message
     with pytest.raises(Exception, match="obs_pt out of range"):
         Solver(-1).set_structure(Nc, Np, oc, op)
+
+
+@pytest.mark.parametrize("k,ok", [(240, True), (241, True), (255, True), (256, False)])
+def test_long_tracks_get_a_chunk_of_their_own_or_a_clean_error(k, ok):
+    """One point seen by k cameras (loop-closure re-targeting produces long tracks, src/camera_frame.h:92-109).
+    Chunk-local indices are bytes: up to 255 observations the point gets its own chunk (round 1 looped forever for
+    241..255); beyond that the structure build refuses with SBA_INVALID_ARGUMENT instead of crashing."""
+    cam = np.concatenate([np.arange(k), np.arange(k)]).astype(np.int32)
+    pt = np.concatenate([np.zeros(k), np.ones(k)]).astype(np.int32)          # two such points
+    extra_c = np.array([0, 1, 2], np.int32); extra_p = np.array([2, 2, 2], np.int32)
+    s = Solver(-1)
+    if ok:
+        s.set_structure(k, 3, np.concatenate([cam, extra_c]), np.concatenate([pt, extra_p]))
+        bp, _ = s.sorted_views()
+        assert sorted(bp.tolist()) == list(range(2 * k + 3))
+        rows, cols = s.schur_pattern()
+        assert rows.size == (k - 1) ** 2                                     # all free cameras co-visible
+    else:
+        with pytest.raises(_capi.SbaError) as e:
+            s.set_structure(k, 3, np.concatenate([cam, extra_c]), np.concatenate([pt, extra_p]))
+        assert e.value.status == _capi.SBA_INVALID_ARGUMENT

@@ -180,3 +180,20 @@ def test_polynomial_root_real_parts_match_numpy(emu):
         got = np.sort(out[:n])
         scale = np.maximum(1.0, np.abs(np.roots(c)).max())
         assert np.abs(got - ref).max() <= 1e-6 * scale, (c, got, ref)
+
+
+def test_envelope_cholesky_path_equals_dense_path(monkeypatch):
+    """Global problems go through a row-envelope Cholesky instead of the dense LLT (oracle/sba_oracle.cpp `Envelope`):
+    same reduced system, same solution — forced both ways on an open chain with loop-closure-free band structure and
+    on a loop, the trajectories must agree to rounding."""
+    from stereo_orb_slam_b200 import pack_window, synthetic
+    for smap in (synthetic.make_config("C5", scale=0.003), synthetic.make_config("C4", scale=0.015)):
+        w = pack_window(smap, 0, smap.num_frames)
+        out = {}
+        for env in ("0", "1"):
+            monkeypatch.setenv("ORACLE_ENVELOPE", env)
+            out[env] = oracle.solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r,
+                                    options=oracle.default_options(max_time_s=0.0, num_threads=0, max_iterations=12))
+        assert out["0"][2]["iterations"] == out["1"][2]["iterations"] == 12
+        assert abs(out["0"][2]["final_cost"] - out["1"][2]["final_cost"]) <= 1e-11 * out["0"][2]["final_cost"]
+        assert np.abs(out["0"][0] - out["1"][0]).max() < 1e-9 and np.abs(out["0"][1] - out["1"][1]).max() < 1e-8

@@ -1,17 +1,21 @@
 #!/usr/bin/env python
-"""bench.py — BA observations/sec through residual + Jacobian + Hessian accumulation + Schur (K1-K3),
-plus LM iterations/sec, on BASELINE.json's configs[1] (C2: 50 keyframes / 40k points / ~200k stereo
-observations per window).  One JSON line on stdout (rank 0).
+"""bench.py — BA observations/sec through residual + Jacobian + Hessian accumulation + Schur (K1-K3), plus LM
+iterations/sec and the end-to-end drop-in rate.  One JSON line on stdout (rank 0).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C2|C1|C4s]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload auto|C1|C2|C4|C4s]
 
-ours       value = observations through K1-K3 per second, state resident in HBM, device time (CUDA events on
-           the solver's stream), L2 flushed between steps; N > 1: every rank owns one independent window
-           (weak scaling, no data-path collective — SURVEY §8(e)), value = all ranks' observations / max time.
-           e2e   = the same unit through the C-ABI one-shot call sba_solve on HOST buffers (structure build,
+Workload (`auto`): N = 1 -> BASELINE.json configs[1] (C2: 50 keyframes / 40k points / ~200k stereo observations, one
+sliding window); N > 1 -> configs[3] (C4: 4541 poses / 1M points / ~5.6M observations), ONE problem whose points
+(and all their observations) are sharded over the N ranks, camera-side sums all-reduced by NCCL inside libsba.so —
+strong scaling with data-path collectives.
+
+ours       value = observations through K1-K3 per second, state resident in HBM, device time (CUDA events on the
+           solver's stream), L2 flushed between steps, max over ranks.
+           e2e   = the same unit through the C-ABI one-shot call sba_solve on pinned HOST buffers (structure build,
                    H2D, the whole LM solve, D2H inside the timed region): observations x linearisations / wall.
-reference  the CPU restatement of the reference's Ceres path (oracle/, "port": Ceres itself cannot be built
-           here) on the box's host cores: the LM solve capped at a few iterations per step, same unit.
+reference  the CPU restatement of the reference's Ceres path (oracle/, "port": Ceres itself cannot be built here)
+           on the box's host cores, on the same workload: value = CPU K1-K3 rate (stage timers inside the oracle's LM
+           solve), e2e = observations x linearisations / wall of the (iteration-capped) solve.  Does not load libsba.so.
 """
 import argparse
 import json
@@ -27,30 +31,66 @@ sys.path.insert(0, ROOT)
 
 METRIC = "BA observations/sec through residual+Jacobian+Hessian accumulation+Schur (K1-K3)"
 UNIT = "obs/s"
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of the same
-# workload (profiles/, see the summary there); None for a kernel without a capture
-TRAFFIC = {"k_schur_chunk": 36198656, "k_lin_chunk": 6119168}   # profiles/r01_f_ncu_full_summary.txt (C2; W written by k_lin_chunk stays in L2)
+NCU_TRAFFIC = os.path.join(ROOT, "profiles", "ncu_traffic.json")     # written by scripts/ncu_summary.py from a --set full capture
 
 
-def make_workload(name, rank=0):
-    from stereo_orb_slam_b200 import pack_window, synthetic
-    if name == "C4s":          # 1/10-scale global BA (454 poses / 100k points), single GPU
-        smap = synthetic.make_config("C4", scale=0.1, seed=synthetic.CONFIGS["C4"]["seed"] + rank)
+def resolve_workload(args):
+    if args.workload != "auto":
+        return args.workload
+    return "C2" if args.gpus <= 1 and int(os.environ.get("WORLD_SIZE", "1")) <= 1 else "C4"
+
+
+def make_workload(name, use_product_pack=True):
+    """The synthetic map of `name` packed as one BA window over all its frames.  The reference arm packs with the
+    numpy restatement (oracle/pack_oracle.py) so that it never loads libsba.so; both give bit-identical arrays
+    (tests/test_host.py)."""
+    from stereo_orb_slam_b200 import synthetic
+    if name == "C4s":
+        smap = synthetic.make_config("C4", scale=0.1)
     else:
-        # every rank solves a window of the same synthetic map (weak scaling: per-GPU work is fixed and identical)
         smap = synthetic.make_config(name)
-    w = pack_window(smap, 0, smap.num_frames)
+    if use_product_pack:
+        from stereo_orb_slam_b200 import pack_window
+        w = pack_window(smap, 0, smap.num_frames)
+    else:
+        from oracle import pack_oracle
+        w = pack_oracle.pack(smap, 0, smap.num_frames)
+        w["poses"] = np.asarray(w["poses"], np.float64).reshape(-1, 6)
+        w["points"] = np.asarray(w["points"], np.float64).reshape(-1, 3)
     w["p_l"], w["p_r"] = smap.p_l, smap.p_r
     fixed = np.zeros(smap.num_frames, np.uint8); fixed[0] = 1
     w["cam_fixed"] = fixed
     return w
 
 
-def algorithmic_bytes(Nobs, Np, Nc, nblk):
-    """SURVEY §8(d) compulsory HBM traffic."""
+def workload_label(name, w):
+    return "%s: %d keyframes / %d points / %d stereo observations" % (
+        name, w["poses"].shape[0], w["points"].shape[0], int(w["obs_cam"].size))
+
+
+def algorithmic_bytes(Nobs, Np, Nc, nblk_upper):
+    """SURVEY 8(d) compulsory HBM traffic (upper-triangle blocks of S)."""
     lin = Nobs * 168 + Np * 96 + Nc * 264
-    schur = Nobs * 144 + Np * 72 + nblk * 288 + Nc * 48
+    schur = Nobs * 144 + Np * 72 + nblk_upper * 288 + Nc * 48
     return lin, schur
+
+
+def algorithmic_flops(obs_pt, Np):
+    """~800 fp64 flop / observation for K1+K2 (4 residuals); Schur 108 + 108 (k + 1) per observation of
+    a point with k observations (upper triangle)."""
+    k = np.bincount(obs_pt, minlength=Np).astype(np.float64)
+    lin = 800.0 * obs_pt.size
+    schur = float((k * (108.0 + 108.0 * (k + 1.0))).sum())
+    return lin, schur
+
+
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu capture."""
+    try:
+        t = json.load(open(NCU_TRAFFIC))
+        return t["kernels"][kernel]["dram_bytes"], t.get("source")
+    except Exception:
+        return None, None
 
 
 class ClockSampler(threading.Thread):
@@ -85,7 +125,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(n)
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(0.005)
 
     def result(self):
         self.stop_flag = True
@@ -101,43 +141,52 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def cpu_k1k3(oracle, w, threads, iters):
+    """CPU K1-K3 rate from the stage timers INSIDE the oracle's LM solve (no per-repeat allocation): one linearisation
+    pass = time_linearize / linearizations, one Schur pass = time_schur / iterations."""
+    opt = oracle.default_options(max_time_s=0.0, num_threads=threads, max_iterations=iters)
+    t0 = time.perf_counter()
+    _, _, s = oracle.solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"], options=opt)
+    wall = time.perf_counter() - t0
+    per_pass = s["time_linearize_s"] / max(s["linearizations"], 1) + s["time_schur_s"] / max(s["iterations"], 1)
+    nobs = int(w["obs_cam"].size)
+    return {"k1k3_obs_per_s": nobs / per_pass, "solve_obs_lin_per_s": nobs * s["linearizations"] / wall,
+            "lm_iters_per_s": s["iterations"] / wall, "wall_s": wall, "summary": s}
+
+
 def run_reference(args):
     """The reference arm: CPU restatement of the reference's Ceres path on the host cores (rank 0 only)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from oracle import oracle
-    w = make_workload(args.workload)
+    name = resolve_workload(args)
+    w = make_workload(name, use_product_pack=False)
     Nobs = int(w["obs_cam"].size)
     cores = oracle.num_procs()
-    cap = 3        # LM iterations per step: a bounded sample of the solve (same per-iteration work as the full solve)
-    opt = oracle.default_options(max_time_s=0.0, num_threads=0, max_iterations=cap)
-
-    def step():
-        t0 = time.perf_counter()
-        _, _, s = oracle.solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"],
-                               options=opt)
-        return time.perf_counter() - t0, s
+    cap = 3 if Nobs < 1000000 else 1      # LM iterations per step: a bounded sample of the solve (same per-iteration work as the full solve)
     for _ in range(min(args.warmup, 1)):
-        step()
-    tot, lin, its = 0.0, 0, 0
+        cpu_k1k3(oracle, w, 0, cap)
+    tot = 0.0; k13 = []; e2e = []; its = []
     for _ in range(args.steps):
-        dt, s = step()
-        tot += dt; lin += s["linearizations"]; its += s["iterations"]
-    value = Nobs * lin / tot
-    k13 = oracle.time_linearize_schur(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"],
-                                      w["cam_fixed"], num_threads=0, repeats=2)
-    sample = "%d LM solves capped at %d iterations each on %s (%d obs); Jet autodiff + Schur + dense Cholesky" % (
-        args.steps, cap, args.workload, Nobs)
+        r = cpu_k1k3(oracle, w, 0, cap)
+        tot += r["wall_s"]; k13.append(r["k1k3_obs_per_s"]); e2e.append(r["solve_obs_lin_per_s"]); its.append(r["lm_iters_per_s"])
+    four = cpu_k1k3(oracle, w, 4, cap)      # the reference's own thread count (src/params.h:37)
+    value = float(np.mean(k13))
+    sample = "%d LM solves capped at %d iterations each on %s; Jet autodiff + Schur + exact Cholesky; stage timers inside the solve" % (
+        args.steps, cap, workload_label(name, w))
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * tot / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": 1e3 * tot / args.steps, "higher_is_better": True,
+            "scaling": "weak" if name in ("C1", "C2") else "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "%s: %d keyframes / %d points / %d stereo observations" % (
-                args.workload, w["poses"].shape[0], w["points"].shape[0], Nobs)},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
-            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "lm_iters_per_s": its / tot, "k1k3_obs_per_s": Nobs / k13,
-            "note": "CPU restatement of the reference's Ceres path — Ceres itself unavailable on this box"}
+            "config": {"workload": workload_label(name, w)},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                             "threads_4": {"k1k3_obs_per_s": four["k1k3_obs_per_s"], "solve_obs_lin_per_s": four["solve_obs_lin_per_s"],
+                                           "lm_iters_per_s": four["lm_iters_per_s"], "note": "the reference's num_threads (src/params.h:37)"}},
+            "e2e": {"value": float(np.mean(e2e)), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                    "what": "observations x linearisations / wall of the capped LM solve"},
+            "lm_iters_per_s": float(np.mean(its)),
+            "note": "CPU restatement of the reference's Ceres path - Ceres itself unavailable on this box (DESIGN 9)"}
     emit(line)
 
 
@@ -153,17 +202,17 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     from stereo_orb_slam_b200 import Solver, default_options
+    from stereo_orb_slam_b200.parallel import shard_points
 
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1 and "SBA_HOST_THREADS" not in os.environ:       # torchrun pins OMP_NUM_THREADS=1; share the host cores instead
         os.environ["SBA_HOST_THREADS"] = str(max(1, (os.cpu_count() or 1) // world))
     if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+        raise SystemExit("bench.py: no CUDA device - the product path has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
-        # keep stdout to the one JSON line: NCCL writes its banner ("NCCL version ...", printed from level VERSION
-        # up, WARN included) and anything else it logs to stderr instead
+        # keep stdout to the one JSON line: NCCL writes its banner and anything else it logs to stderr instead
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
@@ -172,63 +221,112 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    w = make_workload(args.workload, rank)
+    def allreduce(vals, op):
+        t = torch.tensor(vals, dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=op)
+        return [float(v) for v in t]
+
+    name = resolve_workload(args)
+    sharded = world > 1 and name not in ("C1", "C2")
+    w = make_workload(name)
     Nc, Np, Nobs = w["poses"].shape[0], w["points"].shape[0], int(w["obs_cam"].size)
-    sv = Solver(local).set_structure(Nc, Np, w["obs_cam"], w["obs_pt"])
+    warmup = max(args.warmup, 3)
+    opt = default_options(max_time_s=0.0)
+    radius = 1e4
+
+    def make_solver(shard):
+        s = Solver(local)
+        cut = None
+        if shard:
+            uid = [Solver.comm_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(uid, src=0)
+            s.comm_init(rank, world, uid[0])
+            cut = shard_points(w["obs_pt"], Np, world)
+            s.set_point_shard(int(cut[rank]), int(cut[rank + 1]))
+        return s, cut
+
+    sv, cut = make_solver(sharded)
+    sv.set_structure(Nc, Np, w["obs_cam"], w["obs_pt"])
     sv.set_state(w["poses"], w["points"]); sv.set_measurements(w["obs_uv"], w["p_l"], w["p_r"])
     sv.linearize()
-    radius = 1e4
-    nblk = int(sv.schur_pattern()[0].size)
-    B_lin, B_schur = algorithmic_bytes(Nobs, Np, Nc, nblk)
-    opt = default_options(max_time_s=0.0)
+    if sharded:
+        mine = (w["obs_pt"] >= cut[rank]) & (w["obs_pt"] < cut[rank + 1])
+        nobs_local, np_local = int(np.count_nonzero(mine)), int(cut[rank + 1] - cut[rank])
+        obs_pt_local = w["obs_pt"][mine] - cut[rank]
+    else:
+        nobs_local, np_local, obs_pt_local = Nobs, Np, w["obs_pt"]
+    rows, cols = sv.schur_pattern()
+    nblk_upper = int((rows <= cols).sum())
+    B_lin, B_schur = algorithmic_bytes(nobs_local, np_local, Nc, nblk_upper)
+    F_lin, F_schur = algorithmic_flops(obs_pt_local, np_local)
 
     # ---- value: K steps of (linearise + Schur), cold L2 each step, device time on the solver's stream
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(warmup):
         sv.time_stage(8, 1, True, radius)
     sampler = ClockSampler(local); sampler.start()
     barrier()
     l0 = sv.launch_count
-    ms = 0.0
+    per_step = []
     for _ in range(args.steps):
-        ms += sv.time_stage(8, 1, True, radius)
+        per_step.append(sv.time_stage(8, 1, True, radius))
     barrier()
     launches = sv.launch_count - l0
     clocks = sampler.result()
-    t = torch.tensor([ms, float(Nobs)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        tm = t.clone(); dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-        ts = t.clone(); dist.all_reduce(ts, op=dist.ReduceOp.SUM)
-        ms_max, nobs_all = float(tm[0]), float(ts[1])
-    else:
-        ms_max, nobs_all = ms, float(Nobs)
-    value = nobs_all * args.steps / (ms_max * 1e-3)
+    ms = float(np.sum(per_step))
+    ms_max, med_max, worst = allreduce([ms, float(np.median(per_step)), float(np.max(per_step))], dist.ReduceOp.MAX if world > 1 else None)
+    units = Nobs if sharded else Nobs * world          # sharded: ONE problem over all ranks; else one window per rank
+    value = units * args.steps / (ms_max * 1e-3)
 
     # ---- per-stage device times for the roofline (same stream, CUDA events, cold L2)
-    reps = max(args.steps, 5)
-    t_lp = sv.time_stage(0, reps, True, radius); t_lc = sv.time_stage(1, reps, True, radius)
-    t_sp = sv.time_stage(2, reps, True, radius); t_lin = sv.time_stage(3, reps, True, radius)
-    t_sch = sv.time_stage(4, reps, True, radius)
+    reps = max(min(args.steps, 50), 5)
+    t_lp = sv.time_stage(0, reps, True, radius); t_sp = sv.time_stage(2, reps, True, radius)
+    t_lin = sv.time_stage(3, reps, True, radius); t_sch = sv.time_stage(4, reps, True, radius)
     peak, peak_src = measured_peak()
-    # the dominant kernel of the step: k_lin_chunk does the whole of K1/K2 and k_schur_chunk the whole of K3 (their
-    # assembly is in-kernel), so each is charged its stage's full algorithmic bytes
+    fp64_peak = sv.measure_fp64_peak()
+    # the dominant kernel of the step: k_lin_chunk does the whole of K1/K2 and k_schur_chunk the whole of K3 for a chunk,
+    # so each is charged its stage's full algorithmic bytes / flops for the observations of this rank
     if t_sp >= t_lp:
-        dom, t_dom, B_dom = "k_schur_chunk", t_sp, B_schur
+        dom, t_dom, B_dom, F_dom = "k_schur_chunk", t_sp, B_schur, F_schur
     else:
-        dom, t_dom, B_dom = "k_lin_chunk", t_lp, B_lin
+        dom, t_dom, B_dom, F_dom = "k_lin_chunk", t_lp, B_lin, F_lin
     ach = B_dom / (t_dom * 1e-3) / 1e9
+    traffic, traffic_src = ncu_traffic(dom)
 
-    # ---- e2e: sba_solve on host buffers (pinned), whole LM solve, results read back
+    # ---- strong-scaling baseline of the SAME workload on one GPU (rank 0, unsharded), so the line carries its own N = 1
+    base = None
+    if sharded:
+        if rank == 0:
+            s1 = Solver(local).set_structure(Nc, Np, w["obs_cam"], w["obs_pt"])
+            s1.set_state(w["poses"], w["points"]); s1.set_measurements(w["obs_uv"], w["p_l"], w["p_r"])
+            s1.linearize()
+            for _ in range(3):
+                s1.time_stage(8, 1, True, radius)
+            b_ms = float(np.mean([s1.time_stage(8, 1, True, radius) for _ in range(min(args.steps, 20))]))
+            s1.set_state(w["poses"], w["points"])
+            t0 = time.perf_counter(); r1 = s1.run(default_options(max_time_s=0.0, max_iterations=10)); t1 = time.perf_counter() - t0
+            base = {"n_gpus": 1, "value": Nobs / (b_ms * 1e-3), "ms_per_step": b_ms, "lm_iters_per_s": r1["iterations"] / t1,
+                    "final_cost_10_iterations": r1["final_cost"]}
+            s1.close()
+        barrier()
+
+    # ---- LM iterations/s with the state resident (10 iterations), sharded or not
+    sv.set_state(w["poses"], w["points"])
+    barrier(); t0 = time.perf_counter()
+    r10 = sv.run(default_options(max_time_s=0.0, max_iterations=10))
+    barrier(); lm_wall = allreduce([time.perf_counter() - t0], dist.ReduceOp.MAX if world > 1 else None)[0]
+
+    # ---- e2e: sba_solve on pinned host buffers, whole LM solve, results read back
     def pinned(a):
         tt = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
         return tt.numpy(), tt
-    keep = []
-    hb = {}
+    keep = []; hb = {}
     for k in ("poses", "points", "obs_cam", "obs_pt", "obs_uv"):
         hb[k], tt = pinned(w[k]); keep.append(tt)
-    sv2 = Solver(local)
-    for _ in range(1):
-        sv2.solve(hb["poses"], hb["points"], hb["obs_cam"], hb["obs_pt"], hb["obs_uv"], w["p_l"], w["p_r"], options=opt)
-    e_steps = max(3, min(args.steps, 10))
+    sv.close()
+    sv2, _ = make_solver(sharded)
+    sv2.solve(hb["poses"], hb["points"], hb["obs_cam"], hb["obs_pt"], hb["obs_uv"], w["p_l"], w["p_r"], options=opt)      # warm-up
+    e_steps = max(3, min(args.steps, 10)) if not sharded else 2
     barrier()
     t0 = time.perf_counter(); lin = 0; its = 0; solve_s = 0.0; summ = None; brk = {}
     for _ in range(e_steps):
@@ -236,44 +334,58 @@ def run_ours(args):
         lin += summ["linearizations"]; its += summ["iterations"]; solve_s += summ["time_solve_s"]
         brk = {k: brk.get(k, 0.0) + 1e3 * summ[k] / e_steps for k in ("time_structure_s", "time_h2d_s", "time_solve_s", "time_d2h_s")}
     barrier()
-    e_wall = time.perf_counter() - t0
-    te = torch.tensor([e_wall], dtype=torch.float64, device="cuda"); tl = torch.tensor([float(Nobs * lin)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX); dist.all_reduce(tl, op=dist.ReduceOp.SUM)
-    e2e = float(tl[0]) / float(te[0])
+    e_wall = allreduce([time.perf_counter() - t0], dist.ReduceOp.MAX if world > 1 else None)[0]
+    e_units = Nobs * lin if sharded else Nobs * lin * world
+    e2e = e_units / e_wall
     h2d = sum(int(hb[k].nbytes) for k in hb) + 192
     d2h = int(hb["poses"].nbytes + hb["points"].nbytes)
 
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "%s: %d keyframes / %d points / %d stereo observations per window, one window per GPU" % (
-                args.workload, Nc, Np, Nobs), "l2": "flushed between steps (256 MiB memset)", "residual_dim": 4,
-                "schur_blocks": nblk},
+    label = workload_label(name, w)
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
+            "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "strong" if sharded else "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": label, "l2": "flushed between steps (256 MiB memset)", "residual_dim": 4,
+                       "schur_blocks_upper": nblk_upper,
+                       "parallelism": ("points sharded over %d ranks, camera-side sums all-reduced (NCCL)" % world) if sharded else
+                                      ("one window per GPU, no data-path collective" if world > 1 else "single GPU"),
+                       "step": "one linearisation + one Schur step (K1-K3)" + ("" if sharded else ", replayed as one CUDA graph")},
+            "ms_per_step_median": med_max, "ms_per_step_max": worst,
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "host_threads_per_rank": int(os.environ.get("SBA_HOST_THREADS", os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1))), "what": "sba_solve on pinned host buffers: structure build + H2D + full LM solve + D2H; obs x linearisations / wall",
+                    "host_threads_per_rank": int(os.environ.get("SBA_HOST_THREADS", os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1))),
+                    "what": "sba_solve on pinned host buffers: structure build + H2D + full LM solve + D2H; obs x linearisations / wall",
                     "ms_per_solve": 1e3 * e_wall / e_steps, "lm_iterations": its // e_steps, "final_cost": summ["final_cost"],
-                    "termination": summ["termination_name"],
+                    "termination": summ["termination_name"], "pcg_iterations_per_lm_iteration": summ["pcg_iterations"] / max(summ["iterations"], 1),
                     "ms_breakdown": {k.replace("time_", "").replace("_s", ""): v for k, v in brk.items()},
                     "device_ms": {k: summ[k] for k in ("ms_linearize", "ms_schur", "ms_pcg", "ms_update")}},
-            "lm_iters_per_s": its / solve_s,
+            "lm_iters_per_s": r10["iterations"] / lm_wall,
+            "lm_iters_per_s_e2e": its / solve_s,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": TRAFFIC.get(dom), "peak_source": peak_src, "algorithmic_bytes": B_dom, "us_per_launch": 1e3 * t_dom},
-            "stages_us": {"k_lin_chunk": 1e3 * t_lp, "k_assemble_schur": 1e3 * t_lc, "k_schur_chunk": 1e3 * t_sp, "linearize": 1e3 * t_lin,
-                          "schur": 1e3 * t_sch},
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes": B_dom,
+                         "us_per_launch": 1e3 * t_dom,
+                         "fp64": {"achieved": F_dom / (t_dom * 1e-3) / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
+                                  "frac": F_dom / (t_dom * 1e-3) / 1e12 / fp64_peak if fp64_peak > 0 else None,
+                                  "algorithmic_flops": F_dom, "peak_source": "measured here (sba_measure_fp64_peak: register-only DFMA chains)"}},
+            "stages_us": {"k_lin_chunk": 1e3 * t_lp, "k_schur_chunk": 1e3 * t_sp, "linearize": 1e3 * t_lin, "schur": 1e3 * t_sch},
             "stage_roofline": {"linearize_GBs": B_lin / (t_lin * 1e-3) / 1e9, "schur_GBs": B_schur / (t_sch * 1e-3) / 1e9,
-                               "linearize_frac": B_lin / (t_lin * 1e-3) / 1e9 / peak, "schur_frac": B_schur / (t_sch * 1e-3) / 1e9 / peak}}
+                               "linearize_frac": B_lin / (t_lin * 1e-3) / 1e9 / peak, "schur_frac": B_schur / (t_sch * 1e-3) / 1e9 / peak,
+                               "step_frac": (B_lin + B_schur) / (ms_max / args.steps * 1e-3) / 1e9 / peak if not sharded else None}}
+    if base is not None:
+        line["strong_scaling_baseline"] = base
     if rank == 0 and world == 1 and not args.no_cpu:
         from oracle import oracle
         cores = oracle.num_procs()
-        reps_cpu = 3
-        sec = oracle.time_linearize_schur(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"],
-                                          w["cam_fixed"], num_threads=0, repeats=reps_cpu)
-        line["cpu_baseline"] = {"value": Nobs / sec, "unit": UNIT, "cores": cores, "kind": "port",
-                                "sample": "%d passes of linearise (Jet autodiff) + block build + dense Schur over the same %s window" % (reps_cpu, args.workload)}
+        cap = 3 if Nobs < 1000000 else 1
+        allc = cpu_k1k3(oracle, w, 0, cap)
+        four = cpu_k1k3(oracle, w, 4, cap)
+        line["cpu_baseline"] = {"value": allc["k1k3_obs_per_s"], "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": "one LM solve capped at %d iterations on the same %s window; stage timers inside the solve (linearise: Jet autodiff + block build; exact Schur)" % (cap, name),
+                                "threads_4": {"k1k3_obs_per_s": four["k1k3_obs_per_s"], "lm_iters_per_s": four["lm_iters_per_s"],
+                                              "note": "the reference's num_threads (src/params.h:37)"},
+                                "lm_iters_per_s": allc["lm_iters_per_s"]}
     if rank == 0:
         emit(line)
+    sv2.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -281,12 +393,14 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=1000)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="C2", choices=["C1", "C2", "C4s"])
+    ap.add_argument("--workload", default="auto", choices=["auto", "C1", "C2", "C4", "C4s"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
+    if args.impl == "reference" and args.steps > 20:
+        args.steps = 5            # the CPU arm's step is a whole capped LM solve: bounded so the run ends within minutes
     # stdout carries exactly ONE JSON line: file descriptor 1 is pointed at stderr for everything else (NCCL prints
     # its version banner to stdout whatever NCCL_DEBUG_FILE says) and the line goes to the saved descriptor
     global _JSON_OUT

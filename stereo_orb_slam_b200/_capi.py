@@ -19,7 +19,7 @@ SYMBOLS = [
     "sba_get_linearization", "sba_get_schur_pattern", "sba_get_schur_values", "sba_get_sorted_views",
     "sba_num_free_cameras", "sba_launch_count", "sba_comm_unique_id", "sba_comm_init",
     "sba_pack_window", "sba_unpack_window", "sba_matrix_to_pose", "sba_pose_to_matrix",
-    "sba_time_stage", "sba_invert_pose", "sba_normalize_pose", "sba_compose_pose", "sba_get_factor_symbolic",
+    "sba_time_stage", "sba_invert_pose", "sba_normalize_pose", "sba_compose_pose", "sba_get_factor_symbolic", "sba_measure_fp64_peak",
 ]
 
 SBA_OK, SBA_NO_CONVERGENCE, SBA_NUMERICAL_FAILURE, SBA_INVALID_ARGUMENT, SBA_CUDA_ERROR, SBA_NCCL_ERROR = range(6)

@@ -2094,6 +2094,19 @@ __global__ void __launch_bounds__(kThreads) k_step_loop(Dev d, DevParams P, int 
   if (prof) printf("[step] rounds %d  backsub %llu  cam_step %llu  trial_cam %llu  trial_points %llu  reduce+control %llu  apply %llu ns\n", round, tp[0], tp[1], tp[2], tp[3], tp[4], tp[5]);
 }
 
+// FP64 FMA peak of the device (bench.py reports the fp64 fraction beside the HBM fraction): eight
+// independent DFMA chains per thread, no memory traffic.  2 * 8 * iters flop per thread.
+__global__ void __launch_bounds__(256) k_fp64_peak(double* out, int iters, double a, double b) {
+  double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+#pragma unroll 4
+  for (int i = 0; i < iters; ++i) {
+    x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+    x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+  }
+  const double s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+  if (s == 12345.678) out[blockIdx.x * blockDim.x + threadIdx.x] = s;     // never true: keeps the chains alive
+}
+
 // permute the caller's observations into the point-sorted view
 __global__ void k_permute_uv(Dev d, const float4* __restrict__ uv_in, float4* __restrict__ uv_p) {
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -146,6 +146,12 @@ class Solver:
                                           I32(1 if flush_l2 else 0), C.byref(ms)))
         return ms.value
 
+    def measure_fp64_peak(self):
+        """FP64 FMA peak of the device in TFLOP/s (own micro-benchmark, register-only DFMA chains)."""
+        t = D(0)
+        capi.check(self._L.sba_measure_fp64_peak(self._h, C.byref(t)))
+        return t.value
+
     # ---- introspection
     def get_linearization(self, residuals=True):
         r = np.zeros((self.Nobs, 4)) if residuals else None

@@ -108,7 +108,8 @@ def main():
         json_out.write(json.dumps({"mode": args.mode, "workload": label, "n_gpus": world, "scaling": "strong",
                           "k1k3_obs_per_s": nobs * args.steps / (float(t[0]) * 1e-3), "ms_per_step": float(t[0]) / args.steps,
                           "lm_iterations": s["iterations"], "lm_iters_per_s": s["iterations"] / float(t[1]), "solve_s": float(t[1]),
-                          "pcg_iterations": s["pcg_iterations"], "final_cost": final_cost, "termination": s["termination_name"]}) + "\n"); json_out.flush()
+                          "pcg_iterations": s["pcg_iterations"], "final_cost": final_cost, "termination": s["termination_name"],
+                          "device_ms_rank0": {k: s[k] for k in ("ms_linearize", "ms_schur", "ms_pcg", "ms_update")}}) + "\n"); json_out.flush()
     sv.close()
     if world > 1:
         dist.destroy_process_group()

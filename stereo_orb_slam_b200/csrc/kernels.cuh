@@ -280,6 +280,59 @@ __global__ void __launch_bounds__(kThreads) k_lin_finish(Dev d, DevParams P, int
   }
 }
 
+// Point-sharded solve (multi-GPU): the same per-window finish in two halves around ONE packed all-reduce (sum) of
+// [U | gc | cost_red | gslots].  A maximum travels through the sum: every rank writes its value into its own slot of
+// an otherwise zero array, so the reduced array holds all ranks' values and the maximum is taken locally — on the
+// same bits on every rank.
+__global__ void __launch_bounds__(kThreads) k_lin_finish_local(Dev d, int rank, int world) {
+  __shared__ double sm[4];
+  __shared__ double smx[4];
+  const int w = blockIdx.x;
+  double cost[1] = {0.0};
+  double gmax = 0.0;
+  for (int ch = d.win_pchunk_off[w] + threadIdx.x; ch < d.win_pchunk_off[w + 1]; ch += kThreads) {
+    cost[0] += d.lin_part[2 * ch];
+    gmax = fmax(gmax, d.lin_part[2 * ch + 1]);
+  }
+  const double tot = block_sum<1>(cost, sm);
+  const double mx = block_max1(gmax, smx);
+  if (threadIdx.x == 0) d.cost_red[w] = tot;
+  for (int r = threadIdx.x; r < world; r += kThreads) d.gslots[(size_t)r * d.nwin + w] = (r == rank) ? mx : 0.0;
+}
+
+__global__ void __launch_bounds__(kThreads) k_lin_finish_global(Dev d, DevParams P, int keep_cost, int world) {
+  __shared__ double smx[4];
+  const int w = blockIdx.x;
+  double gmax = 0.0;
+  for (int r = threadIdx.x; r < world; r += kThreads) gmax = fmax(gmax, d.gslots[(size_t)r * d.nwin + w]);
+  for (int f = d.win_fc_off[w] + threadIdx.x; f < d.win_fc_off[w + 1]; f += kThreads) {
+    const int c = d.free2cam[f];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) gmax = fmax(gmax, fabs(d.gc[(size_t)c * 6 + i]));
+  }
+  const double mx = block_max1(gmax, smx);
+  if (threadIdx.x == 0) {
+    if (!keep_cost) d.w_cost[w] = d.cost_red[w];
+    d.w_gmax[w] = mx;
+  }
+}
+
+// max-by-sum exchange of a per-window scalar: before the all-reduce every rank fills its own slot, afterwards the
+// maximum over the slots is the global one
+__global__ void k_slots_put(double* __restrict__ slots, const double* __restrict__ v, int nwin, int rank, int world) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nwin * world) return;
+  const int r = i / nwin, w = i - r * nwin;
+  slots[i] = (r == rank) ? v[w] : 0.0;
+}
+__global__ void k_slots_max(double* __restrict__ v, const double* __restrict__ slots, int nwin, int world) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= nwin) return;
+  double m = 0.0;
+  for (int r = 0; r < world; ++r) m = fmax(m, slots[(size_t)r * nwin + w]);
+  v[w] = m;
+}
+
 // --------------------------------------------------------------------------- K3: Schur complement
 // LM damping in Ceres's Jacobi-scaled space mapped back to the unscaled one:
 //   D_j = clamp(s_j^2 H_jj, 1e-6, 1e32) / (s_j^2 radius)        (levenberg_marquardt_strategy)

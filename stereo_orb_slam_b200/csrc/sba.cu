@@ -276,15 +276,18 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   AL(d.poses, nc * 6) AL(d.poses_new, nc * 6) AL(d.pts, np * 3) AL(d.pts_new, np * 3)
   AL(d.campre_new, nc)
   AL(d.W, nobs * 18) AL(d.V, np * 6) AL(d.gp, np * 3) AL(d.Vinv, np * 6) AL(d.tp, np * 3)
-  AL(d.U, nc * 21) AL(d.gc, nc * 6) AL(d.cspart, (size_t)d.ncs * 27)
+  AL(d.U, nc * 27 + nw + nw * kMaxRanks)   // U | gc | cost_red | gslots: one block, one all-reduce per linearisation (multi-GPU)
+  d.gc = d.U + nc * 21; d.cost_red = d.gc + nc * 6; d.gslots = d.cost_red + nw;
+  AL(d.cspart, (size_t)d.ncs * 27)
   AL(d.sc2c, nc * 6) AL(d.sc2p, np * 3) AL(d.lin_part, (size_t)d.npchunk * 2)
-  AL(d.spart, (size_t)d.nlb * 36) AL(d.Su, (size_t)d.nbu * 36) AL(d.rpart, (size_t)d.ncs * 6)
-  AL(d.rhs, nf * 6) AL(d.rsum, nf * 6) AL(d.Minv, nf * 36)
+  AL(d.spart, (size_t)d.nlb * 36) AL(d.Su, (size_t)d.nbu * 36 + nf * 6) AL(d.rpart, (size_t)d.ncs * 6)
+  d.rsum = d.Su + (size_t)d.nbu * 36;      // Su | rsum: one block, one all-reduce per Schur step (multi-GPU)
+  AL(d.rhs, nf * 6) AL(d.Minv, nf * 36)
   AL(d.x, nf * 6) AL(d.r, nf * 6) AL(d.z, nf * 6) AL(d.p, nf * 6) AL(d.Ap, nf * 6) AL(h->pcg_pbuf, nf * 6) AL(h->pcg_rowdot, 2 * nf)
   AL(d.dp, np * 3) AL(d.step_part, (size_t)d.npchunk * 4) AL(d.ls_part, (size_t)d.npchunk * 3)
   AL(d.w_radius, nw) AL(d.w_decf, nw) AL(d.w_cost, nw) AL(d.w_gmax, nw)
-  AL(d.w_gd, nw * 4)   // one block: a multi-GPU solve all-reduces the four step scalars in one call
-  d.w_dDd = d.w_gd + nw; d.w_x2 = d.w_gd + 2 * nw; d.w_dr = d.w_gd + 3 * nw;
+  AL(d.w_gd, nw * 4 + nw * kMaxRanks)   // one block: a multi-GPU solve all-reduces the four step scalars and the max-norm slots in one call
+  d.w_dDd = d.w_gd + nw; d.w_x2 = d.w_gd + 2 * nw; d.w_dr = d.w_gd + 3 * nw; d.dslots = d.w_gd + 4 * nw;
   AL(d.w_dmax, nw + 1)   // + one slot: the ranks' agreed time-out flag
   AL(d.w_ls_red, nw * 3) AL(d.w_step2, nw) AL(d.w_cand, nw)
   AL(d.w_ls_x, nw) AL(d.w_ls_px, nw) AL(d.w_ls_pf, nw) AL(d.w_ls_pg, nw)
@@ -306,10 +309,8 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   CUDA_TRY(cudaMemsetAsync(d.V, 0, std::max<size_t>(1, np * 6) * 8, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.gp, 0, std::max<size_t>(1, np * 3) * 8, h->stream));
   // camera-side sums are only written where a chunk contributes: the rest stays zero for good
-  CUDA_TRY(cudaMemsetAsync(d.U, 0, std::max<size_t>(1, nc * 21) * 8, h->stream));
-  CUDA_TRY(cudaMemsetAsync(d.gc, 0, std::max<size_t>(1, nc * 6) * 8, h->stream));
-  CUDA_TRY(cudaMemsetAsync(d.Su, 0, std::max<size_t>(1, (size_t)d.nbu * 36) * 8, h->stream));
-  CUDA_TRY(cudaMemsetAsync(d.rsum, 0, std::max<size_t>(1, nf * 6) * 8, h->stream));
+  CUDA_TRY(cudaMemsetAsync(d.U, 0, std::max<size_t>(1, nc * 27 + nw + nw * kMaxRanks) * 8, h->stream));   // U | gc | cost_red | gslots
+  CUDA_TRY(cudaMemsetAsync(d.Su, 0, std::max<size_t>(1, (size_t)d.nbu * 36 + nf * 6) * 8, h->stream));   // Su | rsum
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   {
     h->lin_smem = lin_smem_bytes(H.max_chunk_obs, H.max_chunk_pts, H.max_slots);
@@ -529,15 +530,14 @@ static int do_linearize(sba_handle h, bool keep_cost = false, bool fork_tail = f
   }
   LAUNCH(h, k_assemble_cams, d.Nf, kAsmThreads, d);
   if (h->comm.active()) {
+    // ONE packed all-reduce per linearisation: U | gc | window cost | projected-gradient max (a slot per rank)
+    const int world = h->comm.world;
+    LAUNCH(h, k_lin_finish_local, d.nwin, kThreads, d, h->comm.rank, world);
     std::string _err;
-    if (!h->comm.allreduce(d.U, (size_t)d.Nc * 21, false, h->stream, &_err) ||
-        !h->comm.allreduce(d.gc, (size_t)d.Nc * 6, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
-  }
-  LAUNCH(h, k_lin_finish, d.nwin, kThreads, d, P, keep_cost ? 1 : 0);
-  if (h->comm.active()) {
-    std::string _err;
-    if ((!keep_cost && !h->comm.allreduce(d.w_cost, (size_t)d.nwin, false, h->stream, &_err)) ||
-        !h->comm.allreduce(d.w_gmax, (size_t)d.nwin, true, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+    if (!h->comm.allreduce(d.U, (size_t)d.Nc * 27 + (size_t)d.nwin + (size_t)d.nwin * world, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+    LAUNCH(h, k_lin_finish_global, d.nwin, kThreads, d, P, keep_cost ? 1 : 0, world);
+  } else {
+    LAUNCH(h, k_lin_finish, d.nwin, kThreads, d, P, keep_cost ? 1 : 0);
   }
   if (!h->jacobi_done) {
     LAUNCH(h, k_jacobi_scale, cdiv((int64_t)d.Nc * 6 + (int64_t)d.Np * 3, 256), 256, d);
@@ -558,8 +558,7 @@ static int do_schur(sba_handle h) {
   if (fused) { CUDA_TRY(cudaGetLastError()); return SBA_OK; }
   if (h->comm.active()) {
     std::string _err;
-    if (!h->comm.allreduce(d.Su, (size_t)d.nbu * 36, false, h->stream, &_err) ||
-        !h->comm.allreduce(d.rsum, (size_t)d.Nf * 6, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+    if (!h->comm.allreduce(d.Su, (size_t)d.nbu * 36 + (size_t)d.Nf * 6, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }   // Su | rsum
   }
   LAUNCH(h, k_cam_prepare, cdiv(d.Nf, 64), 64, d);
   CUDA_TRY(cudaGetLastError());
@@ -703,9 +702,11 @@ static int do_step(sba_handle h, int* ls_rounds) {
   LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P);
   LAUNCH(h, k_cam_step, d.nwin, kThreads, d, rank);
   if (h->comm.active()) {
-    std::string _err;   // w_gd, w_dDd, w_x2, w_dr are one contiguous block
-    if (!h->comm.allreduce(d.w_gd, (size_t)d.nwin * 4, false, h->stream, &_err) ||
-        !h->comm.allreduce(d.w_dmax, (size_t)d.nwin, true, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+    std::string _err;   // w_gd, w_dDd, w_x2, w_dr and the max-norm slots are one contiguous block: one all-reduce
+    const int world = h->comm.world;
+    LAUNCH(h, k_slots_put, cdiv((int64_t)d.nwin * world, 128), 128, d.dslots, d.w_dmax, d.nwin, h->comm.rank, world);
+    if (!h->comm.allreduce(d.w_gd, (size_t)d.nwin * 4 + (size_t)d.nwin * world, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+    LAUNCH(h, k_slots_max, cdiv(d.nwin, 128), 128, d.w_dmax, d.dslots, d.nwin, world);
   }
   int rounds = 0;
   for (;;) {
@@ -1191,7 +1192,7 @@ int sba_comm_unique_id(uint8_t id[128]) {
 }
 
 int sba_comm_init(sba_handle h, int32_t rank, int32_t world_size, const uint8_t id[128]) {
-  if (!h || h->device < 0 || world_size < 1 || rank < 0 || rank >= world_size) { set_error("bad comm arguments"); return SBA_INVALID_ARGUMENT; }
+  if (!h || h->device < 0 || world_size < 1 || world_size > kMaxRanks || rank < 0 || rank >= world_size) { set_error("bad comm arguments (1 <= world_size <= 16)"); return SBA_INVALID_ARGUMENT; }
   std::string err;
   if (!nccl_api().load(&err)) { set_error(err); return SBA_NCCL_ERROR; }
   CUDA_TRY(cudaSetDevice(h->device));

@@ -14,6 +14,8 @@ struct DevParams {   // solver constants, by value
   int32_t debug;       // SBA_DEBUG_LS: trace the line search of window 0 (device printf)
 };
 
+constexpr int kMaxRanks = 16;    // ranks of one point-sharded solve (slots of the max-by-sum exchange)
+
 struct Dev {
   int32_t Nc, Np, Nf, nwin, nbu, npchunk, ncs, nlb;
   int64_t Nobs;
@@ -38,7 +40,8 @@ struct Dev {
   double *W;                     // [Nobs*18] point order
   double *V, *gp;                // [Np*6], [Np*3]
   double *Vinv, *tp;             // [Np*6], [Np*3]
-  double *U, *gc;                // [Nc*21], [Nc*6]
+  double *U, *gc;                // [Nc*21], [Nc*6]   one block with cost_red and gslots behind: ONE all-reduce per linearisation
+  double *cost_red, *gslots;     // [nwin] window cost partial of this rank; [kMaxRanks*nwin] projected-gradient max, a slot per rank
   double *cspart;                // [ncs*27] per chunk-slot partial of U (21) and gc (6)
   double *sc2c, *sc2p;           // Jacobi scale^2 [Nc*6], [Np*3]
   double *lin_part;              // [npchunk*2] cost, gmax
@@ -47,7 +50,7 @@ struct Dev {
   double *spart;                 // [nlb*36] per local-block partial of sum W Vinv W^T
   double *Su;                    // [nbu*36]
   double *rpart;                 // [ncs*6] per chunk-slot partial of sum W tp
-  double *rsum;                  // [Nf*6] sum over observations of W tp per free camera
+  double *rsum;                  // [Nf*6] sum over observations of W tp per free camera (directly behind Su: one all-reduce)
   double *rhs;                   // [Nf*6]
   double *Minv;                  // [Nf*36]
   // ---- PCG vectors [Nf*6]
@@ -62,7 +65,8 @@ struct Dev {
   // ---- per-window scalars [nwin]
   double *w_radius, *w_decf, *w_cost, *w_cand, *w_gmax;
   double *w_gd, *w_dDd, *w_dr, *w_x2;     // one block [4*nwin] (all-reduced together on multi-GPU)
-  double *w_dmax;                          // max-norm of the step (all-reduced with max)
+  double *w_dmax;                          // max-norm of the step
+  double *dslots;                          // [kMaxRanks*nwin] behind w_gd..w_dr: every rank's max-norm, summed into its own slot
   double *w_ls_red;                        // [3*nwin] trial cost, directional derivative, |step|^2 (raw sums)
   double *w_step2;
   // projected Armijo line search state (sba_linesearch.cuh)

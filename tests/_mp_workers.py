@@ -105,3 +105,32 @@ def gpu_sharded_worker(rank, world, port, out_dir):
     dist.barrier()
     ss.solver.close()
     dist.destroy_process_group()
+
+
+def gpu_sharded_global_worker(rank, world, port, out_dir):
+    """NCCL, one GPU per rank: a C4-shaped loop (454 poses / 100k points) point-sharded, reduced system factored by the
+    replicated block-sparse Cholesky; then the same problem under a tiny wall-clock limit (the ranks must agree on the
+    time-out, ADVICE r1: a rank-local decision leaves the peers inside an all-reduce)."""
+    import torch
+    dist = _init(rank, world, port, "gloo")
+    torch.cuda.set_device(rank)
+    from stereo_orb_slam_b200 import Solver, default_options, pack_window, synthetic
+    from stereo_orb_slam_b200.parallel import ShardedSolver
+    smap = synthetic.make_config("C4", scale=0.1)
+    w = pack_window(smap, 0, smap.num_frames)
+    args = (w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r)
+    opt = default_options(max_time_s=0.0, max_iterations=12)
+    ss = ShardedSolver(rank)
+    poses, points, s = ss.solve(*args, options=opt)
+    pt, xt, st = ss.solve(*args, options=default_options(max_time_s=5e-3))
+    got = [None] * world
+    dist.all_gather_object(got, dict(term=st["termination_name"], it=st["iterations"], cost=st["final_cost"]))
+    if rank == 0:
+        p1, x1, s1 = Solver(0).solve(*args, options=opt)
+        np.savez(os.path.join(out_dir, "result.npz"), poses=poses, points=points, cost=s["final_cost"], it=s["iterations"],
+                 pcg=s["pcg_iterations"], poses1=p1, points1=x1, cost1=s1["final_cost"], it1=s1["iterations"],
+                 t_term=np.array([g["term"] for g in got]), t_it=np.array([g["it"] for g in got]),
+                 t_cost=np.array([g["cost"] for g in got]), t_init=st["initial_cost"])
+    dist.barrier()
+    ss.solver.close()
+    dist.destroy_process_group()

@@ -67,3 +67,20 @@ def test_point_sharded_solve_equals_single_gpu(tmp_path):
     assert np.abs(r["poses"][:, :3] - r["poses1"][:, :3]).max() < 1e-5
     assert np.abs(r["poses"][:, 3:] - r["poses1"][:, 3:]).max() < 1e-4
     assert np.abs(r["points"] - r["points1"]).max() < 1e-4
+
+
+@pytest.mark.gpu
+def test_point_sharded_global_problem_factors_exactly_and_times_out_together(tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs (run with gpurun --gpus 2)")
+    spawn(workers.gpu_sharded_global_worker, 2, tmp_path)
+    r = np.load(tmp_path / "result.npz")
+    # exact reduced solve on both sides: the sharded trajectory equals the single-GPU one to summation order
+    assert int(r["pcg"]) == 0 and int(r["it"]) == int(r["it1"]) == 12
+    assert abs(r["cost"] - r["cost1"]) <= 1e-9 * r["cost1"]
+    assert np.abs(r["poses"] - r["poses1"]).max() < 1e-7 and np.abs(r["points"] - r["points1"]).max() < 1e-6
+    # wall-clock limit: every rank stops with max_time after the SAME iteration with the same cost
+    assert all(t == "max_time" for t in r["t_term"])
+    assert len(set(r["t_it"].tolist())) == 1 and len(set(r["t_cost"].tolist())) == 1
+    assert 0 < r["t_it"][0] < 50 and r["t_cost"][0] < r["t_init"]

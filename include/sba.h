@@ -169,14 +169,15 @@ int sba_get_schur_values(sba_handle h, double* blocks, double* rhs, double* solu
 int sba_get_sorted_views(sba_handle h, int32_t* by_point, int32_t* by_camera);
 /* Symbolic phase of the exact block-sparse Cholesky used when a window has more than 64 free cameras (the global BA
  * calls, src/slam.cpp:156; stands in for CHOLMOD's analysis, src/bundle_adjuster.cpp:26-29).  info = {block columns n,
- * blocks in L, block products, elimination-tree levels}; call once with NULL arrays for the sizes.  perm [n] new -> old
+ * blocks in L, block products, levels, chains}; call once with NULL arrays for the sizes.  perm [n] new -> old
  * free-camera index; col_ptr [n+1] / row_idx [nnzL] pattern of L (diagonal first); init_src [nnzL] block of
  * sba_get_schur_pattern's UPPER blocks that lands there (b, ~b = transposed, INT32_MIN = fill); upd_ptr [nnzL+1] /
- * upd_a, upd_b [nupd] products L_a L_b^T each block receives; lvl_ptr [levels+1] / lvl_cols [n] level sets.
+ * upd_a, upd_b [nupd] products L_a L_b^T each block receives; lvl_ptr [levels+1] / lvl_cols, lvl_len [chains]: level sets
+ * of the elimination tree's chains (columns lvl_cols[c] .. lvl_cols[c] + lvl_len[c] - 1, each the only child of the next).
  * SBA_INVALID_ARGUMENT when the structure has no sparse factorisation. */
-int sba_get_factor_symbolic(sba_handle h, int64_t info[4], int32_t* perm, int32_t* col_ptr, int32_t* row_idx,
+int sba_get_factor_symbolic(sba_handle h, int64_t info[5], int32_t* perm, int32_t* col_ptr, int32_t* row_idx,
                             int32_t* init_src, int64_t* upd_ptr, int32_t* upd_a, int32_t* upd_b, int32_t* lvl_ptr,
-                            int32_t* lvl_cols);
+                            int32_t* lvl_cols, int32_t* lvl_len);
 int32_t sba_num_free_cameras(sba_handle h);
 /* number of kernels launched by this handle so far (bench.py's gpu_launches) */
 int64_t sba_launch_count(sba_handle h);

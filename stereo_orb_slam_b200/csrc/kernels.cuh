@@ -1159,6 +1159,209 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
   if (tid == 0 && bad != 0) d.w_fail[w] = 1;
 }
 
+// ---- banded windows: the whole factorisation in ONE CTA's shared memory ------------------------------------
+// A sliding window's reduced matrix is banded in the reference's frame order (co-visibility reaches a few keyframes
+// back: C2 has 322 of 1225 lower blocks), and Cholesky fill stays inside the monotone column envelope: column k holds
+// block rows k..last[k], last[] made non-decreasing over each column's reach.  When the envelope of every window fits
+// shared memory (C2: 343 blocks = 99 KB; a dense 9-camera window: 45 blocks) one CTA per window runs the right-looking
+// block Cholesky with nothing but CTA barriers on the critical path:
+//   (a) warp 0: 6x6 Cholesky of the diagonal block across six lanes (rows in registers, columns handed round by
+//       shuffles, 1/L_jj by rsqrt) and the inverse of the factor, one column per lane
+//   (b) panel L_ik = A_ik Linv^T for the m = last[k] - k rows below, y_k = Linv y_k
+//   (c) trailing update A_ij -= L_ik L_jk^T over the m (m + 1) / 2 blocks of the envelope it touches, a thread per
+//       element; y_j -= L_jk y_k
+// and the back substitution by warp 0 alone.  Fixed order throughout: bit-reproducible.
+constexpr int kBandThreads = 256;
+
+__host__ __device__ __forceinline__ size_t chol_band_smem_bytes(int nf, int env_blocks) {
+  return ((size_t)env_blocks * 36 + (size_t)nf * 36 + (size_t)nf * 6 + 48) * 8 + ((size_t)2 * nf + 2) * 4;
+}
+
+// Lanes 0..5 of the calling warp hold row `lane` of a symmetric positive definite 6x6 block in a[0..5] (lower part
+// read).  On return every lane j < 6 holds COLUMN j of the inverse of its lower Cholesky factor in x[0..5] (x[i] =
+// Linv[i][j], zero above the diagonal).  Returns false (on all lanes) when a pivot is not positive.
+__device__ __forceinline__ bool warp_chol6_inverse(double (&a)[6], double (&x)[6], int lane) {
+  double inv[6];
+  bool ok = true;
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    const double djj = __shfl_sync(0xffffffffu, a[j], j);
+    ok = ok && (djj > 0.0) && isfinite(djj);
+    inv[j] = rsqrt(ok ? djj : 1.0);
+    const double lij = a[j] * inv[j];             // lane i: L[i][j] (meaningful for i >= j; L[j][j] = d * rsqrt(d))
+    a[j] = lij;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) if (c > j) {
+      const double lcj = __shfl_sync(0xffffffffu, lij, c);
+      if (lane >= c) a[c] -= lij * lcj;
+    }
+  }
+  // every lane gets the strictly lower part of L, then lane j solves L x = e_j
+  double L[6][6];
+#pragma unroll
+  for (int i = 0; i < 6; ++i)
+#pragma unroll
+    for (int t = 0; t < 6; ++t) if (t < i) L[i][t] = __shfl_sync(0xffffffffu, a[t], i);
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    double acc = 0.0;
+#pragma unroll
+    for (int t = 0; t < 6; ++t) if (t < i) acc += L[i][t] * x[t];
+    // x[i] = (e_j[i] - acc) / L[i][i];  rows above the lane's own index stay zero
+    x[i] = (i < lane) ? 0.0 : ((i == lane) ? inv[i] : -acc * inv[i]);
+  }
+  return ok;
+}
+
+__global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t* __restrict__ band_last) {
+  extern __shared__ double smem[];
+  constexpr int T = kBandThreads;
+  const int w = blockIdx.x;
+  const int f0 = d.win_fc_off[w], f1 = d.win_fc_off[w + 1];
+  const int nf = f1 - f0, n = 6 * nf;
+  if (threadIdx.x == 0) d.w_pcg_it[w] = 0;
+  if (nf <= 0) return;
+  if (d.w_status[w] != 0 || d.w_fail[w] != 0) return;     // uniform per CTA; leaves x untouched (unused)
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ int bad;
+  __shared__ int env_total;
+  // per-window envelope: last[k] (window-local) and the block offset of every column
+  int* lastk = reinterpret_cast<int*>(smem);                 // [nf]
+  int* coff = lastk + nf;                                    // [nf + 1]
+  double* base = smem + (2 * nf + 2 + 1) / 2;                // 8-byte aligned past the 2 nf + 1 ints
+  if (tid == 0) {
+    bad = 0;
+    int acc = 0;
+    for (int k = 0; k < nf; ++k) { const int l = band_last[f0 + k] - f0; lastk[k] = l; coff[k] = acc; acc += l - k + 1; }
+    coff[nf] = acc; env_total = acc;
+  }
+  __syncthreads();
+  const int nenv = env_total;
+  double* A = base;                                          // [nenv * 36] column envelopes, block (k + ii, k) at coff[k] + ii
+  double* LI = A + (size_t)nenv * 36;                        // [nf * 36] inverse diagonal factors
+  double* y = LI + (size_t)nf * 36;                          // [n]
+  for (int i = tid; i < nenv * 36; i += T) A[i] = 0.0;
+  for (int i = tid; i < n; i += T) y[i] = d.rhs[(size_t)f0 * 6 + i];
+  __syncthreads();
+  {
+    // upper block (r, c), r <= c, of S  ->  lower block (c, r) = its transpose, in column r
+    const int b0 = d.diag_blk[f0];
+    const int b1 = (f1 < d.Nf) ? d.diag_blk[f1] : d.nbu;
+    for (int i = tid; i < (b1 - b0) * 36; i += T) {
+      const int b = b0 + i / 36, e = i % 36, er = e / 6, ec = e - 6 * er;
+      const int r = d.blk_row[b] - f0, c = d.blk_col[b] - f0;
+      A[(size_t)(coff[r] + (c - r)) * 36 + 6 * ec + er] = d.Su[(size_t)b * 36 + e];
+    }
+  }
+  __syncthreads();
+  for (int k = 0; k < nf; ++k) {
+    const int m = lastk[k] - k;
+    double* colk = A + (size_t)coff[k] * 36;
+    double* li = LI + (size_t)k * 36;
+    // (a) diagonal block
+    if (warp == 0) {
+      double a[6], x[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll
+      for (int c = 0; c < 6; ++c) a[c] = colk[6 * (lane < 6 ? lane : 0) + c];
+      if (!warp_chol6_inverse(a, x, lane) && lane == 0) bad = 1;
+      if (lane < 6) {
+#pragma unroll
+        for (int i = 0; i < 6; ++i) li[6 * i + lane] = x[i];
+      }
+    }
+    __syncthreads();
+    // (b) panel, a thread per block row (it reads its six entries before it writes them: in place), and the
+    //     right-hand side block by the last six threads (one warp: the barrier between reads and writes is a warp's)
+    for (int idx = tid; idx < m * 6; idx += T) {
+      double* row = colk + 36 + (size_t)(idx / 6) * 36 + 6 * (idx % 6);
+      double av[6], o[6];
+#pragma unroll
+      for (int t = 0; t < 6; ++t) av[t] = row[t];
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
+        double acc = 0.0;
+#pragma unroll
+        for (int t = 0; t < 6; ++t) if (t <= c) acc += av[t] * li[6 * c + t];
+        o[c] = acc;
+      }
+#pragma unroll
+      for (int t = 0; t < 6; ++t) row[t] = o[t];
+    }
+    if (warp == T / 32 - 1) {
+      const int c = lane - 26;                               // lanes 26..31
+      double yk = 0.0;
+      if (c >= 0) {
+#pragma unroll
+        for (int t = 0; t < 6; ++t) if (t <= c) yk += li[6 * c + t] * y[6 * k + t];
+      }
+      __syncwarp();
+      if (c >= 0) y[6 * k + c] = yk;
+    }
+    __syncthreads();
+    // (c) trailing update inside the envelope: block (k + ii, k + jj), 1 <= jj <= ii <= m, lives in column k + jj
+    const int npair = m * (m + 1) / 2;
+    for (int idx = tid; idx < npair * 36; idx += T) {
+      const int p = idx / 36, e = idx - 36 * p, r = e / 6, c = e - 6 * r;
+      int ii = (int)((sqrtf(8.f * (float)p + 1.f) - 1.f) * 0.5f);
+      while ((ii + 1) * (ii + 2) / 2 <= p) ++ii;
+      while (ii * (ii + 1) / 2 > p) --ii;
+      const int jj = p - ii * (ii + 1) / 2;                  // 0 <= jj <= ii < m
+      const double* Li = colk + (size_t)(1 + ii) * 36 + 6 * r;
+      const double* Lj = colk + (size_t)(1 + jj) * 36 + 6 * c;
+      const double acc = (Li[0] * Lj[0] + Li[1] * Lj[1] + Li[2] * Lj[2]) + (Li[3] * Lj[3] + Li[4] * Lj[4] + Li[5] * Lj[5]);
+      A[(size_t)(coff[k + 1 + jj] + (ii - jj)) * 36 + e] -= acc;
+    }
+    for (int idx = tid; idx < m * 6; idx += T) {
+      const int ii = idx / 6, r = idx - 6 * ii;
+      const double* Lr = colk + (size_t)(1 + ii) * 36 + 6 * r;
+      double acc = 0.0;
+#pragma unroll
+      for (int t = 0; t < 6; ++t) acc += Lr[t] * y[6 * k + t];
+      y[6 * (k + 1 + ii) + r] -= acc;
+    }
+    __syncthreads();
+  }
+  // back substitution by warp 0: x_k = Linv_kk^T (y_k - sum over the column's rows of L_ik^T x_i), five row groups of
+  // six lanes summed in lane order
+  if (warp == 0) {
+    const int ps = lane / 6, c = lane - 6 * ps;
+    for (int k = nf - 1; k >= 0; --k) {
+      const int m = lastk[k] - k;
+      const double* colk = A + (size_t)coff[k] * 36;
+      double acc = 0.0;
+      if (lane < 30)
+        for (int ii = ps; ii < m; ii += 5) {
+          const double* L = colk + (size_t)(1 + ii) * 36 + c;
+          const double* xi = y + 6 * (k + 1 + ii);
+          acc += (L[0] * xi[0] + L[6] * xi[1] + L[12] * xi[2]) + (L[18] * xi[3] + L[24] * xi[4] + L[30] * xi[5]);
+        }
+      double tot = acc;
+#pragma unroll
+      for (int q = 1; q < 5; ++q) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * q) & 31);
+      const double s = (lane < 6) ? y[6 * k + lane] - tot : 0.0;
+      double v = 0.0;
+#pragma unroll
+      for (int q = 0; q < 6; ++q) {
+        const double sq = __shfl_sync(0xffffffffu, s, q);
+        if (lane < 6 && q >= lane) v += LI[(size_t)k * 36 + 6 * q + lane] * sq;
+      }
+      __syncwarp();
+      if (lane < 6) y[6 * k + lane] = v;
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+  const bool fail = bad != 0;
+  for (int i = tid; i < n; i += T) {
+    const double v = y[i];
+    d.x[(size_t)f0 * 6 + i] = (fail || !isfinite(v)) ? 0.0 : v;
+    d.r[(size_t)f0 * 6 + i] = 0.0;                         // exact solve: no linear residual in the model change
+    if (!isfinite(v)) bad = 1;                             // benign race: every writer stores 1
+  }
+  __syncthreads();
+  if (tid == 0 && bad != 0) d.w_fail[w] = 1;
+}
+
 // The same factorisation for a mid-size window (a 50-keyframe sliding window: 294 unknowns, 1225 lower blocks =
 // 353 KB) on one thread-block CLUSTER of kCholCluster CTAs: block column j lives in the shared memory of CTA
 // j % kCholCluster, so every trailing update is a local shared-memory update.  Per block column k:

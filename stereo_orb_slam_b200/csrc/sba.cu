@@ -77,6 +77,7 @@ struct sba_handle_s {
   bool pcg_cluster_ok = false; size_t pcg_cluster_smem = 0; int pcg_rows_cap = 0, pcg_ent_cap = 0;   // one 8-CTA cluster per window (k_pcg_cluster)
   bool chol_ok = false, chol_in_smem = false; size_t chol_smem = 0; int chol_threads = kCholThreads;   // one CTA per window factors S exactly (k_chol_window)
   bool chol_cluster_ok = false; size_t chol_cluster_smem = 0;   // mid-size windows: one 8-CTA cluster per window (k_chol_cluster)
+  bool chol_band_ok = false; size_t chol_band_smem = 0; const int32_t* band_last = nullptr;   // banded windows: envelope in one CTA's shared memory (k_chol_band)
   size_t lin_smem = 0, schur_smem = 0;   // dynamic shared memory of the per-chunk kernels (largest chunk)
   // exact block-sparse Cholesky of the reduced system for windows of more than kCholMaxCams free cameras (k_spchol)
   SparseCholSymbolic sym; bool sym_ok = false; SpCholDev sp{}; bool spchol_ok = false; int spchol_blocks = 0; double time_symbolic_s = 0.0;
@@ -168,7 +169,7 @@ int sba_create(int device, sba_handle* out) {
       if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_coop, kThreads, 0) == cudaSuccess)
         h->coop_pcg_blocks = per_sm * sms;
       if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_spchol, kSpThreads, 0) == cudaSuccess)
-        h->spchol_blocks = std::min(per_sm, 2) * sms;
+        h->spchol_blocks = std::min(per_sm, 1) * sms;
     }
     if (e == cudaSuccess) {      // a private pool that keeps its freed blocks (no trim at synchronisation points): a
                                  // re-structure on the next Optimize call reuses them; the device's default pool is untouched
@@ -379,6 +380,31 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
       CUDA_TRY(cudaFuncSetAttribute(k_chol_window<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->chol_smem, 1024)));
       CUDA_TRY(cudaStreamSynchronize(h->stream));      // `off` is a local
     }
+    // banded windows: monotone column envelope of every window (Cholesky fill stays inside it); when the largest fits
+    // one CTA's shared memory the whole factorisation runs there (k_chol_band)
+    h->chol_band_ok = false; h->band_last = nullptr;
+    if (h->chol_ok && !std::getenv("SBA_NO_BAND")) {
+      std::vector<int32_t> last((size_t)H.Nf);
+      for (int f = 0; f < H.Nf; ++f) last[f] = f;
+      for (size_t b = 0; b < H.blk_row.size(); ++b) last[H.blk_row[b]] = std::max(last[H.blk_row[b]], H.blk_col[b]);
+      int64_t env_max = 0;
+      for (int w = 0; w < H.nwin; ++w) {
+        const int g0 = H.win_fc_off[w], g1 = H.win_fc_off[w + 1];
+        int64_t env = 0;
+        for (int k = g0; k < g1; ++k) {
+          if (k > g0) last[k] = std::max(last[k], std::min(last[k - 1], g1 - 1));   // a column reaches at least as far as the previous one (it receives its fill)
+          env += last[k] - k + 1;
+        }
+        env_max = std::max(env_max, env);
+      }
+      h->chol_band_smem = chol_band_smem_bytes(nf_max, (int)env_max);
+      if (h->chol_band_smem <= (size_t)200 * 1024) {
+        if ((rc = h->upload(&h->band_last, last))) return rc;
+        CUDA_TRY(cudaFuncSetAttribute(k_chol_band, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->chol_band_smem, 1024)));
+        CUDA_TRY(cudaStreamSynchronize(h->stream));      // `last` is a local
+        h->chol_band_ok = true;
+      }
+    }
     h->chol_cluster_smem = chol_cluster_smem_bytes(std::max(nf_max, 1));
     h->chol_cluster_ok = h->chol_ok && nf_max >= (std::getenv("SBA_FORCE_CLUSTER") ? 1 : 16) && H.nwin <= 64 &&
                          h->chol_cluster_smem <= (size_t)220 * 1024 && !std::getenv("SBA_NO_CLUSTER");
@@ -403,14 +429,15 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
       if ((rc = h->upload(&sp.rowl_col, Y.rowl_col))) return rc;
       if ((rc = h->upload(&sp.lvl_ptr, Y.lvl_ptr))) return rc;
       if ((rc = h->upload(&sp.lvl_cols, Y.lvl_cols))) return rc;
+      if ((rc = h->upload(&sp.lvl_len, Y.lvl_len))) return rc;
       if ((rc = h->alloc(&sp.Lv, (size_t)Y.nnzL() * 36))) return rc;
       if ((rc = h->alloc(&sp.Li, (size_t)Y.n * 36))) return rc;
       if ((rc = h->alloc(&sp.y, (size_t)Y.n * 6))) return rc;
       CUDA_TRY(cudaStreamSynchronize(h->stream));
       h->spchol_ok = true;
       if (std::getenv("SBA_TIMING"))
-        std::fprintf(stderr, "[sba] sparse Cholesky symbolic: %.3f ms, %d block columns, %lld blocks in L (%lld in S), %lld products, %d levels\n",
-                     1e3 * h->time_symbolic_s, Y.n, (long long)Y.nnzL(), (long long)H.blk_row.size(), (long long)Y.nupd(), Y.nlev);
+        std::fprintf(stderr, "[sba] sparse Cholesky symbolic: %.3f ms, %d block columns, %lld blocks in L (%lld in S), %lld products, %lld chains in %d levels\n",
+                     1e3 * h->time_symbolic_s, Y.n, (long long)Y.nnzL(), (long long)H.blk_row.size(), (long long)Y.nupd(), (long long)Y.nchain(), Y.nlev);
     }
   }
   h->time_structure_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
@@ -587,7 +614,9 @@ static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
     it = -1;
   } else if (d.Nf > 0 && h->chol_ok && opt->linear_solver != 1) {
     CUDA_TRY(cudaMemsetAsync(d.counters + 4, 0, 4, h->stream));
-    if (h->chol_cluster_ok) {
+    if (h->chol_band_ok && !std::getenv("SBA_FORCE_CLUSTER")) {
+      k_chol_band<<<d.nwin, kBandThreads, h->chol_band_smem, h->stream>>>(d, h->band_last);
+    } else if (h->chol_cluster_ok) {
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3((unsigned)d.nwin * kCholCluster); cfg.blockDim = dim3(kCholClThreads);
       cfg.dynamicSmemBytes = h->chol_cluster_smem; cfg.stream = h->stream;
@@ -1140,16 +1169,16 @@ int sba_get_sorted_views(sba_handle h, int32_t* by_point, int32_t* by_camera) {
   return SBA_OK;
 }
 
-int sba_get_factor_symbolic(sba_handle h, int64_t info[4], int32_t* perm, int32_t* col_ptr, int32_t* row_idx,
+int sba_get_factor_symbolic(sba_handle h, int64_t info[5], int32_t* perm, int32_t* col_ptr, int32_t* row_idx,
                             int32_t* init_src, int64_t* upd_ptr, int32_t* upd_a, int32_t* upd_b, int32_t* lvl_ptr,
-                            int32_t* lvl_cols) {
+                            int32_t* lvl_cols, int32_t* lvl_len) {
   if (!h || !h->has_structure) { set_error("no structure"); return SBA_INVALID_ARGUMENT; }
   if (!h->sym_ok) { set_error("this structure has no sparse factorisation (every window has <= 64 free cameras, or the pattern is too dense)"); return SBA_INVALID_ARGUMENT; }
   const SparseCholSymbolic& Y = h->sym;
-  if (info) { info[0] = Y.n; info[1] = Y.nnzL(); info[2] = Y.nupd(); info[3] = Y.nlev; }
+  if (info) { info[0] = Y.n; info[1] = Y.nnzL(); info[2] = Y.nupd(); info[3] = Y.nlev; info[4] = Y.nchain(); }
   auto cp = [](auto* dst, const auto& v) { if (dst && !v.empty()) std::memcpy(dst, v.data(), v.size() * sizeof(v[0])); };
   cp(perm, Y.perm); cp(col_ptr, Y.col_ptr); cp(row_idx, Y.row_idx); cp(init_src, Y.init_src); cp(upd_ptr, Y.upd_ptr);
-  cp(upd_a, Y.upd_a); cp(upd_b, Y.upd_b); cp(lvl_ptr, Y.lvl_ptr); cp(lvl_cols, Y.lvl_cols);
+  cp(upd_a, Y.upd_a); cp(upd_b, Y.upd_b); cp(lvl_ptr, Y.lvl_ptr); cp(lvl_cols, Y.lvl_cols); cp(lvl_len, Y.lvl_len);
   return SBA_OK;
 }
 

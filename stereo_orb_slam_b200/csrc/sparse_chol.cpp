@@ -266,22 +266,35 @@ std::string sparse_chol_symbolic(int32_t n, const std::vector<int32_t>& blk_row,
         C.rowl_blk[at] = y; C.rowl_col[at] = k;
       }
   }
-  // ---- level sets of the elimination tree
-  std::vector<int32_t> level(n, 0);
-  int nlev = 1;
+  // ---- chains and their level sets.  A chain is a run of consecutive columns j, j+1, ... in which every column is the
+  // ONLY child of the next one (the columns of a separator, and the whole top of the tree): its columns depend on each
+  // other in sequence, so one CTA factors the chain without a grid barrier in between.  Only the first column of a
+  // chain has children outside it; chains of one level are independent.
+  std::vector<int32_t> nkids(n, 0);
+  for (int j = 0; j < n; ++j) if (C.parent[j] >= 0) nkids[C.parent[j]]++;
+  std::vector<int32_t> chain_of(n, -1), chain_start, chain_len, chain_level;
+  for (int j = 0; j < n; ++j) {
+    const bool cont = j > 0 && C.parent[j - 1] == j && nkids[j] == 1;
+    if (cont) { chain_of[j] = chain_of[j - 1]; chain_len[chain_of[j]]++; }
+    else { chain_of[j] = (int32_t)chain_start.size(); chain_start.push_back(j); chain_len.push_back(1); chain_level.push_back(0); }
+  }
+  // children of a chain's first column belong to earlier chains (smaller indices): one ascending pass
   for (int j = 0; j < n; ++j) {
     const int32_t p = C.parent[j];
-    if (p >= 0) level[p] = std::max(level[p], level[j] + 1);
-    nlev = std::max(nlev, level[j] + 1);
+    if (p >= 0 && chain_of[p] != chain_of[j])
+      chain_level[chain_of[p]] = std::max(chain_level[chain_of[p]], chain_level[chain_of[j]] + 1);
   }
+  const int nchain = (int)chain_start.size();
+  int nlev = 1;
+  for (int c = 0; c < nchain; ++c) nlev = std::max(nlev, chain_level[c] + 1);
   C.nlev = nlev;
   C.lvl_ptr.assign(nlev + 1, 0);
-  for (int j = 0; j < n; ++j) C.lvl_ptr[level[j] + 1]++;
+  for (int c = 0; c < nchain; ++c) C.lvl_ptr[chain_level[c] + 1]++;
   for (int l = 0; l < nlev; ++l) C.lvl_ptr[l + 1] += C.lvl_ptr[l];
-  C.lvl_cols.resize(n);
+  C.lvl_cols.resize(nchain); C.lvl_len.resize(nchain);
   {
     std::vector<int32_t> cur(C.lvl_ptr.begin(), C.lvl_ptr.end() - 1);
-    for (int j = 0; j < n; ++j) C.lvl_cols[cur[level[j]]++] = j;
+    for (int c = 0; c < nchain; ++c) { const int32_t at = cur[chain_level[c]]++; C.lvl_cols[at] = chain_start[c]; C.lvl_len[at] = chain_len[c]; }
   }
   return std::string();
 }

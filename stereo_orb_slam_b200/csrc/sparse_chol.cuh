@@ -21,19 +21,59 @@ struct SpCholDev {
   const int32_t *perm, *col_ptr, *row_idx, *init_src;
   const int64_t* upd_ptr;
   const int32_t *upd_a, *upd_b;
-  const int32_t *rowl_ptr, *rowl_blk, *rowl_col, *lvl_ptr, *lvl_cols;
+  const int32_t *rowl_ptr, *rowl_blk, *rowl_col, *lvl_ptr, *lvl_cols, *lvl_len;
   double* Lv;     // [nnzL * 36] blocks of L, row-major 6x6 (block (i, j): rows of i, columns of j)
   double* Li;     // [n * 36]    inverse diagonal factors (lower)
   double* y;      // [n * 6]     forward-substituted right-hand side, then the solution (new order)
 };
 
-constexpr int kSpThreads = 256;
+constexpr int kSpThreads = 512;
 constexpr int kSpWarps = kSpThreads / 32;
-constexpr int kSpStage = 48;      // blocks of one column staged in shared memory between gather and panel (13.5 KB)
+constexpr int kSpStage = 64;      // blocks of one column staged in shared memory between gather and panel (18 KB)
 
-__global__ void __launch_bounds__(kSpThreads) k_spchol(Dev d, SpCholDev sc) {
+// sum over the products [u0, u1) of one block's list of L_a L_b^T, on the FP64 tensor cores: two m8n8k4 MMAs per
+// product, operands straight from L2 (four products = 16 loads in flight per lane before the first MMA), even and
+// odd products on two accumulator chains.  Lane (g, t) = (lane / 4, lane % 4) ends up with elements 6 g + 2 t, + 1.
+__device__ __forceinline__ void sp_gather(const SpCholDev& sc, int64_t u0, int64_t u1, int lane, double& r0, double& r1) {
+  const int g = lane >> 2, t4 = lane & 3;
+  const bool f0 = g < 6, f1 = g < 6 && t4 < 2;
+  const int o0 = 6 * (f0 ? g : 0) + t4, o1 = 6 * (f1 ? g : 0) + (f1 ? t4 + 4 : 0);
+  double c0 = 0.0, c1 = 0.0, e0 = 0.0, e1 = 0.0;
+  for (int64_t ub = u0; ub < u1; ub += 32) {
+    const int m = (int)min((int64_t)32, u1 - ub);
+    const int ia = (lane < m) ? __ldg(sc.upd_a + ub + lane) : 0;
+    const int ib = (lane < m) ? __ldg(sc.upd_b + ub + lane) : 0;
+    int u = 0;
+    for (; u + 3 < m; u += 4) {
+      double a0[4], a1[4], b0[4], b1[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const double* A = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ia, u + q) * 36;
+        const double* B = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ib, u + q) * 36;
+        a0[q] = f0 ? __ldcg(A + o0) : 0.0; b0[q] = f0 ? __ldcg(B + o0) : 0.0;
+        a1[q] = f1 ? __ldcg(A + o1) : 0.0; b1[q] = f1 ? __ldcg(B + o1) : 0.0;
+      }
+      dmma884(c0, c1, a0[0], b0[0]); dmma884(c0, c1, a1[0], b1[0]);
+      dmma884(e0, e1, a0[1], b0[1]); dmma884(e0, e1, a1[1], b1[1]);
+      dmma884(c0, c1, a0[2], b0[2]); dmma884(c0, c1, a1[2], b1[2]);
+      dmma884(e0, e1, a0[3], b0[3]); dmma884(e0, e1, a1[3], b1[3]);
+    }
+    for (; u < m; ++u) {
+      const double* A = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ia, u) * 36;
+      const double* B = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ib, u) * 36;
+      const double a00 = f0 ? __ldcg(A + o0) : 0.0, b00 = f0 ? __ldcg(B + o0) : 0.0;
+      const double a01 = f1 ? __ldcg(A + o1) : 0.0, b01 = f1 ? __ldcg(B + o1) : 0.0;
+      if (u & 1) { dmma884(e0, e1, a00, b00); dmma884(e0, e1, a01, b01); }
+      else { dmma884(c0, c1, a00, b00); dmma884(c0, c1, a01, b01); }
+    }
+  }
+  r0 = c0 + e0; r1 = c1 + e1;
+}
+
+__global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
   __shared__ double col_st[kSpStage * 36];
+  __shared__ double part[kSpWarps * 36];      // slice partials when a block's product list is split over several warps
   __shared__ double akk[36], li_s[36], tj[8];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (d.nwin == 1 && (d.w_status[0] != 0 || d.w_fail[0] != 0)) {     // uniform over the grid; leaves x untouched (unused)
@@ -54,155 +94,176 @@ __global__ void __launch_bounds__(kSpThreads) k_spchol(Dev d, SpCholDev sc) {
     for (int w = blockIdx.x * kSpThreads + tid; w < d.nwin; w += gridDim.x * kSpThreads) d.w_pcg_it[w] = 0;
   }
   grid.sync();
-  // ---- 1: factorisation + forward substitution, level by level
+  // ---- 1: factorisation + forward substitution: chains of one level in parallel, a chain's columns in sequence
   const int g = lane >> 2, t4 = lane & 3;
-  const bool f0 = g < 6, f1 = g < 6 && t4 < 2;
-  const int o0 = 6 * (f0 ? g : 0) + t4, o1 = 6 * (f1 ? g : 0) + (f1 ? t4 + 4 : 0);
+  const bool fout = g < 6 && t4 < 3;
   const int ps = lane / 6, ri = lane - 6 * ps;
   for (int lvl = 0; lvl < sc.nlev; ++lvl) {
     const int c_begin = __ldg(sc.lvl_ptr + lvl), c_end = __ldg(sc.lvl_ptr + lvl + 1);
     for (int ci = c_begin + blockIdx.x; ci < c_end; ci += gridDim.x) {
-      const int j = __ldg(sc.lvl_cols + ci);
-      const int b0 = __ldg(sc.col_ptr + j), nb = __ldg(sc.col_ptr + j + 1) - b0;
-      const bool staged = nb <= kSpStage;
-      // (a) gather: block = A_ij - sum_k L_ik L_jk^T, one warp per block, products in list order on two
-      //     accumulator chains; update indices come 32 at a time by one coalesced load and are handed round
-      for (int bi = warp; bi < nb; bi += kSpWarps) {
-        const int blk = b0 + bi;
-        const int64_t u0 = sc.upd_ptr[blk], u1 = sc.upd_ptr[blk + 1];
-        double c0 = 0.0, c1 = 0.0, e0 = 0.0, e1 = 0.0;
-        for (int64_t ub = u0; ub < u1; ub += 32) {
-          const int m = (int)min((int64_t)32, u1 - ub);
-          const int ia = (lane < m) ? __ldg(sc.upd_a + ub + lane) : 0;
-          const int ib = (lane < m) ? __ldg(sc.upd_b + ub + lane) : 0;
-          int u = 0;
-          for (; u + 1 < m; u += 2) {
-            const double* A0 = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ia, u) * 36;
-            const double* B0 = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ib, u) * 36;
-            const double* A1 = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ia, u + 1) * 36;
-            const double* B1 = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ib, u + 1) * 36;
-            const double a00 = f0 ? __ldcg(A0 + o0) : 0.0, b00 = f0 ? __ldcg(B0 + o0) : 0.0;
-            const double a01 = f1 ? __ldcg(A0 + o1) : 0.0, b01 = f1 ? __ldcg(B0 + o1) : 0.0;
-            const double a10 = f0 ? __ldcg(A1 + o0) : 0.0, b10 = f0 ? __ldcg(B1 + o0) : 0.0;
-            const double a11 = f1 ? __ldcg(A1 + o1) : 0.0, b11 = f1 ? __ldcg(B1 + o1) : 0.0;
-            dmma884(c0, c1, a00, b00); dmma884(c0, c1, a01, b01);
-            dmma884(e0, e1, a10, b10); dmma884(e0, e1, a11, b11);
+      const int j0 = __ldg(sc.lvl_cols + ci), jn = j0 + __ldg(sc.lvl_len + ci);
+      for (int j = j0; j < jn; ++j) {
+        const int b0 = __ldg(sc.col_ptr + j), nb = __ldg(sc.col_ptr + j + 1) - b0;
+        const bool staged = nb <= kSpStage;
+        // (a) gather: block = A_ij - sum_k L_ik L_jk^T.  Long columns: a warp per block.  Short ones (the separators
+        //     at the top of the tree: few blocks, long lists): every block's list is cut into S contiguous slices,
+        //     a warp per slice, slices summed in order afterwards.
+        const int S = nb >= kSpWarps ? 1 : kSpWarps / nb;
+        if (S == 1) {
+          for (int bi = warp; bi < nb; bi += kSpWarps) {
+            const int blk = b0 + bi;
+            double r0, r1;
+            sp_gather(sc, sc.upd_ptr[blk], sc.upd_ptr[blk + 1], lane, r0, r1);
+            if (fout) {
+              const int e = 6 * g + 2 * t4;
+              const double2 a = __ldcg(reinterpret_cast<const double2*>(sc.Lv + (size_t)blk * 36 + e));
+              const double2 v = make_double2(a.x - r0, a.y - r1);
+              if (bi == 0) { akk[e] = v.x; akk[e + 1] = v.y; }
+              else if (staged) { col_st[bi * 36 + e] = v.x; col_st[bi * 36 + e + 1] = v.y; }
+              else __stcg(reinterpret_cast<double2*>(sc.Lv + (size_t)blk * 36 + e), v);
+            }
           }
-          if (u < m) {
-            const double* A0 = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ia, u) * 36;
-            const double* B0 = sc.Lv + (size_t)__shfl_sync(0xffffffffu, ib, u) * 36;
-            const double a00 = f0 ? __ldcg(A0 + o0) : 0.0, b00 = f0 ? __ldcg(B0 + o0) : 0.0;
-            const double a01 = f1 ? __ldcg(A0 + o1) : 0.0, b01 = f1 ? __ldcg(B0 + o1) : 0.0;
-            dmma884(c0, c1, a00, b00); dmma884(c0, c1, a01, b01);
+        } else {
+          const int bi = warp / S, sl = warp - bi * S;
+          if (bi < nb) {
+            const int64_t u0 = sc.upd_ptr[b0 + bi], len = sc.upd_ptr[b0 + bi + 1] - u0;
+            double r0, r1;
+            sp_gather(sc, u0 + len * sl / S, u0 + len * (sl + 1) / S, lane, r0, r1);
+            if (fout) { part[warp * 36 + 6 * g + 2 * t4] = r0; part[warp * 36 + 6 * g + 2 * t4 + 1] = r1; }
           }
         }
-        if (f0 && t4 < 3) {
-          const int e = 6 * g + 2 * t4;
-          const double2 a = __ldcg(reinterpret_cast<const double2*>(sc.Lv + (size_t)blk * 36 + e));
-          const double2 v = make_double2(a.x - (c0 + e0), a.y - (c1 + e1));
-          if (bi == 0) { akk[e] = v.x; akk[e + 1] = v.y; }
-          else if (staged) { col_st[bi * 36 + e] = v.x; col_st[bi * 36 + e + 1] = v.y; }
-          else __stcg(reinterpret_cast<double2*>(sc.Lv + (size_t)blk * 36 + e), v);
-        }
-      }
-      // (b) right-hand side: t_j = rhs_j - sum_k L_jk y_k  (last warp; five entry groups of six rows, summed in lane order)
-      if (warp == kSpWarps - 1) {
-        double acc = 0.0;
-        if (lane < 30) {
-          const int r1 = __ldg(sc.rowl_ptr + j + 1);
-          for (int e = __ldg(sc.rowl_ptr + j) + ps; e < r1; e += 5) {
-            const double* L = sc.Lv + (size_t)__ldg(sc.rowl_blk + e) * 36 + 6 * ri;
-            const double* yk = sc.y + (size_t)__ldg(sc.rowl_col + e) * 6;
-            acc += (__ldcg(L) * __ldcg(yk) + __ldcg(L + 1) * __ldcg(yk + 1) + __ldcg(L + 2) * __ldcg(yk + 2)) +
-                   (__ldcg(L + 3) * __ldcg(yk + 3) + __ldcg(L + 4) * __ldcg(yk + 4) + __ldcg(L + 5) * __ldcg(yk + 5));
-          }
-        }
-        double tot = acc;
-#pragma unroll
-        for (int q = 1; q < 5; ++q) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * q) & 31);
-        if (lane < 6) tj[lane] = d.rhs[(size_t)__ldg(sc.perm + j) * 6 + lane] - tot;
-      }
-      __syncthreads();
-      // (c) diagonal block: factor, keep the inverse of the factor
-      if (tid == 0) {
-        double li[36];
-        if (!chol6_inverse_factor(akk, li)) d.w_fail[d.fcam_win[__ldg(sc.perm + j)]] = 1;   // benign race: every writer stores 1
-#pragma unroll
-        for (int i = 0; i < 36; ++i) { li_s[i] = li[i]; __stcg(sc.Li + (size_t)j * 36 + i, li[i]); }
-      }
-      __syncthreads();
-      // (d) panel L_ij = A_ij Linv^T (i > j) and y_j = Linv t_j
-      if (staged) {
-        for (int idx = tid; idx < (nb - 1) * 36; idx += kSpThreads) {
-          const int bi = 1 + idx / 36, e = idx % 36, r = e / 6, c = e - 6 * r;
+        // (b) right-hand side: t_j = rhs_j - sum_k L_jk y_k  (last warp; five entry groups of six rows, summed in lane order)
+        if (warp == kSpWarps - 1) {
           double acc = 0.0;
+          if (lane < 30) {
+            const int r1 = __ldg(sc.rowl_ptr + j + 1);
+            for (int e = __ldg(sc.rowl_ptr + j) + ps; e < r1; e += 5) {
+              const double* L = sc.Lv + (size_t)__ldg(sc.rowl_blk + e) * 36 + 6 * ri;
+              const double* yk = sc.y + (size_t)__ldg(sc.rowl_col + e) * 6;
+              acc += (__ldcg(L) * __ldcg(yk) + __ldcg(L + 1) * __ldcg(yk + 1) + __ldcg(L + 2) * __ldcg(yk + 2)) +
+                     (__ldcg(L + 3) * __ldcg(yk + 3) + __ldcg(L + 4) * __ldcg(yk + 4) + __ldcg(L + 5) * __ldcg(yk + 5));
+            }
+          }
+          double tot = acc;
 #pragma unroll
-          for (int q = 0; q < 6; ++q) if (q <= c) acc += col_st[bi * 36 + 6 * r + q] * li_s[6 * c + q];
-          __stcg(sc.Lv + (size_t)(b0 + bi) * 36 + e, acc);
+          for (int q = 1; q < 5; ++q) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * q) & 31);
+          if (lane < 6) tj[lane] = d.rhs[(size_t)__ldg(sc.perm + j) * 6 + lane] - tot;
         }
-      } else {
-        // long columns (dense patterns) stay in L2: a thread per block row, in place (it reads its row before it writes it)
-        for (int idx = tid; idx < (nb - 1) * 6; idx += kSpThreads) {
-          double* row = sc.Lv + (size_t)(b0 + 1 + idx / 6) * 36 + 6 * (idx % 6);
-          double a[6], o[6];
+        __syncthreads();
+        if (S > 1) {
+          // slices of every block summed in slice order (nb < kSpWarps <= kSpStage: the column is staged)
+          for (int idx = tid; idx < nb * 36; idx += kSpThreads) {
+            const int bi = idx / 36, e = idx - 36 * bi;
+            double sum = 0.0;
+            for (int sl = 0; sl < S; ++sl) sum += part[(bi * S + sl) * 36 + e];
+            const double v = __ldcg(sc.Lv + (size_t)(b0 + bi) * 36 + e) - sum;
+            if (bi == 0) akk[e] = v; else col_st[bi * 36 + e] = v;
+          }
+          __syncthreads();
+        }
+        // (c) diagonal block: 6x6 Cholesky across six lanes of warp 0 + the inverse of the factor
+        if (warp == 0) {
+          double a[6], x[6] = {0, 0, 0, 0, 0, 0};
 #pragma unroll
-          for (int q = 0; q < 6; ++q) a[q] = __ldcg(row + q);
+          for (int c = 0; c < 6; ++c) a[c] = akk[6 * (lane < 6 ? lane : 0) + c];
+          if (!warp_chol6_inverse(a, x, lane) && lane == 0) d.w_fail[d.fcam_win[__ldg(sc.perm + j)]] = 1;   // benign race: every writer stores 1
+          if (lane < 6) {
 #pragma unroll
-          for (int c = 0; c < 6; ++c) {
+            for (int i = 0; i < 6; ++i) { li_s[6 * i + lane] = x[i]; __stcg(sc.Li + (size_t)j * 36 + 6 * i + lane, x[i]); }
+          }
+        }
+        __syncthreads();
+        // (d) panel L_ij = A_ij Linv^T (i > j) and y_j = Linv t_j
+        if (staged) {
+          for (int idx = tid; idx < (nb - 1) * 36; idx += kSpThreads) {
+            const int bi = 1 + idx / 36, e = idx % 36, r = e / 6, c = e - 6 * r;
             double acc = 0.0;
 #pragma unroll
-            for (int q = 0; q < 6; ++q) if (q <= c) acc += a[q] * li_s[6 * c + q];
-            o[c] = acc;
+            for (int q = 0; q < 6; ++q) if (q <= c) acc += col_st[bi * 36 + 6 * r + q] * li_s[6 * c + q];
+            __stcg(sc.Lv + (size_t)(b0 + bi) * 36 + e, acc);
           }
+        } else {
+          // long columns (dense patterns) stay in L2: a thread per block row, in place (it reads its row before it writes it)
+          for (int idx = tid; idx < (nb - 1) * 6; idx += kSpThreads) {
+            double* row = sc.Lv + (size_t)(b0 + 1 + idx / 6) * 36 + 6 * (idx % 6);
+            double a[6], o[6];
 #pragma unroll
-          for (int q = 0; q < 6; ++q) __stcg(row + q, o[q]);
+            for (int q = 0; q < 6; ++q) a[q] = __ldcg(row + q);
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+              double acc = 0.0;
+#pragma unroll
+              for (int q = 0; q < 6; ++q) if (q <= c) acc += a[q] * li_s[6 * c + q];
+              o[c] = acc;
+            }
+#pragma unroll
+            for (int q = 0; q < 6; ++q) __stcg(row + q, o[q]);
+          }
         }
-      }
-      if (tid >= kSpThreads - 6) {
-        const int c = tid - (kSpThreads - 6);
-        double acc = 0.0;
+        if (tid >= kSpThreads - 6) {
+          const int c = tid - (kSpThreads - 6);
+          double acc = 0.0;
 #pragma unroll
-        for (int q = 0; q < 6; ++q) if (q <= c) acc += li_s[6 * c + q] * tj[q];
-        __stcg(sc.y + (size_t)j * 6 + c, acc);
+          for (int q = 0; q < 6; ++q) if (q <= c) acc += li_s[6 * c + q] * tj[q];
+          __stcg(sc.y + (size_t)j * 6 + c, acc);
+        }
+        __syncthreads();                          // the column is in L2 for the chain's next one; shared buffers are reused
       }
-      __syncthreads();                          // shared buffers are reused by the CTA's next column
     }
     grid.sync();
   }
-  // ---- 2: back substitution, levels downwards, a warp per column
-  const int gw = (blockIdx.x * kSpThreads + tid) >> 5, nw = (gridDim.x * kSpThreads) >> 5;
+  // ---- 2: back substitution, levels downwards; a chain's columns in sequence (last first) by its CTA:
+  //         x_j = Linv_jj^T (y_j - sum_i L_ij^T x_i), a thread per (block, column), partials summed in block order
+  double* xp = col_st;                            // [kSpThreads] partials
   for (int lvl = sc.nlev - 1; lvl >= 0; --lvl) {
     const int c_begin = __ldg(sc.lvl_ptr + lvl), c_end = __ldg(sc.lvl_ptr + lvl + 1);
-    for (int ci = c_begin + gw; ci < c_end; ci += nw) {
-      const int j = __ldg(sc.lvl_cols + ci);
-      const int b0 = __ldg(sc.col_ptr + j), b1 = __ldg(sc.col_ptr + j + 1);
-      double acc = 0.0;
-      if (lane < 30) {
-        for (int b = b0 + 1 + ps; b < b1; b += 5) {
-          const double* L = sc.Lv + (size_t)b * 36 + ri;                     // column ri of L_ij
-          const double* xi = sc.y + (size_t)__ldg(sc.row_idx + b) * 6;
-          acc += (__ldcg(L) * __ldcg(xi) + __ldcg(L + 6) * __ldcg(xi + 1) + __ldcg(L + 12) * __ldcg(xi + 2)) +
-                 (__ldcg(L + 18) * __ldcg(xi + 3) + __ldcg(L + 24) * __ldcg(xi + 4) + __ldcg(L + 30) * __ldcg(xi + 5));
+    for (int ci = c_begin + blockIdx.x; ci < c_end; ci += gridDim.x) {
+      const int j0 = __ldg(sc.lvl_cols + ci), jn = j0 + __ldg(sc.lvl_len + ci);
+      for (int j = jn - 1; j >= j0; --j) {
+        const int b0 = __ldg(sc.col_ptr + j), nbl = __ldg(sc.col_ptr + j + 1) - b0 - 1;
+        constexpr int G = kSpThreads / 6;         // block groups: thread (gq, c) takes blocks gq, gq + G, ...
+        const int gq = tid / 6, c = tid - 6 * gq;
+        double acc = 0.0;
+        if (gq < G)
+          for (int bb = gq; bb < nbl; bb += G) {
+            const double* L = sc.Lv + (size_t)(b0 + 1 + bb) * 36 + c;                 // column c of L_ij
+            const double* xi = sc.y + (size_t)__ldg(sc.row_idx + b0 + 1 + bb) * 6;
+            acc += (__ldcg(L) * __ldcg(xi) + __ldcg(L + 6) * __ldcg(xi + 1) + __ldcg(L + 12) * __ldcg(xi + 2)) +
+                   (__ldcg(L + 18) * __ldcg(xi + 3) + __ldcg(L + 24) * __ldcg(xi + 4) + __ldcg(L + 30) * __ldcg(xi + 5));
+          }
+        // the six threads that finish the column fetch what they need before the barrier
+        double yv = 0.0, lic[6] = {0, 0, 0, 0, 0, 0};
+        if (tid < 6) {
+          yv = __ldcg(sc.y + (size_t)j * 6 + tid);
+#pragma unroll
+          for (int q = 0; q < 6; ++q) if (q >= tid) lic[q] = __ldcg(sc.Li + (size_t)j * 36 + 6 * q + tid);     // Linv^T row
         }
-      }
-      double tot = acc;
+        xp[tid] = acc;
+        __syncthreads();
+        if (warp == 0) {
+          double s = 0.0;
+          if (lane < 6) {
+            const int ng = min(nbl, G);
+            for (int q = 0; q < ng; ++q) s += xp[6 * q + lane];
+            s = yv - s;
+          }
+          double v = 0.0;
 #pragma unroll
-      for (int q = 1; q < 5; ++q) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * q) & 31);
-      const double s = (lane < 6) ? __ldcg(sc.y + (size_t)j * 6 + lane) - tot : 0.0;
-      double v = 0.0;
-#pragma unroll
-      for (int q = 0; q < 6; ++q) {
-        const double sq = __shfl_sync(0xffffffffu, s, q);
-        if (lane < 6 && q >= lane) v += __ldcg(sc.Li + (size_t)j * 36 + 6 * q + lane) * sq;    // Linv^T
-      }
-      if (lane < 6) {
-        __stcg(sc.y + (size_t)j * 6 + lane, v);
-        const int f = __ldg(sc.perm + j);
-        const int w = d.fcam_win[f];
-        const bool ok = isfinite(v) && __ldcg(d.w_fail + w) == 0;
-        if (!isfinite(v)) d.w_fail[w] = 1;                                    // benign race: every writer stores 1
-        d.x[(size_t)f * 6 + lane] = ok ? v : 0.0;
-        d.r[(size_t)f * 6 + lane] = 0.0;                                      // exact solve: no linear residual in the model change
+          for (int q = 0; q < 6; ++q) {
+            const double sq = __shfl_sync(0xffffffffu, s, q);
+            if (q >= lane) v += lic[q] * sq;
+          }
+          if (lane < 6) {
+            __stcg(sc.y + (size_t)j * 6 + lane, v);
+            const int f = __ldg(sc.perm + j);
+            const int w = d.fcam_win[f];
+            const bool ok = isfinite(v) && __ldcg(d.w_fail + w) == 0;
+            if (!isfinite(v)) d.w_fail[w] = 1;                                    // benign race: every writer stores 1
+            d.x[(size_t)f * 6 + lane] = ok ? v : 0.0;
+            d.r[(size_t)f * 6 + lane] = 0.0;                                      // exact solve: no linear residual in the model change
+          }
+        }
+        __syncthreads();
       }
     }
     if (lvl > 0) grid.sync();

@@ -27,9 +27,11 @@ struct SparseCholSymbolic {
   std::vector<int32_t> upd_a, upd_b;   // [nupd] block ids of L_ik and L_jk, k ascending
   std::vector<int32_t> rowl_ptr;       // [n+1] row lists (forward substitution): blocks (j, k), k < j, k ascending
   std::vector<int32_t> rowl_blk, rowl_col;   // [nnzL - n]
-  std::vector<int32_t> lvl_ptr;        // [nlev+1] level sets of the elimination tree (leaves = level 0)
-  std::vector<int32_t> lvl_cols;       // [n] columns sorted by (level, column)
+  std::vector<int32_t> lvl_ptr;        // [nlev+1] level sets of the CHAINS of the elimination tree (leaves = level 0)
+  std::vector<int32_t> lvl_cols;       // [nchain] first column of each chain, sorted by (level, column)
+  std::vector<int32_t> lvl_len;        // [nchain] its length: columns lvl_cols[c] .. + lvl_len[c] - 1, each the only child of the next
   int32_t nlev = 0;
+  int64_t nchain() const { return (int64_t)lvl_cols.size(); }
   int64_t nnzL() const { return (int64_t)row_idx.size(); }
   int64_t nupd() const { return (int64_t)upd_a.size(); }
 };

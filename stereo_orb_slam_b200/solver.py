@@ -196,17 +196,17 @@ class Solver:
 
     def factor_symbolic(self):
         """Symbolic phase of the block-sparse Cholesky (structures with a window of > 64 free cameras)."""
-        info = (C.c_int64 * 4)()
-        capi.check(self._L.sba_get_factor_symbolic(self._h, info, None, None, None, None, None, None, None, None, None))
-        n, nnz, nupd, nlev = (int(v) for v in info)
-        out = dict(n=n, nnzL=nnz, nupd=nupd, nlev=nlev, perm=np.zeros(n, np.int32), col_ptr=np.zeros(n + 1, np.int32),
+        info = (C.c_int64 * 5)()
+        capi.check(self._L.sba_get_factor_symbolic(self._h, info, None, None, None, None, None, None, None, None, None, None))
+        n, nnz, nupd, nlev, nchain = (int(v) for v in info)
+        out = dict(n=n, nnzL=nnz, nupd=nupd, nlev=nlev, nchain=nchain, perm=np.zeros(n, np.int32), col_ptr=np.zeros(n + 1, np.int32),
                    row_idx=np.zeros(nnz, np.int32), init_src=np.zeros(nnz, np.int32), upd_ptr=np.zeros(nnz + 1, np.int64),
                    upd_a=np.zeros(nupd, np.int32), upd_b=np.zeros(nupd, np.int32), lvl_ptr=np.zeros(nlev + 1, np.int32),
-                   lvl_cols=np.zeros(n, np.int32))
+                   lvl_cols=np.zeros(nchain, np.int32), lvl_len=np.zeros(nchain, np.int32))
         capi.check(self._L.sba_get_factor_symbolic(
             self._h, info, ptr(out["perm"], I32), ptr(out["col_ptr"], I32), ptr(out["row_idx"], I32), ptr(out["init_src"], I32),
             ptr(out["upd_ptr"], I64), ptr(out["upd_a"], I32), ptr(out["upd_b"], I32), ptr(out["lvl_ptr"], I32),
-            ptr(out["lvl_cols"], I32)))
+            ptr(out["lvl_cols"], I32), ptr(out["lvl_len"], I32)))
         return out
 
     @property

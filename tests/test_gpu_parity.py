@@ -97,14 +97,17 @@ def test_pcg_solves_the_reduced_system(small_window):
     assert np.abs(x - xs).max() <= 1e-8 * np.abs(xs).max()
 
 
-@pytest.mark.parametrize("path", ["cholesky", "cholesky_cluster", "cholesky_sparse", "window", "cluster", "multilaunch", "cooperative"])
+@pytest.mark.parametrize("path", ["cholesky", "cholesky_window", "cholesky_cluster", "cholesky_sparse", "window", "cluster", "multilaunch", "cooperative"])
 def test_every_linear_solver_path_solves_the_same_system(small_window, path, monkeypatch):
-    """The reduced system goes through the block Cholesky (windows of <= 64 free cameras, the default there: one CTA
-    per window, or one 8-CTA cluster per window from 16 cameras up) or one of four PCG
+    """The reduced system goes through the block Cholesky (windows of <= 64 free cameras, the default there: the
+    banded envelope in one CTA's shared memory when it fits, else one CTA per window on an L2 workspace, or one
+    8-CTA cluster per window from 16 cameras up; the block-sparse factorisation above 64 cameras) or one of four PCG
     paths depending on its size (one CTA per window, one 8-CTA cluster per window, one cooperative launch over the
     global block-CSR, or the multi-launch path); force each on the same small window."""
-    for k in ("SBA_NO_CLUSTER", "SBA_FORCE_CLUSTER", "SBA_FORCE_MULTILAUNCH", "SBA_FORCE_COOP_PCG", "SBA_NO_DIRECT", "SBA_FORCE_SPARSE_CHOL"):
+    for k in ("SBA_NO_CLUSTER", "SBA_FORCE_CLUSTER", "SBA_FORCE_MULTILAUNCH", "SBA_FORCE_COOP_PCG", "SBA_NO_DIRECT", "SBA_FORCE_SPARSE_CHOL", "SBA_NO_BAND"):
         monkeypatch.delenv(k, raising=False)
+    if path == "cholesky_window":       # "cholesky" itself is the banded single-CTA kernel (k_chol_band); this is k_chol_window
+        monkeypatch.setenv("SBA_NO_BAND", "1")
     if path == "cholesky_sparse":       # the block-sparse factorisation of the global configs, forced on a small window
         monkeypatch.setenv("SBA_FORCE_SPARSE_CHOL", "1")
     elif path in ("cluster", "cholesky_cluster"):
@@ -137,6 +140,7 @@ def test_cholesky_of_a_batch_of_windows_equals_pcg(frames, monkeypatch):
     lower block-triangle in shared memory (<= 20 free cameras) or in the L2-resident workspace (more; the cluster
     kernel is switched off to get there)."""
     monkeypatch.setenv("SBA_NO_CLUSTER", "1")
+    monkeypatch.setenv("SBA_NO_BAND", "1")
     ws = [make_window(frames + i, 300 + 50 * i, 4, 40 + i) for i in range(4)]
     cam_off = np.cumsum([0] + [x["poses"].shape[0] for x in ws]).astype(np.int32)
     pt_off = np.cumsum([0] + [x["points"].shape[0] for x in ws]).astype(np.int32)
@@ -151,6 +155,24 @@ def test_cholesky_of_a_batch_of_windows_equals_pcg(frames, monkeypatch):
         s.linearize(); s.schur(1e4); s.pcg(default_options(pcg_tolerance=1e-13, max_pcg_iterations=500, linear_solver=solver))
         out[name] = s.schur_values()[2].copy()
     assert np.abs(out["chol"] - out["pcg"]).max() <= 1e-8 * np.abs(out["pcg"]).max()
+
+
+@pytest.mark.parametrize("frames,track", [(5, 4), (24, 4), (50, 7), (30, 30)])
+def test_banded_cholesky_of_a_batch_of_windows_equals_numpy(frames, track):
+    """k_chol_band: windows of different sizes in one call, narrow bands (track length 4 / 7) and a fully co-visible
+    window (track length = frames: the envelope is the whole lower triangle), each against numpy on its own block."""
+    ws = [make_window(frames + i, 300 + 50 * i, track, 140 + i) for i in range(3)]
+    b = batch_windows(ws)
+    s = Solver(0).set_structure(b["poses"].shape[0], b["points"].shape[0], b["obs_cam"], b["obs_pt"],
+                                win_cam_off=b["win_cam_off"], win_pt_off=b["win_pt_off"])
+    s.set_state(b["poses"], b["points"]); s.set_measurements(b["obs_uv"], b["p_l"], b["p_r"])
+    s.linearize(); s.schur(1e4)
+    assert s.pcg(default_options(linear_solver=2)) == 0
+    S, rhs, x = s.schur_dense()
+    xs = np.linalg.solve(S, rhs)
+    assert np.abs(x - xs).max() <= 1e-10 * np.abs(xs).max()
+    s.pcg(default_options(linear_solver=2))
+    assert np.array_equal(s.schur_values()[2], x)                       # bit-reproducible
 
 
 def test_cooperative_pcg_is_bit_reproducible_on_a_global_problem():

@@ -45,14 +45,19 @@ def emulate(sym, up, B):
             Lv[b] = B[up[~src]].T
     done = np.zeros(sym["n"], bool)
     col_of = np.repeat(np.arange(sym["n"]), np.diff(sym["col_ptr"]))
+    chain_of = np.zeros(sym["n"], np.int64)
+    for c in range(sym["nchain"]):
+        chain_of[sym["lvl_cols"][c]:sym["lvl_cols"][c] + sym["lvl_len"][c]] = c
     for l in range(sym["nlev"]):
-        cols = sym["lvl_cols"][sym["lvl_ptr"][l]:sym["lvl_ptr"][l + 1]]
-        for j in cols:
+        chains = range(sym["lvl_ptr"][l], sym["lvl_ptr"][l + 1])
+        cols = np.concatenate([np.arange(sym["lvl_cols"][c], sym["lvl_cols"][c] + sym["lvl_len"][c]) for c in chains])
+        for j in cols:          # a chain's columns in sequence; operands come from finished levels or earlier in the chain
             b0, b1 = sym["col_ptr"][j], sym["col_ptr"][j + 1]
             for b in range(b0, b1):
                 for u in range(sym["upd_ptr"][b], sym["upd_ptr"][b + 1]):
                     a, bb = sym["upd_a"][u], sym["upd_b"][u]
-                    assert done[col_of[a]] and col_of[a] == col_of[bb]       # operands come from finished columns
+                    k = col_of[a]
+                    assert col_of[bb] == k and (done[k] or (k < j and k in cols and chain_of[k] == chain_of[j]))
                     Lv[b] -= Lv[a] @ Lv[bb].T
             Ljj = np.linalg.cholesky(Lv[b0])
             Li = np.linalg.inv(Ljj)
@@ -79,7 +84,7 @@ def check(s, rng):
     rows, cols = s.schur_pattern()
     up, B = random_spd(rows, cols, nf, rng)
     assert sym["n"] == nf and sorted(sym["perm"]) == list(range(nf))
-    assert sorted(sym["lvl_cols"]) == list(range(nf))
+    assert int(sym["lvl_len"].sum()) == nf and sym["lvl_ptr"][-1] == sym["nchain"]
     Lv = emulate(sym, up, B)
     L = dense_L(sym, Lv)
     S = np.zeros((6 * nf, 6 * nf))
@@ -97,7 +102,7 @@ def test_banded_chain_orders_into_a_shallow_tree(monkeypatch):
     s = host_structure(smap, monkeypatch, force=False)      # > 64 free cameras: built without forcing
     sym = check(s, np.random.default_rng(1))
     nf = s.num_free_cameras
-    assert sym["nlev"] < nf // 2                             # natural order would give nf levels
+    assert sym["nlev"] <= 12                                 # natural order would give one chain of nf columns
     nS = (s.schur_pattern()[0] <= s.schur_pattern()[1]).sum()
     assert sym["nnzL"] <= 3 * nS                             # modest fill
 

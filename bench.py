@@ -282,11 +282,18 @@ def run_ours(args):
     reps = max(min(args.steps, 50), 5)
     t_lp = sv.time_stage(0, reps, True, radius); t_sp = sv.time_stage(2, reps, True, radius)
     t_lin = sv.time_stage(3, reps, True, radius); t_sch = sv.time_stage(4, reps, True, radius)
+    try:
+        t_fu = sv.time_stage(11, reps, True, radius)      # K1-K3 of every chunk in ONE kernel: what a step runs
+    except Exception:
+        t_fu = None
     peak, peak_src = measured_peak()
     fp64_peak = sv.measure_fp64_peak()
-    # the dominant kernel of the step: k_lin_chunk does the whole of K1/K2 and k_schur_chunk the whole of K3 for a chunk,
-    # so each is charged its stage's full algorithmic bytes / flops for the observations of this rank
-    if t_sp >= t_lp:
+    # the dominant kernel of the step: k_fused_chunk does the whole of K1-K3 for a chunk (it is charged the algorithmic
+    # bytes / flops of BOTH stages, SURVEY 8(d), although W never comes back from HBM); without it k_lin_chunk does
+    # K1/K2 and k_schur_chunk K3, each charged its own stage
+    if t_fu is not None:
+        dom, t_dom, B_dom, F_dom = "k_fused_chunk", t_fu, B_lin + B_schur, F_lin + F_schur
+    elif t_sp >= t_lp:
         dom, t_dom, B_dom, F_dom = "k_schur_chunk", t_sp, B_schur, F_schur
     else:
         dom, t_dom, B_dom, F_dom = "k_lin_chunk", t_lp, B_lin, F_lin
@@ -366,7 +373,8 @@ def run_ours(args):
                          "fp64": {"achieved": F_dom / (t_dom * 1e-3) / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
                                   "frac": F_dom / (t_dom * 1e-3) / 1e12 / fp64_peak if fp64_peak > 0 else None,
                                   "algorithmic_flops": F_dom, "peak_source": "measured here (sba_measure_fp64_peak: register-only DFMA chains)"}},
-            "stages_us": {"k_lin_chunk": 1e3 * t_lp, "k_schur_chunk": 1e3 * t_sp, "linearize": 1e3 * t_lin, "schur": 1e3 * t_sch},
+            "stages_us": {"k_fused_chunk": None if t_fu is None else 1e3 * t_fu, "k_lin_chunk": 1e3 * t_lp, "k_schur_chunk": 1e3 * t_sp,
+                          "linearize_unfused": 1e3 * t_lin, "schur_unfused": 1e3 * t_sch},
             "stage_roofline": {"linearize_GBs": B_lin / (t_lin * 1e-3) / 1e9, "schur_GBs": B_schur / (t_sch * 1e-3) / 1e9,
                                "linearize_frac": B_lin / (t_lin * 1e-3) / 1e9 / peak, "schur_frac": B_schur / (t_sch * 1e-3) / 1e9 / peak,
                                "step_frac": (B_lin + B_schur) / (ms_max / args.steps * 1e-3) / 1e9 / peak if not sharded else None}}

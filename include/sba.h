@@ -146,7 +146,8 @@ int sba_time_linearize_schur(sba_handle h, const sba_options* opt, double radius
  * events on the handle's stream; flush_l2 != 0 overwrites a 256 MiB scratch buffer between launches
  * so every launch starts from a cold L2.  Stages: 0 k_lin_chunk (K0+K1+K2) 1 k_assemble_schur 2 k_schur_chunk (K3)
  * 3 whole linearisation 4 whole Schur step 5 k_backsub 6 k_trial_points 7 one multi-launch PCG iteration
- * 8 linearisation + Schur (one bench step; on a single GPU the step is replayed as one CUDA graph) 9 k_assemble_cams 10 k_lin_finish.  Needs a prior sba_linearize (and
+ * 8 linearisation + Schur (one bench step; on a single GPU the step is replayed as one CUDA graph) 9 k_assemble_cams 10 k_lin_finish
+ * 11 k_fused_chunk (K1-K3 of every chunk in one kernel: what a bench step and the LM loop run from the second linearisation on).  Needs a prior sba_linearize (and
  * sba_schur for stages 1, 5-7).  *ms = mean device milliseconds per launch. */
 int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t stage, int32_t repeats,
                    int32_t flush_l2, double* ms);

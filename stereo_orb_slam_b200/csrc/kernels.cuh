@@ -555,6 +555,285 @@ __global__ void __launch_bounds__(kSchurThreads, 4) k_schur_chunk(Dev d, int max
   }
 }
 
+// ------------------------------------------------------------------------ K0: per-linearisation camera table
+// R / J_l / t of every camera at the current state, written once per linearisation; the fused chunk kernel stages
+// its slot cameras from here instead of recomputing sin / cos behind a barrier in every CTA.
+__global__ void k_campre(Dev d) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= d.Nc) return;
+  CamPre cp;
+  cam_precompute(d.poses + 6 * (size_t)c, cp);
+  d.campre[c] = cp;
+}
+
+// ------------------------------------------------------------------- K1 + K2 + K3 fused, one CTA per chunk
+// A chunk holds ALL observations of its points, so V_p is complete inside the CTA and the Schur step of the chunk
+// can follow its linearisation without W ever coming back from HBM (it is still written once: back-substitution
+// reads it).  Used from the second linearisation on (the damping needs the Jacobi scaling fixed at iteration 0 and
+// the trust-region radius, both known by then); a rejected step re-runs k_schur_chunk alone with the new radius.
+//   A  thread per observation: residual, Huber, block algebra; W -> HBM and kept in registers; camera-side terms
+//      (27) and point-side terms (9) -> shared memory
+//   B  thread per point: V, g_p -> HBM, damped 3x3 Cholesky -> Linv, u (shared), Vinv, t_p (HBM)
+//      || warps from the last one down: per-slot sums of the camera-side terms -> cspart
+//   C  thread per observation: Z = W Linv^T into the (now dead) camera staging area; the chunk's pair lists are
+//      staged into the (now dead) point staging area
+//   D  warp per local block: sum over its pairs of Z_a Z_b^T on the FP64 tensor cores -> spart;
+//      warp per slot: sum of Z u -> rpart
+constexpr int kFusedThreads = 256;
+constexpr int kFZStride = 19;      // odd: observation rows of Z fall into different banks
+
+__host__ __device__ __forceinline__ size_t fused_smem_bytes(int n, int np, int ns) {
+  return ((size_t)n * (kCamStride + 9) + (size_t)ns * 21 + (size_t)np * 12) * 8 + (size_t)((n + 15) & ~15);
+}
+
+__global__ void __launch_bounds__(kFusedThreads, 2) k_fused_chunk(Dev d, DevParams P) {
+  extern __shared__ __align__(16) double smem[];
+  __shared__ double sm1[kFusedThreads / 32];
+  __shared__ double smx[kFusedThreads / 32];
+  const int chunk = blockIdx.x;
+  const int4 c0 = __ldg(d.cdesc + 4 * (size_t)chunk), c1 = __ldg(d.cdesc + 4 * (size_t)chunk + 1), c2 = __ldg(d.cdesc + 4 * (size_t)chunk + 2);
+  const int p0 = c0.x, np = c0.y, e0 = c0.z, n = c0.w;
+  const int w = c1.x, cs0 = c1.y, ns = c1.z, cs1 = cs0 + ns, lb0 = c1.w, lb1 = c1.w + c2.x;
+  const int pq0 = c2.y, npq = c2.z;
+  double* cam_st = smem;                                   // [n * 27]  A: camera-side terms;  C/D: Z [n * 19]
+  double* pt_st = cam_st + (size_t)n * kCamStride;         // [n * 9]   A: V, gp terms;        C/D: pair lists
+  double* cpre = pt_st + (size_t)n * 9;                    // [ns * 21] R Jl t of the chunk's cameras
+  double* xs = cpre + (size_t)ns * 21;                     // [np * 3]  the chunk's points
+  double* Li = xs + (size_t)np * 3;                        // [np * 6]  Linv: 00 10 11 20 21 22
+  double* us = Li + (size_t)np * 6;                        // [np * 3]  u = Linv gp
+  uint8_t* opl = reinterpret_cast<uint8_t*>(us + (size_t)np * 3);   // [n] chunk-local point of each observation
+  double* Z = cam_st;
+  uint16_t* prs = reinterpret_cast<uint16_t*>(pt_st);
+  const bool pairs_staged = (size_t)npq * 2 <= (size_t)n * 72;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int NW = kFusedThreads / 32;
+  // ---- stage: independent loads only
+  const int i = threadIdx.x;
+  const bool act = i < n;
+  int sl = 0, pl = 0;
+  float4 m = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (act) {
+    sl = d.oslot[e0 + i];
+    pl = __ldg(d.ppt + e0 + i) - p0;
+    m = __ldg(d.uv_p + e0 + i);
+    opl[i] = (uint8_t)pl;
+  }
+  for (int k = threadIdx.x; k < np * 3; k += kFusedThreads) xs[k] = d.pts[(size_t)p0 * 3 + k];
+  for (int k = threadIdx.x; k < ns * 21; k += kFusedThreads) {
+    const int s = k / 21;
+    cpre[k] = reinterpret_cast<const double*>(d.campre + __ldg(d.cs_cam + cs0 + s))[k - 21 * s];
+  }
+  // the point threads request what phase B needs now (it arrives while phase A computes)
+  const int q = threadIdx.x;
+  const bool has_pt = q < np;
+  double s2[3] = {1, 1, 1};
+  if (has_pt) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) s2[k] = d.sc2p[(size_t)(p0 + q) * 3 + k];
+  }
+  const double radius = d.w_radius[w];
+  const int pe0 = has_pt ? d.pt_off[p0 + q] - e0 : 0, pe1 = has_pt ? d.pt_off[p0 + q + 1] - e0 : 0;
+  __syncthreads();
+  // ---- A
+  double cost = 0.0;
+  double W[18];
+#pragma unroll
+  for (int k = 0; k < 18; ++k) W[k] = 0.0;
+  if (act) {
+    const CamPre& cp = *reinterpret_cast<const CamPre*>(cpre + 21 * sl);
+    const float uv[4] = {m.x, m.y, m.z, m.w};
+    const double X[3] = {xs[3 * pl], xs[3 * pl + 1], xs[3 * pl + 2]};
+    double qv[3], r[4], D[12];
+    const double sq = project(P.pl, P.pr, cp, X, uv, P.rdim, qv, r, D);
+    double rho, wt;
+    huber(P.huber_delta, sq, rho, wt);
+    cost = 0.5 * rho;
+    double A[6], h[3], G[9];
+    form_A_h(D, r, wt, A, h);
+    form_G(cp, qv, G);
+    {
+      double cu[27];
+#pragma unroll
+      for (int k = 0; k < 27; ++k) cu[k] = 0.0;
+      accum_camera(A, h, G, cu, cu + 21);
+      double* cs = cam_st + (size_t)i * kCamStride;
+#pragma unroll
+      for (int k = 0; k < 27; ++k) cs[k] = cu[k];
+    }
+    double Vc[9];
+    point_contrib(cp, A, h, G, Vc, W);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) pt_st[(size_t)i * 9 + k] = Vc[k];
+    double2* Wo = reinterpret_cast<double2*>(d.W + (size_t)(e0 + i) * 18);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) Wo[k] = make_double2(W[2 * k], W[2 * k + 1]);
+  }
+  __syncthreads();
+  // ---- B: per point V, gp, damped Cholesky
+  double gmax = 0.0;
+  if (has_pt) {
+    const int p = p0 + q;
+    double acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int o = pe0; o < pe1; ++o) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) acc[k] += pt_st[(size_t)o * 9 + k];
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) d.V[(size_t)p * 6 + k] = acc[k];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      d.gp[(size_t)p * 3 + k] = acc[6 + k];
+      const double x = xs[3 * q + k];
+      gmax = fmax(gmax, fabs(x - clampd(x - acc[6 + k], P.lo, P.hi)));   // projected-gradient norm
+    }
+    const double a = acc[0] + lm_damp(s2[0], acc[0], radius);
+    const double dd = acc[3] + lm_damp(s2[1], acc[3], radius);
+    const double f = acc[5] + lm_damp(s2[2], acc[5], radius);
+    const double b = acc[1], c = acc[2], e = acc[4];
+    double i00 = 0, i10 = 0, i11 = 0, i20 = 0, i21 = 0, i22 = 0;
+    bool ok = a > 0.0;
+    if (ok) {
+      const double l00 = sqrt(a);
+      i00 = 1.0 / l00;
+      const double l10 = b * i00, l20 = c * i00;
+      const double r1 = dd - l10 * l10;
+      ok = r1 > 0.0;
+      if (ok) {
+        const double l11 = sqrt(r1);
+        i11 = 1.0 / l11;
+        const double l21 = (e - l20 * l10) * i11;
+        const double r2 = f - l20 * l20 - l21 * l21;
+        ok = r2 > 0.0 && isfinite(r2);
+        if (ok) {
+          i22 = 1.0 / sqrt(r2);
+          i10 = -l10 * i00 * i11;
+          i21 = -l21 * i11 * i22;
+          i20 = -(l20 * i00 + l21 * i10) * i22;
+        }
+      }
+    }
+    if (!ok) { d.w_fail[w] = 1; i00 = i10 = i11 = i20 = i21 = i22 = 0.0; }   // benign race: every writer stores 1
+    const double g0 = acc[6], g1 = acc[7], g2 = acc[8];
+    const double u0 = i00 * g0, u1 = i10 * g0 + i11 * g1, u2 = i20 * g0 + i21 * g1 + i22 * g2;
+    double* vo = d.Vinv + (size_t)p * 6;
+    vo[0] = i00 * i00 + i10 * i10 + i20 * i20; vo[1] = i10 * i11 + i20 * i21; vo[2] = i20 * i22;
+    vo[3] = i11 * i11 + i21 * i21; vo[4] = i21 * i22; vo[5] = i22 * i22;
+    d.tp[(size_t)p * 3] = i00 * u0 + i10 * u1 + i20 * u2;
+    d.tp[(size_t)p * 3 + 1] = i11 * u1 + i21 * u2;
+    d.tp[(size_t)p * 3 + 2] = i22 * u2;
+    Li[q * 6] = i00; Li[q * 6 + 1] = i10; Li[q * 6 + 2] = i11; Li[q * 6 + 3] = i20; Li[q * 6 + 4] = i21; Li[q * 6 + 5] = i22;
+    us[q * 3] = u0; us[q * 3 + 1] = u1; us[q * 3 + 2] = u2;
+  }
+  // ---- per camera slot: U (21) + gc (6), one warp per slot, dealt from the last warp down (the point threads sit
+  //      in the first warps); same fixed order as k_lin_chunk
+  for (int cs = cs0 + (NW - 1 - warp); cs < cs1; cs += NW) {
+    const int c = d.cs_cam[cs];
+    if (d.fc[c] < 0) continue;        // a fixed camera is not an unknown (src/bundle_adjuster.cpp:113)
+    double s0 = 0.0, s1 = 0.0;
+    const int j0 = d.cs_obs_off[cs], j1 = d.cs_obs_off[cs + 1];
+    const double* col = cam_st + (lane < 27 ? lane : 0);
+    for (int jb = j0; jb < j1; jb += 32) {
+      const int mine_o = (jb + lane < j1) ? (int)__ldg(d.sobs + jb + lane) : 0;
+      const int mm = min(32, j1 - jb);
+      int t = 0;
+      for (; t + 3 < mm; t += 4) {
+        const int o0 = __shfl_sync(0xffffffffu, mine_o, t), o1 = __shfl_sync(0xffffffffu, mine_o, t + 1);
+        const int o2 = __shfl_sync(0xffffffffu, mine_o, t + 2), o3 = __shfl_sync(0xffffffffu, mine_o, t + 3);
+        const double v0 = col[o0 * kCamStride], v1 = col[o1 * kCamStride], v2 = col[o2 * kCamStride], v3 = col[o3 * kCamStride];
+        s0 += v0; s1 += v1; s0 += v2; s1 += v3;
+      }
+      for (; t < mm; ++t) {
+        const int o = __shfl_sync(0xffffffffu, mine_o, t);
+        const double v = col[o * kCamStride];
+        if (t & 1) s1 += v; else s0 += v;
+      }
+    }
+    if (lane < 27) d.cspart[(size_t)d.cs_pos[cs] * 27 + lane] = s0 + s1;
+  }
+  // chunk cost and projected-gradient max: warp partials now, summed after the next barrier
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { cost += __shfl_xor_sync(0xffffffffu, cost, o); gmax = fmax(gmax, __shfl_xor_sync(0xffffffffu, gmax, o)); }
+  if (lane == 0) { sm1[warp] = cost; smx[warp] = gmax; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0, mx = 0.0;
+#pragma unroll
+    for (int k = 0; k < NW; ++k) { t += sm1[k]; mx = fmax(mx, smx[k]); }
+    d.lin_part[2 * chunk] = t; d.lin_part[2 * chunk + 1] = mx;
+  }
+  // ---- C: Z = W Linv^T from the registers into the dead camera staging area; pair lists into the dead point staging area
+  if (act) {
+    const double* L = Li + pl * 6;
+    const double i00 = L[0], i10 = L[1], i11 = L[2], i20 = L[3], i21 = L[4], i22 = L[5];
+    double* z = Z + (size_t)i * kFZStride;
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+      const double w0 = W[3 * r], w1 = W[3 * r + 1], w2 = W[3 * r + 2];
+      z[3 * r] = w0 * i00;
+      z[3 * r + 1] = w0 * i10 + w1 * i11;
+      z[3 * r + 2] = w0 * i20 + w1 * i21 + w2 * i22;
+    }
+  }
+  if (pairs_staged)
+    for (int k = threadIdx.x; k < npq; k += kFusedThreads) prs[k] = __ldg(d.pairs + pq0 + k);
+  __syncthreads();
+  // ---- D: local blocks, one warp per block, one FP64 tensor-core MMA (m8n8k4) per pair (see k_schur_chunk)
+  const int g = lane >> 2, t = lane & 3;
+  const bool feeds = g < 6 && t < 3;
+  const double* Zl = Z + (feeds ? 3 * g + t : 0);
+  for (int lb = lb0 + warp; lb < lb1; lb += NW) {
+    const int q0 = d.lb_pair_off[lb] - pq0, q1 = d.lb_pair_off[lb + 1] - pq0;
+    double a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0;
+    auto mma_pair = [&](unsigned pr, double& x0, double& x1) {
+      double a = 0.0, b = 0.0;
+      if (feeds) { a = Zl[(pr & 255u) * kFZStride]; b = Zl[(pr >> 8) * kFZStride]; }
+      dmma884(x0, x1, a, b);
+    };
+    if (pairs_staged) {
+      int qq = q0;
+      if ((qq & 1) && qq < q1) { mma_pair(prs[qq], b0, b1); ++qq; }
+      const uint32_t* pp = reinterpret_cast<const uint32_t*>(prs);
+      for (; qq + 1 < q1; qq += 2) {
+        const uint32_t two = pp[qq >> 1];
+        mma_pair(two & 0xffffu, a0, a1);
+        mma_pair(two >> 16, b0, b1);
+      }
+      if (qq < q1) mma_pair(prs[qq], a0, a1);
+    } else {
+      const uint16_t* gp = d.pairs + pq0;
+      int qq = q0;
+      if ((qq & 1) && qq < q1) { mma_pair(__ldg(gp + qq), b0, b1); ++qq; }
+      for (; qq + 1 < q1; qq += 2) { mma_pair(__ldg(gp + qq), a0, a1); mma_pair(__ldg(gp + qq + 1), b0, b1); }
+      if (qq < q1) mma_pair(__ldg(gp + qq), a0, a1);
+    }
+    if (feeds) *reinterpret_cast<double2*>(d.spart + (size_t)d.lb_pos[lb] * 36 + 6 * g + 2 * t) = make_double2(a0 + b0, a1 + b1);
+  }
+  // ---- right-hand side partials: sum over the slot's observations of W_e tp[point(e)] = Z_e u[point(e)]
+  for (int cs = cs0 + (NW - 1 - warp); cs < cs1; cs += NW) {
+    const int c = d.cs_cam[cs];
+    if (d.fc[c] < 0) continue;
+    double acc[6] = {0, 0, 0, 0, 0, 0};
+    const int j1 = d.cs_obs_off[cs + 1];
+    for (int j = d.cs_obs_off[cs] + lane; j < j1; j += 32) {
+      const int o = d.sobs[j];
+      const double* zz = Z + (size_t)o * kFZStride;
+      const double* u = us + (int)opl[o] * 3;
+      const double t0 = u[0], t1 = u[1], t2 = u[2];
+#pragma unroll
+      for (int r = 0; r < 6; ++r) acc[r] += zz[3 * r] * t0 + zz[3 * r + 1] * t1 + zz[3 * r + 2] * t2;
+    }
+    double mine = 0.0;
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+      double x = acc[r];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+      if (lane == r) mine = x;
+    }
+    if (lane < 6) d.rpart[(size_t)d.cs_pos[cs] * 6 + lane] = mine;
+  }
+}
+
 // Sum of the contiguous partial rows [l0, l1) of one block / camera by a whole CTA of kAsmThreads: warp w takes
 // rows w*8 + pg, + 8*kAsmWarps, ..., so that even a camera seen by > 100 chunks
 // needs one or two batches of independent loads; the warps' totals are then added in warp order through shared

@@ -79,6 +79,8 @@ struct sba_handle_s {
   bool chol_cluster_ok = false; size_t chol_cluster_smem = 0;   // mid-size windows: one 8-CTA cluster per window (k_chol_cluster)
   bool chol_band_ok = false; size_t chol_band_smem = 0; const int32_t* band_last = nullptr;   // banded windows: envelope in one CTA's shared memory (k_chol_band)
   size_t lin_smem = 0, schur_smem = 0;   // dynamic shared memory of the per-chunk kernels (largest chunk)
+  size_t fused_smem = 0; bool fused_ok = false;   // k_fused_chunk (K1-K3 of a chunk in one CTA)
+  bool schur_fresh = false;              // the last linearisation was fused: spart / rpart already hold this radius' Schur partials
   // exact block-sparse Cholesky of the reduced system for windows of more than kCholMaxCams free cameras (k_spchol)
   SparseCholSymbolic sym; bool sym_ok = false; SpCholDev sp{}; bool spchol_ok = false; int spchol_blocks = 0; double time_symbolic_s = 0.0;
 
@@ -275,7 +277,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   AL(uvp, nobs) d.uv_p = uvp;
   AL(h->uv_in, (size_t)Nobs)
   AL(d.poses, nc * 6) AL(d.poses_new, nc * 6) AL(d.pts, np * 3) AL(d.pts_new, np * 3)
-  AL(d.campre_new, nc)
+  AL(d.campre_new, nc) AL(d.campre, nc)
   AL(d.W, nobs * 18) AL(d.V, np * 6) AL(d.gp, np * 3) AL(d.Vinv, np * 6) AL(d.tp, np * 3)
   AL(d.U, nc * 27 + nw + nw * kMaxRanks)   // U | gc | cost_red | gslots: one block, one all-reduce per linearisation (multi-GPU)
   d.gc = d.U + nc * 21; d.cost_red = d.gc + nc * 6; d.gslots = d.cost_red + nw;
@@ -318,6 +320,11 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
     h->schur_smem = schur_smem_bytes(H.max_chunk_obs, H.max_chunk_pts, H.max_chunk_pairs);
     CUDA_TRY(cudaFuncSetAttribute(k_lin_chunk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->lin_smem, 1024)));
     CUDA_TRY(cudaFuncSetAttribute(k_schur_chunk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->schur_smem, 1024)));
+    h->fused_smem = fused_smem_bytes(H.max_chunk_obs, H.max_chunk_pts, H.max_slots);
+    h->fused_ok = h->fused_smem <= (size_t)220 * 1024 && !std::getenv("SBA_NO_FUSED");
+    h->schur_fresh = false;
+    if (h->fused_ok)
+      CUDA_TRY(cudaFuncSetAttribute(k_fused_chunk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fused_smem, 1024)));
   }
   {
     // per-window size of the reduced system -> can one CTA hold it?
@@ -534,13 +541,22 @@ static int join_tail(sba_handle h) {
 // `fork_tail`: single GPU, Jacobi scaling already fixed: the camera-side tail goes to the side stream and the caller
 // (the LM loop, the K1-K3 timing stage) joins after launching k_schur_chunk, which needs none of its results.
 // `lm_begin` >= 0 appends k_lm_begin(first = lm_begin) to the tail.
+// `fuse`: K3 of every chunk rides along (k_fused_chunk at the radii in d.w_radius; needs the Jacobi scaling): the next
+// do_schur only assembles.
 static int do_linearize(sba_handle h, bool keep_cost = false, bool fork_tail = false, int lm_begin = -1,
-                        double initial_radius = 0.0) {
+                        double initial_radius = 0.0, bool fuse = false) {
   Dev& d = h->d;
   const DevParams& P = h->P;
   int rc = join_tail(h);
   if (rc) return rc;
-  if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; }
+  const bool fused = fuse && h->fused_ok && h->jacobi_done && d.npchunk > 0;
+  h->schur_fresh = false;
+  if (fused) {
+    CUDA_TRY(cudaMemsetAsync(d.w_fail, 0, (size_t)d.nwin * 4, h->stream));      // the chunk kernel reports singular point blocks
+    LAUNCH(h, k_campre, cdiv(d.Nc, 128), 128, d);
+    k_fused_chunk<<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P); h->launches++;
+    h->schur_fresh = true;
+  } else if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; }
   if (fork_tail && !h->comm.active() && h->jacobi_done && !std::getenv("SBA_NO_FORK")) {
     CUDA_TRY(cudaEventRecord(h->ev_fork, h->stream));
     CUDA_TRY(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
@@ -548,7 +564,7 @@ static int do_linearize(sba_handle h, bool keep_cost = false, bool fork_tail = f
     if (d.nwin > 0) { k_lin_finish<<<d.nwin, kThreads, 0, h->side>>>(d, P, keep_cost ? 1 : 0); h->launches++; }
     if (lm_begin >= 0) {
       // w_fail is cleared on `stream` (k_schur_chunk may set it concurrently with the tail)
-      CUDA_TRY(cudaMemsetAsync(d.w_fail, 0, (size_t)d.nwin * 4, h->stream));
+      if (!fused) CUDA_TRY(cudaMemsetAsync(d.w_fail, 0, (size_t)d.nwin * 4, h->stream));
       k_lm_begin<<<cdiv(d.nwin, 128), 128, 0, h->side>>>(d, P, initial_radius, lm_begin, 0); h->launches++;
     }
     h->tail_pending = true;
@@ -570,7 +586,7 @@ static int do_linearize(sba_handle h, bool keep_cost = false, bool fork_tail = f
     LAUNCH(h, k_jacobi_scale, cdiv((int64_t)d.Nc * 6 + (int64_t)d.Np * 3, 256), 256, d);
     h->jacobi_done = true;
   }
-  if (lm_begin >= 0) LAUNCH(h, k_lm_begin, cdiv(d.nwin, 128), 128, d, P, initial_radius, lm_begin, 1);
+  if (lm_begin >= 0) LAUNCH(h, k_lm_begin, cdiv(d.nwin, 128), 128, d, P, initial_radius, lm_begin, fused ? 0 : 1);
   CUDA_TRY(cudaGetLastError());
   return SBA_OK;
 }
@@ -578,7 +594,8 @@ static int do_linearize(sba_handle h, bool keep_cost = false, bool fork_tail = f
 // K3: damped Schur complement at the per-window radii in d.w_radius.
 static int do_schur(sba_handle h) {
   Dev& d = h->d;
-  if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++; }
+  if (h->schur_fresh) h->schur_fresh = false;      // the fused linearisation already left this radius' partials
+  else if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++; }
   { const int jrc = join_tail(h); if (jrc) return jrc; }
   const int fused = h->comm.active() ? 0 : 1;     // multi-GPU: the partial sums are all-reduced before the cameras are prepared
   LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, fused);
@@ -835,7 +852,7 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
   int rc = check_ready(h, true);
   if (rc) return rc;
   if (!h->jacobi_done) { set_error("sba_time_stage needs a linearisation (sba_linearize)"); return SBA_INVALID_ARGUMENT; }
-  if (stage < 0 || stage > 10) { set_error("unknown stage"); return SBA_INVALID_ARGUMENT; }
+  if (stage < 0 || stage > 11) { set_error("unknown stage"); return SBA_INVALID_ARGUMENT; }
   if (repeats < 1) repeats = 1;
   sba_options o; if (opt) o = *opt; else sba_default_options(&o);
   CUDA_TRY(cudaSetDevice(h->device));
@@ -864,7 +881,7 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
             cudaGraph_t g = nullptr;
             CUDA_TRY(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
             const int64_t l0 = h->launches;
-            int r1 = do_linearize(h, false, true);
+            int r1 = do_linearize(h, false, true, -1, 0.0, true);
             if (!r1) r1 = do_schur(h);
             const cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
             h->step_launches = (int)(h->launches - l0); h->launches = l0;
@@ -877,9 +894,14 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
           CUDA_TRY(cudaGraphLaunch(h->step_graph, h->stream));
           h->launches += h->step_launches;
         } else {
-          if ((rc = do_linearize(h, false, true))) return rc;
+          if ((rc = do_linearize(h, false, true, -1, 0.0, true))) return rc;
           if ((rc = do_schur(h))) return rc;
         }
+        break;
+      case 11:     // the fused K1-K3 chunk kernel alone (camera table from the last k_campre)
+        if (!h->fused_ok) { set_error("fused chunk kernel unavailable for this structure"); return SBA_INVALID_ARGUMENT; }
+        if (i == 0) { LAUNCH(h, k_campre, cdiv(d.Nc, 128), 128, d); CUDA_TRY(cudaEventRecord(h->ev[6], h->stream)); }
+        if (d.npchunk > 0) { k_fused_chunk<<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P); h->launches++; }
         break;
       case 5: LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P); break;
       case 9: LAUNCH(h, k_assemble_cams, d.Nf, kAsmThreads, d); break;
@@ -987,7 +1009,7 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
     const int accepted = h->h_counters[2];
     if (accepted > 0) {
       CUDA_TRY(cudaEventRecord(h->ev[4], h->stream));
-      if ((rc = do_linearize(h, true, true, 0, o.initial_radius))) return rc;
+      if ((rc = do_linearize(h, true, true, 0, o.initial_radius, true))) return rc;
       CUDA_TRY(cudaEventRecord(h->ev[5], h->stream));
       lin_pending = true;
       S.linearizations++;

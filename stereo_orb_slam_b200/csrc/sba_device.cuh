@@ -35,7 +35,8 @@ struct Dev {
   // ---- state
   double *poses, *poses_new;     // [Nc*6]
   double *pts, *pts_new;         // [Np*3]
-  CamPre *campre_new;            // [Nc] trial cameras of the line search (the linearisation computes its own per chunk)
+  CamPre *campre_new;            // [Nc] trial cameras of the line search
+  CamPre *campre;                // [Nc] cameras of the current state, written once per linearisation (k_campre) for k_fused_chunk
   // ---- linearisation
   double *W;                     // [Nobs*18] point order
   double *V, *gp;                // [Np*6], [Np*3]

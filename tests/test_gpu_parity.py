@@ -175,6 +175,29 @@ def test_banded_cholesky_of_a_batch_of_windows_equals_numpy(frames, track):
     assert np.array_equal(s.schur_values()[2], x)                       # bit-reproducible
 
 
+def test_fused_chunk_kernel_equals_the_two_kernel_path_bit_for_bit(small_window, monkeypatch):
+    """k_fused_chunk (K1-K3 of a chunk in one CTA, W kept in registers) against k_lin_chunk + k_schur_chunk (W through
+    HBM): same operations in the same order, so the reduced system and the whole LM trajectory agree to the bit."""
+    monkeypatch.delenv("SBA_NO_FUSED", raising=False)
+    w = c2_window() if False else small_window
+    s = load(w)
+    s.linearize(); s.schur(1e4)
+    ref = s.schur_values()
+    lin_ref = s.get_linearization(residuals=False)
+    s.time_stage(8, 1, False, 1e4)                      # one bench step = fused kernel + assembly
+    got = s.schur_values()
+    lin = s.get_linearization(residuals=False)
+    assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1])
+    for k in ("U", "V", "W", "gc", "gp"):
+        assert np.array_equal(lin[k], lin_ref[k]), k
+    args = (w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
+    a = Solver(0).solve(*args, options=PARITY)
+    monkeypatch.setenv("SBA_NO_FUSED", "1")
+    b = Solver(0).solve(*args, options=PARITY)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and a[2]["final_cost"] == b[2]["final_cost"]
+    assert a[2]["iterations"] == b[2]["iterations"]
+
+
 def test_cooperative_pcg_is_bit_reproducible_on_a_global_problem():
     """k_pcg_coop on thousands of block-rows: every CTA sums the per-row dots itself, so a fast CTA must not
     overwrite them for the next phase while a slow one is still reading (the two phases use separate buffers).

@@ -1,8 +1,10 @@
 // kernels.cuh — hand-written sm_100a kernels of the stereo BA hot path (fp64, HBM-bound).
 //
-// Stage map:  K0 cam_precompute · K1/K2 lin_points + lin_cameras (residual, analytic
-// Jacobian algebra, Huber, U/V/W/g accumulation; Jacobians never reach HBM, W is written once)
-// · K3 schur_pairs / schur_assemble / rhs · K4 pcg_* · K5 backsub · K6 cost_points · lm_control.
+// Stage map:  K0 k_campre (camera table) · K1/K2 k_lin_chunk (residual, analytic Jacobian algebra,
+// Huber, U/V/W/g accumulation per chunk; Jacobians never reach HBM, W is written once) + k_assemble_cams /
+// k_lin_finish · K3 k_schur_chunk + k_assemble_schur · K1-K3 in one kernel: k_fused_chunk · K4 k_chol_band /
+// k_chol_window / k_chol_cluster (exact, windows of <= 64 free cameras), k_spchol (sparse_chol.cuh, above that),
+// k_pcg_* · K5 + K6 + trust-region control: k_step_loop (single GPU) or k_backsub / k_trial_* / k_ls_* / k_lm_*.
 // No global data-path atomics anywhere: every reduction is a fixed-order tree over statically
 // assigned chunks, so results are bit-reproducible run to run.
 #pragma once
@@ -76,12 +78,12 @@ __global__ void k_project_points(int64_t n, double* __restrict__ pts, double lo,
 // ------------------------------------------------------------------------------- K1/K2 per chunk
 // One CTA per chunk (<= kObsChunk = 256 observations of <= kPointChunk consecutive points), one THREAD PER
 // OBSERVATION.  Everything an observation needs is staged in shared memory first with independent, coalesced
-// loads — the chunk's points, and R / J_l / t of the chunk's few cameras ("slots"), computed here from the poses
-// (K0 folded in) — so the only per-thread global reads are idx (1 + 4 B) and uv (16 B).  W (144 B) goes straight
+// loads — the chunk's points, and R / J_l / t of the chunk's few cameras ("slots") from the per-linearisation camera
+// table (K0 = k_campre) — so the only per-thread global reads are idx (1 + 4 B) and uv (16 B).  W (144 B) goes straight
 // to HBM; the point-side sums (V, gp: 9 doubles) and the camera-side operands (A, h, G: 18 doubles) are reduced
-// inside the CTA — per point by its thread, per camera slot by one warp.  The per-(chunk, slot) camera partials
-// are summed over chunks in list order (fixed, no data atomics) by whichever chunk arrives LAST at the camera's
-// counter, so U and gc are complete when the kernel ends and no assemble launch is needed.
+// inside the CTA — per point by its thread, per camera slot by one warp.  The per-(chunk, slot) camera partials go
+// to `cspart`, one 27-double row per slot at its position in the owning camera's list; k_assemble_cams sums each
+// camera's (contiguous) rows in list order afterwards: fixed order, no data atomics.
 constexpr int kLinThreads = 256;
 constexpr int kCamStride = 27;     // doubles per observation in the camera staging area: its U (21) and gc (6) terms
 
@@ -129,10 +131,11 @@ __global__ void __launch_bounds__(kLinThreads, 3) k_lin_chunk(Dev d, DevParams P
     m = __ldg(d.uv_p + e0 + i);
   }
   for (int k = threadIdx.x; k < np * 3; k += kLinThreads) xs[k] = d.pts[(size_t)p0 * 3 + k];
-  for (int s = threadIdx.x; s < ns; s += kLinThreads) {
-    CamPre cp;
-    cam_precompute(d.poses + 6 * (size_t)d.cs_cam[cs0 + s], cp);
-    *reinterpret_cast<CamPre*>(cpre + 21 * s) = cp;
+  // the slot cameras' R / J_l / t come from the per-linearisation table (k_campre): one instance of the sin / cos code
+  // serves every linearisation kernel, and no CTA waits behind a handful of threads doing trigonometry
+  for (int k = threadIdx.x; k < ns * 21; k += kLinThreads) {
+    const int s = k / 21;
+    cpre[k] = reinterpret_cast<const double*>(d.campre + __ldg(d.cs_cam + cs0 + s))[k - 21 * s];
   }
   __syncthreads();
   double cost = 0.0;
@@ -351,12 +354,11 @@ __device__ __forceinline__ void load_W(const double* __restrict__ W, size_t pos,
 //      u = Linv gp
 //   2. the chunk's W (contiguous in point order) staged ONCE into shared memory with coalesced loads, then each
 //      observation's thread turns its row into Z = W Linv^T in place, so that  W_a Vinv W_b^T = Z_a Z_b^T
-//   3. one warp per local block (slot pair sa, sb): lane e owns ELEMENT e of the 6x6 partial and walks the block's
-//      static pair list (a, b): acc += Z_a[row] . Z_b[col] — 3 FMAs per pair and lane, no cross-lane reduction,
-//      no divergence (elements 32..35 are done 8 pairs at a time by the same warp);  one warp per free slot:
+//   3. one warp per local block (slot pair sa, sb) walks the block's static pair list (a, b): one FP64 tensor-core
+//      MMA (m8n8k4) per pair, D += Z_a Z_b^T with rows / columns 6-7 and k = 3 as zero padding; the accumulator
+//      fragment IS the 6x6 partial (no cross-lane reduction) and goes straight to `spart`;  one warp per free slot:
 //      sum of Z_e u[point(e)] = W_e tp -> rpart
-//   4. whichever chunk arrives LAST at a block's / camera's counter sums that block's / camera's partials in
-//      list order (fixed order, no data atomics): Su and rsum are complete when the kernel ends.
+//   4. k_assemble_schur sums every block's / camera's partial rows (contiguous by construction) in list order.
 // ---- TMA 1-D bulk copy global -> shared (cp.async.bulk, completion on an mbarrier): one elected thread moves a
 // whole tile without spending load/store instructions or registers, and the CTA computes while it is in flight.
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -1450,10 +1452,11 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
 //   (c) trailing update A_ij -= L_ik L_jk^T over the m (m + 1) / 2 blocks of the envelope it touches, a thread per
 //       element; y_j -= L_jk y_k
 // and the back substitution by warp 0 alone.  Fixed order throughout: bit-reproducible.
-constexpr int kBandThreads = 256;
+constexpr int kBandThreads = 512;
 
+// envelope blocks, inverse diagonal factors, right-hand side, the (ii, jj) table of the trailing-update pairs, ints
 __host__ __device__ __forceinline__ size_t chol_band_smem_bytes(int nf, int env_blocks) {
-  return ((size_t)env_blocks * 36 + (size_t)nf * 36 + (size_t)nf * 6 + 48) * 8 + ((size_t)2 * nf + 2) * 4;
+  return ((size_t)env_blocks * 36 + (size_t)nf * 36 + (size_t)nf * 6 + 48) * 8 + ((size_t)2 * nf + 2) * 4 + (size_t)nf * (nf + 1);
 }
 
 // Lanes 0..5 of the calling warp hold row `lane` of a symmetric positive definite 6x6 block in a[0..5] (lower part
@@ -1503,24 +1506,27 @@ __global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t
   if (d.w_status[w] != 0 || d.w_fail[w] != 0) return;     // uniform per CTA; leaves x untouched (unused)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   __shared__ int bad;
-  __shared__ int env_total;
+  __shared__ int env_total, m_max;
   // per-window envelope: last[k] (window-local) and the block offset of every column
   int* lastk = reinterpret_cast<int*>(smem);                 // [nf]
   int* coff = lastk + nf;                                    // [nf + 1]
   double* base = smem + (2 * nf + 2 + 1) / 2;                // 8-byte aligned past the 2 nf + 1 ints
   if (tid == 0) {
     bad = 0;
-    int acc = 0;
-    for (int k = 0; k < nf; ++k) { const int l = band_last[f0 + k] - f0; lastk[k] = l; coff[k] = acc; acc += l - k + 1; }
-    coff[nf] = acc; env_total = acc;
+    int acc = 0, mm = 0;
+    for (int k = 0; k < nf; ++k) { const int l = band_last[f0 + k] - f0; lastk[k] = l; coff[k] = acc; acc += l - k + 1; mm = max(mm, l - k); }
+    coff[nf] = acc; env_total = acc; m_max = mm;
   }
   __syncthreads();
-  const int nenv = env_total;
+  const int nenv = env_total, mmax = m_max;
   double* A = base;                                          // [nenv * 36] column envelopes, block (k + ii, k) at coff[k] + ii
   double* LI = A + (size_t)nenv * 36;                        // [nf * 36] inverse diagonal factors
   double* y = LI + (size_t)nf * 36;                          // [n]
+  uint16_t* ptab = reinterpret_cast<uint16_t*>(y + n + 8);   // [mmax (mmax + 1) / 2] trailing-update pair p -> ii | jj << 8
   for (int i = tid; i < nenv * 36; i += T) A[i] = 0.0;
   for (int i = tid; i < n; i += T) y[i] = d.rhs[(size_t)f0 * 6 + i];
+  for (int ii = tid; ii < mmax; ii += T)
+    for (int jj = 0; jj <= ii; ++jj) ptab[ii * (ii + 1) / 2 + jj] = (uint16_t)(ii | (jj << 8));
   __syncthreads();
   {
     // upper block (r, c), r <= c, of S  ->  lower block (c, r) = its transpose, in column r
@@ -1533,22 +1539,24 @@ __global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t
     }
   }
   __syncthreads();
+  // 6x6 Cholesky + inverse of the diagonal block of column k (warp 0)
+  auto factor_column = [&](int k) {
+    const double* dk = A + (size_t)coff[k] * 36;
+    double a[6], x[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int c = 0; c < 6; ++c) a[c] = dk[6 * (lane < 6 ? lane : 0) + c];
+    if (!warp_chol6_inverse(a, x, lane) && lane == 0) bad = 1;
+    if (lane < 6) {
+#pragma unroll
+      for (int i = 0; i < 6; ++i) LI[(size_t)k * 36 + 6 * i + lane] = x[i];
+    }
+  };
+  if (warp == 0) factor_column(0);
+  __syncthreads();
   for (int k = 0; k < nf; ++k) {
     const int m = lastk[k] - k;
     double* colk = A + (size_t)coff[k] * 36;
-    double* li = LI + (size_t)k * 36;
-    // (a) diagonal block
-    if (warp == 0) {
-      double a[6], x[6] = {0, 0, 0, 0, 0, 0};
-#pragma unroll
-      for (int c = 0; c < 6; ++c) a[c] = colk[6 * (lane < 6 ? lane : 0) + c];
-      if (!warp_chol6_inverse(a, x, lane) && lane == 0) bad = 1;
-      if (lane < 6) {
-#pragma unroll
-        for (int i = 0; i < 6; ++i) li[6 * i + lane] = x[i];
-      }
-    }
-    __syncthreads();
+    const double* li = LI + (size_t)k * 36;
     // (b) panel, a thread per block row (it reads its six entries before it writes them: in place), and the
     //     right-hand side block by the last six threads (one warp: the barrier between reads and writes is a warp's)
     for (int idx = tid; idx < m * 6; idx += T) {
@@ -1577,26 +1585,44 @@ __global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t
       if (c >= 0) y[6 * k + c] = yk;
     }
     __syncthreads();
-    // (c) trailing update inside the envelope: block (k + ii, k + jj), 1 <= jj <= ii <= m, lives in column k + jj
+    // (c) trailing update inside the envelope: block (k + 1 + ii, k + 1 + jj), 0 <= jj <= ii < m, lives in column
+    //     k + 1 + jj.  Look-ahead: warp 0 takes pair 0 = the next diagonal block first and factors it straight away,
+    //     while the other warps run the rest of the update.
     const int npair = m * (m + 1) / 2;
-    for (int idx = tid; idx < npair * 36; idx += T) {
-      const int p = idx / 36, e = idx - 36 * p, r = e / 6, c = e - 6 * r;
-      int ii = (int)((sqrtf(8.f * (float)p + 1.f) - 1.f) * 0.5f);
-      while ((ii + 1) * (ii + 2) / 2 <= p) ++ii;
-      while (ii * (ii + 1) / 2 > p) --ii;
-      const int jj = p - ii * (ii + 1) / 2;                  // 0 <= jj <= ii < m
-      const double* Li = colk + (size_t)(1 + ii) * 36 + 6 * r;
-      const double* Lj = colk + (size_t)(1 + jj) * 36 + 6 * c;
-      const double acc = (Li[0] * Lj[0] + Li[1] * Lj[1] + Li[2] * Lj[2]) + (Li[3] * Lj[3] + Li[4] * Lj[4] + Li[5] * Lj[5]);
-      A[(size_t)(coff[k + 1 + jj] + (ii - jj)) * 36 + e] -= acc;
-    }
-    for (int idx = tid; idx < m * 6; idx += T) {
-      const int ii = idx / 6, r = idx - 6 * ii;
-      const double* Lr = colk + (size_t)(1 + ii) * 36 + 6 * r;
-      double acc = 0.0;
+    if (warp == 0) {
+      if (m > 0) {
+        const double* L1 = colk + 36;
+        double* dst = A + (size_t)coff[k + 1] * 36;
 #pragma unroll
-      for (int t = 0; t < 6; ++t) acc += Lr[t] * y[6 * k + t];
-      y[6 * (k + 1 + ii) + r] -= acc;
+        for (int pass = 0; pass < 2; ++pass) {
+          const int e = lane + 32 * pass;
+          if (e < 36) {
+            const int r = e / 6, c = e - 6 * r;
+            const double* Li = L1 + 6 * r; const double* Lj = L1 + 6 * c;
+            dst[e] -= (Li[0] * Lj[0] + Li[1] * Lj[1] + Li[2] * Lj[2]) + (Li[3] * Lj[3] + Li[4] * Lj[4] + Li[5] * Lj[5]);
+          }
+        }
+        __syncwarp();
+      }
+      if (k + 1 < nf) factor_column(k + 1);
+    } else {
+      for (int idx = tid - 32; idx < (npair - 1) * 36; idx += T - 32) {
+        const int p = 1 + idx / 36, e = idx - 36 * (p - 1), r = e / 6, c = e - 6 * r;
+        const unsigned pr = ptab[p];
+        const int ii = pr & 255u, jj = pr >> 8;
+        const double* Li = colk + (size_t)(1 + ii) * 36 + 6 * r;
+        const double* Lj = colk + (size_t)(1 + jj) * 36 + 6 * c;
+        const double acc = (Li[0] * Lj[0] + Li[1] * Lj[1] + Li[2] * Lj[2]) + (Li[3] * Lj[3] + Li[4] * Lj[4] + Li[5] * Lj[5]);
+        A[(size_t)(coff[k + 1 + jj] + (ii - jj)) * 36 + e] -= acc;
+      }
+      for (int idx = tid - 32; idx < m * 6; idx += T - 32) {
+        const int ii = idx / 6, r = idx - 6 * ii;
+        const double* Lr = colk + (size_t)(1 + ii) * 36 + 6 * r;
+        double acc = 0.0;
+#pragma unroll
+        for (int t = 0; t < 6; ++t) acc += Lr[t] * y[6 * k + t];
+        y[6 * (k + 1 + ii) + r] -= acc;
+      }
     }
     __syncthreads();
   }

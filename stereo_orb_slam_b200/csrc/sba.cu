@@ -551,9 +551,9 @@ static int do_linearize(sba_handle h, bool keep_cost = false, bool fork_tail = f
   if (rc) return rc;
   const bool fused = fuse && h->fused_ok && h->jacobi_done && d.npchunk > 0;
   h->schur_fresh = false;
+  LAUNCH(h, k_campre, cdiv(d.Nc, 128), 128, d);      // K0: camera table of this linearisation
   if (fused) {
     CUDA_TRY(cudaMemsetAsync(d.w_fail, 0, (size_t)d.nwin * 4, h->stream));      // the chunk kernel reports singular point blocks
-    LAUNCH(h, k_campre, cdiv(d.Nc, 128), 128, d);
     k_fused_chunk<<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P); h->launches++;
     h->schur_fresh = true;
   } else if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; }
@@ -867,7 +867,8 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
     if (flush_l2) CUDA_TRY(cudaMemsetAsync(h->flush, i & 0xff, flush_bytes, h->stream));
     CUDA_TRY(cudaEventRecord(h->ev[6], h->stream));
     switch (stage) {
-      case 0: if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; } break;
+      case 0: if (i == 0) { LAUNCH(h, k_campre, cdiv(d.Nc, 128), 128, d); CUDA_TRY(cudaEventRecord(h->ev[6], h->stream)); }
+              if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; } break;
       case 1: LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 1); break;
       case 2: if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++; } break;
       case 3: if ((rc = do_linearize(h))) return rc; break;

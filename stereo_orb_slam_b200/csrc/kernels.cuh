@@ -605,8 +605,10 @@ __global__ void __launch_bounds__(kFusedThreads, 2) k_fused_chunk(Dev d, DevPara
   double* us = Li + (size_t)np * 6;                        // [np * 3]  u = Linv gp
   uint8_t* opl = reinterpret_cast<uint8_t*>(us + (size_t)np * 3);   // [n] chunk-local point of each observation
   double* Z = cam_st;
-  uint16_t* prs = reinterpret_cast<uint16_t*>(pt_st);
-  const bool pairs_staged = (size_t)npq * 2 <= (size_t)n * 72;
+  // pair lists staged as BYTE offsets of the two Z rows (a * 152 | b * 152 << 16): the inner loop spends its issue
+  // slots on the two loads and the MMA, not on unpacking indices
+  uint32_t* prs = reinterpret_cast<uint32_t*>(pt_st);
+  const bool pairs_staged = (size_t)npq * 4 <= (size_t)n * 72;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int NW = kFusedThreads / 32;
   // ---- stage: independent loads only
@@ -775,38 +777,50 @@ __global__ void __launch_bounds__(kFusedThreads, 2) k_fused_chunk(Dev d, DevPara
       z[3 * r + 1] = w0 * i10 + w1 * i11;
       z[3 * r + 2] = w0 * i20 + w1 * i21 + w2 * i22;
     }
+    z[18] = 0.0;                       // the pad element: what the lanes outside the 6x3 operand feed to the MMA
   }
+  constexpr unsigned kRowBytes = kFZStride * 8;
+  static_assert(255u * kRowBytes < 65536u, "row offsets fit 16 bits");
   if (pairs_staged)
-    for (int k = threadIdx.x; k < npq; k += kFusedThreads) prs[k] = __ldg(d.pairs + pq0 + k);
+    for (int k = threadIdx.x; k < npq; k += kFusedThreads) {
+      const unsigned pr = __ldg(d.pairs + pq0 + k);
+      prs[k] = (pr & 255u) * kRowBytes | ((pr >> 8) * kRowBytes) << 16;
+    }
   __syncthreads();
-  // ---- D: local blocks, one warp per block, one FP64 tensor-core MMA (m8n8k4) per pair (see k_schur_chunk)
+  // ---- D: local blocks, one warp per block, one FP64 tensor-core MMA (m8n8k4) per pair (see k_schur_chunk).  Lane
+  //      (g, t) feeds element 3 g + t of both rows; the lanes outside the 6x3 operand read the rows' zero pad.
   const int g = lane >> 2, t = lane & 3;
   const bool feeds = g < 6 && t < 3;
-  const double* Zl = Z + (feeds ? 3 * g + t : 0);
+  const char* Zl = reinterpret_cast<const char*>(Z + (feeds ? 3 * g + t : 18));
   for (int lb = lb0 + warp; lb < lb1; lb += NW) {
     const int q0 = d.lb_pair_off[lb] - pq0, q1 = d.lb_pair_off[lb + 1] - pq0;
     double a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0;
-    auto mma_pair = [&](unsigned pr, double& x0, double& x1) {
-      double a = 0.0, b = 0.0;
-      if (feeds) { a = Zl[(pr & 255u) * kFZStride]; b = Zl[(pr >> 8) * kFZStride]; }
+    auto mma_off = [&](unsigned en, double& x0, double& x1) {
+      const double a = *reinterpret_cast<const double*>(Zl + (en & 0xffffu));
+      const double b = *reinterpret_cast<const double*>(Zl + (en >> 16));
       dmma884(x0, x1, a, b);
     };
     if (pairs_staged) {
+      // even pairs of the list go to one accumulator chain, odd pairs to the other (fixed order)
       int qq = q0;
-      if ((qq & 1) && qq < q1) { mma_pair(prs[qq], b0, b1); ++qq; }
-      const uint32_t* pp = reinterpret_cast<const uint32_t*>(prs);
-      for (; qq + 1 < q1; qq += 2) {
-        const uint32_t two = pp[qq >> 1];
-        mma_pair(two & 0xffffu, a0, a1);
-        mma_pair(two >> 16, b0, b1);
+      if ((qq & 1) && qq < q1) { mma_off(prs[qq], b0, b1); ++qq; }
+      for (; qq + 3 < q1; qq += 4) {
+        const uint2 e01 = *reinterpret_cast<const uint2*>(prs + qq), e23 = *reinterpret_cast<const uint2*>(prs + qq + 2);
+        mma_off(e01.x, a0, a1); mma_off(e01.y, b0, b1);
+        mma_off(e23.x, a0, a1); mma_off(e23.y, b0, b1);
       }
-      if (qq < q1) mma_pair(prs[qq], a0, a1);
+      for (; qq + 1 < q1; qq += 2) {
+        const uint2 e01 = *reinterpret_cast<const uint2*>(prs + qq);
+        mma_off(e01.x, a0, a1); mma_off(e01.y, b0, b1);
+      }
+      if (qq < q1) mma_off(prs[qq], a0, a1);
     } else {
       const uint16_t* gp = d.pairs + pq0;
+      auto mma_idx = [&](unsigned pr, double& x0, double& x1) { mma_off((pr & 255u) * kRowBytes | ((pr >> 8) * kRowBytes) << 16, x0, x1); };
       int qq = q0;
-      if ((qq & 1) && qq < q1) { mma_pair(__ldg(gp + qq), b0, b1); ++qq; }
-      for (; qq + 1 < q1; qq += 2) { mma_pair(__ldg(gp + qq), a0, a1); mma_pair(__ldg(gp + qq + 1), b0, b1); }
-      if (qq < q1) mma_pair(__ldg(gp + qq), a0, a1);
+      if ((qq & 1) && qq < q1) { mma_idx(__ldg(gp + qq), b0, b1); ++qq; }
+      for (; qq + 1 < q1; qq += 2) { mma_idx(__ldg(gp + qq), a0, a1); mma_idx(__ldg(gp + qq + 1), b0, b1); }
+      if (qq < q1) mma_idx(__ldg(gp + qq), a0, a1);
     }
     if (feeds) *reinterpret_cast<double2*>(d.spart + (size_t)d.lb_pos[lb] * 36 + 6 * g + 2 * t) = make_double2(a0 + b0, a1 + b1);
   }
@@ -1452,6 +1466,8 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_chol_window(Dev d) {
 //   (c) trailing update A_ij -= L_ik L_jk^T over the m (m + 1) / 2 blocks of the envelope it touches, a thread per
 //       element; y_j -= L_jk y_k
 // and the back substitution by warp 0 alone.  Fixed order throughout: bit-reproducible.
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+
 constexpr int kBandThreads = 512;
 
 // envelope blocks, inverse diagonal factors, right-hand side, the (ii, jj) table of the trailing-update pairs, ints
@@ -1495,9 +1511,13 @@ __device__ __forceinline__ bool warp_chol6_inverse(double (&a)[6], double (&x)[6
   return ok;
 }
 
-__global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t* __restrict__ band_last) {
+__global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t* __restrict__ band_last, int profile) {
   extern __shared__ double smem[];
   constexpr int T = kBandThreads;
+  // profile != 0 (SBA_DEBUG_LS=2): thread 0 of window 0 prints the nanoseconds per phase, summed over the columns (tuning aid)
+  const bool prof = profile != 0 && blockIdx.x == 0 && threadIdx.x == 0;
+  unsigned long long tq0 = prof ? gtimer() : 0, tq[6] = {0, 0, 0, 0, 0, 0};
+  auto lap = [&](int i) { if (prof) { const unsigned long long t = gtimer(); tq[i] += t - tq0; tq0 = t; } };
   const int w = blockIdx.x;
   const int f0 = d.win_fc_off[w], f1 = d.win_fc_off[w + 1];
   const int nf = f1 - f0, n = 6 * nf;
@@ -1551,8 +1571,10 @@ __global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t
       for (int i = 0; i < 6; ++i) LI[(size_t)k * 36 + 6 * i + lane] = x[i];
     }
   };
+  lap(0);
   if (warp == 0) factor_column(0);
   __syncthreads();
+  lap(2);
   for (int k = 0; k < nf; ++k) {
     const int m = lastk[k] - k;
     double* colk = A + (size_t)coff[k] * 36;
@@ -1585,6 +1607,7 @@ __global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t
       if (c >= 0) y[6 * k + c] = yk;
     }
     __syncthreads();
+    lap(1);
     // (c) trailing update inside the envelope: block (k + 1 + ii, k + 1 + jj), 0 <= jj <= ii < m, lives in column
     //     k + 1 + jj.  Look-ahead: warp 0 takes pair 0 = the next diagonal block first and factors it straight away,
     //     while the other warps run the rest of the update.
@@ -1605,6 +1628,7 @@ __global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t
         __syncwarp();
       }
       if (k + 1 < nf) factor_column(k + 1);
+      lap(2);
     } else {
       for (int idx = tid - 32; idx < (npair - 1) * 36; idx += T - 32) {
         const int p = 1 + idx / 36, e = idx - 36 * (p - 1), r = e / 6, c = e - 6 * r;
@@ -1625,6 +1649,7 @@ __global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t
       }
     }
     __syncthreads();
+    lap(3);
   }
   // back substitution by warp 0: x_k = Linv_kk^T (y_k - sum over the column's rows of L_ik^T x_i), five row groups of
   // six lanes summed in lane order
@@ -1656,6 +1681,7 @@ __global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t
     }
   }
   __syncthreads();
+  lap(4);
   const bool fail = bad != 0;
   for (int i = tid; i < n; i += T) {
     const double v = y[i];
@@ -1665,6 +1691,8 @@ __global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t
   }
   __syncthreads();
   if (tid == 0 && bad != 0) d.w_fail[w] = 1;
+  lap(5);
+  if (prof) printf("[band] nf %d  setup %llu  panel+barrier %llu  diag update+factor (warp 0) %llu  wait for the update %llu  back substitution %llu  write %llu ns\n", nf, tq[0], tq[1], tq[2], tq[3], tq[4], tq[5]);
 }
 
 // The same factorisation for a mid-size window (a 50-keyframe sliding window: 294 unknowns, 1225 lower blocks =
@@ -1676,7 +1704,6 @@ __global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t
 //                columns j > k (A_ij -= L_ik L_jk^T, y_j -= L_jk y_k)
 // Back substitution: the owner of column k holds all L_ik (i > k): x_k = Linv_kk^T (y_k - sum L_ik^T x_i), pushed
 // to every CTA's copy of x, one cluster barrier per column.  Fixed order throughout: bit-reproducible.
-__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 
 constexpr int kCholCluster = 8;
 constexpr int kCholClThreads = 256;

@@ -82,7 +82,7 @@ struct sba_handle_s {
   size_t fused_smem = 0; bool fused_ok = false;   // k_fused_chunk (K1-K3 of a chunk in one CTA)
   bool schur_fresh = false;              // the last linearisation was fused: spart / rpart already hold this radius' Schur partials
   // exact block-sparse Cholesky of the reduced system for windows of more than kCholMaxCams free cameras (k_spchol)
-  SparseCholSymbolic sym; bool sym_ok = false; SpCholDev sp{}; bool spchol_ok = false; int spchol_blocks = 0; double time_symbolic_s = 0.0;
+  SparseCholSymbolic sym; bool sym_ok = false; SpCholDev sp{}; bool spchol_ok = false; int spchol_blocks = 0; size_t spchol_smem = 0; double time_symbolic_s = 0.0;
 
   template <typename T>
   int alloc(T** p, size_t n) {
@@ -429,6 +429,8 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
       if ((rc = h->upload(&sp.row_idx, Y.row_idx))) return rc;
       if ((rc = h->upload(&sp.init_src, Y.init_src))) return rc;
       if ((rc = h->upload(&sp.upd_ptr, Y.upd_ptr))) return rc;
+      if ((rc = h->upload(&sp.upd_ext_end, Y.upd_ext_end))) return rc;
+      if ((rc = h->upload(&sp.rowl_ext_end, Y.rowl_ext_end))) return rc;
       if ((rc = h->upload(&sp.upd_a, Y.upd_a))) return rc;
       if ((rc = h->upload(&sp.upd_b, Y.upd_b))) return rc;
       if ((rc = h->upload(&sp.rowl_ptr, Y.rowl_ptr))) return rc;
@@ -440,8 +442,23 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
       if ((rc = h->alloc(&sp.Lv, (size_t)Y.nnzL() * 36))) return rc;
       if ((rc = h->alloc(&sp.Li, (size_t)Y.n * 36))) return rc;
       if ((rc = h->alloc(&sp.y, (size_t)Y.n * 6))) return rc;
+      {
+        // chains of up to panel_cap blocks are factored out of shared memory; size the launch for the largest that fits
+        int cap = 1;
+        for (size_t c = 0; c < Y.lvl_cols.size(); ++c) {
+          const int nb = Y.col_ptr[Y.lvl_cols[c] + Y.lvl_len[c]] - Y.col_ptr[Y.lvl_cols[c]];
+          if (nb <= kSpPanelMax && Y.lvl_len[c] <= kSpChainMax) cap = std::max(cap, nb);
+        }
+        sp.panel_cap = cap;
+        h->spchol_smem = spchol_smem_bytes(cap);
+        CUDA_TRY(cudaFuncSetAttribute(k_spchol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spchol_smem));
+        int per_sm = 0, sms = 0;
+        CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_spchol, kSpThreads, h->spchol_smem));
+        h->spchol_blocks = std::min(per_sm, 1) * sms;
+      }
       CUDA_TRY(cudaStreamSynchronize(h->stream));
-      h->spchol_ok = true;
+      h->spchol_ok = h->spchol_blocks > 0;
       if (std::getenv("SBA_TIMING"))
         std::fprintf(stderr, "[sba] sparse Cholesky symbolic: %.3f ms, %d block columns, %lld blocks in L (%lld in S), %lld products, %lld chains in %d levels\n",
                      1e3 * h->time_symbolic_s, Y.n, (long long)Y.nnzL(), (long long)H.blk_row.size(), (long long)Y.nupd(), (long long)Y.nchain(), Y.nlev);
@@ -626,13 +643,13 @@ static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
     if (const char* e = std::getenv("SBA_SPCHOL_GRID")) grid = std::max(1, std::min(grid, std::atoi(e)));   // tuning aid
     Dev dd = d; SpCholDev ss = h->sp;
     void* args[] = {&dd, &ss};
-    CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_spchol, dim3(grid), dim3(kSpThreads), args, 0, h->stream));
+    CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_spchol, dim3(grid), dim3(kSpThreads), args, h->spchol_smem, h->stream));
     h->launches++;
     it = -1;
   } else if (d.Nf > 0 && h->chol_ok && opt->linear_solver != 1) {
     CUDA_TRY(cudaMemsetAsync(d.counters + 4, 0, 4, h->stream));
     if (h->chol_band_ok && !std::getenv("SBA_FORCE_CLUSTER")) {
-      k_chol_band<<<d.nwin, kBandThreads, h->chol_band_smem, h->stream>>>(d, h->band_last);
+      k_chol_band<<<d.nwin, kBandThreads, h->chol_band_smem, h->stream>>>(d, h->band_last, (int)(h->P.debug == 2));
     } else if (h->chol_cluster_ok) {
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3((unsigned)d.nwin * kCholCluster); cfg.blockDim = dim3(kCholClThreads);

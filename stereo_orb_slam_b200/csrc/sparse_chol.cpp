@@ -284,6 +284,29 @@ std::string sparse_chol_symbolic(int32_t n, const std::vector<int32_t>& blk_row,
     if (p >= 0 && chain_of[p] != chain_of[j])
       chain_level[chain_of[p]] = std::max(chain_level[chain_of[p]], chain_level[chain_of[j]] + 1);
   }
+  // product lists and row lists are sorted by source column k: the sources OUTSIDE the block's own chain come first
+  // (k < first column of the chain).  The kernel gathers those from L2 for a whole chain at once and runs the
+  // in-chain part out of shared memory.
+  {
+    std::vector<int32_t> col_of_blk(nnzL);
+    for (int j = 0; j < n; ++j) for (int32_t b = C.col_ptr[j]; b < C.col_ptr[j + 1]; ++b) col_of_blk[b] = j;
+    C.upd_ext_end.resize(nnzL);
+    for (int j = 0; j < n; ++j) {
+      const int32_t j0 = chain_start[chain_of[j]];
+      for (int32_t b = C.col_ptr[j]; b < C.col_ptr[j + 1]; ++b) {
+        int64_t u = C.upd_ptr[b];
+        while (u < C.upd_ptr[b + 1] && col_of_blk[C.upd_a[u]] < j0) ++u;
+        C.upd_ext_end[b] = u;
+      }
+    }
+    C.rowl_ext_end.resize(n);
+    for (int j = 0; j < n; ++j) {
+      const int32_t j0 = chain_start[chain_of[j]];
+      int32_t e = C.rowl_ptr[j];
+      while (e < C.rowl_ptr[j + 1] && C.rowl_col[e] < j0) ++e;
+      C.rowl_ext_end[j] = e;
+    }
+  }
   const int nchain = (int)chain_start.size();
   int nlev = 1;
   for (int c = 0; c < nchain; ++c) nlev = std::max(nlev, chain_level[c] + 1);

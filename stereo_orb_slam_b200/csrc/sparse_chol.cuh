@@ -17,11 +17,11 @@
 namespace sba {
 
 struct SpCholDev {
-  int32_t n, nlev, nnzL;
+  int32_t n, nlev, nnzL, panel_cap;
   const int32_t *perm, *col_ptr, *row_idx, *init_src;
-  const int64_t* upd_ptr;
+  const int64_t *upd_ptr, *upd_ext_end;
   const int32_t *upd_a, *upd_b;
-  const int32_t *rowl_ptr, *rowl_blk, *rowl_col, *lvl_ptr, *lvl_cols, *lvl_len;
+  const int32_t *rowl_ptr, *rowl_ext_end, *rowl_blk, *rowl_col, *lvl_ptr, *lvl_cols, *lvl_len;
   double* Lv;     // [nnzL * 36] blocks of L, row-major 6x6 (block (i, j): rows of i, columns of j)
   double* Li;     // [n * 36]    inverse diagonal factors (lower)
   double* y;      // [n * 6]     forward-substituted right-hand side, then the solution (new order)
@@ -29,7 +29,15 @@ struct SpCholDev {
 
 constexpr int kSpThreads = 512;
 constexpr int kSpWarps = kSpThreads / 32;
-constexpr int kSpStage = 64;      // blocks of one column staged in shared memory between gather and panel (18 KB)
+constexpr int kSpStage = 64;       // fallback path: blocks of one column staged in shared memory between gather and panel
+constexpr int kSpPanelMax = 400;   // blocks of one chain held in shared memory (115 KB)
+constexpr int kSpChainMax = 64;    // columns of such a chain
+
+// dynamic shared memory of k_spchol for chains of up to `cap` blocks: panel, external x, row indices, t / y / x of the
+// chain's columns, their inverse factors
+__host__ __device__ __forceinline__ size_t spchol_smem_bytes(int cap) {
+  return ((size_t)cap * 36 + (size_t)cap * 6 + (size_t)(cap + 1) / 2 + kSpChainMax * 6 + kSpChainMax * 36 + 8) * 8;
+}
 
 // sum over the products [u0, u1) of one block's list of L_a L_b^T, on the FP64 tensor cores: two m8n8k4 MMAs per
 // product, operands straight from L2 (four products = 16 loads in flight per lane before the first MMA), even and
@@ -70,8 +78,32 @@ __device__ __forceinline__ void sp_gather(const SpCholDev& sc, int64_t u0, int64
   r0 = c0 + e0; r1 = c1 + e1;
 }
 
+// the same sum for products whose operands sit in the chain's shared-memory panel P (block ids relative to blk0)
+__device__ __forceinline__ void sp_gather_panel(const SpCholDev& sc, const double* P, int blk0, int64_t u0, int64_t u1, int lane,
+                                                double& r0, double& r1) {
+  const int g = lane >> 2, t4 = lane & 3;
+  const bool f0 = g < 6, f1 = g < 6 && t4 < 2;
+  const int o0 = 6 * (f0 ? g : 0) + t4, o1 = 6 * (f1 ? g : 0) + (f1 ? t4 + 4 : 0);
+  double c0 = 0.0, c1 = 0.0, e0 = 0.0, e1 = 0.0;
+  for (int64_t ub = u0; ub < u1; ub += 32) {
+    const int m = (int)min((int64_t)32, u1 - ub);
+    const int ia = (lane < m) ? __ldg(sc.upd_a + ub + lane) - blk0 : 0;
+    const int ib = (lane < m) ? __ldg(sc.upd_b + ub + lane) - blk0 : 0;
+    for (int u = 0; u < m; ++u) {
+      const double* A = P + (size_t)__shfl_sync(0xffffffffu, ia, u) * 36;
+      const double* B = P + (size_t)__shfl_sync(0xffffffffu, ib, u) * 36;
+      const double a00 = f0 ? A[o0] : 0.0, b00 = f0 ? B[o0] : 0.0;
+      const double a01 = f1 ? A[o1] : 0.0, b01 = f1 ? B[o1] : 0.0;
+      if (u & 1) { dmma884(e0, e1, a00, b00); dmma884(e0, e1, a01, b01); }
+      else { dmma884(c0, c1, a00, b00); dmma884(c0, c1, a01, b01); }
+    }
+  }
+  r0 = c0 + e0; r1 = c1 + e1;
+}
+
 __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  extern __shared__ double dyn[];
   __shared__ double col_st[kSpStage * 36];
   __shared__ double part[kSpWarps * 36];      // slice partials when a block's product list is split over several warps
   __shared__ double akk[36], li_s[36], tj[8];
@@ -80,6 +112,13 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
     if (blockIdx.x == 0 && tid == 0) d.w_pcg_it[0] = 0;
     return;
   }
+  // chain panel in shared memory (chains of <= panel_cap blocks and <= kSpChainMax columns; others go column by column through L2)
+  const int cap = sc.panel_cap;
+  double* P = dyn;                                  // [cap * 36]
+  double* xe = P + (size_t)cap * 36;                // [cap * 6]   backward: x of rows outside the chain
+  int* rowi = reinterpret_cast<int*>(xe + (size_t)cap * 6);   // [cap] backward: block rows
+  double* ty = xe + (size_t)cap * 6 + (cap + 1) / 2;          // [kSpChainMax * 6] t_j -> y_j -> x_j of the chain's columns
+  double* LIc = ty + kSpChainMax * 6;               // [kSpChainMax * 36] their inverse diagonal factors
   // ---- 0: scatter S into the pattern of L
   {
     const int64_t tot = (int64_t)sc.nnzL * 36;
@@ -101,13 +140,120 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
   for (int lvl = 0; lvl < sc.nlev; ++lvl) {
     const int c_begin = __ldg(sc.lvl_ptr + lvl), c_end = __ldg(sc.lvl_ptr + lvl + 1);
     for (int ci = c_begin + blockIdx.x; ci < c_end; ci += gridDim.x) {
-      const int j0 = __ldg(sc.lvl_cols + ci), jn = j0 + __ldg(sc.lvl_len + ci);
+      const int j0 = __ldg(sc.lvl_cols + ci), len = __ldg(sc.lvl_len + ci), jn = j0 + len;
+      const int blk0 = __ldg(sc.col_ptr + j0), nblk = __ldg(sc.col_ptr + jn) - blk0;
+      if (nblk <= cap && len <= kSpChainMax) {
+        // ======== the chain's panel lives in shared memory
+        // S1: everything that comes from OUTSIDE the chain, for all its blocks / columns at once (L2 latency is paid once)
+        for (int bi = warp; bi < nblk; bi += kSpWarps) {
+          const int blk = blk0 + bi;
+          double r0, r1;
+          sp_gather(sc, sc.upd_ptr[blk], sc.upd_ext_end[blk], lane, r0, r1);
+          if (fout) {
+            const int e = 6 * g + 2 * t4;
+            const double2 a = __ldcg(reinterpret_cast<const double2*>(sc.Lv + (size_t)blk * 36 + e));
+            P[bi * 36 + e] = a.x - r0; P[bi * 36 + e + 1] = a.y - r1;
+          }
+        }
+        for (int q = kSpWarps - 1 - warp; q < len; q += kSpWarps) {
+          const int j = j0 + q;
+          double acc = 0.0;
+          if (lane < 30) {
+            const int r1 = __ldg(sc.rowl_ext_end + j);
+            for (int e = __ldg(sc.rowl_ptr + j) + ps; e < r1; e += 5) {
+              const double* L = sc.Lv + (size_t)__ldg(sc.rowl_blk + e) * 36 + 6 * ri;
+              const double* yk = sc.y + (size_t)__ldg(sc.rowl_col + e) * 6;
+              acc += (__ldcg(L) * __ldcg(yk) + __ldcg(L + 1) * __ldcg(yk + 1) + __ldcg(L + 2) * __ldcg(yk + 2)) +
+                     (__ldcg(L + 3) * __ldcg(yk + 3) + __ldcg(L + 4) * __ldcg(yk + 4) + __ldcg(L + 5) * __ldcg(yk + 5));
+            }
+          }
+          double tot = acc;
+#pragma unroll
+          for (int qq = 1; qq < 5; ++qq) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * qq) & 31);
+          if (lane < 6) ty[q * 6 + lane] = d.rhs[(size_t)__ldg(sc.perm + j) * 6 + lane] - tot;
+        }
+        __syncthreads();
+        // S2: the chain's columns in sequence, all operands in shared memory
+        for (int q = 0; q < len; ++q) {
+          const int j = j0 + q;
+          const int cb0 = __ldg(sc.col_ptr + j) - blk0, nb = __ldg(sc.col_ptr + j + 1) - blk0 - cb0;
+          if (q > 0) {
+            for (int bi = warp; bi < nb; bi += kSpWarps) {
+              const int blk = blk0 + cb0 + bi;
+              const int64_t u0 = sc.upd_ext_end[blk], u1 = sc.upd_ptr[blk + 1];
+              if (u1 > u0) {
+                double r0, r1;
+                sp_gather_panel(sc, P, blk0, u0, u1, lane, r0, r1);
+                if (fout) { const int e = 6 * g + 2 * t4; P[(cb0 + bi) * 36 + e] -= r0; P[(cb0 + bi) * 36 + e + 1] -= r1; }
+              }
+            }
+            if (warp == kSpWarps - 1) {
+              double acc = 0.0;
+              if (lane < 30) {
+                const int r1 = __ldg(sc.rowl_ptr + j + 1);
+                for (int e = __ldg(sc.rowl_ext_end + j) + ps; e < r1; e += 5) {
+                  const double* L = P + (size_t)(__ldg(sc.rowl_blk + e) - blk0) * 36 + 6 * ri;
+                  const double* yk = ty + (__ldg(sc.rowl_col + e) - j0) * 6;
+                  acc += (L[0] * yk[0] + L[1] * yk[1] + L[2] * yk[2]) + (L[3] * yk[3] + L[4] * yk[4] + L[5] * yk[5]);
+                }
+              }
+              double tot = acc;
+#pragma unroll
+              for (int qq = 1; qq < 5; ++qq) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * qq) & 31);
+              if (lane < 6) ty[q * 6 + lane] -= tot;
+            }
+            __syncthreads();
+          }
+          if (warp == 0) {
+            double a[6], x[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll
+            for (int c = 0; c < 6; ++c) a[c] = P[cb0 * 36 + 6 * (lane < 6 ? lane : 0) + c];
+            if (!warp_chol6_inverse(a, x, lane) && lane == 0) d.w_fail[d.fcam_win[__ldg(sc.perm + j)]] = 1;   // benign race: every writer stores 1
+            if (lane < 6) {
+#pragma unroll
+              for (int i = 0; i < 6; ++i) { li_s[6 * i + lane] = x[i]; __stcg(sc.Li + (size_t)j * 36 + 6 * i + lane, x[i]); }
+            }
+          }
+          __syncthreads();
+          for (int idx = tid; idx < (nb - 1) * 6; idx += kSpThreads) {      // panel: a thread per block row, in place
+            double* row = P + (size_t)(cb0 + 1 + idx / 6) * 36 + 6 * (idx % 6);
+            double av[6], o[6];
+#pragma unroll
+            for (int t = 0; t < 6; ++t) av[t] = row[t];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+              double acc = 0.0;
+#pragma unroll
+              for (int t = 0; t < 6; ++t) if (t <= c) acc += av[t] * li_s[6 * c + t];
+              o[c] = acc;
+            }
+#pragma unroll
+            for (int t = 0; t < 6; ++t) row[t] = o[t];
+          }
+          if (warp == kSpWarps - 1) {
+            const int c = lane - 26;                         // lanes 26..31: y_j = Linv t_j, in place behind a warp barrier
+            double yk = 0.0;
+            if (c >= 0) {
+#pragma unroll
+              for (int t = 0; t < 6; ++t) if (t <= c) yk += li_s[6 * c + t] * ty[q * 6 + t];
+            }
+            __syncwarp();
+            if (c >= 0) ty[q * 6 + c] = yk;
+          }
+          __syncthreads();
+        }
+        // S3: the finished panel and y go to L2
+        for (int i = tid; i < nblk * 36; i += kSpThreads) __stcg(sc.Lv + (size_t)blk0 * 36 + i, P[i]);
+        for (int i = tid; i < len * 6; i += kSpThreads) __stcg(sc.y + (size_t)j0 * 6 + i, ty[i]);
+        __syncthreads();
+        continue;
+      }
+      // ======== long chains (dense patterns): column by column through L2
       for (int j = j0; j < jn; ++j) {
         const int b0 = __ldg(sc.col_ptr + j), nb = __ldg(sc.col_ptr + j + 1) - b0;
         const bool staged = nb <= kSpStage;
-        // (a) gather: block = A_ij - sum_k L_ik L_jk^T.  Long columns: a warp per block.  Short ones (the separators
-        //     at the top of the tree: few blocks, long lists): every block's list is cut into S contiguous slices,
-        //     a warp per slice, slices summed in order afterwards.
+        // (a) gather: block = A_ij - sum_k L_ik L_jk^T.  Long columns: a warp per block.  Short ones: every block's
+        //     list is cut into S contiguous slices, a warp per slice, slices summed in order afterwards.
         const int S = nb >= kSpWarps ? 1 : kSpWarps / nb;
         if (S == 1) {
           for (int bi = warp; bi < nb; bi += kSpWarps) {
@@ -126,9 +272,9 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
         } else {
           const int bi = warp / S, sl = warp - bi * S;
           if (bi < nb) {
-            const int64_t u0 = sc.upd_ptr[b0 + bi], len = sc.upd_ptr[b0 + bi + 1] - u0;
+            const int64_t u0 = sc.upd_ptr[b0 + bi], ulen = sc.upd_ptr[b0 + bi + 1] - u0;
             double r0, r1;
-            sp_gather(sc, u0 + len * sl / S, u0 + len * (sl + 1) / S, lane, r0, r1);
+            sp_gather(sc, u0 + ulen * sl / S, u0 + ulen * (sl + 1) / S, lane, r0, r1);
             if (fout) { part[warp * 36 + 6 * g + 2 * t4] = r0; part[warp * 36 + 6 * g + 2 * t4 + 1] = r1; }
           }
         }
@@ -151,7 +297,6 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
         }
         __syncthreads();
         if (S > 1) {
-          // slices of every block summed in slice order (nb < kSpWarps <= kSpStage: the column is staged)
           for (int idx = tid; idx < nb * 36; idx += kSpThreads) {
             const int bi = idx / 36, e = idx - 36 * bi;
             double sum = 0.0;
@@ -183,7 +328,6 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
             __stcg(sc.Lv + (size_t)(b0 + bi) * 36 + e, acc);
           }
         } else {
-          // long columns (dense patterns) stay in L2: a thread per block row, in place (it reads its row before it writes it)
           for (int idx = tid; idx < (nb - 1) * 6; idx += kSpThreads) {
             double* row = sc.Lv + (size_t)(b0 + 1 + idx / 6) * 36 + 6 * (idx % 6);
             double a[6], o[6];
@@ -215,28 +359,58 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
   // ---- 2: back substitution, levels downwards; a chain's columns in sequence (last first) by its CTA:
   //         x_j = Linv_jj^T (y_j - sum_i L_ij^T x_i), a thread per (block, column), partials summed in block order
   double* xp = col_st;                            // [kSpThreads] partials
+  constexpr int G = kSpThreads / 6;               // block groups: thread (gq, c) takes blocks gq, gq + G, ...
+  const int gq = tid / 6, cc = tid - 6 * gq;
   for (int lvl = sc.nlev - 1; lvl >= 0; --lvl) {
     const int c_begin = __ldg(sc.lvl_ptr + lvl), c_end = __ldg(sc.lvl_ptr + lvl + 1);
     for (int ci = c_begin + blockIdx.x; ci < c_end; ci += gridDim.x) {
-      const int j0 = __ldg(sc.lvl_cols + ci), jn = j0 + __ldg(sc.lvl_len + ci);
+      const int j0 = __ldg(sc.lvl_cols + ci), len = __ldg(sc.lvl_len + ci), jn = j0 + len;
+      const int blk0 = __ldg(sc.col_ptr + j0), nblk = __ldg(sc.col_ptr + jn) - blk0;
+      const bool panel = nblk <= cap && len <= kSpChainMax;
+      if (panel) {
+        // the whole chain comes in by one round of independent loads: panel, block rows, x of the rows outside it,
+        // y and the inverse factors of its columns
+        for (int i = tid; i < nblk * 36; i += kSpThreads) P[i] = __ldcg(sc.Lv + (size_t)blk0 * 36 + i);
+        for (int i = tid; i < nblk * 6; i += kSpThreads) {
+          const int b = i / 6, row = __ldg(sc.row_idx + blk0 + b);
+          if (i == 6 * b) rowi[b] = row;
+          xe[i] = (row >= jn) ? __ldcg(sc.y + (size_t)row * 6 + (i - 6 * b)) : 0.0;
+        }
+        for (int i = tid; i < len * 6; i += kSpThreads) ty[i] = __ldcg(sc.y + (size_t)j0 * 6 + i);
+        for (int i = tid; i < len * 36; i += kSpThreads) LIc[i] = __ldcg(sc.Li + (size_t)j0 * 36 + i);
+        __syncthreads();
+      }
       for (int j = jn - 1; j >= j0; --j) {
         const int b0 = __ldg(sc.col_ptr + j), nbl = __ldg(sc.col_ptr + j + 1) - b0 - 1;
-        constexpr int G = kSpThreads / 6;         // block groups: thread (gq, c) takes blocks gq, gq + G, ...
-        const int gq = tid / 6, c = tid - 6 * gq;
         double acc = 0.0;
-        if (gq < G)
-          for (int bb = gq; bb < nbl; bb += G) {
-            const double* L = sc.Lv + (size_t)(b0 + 1 + bb) * 36 + c;                 // column c of L_ij
-            const double* xi = sc.y + (size_t)__ldg(sc.row_idx + b0 + 1 + bb) * 6;
-            acc += (__ldcg(L) * __ldcg(xi) + __ldcg(L + 6) * __ldcg(xi + 1) + __ldcg(L + 12) * __ldcg(xi + 2)) +
-                   (__ldcg(L + 18) * __ldcg(xi + 3) + __ldcg(L + 24) * __ldcg(xi + 4) + __ldcg(L + 30) * __ldcg(xi + 5));
-          }
-        // the six threads that finish the column fetch what they need before the barrier
         double yv = 0.0, lic[6] = {0, 0, 0, 0, 0, 0};
-        if (tid < 6) {
-          yv = __ldcg(sc.y + (size_t)j * 6 + tid);
+        if (panel) {
+          if (gq < G)
+            for (int bb = gq; bb < nbl; bb += G) {
+              const int b = b0 + 1 + bb - blk0;
+              const double* L = P + (size_t)b * 36 + cc;
+              const int row = rowi[b];
+              const double* xi = (row < jn) ? ty + (row - j0) * 6 : xe + b * 6;
+              acc += (L[0] * xi[0] + L[6] * xi[1] + L[12] * xi[2]) + (L[18] * xi[3] + L[24] * xi[4] + L[30] * xi[5]);
+            }
+          if (tid < 6) {
+            yv = ty[(j - j0) * 6 + tid];
 #pragma unroll
-          for (int q = 0; q < 6; ++q) if (q >= tid) lic[q] = __ldcg(sc.Li + (size_t)j * 36 + 6 * q + tid);     // Linv^T row
+            for (int q = 0; q < 6; ++q) if (q >= tid) lic[q] = LIc[(j - j0) * 36 + 6 * q + tid];
+          }
+        } else {
+          if (gq < G)
+            for (int bb = gq; bb < nbl; bb += G) {
+              const double* L = sc.Lv + (size_t)(b0 + 1 + bb) * 36 + cc;               // column cc of L_ij
+              const double* xi = sc.y + (size_t)__ldg(sc.row_idx + b0 + 1 + bb) * 6;
+              acc += (__ldcg(L) * __ldcg(xi) + __ldcg(L + 6) * __ldcg(xi + 1) + __ldcg(L + 12) * __ldcg(xi + 2)) +
+                     (__ldcg(L + 18) * __ldcg(xi + 3) + __ldcg(L + 24) * __ldcg(xi + 4) + __ldcg(L + 30) * __ldcg(xi + 5));
+            }
+          if (tid < 6) {
+            yv = __ldcg(sc.y + (size_t)j * 6 + tid);
+#pragma unroll
+            for (int q = 0; q < 6; ++q) if (q >= tid) lic[q] = __ldcg(sc.Li + (size_t)j * 36 + 6 * q + tid);     // Linv^T row
+          }
         }
         xp[tid] = acc;
         __syncthreads();
@@ -254,6 +428,7 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
             if (q >= lane) v += lic[q] * sq;
           }
           if (lane < 6) {
+            if (panel) ty[(j - j0) * 6 + lane] = v;
             __stcg(sc.y + (size_t)j * 6 + lane, v);
             const int f = __ldg(sc.perm + j);
             const int w = d.fcam_win[f];

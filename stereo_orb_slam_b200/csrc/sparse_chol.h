@@ -25,6 +25,8 @@ struct SparseCholSymbolic {
                                        //        INT32_MIN: fill-in (starts at zero)
   std::vector<int64_t> upd_ptr;        // [nnzL+1] products received by each block
   std::vector<int32_t> upd_a, upd_b;   // [nupd] block ids of L_ik and L_jk, k ascending
+  std::vector<int64_t> upd_ext_end;    // [nnzL] end of the products whose source column lies outside the block's chain (they come first)
+  std::vector<int32_t> rowl_ext_end;   // [n] idem for the row lists
   std::vector<int32_t> rowl_ptr;       // [n+1] row lists (forward substitution): blocks (j, k), k < j, k ascending
   std::vector<int32_t> rowl_blk, rowl_col;   // [nnzL - n]
   std::vector<int32_t> lvl_ptr;        // [nlev+1] level sets of the CHAINS of the elimination tree (leaves = level 0)

@@ -588,7 +588,8 @@ __host__ __device__ __forceinline__ size_t fused_smem_bytes(int n, int np, int n
   return ((size_t)n * (kCamStride + 9) + (size_t)ns * 21 + (size_t)np * 12) * 8 + (size_t)((n + 15) & ~15);
 }
 
-__global__ void __launch_bounds__(kFusedThreads, 2) k_fused_chunk(Dev d, DevParams P) {
+template <int OCC>
+__global__ void __launch_bounds__(kFusedThreads, OCC) k_fused_chunk(Dev d, DevParams P) {
   extern __shared__ __align__(16) double smem[];
   __shared__ double sm1[kFusedThreads / 32];
   __shared__ double smx[kFusedThreads / 32];
@@ -912,9 +913,13 @@ __global__ void __launch_bounds__(kAsmThreads) k_assemble_cams(Dev d) {
 //   camera CTA   rsum[f] = sum of the camera's W tp partials; with `prepare` (single GPU: no all-reduce in
 //                between) it also assembles its own diagonal block and does the work of k_cam_prepare:
 //                S_ff += U + D, Minv = S_ff^-1, rhs = rsum - gc
-__global__ void __launch_bounds__(kAsmThreads) k_assemble_schur(Dev d, int prepare) {
+// mode bits: 1 prepare · 2 the camera CTA also sums its own U / gc partials (the work of k_assemble_cams: after a fused
+// linearisation nothing else is between the chunk kernel and the solve) · 4 no block-Jacobi inverse (exact solvers)
+__global__ void __launch_bounds__(kAsmThreads) k_assemble_schur(Dev d, int mode) {
+  const int prepare = mode & 1;
   __shared__ double sm[kAsmWarps * 36];
   __shared__ double sM[36];
+  __shared__ double sU[28];
   if ((int)blockIdx.x < d.nbu) {
     const int b = blockIdx.x;
     if (prepare && d.blk_row[b] == d.blk_col[b]) return;     // diagonal blocks belong to the camera CTAs
@@ -932,8 +937,21 @@ __global__ void __launch_bounds__(kAsmThreads) k_assemble_schur(Dev d, int prepa
   int b0 = 0, b1 = 0;
   double u = 0.0, damp = 0.0, gcv = 0.0;
   const int ti = threadIdx.x / 6, tj = threadIdx.x - 6 * ti;
-  if (prepare) {
-    b0 = d.blk_part_off[db]; b1 = d.blk_part_off[db + 1];
+  if (prepare) { b0 = d.blk_part_off[db]; b1 = d.blk_part_off[db + 1]; }
+  if (mode & 2) {
+    double s2 = 1.0, rad = 1.0;
+    if (threadIdx.x < 6) { s2 = d.sc2c[(size_t)c * 6 + threadIdx.x]; rad = d.w_radius[w]; }
+    const double t27 = cta_gather<27, 7>(d.cspart, r0, r1, sm);
+    if (threadIdx.x < 21) d.U[(size_t)c * 21 + threadIdx.x] = t27;
+    else if (threadIdx.x < 27) d.gc[(size_t)c * 6 + (threadIdx.x - 21)] = t27;
+    if (threadIdx.x < 27) sU[threadIdx.x] = t27;
+    __syncthreads();                                         // sU complete; sm is reused by the next gather
+    if (threadIdx.x < 36) u = sU[(ti <= tj) ? up6(ti, tj) : up6(tj, ti)];
+    if (threadIdx.x < 6) { gcv = sU[21 + threadIdx.x]; sM[threadIdx.x] = lm_damp(s2, sU[up6(threadIdx.x, threadIdx.x)], rad); }
+    __syncthreads();
+    if (threadIdx.x < 36 && ti == tj) damp = sM[ti];
+    __syncthreads();                                         // sM is reused below
+  } else if (prepare) {
     if (threadIdx.x < 36) {
       u = d.U[(size_t)c * 21 + ((ti <= tj) ? up6(ti, tj) : up6(tj, ti))];
       if (ti == tj) damp = lm_damp(d.sc2c[(size_t)c * 6 + ti], u, d.w_radius[w]);
@@ -951,7 +969,7 @@ __global__ void __launch_bounds__(kAsmThreads) k_assemble_schur(Dev d, int prepa
     d.Su[(size_t)db * 36 + threadIdx.x] = v;
   }
   __syncthreads();
-  if (threadIdx.x != 0) return;
+  if (threadIdx.x != 0 || (mode & 4)) return;
   // one thread per camera factorises (all cameras in parallel, registers only)
   double M[36];
 #pragma unroll
@@ -1312,6 +1330,58 @@ __device__ __forceinline__ bool chol6_inverse_factor(const double* a, double* li
   return ok;
 }
 
+// 1 / sqrt(s) to double precision without the library routine's latency: single-precision MUFU seed (22 bits), two
+// Newton steps in fp64 (44, then 88 bits).  Arguments outside the float range take the library path.
+__device__ __forceinline__ double fast_rsqrt(double s) {
+  if (!(s > 1e-30 && s < 1e30)) return rsqrt(s);
+  double y = (double)rsqrtf((float)s);
+  const double h = 0.5 * s;
+  y = y * (1.5 - h * y * y);
+  y = y * (1.5 - h * y * y);
+  return y;
+}
+
+// chol6_inverse_factor with the short-latency reciprocal square root: ONE thread, everything in registers — the rows'
+// updates are independent, so the thread's own instruction-level parallelism covers what a warp-wide version pays
+// in shuffles (the banded and block-sparse factorisations call this once per block column, on their critical path).
+__device__ __forceinline__ bool chol6_inverse_factor_fast(const double* a, double* li) {
+  double L[6][6], inv[6];
+  bool ok = true;
+#pragma unroll
+  for (int i = 0; i < 6; ++i)
+#pragma unroll
+    for (int j = 0; j < 6; ++j) if (j <= i) L[i][j] = a[6 * i + j];
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    const double s = L[j][j];
+    ok = ok && (s > 0.0) && isfinite(s);
+    inv[j] = fast_rsqrt(ok ? s : 1.0);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) if (i > j) L[i][j] *= inv[j];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) if (i > j) {
+#pragma unroll
+      for (int c = 0; c < 6; ++c) if (c > j && c <= i) L[i][c] -= L[i][j] * L[c][j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      double v = 0.0;
+      if (i == j) v = inv[j];
+      else if (i > j) {
+        double acc = 0.0;
+#pragma unroll
+        for (int t = 0; t < 6; ++t) if (t >= j && t < i) acc += L[i][t] * li[6 * t + j];
+        v = -acc * inv[i];
+      }
+      li[6 * i + j] = v;
+    }
+  }
+  return ok;
+}
+
 // WS_SMEM: the lower block-triangle itself sits in shared memory (windows of <= kCholSmemCams free cameras: no L2
 // round trip anywhere in the factorisation); otherwise in the L2-resident workspace.
 template <bool WS_SMEM>
@@ -1560,15 +1630,12 @@ __global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t
   }
   __syncthreads();
   // 6x6 Cholesky + inverse of the diagonal block of column k (warp 0)
-  auto factor_column = [&](int k) {
-    const double* dk = A + (size_t)coff[k] * 36;
-    double a[6], x[6] = {0, 0, 0, 0, 0, 0};
+  auto factor_column = [&](int k) {       // lane 0 of warp 0
+    if (lane == 0) {
+      double li[36];
+      if (!chol6_inverse_factor_fast(A + (size_t)coff[k] * 36, li)) bad = 1;
 #pragma unroll
-    for (int c = 0; c < 6; ++c) a[c] = dk[6 * (lane < 6 ? lane : 0) + c];
-    if (!warp_chol6_inverse(a, x, lane) && lane == 0) bad = 1;
-    if (lane < 6) {
-#pragma unroll
-      for (int i = 0; i < 6; ++i) LI[(size_t)k * 36 + 6 * i + lane] = x[i];
+      for (int i = 0; i < 36; ++i) LI[(size_t)k * 36 + i] = li[i];
     }
   };
   lap(0);

@@ -79,8 +79,11 @@ struct sba_handle_s {
   bool chol_cluster_ok = false; size_t chol_cluster_smem = 0;   // mid-size windows: one 8-CTA cluster per window (k_chol_cluster)
   bool chol_band_ok = false; size_t chol_band_smem = 0; const int32_t* band_last = nullptr;   // banded windows: envelope in one CTA's shared memory (k_chol_band)
   size_t lin_smem = 0, schur_smem = 0;   // dynamic shared memory of the per-chunk kernels (largest chunk)
-  size_t fused_smem = 0; bool fused_ok = false;   // k_fused_chunk (K1-K3 of a chunk in one CTA)
+  size_t fused_smem = 0; bool fused_ok = false; int fused_occ = 2;   // k_fused_chunk (K1-K3 of a chunk in one CTA)
   bool schur_fresh = false;              // the last linearisation was fused: spart / rpart already hold this radius' Schur partials
+  // ... and on a single GPU its camera-side assembly and finish are left to the next do_schur (one assemble kernel for
+  // U / gc / S / rhs; cost + gradient test on the side stream while the solve runs)
+  bool cams_pending = false; bool pend_keep_cost = false; int pend_lm_begin = -1; double pend_radius = 0.0;
   // exact block-sparse Cholesky of the reduced system for windows of more than kCholMaxCams free cameras (k_spchol)
   SparseCholSymbolic sym; bool sym_ok = false; SpCholDev sp{}; bool spchol_ok = false; int spchol_blocks = 0; size_t spchol_smem = 0; double time_symbolic_s = 0.0;
 
@@ -324,7 +327,11 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
     h->fused_ok = h->fused_smem <= (size_t)220 * 1024 && !std::getenv("SBA_NO_FUSED");
     h->schur_fresh = false;
     if (h->fused_ok)
-      CUDA_TRY(cudaFuncSetAttribute(k_fused_chunk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fused_smem, 1024)));
+    {
+      h->fused_occ = (std::getenv("SBA_FUSED_OCC") && std::atoi(std::getenv("SBA_FUSED_OCC")) == 3) ? 3 : 2;   // tuning aid: 3 CTAs / SM (85 registers, spills)
+      CUDA_TRY(cudaFuncSetAttribute(k_fused_chunk<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fused_smem, 1024)));
+      CUDA_TRY(cudaFuncSetAttribute(k_fused_chunk<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fused_smem, 1024)));
+    }
   }
   {
     // per-window size of the reduced system -> can one CTA hold it?
@@ -571,9 +578,17 @@ static int do_linearize(sba_handle h, bool keep_cost = false, bool fork_tail = f
   LAUNCH(h, k_campre, cdiv(d.Nc, 128), 128, d);      // K0: camera table of this linearisation
   if (fused) {
     CUDA_TRY(cudaMemsetAsync(d.w_fail, 0, (size_t)d.nwin * 4, h->stream));      // the chunk kernel reports singular point blocks
-    k_fused_chunk<<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P); h->launches++;
+    if (h->fused_occ == 3) k_fused_chunk<3><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
+    else k_fused_chunk<2><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
+    h->launches++;
     h->schur_fresh = true;
   } else if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; }
+  h->cams_pending = false;
+  if (fused && fork_tail && !h->comm.active() && !std::getenv("SBA_NO_FORK")) {
+    h->cams_pending = true; h->pend_keep_cost = keep_cost; h->pend_lm_begin = lm_begin; h->pend_radius = initial_radius;
+    CUDA_TRY(cudaGetLastError());
+    return SBA_OK;
+  }
   if (fork_tail && !h->comm.active() && h->jacobi_done && !std::getenv("SBA_NO_FORK")) {
     CUDA_TRY(cudaEventRecord(h->ev_fork, h->stream));
     CUDA_TRY(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
@@ -609,11 +624,24 @@ static int do_linearize(sba_handle h, bool keep_cost = false, bool fork_tail = f
 }
 
 // K3: damped Schur complement at the per-window radii in d.w_radius.
-static int do_schur(sba_handle h) {
+static int do_schur(sba_handle h, bool exact_solver = false) {
   Dev& d = h->d;
   if (h->schur_fresh) h->schur_fresh = false;      // the fused linearisation already left this radius' partials
   else if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++; }
   { const int jrc = join_tail(h); if (jrc) return jrc; }
+  if (h->cams_pending) {
+    // after a fused linearisation (single GPU): ONE assemble kernel for U / gc / S / rhs, then the window cost and the
+    // gradient test on the side stream while the linear solve runs (do_step joins)
+    h->cams_pending = false;
+    LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 3 | (exact_solver ? 4 : 0));
+    CUDA_TRY(cudaEventRecord(h->ev_fork, h->stream));
+    CUDA_TRY(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+    if (d.nwin > 0) { k_lin_finish<<<d.nwin, kThreads, 0, h->side>>>(d, h->P, h->pend_keep_cost ? 1 : 0); h->launches++; }
+    if (h->pend_lm_begin >= 0) { k_lm_begin<<<cdiv(d.nwin, 128), 128, 0, h->side>>>(d, h->P, h->pend_radius, h->pend_lm_begin, 0); h->launches++; }
+    h->tail_pending = true;
+    CUDA_TRY(cudaGetLastError());
+    return SBA_OK;
+  }
   const int fused = h->comm.active() ? 0 : 1;     // multi-GPU: the partial sums are all-reduced before the cameras are prepared
   LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, fused);
   if (fused) { CUDA_TRY(cudaGetLastError()); return SBA_OK; }
@@ -743,6 +771,7 @@ static int do_ls_round(sba_handle h) {
 static int do_step(sba_handle h, int* ls_rounds) {
   Dev& d = h->d;
   const DevParams& P = h->P;
+  { const int jrc = join_tail(h); if (jrc) return jrc; }
   const int rank = (int)(h->comm.active() ? h->comm.rank : 0);
   if (!h->comm.active() && h->coop_blocks > 0) {
     // single GPU: the whole step in one cooperative launch (k_step_loop), one host read at the end
@@ -818,6 +847,7 @@ int sba_schur(sba_handle h, const sba_options* opt, double radius) {
   fill_params(h, &o);
   if ((rc = set_radius(h, radius))) return rc;
   if ((rc = do_schur(h))) return rc;
+  if ((rc = join_tail(h))) return rc;
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   return SBA_OK;
 }
@@ -901,6 +931,7 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
             const int64_t l0 = h->launches;
             int r1 = do_linearize(h, false, true, -1, 0.0, true);
             if (!r1) r1 = do_schur(h);
+            if (!r1) r1 = join_tail(h);
             const cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
             h->step_launches = (int)(h->launches - l0); h->launches = l0;
             if (r1) return r1;
@@ -914,12 +945,17 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
         } else {
           if ((rc = do_linearize(h, false, true, -1, 0.0, true))) return rc;
           if ((rc = do_schur(h))) return rc;
+          if ((rc = join_tail(h))) return rc;
         }
         break;
       case 11:     // the fused K1-K3 chunk kernel alone (camera table from the last k_campre)
         if (!h->fused_ok) { set_error("fused chunk kernel unavailable for this structure"); return SBA_INVALID_ARGUMENT; }
         if (i == 0) { LAUNCH(h, k_campre, cdiv(d.Nc, 128), 128, d); CUDA_TRY(cudaEventRecord(h->ev[6], h->stream)); }
-        if (d.npchunk > 0) { k_fused_chunk<<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P); h->launches++; }
+        if (d.npchunk > 0) {
+          if (h->fused_occ == 3) k_fused_chunk<3><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
+          else k_fused_chunk<2><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
+          h->launches++;
+        }
         break;
       case 5: LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P); break;
       case 9: LAUNCH(h, k_assemble_cams, d.Nf, kAsmThreads, d); break;
@@ -1008,7 +1044,7 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
       break;
     }
     CUDA_TRY(cudaEventRecord(h->ev[0], h->stream));
-    if ((rc = do_schur(h))) return rc;
+    if ((rc = do_schur(h, o.linear_solver != 1 && (h->chol_ok || h->spchol_ok)))) return rc;
     CUDA_TRY(cudaEventRecord(h->ev[1], h->stream));
     int32_t pit = 0;
     if ((rc = do_pcg(h, &o, &pit))) return rc;
@@ -1048,6 +1084,12 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
   }
   // windows still running here hit the iteration limit
   if ((rc = join_tail(h))) return rc;
+  if (h->cams_pending) {      // the last linearisation's camera-side assembly was left to a Schur step that never came
+    h->cams_pending = false;
+    LAUNCH(h, k_assemble_cams, d.Nf, kAsmThreads, d);
+    LAUNCH(h, k_lin_finish, d.nwin, kThreads, d, P, h->pend_keep_cost ? 1 : 0);
+    if (h->pend_lm_begin >= 0) LAUNCH(h, k_lm_begin, cdiv(d.nwin, 128), 128, d, P, h->pend_radius, h->pend_lm_begin, 0);
+  }
   std::vector<int32_t> st((size_t)d.nwin), its((size_t)d.nwin), succ((size_t)d.nwin);
   CUDA_TRY(cudaMemcpyAsync(st.data(), d.w_status, st.size() * 4, cudaMemcpyDeviceToHost, h->stream));
   CUDA_TRY(cudaMemcpyAsync(its.data(), d.w_iter, its.size() * 4, cudaMemcpyDeviceToHost, h->stream));

@@ -204,15 +204,11 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
             }
             __syncthreads();
           }
-          if (warp == 0) {
-            double a[6], x[6] = {0, 0, 0, 0, 0, 0};
+          if (tid == 0) {
+            double li[36];
+            if (!chol6_inverse_factor_fast(P + cb0 * 36, li)) d.w_fail[d.fcam_win[__ldg(sc.perm + j)]] = 1;   // benign race: every writer stores 1
 #pragma unroll
-            for (int c = 0; c < 6; ++c) a[c] = P[cb0 * 36 + 6 * (lane < 6 ? lane : 0) + c];
-            if (!warp_chol6_inverse(a, x, lane) && lane == 0) d.w_fail[d.fcam_win[__ldg(sc.perm + j)]] = 1;   // benign race: every writer stores 1
-            if (lane < 6) {
-#pragma unroll
-              for (int i = 0; i < 6; ++i) { li_s[6 * i + lane] = x[i]; __stcg(sc.Li + (size_t)j * 36 + 6 * i + lane, x[i]); }
-            }
+            for (int i = 0; i < 36; ++i) { li_s[i] = li[i]; __stcg(sc.Li + (size_t)j * 36 + i, li[i]); }
           }
           __syncthreads();
           for (int idx = tid; idx < (nb - 1) * 6; idx += kSpThreads) {      // panel: a thread per block row, in place
@@ -307,15 +303,11 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
           __syncthreads();
         }
         // (c) diagonal block: 6x6 Cholesky across six lanes of warp 0 + the inverse of the factor
-        if (warp == 0) {
-          double a[6], x[6] = {0, 0, 0, 0, 0, 0};
+        if (tid == 0) {
+          double li[36];
+          if (!chol6_inverse_factor_fast(akk, li)) d.w_fail[d.fcam_win[__ldg(sc.perm + j)]] = 1;   // benign race: every writer stores 1
 #pragma unroll
-          for (int c = 0; c < 6; ++c) a[c] = akk[6 * (lane < 6 ? lane : 0) + c];
-          if (!warp_chol6_inverse(a, x, lane) && lane == 0) d.w_fail[d.fcam_win[__ldg(sc.perm + j)]] = 1;   // benign race: every writer stores 1
-          if (lane < 6) {
-#pragma unroll
-            for (int i = 0; i < 6; ++i) { li_s[6 * i + lane] = x[i]; __stcg(sc.Li + (size_t)j * 36 + 6 * i + lane, x[i]); }
-          }
+          for (int i = 0; i < 36; ++i) { li_s[i] = li[i]; __stcg(sc.Li + (size_t)j * 36 + i, li[i]); }
         }
         __syncthreads();
         // (d) panel L_ij = A_ij Linv^T (i > j) and y_j = Linv t_j

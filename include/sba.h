@@ -188,6 +188,34 @@ int64_t sba_launch_count(sba_handle h);
 int sba_comm_unique_id(uint8_t id[128]);
 int sba_comm_init(sba_handle h, int32_t rank, int32_t world_size, const uint8_t id[128]);
 
+/* ---- device-resident map ------------------------------------------------------- */
+/* The reference's BundleAdjuster holds references to the SLAM map (m_cam_frames / m_ldm_points,
+ * src/bundle_adjuster.h:21-22) and is called once per frame on (n-1, n) and every refine_interval frames on a sliding
+ * window (src/slam.cpp:122-129).  With these entry points the map lives inside the handle between calls: map points and
+ * stereo pixels stay in HBM (only a new frame's observations and points are uploaded, once), the integer side (which
+ * point an observation sees) and the poses are mirrored on the host, where the reference's index build (:57-102) and
+ * its f32 pose (de)parameterisation (src/math_utils.h:12-41) run.  Results of sba_map_optimize are bit-identical to
+ * sba_pack_window + sba_solve + sba_unpack_window on the same map.  Single GPU. */
+int sba_map_reset(sba_handle h);
+/* VisualOdometer::Update (src/visual_odometer.cpp:335-444): a new frame with its pose T_wc (f32 4x4 row-major), its
+ * observations (global point id + u_l v_l u_r v_r) and the points it creates (ids continue the map's numbering). */
+int sba_map_append_frame(sba_handle h, const float* T_wc16, int64_t nobs, const uint32_t* obs_point_id, const float* obs_uv,
+                         int32_t num_new_points, const float* new_points_xyz);
+int64_t sba_map_num_frames(sba_handle h);
+int64_t sba_map_num_points(sba_handle h);
+/* BundleAdjuster::Optimize(start, end) on the resident map (src/bundle_adjuster.cpp:39-133): half-open window, first
+ * camera fixed, every window camera and point written back (poses through PoseToMatrix / inverse / Normalize as the
+ * Frame::GlobalPose setter does, src/camera_frame.h:32-49; points narrowed to f32, src/map_point.h:30-35). */
+int sba_map_optimize(sba_handle h, int32_t start, int32_t end, const double* p_l, const double* p_r, const sba_options* opt,
+                     sba_summary* summary);
+int sba_map_get_poses(sba_handle h, int32_t first, int32_t count, float* T_wc16);
+int sba_map_set_pose(sba_handle h, int32_t frame, const float* T_wc16);          /* Frame::GlobalPose(pose) by other callers */
+int sba_map_get_points(sba_handle h, int64_t first, int64_t count, float* xyz);
+int sba_map_set_points(sba_handle h, int64_t first, int64_t count, const float* xyz);
+/* ids of the points the last sba_map_optimize wrote back (returns their number) and its phase times in ms:
+ * {index build + poses, structure, state on device, solve, unpack}. */
+int64_t sba_map_last_window(sba_handle h, uint32_t* point_ids, int64_t capacity, double* ms5);
+
 /* ---- host side of BundleAdjuster::Optimize ------------------------------------------------------ */
 /* Pack window [start,end) of a map (reference: src/bundle_adjuster.cpp:41-110).
  *   T_wc [N*16] f32 row-major world-from-camera (Frame::GlobalPose), map_points [M*3] f32,

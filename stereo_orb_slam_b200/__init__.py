@@ -7,5 +7,6 @@ raises if the library has not been built (no CPU fallback).
 from ._capi import Options, Summary, SbaError, default_options, LIB_PATH  # noqa: F401
 from .solver import Solver  # noqa: F401
 from .bundle_adjuster import BundleAdjuster, pack_window, unpack_window, matrix_to_pose, pose_to_matrix  # noqa: F401
+from .device_map import ResidentBundleAdjuster, replay  # noqa: F401
 from . import synthetic  # noqa: F401
 from . import dump_io  # noqa: F401

@@ -20,6 +20,8 @@ SYMBOLS = [
     "sba_num_free_cameras", "sba_launch_count", "sba_comm_unique_id", "sba_comm_init",
     "sba_pack_window", "sba_unpack_window", "sba_matrix_to_pose", "sba_pose_to_matrix",
     "sba_time_stage", "sba_invert_pose", "sba_normalize_pose", "sba_compose_pose", "sba_get_factor_symbolic", "sba_measure_fp64_peak",
+    "sba_map_reset", "sba_map_append_frame", "sba_map_num_frames", "sba_map_num_points", "sba_map_optimize", "sba_map_get_poses",
+    "sba_map_set_pose", "sba_map_get_points", "sba_map_set_points", "sba_map_last_window",
 ]
 
 SBA_OK, SBA_NO_CONVERGENCE, SBA_NUMERICAL_FAILURE, SBA_INVALID_ARGUMENT, SBA_CUDA_ERROR, SBA_NCCL_ERROR = range(6)
@@ -73,6 +75,8 @@ def lib():
         L.sba_last_error.restype = C.c_char_p
         L.sba_get_schur_pattern.restype = C.c_int64
         L.sba_launch_count.restype = C.c_int64
+        for f in ("sba_map_num_frames", "sba_map_num_points", "sba_map_last_window"):
+            getattr(L, f).restype = C.c_int64
         L.sba_destroy.restype = None
         L.sba_default_options.restype = None
         L.sba_matrix_to_pose.restype = None

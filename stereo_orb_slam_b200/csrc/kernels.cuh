@@ -2762,6 +2762,21 @@ __global__ void __launch_bounds__(256) k_fp64_peak(double* out, int iters, doubl
   if (s == 12345.678) out[blockIdx.x * blockDim.x + threadIdx.x] = s;     // never true: keeps the chains alive
 }
 
+// ---- device-resident map (sba_map_*): the window's points are gathered from / scattered to the map's f32 storage by
+// their global ids, exactly as the pack / unpack loops do on the host (reference: src/bundle_adjuster.cpp:83-87, :128-132)
+__global__ void k_map_gather_points(int np, const uint32_t* __restrict__ ids, const float* __restrict__ map_points, double* __restrict__ pts) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= np * 3) return;
+  const int i = t / 3, c = t - 3 * i;
+  pts[t] = (double)map_points[(size_t)ids[i] * 3 + c];
+}
+__global__ void k_map_scatter_points(int np, const uint32_t* __restrict__ ids, const double* __restrict__ pts, float* __restrict__ map_points) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= np * 3) return;
+  const int i = t / 3, c = t - 3 * i;
+  map_points[(size_t)ids[i] * 3 + c] = (float)pts[t];
+}
+
 // permute the caller's observations into the point-sorted view
 __global__ void k_permute_uv(Dev d, const float4* __restrict__ uv_in, float4* __restrict__ uv_p) {
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -12,6 +12,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/sba.h"
@@ -41,7 +42,25 @@ inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 inline int dbg_mask() { const char* e = std::getenv("SBA_DEBUG_MASK"); return e ? std::atoi(e) : 0; }
 }  // namespace
 
+// Device-resident map (sba_map_*): what the reference keeps in m_cam_frames / m_ldm_points
+// (src/bundle_adjuster.h:21-22).  Floats that only the solver reads live on the GPU (map points, stereo pixels); the
+// integer side (which point every observation sees) and the poses stay mirrored on the host, where the index build
+// and the f32 pose (de)parameterisation of the reference run.
+struct DeviceMap {
+  std::vector<float> T_wc;              // [N*16] world-from-camera, host mirror (Frame::GlobalPose)
+  std::vector<int64_t> frame_off{0};    // [N+1]
+  std::vector<uint32_t> obs_point_id;   // [K]
+  float* d_points = nullptr; size_t n_points = 0, cap_points = 0;   // [M*3] f32 (MapPoint::Position)
+  float4* d_uv = nullptr; size_t n_obs = 0, cap_obs = 0;            // [K] (u_l, v_l, u_r, v_r)
+  uint32_t* d_ids = nullptr; size_t cap_ids = 0;                    // global ids of the last window's points
+  // scratch of the last window (host)
+  std::vector<uint32_t> ids; std::vector<int32_t> cam, pt; std::vector<double> poses;
+  int32_t last_start = 0, last_end = 0;
+  double ms_pack = 0.0, ms_structure = 0.0, ms_upload = 0.0, ms_solve = 0.0, ms_unpack = 0.0;
+};
+
 struct sba_handle_s {
+  DeviceMap map;
   int device = -1;            // -1: host-only handle (structure build / introspection only)
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[8] = {};
@@ -209,6 +228,9 @@ void sba_destroy(sba_handle h) {
     if (h->side) cudaStreamSynchronize(h->side);
     h->comm.destroy();
     h->free_all();
+    if (h->map.d_points) cudaFree(h->map.d_points);
+    if (h->map.d_uv) cudaFree(h->map.d_uv);
+    if (h->map.d_ids) cudaFree(h->map.d_ids);
     if (h->stream) cudaStreamSynchronize(h->stream);     // the frees above are stream-ordered
     if (h->pool) cudaMemPoolDestroy(h->pool);
     for (int i = 0; i < 8; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -1290,6 +1312,167 @@ int sba_measure_fp64_peak(sba_handle h, double* tflops) {
 
 int32_t sba_num_free_cameras(sba_handle h) { return (h && h->has_structure) ? h->H.Nf : -1; }
 int64_t sba_launch_count(sba_handle h) { return h ? h->launches : -1; }
+
+// ---- device-resident map -------------------------------------------------------------
+extern "C++" {
+template <typename T>
+static int grow_device(T** p, size_t* cap, size_t used, size_t need, cudaStream_t stream) {
+  if (need <= *cap) return SBA_OK;
+  size_t ncap = std::max<size_t>(need, std::max<size_t>(*cap * 2, 1024));
+  T* q = nullptr;
+  CUDA_TRY(cudaMalloc((void**)&q, ncap * sizeof(T)));
+  if (*p && used) CUDA_TRY(cudaMemcpyAsync(q, *p, used * sizeof(T), cudaMemcpyDeviceToDevice, stream));
+  if (*p) { CUDA_TRY(cudaStreamSynchronize(stream)); CUDA_TRY(cudaFree(*p)); }
+  *p = q; *cap = ncap;
+  return SBA_OK;
+}
+}
+
+int sba_map_reset(sba_handle h) {
+  if (!h) { set_error("null handle"); return SBA_INVALID_ARGUMENT; }
+  DeviceMap& M = h->map;
+  M.T_wc.clear(); M.frame_off.assign(1, 0); M.obs_point_id.clear(); M.n_points = 0; M.n_obs = 0;
+  return SBA_OK;
+}
+
+int sba_map_append_frame(sba_handle h, const float* T_wc16, int64_t nobs, const uint32_t* obs_point_id, const float* obs_uv,
+                         int32_t num_new_points, const float* new_points) {
+  if (!h || !T_wc16 || nobs < 0 || num_new_points < 0 || (nobs > 0 && (!obs_point_id || !obs_uv)) || (num_new_points > 0 && !new_points)) {
+    set_error("sba_map_append_frame: bad arguments"); return SBA_INVALID_ARGUMENT;
+  }
+  if (h->device < 0) { set_error("host-only handle: no CUDA device bound (there is no CPU fallback)"); return SBA_CUDA_ERROR; }
+  DeviceMap& M = h->map;
+  const size_t np_after = M.n_points + (size_t)num_new_points;
+  for (int64_t k = 0; k < nobs; ++k)
+    if (obs_point_id[k] >= np_after) { set_error("sba_map_append_frame: observation of an unknown map point"); return SBA_INVALID_ARGUMENT; }
+  CUDA_TRY(cudaSetDevice(h->device));
+  int rc;
+  if ((rc = grow_device(&M.d_points, &M.cap_points, M.n_points * 3, np_after * 3, h->stream))) return rc;
+  if ((rc = grow_device(&M.d_uv, &M.cap_obs, M.n_obs, M.n_obs + (size_t)nobs, h->stream))) return rc;
+  if (num_new_points > 0)
+    CUDA_TRY(cudaMemcpyAsync(M.d_points + M.n_points * 3, new_points, (size_t)num_new_points * 12, cudaMemcpyHostToDevice, h->stream));
+  if (nobs > 0) CUDA_TRY(cudaMemcpyAsync(M.d_uv + M.n_obs, obs_uv, (size_t)nobs * 16, cudaMemcpyHostToDevice, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));        // the caller's buffers may be pageable and short-lived
+  M.T_wc.insert(M.T_wc.end(), T_wc16, T_wc16 + 16);
+  M.obs_point_id.insert(M.obs_point_id.end(), obs_point_id, obs_point_id + nobs);
+  M.frame_off.push_back(M.frame_off.back() + nobs);
+  M.n_points = np_after; M.n_obs += (size_t)nobs;
+  return SBA_OK;
+}
+
+int64_t sba_map_num_frames(sba_handle h) { return h ? (int64_t)h->map.frame_off.size() - 1 : -1; }
+int64_t sba_map_num_points(sba_handle h) { return h ? (int64_t)h->map.n_points : -1; }
+
+int sba_map_optimize(sba_handle h, int32_t start, int32_t end, const double* p_l, const double* p_r, const sba_options* opt,
+                     sba_summary* sum) {
+  if (!h || !p_l || !p_r) { set_error("null argument"); return SBA_INVALID_ARGUMENT; }
+  if (h->device < 0) { set_error("host-only handle: no CUDA device bound (there is no CPU fallback)"); return SBA_CUDA_ERROR; }
+  if (h->comm.active()) { set_error("sba_map_optimize is a single-GPU path"); return SBA_INVALID_ARGUMENT; }
+  DeviceMap& M = h->map;
+  const int32_t N = (int32_t)M.frame_off.size() - 1;
+  if (start < 0 || end < start || end > N) { set_error("sba_map_optimize: bad window"); return SBA_INVALID_ARGUMENT; }
+  if (sum) std::memset(sum, 0, sizeof(*sum));
+  if (end == start) return SBA_OK;
+  using clk = std::chrono::steady_clock;
+  auto ms_since = [](clk::time_point a) { return 1e3 * std::chrono::duration<double>(clk::now() - a).count(); };
+  const auto t0 = clk::now();
+  // ---- pack, integer side + poses (reference: src/bundle_adjuster.cpp:57-102; same scan order, same numbering)
+  const int32_t nc = end - start;
+  const int64_t k0 = M.frame_off[start], nobs = M.frame_off[end] - k0;
+  M.poses.resize((size_t)nc * 6); M.cam.resize((size_t)nobs); M.pt.resize((size_t)nobs); M.ids.clear();
+  {
+    std::unordered_map<uint32_t, int32_t> idx;
+    idx.reserve((size_t)nobs);
+    int64_t ko = 0;
+    for (int32_t f = start; f < end; ++f) {
+      float T_cw[16];
+      if (sba_invert_pose(M.T_wc.data() + (size_t)f * 16, T_cw) != SBA_OK) { set_error("singular frame pose"); return SBA_INVALID_ARGUMENT; }
+      sba_matrix_to_pose(T_cw, M.poses.data() + (size_t)(f - start) * 6);
+      for (int64_t k = M.frame_off[f]; k < M.frame_off[f + 1]; ++k, ++ko) {
+        const uint32_t gid = M.obs_point_id[k];
+        auto it = idx.find(gid);
+        int32_t pi;
+        if (it == idx.end()) { pi = (int32_t)M.ids.size(); M.ids.push_back(gid); idx.emplace(gid, pi); }
+        else pi = it->second;
+        M.cam[ko] = f - start; M.pt[ko] = pi;
+      }
+    }
+  }
+  const int32_t np = (int32_t)M.ids.size();
+  M.ms_pack = ms_since(t0);
+  const auto t1 = clk::now();
+  int rc = sba_set_structure(h, nc, np, nobs, M.cam.data(), M.pt.data(), nullptr, 1, nullptr, nullptr);
+  if (rc) return rc;
+  M.ms_structure = ms_since(t1);
+  const auto t2 = clk::now();
+  // ---- state and measurements never leave the device: points gathered by id, pixels are a slice of the map's array
+  Dev& d = h->d;
+  CUDA_TRY(cudaSetDevice(h->device));
+  if ((rc = grow_device(&M.d_ids, &M.cap_ids, 0, (size_t)np, h->stream))) return rc;
+  CUDA_TRY(cudaMemcpyAsync(d.poses, M.poses.data(), (size_t)nc * 48, cudaMemcpyHostToDevice, h->stream));
+  if (np > 0) {
+    CUDA_TRY(cudaMemcpyAsync(M.d_ids, M.ids.data(), (size_t)np * 4, cudaMemcpyHostToDevice, h->stream));
+    LAUNCH(h, k_map_gather_points, cdiv((int64_t)np * 3, 256), 256, np, M.d_ids, M.d_points, d.pts);
+  }
+  LAUNCH(h, k_permute_uv, cdiv(d.Nobs, 256), 256, d, M.d_uv + k0, const_cast<float4*>(d.uv_p));
+  CUDA_TRY(cudaGetLastError());
+  std::memcpy(h->P.pl, p_l, 96); std::memcpy(h->P.pr, p_r, 96);
+  h->has_state = h->has_meas = true; h->jacobi_done = false;
+  M.ms_upload = ms_since(t2);
+  const auto t3 = clk::now();
+  sba_summary S;
+  const int run_rc = sba_run(h, opt, &S);
+  if (run_rc != SBA_OK && run_rc != SBA_NO_CONVERGENCE && run_rc != SBA_NUMERICAL_FAILURE) return run_rc;
+  M.ms_solve = ms_since(t3);
+  const auto t4 = clk::now();
+  // ---- unpack (reference :121-132): points back into the map on the device, poses through the host's f32 path
+  if (np > 0) LAUNCH(h, k_map_scatter_points, cdiv((int64_t)np * 3, 256), 256, np, M.d_ids, d.pts, M.d_points);
+  CUDA_TRY(cudaMemcpyAsync(M.poses.data(), d.poses, (size_t)nc * 48, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  if ((rc = sba_unpack_window(M.T_wc.data(), nullptr, start, end, M.poses.data(), nullptr, nullptr, 0))) return rc;
+  M.ms_unpack = ms_since(t4);
+  M.last_start = start; M.last_end = end;
+  S.time_structure_s = 1e-3 * (M.ms_pack + M.ms_structure); S.time_h2d_s = 1e-3 * M.ms_upload; S.time_d2h_s = 1e-3 * M.ms_unpack;
+  S.time_total_s = 1e-3 * ms_since(t0);
+  if (sum) *sum = S;
+  return run_rc;
+}
+
+int sba_map_get_poses(sba_handle h, int32_t first, int32_t count, float* T_wc16) {
+  if (!h || !T_wc16 || first < 0 || count < 0 || (size_t)(first + count) * 16 > h->map.T_wc.size()) { set_error("bad range"); return SBA_INVALID_ARGUMENT; }
+  std::memcpy(T_wc16, h->map.T_wc.data() + (size_t)first * 16, (size_t)count * 64);
+  return SBA_OK;
+}
+int sba_map_set_pose(sba_handle h, int32_t frame, const float* T_wc16) {
+  if (!h || !T_wc16 || frame < 0 || (size_t)(frame + 1) * 16 > h->map.T_wc.size()) { set_error("bad frame"); return SBA_INVALID_ARGUMENT; }
+  std::memcpy(h->map.T_wc.data() + (size_t)frame * 16, T_wc16, 64);
+  return SBA_OK;
+}
+int sba_map_get_points(sba_handle h, int64_t first, int64_t count, float* xyz) {
+  if (!h || !xyz || first < 0 || count < 0 || (size_t)(first + count) > h->map.n_points) { set_error("bad range"); return SBA_INVALID_ARGUMENT; }
+  if (h->device < 0) return SBA_CUDA_ERROR;
+  CUDA_TRY(cudaSetDevice(h->device));
+  if (count > 0) CUDA_TRY(cudaMemcpyAsync(xyz, h->map.d_points + (size_t)first * 3, (size_t)count * 12, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return SBA_OK;
+}
+int sba_map_set_points(sba_handle h, int64_t first, int64_t count, const float* xyz) {
+  if (!h || !xyz || first < 0 || count < 0 || (size_t)(first + count) > h->map.n_points) { set_error("bad range"); return SBA_INVALID_ARGUMENT; }
+  if (h->device < 0) return SBA_CUDA_ERROR;
+  CUDA_TRY(cudaSetDevice(h->device));
+  if (count > 0) CUDA_TRY(cudaMemcpyAsync(h->map.d_points + (size_t)first * 3, xyz, (size_t)count * 12, cudaMemcpyHostToDevice, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return SBA_OK;
+}
+/* the last window's point ids (what Optimize wrote back) and the wall milliseconds of its phases:
+ * ms[5] = {pack (index build + poses), structure, state on device, solve, unpack} */
+int64_t sba_map_last_window(sba_handle h, uint32_t* point_ids, int64_t capacity, double* ms) {
+  if (!h) return -1;
+  const DeviceMap& M = h->map;
+  if (point_ids) std::memcpy(point_ids, M.ids.data(), (size_t)std::min<int64_t>(capacity, (int64_t)M.ids.size()) * 4);
+  if (ms) { ms[0] = M.ms_pack; ms[1] = M.ms_structure; ms[2] = M.ms_upload; ms[3] = M.ms_solve; ms[4] = M.ms_unpack; }
+  return (int64_t)M.ids.size();
+}
 
 // ---- multi-GPU --------------------------------------------------------------------------------------
 int sba_comm_unique_id(uint8_t id[128]) {

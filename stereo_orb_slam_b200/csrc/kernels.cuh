@@ -115,6 +115,7 @@ __global__ void __launch_bounds__(kLinThreads, 3) k_lin_chunk(Dev d, DevParams P
   const int chunk = blockIdx.x;
   const int4 c0 = __ldg(d.cdesc + 4 * (size_t)chunk), c1 = __ldg(d.cdesc + 4 * (size_t)chunk + 1);   // one record, one round trip
   const int p0 = c0.x, np = c0.y, e0 = c0.z, n = c0.w;
+  if (n > kMaxSlots) return;                               // a long track: k_lin_long's
   const int cs0 = c1.y, ns = c1.z, cs1 = cs0 + ns;
   double* cam_st = smem;                                   // [n * kCamStride]  A(6) h(3) G(9)
   double* pt_st = cam_st + (size_t)n * kCamStride;         // [n * 9]           V(6) gp(3)
@@ -403,6 +404,7 @@ __global__ void __launch_bounds__(kSchurThreads, 4) k_schur_chunk(Dev d, int max
   const int chunk = blockIdx.x;
   const int4 c0 = __ldg(d.cdesc + 4 * (size_t)chunk), c1 = __ldg(d.cdesc + 4 * (size_t)chunk + 1), c2 = __ldg(d.cdesc + 4 * (size_t)chunk + 2);
   const int p0 = c0.x, np = c0.y, e0 = c0.z, n = c0.w;
+  if (n > kMaxSlots) return;                               // a long track: k_schur_long's
   const int w = c1.x, cs0 = c1.y, cs1 = c1.y + c1.z, lb0 = c1.w, lb1 = c1.w + c2.x;
   const int pq0 = c2.y, npq = c2.z;
   double* Z = smem;                                     // [n * kZStride]
@@ -596,6 +598,7 @@ __global__ void __launch_bounds__(kFusedThreads, OCC) k_fused_chunk(Dev d, DevPa
   const int chunk = blockIdx.x;
   const int4 c0 = __ldg(d.cdesc + 4 * (size_t)chunk), c1 = __ldg(d.cdesc + 4 * (size_t)chunk + 1), c2 = __ldg(d.cdesc + 4 * (size_t)chunk + 2);
   const int p0 = c0.x, np = c0.y, e0 = c0.z, n = c0.w;
+  if (n > kMaxSlots) return;                               // a long track: k_lin_long + k_schur_long
   const int w = c1.x, cs0 = c1.y, ns = c1.z, cs1 = cs0 + ns, lb0 = c1.w, lb1 = c1.w + c2.x;
   const int pq0 = c2.y, npq = c2.z;
   double* cam_st = smem;                                   // [n * 27]  A: camera-side terms;  C/D: Z [n * 19]
@@ -848,6 +851,184 @@ __global__ void __launch_bounds__(kFusedThreads, OCC) k_fused_chunk(Dev d, DevPa
       if (lane == r) mine = x;
     }
     if (lane < 6) d.rpart[(size_t)d.cs_pos[cs] * 6 + lane] = mine;
+  }
+}
+
+// ------------------------------------------------------------------ long tracks (points with > 255 observations)
+// Loop-closure re-targeting (src/camera_frame.h:92-109) can give one map point hundreds of observations; the
+// reference has no limit.  Such a point is a chunk of its own with one slot per observation and one local block
+// per ordered pair of free observations; three small kernels do for it what the chunk kernels do for the rest, in
+// the same fixed orders (per-thread strided partials, then a fixed tree), feeding the same partial lists.
+constexpr int kLongThreads = 256;
+
+// sum of nine per-thread values over the CTA in a fixed order; every thread returns all nine totals
+__device__ __forceinline__ void long_sum9(double (&v)[9], double* sm /* [9 * 8] */) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) {
+    double x = v[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane == 0) sm[i * 8 + warp] = x;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 9; ++i) {
+    double t = 0.0;
+#pragma unroll
+    for (int k = 0; k < kLongThreads / 32; ++k) t += sm[i * 8 + k];
+    v[i] = t;
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kLongThreads) k_lin_long(Dev d, DevParams P) {
+  __shared__ double sm[9 * 8];
+  const int chunk = d.long_chunks[blockIdx.x];
+  const int4 c0 = __ldg(d.cdesc + 4 * (size_t)chunk), c1 = __ldg(d.cdesc + 4 * (size_t)chunk + 1);
+  const int p = c0.x, e0 = c0.z, n = c0.w, cs0 = c1.y;
+  const double X[3] = {d.pts[(size_t)p * 3], d.pts[(size_t)p * 3 + 1], d.pts[(size_t)p * 3 + 2]};
+  double acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};     // V (6), gp (3) over this thread's observations, in order
+  double cost = 0.0;
+  for (int i = threadIdx.x; i < n; i += kLongThreads) {
+    const int e = e0 + i;
+    const int cam = __ldg(d.pcam + e);
+    CamPre cp;
+    load_campre(d.campre, cam, cp);
+    const float4 m = __ldg(d.uv_p + e);
+    const float uv[4] = {m.x, m.y, m.z, m.w};
+    double q[3], r[4], D[12];
+    const double s = project(P.pl, P.pr, cp, X, uv, P.rdim, q, r, D);
+    double rho, wt;
+    huber(P.huber_delta, s, rho, wt);
+    cost += 0.5 * rho;
+    double A[6], h[3], G[9];
+    form_A_h(D, r, wt, A, h);
+    form_G(cp, q, G);
+    if (d.fc[cam] >= 0) {            // the observation is its own slot: its camera-side terms ARE the slot's partial row
+      double cu[27];
+#pragma unroll
+      for (int k = 0; k < 27; ++k) cu[k] = 0.0;
+      accum_camera(A, h, G, cu, cu + 21);
+      double* row = d.cspart + (size_t)d.cs_pos[cs0 + i] * 27;
+#pragma unroll
+      for (int k = 0; k < 27; ++k) row[k] = cu[k];
+    }
+    double Vc[9], W[18];
+    point_contrib(cp, A, h, G, Vc, W);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) acc[k] += Vc[k];
+    double2* Wo = reinterpret_cast<double2*>(d.W + (size_t)e * 18);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) Wo[k] = make_double2(W[2 * k], W[2 * k + 1]);
+    if (d.r_dbg) {
+      const double sq = sqrt(wt);
+      double* ro = d.r_dbg + (size_t)d.perm_p[e] * 4;
+      ro[0] = sq * r[0]; ro[1] = sq * r[1]; ro[2] = sq * r[2]; ro[3] = sq * r[3];
+    }
+  }
+  long_sum9(acc, sm);
+  double cv[9] = {cost, 0, 0, 0, 0, 0, 0, 0, 0};
+  long_sum9(cv, sm);
+  if (threadIdx.x == 0) {
+    double gmax = 0.0;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) d.V[(size_t)p * 6 + k] = acc[k];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      d.gp[(size_t)p * 3 + k] = acc[6 + k];
+      gmax = fmax(gmax, fabs(X[k] - clampd(X[k] - acc[6 + k], P.lo, P.hi)));
+    }
+    d.lin_part[2 * chunk] = cv[0]; d.lin_part[2 * chunk + 1] = gmax;
+  }
+}
+
+// damped 3x3 Cholesky of the point, Z = W Linv^T of every observation -> zlong, per-slot right-hand-side rows
+__global__ void __launch_bounds__(kLongThreads) k_schur_long(Dev d) {
+  __shared__ double sL[6], sU3[3];
+  const int li = blockIdx.x, chunk = d.long_chunks[li];
+  const int4 c0 = __ldg(d.cdesc + 4 * (size_t)chunk), c1 = __ldg(d.cdesc + 4 * (size_t)chunk + 1);
+  const int p = c0.x, e0 = c0.z, n = c0.w, w = c1.x, cs0 = c1.y;
+  if (threadIdx.x == 0) {
+    const double* V = d.V + (size_t)p * 6;
+    const double radius = d.w_radius[w];
+    const double a = V[0] + lm_damp(d.sc2p[(size_t)p * 3], V[0], radius);
+    const double dd = V[3] + lm_damp(d.sc2p[(size_t)p * 3 + 1], V[3], radius);
+    const double f = V[5] + lm_damp(d.sc2p[(size_t)p * 3 + 2], V[5], radius);
+    const double b = V[1], c = V[2], e = V[4];
+    double i00 = 0, i10 = 0, i11 = 0, i20 = 0, i21 = 0, i22 = 0;
+    bool ok = a > 0.0;
+    if (ok) {
+      const double l00 = sqrt(a);
+      i00 = 1.0 / l00;
+      const double l10 = b * i00, l20 = c * i00;
+      const double r1 = dd - l10 * l10;
+      ok = r1 > 0.0;
+      if (ok) {
+        const double l11 = sqrt(r1);
+        i11 = 1.0 / l11;
+        const double l21 = (e - l20 * l10) * i11;
+        const double r2 = f - l20 * l20 - l21 * l21;
+        ok = r2 > 0.0 && isfinite(r2);
+        if (ok) {
+          i22 = 1.0 / sqrt(r2);
+          i10 = -l10 * i00 * i11;
+          i21 = -l21 * i11 * i22;
+          i20 = -(l20 * i00 + l21 * i10) * i22;
+        }
+      }
+    }
+    if (!ok) { d.w_fail[w] = 1; i00 = i10 = i11 = i20 = i21 = i22 = 0.0; }
+    const double g0 = d.gp[(size_t)p * 3], g1 = d.gp[(size_t)p * 3 + 1], g2 = d.gp[(size_t)p * 3 + 2];
+    const double u0 = i00 * g0, u1 = i10 * g0 + i11 * g1, u2 = i20 * g0 + i21 * g1 + i22 * g2;
+    double* vo = d.Vinv + (size_t)p * 6;
+    vo[0] = i00 * i00 + i10 * i10 + i20 * i20; vo[1] = i10 * i11 + i20 * i21; vo[2] = i20 * i22;
+    vo[3] = i11 * i11 + i21 * i21; vo[4] = i21 * i22; vo[5] = i22 * i22;
+    d.tp[(size_t)p * 3] = i00 * u0 + i10 * u1 + i20 * u2;
+    d.tp[(size_t)p * 3 + 1] = i11 * u1 + i21 * u2;
+    d.tp[(size_t)p * 3 + 2] = i22 * u2;
+    sL[0] = i00; sL[1] = i10; sL[2] = i11; sL[3] = i20; sL[4] = i21; sL[5] = i22;
+    sU3[0] = u0; sU3[1] = u1; sU3[2] = u2;
+  }
+  __syncthreads();
+  const double i00 = sL[0], i10 = sL[1], i11 = sL[2], i20 = sL[3], i21 = sL[4], i22 = sL[5];
+  const double t0 = sU3[0], t1 = sU3[1], t2 = sU3[2];
+  double* Zb = d.zlong + (size_t)d.long_zoff[li] * 18;
+  for (int i = threadIdx.x; i < n; i += kLongThreads) {
+    double W[18];
+    load_W(d.W, (size_t)(e0 + i), W);
+    double* z = Zb + (size_t)i * 18;
+    double acc[6];
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+      const double w0 = W[3 * r], w1 = W[3 * r + 1], w2 = W[3 * r + 2];
+      const double z0 = w0 * i00, z1 = w0 * i10 + w1 * i11, z2 = w0 * i20 + w1 * i21 + w2 * i22;
+      z[3 * r] = z0; z[3 * r + 1] = z1; z[3 * r + 2] = z2;
+      acc[r] = z0 * t0 + z1 * t1 + z2 * t2;
+    }
+    if (d.fc[__ldg(d.pcam + e0 + i)] >= 0) {
+      double* row = d.rpart + (size_t)d.cs_pos[cs0 + i] * 6;
+#pragma unroll
+      for (int r = 0; r < 6; ++r) row[r] = acc[r];
+    }
+  }
+}
+
+// every local block of the long chunks is ONE product Z_a Z_b^T: a thread per element, grid-stride over all of them
+__global__ void k_schur_long_pairs(Dev d) {
+  const int64_t tot = (int64_t)d.long_lb_off[d.nlong] * 36;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < tot; t += (int64_t)gridDim.x * blockDim.x) {
+    const int l = (int)(t / 36), e = (int)(t - 36 * (int64_t)l), r = e / 6, c = e - 6 * r;
+    int li = 0;                                              // few long chunks: linear search
+    while (l >= d.long_lb_off[li + 1]) ++li;
+    const int chunk = d.long_chunks[li];
+    const int4 c1 = __ldg(d.cdesc + 4 * (size_t)chunk + 1);
+    const int lb = c1.w + (l - d.long_lb_off[li]);
+    const int q = d.lb_pair_off[lb];
+    const int a = d.pairs[q], b = d.pairs[q + 1];
+    const double* Za = d.zlong + ((size_t)d.long_zoff[li] + a) * 18 + 3 * r;
+    const double* Zb = d.zlong + ((size_t)d.long_zoff[li] + b) * 18 + 3 * c;
+    d.spart[(size_t)d.lb_pos[lb] * 36 + e] = Za[0] * Zb[0] + Za[1] * Zb[1] + Za[2] * Zb[2];
   }
 }
 

@@ -295,6 +295,8 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   UP(slot_off) UP(cs_cam) UP(cs_obs_off) UP(lb_off) UP(lb_blk) UP(lb_pair_off) UP(pairs) UP(oslot) UP(lb_sa) UP(lb_sb) UP(sobs)
   UP(blk_row) UP(blk_col) UP(diag_blk) UP(blk_part_off) UP(blk_part) UP(cam_part_off) UP(cam_part)
   UP(row_ptr) UP(bsr_col) UP(bsr_blk) UP(lb_pos) UP(cs_pos)
+  d.nlong = (int32_t)H.long_chunks.size();
+  if (d.nlong > 0) { UP(long_chunks) UP(long_zoff) UP(long_lb_off) }
 #undef UP
   const size_t nobs = (size_t)H.Nobs, nc = (size_t)H.Nc, np = (size_t)H.Np, nf = (size_t)H.Nf, nw = (size_t)H.nwin;
 #define AL(ptr, n) if ((rc = h->alloc(&ptr, (n)))) return rc;
@@ -303,6 +305,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   AL(h->uv_in, (size_t)Nobs)
   AL(d.poses, nc * 6) AL(d.poses_new, nc * 6) AL(d.pts, np * 3) AL(d.pts_new, np * 3)
   AL(d.campre_new, nc) AL(d.campre, nc)
+  if (d.nlong > 0) AL(d.zlong, (size_t)H.long_zoff.back() * 18)
   AL(d.W, nobs * 18) AL(d.V, np * 6) AL(d.gp, np * 3) AL(d.Vinv, np * 6) AL(d.tp, np * 3)
   AL(d.U, nc * 27 + nw + nw * kMaxRanks)   // U | gc | cost_red | gslots: one block, one all-reduce per linearisation (multi-GPU)
   d.gc = d.U + nc * 21; d.cost_red = d.gc + nc * 6; d.gslots = d.cost_red + nw;
@@ -605,6 +608,10 @@ static int do_linearize(sba_handle h, bool keep_cost = false, bool fork_tail = f
     h->launches++;
     h->schur_fresh = true;
   } else if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; }
+  if (d.nlong > 0) {        // long tracks (> 255 observations of one point): their own kernels, same partial lists
+    LAUNCH(h, k_lin_long, d.nlong, kLongThreads, d, P);
+    if (fused) { LAUNCH(h, k_schur_long, d.nlong, kLongThreads, d); LAUNCH(h, k_schur_long_pairs, 296, 256, d); }
+  }
   h->cams_pending = false;
   if (fused && fork_tail && !h->comm.active() && !std::getenv("SBA_NO_FORK")) {
     h->cams_pending = true; h->pend_keep_cost = keep_cost; h->pend_lm_begin = lm_begin; h->pend_radius = initial_radius;
@@ -649,7 +656,10 @@ static int do_linearize(sba_handle h, bool keep_cost = false, bool fork_tail = f
 static int do_schur(sba_handle h, bool exact_solver = false) {
   Dev& d = h->d;
   if (h->schur_fresh) h->schur_fresh = false;      // the fused linearisation already left this radius' partials
-  else if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++; }
+  else if (d.npchunk > 0) {
+    k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++;
+    if (d.nlong > 0) { LAUNCH(h, k_schur_long, d.nlong, kLongThreads, d); LAUNCH(h, k_schur_long_pairs, 296, 256, d); }
+  }
   { const int jrc = join_tail(h); if (jrc) return jrc; }
   if (h->cams_pending) {
     // after a fused linearisation (single GPU): ONE assemble kernel for U / gc / S / rhs, then the window cost and the
@@ -801,7 +811,7 @@ static int do_step(sba_handle h, int* ls_rounds) {
     int grid = std::max(1, std::min(h->coop_blocks, want));
     if (const char* e = std::getenv("SBA_STEP_GRID")) grid = std::max(1, std::min(grid, std::atoi(e)));   // tuning aid
     Dev dd = d; DevParams pp = P;
-    int fused_cams = h->H.max_slots <= kTrialSlots ? 1 : 0;
+    int fused_cams = (h->H.max_slots <= kTrialSlots && h->H.long_chunks.empty()) ? 1 : 0;
     void* args[] = {&dd, &pp, &fused_cams};
     CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_step_loop, dim3(grid), dim3(kThreads), args, 0, h->stream));
     h->launches++;

@@ -30,6 +30,10 @@ struct Dev {
   const int32_t *blk_row, *blk_col, *diag_blk, *blk_part_off, *blk_part, *cam_part_off, *cam_part;
   const int32_t *row_ptr, *bsr_col, *bsr_blk;
   const int32_t *lb_pos, *cs_pos;
+  // long tracks (points with > 255 observations: one chunk each, k_*_long kernels)
+  const int32_t *long_chunks, *long_zoff, *long_lb_off;   // [nlong], [nlong+1], [nlong+1]
+  int32_t nlong;
+  double* zlong;                 // [long_zoff[nlong] * 18] Z = W Linv^T of their observations
   // ---- measurements (const during a solve)
   const float4 *uv_p;   // [Nobs] point order
   // ---- state

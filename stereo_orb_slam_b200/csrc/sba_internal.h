@@ -1,6 +1,7 @@
 // sba_internal.h — host-side structure tables of the stereo bundle adjuster (not part of the ABI).
 #pragma once
 #include <cstdint>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -11,6 +12,7 @@ constexpr int kPointChunk = 128;     // max points per chunk
 constexpr int kObsChunk = 240;       // max observations per chunk (= CTA size of the thread-per-observation kernels;
                                      // chunk-local observation indices fit a byte)
 constexpr int kMaxSlots = 255;       // distinct cameras per chunk (slot index is a byte)
+constexpr int kMaxLongObs = 4096;    // observations of one point in the long-track path (its cameras form a dense k x k block of S)
 
 // Everything that depends only on (obs_cam, obs_pt, cam_fixed, windows): built once on the host
 // (reference: the index build of src/bundle_adjuster.cpp:57-110 fixes obs->cam/pt; the rest is new).
@@ -57,7 +59,16 @@ struct HostStructure {
   // of one point with slot(a) = sa, slot(b) = sb, points ascending; its partial is sum_pairs W_a Vinv W_b^T
   std::vector<int32_t> lb_pair_off;                             // [nlb+1]
   std::vector<uint16_t> pairs;                                  // [npairs]
-  int32_t max_slots = 0, max_chunk_obs = 0, max_chunk_pts = 0, max_chunk_pairs = 0;  // over owned chunks (shared-memory sizing)
+  int32_t max_slots = 0, max_chunk_obs = 0, max_chunk_pts = 0, max_chunk_pairs = 0;  // over owned REGULAR chunks (shared-memory sizing)
+  // long tracks: a point with more than kMaxSlots observations (loop-closure re-targeting, src/camera_frame.h:92-109)
+  // is a chunk of its own, handled by the k_*_long kernels: one slot per observation, one local block per ordered
+  // observation pair (its `pairs` entry is the two chunk-local observation indices, 16 bits each)
+  std::vector<int32_t> long_chunks;                             // owned chunk ids
+  std::vector<int32_t> long_zoff;                               // [nlong+1] offsets (observations) into the Z scratch
+  std::vector<int32_t> long_lb_off;                             // [nlong+1] prefix of their local-block counts
+  // build workspace kept between calls on one handle (per-chunk tables, sort buffers): BundleAdjuster::Optimize
+  // re-structures on every call, and fresh vectors cost more in page faults and allocator calls than the build itself
+  std::shared_ptr<void> work;
   // reduced camera matrix: upper blocks (row <= col, free indices), sorted (row, col); partial lists
   std::vector<int32_t> blk_row, blk_col;                        // [nbu]
   std::vector<int32_t> blk_part_off;                            // [nbu+1]

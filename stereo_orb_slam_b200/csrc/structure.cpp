@@ -21,7 +21,21 @@ namespace sba {
 
 namespace {
 
-struct ChunkRange { int32_t p0, p1, win; bool owned; };
+struct ChunkRange { int32_t p0, p1, win; bool owned; bool is_long; };
+struct LB { uint8_t sa, sb; int64_t key; };
+struct ChunkTab {
+  std::vector<int32_t> cams, slot_obs_off;
+  std::vector<uint8_t> oslot;
+  std::vector<uint16_t> sobs;
+  std::vector<LB> lbs;
+  std::vector<int32_t> lb_pair_cnt;     // [nlb]
+  std::vector<uint16_t> pairs;          // grouped by lb
+};
+struct Work {
+  std::vector<ChunkRange> cr;
+  std::vector<ChunkTab> tab;
+  std::vector<int32_t> gpt_off, gperm, pt_win;
+};
 
 // chunk boundaries over ALL points (unowned ones only feed the block pattern): never across a window, never
 // across the owned range, <= kPointChunk points, <= obs_cap observations
@@ -38,16 +52,22 @@ bool make_chunks(const HostStructure& H, const std::vector<int32_t>& gpt_off, in
       else if (p < H.pt_begin) limit = std::min(limit, H.pt_begin);
       int q = p;
       int nobs = 0;
+      bool is_long = false;
       while (q < limit && q - p < kPointChunk) {
         const int k = gpt_off[q + 1] - gpt_off[q];
-        if (k > kMaxSlots) { *err = "a point has more than 255 observations (unsupported track length)"; return false; }
+        if (k > kMaxLongObs) { *err = "a point has more than 4096 observations (unsupported track length)"; return false; }
+        if (k > kMaxSlots) {       // long track: a chunk of its own for the k_*_long kernels
+          if (q > p) break;
+          is_long = true; nobs = k; ++q;
+          break;
+        }
         // a point never straddles chunks; one whose track alone exceeds the tuning cap (obs_cap < k <= 255) gets a
         // chunk of its own — chunk-local indices are bytes and the per-observation kernels run 256 threads
         if (nobs + k > obs_cap && q > p) break;
         nobs += k; ++q;
       }
       if (q == p) { *err = "internal: empty chunk"; return false; }
-      out->push_back(ChunkRange{p, q, w, owned});
+      out->push_back(ChunkRange{p, q, w, owned, is_long});
       p = q;
     }
   }
@@ -64,7 +84,12 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
   if (nwin < 1) nwin = 1;
   if (pt_begin < 0 || pt_end > Np || pt_begin > pt_end) return "bad point shard";
   HostStructure& H = *S;
-  H = HostStructure();
+  // vectors keep their capacity from the previous build on this handle (every one is re-sized / re-assigned below)
+  H.Nf = 0; H.Nobs = 0; H.obs_cap = kObsChunk;
+  H.max_slots = H.max_chunk_obs = H.max_chunk_pts = H.max_chunk_pairs = 0;
+  H.long_chunks.clear(); H.long_zoff.clear(); H.long_lb_off.clear();
+  if (!H.work) H.work = std::make_shared<Work>();
+  Work& Wk = *static_cast<Work*>(H.work.get());
   const bool timing = std::getenv("SBA_TIMING") != nullptr;
   // host threads of the structure build: SBA_HOST_THREADS, else the OpenMP default (launchers such as torchrun set
   // OMP_NUM_THREADS=1 for every rank, which is the wrong default for this short, embarrassingly parallel build)
@@ -92,7 +117,8 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     H.win_cam_off[0] = 0; H.win_cam_off[1] = Nc; H.win_pt_off[0] = 0; H.win_pt_off[1] = Np;
   }
   H.cam_win.resize(Nc);
-  std::vector<int32_t> pt_win(Np);
+  std::vector<int32_t>& pt_win = Wk.pt_win;
+  pt_win.resize(Np);
   for (int w = 0; w < nwin; ++w) {
     for (int c = H.win_cam_off[w]; c < H.win_cam_off[w + 1]; ++c) H.cam_win[c] = w;
     for (int p = H.win_pt_off[w]; p < H.win_pt_off[w + 1]; ++p) pt_win[p] = w;
@@ -112,7 +138,8 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
   for (int c = 0; c < Nc; ++c) if (H.fc[c] >= 0) { H.free2cam[H.fc[c]] = c; H.fcam_win[H.fc[c]] = H.cam_win[c]; }
 
   // ---- validate + global point-order counting sort (stable in input order)
-  std::vector<int32_t> gpt_off(Np + 1, 0);
+  std::vector<int32_t>& gpt_off = Wk.gpt_off;
+  gpt_off.assign((size_t)Np + 1, 0);
   for (int64_t k = 0; k < NobsAll; ++k) {
     const int32_t c = obs_cam[k], p = obs_pt[k];
     if (c < 0 || c >= Nc) return "obs_cam out of range";
@@ -121,7 +148,8 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     gpt_off[p + 1]++;
   }
   for (int p = 0; p < Np; ++p) gpt_off[p + 1] += gpt_off[p];
-  std::vector<int32_t> gperm(NobsAll);
+  std::vector<int32_t>& gperm = Wk.gperm;
+  gperm.resize((size_t)NobsAll);
   {
     std::vector<int32_t> cur(gpt_off.begin(), gpt_off.end() - 1);
     for (int64_t k = 0; k < NobsAll; ++k) gperm[cur[obs_pt[k]]++] = (int32_t)k;
@@ -147,24 +175,15 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
 
   lap("point-order views");
   // ---- chunks, camera slots, local blocks
-  struct LB { uint8_t sa, sb; int64_t key; };
-  struct ChunkTab {
-    std::vector<int32_t> cams, slot_obs_off;
-    std::vector<uint8_t> oslot;
-    std::vector<uint16_t> sobs;
-    std::vector<LB> lbs;
-    std::vector<int32_t> lb_pair_cnt;     // [nlb]
-    std::vector<uint16_t> pairs;          // grouped by lb
-  };
-  std::vector<ChunkRange> cr;
-  std::vector<ChunkTab> tab;
+  std::vector<ChunkRange>& cr = Wk.cr;
+  std::vector<ChunkTab>& tab = Wk.tab;
   int obs_cap = kObsChunk;
   if (const char* e = std::getenv("SBA_OBS_CAP")) obs_cap = std::min(kObsChunk, std::max(8, std::atoi(e)));   // tuning aid
   for (int attempt = 0; attempt < 2; ++attempt) {
     std::string err;
     if (!make_chunks(H, gpt_off, obs_cap, &cr, &err)) return err;
     const int nch = (int)cr.size();
-    tab.assign(nch, ChunkTab());
+    if ((int)tab.size() < nch) tab.resize(nch);        // tables (and their capacity) of earlier builds are reused
     bool overflow = false;
 #pragma omp parallel num_threads(nthreads)
     {
@@ -175,8 +194,37 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
       for (int ch = 0; ch < nch; ++ch) {
         const ChunkRange& R = cr[ch];
         ChunkTab& T = tab[ch];
+        T.cams.clear(); T.lbs.clear(); T.pairs.clear(); T.lb_pair_cnt.clear(); T.oslot.clear(); T.sobs.clear(); T.slot_obs_off.clear();
         const int32_t g0 = gpt_off[R.p0], g1 = gpt_off[R.p1];
         const int n = g1 - g0;
+        if (R.is_long) {
+          // one slot per observation, one local block per ordered pair (a, b) of free observations with
+          // fc[cam(b)] > fc[cam(a)], or the same camera (then both orders: Z_a Z_b^T and Z_b Z_a^T land on (f, f))
+          T.cams.resize(n);
+          for (int i = 0; i < n; ++i) T.cams[i] = obs_cam[gperm[g0 + i]];
+          struct LL { int64_t key; uint16_t a, b; };
+          std::vector<LL> ll;
+          for (int a = 0; a < n; ++a) {
+            const int64_t fa = H.fc[T.cams[a]];
+            if (fa < 0) continue;
+            for (int b = 0; b < n; ++b) {
+              const int64_t fb = H.fc[T.cams[b]];
+              if (fb < fa) continue;
+              if (fb == fa && T.cams[a] != T.cams[b]) continue;
+              ll.push_back(LL{fa * (int64_t)Nf + fb, (uint16_t)a, (uint16_t)b});
+            }
+          }
+          std::stable_sort(ll.begin(), ll.end(), [](const LL& x, const LL& y) { return x.key < y.key; });
+          T.lbs.resize(ll.size()); T.pairs.resize(ll.size() * 2); T.lb_pair_cnt.assign(ll.size(), 2);
+          for (size_t l = 0; l < ll.size(); ++l) { T.lbs[l] = LB{0, 0, ll[l].key}; T.pairs[2 * l] = ll[l].a; T.pairs[2 * l + 1] = ll[l].b; }
+          if (R.owned) {
+            T.oslot.assign(n, 0);
+            T.slot_obs_off.resize(n + 1); T.sobs.resize(n);
+            for (int i = 0; i <= n; ++i) T.slot_obs_off[i] = i;
+            for (int i = 0; i < n; ++i) T.sobs[i] = (uint16_t)i;
+          }
+          continue;
+        }
         T.oslot.resize(n);
         bool bad = false;
         for (int i = 0; i < n; ++i) {
@@ -218,7 +266,7 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
               T.lbs.push_back(LB{(uint8_t)sa, (uint8_t)sb, fa * (int64_t)Nf + fb});
             }
         std::sort(T.lbs.begin(), T.lbs.end(), [](const LB& x, const LB& y) { return x.key < y.key; });
-        if (!R.owned) { T.oslot.clear(); T.oslot.shrink_to_fit(); continue; }
+        if (!R.owned) { T.oslot.clear(); continue; }
         // observations grouped by slot (stable)
         cnt.assign(ns + 1, 0);
         for (int i = 0; i < n; ++i) cnt[T.oslot[i] + 1]++;
@@ -306,10 +354,17 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
       H.slot_off[i + 1] = H.slot_off[i] + (int32_t)T.cams.size();
       H.lb_off[i + 1] = H.lb_off[i] + (int32_t)T.lbs.size();
       pair_off[i + 1] = pair_off[i] + (int64_t)T.pairs.size();
-      H.max_slots = std::max(H.max_slots, (int32_t)T.cams.size());
-      H.max_chunk_obs = std::max(H.max_chunk_obs, (int32_t)T.oslot.size());
-      H.max_chunk_pts = std::max(H.max_chunk_pts, R.p1 - R.p0);
-      H.max_chunk_pairs = std::max(H.max_chunk_pairs, (int32_t)std::min<size_t>(T.pairs.size(), 1u << 30));
+      if (R.is_long) {
+        if (H.long_chunks.empty()) { H.long_zoff.assign(1, 0); H.long_lb_off.assign(1, 0); }
+        H.long_chunks.push_back(i);
+        H.long_zoff.push_back(H.long_zoff.back() + (int32_t)T.cams.size());
+        H.long_lb_off.push_back(H.long_lb_off.back() + (int32_t)T.lbs.size());
+      } else {
+        H.max_slots = std::max(H.max_slots, (int32_t)T.cams.size());
+        H.max_chunk_obs = std::max(H.max_chunk_obs, (int32_t)T.oslot.size());
+        H.max_chunk_pts = std::max(H.max_chunk_pts, R.p1 - R.p0);
+        H.max_chunk_pairs = std::max(H.max_chunk_pairs, (int32_t)std::min<size_t>(T.pairs.size(), 1u << 30));
+      }
     }
     while (w_next <= nwin) H.win_pchunk_off[w_next++] = nch;
   }
@@ -340,7 +395,7 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     }
     if (!T.pairs.empty()) std::memcpy(H.pairs.data() + pair_off[i], T.pairs.data(), T.pairs.size() * sizeof(uint16_t));
   }
-  std::vector<ChunkTab>().swap(tab);
+  if (NobsAll > 4000000) { std::vector<ChunkTab>().swap(tab); std::vector<int32_t>().swap(gperm); }   // global problems: do not sit on hundreds of MB
   {
     const int nch = (int)H.pchunk_begin.size();
     H.cdesc.assign((size_t)nch * 16, 0);
@@ -352,6 +407,7 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
       D[8] = H.lb_off[ch + 1] - H.lb_off[ch]; D[9] = H.lb_pair_off[H.lb_off[ch]];
       D[10] = H.lb_pair_off[H.lb_off[ch + 1]] - H.lb_pair_off[H.lb_off[ch]];
     }
+    for (size_t li = 0; li < H.long_chunks.size(); ++li) H.cdesc[(size_t)H.long_chunks[li] * 16 + 11] = 1 + (int32_t)li;   // long-track chunk (1-based)
   }
 
   lap("flatten");

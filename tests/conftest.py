@@ -50,6 +50,38 @@ def batch_windows(ws):
                 p_l=ws[0]["p_l"], p_r=ws[0]["p_r"])
 
 
+def long_track_map(num_frames=260, num_long=10, num_short=500, seed=5):
+    """A map in which `num_long` points are seen by EVERY frame (tracks longer than a chunk's 255-observation cap —
+    what loop-closure re-targeting produces, src/camera_frame.h:92-109) plus short-track points: a slowly drifting
+    rig in front of a point cloud."""
+    from stereo_orb_slam_b200 import synthetic
+    rng = np.random.default_rng(seed)
+    cam = synthetic.KITTI
+    T = np.zeros((num_frames, 4, 4)); T[:, 3, 3] = 1
+    f = np.arange(num_frames)
+    T[:, :3, :3] = synthetic._rot(0.002 * np.sin(0.05 * f), 0.004 * np.sin(0.03 * f), np.zeros(num_frames))
+    T[:, :3, 3] = np.stack([0.4 * np.sin(0.04 * f), 0.05 * np.cos(0.06 * f), 0.01 * f], axis=1)
+    R_cw = np.transpose(T[:, :3, :3], (0, 2, 1)); t_cw = -np.einsum("nij,nj->ni", R_cw, T[:, :3, 3])
+    n_pts = num_long + num_short
+    X = np.stack([rng.uniform(-3, 3, n_pts), rng.uniform(-1, 1, n_pts), rng.uniform(8, 20, n_pts)], axis=1)
+    first = np.concatenate([np.zeros(num_long, np.int64), np.sort(rng.integers(0, num_frames - 5, num_short))])
+    last = np.concatenate([np.full(num_long, num_frames), first[num_long:] + 5])
+    fr, pid = [], []
+    for fi in range(num_frames):
+        vis = np.nonzero((first <= fi) & (fi < last))[0]
+        fr.append(np.full(vis.size, fi)); pid.append(vis)
+    fr = np.concatenate(fr); pid = np.concatenate(pid)
+    uv, z = synthetic._project(R_cw[fr], t_cw[fr], X[pid], cam)
+    uv32 = (uv + rng.normal(0, 0.3, uv.shape)).astype(np.float32)
+    frame_off = np.zeros(num_frames + 1, np.int64); np.add.at(frame_off, fr + 1, 1); frame_off = np.cumsum(frame_off)
+    T0 = T.copy()
+    T0[1:, :3, 3] += rng.normal(0, 0.01, (num_frames - 1, 3))
+    p_l, p_r = synthetic.projection_matrices(cam)
+    return synthetic.StereoMap(T_wc=T0.astype(np.float32), points=(X + rng.normal(0, 0.05, X.shape)).astype(np.float32),
+                               frame_off=frame_off, obs_point_id=pid.astype(np.uint32), obs_uv=uv32,
+                               obs_sigma=np.ones(fr.size, np.float32), p_l=p_l, p_r=p_r, gt_T_wc=T, gt_points=X)
+
+
 @pytest.fixture(scope="session")
 def small_window():
     return make_window(8, 600, 5, seed=7)

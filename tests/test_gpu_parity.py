@@ -8,7 +8,7 @@ import pytest
 
 from oracle import oracle
 from stereo_orb_slam_b200 import BundleAdjuster, Solver, _capi, default_options, pack_window, synthetic
-from conftest import batch_windows, make_window
+from conftest import batch_windows, long_track_map, make_window
 
 pytestmark = pytest.mark.gpu
 
@@ -458,6 +458,36 @@ def test_sparse_cholesky_solves_the_reduced_system_of_a_loop():
     assert np.abs(x - xs).max() <= 1e-10 * np.abs(xs).max()
     s.pcg(default_options(linear_solver=2))
     assert np.array_equal(s.schur_values()[2], x)
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_long_tracks_match_the_oracle(fused, monkeypatch):
+    """Points seen by 260 frames (> 255 observations: the long-track kernels) next to ordinary short tracks: blocks
+    and the full solve against the oracle, through the fused and the two-kernel linearisation."""
+    if not fused:
+        monkeypatch.setenv("SBA_NO_FUSED", "1")
+    smap = long_track_map()
+    w = pack_window(smap, 0, smap.num_frames)
+    w["p_l"], w["p_r"] = smap.p_l, smap.p_r
+    s = load(w)
+    s.linearize()
+    g = s.get_linearization()
+    ref = oracle.linearize(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
+    for k in ("V", "W", "gp"):
+        assert relerr(g[k], ref[k]) < 1e-9, k
+    for k in ("U", "gc"):
+        assert relerr(g[k][1:], ref[k][1:]) < 1e-9, k
+    assert abs(g["cost"][0] - ref["cost"]) <= 1e-12 * ref["cost"]
+    fixed = np.zeros(smap.num_frames, np.uint8); fixed[0] = 1
+    s.schur(1e12)
+    S, rhs, _ = s.schur_dense()
+    So, rhso = oracle.schur(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"], fixed, 1e12)
+    assert relerr(S, So) < 1e-8 and relerr(rhs, rhso) < 1e-8
+    args = (w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"])
+    pg, xg, sg = Solver(0).solve(*args, options=default_options(max_time_s=0.0, max_iterations=15))
+    po, xo, so = oracle.solve(*args, options=oracle_opts(max_iterations=15))
+    assert sg["iterations"] == so["iterations"]
+    check_solution(w, sg, pg, xg, so, po, xo)
 
 
 def test_wall_clock_limit_terminates_with_the_state_written_back():

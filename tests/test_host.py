@@ -164,11 +164,12 @@ def test_structure_is_independent_of_the_host_thread_count(monkeypatch):
         Solver(-1).set_structure(Nc, Np, oc, op)
 
 
-@pytest.mark.parametrize("k,ok", [(240, True), (241, True), (255, True), (256, False)])
-def test_long_tracks_get_a_chunk_of_their_own_or_a_clean_error(k, ok):
-    """One point seen by k cameras (loop-closure re-targeting produces long tracks, src/camera_frame.h:92-109).
-    Chunk-local indices are bytes: up to 255 observations the point gets its own chunk (round 1 looped forever for
-    241..255); beyond that the structure build refuses with SBA_INVALID_ARGUMENT instead of crashing."""
+@pytest.mark.parametrize("k,ok", [(240, True), (241, True), (255, True), (256, True), (700, True), (4097, False)])
+def test_long_tracks_are_chunks_of_their_own(k, ok):
+    """One point seen by k cameras (loop-closure re-targeting produces long tracks, src/camera_frame.h:92-109; the
+    reference has no limit).  Up to 255 observations the point rides in a byte-indexed chunk (round 1 looped forever
+    for 241..255); above that it becomes a long-track chunk (one slot per observation, k_*_long kernels); beyond 4096
+    the structure build refuses with SBA_INVALID_ARGUMENT instead of crashing."""
     cam = np.concatenate([np.arange(k), np.arange(k)]).astype(np.int32)
     pt = np.concatenate([np.zeros(k), np.ones(k)]).astype(np.int32)          # two such points
     extra_c = np.array([0, 1, 2], np.int32); extra_p = np.array([2, 2, 2], np.int32)
@@ -183,3 +184,14 @@ def test_long_tracks_get_a_chunk_of_their_own_or_a_clean_error(k, ok):
         with pytest.raises(_capi.SbaError) as e:
             s.set_structure(k, 3, np.concatenate([cam, extra_c]), np.concatenate([pt, extra_p]))
         assert e.value.status == _capi.SBA_INVALID_ARGUMENT
+
+
+def test_long_track_pattern_equals_the_oracle_pattern():
+    from conftest import long_track_map
+    smap = long_track_map(num_frames=270, num_long=3, num_short=60)
+    w = pack_window(smap, 0, smap.num_frames)
+    s = Solver(-1).set_structure(w["poses"].shape[0], w["points"].shape[0], w["obs_cam"], w["obs_pt"])
+    rows, cols = s.schur_pattern()
+    fixed = np.zeros(smap.num_frames, np.uint8); fixed[0] = 1
+    r2, c2 = oracle.schur_pattern(w["poses"].shape[0], w["points"].shape[0], w["obs_cam"], w["obs_pt"], fixed)
+    assert np.array_equal(rows, r2) and np.array_equal(cols, c2)

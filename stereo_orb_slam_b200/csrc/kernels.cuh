@@ -2579,10 +2579,26 @@ __device__ __forceinline__ void dev_cam_step(const Dev& d, int w, int rank) {
       }
     }
   }
-  for (int ch = d.win_pchunk_off[w] + threadIdx.x; ch < d.win_pchunk_off[w + 1]; ch += kThreads) {
+  // (a global window has tens of thousands of chunk partials for this one CTA: eight rows in flight per thread, added in
+  // the same order as one at a time)
+  {
+    const int c1 = d.win_pchunk_off[w + 1];
+    int ch = d.win_pchunk_off[w] + threadIdx.x;
+    for (; ch + 7 * kThreads < c1; ch += 8 * kThreads) {
+      double2 va[8], vb[8];
 #pragma unroll
-    for (int i = 0; i < 3; ++i) part[i] += d.step_part[(size_t)ch * 4 + i];
-    dmax = fmax(dmax, d.step_part[(size_t)ch * 4 + 3]);
+      for (int u = 0; u < 8; ++u) {
+        const double2* q = reinterpret_cast<const double2*>(d.step_part + (size_t)(ch + u * kThreads) * 4);
+        va[u] = __ldcg(q); vb[u] = __ldcg(q + 1);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { part[0] += va[u].x; part[1] += va[u].y; part[2] += vb[u].x; dmax = fmax(dmax, vb[u].y); }
+    }
+    for (; ch < c1; ch += kThreads) {
+      const double2* q = reinterpret_cast<const double2*>(d.step_part + (size_t)ch * 4);
+      const double2 va = __ldcg(q), vb = __ldcg(q + 1);
+      part[0] += va.x; part[1] += va.y; part[2] += vb.x; dmax = fmax(dmax, vb.y);
+    }
   }
   double tot = block_sum<4>(part, sm);
   const double mx = block_max1(dmax, smx);
@@ -2737,9 +2753,24 @@ __device__ __forceinline__ void dev_ls_reduce(const Dev& d, int w, int rank) {
   const int st = __ldcg(d.w_ls_state + w);
   if (st < 1 || st > 3) return;
   double part[3] = {0, 0, 0};
-  for (int ch = d.win_pchunk_off[w] + threadIdx.x; ch < d.win_pchunk_off[w + 1]; ch += kThreads) {
+  {
+    const int c1 = d.win_pchunk_off[w + 1];
+    int ch = d.win_pchunk_off[w] + threadIdx.x;
+    for (; ch + 7 * kThreads < c1; ch += 8 * kThreads) {     // eight rows in flight per thread, same order of additions
+      double v[8][3];
 #pragma unroll
-    for (int i = 0; i < 3; ++i) part[i] += __ldcg(d.ls_part + (size_t)ch * 3 + i);
+      for (int u = 0; u < 8; ++u)
+#pragma unroll
+        for (int i = 0; i < 3; ++i) v[u][i] = __ldcg(d.ls_part + (size_t)(ch + u * kThreads) * 3 + i);
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+#pragma unroll
+        for (int i = 0; i < 3; ++i) part[i] += v[u][i];
+    }
+    for (; ch < c1; ch += kThreads) {
+#pragma unroll
+      for (int i = 0; i < 3; ++i) part[i] += __ldcg(d.ls_part + (size_t)ch * 3 + i);
+    }
   }
   if (rank == 0)
     for (int c = d.win_cam_off[w] + threadIdx.x; c < d.win_cam_off[w + 1]; c += kThreads) {

@@ -216,6 +216,22 @@ int sba_map_set_points(sba_handle h, int64_t first, int64_t count, const float* 
  * {index build + poses, structure, state on device, solve, unpack}. */
 int64_t sba_map_last_window(sba_handle h, uint32_t* point_ids, int64_t capacity, double* ms5);
 
+/* ---- pose-graph optimisation ---------------------------------------------------- */
+/* What PoseGraphOptimizer::Optimize hands to g2o (src/pose_graph_optimizer.cpp:34-96): SE3 vertices = the frames'
+ * world-from-camera poses, edges (i, j) with measurement Z = X_i^-1 X_j (odometry :143-168: Frame::RelativePose; loop
+ * closures :192-211), information diag(0.01, 0.01, 0.01, 1, 1, 1) (translation first, :23-26), Huber kernel (:162),
+ * vertex 0 fixed (:123-126), 10 Levenberg iterations (:66).  Poses are 4x4 row-major f64 (g2o works in double on the
+ * Frames' float poses), updated in place.  fixed NULL = vertex 0; information6 NULL = the reference's diagonal. */
+typedef struct sba_pgo_summary {
+  double  initial_chi2, final_chi2, final_lambda;
+  int32_t iterations, trials;    /* Levenberg iterations run; linear solves tried (g2o retries with a larger lambda) */
+  int32_t termination;           /* 0 iteration limit, 1 g2o's Terminate (10 failed trials / zero gain / lambda overflow) */
+  double  time_total_s, time_symbolic_s;
+} sba_pgo_summary;
+int sba_pgo_optimize(sba_handle h, int32_t num_vertices, double* T_wc, int32_t num_edges, const int32_t* edge_i, const int32_t* edge_j,
+                     const double* Z, const uint8_t* fixed, const double* information6, double huber_delta, int32_t iterations,
+                     sba_pgo_summary* summary);
+
 /* ---- host side of BundleAdjuster::Optimize ------------------------------------------------------ */
 /* Pack window [start,end) of a map (reference: src/bundle_adjuster.cpp:41-110).
  *   T_wc [N*16] f32 row-major world-from-camera (Frame::GlobalPose), map_points [M*3] f32,

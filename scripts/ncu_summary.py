@@ -33,7 +33,7 @@ def main():
     lines, traffic = [], {}
     for r in rows[start + 2:]:
         name = r[hdr.index('Kernel Name')]
-        short = name.split('(')[0].split('::')[-1]
+        short = name.split('(')[0].split('::')[-1].replace('void ', '').split('<')[0].strip()
         lines.append('----- ' + name)
         for k in KEYS:
             if k in hdr:

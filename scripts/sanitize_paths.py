@@ -1,7 +1,11 @@
-"""Every solver path once on a small problem — the workload compute-sanitizer runs (memcheck / racecheck):
+"""Every solver path on a small problem, TWICE, results compared bit for bit.
 
+Written as the workload for compute-sanitizer (memcheck / racecheck):
   compute-sanitizer --tool memcheck  python scripts/sanitize_paths.py
-  compute-sanitizer --tool racecheck python scripts/sanitize_paths.py
+On this pool compute-sanitizer is closed (profiles/r02_sanitizer_closed.log: "runs under it have left GPUs needing a
+reset"), so the script is its own check: every reduction in the library has a fixed order, hence any data race shows
+up as a run-to-run difference in the last bits (that is how round 1's k_pcg_coop race was found); each path must
+reproduce itself exactly.
 
 Paths: chunk kernels fused and unfused, k_chol_band / k_chol_window / k_chol_cluster, k_spchol (panel and column
 paths), the four PCG paths, k_step_loop and the multi-launch step, long tracks, batched windows, the resident map."""
@@ -26,7 +30,7 @@ CASES = [
 def one(kind, solver):
     import numpy as np
     from stereo_orb_slam_b200 import Solver, default_options, pack_window, replay, synthetic
-    opt = default_options(max_time_s=0.0, max_iterations=3, linear_solver=solver)
+    opt = default_options(max_time_s=0.0, max_iterations=6, linear_solver=solver)
     if kind == "small":
         smap = synthetic.make_map(num_frames=8, num_points=600, track_len=5, seed=7)
     elif kind == "loop":
@@ -36,12 +40,23 @@ def one(kind, solver):
         smap = long_track_map(num_frames=258, num_long=2, num_short=80)
     elif kind == "map":
         smap = synthetic.make_map(num_frames=12, num_points=500, track_len=5, seed=11)
-        ba, calls = replay(smap, interval=5, options=opt)
-        print("   map replay:", len(calls), "calls, last cost %.6e" % calls[-1][2]["final_cost"])
+        outs = []
+        for _ in range(2):
+            ba, calls = replay(smap, interval=5, options=opt)
+            outs.append((ba.poses().copy(), ba.points().copy()))
+        same = np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+        print("   map replay:", len(calls), "calls, last cost %.6e, two replays %s" % (calls[-1][2]["final_cost"], "bit-identical" if same else "DIFFER"))
+        if not same:
+            raise SystemExit("run-to-run difference in the map replay")
         return
     w = pack_window(smap, 0, smap.num_frames)
-    p, x, s = Solver(0).solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r, options=opt)
-    print("   %s: cost %.6e -> %.6e, %d iterations" % (kind, s["initial_cost"], s["final_cost"], s["iterations"]))
+    runs = [Solver(0).solve(w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], smap.p_l, smap.p_r, options=opt) for _ in range(3)]
+    p, x, s = runs[0]
+    same = all(np.array_equal(r[0], p) and np.array_equal(r[1], x) and r[2]["final_cost"] == s["final_cost"] for r in runs[1:])
+    print("   %s: cost %.6e -> %.6e, %d iterations, three runs %s" % (kind, s["initial_cost"], s["final_cost"], s["iterations"],
+                                                                       "bit-identical" if same else "DIFFER"))
+    if not same:
+        raise SystemExit("run-to-run difference on path: " + kind)
 
 
 if __name__ == "__main__":

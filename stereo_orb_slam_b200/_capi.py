@@ -21,7 +21,7 @@ SYMBOLS = [
     "sba_pack_window", "sba_unpack_window", "sba_matrix_to_pose", "sba_pose_to_matrix",
     "sba_time_stage", "sba_invert_pose", "sba_normalize_pose", "sba_compose_pose", "sba_get_factor_symbolic", "sba_measure_fp64_peak",
     "sba_map_reset", "sba_map_append_frame", "sba_map_num_frames", "sba_map_num_points", "sba_map_optimize", "sba_map_get_poses",
-    "sba_map_set_pose", "sba_map_get_points", "sba_map_set_points", "sba_map_last_window",
+    "sba_map_set_pose", "sba_map_get_points", "sba_map_set_points", "sba_map_last_window", "sba_pgo_optimize",
 ]
 
 SBA_OK, SBA_NO_CONVERGENCE, SBA_NUMERICAL_FAILURE, SBA_INVALID_ARGUMENT, SBA_CUDA_ERROR, SBA_NCCL_ERROR = range(6)
@@ -53,6 +53,14 @@ class Summary(C.Structure):
         d = {f: getattr(self, f) for f, _ in self._fields_}
         d["termination_name"] = TERMINATION.get(d["termination"], str(d["termination"]))
         return d
+
+
+class PgoSummary(C.Structure):
+    _fields_ = [("initial_chi2", C.c_double), ("final_chi2", C.c_double), ("final_lambda", C.c_double), ("iterations", C.c_int32),
+                ("trials", C.c_int32), ("termination", C.c_int32), ("time_total_s", C.c_double), ("time_symbolic_s", C.c_double)]
+
+    def as_dict(self):
+        return {f: getattr(self, f) for f, _ in self._fields_}
 
 
 class SbaError(RuntimeError):

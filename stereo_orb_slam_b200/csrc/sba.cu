@@ -6,11 +6,13 @@
 // trust-region control.  The host only sequences launches and reads one counter per iteration.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <limits>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -19,6 +21,7 @@
 #include "kernels.cuh"
 #include "sba_comm.h"
 #include "sba_internal.h"
+#include "pgo.cuh"
 #include "sparse_chol.cuh"
 #include "sparse_chol.h"
 
@@ -249,6 +252,48 @@ int sba_set_point_shard(sba_handle h, int32_t pt_begin, int32_t pt_end) {
   return SBA_OK;
 }
 
+// Device side of a symbolic factorisation: index tables, L / Linv / y storage (through the handle's allocation list),
+// the chain-panel capacity and the cooperative grid of k_spchol.
+static int setup_spchol(sba_handle h, const SparseCholSymbolic& Y, SpCholDev* spo, size_t* smem, int* blocks) {
+  SpCholDev& sp = *spo;
+  int rc;
+  sp.n = Y.n; sp.nlev = Y.nlev; sp.nnzL = (int32_t)Y.nnzL();
+  if ((rc = h->upload(&sp.perm, Y.perm))) return rc;
+  if ((rc = h->upload(&sp.col_ptr, Y.col_ptr))) return rc;
+  if ((rc = h->upload(&sp.row_idx, Y.row_idx))) return rc;
+  if ((rc = h->upload(&sp.init_src, Y.init_src))) return rc;
+  if ((rc = h->upload(&sp.upd_ptr, Y.upd_ptr))) return rc;
+  if ((rc = h->upload(&sp.upd_ext_end, Y.upd_ext_end))) return rc;
+  if ((rc = h->upload(&sp.rowl_ext_end, Y.rowl_ext_end))) return rc;
+  if ((rc = h->upload(&sp.upd_a, Y.upd_a))) return rc;
+  if ((rc = h->upload(&sp.upd_b, Y.upd_b))) return rc;
+  if ((rc = h->upload(&sp.rowl_ptr, Y.rowl_ptr))) return rc;
+  if ((rc = h->upload(&sp.rowl_blk, Y.rowl_blk))) return rc;
+  if ((rc = h->upload(&sp.rowl_col, Y.rowl_col))) return rc;
+  if ((rc = h->upload(&sp.lvl_ptr, Y.lvl_ptr))) return rc;
+  if ((rc = h->upload(&sp.lvl_cols, Y.lvl_cols))) return rc;
+  if ((rc = h->upload(&sp.lvl_len, Y.lvl_len))) return rc;
+  if ((rc = h->alloc(&sp.Lv, (size_t)Y.nnzL() * 36))) return rc;
+  if ((rc = h->alloc(&sp.Li, (size_t)Y.n * 36))) return rc;
+  if ((rc = h->alloc(&sp.y, (size_t)Y.n * 6))) return rc;
+  // chains of up to panel_cap blocks are factored out of shared memory; size the launch for the largest that fits
+  int cap = 1;
+  for (size_t c = 0; c < Y.lvl_cols.size(); ++c) {
+    const int nb = Y.col_ptr[Y.lvl_cols[c] + Y.lvl_len[c]] - Y.col_ptr[Y.lvl_cols[c]];
+    if (nb <= kSpPanelMax && Y.lvl_len[c] <= kSpChainMax) cap = std::max(cap, nb);
+  }
+  sp.panel_cap = cap;
+  *smem = spchol_smem_bytes(cap);
+  // (the attribute is per function, not per launch: always the largest panel, so that handles and PGO calls with
+  // different capacities never lower it under each other)
+  CUDA_TRY(cudaFuncSetAttribute(k_spchol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)spchol_smem_bytes(kSpPanelMax)));
+  int per_sm = 0, sms = 0;
+  CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
+  CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_spchol, kSpThreads, *smem));
+  *blocks = std::min(per_sm, 1) * sms;
+  return SBA_OK;
+}
+
 int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const int32_t* obs_cam,
                       const int32_t* obs_pt, const uint8_t* cam_fixed, int32_t nwin,
                       const int32_t* win_cam_off, const int32_t* win_pt_off) {
@@ -454,41 +499,7 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   if (h->sym_ok && h->spchol_blocks > 0 && (!h->chol_ok || std::getenv("SBA_FORCE_SPARSE_CHOL"))) {
     {
       const SparseCholSymbolic& Y = h->sym;
-      SpCholDev& sp = h->sp;
-      sp.n = Y.n; sp.nlev = Y.nlev; sp.nnzL = (int32_t)Y.nnzL();
-      if ((rc = h->upload(&sp.perm, Y.perm))) return rc;
-      if ((rc = h->upload(&sp.col_ptr, Y.col_ptr))) return rc;
-      if ((rc = h->upload(&sp.row_idx, Y.row_idx))) return rc;
-      if ((rc = h->upload(&sp.init_src, Y.init_src))) return rc;
-      if ((rc = h->upload(&sp.upd_ptr, Y.upd_ptr))) return rc;
-      if ((rc = h->upload(&sp.upd_ext_end, Y.upd_ext_end))) return rc;
-      if ((rc = h->upload(&sp.rowl_ext_end, Y.rowl_ext_end))) return rc;
-      if ((rc = h->upload(&sp.upd_a, Y.upd_a))) return rc;
-      if ((rc = h->upload(&sp.upd_b, Y.upd_b))) return rc;
-      if ((rc = h->upload(&sp.rowl_ptr, Y.rowl_ptr))) return rc;
-      if ((rc = h->upload(&sp.rowl_blk, Y.rowl_blk))) return rc;
-      if ((rc = h->upload(&sp.rowl_col, Y.rowl_col))) return rc;
-      if ((rc = h->upload(&sp.lvl_ptr, Y.lvl_ptr))) return rc;
-      if ((rc = h->upload(&sp.lvl_cols, Y.lvl_cols))) return rc;
-      if ((rc = h->upload(&sp.lvl_len, Y.lvl_len))) return rc;
-      if ((rc = h->alloc(&sp.Lv, (size_t)Y.nnzL() * 36))) return rc;
-      if ((rc = h->alloc(&sp.Li, (size_t)Y.n * 36))) return rc;
-      if ((rc = h->alloc(&sp.y, (size_t)Y.n * 6))) return rc;
-      {
-        // chains of up to panel_cap blocks are factored out of shared memory; size the launch for the largest that fits
-        int cap = 1;
-        for (size_t c = 0; c < Y.lvl_cols.size(); ++c) {
-          const int nb = Y.col_ptr[Y.lvl_cols[c] + Y.lvl_len[c]] - Y.col_ptr[Y.lvl_cols[c]];
-          if (nb <= kSpPanelMax && Y.lvl_len[c] <= kSpChainMax) cap = std::max(cap, nb);
-        }
-        sp.panel_cap = cap;
-        h->spchol_smem = spchol_smem_bytes(cap);
-        CUDA_TRY(cudaFuncSetAttribute(k_spchol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spchol_smem));
-        int per_sm = 0, sms = 0;
-        CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
-        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_spchol, kSpThreads, h->spchol_smem));
-        h->spchol_blocks = std::min(per_sm, 1) * sms;
-      }
+      if ((rc = setup_spchol(h, Y, &h->sp, &h->spchol_smem, &h->spchol_blocks))) return rc;
       CUDA_TRY(cudaStreamSynchronize(h->stream));
       h->spchol_ok = h->spchol_blocks > 0;
       if (std::getenv("SBA_TIMING"))
@@ -1482,6 +1493,173 @@ int64_t sba_map_last_window(sba_handle h, uint32_t* point_ids, int64_t capacity,
   if (point_ids) std::memcpy(point_ids, M.ids.data(), (size_t)std::min<int64_t>(capacity, (int64_t)M.ids.size()) * 4);
   if (ms) { ms[0] = M.ms_pack; ms[1] = M.ms_structure; ms[2] = M.ms_upload; ms[3] = M.ms_solve; ms[4] = M.ms_unpack; }
   return (int64_t)M.ids.size();
+}
+
+// ---- pose-graph optimisation ----------------------------------------------------------
+static int pgo_run(sba_handle h, int32_t n, double* T_wc, int32_t m, const int32_t* edge_i, const int32_t* edge_j, const double* Z,
+                   const uint8_t* fixed, const double* information6, double huber_delta, int32_t iterations, sba_pgo_summary* out) {
+  using clk = std::chrono::steady_clock;
+  const auto t0 = clk::now();
+  int rc;
+  // ---- structure: free vertices, upper block pattern, partial lists (fixed summation order)
+  std::vector<int32_t> fv((size_t)n);
+  int32_t nf = 0;
+  for (int v = 0; v < n; ++v) fv[v] = ((fixed ? fixed[v] != 0 : v == 0)) ? -1 : nf++;
+  if (nf == 0 || m == 0) return SBA_OK;
+  std::vector<int64_t> keys;
+  keys.reserve((size_t)nf + m);
+  for (int f = 0; f < nf; ++f) keys.push_back((int64_t)f * nf + f);
+  for (int k = 0; k < m; ++k) {
+    const int32_t i = edge_i[k], j = edge_j[k];
+    if (i < 0 || j < 0 || i >= n || j >= n || i == j) { set_error("sba_pgo_optimize: bad edge"); return SBA_INVALID_ARGUMENT; }
+    const int64_t a = fv[i], b = fv[j];
+    if (a >= 0 && b >= 0) keys.push_back(std::min(a, b) * nf + std::max(a, b));
+  }
+  std::sort(keys.begin(), keys.end());
+  keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
+  const int32_t nbu = (int32_t)keys.size();
+  std::vector<int32_t> blk_row(nbu), blk_col(nbu);
+  for (int b = 0; b < nbu; ++b) { blk_row[b] = (int32_t)(keys[b] / nf); blk_col[b] = (int32_t)(keys[b] % nf); }
+  auto blk_of = [&](int64_t r, int64_t c) { return (int32_t)(std::lower_bound(keys.begin(), keys.end(), r * nf + c) - keys.begin()); };
+  std::vector<std::vector<int32_t>> bl((size_t)nbu), vl((size_t)nf);
+  for (int k = 0; k < m; ++k) {
+    const int64_t a = fv[edge_i[k]], b = fv[edge_j[k]];
+    if (a >= 0) { bl[blk_of(a, a)].push_back(k * 4 + 0); vl[a].push_back(k * 2 + 0); }
+    if (b >= 0) { bl[blk_of(b, b)].push_back(k * 4 + 1); vl[b].push_back(k * 2 + 1); }
+    if (a >= 0 && b >= 0) bl[blk_of(std::min(a, b), std::max(a, b))].push_back(k * 4 + (a < b ? 2 : 3));
+  }
+  std::vector<int32_t> bpo((size_t)nbu + 1, 0), bp, vpo((size_t)nf + 1, 0), vp;
+  for (int b = 0; b < nbu; ++b) { bpo[b + 1] = bpo[b] + (int32_t)bl[b].size(); bp.insert(bp.end(), bl[b].begin(), bl[b].end()); }
+  for (int f = 0; f < nf; ++f) { vpo[f + 1] = vpo[f] + (int32_t)vl[f].size(); vp.insert(vp.end(), vl[f].begin(), vl[f].end()); }
+  SparseCholSymbolic Y;
+  const auto ts = clk::now();
+  const std::string serr = sparse_chol_symbolic(nf, blk_row, blk_col, (int64_t)256 << 20, &Y);
+  if (!serr.empty()) { set_error("sba_pgo_optimize: " + serr); return SBA_INVALID_ARGUMENT; }
+  out->time_symbolic_s = std::chrono::duration<double>(clk::now() - ts).count();
+  // ---- device state
+  std::vector<double> X((size_t)n * 12), Zc((size_t)m * 12);
+  auto to12 = [](const double* T, double* o) {
+    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) o[3 * r + c] = T[4 * r + c]; o[9 + r] = T[4 * r + 3]; }
+  };
+  for (int v = 0; v < n; ++v) to12(T_wc + (size_t)v * 16, &X[(size_t)v * 12]);
+  for (int k = 0; k < m; ++k) to12(Z + (size_t)k * 16, &Zc[(size_t)k * 12]);
+  std::vector<int32_t> ei(edge_i, edge_i + m), ej(edge_j, edge_j + m);
+  PgoDev g{};
+  g.n = n; g.nf = nf; g.m = m; g.nbu = nbu; g.huber_delta = huber_delta;
+  static const double ref_info[6] = {0.01, 0.01, 0.01, 1.0, 1.0, 1.0};      // src/pose_graph_optimizer.cpp:23-26
+  for (int a = 0; a < 6; ++a) g.info[a] = information6 ? information6[a] : ref_info[a];
+  if ((rc = h->upload(&g.fv, fv))) return rc;
+  if ((rc = h->upload(&g.ei, ei))) return rc;
+  if ((rc = h->upload(&g.ej, ej))) return rc;
+  if ((rc = h->upload(&g.Z, Zc))) return rc;
+  { const double* xp = nullptr; if ((rc = h->upload(&xp, X))) return rc; g.X = const_cast<double*>(xp); }
+  if ((rc = h->upload(&g.blk_part_off, bpo))) return rc;
+  if ((rc = h->upload(&g.blk_part, bp))) return rc;
+  if ((rc = h->upload(&g.vtx_part_off, vpo))) return rc;
+  if ((rc = h->upload(&g.vtx_part, vp))) return rc;
+  if ((rc = h->upload(&g.blk_row, blk_row))) return rc;
+  if ((rc = h->upload(&g.blk_col, blk_col))) return rc;
+  if ((rc = h->alloc(&g.Xn, (size_t)n * 12))) return rc;
+  if ((rc = h->alloc(&g.epart, (size_t)m * 120))) return rc;
+  if ((rc = h->alloc(&g.echi, (size_t)m))) return rc;
+  if ((rc = h->alloc(&g.H0, (size_t)nbu * 36))) return rc;
+  if ((rc = h->alloc(&g.b0, (size_t)nf * 6))) return rc;
+  if ((rc = h->alloc(&g.Su, (size_t)nbu * 36))) return rc;
+  if ((rc = h->alloc(&g.rhs, (size_t)nf * 6))) return rc;
+  if ((rc = h->alloc(&g.x, (size_t)nf * 6))) return rc;
+  if ((rc = h->alloc(&g.red, 4))) return rc;
+  // the factorisation kernel sees the system through a Dev: one window, every column in it
+  Dev dd{};
+  dd.nwin = 1; dd.Nf = nf; dd.nbu = nbu; dd.Su = g.Su; dd.rhs = g.rhs; dd.x = g.x;
+  int32_t* flags = nullptr; int32_t* fwin = nullptr;
+  if ((rc = h->alloc(&dd.r, (size_t)nf * 6))) return rc;
+  if ((rc = h->alloc(&flags, 4))) return rc;
+  if ((rc = h->alloc(&fwin, (size_t)nf))) return rc;
+  CUDA_TRY(cudaMemsetAsync(flags, 0, 16, h->stream));
+  CUDA_TRY(cudaMemsetAsync(fwin, 0, (size_t)nf * 4, h->stream));
+  dd.w_status = flags; dd.w_fail = flags + 1; dd.w_pcg_it = flags + 2; dd.fcam_win = fwin;
+  SpCholDev sp{}; size_t sp_smem = 0; int sp_blocks = 0;
+  if ((rc = setup_spchol(h, Y, &sp, &sp_smem, &sp_blocks))) return rc;
+  if (sp_blocks <= 0) { set_error("sba_pgo_optimize: cooperative launch unavailable"); return SBA_CUDA_ERROR; }
+  CUDA_TRY(cudaStreamSynchronize(h->stream));          // the host vectors above are locals
+  auto read_red = [&](double* r3) -> int {
+    CUDA_TRY(cudaMemcpyAsync(r3, g.red, 24, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return SBA_OK;
+  };
+  const int ge = cdiv(m, 128), gv = cdiv(n, 128);
+  // ---- g2o OptimizationAlgorithmLevenberg restated (oracle/pgo_oracle.py optimize)
+  double lambda = -1.0, ni = 2.0, cur = 0.0, red[3];
+  for (int it = 0; it < iterations; ++it) {
+    LAUNCH(h, k_pgo_linearize, ge, 128, g);
+    LAUNCH(h, k_pgo_assemble, nbu + nf, 64, g);
+    LAUNCH(h, k_pgo_reduce, 1, 256, g, 0.0);
+    if ((rc = read_red(red))) return rc;
+    cur = red[0];
+    if (it == 0) out->initial_chi2 = cur;
+    if (lambda < 0.0) lambda = 1e-5 * std::max(red[2], 0.0);
+    double rho = 0.0;
+    int qmax = 0;
+    do {
+      LAUNCH(h, k_pgo_damp, cdiv(std::max((int64_t)nbu * 36, (int64_t)nf * 6), 256), 256, g, lambda);
+      CUDA_TRY(cudaMemsetAsync(flags + 1, 0, 4, h->stream));
+      { Dev d2 = dd; SpCholDev s2 = sp; void* args[] = {&d2, &s2};
+        CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_spchol, dim3(sp_blocks), dim3(kSpThreads), args, sp_smem, h->stream)); h->launches++; }
+      LAUNCH(h, k_pgo_update, gv, 128, g);
+      LAUNCH(h, k_pgo_chi2, ge, 128, g);
+      LAUNCH(h, k_pgo_reduce, 1, 256, g, lambda);
+      int32_t failed = 0;
+      CUDA_TRY(cudaMemcpyAsync(&failed, flags + 1, 4, cudaMemcpyDeviceToHost, h->stream));
+      if ((rc = read_red(red))) return rc;
+      const double tmp = (failed || !std::isfinite(red[0])) ? std::numeric_limits<double>::infinity() : red[0];
+      const double scale = red[1] + 1e-3;
+      rho = (cur - tmp) / scale;
+      out->trials++;
+      if (rho > 0.0 && std::isfinite(tmp)) {
+        const double t = 2.0 * rho - 1.0;
+        const double alpha = std::min(1.0 - t * t * t, 2.0 / 3.0);
+        lambda *= std::max(1.0 / 3.0, alpha); ni = 2.0;
+        cur = tmp;
+        LAUNCH(h, k_pgo_accept, cdiv((int64_t)n * 12, 256), 256, g);
+      } else {
+        lambda *= ni; ni *= 2.0;
+        if (!std::isfinite(lambda)) break;
+      }
+      ++qmax;
+    } while (rho < 0.0 && qmax < 10);
+    out->iterations = it + 1;
+    if (qmax == 10 || rho == 0.0 || !std::isfinite(lambda)) { out->termination = 1; break; }
+  }
+  out->final_chi2 = cur; out->final_lambda = lambda;
+  CUDA_TRY(cudaMemcpyAsync(X.data(), g.X, X.size() * 8, cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  for (int v = 0; v < n; ++v) {
+    double* T = T_wc + (size_t)v * 16; const double* o = &X[(size_t)v * 12];
+    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) T[4 * r + c] = o[3 * r + c]; T[4 * r + 3] = o[9 + r]; }
+    T[12] = T[13] = T[14] = 0.0; T[15] = 1.0;
+  }
+  out->time_total_s = std::chrono::duration<double>(clk::now() - t0).count();
+  return SBA_OK;
+}
+
+int sba_pgo_optimize(sba_handle h, int32_t num_vertices, double* T_wc, int32_t num_edges, const int32_t* edge_i, const int32_t* edge_j,
+                     const double* Z, const uint8_t* fixed, const double* information6, double huber_delta, int32_t iterations,
+                     sba_pgo_summary* summary) {
+  if (!h || num_vertices < 0 || num_edges < 0 || (num_vertices > 0 && !T_wc) || (num_edges > 0 && (!edge_i || !edge_j || !Z)) ||
+      !(huber_delta > 0.0) || iterations < 0) { set_error("sba_pgo_optimize: bad arguments"); return SBA_INVALID_ARGUMENT; }
+  if (h->device < 0) { set_error("host-only handle: no CUDA device bound (there is no CPU fallback)"); return SBA_CUDA_ERROR; }
+  sba_pgo_summary S; std::memset(&S, 0, sizeof(S));
+  CUDA_TRY(cudaSetDevice(h->device));
+  // the graph's buffers live in their own allocation list, released when the call returns (the BA structure of the
+  // handle, if any, is untouched)
+  std::vector<void*> keep;
+  keep.swap(h->allocs);
+  const int rc = pgo_run(h, num_vertices, T_wc, num_edges, edge_i, edge_j, Z, fixed, information6, huber_delta, iterations, &S);
+  for (void* p : h->allocs) cudaFreeAsync(p, h->stream);
+  cudaStreamSynchronize(h->stream);
+  h->allocs.swap(keep);
+  if (summary) *summary = S;
+  return rc;
 }
 
 // ---- multi-GPU --------------------------------------------------------------------------------------

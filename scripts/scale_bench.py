@@ -66,7 +66,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    opt = default_options(max_time_s=0.0, max_iterations=args.iters)
+    opt = default_options(max_time_s=0.0, max_iterations=args.iters, verbose=1 if os.environ.get("SCALE_VERBOSE") else 0)
     sv = Solver(local)
     if args.mode == "C3":
         lo, hi = shard_windows(args.windows, world)[rank]

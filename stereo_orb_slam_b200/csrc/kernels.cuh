@@ -2557,6 +2557,8 @@ __global__ void __launch_bounds__(kThreads) k_backsub(Dev d, DevParams P) { dev_
 
 // one CTA per window: the step scalars (cameras + point chunk partials) and the line-search start state.
 // (multi-GPU: camera terms are counted on rank 0 only; the scalars are all-reduced afterwards)
+__device__ __forceinline__ void cam_step_finish(const Dev& d, int w, double (&part)[4], double dmax, double* sm, double* smx);
+
 __device__ __forceinline__ void dev_cam_step(const Dev& d, int w, int rank) {
   __shared__ double sm[4 * 4];
   __shared__ double smx[4];
@@ -2600,6 +2602,11 @@ __device__ __forceinline__ void dev_cam_step(const Dev& d, int w, int rank) {
       part[0] += va.x; part[1] += va.y; part[2] += vb.x; dmax = fmax(dmax, vb.y);
     }
   }
+  cam_step_finish(d, w, part, dmax, sm, smx);
+}
+
+// the window's step scalars from per-thread partials (fixed order: block tree), and the line-search start state
+__device__ __forceinline__ void cam_step_finish(const Dev& d, int w, double (&part)[4], double dmax, double* sm, double* smx) {
   double tot = block_sum<4>(part, sm);
   const double mx = block_max1(dmax, smx);
   if (threadIdx.x == 0 && d.w_fail[w] != 0) tot = nan("");   // poison the model change: invalid step on every rank
@@ -2918,31 +2925,129 @@ __global__ void k_apply_cams(Dev d) { dev_apply_cam(d, blockIdx.x * blockDim.x +
 // is still searching, then accepted candidates become the state.  Replaces 5 launches, a memset and a host round
 // trip per line-search round.  The searching counter alternates between counters[3] and [5] so that resetting
 // one never races with reading the other; counters[6] returns the number of rounds.
+// ---- one global window (thousands of cameras, 10^4..10^5 chunks): the window's reductions in two levels.  Every CTA of
+// the step loop first sums the rows it produced itself (chunk order) and its slice of the cameras into one row of
+// `cta_part`; the window's CTA then adds a few hundred rows instead of walking 10^5 chunk partials alone.
+//   row layout: [0..2] chunk g.dp, dp D dp, |x|^2  [3] chunk max|dp|  [4..7] camera g.d, d D d, |x|^2, dc.r  [8] camera max|dc|
+//               [9..11] trial cost, directional derivative, |x_trial - x|^2 (points)  [12] |x_trial - x|^2 (cameras)
+__device__ __forceinline__ void dev_step_partials_one(const Dev& d, int nb) {
+  __shared__ double sm[4 * 4];
+  __shared__ double smx[4];
+  double* row = d.cta_part + (size_t)blockIdx.x * 16;
+  if (threadIdx.x < 4) {
+    double a = 0.0;
+    for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) {
+      const double v = __ldcg(d.step_part + (size_t)ch * 4 + threadIdx.x);
+      a = (threadIdx.x < 3) ? a + v : fmax(a, v);
+    }
+    row[threadIdx.x] = a;
+  }
+  double part[4] = {0, 0, 0, 0};
+  double dmax = 0.0;
+  const double radius = d.w_radius[0];
+  for (int c = blockIdx.x * kThreads + threadIdx.x; c < d.Nc; c += nb * kThreads) {
+    const int f = d.fc[c];
+    if (f < 0) continue;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      const double x = d.poses[(size_t)c * 6 + i];
+      const double dc = d.x[(size_t)f * 6 + i];
+      dmax = fmax(dmax, fabs(dc));
+      part[0] += d.gc[(size_t)c * 6 + i] * dc;
+      part[1] += lm_damp(d.sc2c[(size_t)c * 6 + i], d.U[(size_t)c * 21 + up6(i, i)], radius) * dc * dc;
+      part[2] += x * x;
+      part[3] += dc * d.r[(size_t)f * 6 + i];
+    }
+  }
+  const double tot = block_sum<4>(part, sm);
+  const double mx = block_max1(dmax, smx);
+  if (threadIdx.x < 4) row[4 + threadIdx.x] = tot;
+  if (threadIdx.x == 4) row[8] = mx;
+}
+
+__device__ __forceinline__ void dev_cam_step_one(const Dev& d, int nb) {
+  __shared__ double sm[4 * 4];
+  __shared__ double smx[4];
+  double part[4] = {0, 0, 0, 0};
+  double dmax = 0.0;
+  for (int r = threadIdx.x; r < nb; r += kThreads) {
+    const double* row = d.cta_part + (size_t)r * 16;
+    part[0] += __ldcg(row + 4) + __ldcg(row); part[1] += __ldcg(row + 5) + __ldcg(row + 1); part[2] += __ldcg(row + 6) + __ldcg(row + 2);
+    part[3] += __ldcg(row + 7);
+    dmax = fmax(dmax, fmax(__ldcg(row + 3), __ldcg(row + 8)));
+  }
+  cam_step_finish(d, 0, part, dmax, sm, smx);
+}
+
+__device__ __forceinline__ void dev_ls_partials_one(const Dev& d, int nb, double cam2) {
+  __shared__ double sm[4];
+  double* row = d.cta_part + (size_t)blockIdx.x * 16;
+  if (threadIdx.x < 3) {
+    double a = 0.0;
+    for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) a += __ldcg(d.ls_part + (size_t)ch * 3 + threadIdx.x);
+    row[9 + threadIdx.x] = a;
+  }
+  double c2[1] = {cam2};
+  const double tot = block_sum<1>(c2, sm);
+  if (threadIdx.x == 0) row[12] = tot;
+}
+
+__device__ __forceinline__ void dev_ls_reduce_one(const Dev& d, int nb) {
+  __shared__ double sm[4 * 3];
+  const int st = __ldcg(d.w_ls_state);
+  if (st < 1 || st > 3) return;
+  double part[3] = {0, 0, 0};
+  for (int r = threadIdx.x; r < nb; r += kThreads) {
+    const double* row = d.cta_part + (size_t)r * 16;
+    part[0] += __ldcg(row + 9); part[1] += __ldcg(row + 10); part[2] += __ldcg(row + 11) + __ldcg(row + 12);
+  }
+  const double tot = block_sum<3>(part, sm);
+  if (threadIdx.x < 3) d.w_ls_red[(size_t)threadIdx.x * d.nwin] = tot;
+}
+
 __global__ void __launch_bounds__(kThreads) k_step_loop(Dev d, DevParams P, int fused_cams) {
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
   const int nb = gridDim.x;
+  const bool one = d.nwin == 1 && d.npchunk > 4 * nb;      // one global window: two-level reductions
   // P.debug == 2 (SBA_DEBUG_LS=2): block 0 prints the nanoseconds spent in each phase (tuning aid)
   const bool prof = P.debug == 2 && blockIdx.x == 0 && threadIdx.x == 0;
   unsigned long long t0 = prof ? gtimer() : 0, tp[6] = {0, 0, 0, 0, 0, 0};
   auto lap = [&](int k) { if (prof) { const unsigned long long t = gtimer(); tp[k] += t - t0; t0 = t; } };
   for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) { dev_backsub(d, P, ch); __syncthreads(); }
   if (blockIdx.x == 0 && threadIdx.x == 0) { d.counters[0] = 0; d.counters[2] = 0; d.counters[3] = 0; d.counters[5] = 0; }
+  if (one) dev_step_partials_one(d, nb);
   grid.sync();
   lap(0);
-  for (int w = blockIdx.x; w < d.nwin; w += nb) { dev_cam_step(d, w, 0); __syncthreads(); }
+  if (one) { if (blockIdx.x == 0) dev_cam_step_one(d, nb); }
+  else for (int w = blockIdx.x; w < d.nwin; w += nb) { dev_cam_step(d, w, 0); __syncthreads(); }
   grid.sync();
   lap(1);
   int round = 0;
   for (;;) {
     int32_t* cnt = d.counters + ((round & 1) ? 5 : 3);
     int32_t* other = d.counters + ((round & 1) ? 3 : 5);
-    for (int c = blockIdx.x * kThreads + threadIdx.x; c < d.Nc; c += nb * kThreads) dev_trial_cam(d, c);
+    double cam2 = 0.0;
+    for (int c = blockIdx.x * kThreads + threadIdx.x; c < d.Nc; c += nb * kThreads) {
+      dev_trial_cam(d, c);
+      if (one) {           // this thread's share of |x_trial - x|^2 over the cameras (it wrote poses_new[c] itself)
+#pragma unroll
+        for (int i = 0; i < 6; ++i) { const double dd = __ldcg(d.poses_new + (size_t)c * 6 + i) - d.poses[(size_t)c * 6 + i]; cam2 += dd * dd; }
+      }
+    }
     if (!fused_cams) grid.sync();         // the chunks read campre_new only when one of them has too many cameras to stage
     lap(2);
     for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) { dev_trial_points(d, P, ch); __syncthreads(); }
+    if (one) dev_ls_partials_one(d, nb, cam2);
     grid.sync();
     lap(3);
     if (blockIdx.x == 0 && threadIdx.x == 0) *other = 0;
+    if (one) {
+      if (blockIdx.x == 0) {
+        dev_ls_reduce_one(d, nb);
+        __syncthreads();
+        if (threadIdx.x == 0) { dev_ls_control(d, P, 0, cnt); dev_lm_control(d, P, 0); }
+      }
+    } else
     for (int w = blockIdx.x; w < d.nwin; w += nb) {
       dev_ls_reduce(d, w, 0);
       __syncthreads();

@@ -67,6 +67,8 @@ struct Dev {
   double *dp;                    // [Np*3] point step (back-substitution)
   double *step_part;             // [npchunk*4]  g.dp, dp D dp, |x|^2, max|dp|
   double *ls_part;               // [npchunk*3]  trial cost, directional derivative, |x_trial - x|^2
+  double *cta_part;              // [step-loop CTAs * 16] one global window: per-CTA partials of the rows above and of the
+                                 //   camera terms, so that the window's reductions sum a few hundred rows, not 10^5
   // ---- per-window scalars [nwin]
   double *w_radius, *w_decf, *w_cost, *w_cand, *w_gmax;
   double *w_gd, *w_dDd, *w_dr, *w_x2;     // one block [4*nwin] (all-reduced together on multi-GPU)

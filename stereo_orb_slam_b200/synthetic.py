@@ -233,7 +233,10 @@ CONFIGS = {
     "C2": dict(num_frames=50, num_points=40000, track_len=7, seed=0xBA00 + 1),
     "C3": dict(num_frames=10, num_points=5000, track_len=8, seed=0xBA00 + 2),   # per window: seed + window id
     "C4": dict(num_frames=4541, num_points=1000000, track_len=7, seed=0xBA00 + 3, loop=True, loop_frames=40),
-    "C5": dict(num_frames=20000, num_points=5000000, track_len=7, seed=0xBA00 + 4),
+    # 20 000 frames at ~1 m per frame: a straight open chain would leave the reference's +-1e4 m point box
+    # (src/params.h:44,47) and half the map would be clamped at iteration 0 (round 1's "C5 does not converge"); the path
+    # is one wide circuit (radius ~3.2 km) WITHOUT loop-closure observations — still an open chain as a graph.
+    "C5": dict(num_frames=20000, num_points=5000000, track_len=7, seed=0xBA00 + 4, loop=True, loop_frames=0),
 }
 
 

@@ -401,6 +401,25 @@ def run_ours(args):
                                         "sliding window Optimize(n-20, n) every 10 frames (src/slam.cpp:122-129), device-resident map",
                                 "per_frame_call_ms_median": float(np.median(lat["frame"])), "per_frame_call_ms_max": float(np.max(lat["frame"])),
                                 "sliding_window_call_ms_median": float(np.median(lat["window"])), "calls": len(lat["frame"]) + len(lat["window"])}
+    if rank == 0 and world == 1:
+        # ---- N4: the stereo RANSAC alignment that precedes BA (src/visual_odometer.cpp:93-103), one frame pair of 500
+        #      matches through the C-ABI with host buffers; wall clock per call
+        from stereo_orb_slam_b200 import StereoRansac, GlibcRand, synthetic
+        pairs, _, bad, P_l, P_r = synthetic.make_stereo_pairs(500, 1)
+        rs = StereoRansac(P_l, P_r, solver=sv2)
+        S = GlibcRand(1).draws(100, 500)
+        for _ in range(5):
+            rs.Solve(pairs, samples=S)
+        ts = []
+        for _ in range(50):
+            t0 = time.perf_counter(); rs.Solve(pairs, samples=S); ts.append(time.perf_counter() - t0)
+        line["ransac"] = {"what": "sba_ransac_stereo: 500 temporal matches, 100 hypotheses (3-point Umeyama on DLT-triangulated points, 4-term "
+                                  "reprojection test < 3 px), host buffers", "ms_per_call_median": 1e3 * float(np.median(ts)),
+                          "inlier_tests_per_s": 100 * 500 / float(np.median(ts)), "kernels_per_call": 3}
+        if not args.no_cpu:
+            from oracle import ransac_oracle
+            t0 = time.perf_counter(); ransac_oracle.solve(pairs[:, 0], pairs[:, 1], P_l, P_r, S); dt = time.perf_counter() - t0
+            line["ransac"]["cpu_port_ms"] = 1e3 * dt
     if rank == 0 and world == 1 and not args.no_cpu:
         from oracle import oracle
         cores = oracle.num_procs()

@@ -232,6 +232,39 @@ int sba_pgo_optimize(sba_handle h, int32_t num_vertices, double* T_wc, int32_t n
                      const double* Z, const uint8_t* fixed, const double* information6, double huber_delta, int32_t iterations,
                      sba_pgo_summary* summary);
 
+/* ---- N4: stereo RANSAC rigid alignment ---------------------------------------------------------- */
+/* Replaces RANSAC::Solver<ObservationPair, Eigen::Matrix4f>::Solve over StereoTransModel
+ * (ransac_solver/include/ransac_solver.h:51-166; ransac_solver/include/stereo_reprojection.h:28-134), which
+ * VisualOdometer::CalcTransformation (src/visual_odometer.cpp:93-103) calls once per frame and the loop closer once
+ * per candidate (src/pose_graph_optimizer.cpp:189).  Options = RANSAC::Option (ransac_solver.h:13-19) with the values
+ * src/params.h:18-27 sets, plus the model's pixel threshold (stereo_reprojection.h:126). */
+typedef struct sba_ransac_options {
+  int32_t max_iterations;        /* 100 */
+  int32_t final_model_fitting;   /* 0 */
+  int32_t early_termination;     /* 0 */
+  float   concensus_ratio;       /* 0.8 (the reference's spelling) */
+  float   inlier_threshold;      /* 3.0 px on sqrt(du_l^2 + dv_l^2 + du_r^2 + dv_r^2) */
+} sba_ransac_options;
+void sba_ransac_default_options(sba_ransac_options* o);
+/* num_problems independent alignments in one call; problem b owns elements [offsets[b], offsets[b+1]).
+ *   obs_first / obs_second [n*4] f32 (u_l, v_l, u_r, v_r) = ObservationPair::first / ::second: the model maps the
+ *     points triangulated from `first` onto those from `second`
+ *   P_l / P_r [12] f32 row-major 3x4 projection matrices (StereoTransModel::SetCameraParams)
+ *   samples [num_problems * max_iterations * 3] i32 element indices local to the problem: the three draws
+ *     `rand() % size` of every iteration (ransac_solver.h:84-90), made by the caller so that its generator — the
+ *     reference's rand() included — reproduces; NULL = a counter-based draw from `seed`
+ * Outputs: T [num_problems*16] f32 row-major (Solve's return value), labels [n] u8 and losses [n] f32 (its `labels`
+ * / `losses` out-parameters); optional best_iteration [num_problems] and counts [num_problems*max_iterations]
+ * (inlier count of every hypothesis; -1 = not run because of early termination).
+ * Element weights are not an argument: the reference's models ignore them.  A problem with no elements gets T = 0.
+ * CalcTransformation's "fewer than 10 pairs -> false" guard belongs to the caller. */
+int sba_ransac_stereo(sba_handle h, int32_t num_problems, const int64_t* offsets, const float* obs_first, const float* obs_second,
+                      const float* P_l, const float* P_r, const sba_ransac_options* options, const int32_t* samples, uint64_t seed,
+                      float* T, uint8_t* labels, float* losses, int32_t* best_iteration, int32_t* counts);
+/* triangulated points of the last sba_ransac_stereo call's inputs are not kept; this evaluates cv::triangulatePoints
+ * + division by w (stereo_reprojection.h:79-92) for n stereo observations: xyz [n*3] f32 */
+int sba_triangulate_stereo(sba_handle h, int64_t n, const float* obs, const float* P_l, const float* P_r, float* xyz);
+
 /* ---- host side of BundleAdjuster::Optimize ------------------------------------------------------ */
 /* Pack window [start,end) of a map (reference: src/bundle_adjuster.cpp:41-110).
  *   T_wc [N*16] f32 row-major world-from-camera (Frame::GlobalPose), map_points [M*3] f32,

@@ -9,5 +9,6 @@ from .solver import Solver  # noqa: F401
 from .bundle_adjuster import BundleAdjuster, pack_window, unpack_window, matrix_to_pose, pose_to_matrix  # noqa: F401
 from .device_map import ResidentBundleAdjuster, replay  # noqa: F401
 from .pose_graph import optimize_pose_graph, odometry_graph  # noqa: F401
+from .ransac import RansacOption, StereoRansac, CalcTransformation, GlibcRand, triangulate_stereo  # noqa: F401
 from . import synthetic  # noqa: F401
 from . import dump_io  # noqa: F401

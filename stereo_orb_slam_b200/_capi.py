@@ -22,6 +22,7 @@ SYMBOLS = [
     "sba_time_stage", "sba_invert_pose", "sba_normalize_pose", "sba_compose_pose", "sba_get_factor_symbolic", "sba_measure_fp64_peak",
     "sba_map_reset", "sba_map_append_frame", "sba_map_num_frames", "sba_map_num_points", "sba_map_optimize", "sba_map_get_poses",
     "sba_map_set_pose", "sba_map_get_points", "sba_map_set_points", "sba_map_last_window", "sba_pgo_optimize",
+    "sba_ransac_default_options", "sba_ransac_stereo", "sba_triangulate_stereo",
 ]
 
 SBA_OK, SBA_NO_CONVERGENCE, SBA_NUMERICAL_FAILURE, SBA_INVALID_ARGUMENT, SBA_CUDA_ERROR, SBA_NCCL_ERROR = range(6)
@@ -63,6 +64,12 @@ class PgoSummary(C.Structure):
         return {f: getattr(self, f) for f, _ in self._fields_}
 
 
+class RansacOptions(C.Structure):
+    """sba_ransac_options = RANSAC::Option (ransac_solver/include/ransac_solver.h:13-19) + the model's pixel threshold."""
+    _fields_ = [("max_iterations", C.c_int32), ("final_model_fitting", C.c_int32), ("early_termination", C.c_int32),
+                ("concensus_ratio", C.c_float), ("inlier_threshold", C.c_float)]
+
+
 class SbaError(RuntimeError):
     def __init__(self, status, msg):
         super().__init__("libsba: status %d (%s): %s" % (status, msg[0], msg[1]))
@@ -87,6 +94,7 @@ def lib():
             getattr(L, f).restype = C.c_int64
         L.sba_destroy.restype = None
         L.sba_default_options.restype = None
+        L.sba_ransac_default_options.restype = None
         L.sba_matrix_to_pose.restype = None
         L.sba_pose_to_matrix.restype = None
         L.sba_normalize_pose.restype = None

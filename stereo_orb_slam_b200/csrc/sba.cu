@@ -22,6 +22,7 @@
 #include "sba_comm.h"
 #include "sba_internal.h"
 #include "pgo.cuh"
+#include "ransac.cuh"
 #include "sparse_chol.cuh"
 #include "sparse_chol.h"
 
@@ -86,6 +87,7 @@ struct sba_handle_s {
   int step_launches = 0;
   cudaGraphExec_t step_graph = nullptr;   // one K1-K3 step (stage 8) captured once per structure: a single launch per step
   int32_t* h_counters = nullptr;      // pinned
+  uint8_t* stage = nullptr; size_t stage_bytes = 0;   // pinned staging of sba_ransac_stereo (grown on demand)
   int64_t launches = 0;
   int64_t nobs_all = 0;
   sba::Comm comm;                     // NCCL (multi-GPU), inactive on 1 GPU
@@ -238,6 +240,7 @@ void sba_destroy(sba_handle h) {
     if (h->pool) cudaMemPoolDestroy(h->pool);
     for (int i = 0; i < 8; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     if (h->h_counters) cudaFreeHost(h->h_counters);
+    if (h->stage) cudaFreeHost(h->stage);
     if (h->side) cudaStreamDestroy(h->side);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
@@ -1660,6 +1663,135 @@ int sba_pgo_optimize(sba_handle h, int32_t num_vertices, double* T_wc, int32_t n
   cudaStreamSynchronize(h->stream);
   h->allocs.swap(keep);
   if (summary) *summary = S;
+  return rc;
+}
+
+// ---- N4: stereo RANSAC alignment (ransac.cuh) --------------------------------------------------------
+void sba_ransac_default_options(sba_ransac_options* o) {
+  if (!o) return;
+  o->max_iterations = 100;          // src/params.h:27
+  o->final_model_fitting = 0;       // :18
+  o->early_termination = 0;         // :21
+  o->concensus_ratio = 0.8f;        // :24
+  o->inlier_threshold = 3.0f;       // ransac_solver/include/stereo_reprojection.h:126
+}
+
+static int ransac_run(sba_handle h, int32_t nprob, const int64_t* off, const float* a, const float* b, const float* P_l, const float* P_r,
+                      const sba_ransac_options& o, const int32_t* samples, uint64_t seed, float* T, uint8_t* labels, float* losses,
+                      int32_t* best_it, int32_t* counts) {
+  int rc;
+  const int64_t n = off[nprob];
+  const int iters = o.max_iterations;
+  const size_t nh = (size_t)nprob * std::max(iters, 1);
+  RansacDev d{};
+  d.nprob = nprob; d.iters = iters; d.seed = seed; d.thr_px = o.inlier_threshold; d.ratio = o.concensus_ratio;
+  d.final_fit = o.final_model_fitting ? 1 : 0; d.early = o.early_termination ? 1 : 0;
+  std::memcpy(d.Pl, P_l, 48); std::memcpy(d.Pr, P_r, 48);
+  // one device arena, one packed upload, one packed download: a single frame pair (the visual odometer's call) is
+  // latency-bound, every separate allocation / copy costs more than the kernels
+  auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
+  const bool have_s = samples && iters > 0;
+  const size_t in_a = 0, in_b = in_a + (size_t)n * 16, in_off = in_b + (size_t)n * 16, in_s = up16(in_off + ((size_t)nprob + 1) * 8);
+  const size_t in_bytes = up16(in_s + (have_s ? nh * 12 : 0));
+  const size_t o_T = 0, o_loss = o_T + (size_t)nprob * 64, o_best = up16(o_loss + (size_t)n * 4), o_cnt = up16(o_best + (size_t)nprob * 4);
+  const size_t o_lab = up16(o_cnt + nh * 4), out_bytes = up16(o_lab + (size_t)n);
+  const size_t w_src = in_bytes + out_bytes, w_dst = w_src + (size_t)n * 16, w_T = w_dst + (size_t)n * 16, total = w_T + nh * 48;
+  uint8_t* arena = nullptr;
+  if ((rc = h->alloc(&arena, total))) return rc;
+  if (h->stage_bytes < std::max(in_bytes, out_bytes)) {
+    if (h->stage) cudaFreeHost(h->stage);
+    h->stage = nullptr; h->stage_bytes = 0;
+    const size_t want = std::max<size_t>(std::max(in_bytes, out_bytes) * 2, 1 << 16);
+    CUDA_TRY(cudaMallocHost((void**)&h->stage, want));
+    h->stage_bytes = want;
+  }
+  uint8_t* hs = h->stage;
+  if (n > 0) { std::memcpy(hs + in_a, a, (size_t)n * 16); std::memcpy(hs + in_b, b, (size_t)n * 16); }
+  std::memcpy(hs + in_off, off, ((size_t)nprob + 1) * 8);
+  if (have_s) std::memcpy(hs + in_s, samples, nh * 12);
+  CUDA_TRY(cudaMemcpyAsync(arena, hs, in_bytes, cudaMemcpyHostToDevice, h->stream));
+  d.first = (const float4*)(arena + in_a); d.second = (const float4*)(arena + in_b); d.off = (const int64_t*)(arena + in_off);
+  d.samples = have_s ? (const int32_t*)(arena + in_s) : nullptr;
+  uint8_t* ob = arena + in_bytes;
+  d.T_out = (float*)(ob + o_T); d.losses = (float*)(ob + o_loss); d.best_it = (int32_t*)(ob + o_best); d.counts = (int32_t*)(ob + o_cnt);
+  d.labels = ob + o_lab;
+  d.src = (float4*)(arena + w_src); d.dst = (float4*)(arena + w_dst); d.Thyp = (float*)(arena + w_T);
+  LAUNCH(h, k_ransac_triangulate, (unsigned)cdiv(2 * n, 128), 128, d, n, 2 * n);
+  if (iters > 0) {
+    k_ransac_hypotheses<<<dim3((unsigned)iters, (unsigned)nprob), kRansacThreads, 0, h->stream>>>(d);
+    h->launches++;
+  }
+  LAUNCH(h, k_ransac_finish, nprob, kRansacFinishThreads, d);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaMemcpyAsync(hs, ob, out_bytes, cudaMemcpyDeviceToHost, h->stream));   // the upload has been consumed: stream order
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  std::memcpy(T, hs + o_T, (size_t)nprob * 64);
+  if (n > 0) { std::memcpy(labels, hs + o_lab, (size_t)n); std::memcpy(losses, hs + o_loss, (size_t)n * 4); }
+  if (best_it) std::memcpy(best_it, hs + o_best, (size_t)nprob * 4);
+  if (counts && iters > 0) std::memcpy(counts, hs + o_cnt, nh * 4);
+  return SBA_OK;
+}
+
+int sba_ransac_stereo(sba_handle h, int32_t num_problems, const int64_t* offsets, const float* obs_first, const float* obs_second,
+                      const float* P_l, const float* P_r, const sba_ransac_options* options, const int32_t* samples, uint64_t seed,
+                      float* T, uint8_t* labels, float* losses, int32_t* best_iteration, int32_t* counts) {
+  if (!h || num_problems < 0 || !offsets || !P_l || !P_r || (num_problems > 0 && !T)) { set_error("sba_ransac_stereo: bad arguments"); return SBA_INVALID_ARGUMENT; }
+  sba_ransac_options o;
+  if (options) o = *options; else sba_ransac_default_options(&o);
+  if (o.max_iterations < 0 || o.max_iterations > 65535 || !(o.inlier_threshold > 0.f)) { set_error("sba_ransac_stereo: bad options (0 <= max_iterations <= 65535, inlier_threshold > 0)"); return SBA_INVALID_ARGUMENT; }
+  if (num_problems > 65535) { set_error("sba_ransac_stereo: at most 65535 problems per call"); return SBA_INVALID_ARGUMENT; }
+  if (offsets[0] != 0) { set_error("sba_ransac_stereo: offsets[0] must be 0"); return SBA_INVALID_ARGUMENT; }
+  for (int b = 0; b < num_problems; ++b) {
+    const int64_t nb = offsets[b + 1] - offsets[b];
+    if (nb < 0) { set_error("sba_ransac_stereo: offsets must be non-decreasing"); return SBA_INVALID_ARGUMENT; }
+    if (samples)
+      for (int64_t k = 0; k < (int64_t)o.max_iterations * 3 && nb > 0; ++k) {
+        const int32_t s = samples[((int64_t)b * o.max_iterations) * 3 + k];
+        if (s < 0 || s >= nb) { set_error("sba_ransac_stereo: sample index out of range"); return SBA_INVALID_ARGUMENT; }
+      }
+  }
+  const int64_t n = offsets[num_problems];
+  if (n > 0 && (!obs_first || !obs_second || !labels || !losses)) { set_error("sba_ransac_stereo: null element / output arrays"); return SBA_INVALID_ARGUMENT; }
+  if (h->device < 0) { set_error("host-only handle: no CUDA device bound (there is no CPU fallback)"); return SBA_CUDA_ERROR; }
+  if (num_problems == 0) return SBA_OK;
+  CUDA_TRY(cudaSetDevice(h->device));
+  std::vector<void*> keep;                 // call-local buffers, released on return (the handle's BA structure is untouched)
+  keep.swap(h->allocs);
+  const int rc = ransac_run(h, num_problems, offsets, obs_first, obs_second, P_l, P_r, o, samples, seed, T, labels, losses, best_iteration, counts);
+  for (void* p : h->allocs) cudaFreeAsync(p, h->stream);
+  cudaStreamSynchronize(h->stream);
+  h->allocs.swap(keep);
+  return rc;
+}
+
+int sba_triangulate_stereo(sba_handle h, int64_t n, const float* obs, const float* P_l, const float* P_r, float* xyz) {
+  if (!h || n < 0 || !P_l || !P_r || (n > 0 && (!obs || !xyz))) { set_error("sba_triangulate_stereo: bad arguments"); return SBA_INVALID_ARGUMENT; }
+  if (h->device < 0) { set_error("host-only handle: no CUDA device bound (there is no CPU fallback)"); return SBA_CUDA_ERROR; }
+  if (n == 0) return SBA_OK;
+  CUDA_TRY(cudaSetDevice(h->device));
+  std::vector<void*> keep;
+  keep.swap(h->allocs);
+  auto run = [&]() -> int {
+    int rc;
+    RansacDev d{};
+    std::memcpy(d.Pl, P_l, 48); std::memcpy(d.Pr, P_r, 48);
+    float4* d_a = nullptr;
+    if ((rc = h->alloc(&d_a, (size_t)n))) return rc;
+    if ((rc = h->alloc(&d.src, (size_t)n))) return rc;
+    CUDA_TRY(cudaMemcpyAsync(d_a, obs, (size_t)n * 16, cudaMemcpyHostToDevice, h->stream));
+    d.first = d_a;
+    LAUNCH(h, k_ransac_triangulate, (unsigned)cdiv(n, 128), 128, d, n, n);
+    CUDA_TRY(cudaGetLastError());
+    std::vector<float> tmp((size_t)n * 4);
+    CUDA_TRY(cudaMemcpyAsync(tmp.data(), d.src, (size_t)n * 16, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    for (int64_t i = 0; i < n; ++i) { xyz[3 * i] = tmp[4 * i]; xyz[3 * i + 1] = tmp[4 * i + 1]; xyz[3 * i + 2] = tmp[4 * i + 2]; }
+    return SBA_OK;
+  };
+  const int rc = run();
+  for (void* p : h->allocs) cudaFreeAsync(p, h->stream);
+  cudaStreamSynchronize(h->stream);
+  h->allocs.swap(keep);
   return rc;
 }
 

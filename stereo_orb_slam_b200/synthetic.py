@@ -227,6 +227,37 @@ def make_map(num_frames, num_points, track_len, seed, noise_px=0.5, outlier_frac
                                track_len=track_len, seed=int(seed), noise_free=bool(noise_free)))
 
 
+def make_stereo_pairs(n, seed, outlier_frac=0.3, noise_px=0.1, cam=KITTI, motion=None, z_max=30.0):
+    """Temporal matches between two stereo frames as VisualOdometer::Track builds them (src/visual_odometer.cpp:157-171):
+    obs_pairs [n,2,4] f32 with [:,0] = the current frame's (u_l, v_l, u_r, v_r) and [:,1] = the previous frame's, so the
+    model RANSAC estimates maps current-frame points into the previous frame (= the frame's relative pose).
+    Points 4 m to z_max ahead (3-point fits on triangulated points degrade quickly with depth), pixel noise on all four coordinates,
+    `outlier_frac` of the pairs mismatched (second observation replaced by another point's).
+    Returns (obs_pairs, T_prev_from_curr [4,4] f64, is_outlier [n] bool, P_l [3,4] f32, P_r [3,4] f32)."""
+    rng = np.random.default_rng(seed)
+    if motion is None:
+        w = rng.normal(0, np.deg2rad(1.0), 3)
+        t = np.array([rng.normal(0, 0.05), rng.normal(0, 0.02), rng.uniform(0.6, 1.3)])
+    else:
+        w, t = np.asarray(motion[0], np.float64), np.asarray(motion[1], np.float64)
+    T = np.eye(4)
+    T[:3, :3] = _rodrigues(w[None])[0]; T[:3, 3] = t
+    z = rng.uniform(4.0, z_max, n)
+    u = rng.uniform(40, cam["width"] - 40, n); v = rng.uniform(20, cam["height"] - 20, n)
+    Xc = np.stack([(u - cam["cx"]) * z / cam["fx"], (v - cam["cy"]) * z / cam["fy"], z], axis=1)     # current camera frame
+    Xp = Xc @ T[:3, :3].T + T[:3, 3]                                                                # previous camera frame
+    I = np.broadcast_to(np.eye(3), (n, 3, 3)); O = np.zeros((n, 3))
+    oc, _ = _project(I, O, Xc, cam)
+    op, _ = _project(I, O, Xp, cam)
+    oc = oc + rng.normal(0, noise_px, oc.shape); op = op + rng.normal(0, noise_px, op.shape)
+    bad = rng.random(n) < outlier_frac
+    perm = rng.permutation(n)
+    op[bad] = op[perm][bad] + rng.normal(0, 5.0, (int(bad.sum()), 4))
+    p_l, p_r = projection_matrices(cam)
+    pairs = np.stack([oc, op], axis=1).astype(np.float32)
+    return pairs, T, bad, p_l.reshape(3, 4).astype(np.float32), p_r.reshape(3, 4).astype(np.float32)
+
+
 # BASELINE.json configs (SURVEY.md §8): name -> generator arguments
 CONFIGS = {
     "C1": dict(num_frames=10, num_points=5000, track_len=8, seed=0xBA00 + 0),

@@ -95,6 +95,9 @@ def main():
     barrier()
     ms = sum(sv.time_stage(8, 1, True, 1e4) for _ in range(args.steps))
     barrier()
+    # the solve kernels (factorisation, step loop) load and set up on their first launch: two untimed LM iterations first
+    sv.set_state(b["poses"], b["points"])
+    sv.run(default_options(max_time_s=0.0, max_iterations=2))
     sv.set_state(b["poses"], b["points"])
     barrier(); t0 = time.perf_counter()
     s = sv.run(opt)

@@ -67,7 +67,7 @@ struct sba_handle_s {
   DeviceMap map;
   int device = -1;            // -1: host-only handle (structure build / introspection only)
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev[8] = {};
+  cudaEvent_t ev[12] = {};     // [8..11]: the second pair of linearisation events of the run-ahead LM loop
   // The camera-side tail of a linearisation (k_assemble_cams, k_lin_finish, k_lm_begin: a few dozen small CTAs)
   // runs on `side`, forked after k_lin_chunk, while the next k_schur_chunk fills the SMs on `stream`;
   // join_tail() makes `stream` wait for it before the first consumer of U / gc / the window scalars.
@@ -87,6 +87,7 @@ struct sba_handle_s {
   int step_launches = 0;
   cudaGraphExec_t step_graph = nullptr;   // one K1-K3 step (stage 8) captured once per structure: a single launch per step
   int32_t* h_counters = nullptr;      // pinned
+  unsigned long long* stamps = nullptr;   // SBA_DEBUG_LS=2
   uint8_t* stage = nullptr; size_t stage_bytes = 0;   // pinned staging of sba_ransac_stereo (grown on demand)
   int64_t launches = 0;
   int64_t nobs_all = 0;
@@ -153,6 +154,16 @@ struct sba_handle_s {
     }                                                                        \
   } while (0)
 
+// SBA_DEBUG_LS=2: device-side time stamps between the kernels of an LM iteration, on both streams (tuning aid)
+__global__ void k_stamp(unsigned long long* buf, int idx) { buf[idx] = gtimer(); }
+static void stamp(sba_handle h, cudaStream_t st, int idx) {
+  if (h->P.debug != 2) return;
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(h->stream, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return;
+  if (!h->stamps) { if (cudaMalloc((void**)&h->stamps, 32 * 8) != cudaSuccess) return; cudaMemset(h->stamps, 0, 32 * 8); }
+  k_stamp<<<1, 1, 0, st>>>(h->stamps, idx);
+}
+
 extern "C" {
 
 void sba_default_options(sba_options* o) {
@@ -185,7 +196,7 @@ int sba_create(int device, sba_handle* out) {
     // No CPU fallback: a handle on a device needs a working CUDA device, loudly.
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
-    for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
+    for (int i = 0; i < 12 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
@@ -238,9 +249,10 @@ void sba_destroy(sba_handle h) {
     if (h->map.d_ids) cudaFree(h->map.d_ids);
     if (h->stream) cudaStreamSynchronize(h->stream);     // the frees above are stream-ordered
     if (h->pool) cudaMemPoolDestroy(h->pool);
-    for (int i = 0; i < 8; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    for (int i = 0; i < 12; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     if (h->h_counters) cudaFreeHost(h->h_counters);
     if (h->stage) cudaFreeHost(h->stage);
+    if (h->stamps) cudaFree(h->stamps);
     if (h->side) cudaStreamDestroy(h->side);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
@@ -680,11 +692,15 @@ static int do_schur(sba_handle h, bool exact_solver = false) {
     // after a fused linearisation (single GPU): ONE assemble kernel for U / gc / S / rhs, then the window cost and the
     // gradient test on the side stream while the linear solve runs (do_step joins)
     h->cams_pending = false;
+    stamp(h, h->stream, 0);
     LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 3 | (exact_solver ? 4 : 0));
+    stamp(h, h->stream, 1);
     CUDA_TRY(cudaEventRecord(h->ev_fork, h->stream));
     CUDA_TRY(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+    stamp(h, h->side, 2);
     if (d.nwin > 0) { k_lin_finish<<<d.nwin, kThreads, 0, h->side>>>(d, h->P, h->pend_keep_cost ? 1 : 0); h->launches++; }
     if (h->pend_lm_begin >= 0) { k_lm_begin<<<cdiv(d.nwin, 128), 128, 0, h->side>>>(d, h->P, h->pend_radius, h->pend_lm_begin, 0); h->launches++; }
+    stamp(h, h->side, 3);
     h->tail_pending = true;
     CUDA_TRY(cudaGetLastError());
     return SBA_OK;
@@ -718,8 +734,10 @@ static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
     if (const char* e = std::getenv("SBA_SPCHOL_GRID")) grid = std::max(1, std::min(grid, std::atoi(e)));   // tuning aid
     Dev dd = d; SpCholDev ss = h->sp;
     void* args[] = {&dd, &ss};
+    stamp(h, h->stream, 4);
     CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_spchol, dim3(grid), dim3(kSpThreads), args, h->spchol_smem, h->stream));
     h->launches++;
+    stamp(h, h->stream, 5);
     it = -1;
   } else if (d.Nf > 0 && h->chol_ok && opt->linear_solver != 1) {
     CUDA_TRY(cudaMemsetAsync(d.counters + 4, 0, 4, h->stream));
@@ -815,7 +833,9 @@ static int do_ls_round(sba_handle h) {
 
 // K5 + K6 + trust-region control: step, line search (Ceres: bounds => projected Armijo search after every
 // trust-region step), accept / reject per window.  Leaves counters [0] running [2] accepted on the host.
-static int do_step(sba_handle h, int* ls_rounds) {
+// `defer`: single-GPU cooperative path only — enqueue the step, the read-back of the counters and ev[3], and return
+// without waiting; the caller synchronises on ev[3] before it looks at h_counters.
+static int do_step(sba_handle h, int* ls_rounds, bool defer = false) {
   Dev& d = h->d;
   const DevParams& P = h->P;
   { const int jrc = join_tail(h); if (jrc) return jrc; }
@@ -828,10 +848,35 @@ static int do_step(sba_handle h, int* ls_rounds) {
     Dev dd = d; DevParams pp = P;
     int fused_cams = (h->H.max_slots <= kTrialSlots && h->H.long_chunks.empty()) ? 1 : 0;
     void* args[] = {&dd, &pp, &fused_cams};
+    cudaEvent_t dbg[3] = {nullptr, nullptr, nullptr};
+    const bool dbg_ev = P.debug == 2 && !defer;           // SBA_DEBUG_LS=2: where the step's wall time goes
+    const auto th0 = std::chrono::steady_clock::now();
+    if (dbg_ev) { for (auto& e : dbg) cudaEventCreate(&e); cudaEventRecord(dbg[0], h->stream); }
+    stamp(h, h->stream, 6);
     CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_step_loop, dim3(grid), dim3(kThreads), args, 0, h->stream));
     h->launches++;
+    stamp(h, h->stream, 7);
+    if (dbg_ev) cudaEventRecord(dbg[1], h->stream);
     CUDA_TRY(cudaMemcpyAsync(h->h_counters, d.counters, 32, cudaMemcpyDeviceToHost, h->stream));
+    if (dbg_ev) cudaEventRecord(dbg[2], h->stream);
+    const auto th1 = std::chrono::steady_clock::now();
+    if (defer) { CUDA_TRY(cudaEventRecord(h->ev[3], h->stream)); return SBA_OK; }
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (dbg_ev) {
+      const auto th2 = std::chrono::steady_clock::now();
+      float k = 0.f, c = 0.f;
+      cudaEventElapsedTime(&k, dbg[0], dbg[1]); cudaEventElapsedTime(&c, dbg[1], dbg[2]);
+      std::fprintf(stderr, "[step host] enqueue %.1f us, wait %.1f us | device: kernel %.1f us, d2h %.1f us\n",
+                   std::chrono::duration<double, std::micro>(th1 - th0).count(), std::chrono::duration<double, std::micro>(th2 - th1).count(), k * 1e3, c * 1e3);
+      for (auto& e : dbg) cudaEventDestroy(e);
+      if (h->stamps) {
+        unsigned long long t[8];
+        cudaMemcpy(t, h->stamps, sizeof(t), cudaMemcpyDeviceToHost);
+        auto us = [&](int i) { return (double)((long long)t[i] - (long long)t[0]) * 1e-3; };
+        std::fprintf(stderr, "[stamps us] assemble 0..%.1f | side: tail %.1f..%.1f | solve %.1f..%.1f | step %.1f..%.1f\n",
+                     us(1), us(2), us(3), us(4), us(5), us(6), us(7));
+      }
+    }
     if (ls_rounds) *ls_rounds += h->h_counters[6];
     return SBA_OK;
   }
@@ -1063,13 +1108,17 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   for (double c : wcost) S.initial_cost += c;
   bool lin_pending = true;
+  cudaEvent_t* lin_ev = h->ev + 4;
+  int lin_slot = 1;
   auto take_lin_time = [&]() {
     if (!lin_pending) return;
     float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, h->ev[4], h->ev[5]) == cudaSuccess) S.ms_linearize += ms;
+    if (cudaEventElapsedTime(&ms, lin_ev[0], lin_ev[1]) == cudaSuccess) S.ms_linearize += ms;
     lin_pending = false;
   };
   take_lin_time();
+  // single GPU, cooperative step, fused K1-K3: the host runs one linearisation ahead of the step's outcome
+  const bool run_ahead = !h->comm.active() && h->coop_blocks > 0 && h->fused_ok && !o.verbose && !std::getenv("SBA_NO_RUN_AHEAD");
 
   int running = d.nwin;
   int ls_rounds = 0;
@@ -1096,11 +1145,27 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
     int32_t pit = 0;
     if ((rc = do_pcg(h, &o, &pit))) return rc;
     CUDA_TRY(cudaEventRecord(h->ev[2], h->stream));
-    if ((rc = do_step(h, &ls_rounds))) return rc;      // syncs; h_counters holds [running, -, accepted, -, pcg its]
+    if (run_ahead) {
+      // The next linearisation does not depend on what the host learns from this step: a rejected step re-linearises
+      // at the same point (same bits; the fused kernel rebuilds the Schur partials at the reduced radius), a finished
+      // window ignores it.  So it goes out BEFORE the host waits for the step's counters, and the ~25 us of
+      // wake-up + launch latency per iteration overlap with it instead of idling the GPU.
+      if ((rc = do_step(h, &ls_rounds, true))) return rc;
+      cudaEvent_t* le = h->ev + (lin_slot ? 8 : 4);      // the previous linearisation's events stay readable
+      CUDA_TRY(cudaEventRecord(le[0], h->stream));
+      if ((rc = do_linearize(h, true, true, 0, o.initial_radius, true))) return rc;
+      CUDA_TRY(cudaEventRecord(le[1], h->stream));
+      CUDA_TRY(cudaEventSynchronize(h->ev[3]));
+      take_lin_time();                                   // the previous one finished before this step began
+      lin_ev = le; lin_slot ^= 1; lin_pending = true;
+      ls_rounds += h->h_counters[6];
+    } else {
+      if ((rc = do_step(h, &ls_rounds))) return rc;      // syncs; h_counters holds [running, -, accepted, -, pcg its]
+      CUDA_TRY(cudaEventRecord(h->ev[3], h->stream));
+      CUDA_TRY(cudaEventSynchronize(h->ev[3]));
+      take_lin_time();
+    }
     S.pcg_iterations += (pit >= 0) ? pit : h->h_counters[4];
-    CUDA_TRY(cudaEventRecord(h->ev[3], h->stream));
-    CUDA_TRY(cudaEventSynchronize(h->ev[3]));
-    take_lin_time();
     float a = 0.f, b = 0.f, c = 0.f;
     CUDA_TRY(cudaEventElapsedTime(&a, h->ev[0], h->ev[1]));
     CUDA_TRY(cudaEventElapsedTime(&b, h->ev[1], h->ev[2]));
@@ -1108,7 +1173,9 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
     S.ms_schur += a; S.ms_pcg += b; S.ms_update += c;
     running = h->h_counters[0];
     const int accepted = h->h_counters[2];
-    if (accepted > 0) {
+    if (run_ahead) {
+      if (accepted > 0) S.linearizations++;
+    } else if (accepted > 0) {
       CUDA_TRY(cudaEventRecord(h->ev[4], h->stream));
       if ((rc = do_linearize(h, true, true, 0, o.initial_radius, true))) return rc;
       CUDA_TRY(cudaEventRecord(h->ev[5], h->stream));
@@ -1700,6 +1767,7 @@ static int ransac_run(sba_handle h, int32_t nprob, const int64_t* off, const flo
   if ((rc = h->alloc(&arena, total))) return rc;
   if (h->stage_bytes < std::max(in_bytes, out_bytes)) {
     if (h->stage) cudaFreeHost(h->stage);
+    if (h->stamps) cudaFree(h->stamps);
     h->stage = nullptr; h->stage_bytes = 0;
     const size_t want = std::max<size_t>(std::max(in_bytes, out_bytes) * 2, 1 << 16);
     CUDA_TRY(cudaMallocHost((void**)&h->stage, want));

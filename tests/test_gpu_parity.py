@@ -387,6 +387,27 @@ def test_config2_stress_without_the_reference_gates():
     assert np.abs(x50).max() <= 1e4                                                    # the bounds hold
 
 
+def test_run_ahead_lm_loop_equals_the_synchronous_loop_bit_for_bit(monkeypatch):
+    """Single GPU: the next linearisation is enqueued before the host reads the step's outcome (a rejected step
+    re-linearises at the same point, a finished window ignores it).  The trajectory — rejected steps, line searches,
+    windows finishing at different iterations — must equal the synchronous loop's to the bit."""
+    cases = []
+    w = make_window(8, 600, 5, 3, vo_gates=False, noise_px=2.0)    # rejected steps (47 of 50 succeed), points at the bounds
+    cases.append(((w["poses"], w["points"], w["obs_cam"], w["obs_pt"], w["obs_uv"], w["p_l"], w["p_r"]), {}))
+    b = batch_windows([make_window(6 + (i % 3), 300 + 40 * i, 4, 70 + i) for i in range(12)])
+    cases.append(((b["poses"], b["points"], b["obs_cam"], b["obs_pt"], b["obs_uv"], b["p_l"], b["p_r"]),
+                  dict(win_cam_off=b["win_cam_off"], win_pt_off=b["win_pt_off"])))
+    for args, kw in cases:
+        monkeypatch.delenv("SBA_NO_RUN_AHEAD", raising=False)
+        a = Solver(0).solve(*args, options=PARITY, **kw)
+        monkeypatch.setenv("SBA_NO_RUN_AHEAD", "1")
+        c = Solver(0).solve(*args, options=PARITY, **kw)
+        assert np.array_equal(a[0], c[0]) and np.array_equal(a[1], c[1])
+        for k in ("final_cost", "iterations", "successful_steps", "linearizations", "termination"):
+            assert a[2][k] == c[2][k], k
+        assert a[2]["successful_steps"] < a[2]["iterations"] or kw      # the stress window does reject steps
+
+
 def test_config3_many_windows_match_the_oracle():
     """BASELINE.json configs[2] shape: 256 DISTINCT 10-keyframe windows (seed + window id) in one batched call, every
     window with its own trust region; 16 of them, spread over the batch, are checked against oracle.solve at the

@@ -299,6 +299,25 @@ static int setup_spchol(sba_handle h, const SparseCholSymbolic& Y, SpCholDev* sp
   }
   sp.panel_cap = cap;
   *smem = spchol_smem_bytes(cap);
+  // phase A of every level (products and right-hand-side terms that come from OUTSIDE a chain) is spread over the whole
+  // grid: flat lists of the blocks / columns of the level's shared-memory chains
+  {
+    std::vector<int32_t> bptr((size_t)Y.nlev + 1, 0), cptr((size_t)Y.nlev + 1, 0), blks, cols;
+    for (int l = 0; l < Y.nlev; ++l) {
+      for (int c = Y.lvl_ptr[l]; c < Y.lvl_ptr[l + 1]; ++c) {
+        const int j0 = Y.lvl_cols[c], jn = j0 + Y.lvl_len[c];
+        const int b0 = Y.col_ptr[j0], b1 = Y.col_ptr[jn];
+        if (b1 - b0 > cap || Y.lvl_len[c] > kSpChainMax) continue;       // long chains keep the column-by-column path
+        for (int b = b0; b < b1; ++b) if (Y.upd_ext_end[b] > Y.upd_ptr[b]) blks.push_back(b);
+        for (int j = j0; j < jn; ++j) cols.push_back(j);
+      }
+      bptr[l + 1] = (int32_t)blks.size(); cptr[l + 1] = (int32_t)cols.size();
+    }
+    if ((rc = h->upload(&sp.pa_blk_ptr, bptr))) return rc;
+    if ((rc = h->upload(&sp.pa_blk, blks))) return rc;
+    if ((rc = h->upload(&sp.pa_col_ptr, cptr))) return rc;
+    if ((rc = h->upload(&sp.pa_col, cols))) return rc;
+  }
   // (the attribute is per function, not per launch: always the largest panel, so that handles and PGO calls with
   // different capacities never lower it under each other)
   CUDA_TRY(cudaFuncSetAttribute(k_spchol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)spchol_smem_bytes(kSpPanelMax)));
@@ -733,6 +752,7 @@ static int do_pcg(sba_handle h, const sba_options* opt, int32_t* iters_out) {
     int grid = std::max(1, h->spchol_blocks);
     if (const char* e = std::getenv("SBA_SPCHOL_GRID")) grid = std::max(1, std::min(grid, std::atoi(e)));   // tuning aid
     Dev dd = d; SpCholDev ss = h->sp;
+    ss.profile = (h->P.debug == 2) ? 1 : 0;
     void* args[] = {&dd, &ss};
     stamp(h, h->stream, 4);
     CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_spchol, dim3(grid), dim3(kSpThreads), args, h->spchol_smem, h->stream));

@@ -18,10 +18,12 @@ namespace sba {
 
 struct SpCholDev {
   int32_t n, nlev, nnzL, panel_cap;
+  int32_t profile;   // SBA_DEBUG_LS=2: block 0 prints the time of every tree level (tuning aid)
   const int32_t *perm, *col_ptr, *row_idx, *init_src;
   const int64_t *upd_ptr, *upd_ext_end;
   const int32_t *upd_a, *upd_b;
   const int32_t *rowl_ptr, *rowl_ext_end, *rowl_blk, *rowl_col, *lvl_ptr, *lvl_cols, *lvl_len;
+  const int32_t *pa_blk_ptr, *pa_blk, *pa_col_ptr, *pa_col;   // per level: blocks with outside products / columns of the shared-memory chains
   double* Lv;     // [nnzL * 36] blocks of L, row-major 6x6 (block (i, j): rows of i, columns of j)
   double* Li;     // [n * 36]    inverse diagonal factors (lower)
   double* y;      // [n * 6]     forward-substituted right-hand side, then the solution (new order)
@@ -133,45 +135,65 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
     for (int w = blockIdx.x * kSpThreads + tid; w < d.nwin; w += gridDim.x * kSpThreads) d.w_pcg_it[w] = 0;
   }
   grid.sync();
+  const bool prof = sc.profile && blockIdx.x == 0 && tid == 0;
+  unsigned long long tprev = prof ? gtimer() : 0;
+  auto lap = [&](const char* what, int lvl, int nchain) {
+    if (!prof) return;
+    const unsigned long long t = gtimer();
+    printf("[spchol] %s level %d (%d chains) %.1f us\n", what, lvl, nchain, (double)(t - tprev) * 1e-3);
+    tprev = t;
+  };
   // ---- 1: factorisation + forward substitution: chains of one level in parallel, a chain's columns in sequence
   const int g = lane >> 2, t4 = lane & 3;
   const bool fout = g < 6 && t4 < 3;
   const int ps = lane / 6, ri = lane - 6 * ps;
   for (int lvl = 0; lvl < sc.nlev; ++lvl) {
     const int c_begin = __ldg(sc.lvl_ptr + lvl), c_end = __ldg(sc.lvl_ptr + lvl + 1);
+    // ---- phase A, whole grid: everything that comes from OUTSIDE a chain — finished columns of lower levels, read
+    //      through L2 — for all blocks and columns of the level at once, a warp per block / column.  In the upper
+    //      levels a few chains own thousands of products; spread over the grid they cost one L2 round instead of dozens.
+    {
+      const int gw = blockIdx.x * kSpWarps + warp, nw = gridDim.x * kSpWarps;
+      const int b_begin = __ldg(sc.pa_blk_ptr + lvl), b_end = __ldg(sc.pa_blk_ptr + lvl + 1);
+      for (int w = b_begin + gw; w < b_end; w += nw) {
+        const int blk = __ldg(sc.pa_blk + w);
+        double r0, r1;
+        sp_gather(sc, sc.upd_ptr[blk], sc.upd_ext_end[blk], lane, r0, r1);
+        if (fout) {
+          const int e = 6 * g + 2 * t4;
+          double2* dst = reinterpret_cast<double2*>(sc.Lv + (size_t)blk * 36 + e);
+          const double2 a = __ldcg(dst);
+          __stcg(dst, make_double2(a.x - r0, a.y - r1));
+        }
+      }
+      const int q_begin = __ldg(sc.pa_col_ptr + lvl), q_end = __ldg(sc.pa_col_ptr + lvl + 1);
+      for (int w = q_begin + (nw - 1 - gw); w < q_end; w += nw) {       // columns from the other end of the grid
+        const int j = __ldg(sc.pa_col + w);
+        double acc = 0.0;
+        if (lane < 30) {
+          const int r1 = __ldg(sc.rowl_ext_end + j);
+          for (int e = __ldg(sc.rowl_ptr + j) + ps; e < r1; e += 5) {
+            const double* L = sc.Lv + (size_t)__ldg(sc.rowl_blk + e) * 36 + 6 * ri;
+            const double* yk = sc.y + (size_t)__ldg(sc.rowl_col + e) * 6;
+            acc += (__ldcg(L) * __ldcg(yk) + __ldcg(L + 1) * __ldcg(yk + 1) + __ldcg(L + 2) * __ldcg(yk + 2)) +
+                   (__ldcg(L + 3) * __ldcg(yk + 3) + __ldcg(L + 4) * __ldcg(yk + 4) + __ldcg(L + 5) * __ldcg(yk + 5));
+          }
+        }
+        double tot = acc;
+#pragma unroll
+        for (int qq = 1; qq < 5; ++qq) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * qq) & 31);
+        if (lane < 6) __stcg(sc.y + (size_t)j * 6 + lane, d.rhs[(size_t)__ldg(sc.perm + j) * 6 + lane] - tot);
+      }
+    }
+    grid.sync();
     for (int ci = c_begin + blockIdx.x; ci < c_end; ci += gridDim.x) {
       const int j0 = __ldg(sc.lvl_cols + ci), len = __ldg(sc.lvl_len + ci), jn = j0 + len;
       const int blk0 = __ldg(sc.col_ptr + j0), nblk = __ldg(sc.col_ptr + jn) - blk0;
       if (nblk <= cap && len <= kSpChainMax) {
         // ======== the chain's panel lives in shared memory
-        // S1: everything that comes from OUTSIDE the chain, for all its blocks / columns at once (L2 latency is paid once)
-        for (int bi = warp; bi < nblk; bi += kSpWarps) {
-          const int blk = blk0 + bi;
-          double r0, r1;
-          sp_gather(sc, sc.upd_ptr[blk], sc.upd_ext_end[blk], lane, r0, r1);
-          if (fout) {
-            const int e = 6 * g + 2 * t4;
-            const double2 a = __ldcg(reinterpret_cast<const double2*>(sc.Lv + (size_t)blk * 36 + e));
-            P[bi * 36 + e] = a.x - r0; P[bi * 36 + e + 1] = a.y - r1;
-          }
-        }
-        for (int q = kSpWarps - 1 - warp; q < len; q += kSpWarps) {
-          const int j = j0 + q;
-          double acc = 0.0;
-          if (lane < 30) {
-            const int r1 = __ldg(sc.rowl_ext_end + j);
-            for (int e = __ldg(sc.rowl_ptr + j) + ps; e < r1; e += 5) {
-              const double* L = sc.Lv + (size_t)__ldg(sc.rowl_blk + e) * 36 + 6 * ri;
-              const double* yk = sc.y + (size_t)__ldg(sc.rowl_col + e) * 6;
-              acc += (__ldcg(L) * __ldcg(yk) + __ldcg(L + 1) * __ldcg(yk + 1) + __ldcg(L + 2) * __ldcg(yk + 2)) +
-                     (__ldcg(L + 3) * __ldcg(yk + 3) + __ldcg(L + 4) * __ldcg(yk + 4) + __ldcg(L + 5) * __ldcg(yk + 5));
-            }
-          }
-          double tot = acc;
-#pragma unroll
-          for (int qq = 1; qq < 5; ++qq) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * qq) & 31);
-          if (lane < 6) ty[q * 6 + lane] = d.rhs[(size_t)__ldg(sc.perm + j) * 6 + lane] - tot;
-        }
+        // S1: the panel (outside products already subtracted by phase A) and t of its columns come in coalesced
+        for (int i = tid; i < nblk * 36; i += kSpThreads) P[i] = __ldcg(sc.Lv + (size_t)blk0 * 36 + i);
+        for (int i = tid; i < len * 6; i += kSpThreads) ty[i] = __ldcg(sc.y + (size_t)j0 * 6 + i);
         __syncthreads();
         // S2: the chain's columns in sequence, all operands in shared memory
         for (int q = 0; q < len; ++q) {
@@ -347,6 +369,7 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
       }
     }
     grid.sync();
+    lap("fwd", lvl, c_end - c_begin);
   }
   // ---- 2: back substitution, levels downwards; a chain's columns in sequence (last first) by its CTA:
   //         x_j = Linv_jj^T (y_j - sum_i L_ij^T x_i), a thread per (block, column), partials summed in block order
@@ -358,10 +381,9 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
     for (int ci = c_begin + blockIdx.x; ci < c_end; ci += gridDim.x) {
       const int j0 = __ldg(sc.lvl_cols + ci), len = __ldg(sc.lvl_len + ci), jn = j0 + len;
       const int blk0 = __ldg(sc.col_ptr + j0), nblk = __ldg(sc.col_ptr + jn) - blk0;
-      const bool panel = nblk <= cap && len <= kSpChainMax;
-      if (panel) {
-        // the whole chain comes in by one round of independent loads: panel, block rows, x of the rows outside it,
-        // y and the inverse factors of its columns
+      if (nblk <= cap && len <= kSpChainMax) {
+        // ======== shared-memory chain.  The whole chain comes in by one round of independent loads: panel, block rows,
+        // x of the rows outside it, y and the inverse factors of its columns ...
         for (int i = tid; i < nblk * 36; i += kSpThreads) P[i] = __ldcg(sc.Lv + (size_t)blk0 * 36 + i);
         for (int i = tid; i < nblk * 6; i += kSpThreads) {
           const int b = i / 6, row = __ldg(sc.row_idx + blk0 + b);
@@ -371,38 +393,96 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
         for (int i = tid; i < len * 6; i += kSpThreads) ty[i] = __ldcg(sc.y + (size_t)j0 * 6 + i);
         for (int i = tid; i < len * 36; i += kSpThreads) LIc[i] = __ldcg(sc.Li + (size_t)j0 * 36 + i);
         __syncthreads();
+        // ... then what the rows OUTSIDE the chain contribute, for all its columns at once: a thread per (block, component)
+        // forms L_b^T x_b in place of x_b (values held in registers across the barrier), a thread per (column, component)
+        // adds its column's blocks in block order ...
+        {
+          constexpr int kMaxIt = (kSpPanelMax * 6 + kSpThreads - 1) / kSpThreads;
+          double v[kMaxIt];
+#pragma unroll
+          for (int k = 0; k < kMaxIt; ++k) {
+            const int i = tid + k * kSpThreads;
+            v[k] = 0.0;
+            if (i < nblk * 6) {
+              const int bb = i / 6, c = i - 6 * bb;
+              if (rowi[bb] >= jn) {
+                const double* L = P + (size_t)bb * 36 + c;
+                const double* xi = xe + bb * 6;
+                v[k] = (L[0] * xi[0] + L[6] * xi[1] + L[12] * xi[2]) + (L[18] * xi[3] + L[24] * xi[4] + L[30] * xi[5]);
+              }
+            }
+          }
+          __syncthreads();
+#pragma unroll
+          for (int k = 0; k < kMaxIt; ++k) { const int i = tid + k * kSpThreads; if (i < nblk * 6) xe[i] = v[k]; }
+          __syncthreads();
+          if (tid < len * 6) {
+            const int q = tid / 6, c = tid - 6 * q;
+            const int cb0 = __ldg(sc.col_ptr + j0 + q) - blk0, cb1 = __ldg(sc.col_ptr + j0 + q + 1) - blk0;
+            double e = 0.0;
+            for (int bb = cb0 + 1; bb < cb1; ++bb) e += xe[bb * 6 + c];      // in-chain rows hold 0
+            ty[tid] -= e;
+          }
+          __syncthreads();
+        }
+        // ... and the chain's own columns in sequence (last first) by warp 0 alone: only the in-chain blocks are left
+        if (warp == 0) {
+          for (int j = jn - 1; j >= j0; --j) {
+            const int q = j - j0;
+            const int cb0 = __ldg(sc.col_ptr + j) - blk0, cb1 = __ldg(sc.col_ptr + j + 1) - blk0;
+            double acc = 0.0;
+            if (lane < 30) {
+              for (int bb = cb0 + 1 + ps; bb < cb1; bb += 5) {
+                const int row = rowi[bb];
+                if (row >= jn) break;                       // rows ascend: the rest of the column lies outside the chain
+                const double* L = P + (size_t)bb * 36 + ri;
+                const double* xi = ty + (row - j0) * 6;
+                acc += (L[0] * xi[0] + L[6] * xi[1] + L[12] * xi[2]) + (L[18] * xi[3] + L[24] * xi[4] + L[30] * xi[5]);
+              }
+            }
+            double tot = acc;
+#pragma unroll
+            for (int qq = 1; qq < 5; ++qq) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * qq) & 31);
+            const double sj = (lane < 6) ? ty[q * 6 + lane] - tot : 0.0;
+            double vv = 0.0;
+#pragma unroll
+            for (int t = 0; t < 6; ++t) {
+              const double st = __shfl_sync(0xffffffffu, sj, t);
+              if (lane < 6 && t >= lane) vv += LIc[q * 36 + 6 * t + lane] * st;
+            }
+            __syncwarp();
+            if (lane < 6) {
+              ty[q * 6 + lane] = vv;
+              __stcg(sc.y + (size_t)j * 6 + lane, vv);
+              const int f = __ldg(sc.perm + j);
+              const int w = d.fcam_win[f];
+              const bool ok = isfinite(vv) && __ldcg(d.w_fail + w) == 0;
+              if (!isfinite(vv)) d.w_fail[w] = 1;                                   // benign race: every writer stores 1
+              d.x[(size_t)f * 6 + lane] = ok ? vv : 0.0;
+              d.r[(size_t)f * 6 + lane] = 0.0;                                      // exact solve: no linear residual in the model change
+            }
+            __syncwarp();
+          }
+        }
+        __syncthreads();
+        continue;
       }
+      // ======== long chains: column by column through L2, a thread per (block, column), partials summed in block order
       for (int j = jn - 1; j >= j0; --j) {
         const int b0 = __ldg(sc.col_ptr + j), nbl = __ldg(sc.col_ptr + j + 1) - b0 - 1;
         double acc = 0.0;
         double yv = 0.0, lic[6] = {0, 0, 0, 0, 0, 0};
-        if (panel) {
-          if (gq < G)
-            for (int bb = gq; bb < nbl; bb += G) {
-              const int b = b0 + 1 + bb - blk0;
-              const double* L = P + (size_t)b * 36 + cc;
-              const int row = rowi[b];
-              const double* xi = (row < jn) ? ty + (row - j0) * 6 : xe + b * 6;
-              acc += (L[0] * xi[0] + L[6] * xi[1] + L[12] * xi[2]) + (L[18] * xi[3] + L[24] * xi[4] + L[30] * xi[5]);
-            }
-          if (tid < 6) {
-            yv = ty[(j - j0) * 6 + tid];
-#pragma unroll
-            for (int q = 0; q < 6; ++q) if (q >= tid) lic[q] = LIc[(j - j0) * 36 + 6 * q + tid];
+        if (gq < G)
+          for (int bb = gq; bb < nbl; bb += G) {
+            const double* L = sc.Lv + (size_t)(b0 + 1 + bb) * 36 + cc;               // column cc of L_ij
+            const double* xi = sc.y + (size_t)__ldg(sc.row_idx + b0 + 1 + bb) * 6;
+            acc += (__ldcg(L) * __ldcg(xi) + __ldcg(L + 6) * __ldcg(xi + 1) + __ldcg(L + 12) * __ldcg(xi + 2)) +
+                   (__ldcg(L + 18) * __ldcg(xi + 3) + __ldcg(L + 24) * __ldcg(xi + 4) + __ldcg(L + 30) * __ldcg(xi + 5));
           }
-        } else {
-          if (gq < G)
-            for (int bb = gq; bb < nbl; bb += G) {
-              const double* L = sc.Lv + (size_t)(b0 + 1 + bb) * 36 + cc;               // column cc of L_ij
-              const double* xi = sc.y + (size_t)__ldg(sc.row_idx + b0 + 1 + bb) * 6;
-              acc += (__ldcg(L) * __ldcg(xi) + __ldcg(L + 6) * __ldcg(xi + 1) + __ldcg(L + 12) * __ldcg(xi + 2)) +
-                     (__ldcg(L + 18) * __ldcg(xi + 3) + __ldcg(L + 24) * __ldcg(xi + 4) + __ldcg(L + 30) * __ldcg(xi + 5));
-            }
-          if (tid < 6) {
-            yv = __ldcg(sc.y + (size_t)j * 6 + tid);
+        if (tid < 6) {
+          yv = __ldcg(sc.y + (size_t)j * 6 + tid);
 #pragma unroll
-            for (int q = 0; q < 6; ++q) if (q >= tid) lic[q] = __ldcg(sc.Li + (size_t)j * 36 + 6 * q + tid);     // Linv^T row
-          }
+          for (int q = 0; q < 6; ++q) if (q >= tid) lic[q] = __ldcg(sc.Li + (size_t)j * 36 + 6 * q + tid);     // Linv^T row
         }
         xp[tid] = acc;
         __syncthreads();
@@ -420,7 +500,6 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
             if (q >= lane) v += lic[q] * sq;
           }
           if (lane < 6) {
-            if (panel) ty[(j - j0) * 6 + lane] = v;
             __stcg(sc.y + (size_t)j * 6 + lane, v);
             const int f = __ldg(sc.perm + j);
             const int w = d.fcam_win[f];
@@ -434,6 +513,7 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
       }
     }
     if (lvl > 0) grid.sync();
+    lap("bwd", lvl, c_end - c_begin);
   }
 }
 

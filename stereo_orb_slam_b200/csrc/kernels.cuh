@@ -2505,45 +2505,103 @@ __global__ void __launch_bounds__(kThreads) k_pcg_coop(Dev d, DevParams P, int m
 }
 
 // ------------------------------------------------------------------------- K5: back-substitution
-// thread per point: dp = -Vinv (gp + sum_obs W_e^T dc[cam(e)])   (stored; the candidate is formed by the
-// line-search kernels).  chunk partials: g.dp, dp^T D dp, |x|^2, max|dp|
+// dp = -Vinv (gp + sum_obs W_e^T dc[cam(e)])   (stored; the candidate is formed by the line-search kernels).
+// A thread per OBSERVATION forms W_e^T dc (its row of W is one independent load; the camera steps of the chunk's slots
+// are staged in shared memory meanwhile), then a thread per point adds its observations in order.  A thread per point
+// walking its observations paid three dependent L2 round trips per observation.
+// chunk partials: g.dp, dp^T D dp, |x|^2, max|dp|
+constexpr int kBackObs = 256;       // observations of a regular chunk (<= 240, structure.cpp)
+constexpr int kBackSlots = 64;      // camera slots staged; chunks with more read the camera steps through L2
 __device__ __forceinline__ void dev_backsub(const Dev& d, const DevParams& P, int chunk) {
   __shared__ double sm[4 * 3];
   __shared__ double smx[4];
-  const int p = d.pchunk_begin[chunk] + threadIdx.x;
-  const int w = d.pchunk_win[chunk];
-  double part[3] = {0, 0, 0};
-  double dmax = 0.0;
-  if (p < d.pchunk_end[chunk]) {
-    const double g0 = d.gp[(size_t)p * 3], g1 = d.gp[(size_t)p * 3 + 1], g2 = d.gp[(size_t)p * 3 + 2];
-    double t0 = g0, t1 = g1, t2 = g2;
-    const int e1 = d.pt_off[p + 1];
-    for (int e = d.pt_off[p]; e < e1; ++e) {
-      const int f = __ldg(d.fc + __ldg(d.pcam + e));
-      if (f < 0) continue;
-      double W[18];
-      load_W(d.W, (size_t)e, W);
-#pragma unroll
-      for (int i = 0; i < 6; ++i) {
-        const double dc = d.x[(size_t)f * 6 + i];
-        t0 += W[3 * i] * dc; t1 += W[3 * i + 1] * dc; t2 += W[3 * i + 2] * dc;
-      }
+  __shared__ double sobs[kBackObs * 3];
+  __shared__ double dcs[kBackSlots * 6];
+  const int4 cd0 = __ldg(d.cdesc + 4 * (size_t)chunk), cd1 = __ldg(d.cdesc + 4 * (size_t)chunk + 1);
+  const int p0 = cd0.x, np = cd0.y, e0 = cd0.z, n = cd0.w, w = cd1.x, cs0 = cd1.y, ns = cd1.z;
+  const bool regular = n <= kBackObs;
+  const bool staged = regular && ns <= kBackSlots;
+  if (staged) {
+    for (int i = threadIdx.x; i < ns * 6; i += kThreads) {
+      const int sl = i / 6;
+      const int f = __ldg(d.fc + __ldg(d.cs_cam + cs0 + sl));
+      dcs[i] = (f >= 0) ? d.x[(size_t)f * 6 + (i - 6 * sl)] : 0.0;     // a fixed camera's (absent) columns of W are never read
     }
-    double Vi[6];
+  }
+  // this thread's point: everything that depends only on p is requested now, ahead of both barriers
+  const int p = p0 + threadIdx.x;
+  const bool has_p = (int)threadIdx.x < np;
+  double gq[3] = {0, 0, 0}, Vi[6] = {0, 0, 0, 0, 0, 0}, Vd[3] = {0, 0, 0}, xq[3] = {0, 0, 0}, sq[3] = {0, 0, 0};
+  int i0 = 0, i1 = 0;
+  if (has_p) {
+    i0 = d.pt_off[p] - e0; i1 = d.pt_off[p + 1] - e0;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { gq[i] = d.gp[(size_t)p * 3 + i]; xq[i] = d.pts[(size_t)p * 3 + i]; sq[i] = d.sc2p[(size_t)p * 3 + i]; }
 #pragma unroll
     for (int i = 0; i < 6; ++i) Vi[i] = d.Vinv[(size_t)p * 6 + i];
+    Vd[0] = d.V[(size_t)p * 6]; Vd[1] = d.V[(size_t)p * 6 + 3]; Vd[2] = d.V[(size_t)p * 6 + 5];
+  }
+  const double radius = d.w_radius[w];
+  double tl[3] = {0, 0, 0};          // long chunk (one point, thousands of observations): this thread's share
+  if (staged) {
+    // the rows of W first: independent loads, issued before the barrier the staged camera steps need
+    double Wr[2][18];
+    int sl[2] = {0, 0};
+    static_assert(kBackObs <= 2 * kThreads, "two observations per thread");
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int i = threadIdx.x + k * kThreads;
+      if (i < n) { load_W(d.W, (size_t)(e0 + i), Wr[k]); sl[k] = d.oslot[e0 + i]; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int i = threadIdx.x + k * kThreads;
+      if (i < n) {
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+        const double* dc = dcs + 6 * sl[k];
+#pragma unroll
+        for (int q = 0; q < 6; ++q) { s0 += Wr[k][3 * q] * dc[q]; s1 += Wr[k][3 * q + 1] * dc[q]; s2 += Wr[k][3 * q + 2] * dc[q]; }
+        sobs[3 * i] = s0; sobs[3 * i + 1] = s1; sobs[3 * i + 2] = s2;
+      }
+    }
+  } else {
+    for (int i = threadIdx.x; i < n; i += kThreads) {
+      const int f = __ldg(d.fc + __ldg(d.pcam + e0 + i));
+      double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+      if (f >= 0) {
+        double W[18];
+        load_W(d.W, (size_t)(e0 + i), W);
+#pragma unroll
+        for (int q = 0; q < 6; ++q) { const double dc = d.x[(size_t)f * 6 + q]; s0 += W[3 * q] * dc; s1 += W[3 * q + 1] * dc; s2 += W[3 * q + 2] * dc; }
+      }
+      if (regular) { sobs[3 * i] = s0; sobs[3 * i + 1] = s1; sobs[3 * i + 2] = s2; }
+      else { tl[0] += s0; tl[1] += s1; tl[2] += s2; }
+    }
+  }
+  __syncthreads();
+  if (!regular) {                    // fixed-order block sum of the shares; the chunk's one point belongs to thread 0
+    (void)block_sum<3>(tl, sm);      // leaves the four warp sums in sm (the next block_sum starts with a barrier)
+    if (threadIdx.x == 0) {
+#pragma unroll
+      for (int i = 0; i < 3; ++i) tl[i] = ((sm[i] + sm[3 + i]) + sm[6 + i]) + sm[9 + i];
+    }
+  }
+  double part[3] = {0, 0, 0};
+  double dmax = 0.0;
+  if (has_p) {
+    double t0 = gq[0], t1 = gq[1], t2 = gq[2];
+    if (regular) {
+      for (int i = i0; i < i1; ++i) { t0 += sobs[3 * i]; t1 += sobs[3 * i + 1]; t2 += sobs[3 * i + 2]; }
+    } else { t0 += tl[0]; t1 += tl[1]; t2 += tl[2]; }
     const double dp[3] = {-(Vi[0] * t0 + Vi[1] * t1 + Vi[2] * t2), -(Vi[1] * t0 + Vi[3] * t1 + Vi[4] * t2),
                           -(Vi[2] * t0 + Vi[4] * t1 + Vi[5] * t2)};
-    const double radius = d.w_radius[w];
-    const double Vd[3] = {d.V[(size_t)p * 6], d.V[(size_t)p * 6 + 3], d.V[(size_t)p * 6 + 5]};
-    const double g[3] = {g0, g1, g2};
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
-      const double x = d.pts[(size_t)p * 3 + i];
       d.dp[(size_t)p * 3 + i] = dp[i];
-      part[0] += g[i] * dp[i];
-      part[1] += lm_damp(d.sc2p[(size_t)p * 3 + i], Vd[i], radius) * dp[i] * dp[i];
-      part[2] += x * x;
+      part[0] += gq[i] * dp[i];
+      part[1] += lm_damp(sq[i], Vd[i], radius) * dp[i] * dp[i];
+      part[2] += xq[i] * xq[i];
       dmax = fmax(dmax, fabs(dp[i]));
     }
   }
@@ -2698,18 +2756,26 @@ __device__ __forceinline__ void dev_trial_points(const Dev& d, const DevParams& 
       part[2] += (X - x) * (X - x);
     }
   }
+  // a regular chunk has at most two observations per thread: their index / pixel loads do not depend on the staged
+  // cameras and go out before the barrier (one L2 round trip less on the chunk's critical path)
+  const bool pre = staged && n <= 2 * kThreads;
+  int pre_pl[2] = {0, 0}, pre_sl[2] = {0, 0};
+  float4 pre_m[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+  if (pre) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int i = threadIdx.x + k * kThreads;
+      if (i < n) { pre_pl[k] = __ldg(d.ppt + e0 + i) - p0; pre_m[k] = __ldg(d.uv_p + e0 + i); pre_sl[k] = d.oslot[e0 + i]; }
+    }
+  }
   __syncthreads();
   // thread per observation: its cost and (state 2) its share of the directional derivative
-  for (int i = threadIdx.x; i < n; i += kThreads) {
-    const int e = e0 + i;
-    const int pl = __ldg(d.ppt + e) - p0;
-    const float4 m = __ldg(d.uv_p + e);
+  auto one = [&](int e, int pl, const float4 m, int sl) {
     const float uv[4] = {m.x, m.y, m.z, m.w};
     const double X[3] = {Xs[3 * pl], Xs[3 * pl + 1], Xs[3 * pl + 2]};
     CamPre cp;
     int f;
     if (staged) {
-      const int sl = d.oslot[e];
       const double* src = cps + 21 * sl;
 #pragma unroll
       for (int k = 0; k < 9; ++k) cp.R[k] = src[k];
@@ -2746,6 +2812,18 @@ __device__ __forceinline__ void dev_trial_points(const Dev& d, const DevParams& 
         for (int k = 0; k < 3; ++k) v[k] += G[3 * k] * dc[0] + G[3 * k + 1] * dc[1] + G[3 * k + 2] * dc[2] + dc[3 + k];
       }
       part[1] += h[0] * v[0] + h[1] * v[1] + h[2] * v[2];
+    }
+  };
+  if (pre) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int i = threadIdx.x + k * kThreads;
+      if (i < n) one(e0 + i, pre_pl[k], pre_m[k], pre_sl[k]);
+    }
+  } else {
+    for (int i = threadIdx.x; i < n; i += kThreads) {
+      const int e = e0 + i;
+      one(e, __ldg(d.ppt + e) - p0, __ldg(d.uv_p + e), staged ? (int)d.oslot[e] : 0);
     }
   }
   const double tot = block_sum<3>(part, sm);
@@ -3005,7 +3083,11 @@ __device__ __forceinline__ void dev_ls_reduce_one(const Dev& d, int nb) {
   if (threadIdx.x < 3) d.w_ls_red[(size_t)threadIdx.x * d.nwin] = tot;
 }
 
-__global__ void __launch_bounds__(kThreads) k_step_loop(Dev d, DevParams P, int fused_cams) {
+// (4 CTAs per SM: the step's phases are bound by L2 latency, not by registers; measured 2 -> 4: C4 step 1.08 -> 0.64 ms)
+#ifndef SBA_STEP_MIN_BLOCKS
+#define SBA_STEP_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(kThreads, SBA_STEP_MIN_BLOCKS) k_step_loop(Dev d, DevParams P, int fused_cams) {
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
   const int nb = gridDim.x;
   const bool one = d.nwin == 1 && d.npchunk > 4 * nb;      // one global window: two-level reductions

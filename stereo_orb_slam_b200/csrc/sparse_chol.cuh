@@ -136,13 +136,10 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
   }
   grid.sync();
   const bool prof = sc.profile && blockIdx.x == 0 && tid == 0;
-  unsigned long long tprev = prof ? gtimer() : 0;
-  auto lap = [&](const char* what, int lvl, int nchain) {
-    if (!prof) return;
-    const unsigned long long t = gtimer();
-    printf("[spchol] %s level %d (%d chains) %.1f us\n", what, lvl, nchain, (double)(t - tprev) * 1e-3);
-    tprev = t;
-  };
+  unsigned long long tstamp[48];                    // local memory, touched in profile mode only
+  int nstamp = 0;
+  if (prof) tstamp[nstamp++] = gtimer();
+  auto lap = [&]() { if (prof && nstamp < 48) tstamp[nstamp++] = gtimer(); };
   // ---- 1: factorisation + forward substitution: chains of one level in parallel, a chain's columns in sequence
   const int g = lane >> 2, t4 = lane & 3;
   const bool fout = g < 6 && t4 < 3;
@@ -369,7 +366,7 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
       }
     }
     grid.sync();
-    lap("fwd", lvl, c_end - c_begin);
+    lap();
   }
   // ---- 2: back substitution, levels downwards; a chain's columns in sequence (last first) by its CTA:
   //         x_j = Linv_jj^T (y_j - sum_i L_ij^T x_i), a thread per (block, column), partials summed in block order
@@ -513,7 +510,14 @@ __global__ void __launch_bounds__(kSpThreads, 1) k_spchol(Dev d, SpCholDev sc) {
       }
     }
     if (lvl > 0) grid.sync();
-    lap("bwd", lvl, c_end - c_begin);
+    lap();
+  }
+  if (prof) {
+    printf("[spchol] us per level, fwd:");
+    for (int i = 1; i <= sc.nlev && i < nstamp; ++i) printf(" %.1f", (double)(tstamp[i] - tstamp[i - 1]) * 1e-3);
+    printf(" | bwd (top first):");
+    for (int i = sc.nlev + 1; i < nstamp; ++i) printf(" %.1f", (double)(tstamp[i] - tstamp[i - 1]) * 1e-3);
+    printf(" | total %.1f\n", (double)(tstamp[nstamp - 1] - tstamp[0]) * 1e-3);
   }
 }
 

@@ -222,7 +222,11 @@ __global__ void __launch_bounds__(kRansacThreads) k_ransac_hypotheses(RansacDev 
   __shared__ float T12[12];
   __shared__ int wsum[kRansacThreads / 32];
   const int64_t hyp = (int64_t)pb * d.iters + it;
-  if (n <= 0) { if (threadIdx.x == 0) d.counts[hyp] = 0; return; }
+  if (n <= 0) {                        // no elements: count 0 and a zero model (sba.h: such a problem gets T = 0)
+    if (threadIdx.x == 0) d.counts[hyp] = 0;
+    if (threadIdx.x < 12) d.Thyp[hyp * 12 + threadIdx.x] = 0.f;
+    return;
+  }
   if (threadIdx.x == 0) {
     int64_t idx[3];
 #pragma unroll

@@ -265,6 +265,33 @@ int sba_ransac_stereo(sba_handle h, int32_t num_problems, const int64_t* offsets
  * + division by w (stereo_reprojection.h:79-92) for n stereo observations: xyz [n*3] f32 */
 int sba_triangulate_stereo(sba_handle h, int64_t n, const float* obs, const float* P_l, const float* P_r, float* xyz);
 
+/* ---- allocation-free variant of the stereo RANSAC alignment -------------------------------------- */
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same computation and
+ * same kernels as sba_ransac_stereo, but:
+ *   - inputs and outputs are DEVICE pointers supplied by the caller (d_offsets [num_problems+1] i64, d_obs_first /
+ *     d_obs_second [num_elements*4] f32 16-byte aligned, d_samples [num_problems*max_iterations*3] i32 or NULL = draw
+ *     from `seed`; d_T [num_problems*16] f32, d_labels [num_elements] u8, d_losses [num_elements] f32, optional
+ *     d_best_iteration [num_problems] i32 and d_counts [num_problems*max_iterations] i32); P_l / P_r / options are
+ *     small HOST arguments that travel as kernel parameters; sample indices are not validated (out-of-range -> 0);
+ *   - the scratch (triangulated points of both observation sets, the models of all hypotheses, and the counts /
+ *     chosen iteration when the caller passes NULL for them) lives in ONE file-scope device array of fixed size
+ *     (about 3 MiB, held by every GPU that loads the library until exit); problems beyond
+ *     SBA_NOALLOC_MAX_ELEMENTS elements in total or SBA_NOALLOC_MAX_HYPOTHESES = num_problems * max_iterations
+ *     hypotheses are rejected with SBA_INVALID_ARGUMENT;
+ *   - the call allocates nothing on the device or in pinned memory (no cudaMalloc* / cudaFree* / cudaHostAlloc, no
+ *     memory pool); it enqueues two memsets and three kernels on `stream` (a cudaStream_t; NULL = the handle's own
+ *     stream, and then the call also waits for completion) and otherwise returns without synchronising.
+ * Every call on a GPU shares the array and finds the previous call's contents in it (what must start at zero is
+ * cleared by the call itself): calls that overlap on the same GPU — different streams, different handles or
+ * processes' threads — RACE.  Serialise them. */
+#define SBA_NOALLOC_MAX_ELEMENTS   65536
+#define SBA_NOALLOC_MAX_HYPOTHESES 16384
+int sba_ransac_stereo_noalloc(sba_handle h, int32_t num_problems, int64_t num_elements, const int64_t* d_offsets,
+                              const float* d_obs_first, const float* d_obs_second, const float* P_l, const float* P_r,
+                              const sba_ransac_options* options, const int32_t* d_samples, uint64_t seed, float* d_T,
+                              uint8_t* d_labels, float* d_losses, int32_t* d_best_iteration, int32_t* d_counts, void* stream);
+
 /* ---- host side of BundleAdjuster::Optimize ------------------------------------------------------ */
 /* Pack window [start,end) of a map (reference: src/bundle_adjuster.cpp:41-110).
  *   T_wc [N*16] f32 row-major world-from-camera (Frame::GlobalPose), map_points [M*3] f32,

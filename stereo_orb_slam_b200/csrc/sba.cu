@@ -13,6 +13,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <mutex>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -1881,6 +1882,90 @@ int sba_triangulate_stereo(sba_handle h, int64_t n, const float* obs, const floa
   cudaStreamSynchronize(h->stream);
   h->allocs.swap(keep);
   return rc;
+}
+
+// ---- allocation-free RANSAC (no counterpart in the reference) ----------------
+// Scratch of sba_ransac_stereo_noalloc: one fixed array per GPU that loads this library.  In HOST code the name below
+// is only a stand-in for the symbol — its device address comes from cudaGetSymbolAddress, once per device.
+namespace {
+constexpr size_t kNaSrc = 0;                                                              // float4 [MAX_ELEMENTS]
+constexpr size_t kNaDst = kNaSrc + (size_t)SBA_NOALLOC_MAX_ELEMENTS * 16;                 // float4 [MAX_ELEMENTS]
+constexpr size_t kNaThyp = kNaDst + (size_t)SBA_NOALLOC_MAX_ELEMENTS * 16;                // float  [MAX_HYPOTHESES * 12]
+constexpr size_t kNaCounts = kNaThyp + (size_t)SBA_NOALLOC_MAX_HYPOTHESES * 48;           // int32  [MAX_HYPOTHESES]
+constexpr size_t kNaBest = kNaCounts + (size_t)SBA_NOALLOC_MAX_HYPOTHESES * 4;            // int32  [MAX_HYPOTHESES] (one per problem)
+constexpr size_t kNaBytes = kNaBest + (size_t)SBA_NOALLOC_MAX_HYPOTHESES * 4;
+constexpr int kNaMaxDevices = 64;
+}  // namespace
+static __device__ __align__(256) unsigned char g_ransac_noalloc_scratch[kNaBytes];
+static unsigned char* g_na_scratch_ptr[kNaMaxDevices] = {};      // device addresses of the array, by device ordinal
+static std::mutex g_na_mutex;
+
+// device address of the scratch array on h's device (resolved on first use, with that device current)
+static int noalloc_scratch(sba_handle h, unsigned char** out) {
+  if (h->device < 0 || h->device >= kNaMaxDevices) { set_error("sba_ransac_stereo_noalloc: device ordinal out of range"); return SBA_INVALID_ARGUMENT; }
+  std::lock_guard<std::mutex> lock(g_na_mutex);
+  if (!g_na_scratch_ptr[h->device]) {
+    CUDA_TRY(cudaSetDevice(h->device));
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_ransac_noalloc_scratch);
+    if (e != cudaSuccess || !p) { set_error(std::string("cudaGetSymbolAddress(scratch): ") + cudaGetErrorString(e)); return SBA_CUDA_ERROR; }
+    g_na_scratch_ptr[h->device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_na_scratch_ptr[h->device];
+  return SBA_OK;
+}
+
+int sba_ransac_stereo_noalloc(sba_handle h, int32_t num_problems, int64_t num_elements, const int64_t* d_offsets,
+                              const float* d_obs_first, const float* d_obs_second, const float* P_l, const float* P_r,
+                              const sba_ransac_options* options, const int32_t* d_samples, uint64_t seed, float* d_T,
+                              uint8_t* d_labels, float* d_losses, int32_t* d_best_iteration, int32_t* d_counts, void* stream) {
+  if (!h || num_problems < 0 || num_elements < 0 || !d_offsets || !P_l || !P_r || (num_problems > 0 && !d_T) ||
+      (num_elements > 0 && (!d_obs_first || !d_obs_second || !d_labels || !d_losses))) { set_error("sba_ransac_stereo_noalloc: bad arguments"); return SBA_INVALID_ARGUMENT; }
+  if (h->device < 0) { set_error("host-only handle: no CUDA device bound (there is no CPU fallback)"); return SBA_CUDA_ERROR; }
+  sba_ransac_options o;
+  if (options) o = *options; else sba_ransac_default_options(&o);
+  if (o.max_iterations < 0 || o.max_iterations > 65535 || !(o.inlier_threshold > 0.f)) { set_error("sba_ransac_stereo_noalloc: bad options (0 <= max_iterations <= 65535, inlier_threshold > 0)"); return SBA_INVALID_ARGUMENT; }
+  if (num_problems > 65535) { set_error("sba_ransac_stereo_noalloc: at most 65535 problems per call"); return SBA_INVALID_ARGUMENT; }
+  const int64_t nhyp = (int64_t)num_problems * std::max(o.max_iterations, 1);
+  if (num_elements > SBA_NOALLOC_MAX_ELEMENTS) {
+    set_error("sba_ransac_stereo_noalloc: " + std::to_string(num_elements) + " elements exceed the fixed scratch (SBA_NOALLOC_MAX_ELEMENTS = " +
+              std::to_string(SBA_NOALLOC_MAX_ELEMENTS) + "); use sba_ransac_stereo");
+    return SBA_INVALID_ARGUMENT;
+  }
+  if (nhyp > SBA_NOALLOC_MAX_HYPOTHESES) {
+    set_error("sba_ransac_stereo_noalloc: " + std::to_string(nhyp) + " hypotheses (problems x iterations) exceed the fixed scratch (SBA_NOALLOC_MAX_HYPOTHESES = " +
+              std::to_string(SBA_NOALLOC_MAX_HYPOTHESES) + "); use sba_ransac_stereo");
+    return SBA_INVALID_ARGUMENT;
+  }
+  if ((reinterpret_cast<uintptr_t>(d_obs_first) & 15) || (reinterpret_cast<uintptr_t>(d_obs_second) & 15)) { set_error("sba_ransac_stereo_noalloc: observation arrays must be 16-byte aligned"); return SBA_INVALID_ARGUMENT; }
+  if (num_problems == 0) return SBA_OK;
+  CUDA_TRY(cudaSetDevice(h->device));
+  unsigned char* scratch = nullptr;
+  { const int rc = noalloc_scratch(h, &scratch); if (rc) return rc; }
+  cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : h->stream;
+  const int iters = o.max_iterations;
+  RansacDev d{};
+  d.nprob = num_problems; d.iters = iters; d.seed = seed; d.thr_px = o.inlier_threshold; d.ratio = o.concensus_ratio;
+  d.final_fit = o.final_model_fitting ? 1 : 0; d.early = o.early_termination ? 1 : 0;
+  std::memcpy(d.Pl, P_l, 48); std::memcpy(d.Pr, P_r, 48);
+  d.off = d_offsets; d.first = reinterpret_cast<const float4*>(d_obs_first); d.second = reinterpret_cast<const float4*>(d_obs_second);
+  d.samples = iters > 0 ? d_samples : nullptr;
+  d.src = reinterpret_cast<float4*>(scratch + kNaSrc); d.dst = reinterpret_cast<float4*>(scratch + kNaDst);
+  d.Thyp = reinterpret_cast<float*>(scratch + kNaThyp);
+  d.counts = d_counts ? d_counts : reinterpret_cast<int32_t*>(scratch + kNaCounts);
+  d.best_it = d_best_iteration ? d_best_iteration : reinterpret_cast<int32_t*>(scratch + kNaBest);
+  d.T_out = d_T; d.labels = d_labels; d.losses = d_losses;
+  // the array keeps the previous call's contents: a problem without elements writes no model, and one without
+  // iterations no count — both regions are read by the finish kernel and start from zero
+  CUDA_TRY(cudaMemsetAsync(d.Thyp, 0, (size_t)nhyp * 48, st));
+  if (iters > 0) CUDA_TRY(cudaMemsetAsync(d.counts, 0, (size_t)num_problems * iters * 4, st));
+  const int64_t n = num_elements;
+  if (n > 0) { k_ransac_triangulate<<<(unsigned)cdiv(2 * n, 128), 128, 0, st>>>(d, n, 2 * n); h->launches++; }
+  if (iters > 0) { k_ransac_hypotheses<<<dim3((unsigned)iters, (unsigned)num_problems), kRansacThreads, 0, st>>>(d); h->launches++; }
+  k_ransac_finish<<<num_problems, kRansacFinishThreads, 0, st>>>(d); h->launches++;
+  CUDA_TRY(cudaGetLastError());
+  if (!stream) CUDA_TRY(cudaStreamSynchronize(st));
+  return SBA_OK;
 }
 
 // ---- multi-GPU --------------------------------------------------------------------------------------

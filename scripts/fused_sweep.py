@@ -16,8 +16,7 @@ if len(sys.argv) > 1 and sys.argv[1] == "one":
     out.update(solve_ms=1e3 * s["time_solve_s"], its=s["iterations"], dev={k: round(s[k], 2) for k in ("ms_linearize", "ms_schur", "ms_pcg", "ms_update")})
     print(json.dumps(out))
 else:
-    for env in ({}, {"SBA_NO_FUSED": "1"}, {"SBA_FUSED_OCC": "3", "SBA_OBS_CAP": "200"}, {"SBA_FUSED_OCC": "3", "SBA_OBS_CAP": "160"},
-                {"SBA_FUSED_OCC": "2", "SBA_OBS_CAP": "200"}, {"SBA_FUSED_OCC": "3"}):
+    for env in ({}, {"SBA_OBS_CAP": "120"}):
         e = dict(os.environ); e.update(env)
         r = subprocess.run([sys.executable, __file__, "one"], env=e, capture_output=True, text=True)
         print(env, r.stdout.strip().splitlines()[-1] if r.stdout.strip() else r.stderr[-300:], flush=True)

@@ -585,21 +585,29 @@ __global__ void k_campre(Dev d) {
 //      warp per slot: sum of Z u -> rpart
 constexpr int kFusedThreads = 256;
 constexpr int kFZStride = 19;      // odd: observation rows of Z fall into different banks
+constexpr int kFIdxSlots = 64;     // k_fused_chunk stages the index tables of chunks with at most this many camera slots
+constexpr int kFIdxLb = 192;       // ... and at most this many local blocks (others read them from global memory)
 
 __host__ __device__ __forceinline__ size_t fused_smem_bytes(int n, int np, int ns) {
   return ((size_t)n * (kCamStride + 9) + (size_t)ns * 21 + (size_t)np * 12) * 8 + (size_t)((n + 15) & ~15);
 }
 
-template <int OCC>
-__global__ void __launch_bounds__(kFusedThreads, OCC) k_fused_chunk(Dev d, DevParams P) {
+__device__ __forceinline__ unsigned long long gtimer();
+// NT threads per CTA: 256 for chunks of up to 255 observations, 128 for chunks of up to 128 (twice the CTAs per SM)
+template <int OCC, bool PROF = false, int NT = kFusedThreads>
+__global__ void __launch_bounds__(NT, OCC) k_fused_chunk(Dev d, DevParams P) {
+  // PROF (SBA_DEBUG_LS=2, sba_time_stage 11): thread 0 of a few CTAs prints the nanoseconds between the phase boundaries
+  unsigned long long tph[8]; int nph = 0;
+  auto mark = [&]() { if constexpr (PROF) { if (threadIdx.x == 0 && nph < 8) tph[nph++] = gtimer(); } };
+  mark();
   extern __shared__ __align__(16) double smem[];
-  __shared__ double sm1[kFusedThreads / 32];
-  __shared__ double smx[kFusedThreads / 32];
+  __shared__ double sm1[NT / 32];
+  __shared__ double smx[NT / 32];
   const int chunk = blockIdx.x;
   const int4 c0 = __ldg(d.cdesc + 4 * (size_t)chunk), c1 = __ldg(d.cdesc + 4 * (size_t)chunk + 1), c2 = __ldg(d.cdesc + 4 * (size_t)chunk + 2);
   const int p0 = c0.x, np = c0.y, e0 = c0.z, n = c0.w;
   if (n > kMaxSlots) return;                               // a long track: k_lin_long + k_schur_long
-  const int w = c1.x, cs0 = c1.y, ns = c1.z, cs1 = cs0 + ns, lb0 = c1.w, lb1 = c1.w + c2.x;
+  const int w = c1.x, cs0 = c1.y, ns = c1.z, lb0 = c1.w, lb1 = c1.w + c2.x;
   const int pq0 = c2.y, npq = c2.z;
   double* cam_st = smem;                                   // [n * 27]  A: camera-side terms;  C/D: Z [n * 19]
   double* pt_st = cam_st + (size_t)n * kCamStride;         // [n * 9]   A: V, gp terms;        C/D: pair lists
@@ -608,28 +616,60 @@ __global__ void __launch_bounds__(kFusedThreads, OCC) k_fused_chunk(Dev d, DevPa
   double* Li = xs + (size_t)np * 3;                        // [np * 6]  Linv: 00 10 11 20 21 22
   double* us = Li + (size_t)np * 6;                        // [np * 3]  u = Linv gp
   uint8_t* opl = reinterpret_cast<uint8_t*>(us + (size_t)np * 3);   // [n] chunk-local point of each observation
-  double* Z = cam_st;
+  double* Z = cam_st + 1;                                  // one zero element in front of row 0 (see phase D)
   // pair lists staged as BYTE offsets of the two Z rows (a * 152 | b * 152 << 16): the inner loop spends its issue
   // slots on the two loads and the MMA, not on unpacking indices
   uint32_t* prs = reinterpret_cast<uint32_t*>(pt_st);
   const bool pairs_staged = (size_t)npq * 4 <= (size_t)n * 72;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  constexpr int NW = kFusedThreads / 32;
-  // ---- stage: independent loads only
+  constexpr int NW = NT / 32;
+  __shared__ int s_off[kFIdxSlots + 1];      // slot -> first entry of s_sobs
+  __shared__ int s_pos[kFIdxSlots];          // slot -> row of cspart / rpart, -1 for a fixed camera
+  __shared__ int s_lbq[kFIdxLb + 1];         // local block -> first pair (relative to the chunk's list)
+  __shared__ int s_lbpos[kFIdxLb];           // local block -> row of spart
+  __shared__ uint8_t s_sobs[256];            // chunk-local observation indices grouped by slot
+  const bool idx_staged = ns <= kFIdxSlots && lb1 - lb0 <= kFIdxLb;
+  // range of slot sl in the grouped observation list (chunk-local), its output row (-1: fixed camera), an entry of the list
+  auto slot_of = [&](int sl, int& j0, int& j1) -> int {
+    if (idx_staged) { j0 = s_off[sl]; j1 = s_off[sl + 1]; return s_pos[sl]; }
+    const int cs = cs0 + sl;
+    j0 = d.cs_obs_off[cs] - e0; j1 = d.cs_obs_off[cs + 1] - e0;
+    return (d.fc[d.cs_cam[cs]] >= 0) ? d.cs_pos[cs] : -1;
+  };
+  auto sobs_at = [&](int j) -> int { return idx_staged ? (int)s_sobs[j] : (int)__ldg(d.sobs + e0 + j); };
+  // ---- stage.  ALL global loads first, into registers, in two dependency levels; the shared-memory stores after them.
+  // (The pointers in Dev are generic: the compiler will not move a global load above a shared store, so a sequence of
+  // "load, store" loops costs one round trip to L2 per loop.)
   const int i = threadIdx.x;
   const bool act = i < n;
+  const int nlb = lb1 - lb0;
+  // level 1: everything addressed by the chunk record alone
   int sl = 0, pl = 0;
   float4 m = make_float4(0.f, 0.f, 0.f, 0.f);
   if (act) {
     sl = d.oslot[e0 + i];
     pl = __ldg(d.ppt + e0 + i) - p0;
     m = __ldg(d.uv_p + e0 + i);
-    opl[i] = (uint8_t)pl;
   }
-  for (int k = threadIdx.x; k < np * 3; k += kFusedThreads) xs[k] = d.pts[(size_t)p0 * 3 + k];
-  for (int k = threadIdx.x; k < ns * 21; k += kFusedThreads) {
-    const int s = k / 21;
-    cpre[k] = reinterpret_cast<const double*>(d.campre + __ldg(d.cs_cam + cs0 + s))[k - 21 * s];
+  constexpr int KX = (kPointChunk * 3 + NT - 1) / NT, KL = (kFIdxLb + NT) / NT;    // point coordinates / block-table entries per thread
+  double x_r[KX];
+#pragma unroll
+  for (int u = 0; u < KX; ++u) x_r[u] = (i + u * NT < np * 3) ? d.pts[(size_t)p0 * 3 + i + u * NT] : 0.0;
+  const int cp_s = i / 21;                                          // camera-table element i of the staged block
+  const int cp_cam = (i < ns * 21) ? __ldg(d.cs_cam + cs0 + cp_s) : -1;
+  static_assert(kFIdxSlots < NT, "one slot entry per thread");
+  int r_sobs = 0, r_off = 0, r_cam = -1, r_pos = 0, r_lbq[KL], r_lbpos[KL];
+#pragma unroll
+  for (int u = 0; u < KL; ++u) { r_lbq[u] = 0; r_lbpos[u] = 0; }
+  if (idx_staged) {
+    if (act) r_sobs = (int)__ldg(d.sobs + e0 + i);
+    if (i <= ns) r_off = __ldg(d.cs_obs_off + cs0 + i) - e0;
+    if (i < ns) { r_cam = __ldg(d.cs_cam + cs0 + i); r_pos = __ldg(d.cs_pos + cs0 + i); }
+#pragma unroll
+    for (int u = 0; u < KL; ++u) {
+      if (i + u * NT <= nlb) r_lbq[u] = __ldg(d.lb_pair_off + lb0 + i + u * NT) - pq0;
+      if (i + u * NT < nlb) r_lbpos[u] = __ldg(d.lb_pos + lb0 + i + u * NT);
+    }
   }
   // the point threads request what phase B needs now (it arrives while phase A computes)
   const int q = threadIdx.x;
@@ -641,7 +681,31 @@ __global__ void __launch_bounds__(kFusedThreads, OCC) k_fused_chunk(Dev d, DevPa
   }
   const double radius = d.w_radius[w];
   const int pe0 = has_pt ? d.pt_off[p0 + q] - e0 : 0, pe1 = has_pt ? d.pt_off[p0 + q + 1] - e0 : 0;
+  // level 2: what a level-1 index addresses
+  const double cp_v = (cp_cam >= 0) ? reinterpret_cast<const double*>(d.campre + cp_cam)[i - 21 * cp_s] : 0.0;
+  const int r_fc = (r_cam >= 0) ? d.fc[r_cam] : -1;
+  // stores
+  if (act) opl[i] = (uint8_t)pl;
+#pragma unroll
+  for (int u = 0; u < KX; ++u) if (i + u * NT < np * 3) xs[i + u * NT] = x_r[u];
+  if (cp_cam >= 0) cpre[i] = cp_v;
+  if (idx_staged) {
+    if (act) s_sobs[i] = (uint8_t)r_sobs;
+    if (i <= ns) s_off[i] = r_off;
+    if (i < ns) s_pos[i] = (r_fc >= 0) ? r_pos : -1;
+#pragma unroll
+    for (int u = 0; u < KL; ++u) {
+      if (i + u * NT <= nlb) s_lbq[i + u * NT] = r_lbq[u];
+      if (i + u * NT < nlb) s_lbpos[i + u * NT] = r_lbpos[u];
+    }
+  }
+  // chunks with more than 12 camera slots: the rest of the camera table
+  for (int k = i + NT; k < ns * 21; k += NT) {
+    const int s = k / 21;
+    cpre[k] = reinterpret_cast<const double*>(d.campre + __ldg(d.cs_cam + cs0 + s))[k - 21 * s];
+  }
   __syncthreads();
+  mark();
   // ---- A
   double cost = 0.0;
   double W[18];
@@ -677,6 +741,7 @@ __global__ void __launch_bounds__(kFusedThreads, OCC) k_fused_chunk(Dev d, DevPa
     for (int k = 0; k < 9; ++k) Wo[k] = make_double2(W[2 * k], W[2 * k + 1]);
   }
   __syncthreads();
+  mark();
   // ---- B: per point V, gp, damped Cholesky
   double gmax = 0.0;
   if (has_pt) {
@@ -732,16 +797,17 @@ __global__ void __launch_bounds__(kFusedThreads, OCC) k_fused_chunk(Dev d, DevPa
     Li[q * 6] = i00; Li[q * 6 + 1] = i10; Li[q * 6 + 2] = i11; Li[q * 6 + 3] = i20; Li[q * 6 + 4] = i21; Li[q * 6 + 5] = i22;
     us[q * 3] = u0; us[q * 3 + 1] = u1; us[q * 3 + 2] = u2;
   }
+  mark();
   // ---- per camera slot: U (21) + gc (6), one warp per slot, dealt from the last warp down (the point threads sit
   //      in the first warps); same fixed order as k_lin_chunk
-  for (int cs = cs0 + (NW - 1 - warp); cs < cs1; cs += NW) {
-    const int c = d.cs_cam[cs];
-    if (d.fc[c] < 0) continue;        // a fixed camera is not an unknown (src/bundle_adjuster.cpp:113)
+  for (int sl = NW - 1 - warp; sl < ns; sl += NW) {
+    int j0, j1;
+    const int row = slot_of(sl, j0, j1);
+    if (row < 0) continue;            // a fixed camera is not an unknown (src/bundle_adjuster.cpp:113)
     double s0 = 0.0, s1 = 0.0;
-    const int j0 = d.cs_obs_off[cs], j1 = d.cs_obs_off[cs + 1];
     const double* col = cam_st + (lane < 27 ? lane : 0);
     for (int jb = j0; jb < j1; jb += 32) {
-      const int mine_o = (jb + lane < j1) ? (int)__ldg(d.sobs + jb + lane) : 0;
+      const int mine_o = (jb + lane < j1) ? sobs_at(jb + lane) : 0;
       const int mm = min(32, j1 - jb);
       int t = 0;
       for (; t + 3 < mm; t += 4) {
@@ -756,7 +822,7 @@ __global__ void __launch_bounds__(kFusedThreads, OCC) k_fused_chunk(Dev d, DevPa
         if (t & 1) s1 += v; else s0 += v;
       }
     }
-    if (lane < 27) d.cspart[(size_t)d.cs_pos[cs] * 27 + lane] = s0 + s1;
+    if (lane < 27) d.cspart[(size_t)row * 27 + lane] = s0 + s1;
   }
   // chunk cost and projected-gradient max: warp partials now, summed after the next barrier
 #pragma unroll
@@ -769,6 +835,7 @@ __global__ void __launch_bounds__(kFusedThreads, OCC) k_fused_chunk(Dev d, DevPa
     for (int k = 0; k < NW; ++k) { t += sm1[k]; mx = fmax(mx, smx[k]); }
     d.lin_part[2 * chunk] = t; d.lin_part[2 * chunk + 1] = mx;
   }
+  mark();
   // ---- C: Z = W Linv^T from the registers into the dead camera staging area; pair lists into the dead point staging area
   if (act) {
     const double* L = Li + pl * 6;
@@ -783,21 +850,27 @@ __global__ void __launch_bounds__(kFusedThreads, OCC) k_fused_chunk(Dev d, DevPa
     }
     z[18] = 0.0;                       // the pad element: what the lanes outside the 6x3 operand feed to the MMA
   }
+  if (threadIdx.x == 0) cam_st[0] = 0.0;
   constexpr unsigned kRowBytes = kFZStride * 8;
   static_assert(255u * kRowBytes < 65536u, "row offsets fit 16 bits");
   if (pairs_staged)
-    for (int k = threadIdx.x; k < npq; k += kFusedThreads) {
+    for (int k = threadIdx.x; k < npq; k += NT) {
       const unsigned pr = __ldg(d.pairs + pq0 + k);
       prs[k] = (pr & 255u) * kRowBytes | ((pr >> 8) * kRowBytes) << 16;
     }
   __syncthreads();
+  mark();
   // ---- D: local blocks, one warp per block, one FP64 tensor-core MMA (m8n8k4) per pair (see k_schur_chunk).  Lane
   //      (g, t) feeds element 3 g + t of both rows; the lanes outside the 6x3 operand read the rows' zero pad.
   const int g = lane >> 2, t = lane & 3;
   const bool feeds = g < 6 && t < 3;
-  const char* Zl = reinterpret_cast<const char*>(Z + (feeds ? 3 * g + t : 18));
+  // The idle lanes read a zero: the pad behind the row (element 18) in the upper half-warp, the pad in front of it
+  // (element -1 = the previous row's pad) in the lower one.  A 64-bit load is served half-warp by half-warp; in the lower
+  // half elements 0..11 occupy 24 consecutive banks and element 18 falls on the bank of element 2 (a 2-way conflict on
+  // every operand load), element -1 does not; in the upper half (elements 12..17) it is the other way round.
+  const char* Zl = reinterpret_cast<const char*>(Z + (feeds ? 3 * g + t : (lane < 16 ? -1 : 18)));
   for (int lb = lb0 + warp; lb < lb1; lb += NW) {
-    const int q0 = d.lb_pair_off[lb] - pq0, q1 = d.lb_pair_off[lb + 1] - pq0;
+    const int q0 = idx_staged ? s_lbq[lb - lb0] : d.lb_pair_off[lb] - pq0, q1 = idx_staged ? s_lbq[lb - lb0 + 1] : d.lb_pair_off[lb + 1] - pq0;
     double a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0;
     auto mma_off = [&](unsigned en, double& x0, double& x1) {
       const double a = *reinterpret_cast<const double*>(Zl + (en & 0xffffu));
@@ -826,16 +899,17 @@ __global__ void __launch_bounds__(kFusedThreads, OCC) k_fused_chunk(Dev d, DevPa
       for (; qq + 1 < q1; qq += 2) { mma_idx(__ldg(gp + qq), a0, a1); mma_idx(__ldg(gp + qq + 1), b0, b1); }
       if (qq < q1) mma_idx(__ldg(gp + qq), a0, a1);
     }
-    if (feeds) *reinterpret_cast<double2*>(d.spart + (size_t)d.lb_pos[lb] * 36 + 6 * g + 2 * t) = make_double2(a0 + b0, a1 + b1);
+    if (feeds) *reinterpret_cast<double2*>(d.spart + (size_t)(idx_staged ? s_lbpos[lb - lb0] : d.lb_pos[lb]) * 36 + 6 * g + 2 * t) = make_double2(a0 + b0, a1 + b1);
   }
+  mark();
   // ---- right-hand side partials: sum over the slot's observations of W_e tp[point(e)] = Z_e u[point(e)]
-  for (int cs = cs0 + (NW - 1 - warp); cs < cs1; cs += NW) {
-    const int c = d.cs_cam[cs];
-    if (d.fc[c] < 0) continue;
+  for (int sl = NW - 1 - warp; sl < ns; sl += NW) {
+    int j0, j1;
+    const int row = slot_of(sl, j0, j1);
+    if (row < 0) continue;
     double acc[6] = {0, 0, 0, 0, 0, 0};
-    const int j1 = d.cs_obs_off[cs + 1];
-    for (int j = d.cs_obs_off[cs] + lane; j < j1; j += 32) {
-      const int o = d.sobs[j];
+    for (int j = j0 + lane; j < j1; j += 32) {
+      const int o = sobs_at(j);
       const double* zz = Z + (size_t)o * kFZStride;
       const double* u = us + (int)opl[o] * 3;
       const double t0 = u[0], t1 = u[1], t2 = u[2];
@@ -850,7 +924,13 @@ __global__ void __launch_bounds__(kFusedThreads, OCC) k_fused_chunk(Dev d, DevPa
       for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
       if (lane == r) mine = x;
     }
-    if (lane < 6) d.rpart[(size_t)d.cs_pos[cs] * 6 + lane] = mine;
+    if (lane < 6) d.rpart[(size_t)row * 6 + lane] = mine;
+  }
+  if constexpr (PROF) {
+    mark();
+    if (threadIdx.x == 0 && (blockIdx.x % 211) == 0)
+      printf("[fused] cta %d n %d np %d ns %d pairs %d | stage %llu A %llu B %llu slots %llu C %llu D %llu rhs %llu | total %llu ns\n", (int)blockIdx.x, n, np, ns, npq,
+             tph[1] - tph[0], tph[2] - tph[1], tph[3] - tph[2], tph[4] - tph[3], tph[5] - tph[4], tph[6] - tph[5], tph[7] - tph[6], tph[7] - tph[0]);
   }
 }
 

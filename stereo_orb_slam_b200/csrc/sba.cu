@@ -105,7 +105,7 @@ struct sba_handle_s {
   bool chol_cluster_ok = false; size_t chol_cluster_smem = 0;   // mid-size windows: one 8-CTA cluster per window (k_chol_cluster)
   bool chol_band_ok = false; size_t chol_band_smem = 0; const int32_t* band_last = nullptr;   // banded windows: envelope in one CTA's shared memory (k_chol_band)
   size_t lin_smem = 0, schur_smem = 0;   // dynamic shared memory of the per-chunk kernels (largest chunk)
-  size_t fused_smem = 0; bool fused_ok = false; int fused_occ = 2;   // k_fused_chunk (K1-K3 of a chunk in one CTA)
+  size_t fused_smem = 0; bool fused_ok = false; int fused_occ = 2; int fused_nt = 256;   // k_fused_chunk (K1-K3 of a chunk in one CTA)
   bool schur_fresh = false;              // the last linearisation was fused: spart / rpart already hold this radius' Schur partials
   // ... and on a single GPU its camera-side assembly and finish are left to the next do_schur (one assemble kernel for
   // U / gc / S / rhs; cost + gradient test on the side stream while the solve runs)
@@ -387,11 +387,17 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   AL(d.campre_new, nc) AL(d.campre, nc)
   if (d.nlong > 0) AL(d.zlong, (size_t)H.long_zoff.back() * 18)
   AL(d.W, nobs * 18) AL(d.V, np * 6) AL(d.gp, np * 3) AL(d.Vinv, np * 6) AL(d.tp, np * 3)
-  AL(d.U, nc * 27 + nw + nw * kMaxRanks)   // U | gc | cost_red | gslots: one block, one all-reduce per linearisation (multi-GPU)
+  // U | gc | cost_red | gslots | (pad) | Su | rsum: ONE block.  Multi-GPU: one all-reduce per linearisation over the
+  // first four, one per Schur step over the last two — or, after a fused linearisation, a single one over everything
+  // (the never-written gap between them stays zero)
+  const size_t lin_len = ((nc * 27 + nw + nw * kMaxRanks) + 31) & ~(size_t)31;
+  AL(d.U, lin_len + (size_t)d.nbu * 36 + nf * 6)
+  CUDA_TRY(cudaMemsetAsync(d.U, 0, (lin_len + (size_t)d.nbu * 36 + nf * 6) * sizeof(double), h->stream));
   d.gc = d.U + nc * 21; d.cost_red = d.gc + nc * 6; d.gslots = d.cost_red + nw;
+  d.Su = d.U + lin_len;
   AL(d.cspart, (size_t)d.ncs * 27)
   AL(d.sc2c, nc * 6) AL(d.sc2p, np * 3) AL(d.lin_part, (size_t)d.npchunk * 2)
-  AL(d.spart, (size_t)d.nlb * 36) AL(d.Su, (size_t)d.nbu * 36 + nf * 6) AL(d.rpart, (size_t)d.ncs * 6)
+  AL(d.spart, (size_t)d.nlb * 36) AL(d.rpart, (size_t)d.ncs * 6)
   d.rsum = d.Su + (size_t)d.nbu * 36;      // Su | rsum: one block, one all-reduce per Schur step (multi-GPU)
   AL(d.rhs, nf * 6) AL(d.Minv, nf * 36)
   AL(d.x, nf * 6) AL(d.r, nf * 6) AL(d.z, nf * 6) AL(d.p, nf * 6) AL(d.Ap, nf * 6) AL(h->pcg_pbuf, nf * 6) AL(h->pcg_rowdot, 2 * nf)
@@ -437,6 +443,8 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
       h->fused_occ = (std::getenv("SBA_FUSED_OCC") && std::atoi(std::getenv("SBA_FUSED_OCC")) == 3) ? 3 : 2;   // tuning aid: 3 CTAs / SM (85 registers, spills)
       CUDA_TRY(cudaFuncSetAttribute(k_fused_chunk<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fused_smem, 1024)));
       CUDA_TRY(cudaFuncSetAttribute(k_fused_chunk<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fused_smem, 1024)));
+      CUDA_TRY(cudaFuncSetAttribute((k_fused_chunk<4, false, 128>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fused_smem, 1024)));
+      h->fused_nt = (H.max_chunk_obs <= 128 && H.max_chunk_pts <= 128 && !std::getenv("SBA_FUSED_NT256")) ? 128 : 256;
     }
   }
   {
@@ -626,6 +634,15 @@ int sba_get_state(sba_handle h, double* poses, double* points) {
 
 // K0 + K1 + K2 at the current state (d.poses / d.pts).
 // `stream` waits for the forked tail of the last linearisation (no-op when none is pending)
+// the fused K1-K3 chunk kernel: 128-thread CTAs (4 per SM) when every regular chunk has at most 128 observations
+static void launch_fused(sba_handle h) {
+  const Dev& d = h->d; const DevParams& P = h->P;
+  if (h->fused_nt == 128) k_fused_chunk<4, false, 128><<<d.npchunk, 128, h->fused_smem, h->stream>>>(d, P);
+  else if (h->fused_occ == 3) k_fused_chunk<3><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
+  else k_fused_chunk<2><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
+  h->launches++;
+}
+
 static int join_tail(sba_handle h) {
   if (!h->tail_pending) return SBA_OK;
   CUDA_TRY(cudaEventRecord(h->ev_join, h->side));
@@ -650,9 +667,7 @@ static int do_linearize(sba_handle h, bool keep_cost = false, bool fork_tail = f
   LAUNCH(h, k_campre, cdiv(d.Nc, 128), 128, d);      // K0: camera table of this linearisation
   if (fused) {
     CUDA_TRY(cudaMemsetAsync(d.w_fail, 0, (size_t)d.nwin * 4, h->stream));      // the chunk kernel reports singular point blocks
-    if (h->fused_occ == 3) k_fused_chunk<3><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
-    else k_fused_chunk<2><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
-    h->launches++;
+    launch_fused(h);
     h->schur_fresh = true;
   } else if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; }
   if (d.nlong > 0) {        // long tracks (> 255 observations of one point): their own kernels, same partial lists
@@ -660,7 +675,7 @@ static int do_linearize(sba_handle h, bool keep_cost = false, bool fork_tail = f
     if (fused) { LAUNCH(h, k_schur_long, d.nlong, kLongThreads, d); LAUNCH(h, k_schur_long_pairs, 296, 256, d); }
   }
   h->cams_pending = false;
-  if (fused && fork_tail && !h->comm.active() && !std::getenv("SBA_NO_FORK")) {
+  if (fused && fork_tail && !std::getenv("SBA_NO_FORK")) {      // single GPU and point-sharded alike
     h->cams_pending = true; h->pend_keep_cost = keep_cost; h->pend_lm_begin = lm_begin; h->pend_radius = initial_radius;
     CUDA_TRY(cudaGetLastError());
     return SBA_OK;
@@ -712,6 +727,20 @@ static int do_schur(sba_handle h, bool exact_solver = false) {
     // after a fused linearisation (single GPU): ONE assemble kernel for U / gc / S / rhs, then the window cost and the
     // gradient test on the side stream while the linear solve runs (do_step joins)
     h->cams_pending = false;
+    if (h->comm.active()) {
+      // point-sharded: this rank's share of U | gc | S | rsum by ONE assemble kernel, its cost and gradient maximum,
+      // then ONE all-reduce over the whole block instead of one per linearisation plus one per Schur step
+      const int world = h->comm.world;
+      LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 2);
+      LAUNCH(h, k_lin_finish_local, d.nwin, kThreads, d, h->comm.rank, world);
+      std::string _err;
+      if (!h->comm.allreduce(d.U, (size_t)((d.rsum + (size_t)d.Nf * 6) - d.U), false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+      LAUNCH(h, k_lin_finish_global, d.nwin, kThreads, d, h->P, h->pend_keep_cost ? 1 : 0, world);
+      if (h->pend_lm_begin >= 0) LAUNCH(h, k_lm_begin, cdiv(d.nwin, 128), 128, d, h->P, h->pend_radius, h->pend_lm_begin, 0);
+      LAUNCH(h, k_cam_prepare, cdiv(d.Nf, 64), 64, d);
+      CUDA_TRY(cudaGetLastError());
+      return SBA_OK;
+    }
     stamp(h, h->stream, 0);
     LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 3 | (exact_solver ? 4 : 0));
     stamp(h, h->stream, 1);
@@ -1065,8 +1094,11 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
         if (!h->fused_ok) { set_error("fused chunk kernel unavailable for this structure"); return SBA_INVALID_ARGUMENT; }
         if (i == 0) { LAUNCH(h, k_campre, cdiv(d.Nc, 128), 128, d); CUDA_TRY(cudaEventRecord(h->ev[6], h->stream)); }
         if (d.npchunk > 0) {
-          if (h->fused_occ == 3) k_fused_chunk<3><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
-          else k_fused_chunk<2><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
+          if (P.debug == 2 && i == 0) {
+            cudaFuncSetAttribute(k_fused_chunk<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fused_smem);
+            k_fused_chunk<2, true><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
+          }
+          else { launch_fused(h); h->launches--; }
           h->launches++;
         }
         break;
@@ -1222,7 +1254,15 @@ int sba_run(sba_handle h, const sba_options* opt, sba_summary* sum) {
   if (h->cams_pending) {      // the last linearisation's camera-side assembly was left to a Schur step that never came
     h->cams_pending = false;
     LAUNCH(h, k_assemble_cams, d.Nf, kAsmThreads, d);
-    LAUNCH(h, k_lin_finish, d.nwin, kThreads, d, P, h->pend_keep_cost ? 1 : 0);
+    if (h->comm.active()) {
+      const int world = h->comm.world;
+      LAUNCH(h, k_lin_finish_local, d.nwin, kThreads, d, h->comm.rank, world);
+      std::string _err;
+      if (!h->comm.allreduce(d.U, (size_t)d.Nc * 27 + (size_t)d.nwin + (size_t)d.nwin * world, false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
+      LAUNCH(h, k_lin_finish_global, d.nwin, kThreads, d, P, h->pend_keep_cost ? 1 : 0, world);
+    } else {
+      LAUNCH(h, k_lin_finish, d.nwin, kThreads, d, P, h->pend_keep_cost ? 1 : 0);
+    }
     if (h->pend_lm_begin >= 0) LAUNCH(h, k_lm_begin, cdiv(d.nwin, 128), 128, d, P, h->pend_radius, h->pend_lm_begin, 0);
   }
   std::vector<int32_t> st((size_t)d.nwin), its((size_t)d.nwin), succ((size_t)d.nwin);

@@ -175,11 +175,17 @@ def test_banded_cholesky_of_a_batch_of_windows_equals_numpy(frames, track):
     assert np.array_equal(s.schur_values()[2], x)                       # bit-reproducible
 
 
-def test_fused_chunk_kernel_equals_the_two_kernel_path_bit_for_bit(small_window, monkeypatch):
+@pytest.mark.parametrize("case", ["few_slots", "many_slots", "small_chunks"])
+def test_fused_chunk_kernel_equals_the_two_kernel_path_bit_for_bit(small_window, monkeypatch, case):
     """k_fused_chunk (K1-K3 of a chunk in one CTA, W kept in registers) against k_lin_chunk + k_schur_chunk (W through
-    HBM): same operations in the same order, so the reduced system and the whole LM trajectory agree to the bit."""
+    HBM): same operations in the same order, so the reduced system and the whole LM trajectory agree to the bit.
+    few_slots: the chunk's index tables are staged in shared memory; many_slots (every point seen by 30 cameras: 465
+    local blocks per chunk): they are read from global memory; small_chunks: the 128-thread variant."""
     monkeypatch.delenv("SBA_NO_FUSED", raising=False)
-    w = c2_window() if False else small_window
+    monkeypatch.delenv("SBA_OBS_CAP", raising=False)
+    if case == "small_chunks":
+        monkeypatch.setenv("SBA_OBS_CAP", "100")
+    w = make_window(30, 300, 30, seed=17) if case == "many_slots" else small_window
     s = load(w)
     s.linearize(); s.schur(1e4)
     ref = s.schur_values()

@@ -34,7 +34,8 @@ struct ChunkTab {
 struct Work {
   std::vector<ChunkRange> cr;
   std::vector<ChunkTab> tab;
-  std::vector<int32_t> gpt_off, gperm, pt_win;
+  std::vector<int32_t> gpt_off, gperm, pt_win, tmp;
+  std::vector<int64_t> hist;
 };
 
 // chunk boundaries over ALL points (unowned ones only feed the block pattern): never across a window, never
@@ -140,19 +141,78 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
   // ---- validate + global point-order counting sort (stable in input order)
   std::vector<int32_t>& gpt_off = Wk.gpt_off;
   gpt_off.assign((size_t)Np + 1, 0);
-  for (int64_t k = 0; k < NobsAll; ++k) {
-    const int32_t c = obs_cam[k], p = obs_pt[k];
-    if (c < 0 || c >= Nc) return "obs_cam out of range";
-    if (p < 0 || p >= Np) return "obs_pt out of range";
-    if (H.cam_win[c] != pt_win[p]) return "observation links a camera and a point of different windows";
-    gpt_off[p + 1]++;
-  }
-  for (int p = 0; p < Np; ++p) gpt_off[p + 1] += gpt_off[p];
   std::vector<int32_t>& gperm = Wk.gperm;
   gperm.resize((size_t)NobsAll);
-  {
+  if (NobsAll < 65536 || nthreads < 2) {
+    for (int64_t k = 0; k < NobsAll; ++k) {
+      const int32_t c = obs_cam[k], p = obs_pt[k];
+      if (c < 0 || c >= Nc) return "obs_cam out of range";
+      if (p < 0 || p >= Np) return "obs_pt out of range";
+      if (H.cam_win[c] != pt_win[p]) return "observation links a camera and a point of different windows";
+      gpt_off[p + 1]++;
+    }
+    for (int p = 0; p < Np; ++p) gpt_off[p + 1] += gpt_off[p];
     std::vector<int32_t> cur(gpt_off.begin(), gpt_off.end() - 1);
     for (int64_t k = 0; k < NobsAll; ++k) gperm[cur[obs_pt[k]]++] = (int32_t)k;
+  } else {
+    // two stable levels, both parallel: (1) every thread scatters its contiguous slice of the input into buckets of
+    // 2^shift consecutive points (per-thread histograms, offsets ordered bucket-major then thread-major, so equal keys
+    // keep their input order); (2) a counting sort inside every bucket, buckets in parallel
+    int shift = 0;
+    while ((Np >> shift) > 2048) ++shift;
+    const int B = (Np >> shift) + 1, T = nthreads;
+    std::vector<int64_t>& hist = Wk.hist; hist.assign((size_t)T * B, 0);
+    std::vector<int32_t>& tmp = Wk.tmp; tmp.resize((size_t)NobsAll);
+    std::vector<int64_t> bstart((size_t)B + 1, 0);
+    int bad = 0; int64_t bad_at = -1;      // the EARLIEST offending observation decides the message, as in the serial scan
+#pragma omp parallel num_threads(T)
+    {
+      const int t = omp_get_thread_num();
+      const int64_t k0 = NobsAll * t / T, k1 = NobsAll * (t + 1) / T;
+      int64_t* h = hist.data() + (size_t)t * B;
+      int mybad = 0; int64_t my_at = -1;
+      for (int64_t k = k0; k < k1; ++k) {
+        const int32_t c = obs_cam[k], p = obs_pt[k];
+        if (c < 0 || c >= Nc) { mybad = 1; my_at = k; break; }
+        if (p < 0 || p >= Np) { mybad = 2; my_at = k; break; }
+        if (H.cam_win[c] != pt_win[p]) { mybad = 3; my_at = k; break; }
+        h[p >> shift]++;
+      }
+      if (mybad) {
+#pragma omp critical
+        { if (!bad || my_at < bad_at) { bad = mybad; bad_at = my_at; } }
+      }
+#pragma omp barrier
+#pragma omp single
+      {
+        if (!bad) {
+          int64_t run = 0;
+          for (int bb = 0; bb < B; ++bb) {
+            bstart[bb] = run;
+            for (int tt = 0; tt < T; ++tt) { const int64_t c = hist[(size_t)tt * B + bb]; hist[(size_t)tt * B + bb] = run; run += c; }
+          }
+          bstart[B] = run;
+        }
+      }     // implicit barrier
+      if (!bad) {
+        for (int64_t k = k0; k < k1; ++k) tmp[h[obs_pt[k] >> shift]++] = (int32_t)k;
+#pragma omp barrier
+#pragma omp for schedule(dynamic, 8)
+        for (int bb = 0; bb < B; ++bb) {
+          const int32_t q0 = (int32_t)std::min<int64_t>((int64_t)bb << shift, Np), q1 = (int32_t)std::min<int64_t>(((int64_t)bb + 1) << shift, Np);
+          const int64_t s0 = bstart[bb], s1 = bstart[bb + 1];
+          // counts of the bucket's points into gpt_off[p + 1] (each bucket owns its own slots), then local offsets
+          for (int64_t j = s0; j < s1; ++j) gpt_off[obs_pt[tmp[j]] + 1]++;
+          int64_t run = s0;
+          for (int32_t q = q0; q < q1; ++q) { const int32_t c = gpt_off[q + 1]; gpt_off[q + 1] = (int32_t)run; run += c; }   // start of q, kept in slot q + 1
+          for (int64_t j = s0; j < s1; ++j) { const int32_t k = tmp[j]; gperm[gpt_off[obs_pt[k] + 1]++] = k; }               // slot q + 1 ends as end of q
+        }
+      }
+    }
+    if (bad == 1) return "obs_cam out of range";
+    if (bad == 2) return "obs_pt out of range";
+    if (bad == 3) return "observation links a camera and a point of different windows";
+    gpt_off[0] = 0;
   }
   lap("validate + counting sort");
   // ---- local (owned) slice of the point order
@@ -312,6 +372,8 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
   // ---- block pattern: union of all chunks' local blocks + the diagonal of every free camera
   std::vector<int64_t> keys;
   std::vector<int32_t> key_blk;        // small Nf: block id by key (dense Nf x Nf map)
+  std::vector<uint64_t> bit_words;     // mid-size Nf: bitmap of the blocks + rank per word
+  std::vector<int32_t> bit_rank;
   const bool dense_map = (int64_t)Nf * Nf <= ((int64_t)1 << 22);
   if (dense_map) {
     std::vector<uint8_t> mark((size_t)Nf * Nf, 0);
@@ -319,6 +381,24 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     for (int ch = 0; ch < nch_all; ++ch) for (const LB& b : tab[ch].lbs) mark[(size_t)b.key] = 1;
     key_blk.assign((size_t)Nf * Nf, -1);
     for (size_t k = 0; k < mark.size(); ++k) if (mark[k]) { key_blk[k] = (int32_t)keys.size(); keys.push_back((int64_t)k); }
+  } else if ((int64_t)Nf * Nf <= ((int64_t)1 << 32)) {
+    // up to 65 536 free cameras: one bit per block of the Nf x Nf grid (512 MB at most, 2.6 MB at KITTI-00 scale), marked
+    // from the chunks' local blocks and read back in key order with a rank (prefix popcount) per word for the look-ups
+    // below.  Sorting the ~650 000 local-block keys of a KITTI-00-sized map took 45 ms, a third of the whole build.
+    const size_t nbits = (size_t)Nf * Nf, nwords = (nbits + 63) / 64;
+    bit_words.assign(nwords, 0);
+    for (int f = 0; f < Nf; ++f) { const size_t k = (size_t)f * Nf + f; bit_words[k >> 6] |= (uint64_t)1 << (k & 63); }
+    for (int ch = 0; ch < nch_all; ++ch) for (const LB& b : tab[ch].lbs) bit_words[(size_t)b.key >> 6] |= (uint64_t)1 << ((size_t)b.key & 63);
+    bit_rank.resize(nwords + 1);
+    size_t tot = 0;
+    for (size_t wd = 0; wd < nwords; ++wd) { bit_rank[wd] = (int32_t)tot; tot += (size_t)__builtin_popcountll(bit_words[wd]); }
+    bit_rank[nwords] = (int32_t)tot;
+    keys.resize(tot);
+    size_t o = 0;
+    for (size_t wd = 0; wd < nwords; ++wd) {
+      uint64_t v = bit_words[wd];
+      while (v) { keys[o++] = (int64_t)(wd * 64 + (size_t)__builtin_ctzll(v)); v &= v - 1; }
+    }
   } else {
     size_t tot = (size_t)Nf;
     for (int ch = 0; ch < nch_all; ++ch) tot += tab[ch].lbs.size();
@@ -389,7 +469,11 @@ std::string build_structure(int32_t Nc, int32_t Np, int64_t NobsAll, const int32
     for (size_t l = 0; l < T.lbs.size(); ++l) {
       const LB& b = T.lbs[l];
       H.lb_sa[l0 + l] = b.sa; H.lb_sb[l0 + l] = b.sb;
-      H.lb_blk[l0 + l] = dense_map ? key_blk[(size_t)b.key] : (int32_t)(std::lower_bound(keys.begin(), keys.end(), b.key) - keys.begin());
+      if (dense_map) H.lb_blk[l0 + l] = key_blk[(size_t)b.key];
+      else if (!bit_words.empty()) {
+        const size_t k = (size_t)b.key;
+        H.lb_blk[l0 + l] = bit_rank[k >> 6] + (int32_t)__builtin_popcountll(bit_words[k >> 6] & (((uint64_t)1 << (k & 63)) - 1));
+      } else H.lb_blk[l0 + l] = (int32_t)(std::lower_bound(keys.begin(), keys.end(), b.key) - keys.begin());
       q += T.lb_pair_cnt[l];
       H.lb_pair_off[l0 + l + 1] = (int32_t)q;
     }

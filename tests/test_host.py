@@ -94,7 +94,9 @@ def test_unpack_writes_window_only():
 
 
 @pytest.mark.parametrize("cfg", [dict(num_frames=10, num_points=500, track_len=4, seed=1),
-                                 dict(num_frames=30, num_points=800, track_len=6, seed=2, loop=True, loop_frames=5)])
+                                 dict(num_frames=30, num_points=800, track_len=6, seed=2, loop=True, loop_frames=5),
+                                 # > 2048 free cameras: the pattern comes from the block bitmap, not the dense map
+                                 dict(num_frames=2300, num_points=12000, track_len=5, seed=3, loop=True, loop_frames=20)])
 def test_structure_sorted_views_and_schur_pattern_bit_exact(cfg):
     w = make_window(**cfg)
     Nc, Np = w["poses"].shape[0], w["points"].shape[0]

@@ -1979,32 +1979,33 @@ __global__ void __launch_bounds__(kBandThreads) k_chol_band(Dev d, const int32_t
     __syncthreads();
     lap(3);
   }
-  // back substitution by warp 0: x_k = Linv_kk^T (y_k - sum over the column's rows of L_ik^T x_i), five row groups of
-  // six lanes summed in lane order
+  // back substitution by warp 0, right-looking: as soon as x_k is known it is taken out of every y_j that sees it
+  // (the columns j < k whose envelope reaches row k: y_j -= L_kj^T x_k), so that a column's critical path is two 6x6
+  // matrix-vector products — x_k = Linv_kk^T y_k, then the update of y_{k-1} — instead of a gather over its whole
+  // envelope.  Lane group q (six lanes) updates column k - 1 - q, columns further away in a second pass.
   if (warp == 0) {
     const int ps = lane / 6, c = lane - 6 * ps;
     for (int k = nf - 1; k >= 0; --k) {
-      const int m = lastk[k] - k;
-      const double* colk = A + (size_t)coff[k] * 36;
-      double acc = 0.0;
-      if (lane < 30)
-        for (int ii = ps; ii < m; ii += 5) {
-          const double* L = colk + (size_t)(1 + ii) * 36 + c;
-          const double* xi = y + 6 * (k + 1 + ii);
-          acc += (L[0] * xi[0] + L[6] * xi[1] + L[12] * xi[2]) + (L[18] * xi[3] + L[24] * xi[4] + L[30] * xi[5]);
-        }
-      double tot = acc;
-#pragma unroll
-      for (int q = 1; q < 5; ++q) tot += __shfl_sync(0xffffffffu, acc, (lane + 6 * q) & 31);
-      const double s = (lane < 6) ? y[6 * k + lane] - tot : 0.0;
+      // x_k: lane c < 6 holds s_c = y_k[c]; v_c = sum_{q >= c} Linv[q][c] s_q
+      const double s = (lane < 6) ? y[6 * k + lane] : 0.0;
       double v = 0.0;
 #pragma unroll
       for (int q = 0; q < 6; ++q) {
         const double sq = __shfl_sync(0xffffffffu, s, q);
         if (lane < 6 && q >= lane) v += LI[(size_t)k * 36 + 6 * q + lane] * sq;
       }
-      __syncwarp();
       if (lane < 6) y[6 * k + lane] = v;
+      double xk[6];
+#pragma unroll
+      for (int q = 0; q < 6; ++q) xk[q] = __shfl_sync(0xffffffffu, v, q);
+      // y_j -= L_kj^T x_k for j = k - 1 - jj, jj = ps, ps + 5, ...; block (k, j) sits in column j at row offset k - j
+      if (lane < 30)
+        for (int jj = ps; jj < min(k, mmax); jj += 5) {
+          const int j = k - 1 - jj;
+          if (lastk[j] < k) continue;                                       // column j's envelope ends above row k
+          const double* L = A + (size_t)(coff[j] + (k - j)) * 36 + c;       // column c of L_kj = row c of its transpose
+          y[6 * j + c] -= (L[0] * xk[0] + L[6] * xk[1] + L[12] * xk[2]) + (L[18] * xk[3] + L[24] * xk[4] + L[30] * xk[5]);
+        }
       __syncwarp();
     }
   }

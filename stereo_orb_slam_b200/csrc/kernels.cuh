@@ -258,10 +258,9 @@ __global__ void k_jacobi_scale(Dev d) {
 
 // per window: cost = sum of chunk costs, gmax = max(chunk gmax, |gc| of free cameras);
 // gradient-tolerance test (Ceres: after every accepted step and at iteration 0).
-__global__ void __launch_bounds__(kThreads) k_lin_finish(Dev d, DevParams P, int keep_cost) {
+__device__ __forceinline__ void dev_lin_finish(const Dev& d, const DevParams& P, int w, int keep_cost) {
   __shared__ double sm[4];
   __shared__ double smx[4];
-  const int w = blockIdx.x;
   double cost[1] = {0.0};
   double gmax = 0.0;
   for (int ch = d.win_pchunk_off[w] + threadIdx.x; ch < d.win_pchunk_off[w + 1]; ch += kThreads) {
@@ -271,7 +270,7 @@ __global__ void __launch_bounds__(kThreads) k_lin_finish(Dev d, DevParams P, int
   for (int f = d.win_fc_off[w] + threadIdx.x; f < d.win_fc_off[w + 1]; f += kThreads) {
     const int c = d.free2cam[f];
 #pragma unroll
-    for (int i = 0; i < 6; ++i) gmax = fmax(gmax, fabs(d.gc[(size_t)c * 6 + i]));
+    for (int i = 0; i < 6; ++i) gmax = fmax(gmax, fabs(__ldcg(d.gc + (size_t)c * 6 + i)));      // (may come from other CTAs of this launch)
   }
   const double tot = block_sum<1>(cost, sm);
   const double mx = block_max1(gmax, smx);
@@ -283,6 +282,8 @@ __global__ void __launch_bounds__(kThreads) k_lin_finish(Dev d, DevParams P, int
     d.w_gmax[w] = mx;
   }
 }
+
+__global__ void __launch_bounds__(kThreads) k_lin_finish(Dev d, DevParams P, int keep_cost) { dev_lin_finish(d, P, blockIdx.x, keep_cost); }
 
 // Point-sharded solve (multi-GPU): the same per-window finish in two halves around ONE packed all-reduce (sum) of
 // [U | gc | cost_red | gslots].  A maximum travels through the sum: every rank writes its value into its own slot of
@@ -1176,7 +1177,42 @@ __global__ void __launch_bounds__(kAsmThreads) k_assemble_cams(Dev d) {
 //                S_ff += U + D, Minv = S_ff^-1, rhs = rsum - gc
 // mode bits: 1 prepare · 2 the camera CTA also sums its own U / gc partials (the work of k_assemble_cams: after a fused
 // linearisation nothing else is between the chunk kernel and the solve) · 4 no block-Jacobi inverse (exact solvers)
-__global__ void __launch_bounds__(kAsmThreads) k_assemble_schur(Dev d, int mode) {
+__device__ __forceinline__ void dev_lm_begin(const Dev& d, const DevParams& P, int w, double initial_radius, int first, int clear_fail);
+__device__ __forceinline__ void dev_lm_begin(const Dev& d, const DevParams& P, int w, double initial_radius, int first, int clear_fail);
+// Ticket of k_assemble_schur (mode bit 8): a window's camera CTAs and its chunk-sum CTA each draw one; whoever draws the
+// last one sees everybody's results and finishes the window: cost, gradient maximum (= k_lin_finish), gradient test.
+__device__ __forceinline__ void assemble_ticket(const Dev& d, const DevParams& P, int w, int keep_cost, int lm_begin) {
+  __shared__ int s_last;
+  __shared__ double smx[4];
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int ntick = d.win_fc_off[w + 1] - d.win_fc_off[w] + 1;
+    const int t = atomicAdd(d.win_done + w, 1);
+    s_last = (t == ntick - 1) ? 1 : 0;
+    if (s_last) d.win_done[w] = 0;                           // ready for the next launch
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  double gmax = 0.0;
+  for (int f = d.win_fc_off[w] + threadIdx.x; f < d.win_fc_off[w + 1]; f += kThreads) {
+    const int c = d.free2cam[f];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) gmax = fmax(gmax, fabs(__ldcg(d.gc + (size_t)c * 6 + i)));
+  }
+  const double mx = block_max1(gmax, smx);
+  if (threadIdx.x == 0) {
+    if (!keep_cost) d.w_cost[w] = __ldcg(d.win_part + 2 * w);
+    d.w_gmax[w] = fmax(mx, __ldcg(d.win_part + 2 * w + 1));
+    if (lm_begin) dev_lm_begin(d, P, w, 0.0, 0, 0);
+  }
+}
+
+// mode bit 8 (single GPU, every window has a free camera): the LAST camera CTA of a window to finish also runs the
+// window's finish (cost, gradient maximum: k_lin_finish) and, with lm_begin != 0, the gradient-tolerance test
+// (k_lm_begin, first = 0) — a ticket per window instead of two more launches on a side stream.
+__global__ void __launch_bounds__(kAsmThreads) k_assemble_schur(Dev d, int mode, DevParams P, int keep_cost, int lm_begin) {
   const int prepare = mode & 1;
   __shared__ double sm[kAsmWarps * 36];
   __shared__ double sM[36];
@@ -1189,7 +1225,24 @@ __global__ void __launch_bounds__(kAsmThreads) k_assemble_schur(Dev d, int mode)
     return;
   }
   const int f = blockIdx.x - d.nbu;
-  if (f >= d.Nf) return;
+  if (f >= d.Nf) {
+    // mode bit 8: one more CTA per window sums the window's chunk costs and gradient maxima while the camera CTAs work
+    const int ww = f - d.Nf;
+    if (!(mode & 8) || ww >= d.nwin) return;
+    __shared__ double smw[4];
+    __shared__ double smxw[4];
+    double cost[1] = {0.0};
+    double gmax = 0.0;
+    for (int ch = d.win_pchunk_off[ww] + threadIdx.x; ch < d.win_pchunk_off[ww + 1]; ch += kThreads) {
+      cost[0] += d.lin_part[2 * ch];
+      gmax = fmax(gmax, d.lin_part[2 * ch + 1]);
+    }
+    const double tot = block_sum<1>(cost, smw);            // the same sum, in the same order, as k_lin_finish
+    const double mx = block_max1(gmax, smxw);
+    if (threadIdx.x == 0) { d.win_part[2 * ww] = tot; d.win_part[2 * ww + 1] = mx; }
+    assemble_ticket(d, P, ww, keep_cost, lm_begin);
+    return;
+  }
   // every index and scalar the two gathers and the prepare step need is requested up front, so that their
   // latencies overlap instead of chaining behind the barriers of cta_gather
   const int c = d.free2cam[f];
@@ -1221,27 +1274,31 @@ __global__ void __launch_bounds__(kAsmThreads) k_assemble_schur(Dev d, int mode)
   }
   const double rs = cta_gather<6, 2>(d.rpart, r0, r1, sm);
   if (threadIdx.x < 6) { d.rsum[(size_t)f * 6 + threadIdx.x] = rs; if (prepare) d.rhs[(size_t)f * 6 + threadIdx.x] = rs - gcv; }
-  if (!prepare) return;
-  __syncthreads();                                           // sm is reused
-  const double tot = cta_gather<36, 9>(d.spart, b0, b1, sm);
-  if (threadIdx.x < 36) {
-    const double v = -tot + u + damp;
-    sM[threadIdx.x] = v;
-    d.Su[(size_t)db * 36 + threadIdx.x] = v;
+  if (prepare) {
+    __syncthreads();                                           // sm is reused
+    const double tot = cta_gather<36, 9>(d.spart, b0, b1, sm);
+    if (threadIdx.x < 36) {
+      const double v = -tot + u + damp;
+      sM[threadIdx.x] = v;
+      d.Su[(size_t)db * 36 + threadIdx.x] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && !(mode & 4)) {
+      // one thread per camera factorises (all cameras in parallel, registers only)
+      double M[36];
+#pragma unroll
+      for (int i = 0; i < 36; ++i) M[i] = sM[i];
+      if (!inv_spd6(M)) {
+        d.w_fail[w] = 1;
+#pragma unroll
+        for (int i = 0; i < 36; ++i) M[i] = (i % 7 == 0) ? 1.0 : 0.0;
+      }
+#pragma unroll
+      for (int i = 0; i < 36; ++i) d.Minv[(size_t)f * 36 + i] = M[i];
+    }
   }
-  __syncthreads();
-  if (threadIdx.x != 0 || (mode & 4)) return;
-  // one thread per camera factorises (all cameras in parallel, registers only)
-  double M[36];
-#pragma unroll
-  for (int i = 0; i < 36; ++i) M[i] = sM[i];
-  if (!inv_spd6(M)) {
-    d.w_fail[w] = 1;
-#pragma unroll
-    for (int i = 0; i < 36; ++i) M[i] = (i % 7 == 0) ? 1.0 : 0.0;
-  }
-#pragma unroll
-  for (int i = 0; i < 36; ++i) d.Minv[(size_t)f * 36 + i] = M[i];
+  if (!(mode & 8)) return;
+  assemble_ticket(d, P, w, keep_cost, lm_begin);
 }
 
 // thread per free camera: add U + D to the diagonal block, rhs = -gc + rsum, Minv = (S_ii)^-1
@@ -2954,9 +3011,7 @@ __global__ void __launch_bounds__(kThreads) k_ls_reduce(Dev d, int rank) { dev_l
 // options from the reference: src/bundle_adjuster.cpp:14-36).  Thread per window.
 
 // after a linearisation: gradient-tolerance test; `first` also initialises the LM state
-__global__ void k_lm_begin(Dev d, DevParams P, double initial_radius, int first, int clear_fail) {
-  const int w = blockIdx.x * blockDim.x + threadIdx.x;
-  if (w >= d.nwin) return;
+__device__ __forceinline__ void dev_lm_begin(const Dev& d, const DevParams& P, int w, double initial_radius, int first, int clear_fail) {
   if (first) {
     d.w_radius[w] = initial_radius; d.w_decf[w] = 2.0; d.w_status[w] = 0; d.w_iter[w] = 0; d.w_succ[w] = 0;
     d.w_invalid[w] = 0; d.w_accept[w] = 0;
@@ -2966,6 +3021,10 @@ __global__ void k_lm_begin(Dev d, DevParams P, double initial_radius, int first,
     if (!isfinite(d.w_cost[w])) d.w_status[w] = -2;                       // numerical failure
     else if (d.w_gmax[w] <= P.gtol) d.w_status[w] = 3;                    // gradient tolerance
   }
+}
+__global__ void k_lm_begin(Dev d, DevParams P, double initial_radius, int first, int clear_fail) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w < d.nwin) dev_lm_begin(d, P, w, initial_radius, first, clear_fail);
 }
 
 // Projected Armijo line search, one thread per window (ArmijoLineSearch::DoSearch restated; see

@@ -109,6 +109,7 @@ struct sba_handle_s {
   bool schur_fresh = false;              // the last linearisation was fused: spart / rpart already hold this radius' Schur partials
   // ... and on a single GPU its camera-side assembly and finish are left to the next do_schur (one assemble kernel for
   // U / gc / S / rhs; cost + gradient test on the side stream while the solve runs)
+  bool every_window_free = false;     // every window has at least one free camera (k_assemble_schur can finish the windows itself)
   bool cams_pending = false; bool pend_keep_cost = false; int pend_lm_begin = -1; double pend_radius = 0.0;
   // exact block-sparse Cholesky of the reduced system for windows of more than kCholMaxCams free cameras (k_spchol)
   SparseCholSymbolic sym; bool sym_ok = false; SpCholDev sp{}; bool spchol_ok = false; int spchol_blocks = 0; size_t spchol_smem = 0; double time_symbolic_s = 0.0;
@@ -347,6 +348,8 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
     // nested-dissection ordering, elimination-tree levels, static update lists — once per structure
     int nf_max = 0;
     for (int w = 0; w < h->H.nwin; ++w) nf_max = std::max(nf_max, h->H.win_fc_off[w + 1] - h->H.win_fc_off[w]);
+    h->every_window_free = h->H.nwin > 0;
+    for (int w = 0; w < h->H.nwin; ++w) if (h->H.win_fc_off[w + 1] == h->H.win_fc_off[w]) h->every_window_free = false;
     if (h->H.Nf > 0 && (nf_max > kCholMaxCams || std::getenv("SBA_FORCE_SPARSE_CHOL")) && !std::getenv("SBA_NO_SPARSE_CHOL")) {
       const auto ts = std::chrono::steady_clock::now();
       const std::string serr = sparse_chol_symbolic(h->H.Nf, h->H.blk_row, h->H.blk_col, (int64_t)256 << 20, &h->sym);
@@ -403,6 +406,8 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   AL(d.x, nf * 6) AL(d.r, nf * 6) AL(d.z, nf * 6) AL(d.p, nf * 6) AL(d.Ap, nf * 6) AL(h->pcg_pbuf, nf * 6) AL(h->pcg_rowdot, 2 * nf)
   AL(d.dp, np * 3) AL(d.step_part, (size_t)d.npchunk * 4) AL(d.ls_part, (size_t)d.npchunk * 3)
   AL(d.cta_part, (size_t)std::max(h->coop_blocks, 1) * 16)
+  AL(d.win_done, nw) AL(d.win_part, nw * 2)
+  CUDA_TRY(cudaMemsetAsync(d.win_done, 0, nw * sizeof(int32_t), h->stream));
   AL(d.w_radius, nw) AL(d.w_decf, nw) AL(d.w_cost, nw) AL(d.w_gmax, nw)
   AL(d.w_gd, nw * 4 + nw * kMaxRanks)   // one block: a multi-GPU solve all-reduces the four step scalars and the max-norm slots in one call
   d.w_dDd = d.w_gd + nw; d.w_x2 = d.w_gd + 2 * nw; d.w_dr = d.w_gd + 3 * nw; d.dslots = d.w_gd + 4 * nw;
@@ -731,7 +736,7 @@ static int do_schur(sba_handle h, bool exact_solver = false) {
       // point-sharded: this rank's share of U | gc | S | rsum by ONE assemble kernel, its cost and gradient maximum,
       // then ONE all-reduce over the whole block instead of one per linearisation plus one per Schur step
       const int world = h->comm.world;
-      LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 2);
+      LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 2, h->P, 0, 0);
       LAUNCH(h, k_lin_finish_local, d.nwin, kThreads, d, h->comm.rank, world);
       std::string _err;
       if (!h->comm.allreduce(d.U, (size_t)((d.rsum + (size_t)d.Nf * 6) - d.U), false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }
@@ -742,7 +747,15 @@ static int do_schur(sba_handle h, bool exact_solver = false) {
       return SBA_OK;
     }
     stamp(h, h->stream, 0);
-    LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 3 | (exact_solver ? 4 : 0));
+    if (h->every_window_free && h->pend_lm_begin <= 0 && !std::getenv("SBA_NO_TICKET")) {
+      // the last camera CTA of every window finishes the window (cost, gradient maximum, gradient-tolerance test): no
+      // side stream, two launches fewer
+      LAUNCH(h, k_assemble_schur, d.nbu + d.Nf + d.nwin, kAsmThreads, d, 3 | 8 | (exact_solver ? 4 : 0), h->P, h->pend_keep_cost ? 1 : 0, h->pend_lm_begin == 0 ? 1 : 0);
+      stamp(h, h->stream, 1);
+      CUDA_TRY(cudaGetLastError());
+      return SBA_OK;
+    }
+    LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 3 | (exact_solver ? 4 : 0), h->P, 0, 0);
     stamp(h, h->stream, 1);
     CUDA_TRY(cudaEventRecord(h->ev_fork, h->stream));
     CUDA_TRY(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
@@ -755,7 +768,7 @@ static int do_schur(sba_handle h, bool exact_solver = false) {
     return SBA_OK;
   }
   const int fused = h->comm.active() ? 0 : 1;     // multi-GPU: the partial sums are all-reduced before the cameras are prepared
-  LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, fused);
+  LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, fused, h->P, 0, 0);
   if (fused) { CUDA_TRY(cudaGetLastError()); return SBA_OK; }
   if (h->comm.active()) {
     std::string _err;
@@ -1058,7 +1071,7 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
     switch (stage) {
       case 0: if (i == 0) { LAUNCH(h, k_campre, cdiv(d.Nc, 128), 128, d); CUDA_TRY(cudaEventRecord(h->ev[6], h->stream)); }
               if (d.npchunk > 0) { k_lin_chunk<<<d.npchunk, kLinThreads, h->lin_smem, h->stream>>>(d, P, dbg_mask() >> 8); h->launches++; } break;
-      case 1: LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 1); break;
+      case 1: LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 1, h->P, 0, 0); break;
       case 2: if (d.npchunk > 0) { k_schur_chunk<<<d.npchunk, kSchurThreads, h->schur_smem, h->stream>>>(d, h->H.max_chunk_pairs, dbg_mask()); h->launches++; } break;
       case 3: if ((rc = do_linearize(h))) return rc; break;
       case 4: if ((rc = do_schur(h))) return rc; break;

@@ -67,6 +67,8 @@ struct Dev {
   double *dp;                    // [Np*3] point step (back-substitution)
   double *step_part;             // [npchunk*4]  g.dp, dp D dp, |x|^2, max|dp|
   double *ls_part;               // [npchunk*3]  trial cost, directional derivative, |x_trial - x|^2
+  double *win_part;              // [nwin*2] cost and gradient maximum over a window's chunks (k_assemble_schur's window CTAs)
+  int32_t *win_done;             // [nwin] tickets of k_assemble_schur's camera CTAs (zero between launches)
   double *cta_part;              // [step-loop CTAs * 16] one global window: per-CTA partials of the rows above and of the
                                  //   camera terms, so that the window's reductions sum a few hundred rows, not 10^5
   // ---- per-window scalars [nwin]

@@ -122,11 +122,13 @@ def gpu_sharded_global_worker(rank, world, port, out_dir):
     opt = default_options(max_time_s=0.0, max_iterations=12)
     ss = ShardedSolver(rank)
     poses, points, s = ss.solve(*args, options=opt)
-    # wall-clock limit: a third of what THIS rank measures for a second, warm 12-iteration solve (the problem needs more
-    # than 12 iterations to converge, so the limit falls inside the run; the ranks' limits and clocks differ, which is the
-    # point: they must still stop together)
+    # wall-clock limit from THIS rank's own measurements of warm solves (the problem needs more than 12 iterations to
+    # converge; the ranks' limits and clocks differ, which is the point: they must still stop together)
     _, _, s_warm = ss.solve(*args, options=opt)
-    pt, xt, st = ss.solve(*args, options=default_options(max_time_s=0.33 * s_warm["time_solve_s"]))
+    _, _, s_one = ss.solve(*args, options=default_options(max_time_s=0.0, max_iterations=1))
+    # (the clock starts before the uploads of the structure are waited for: half-way between a 1-iteration and a
+    # 12-iteration solve is inside the run whatever that wait costs)
+    pt, xt, st = ss.solve(*args, options=default_options(max_time_s=0.5 * (s_one["time_solve_s"] + s_warm["time_solve_s"])))
     got = [None] * world
     dist.all_gather_object(got, dict(term=st["termination_name"], it=st["iterations"], cost=st["final_cost"]))
     if rank == 0:

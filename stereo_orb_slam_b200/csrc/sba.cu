@@ -24,6 +24,7 @@
 #include "sba_internal.h"
 #include "pgo.cuh"
 #include "ransac.cuh"
+#include "fused_persist.cuh"
 #include "sparse_chol.cuh"
 #include "sparse_chol.h"
 
@@ -105,7 +106,8 @@ struct sba_handle_s {
   bool chol_cluster_ok = false; size_t chol_cluster_smem = 0;   // mid-size windows: one 8-CTA cluster per window (k_chol_cluster)
   bool chol_band_ok = false; size_t chol_band_smem = 0; const int32_t* band_last = nullptr;   // banded windows: envelope in one CTA's shared memory (k_chol_band)
   size_t lin_smem = 0, schur_smem = 0;   // dynamic shared memory of the per-chunk kernels (largest chunk)
-  size_t fused_smem = 0; bool fused_ok = false; int fused_occ = 2; int fused_nt = 256;   // k_fused_chunk (K1-K3 of a chunk in one CTA)
+  size_t fused_smem = 0; bool fused_ok = false; int fused_occ = 2; int fused_nt = 256;
+  bool persist_ok = false; int persist_grid = 0;      // k_fused_persist (persistent CTAs, inputs of the next chunk prefetched)   // k_fused_chunk (K1-K3 of a chunk in one CTA)
   bool schur_fresh = false;              // the last linearisation was fused: spart / rpart already hold this radius' Schur partials
   // ... and on a single GPU its camera-side assembly and finish are left to the next do_schur (one assemble kernel for
   // U / gc / S / rhs; cost + gradient test on the side stream while the solve runs)
@@ -121,7 +123,8 @@ struct sba_handle_s {
     void* q = nullptr;
     // stream-ordered pool: after the first solve a re-structure (every BundleAdjuster::Optimize call) reuses the
     // pool's cached blocks instead of paying ~100 cudaMalloc/cudaFree round trips
-    cudaError_t e = pool ? cudaMallocFromPoolAsync(&q, n * sizeof(T), pool, stream) : cudaMallocAsync(&q, n * sizeof(T), stream);
+    // (+16 bytes: k_fused_persist copies byte / 16-bit arrays in aligned 32-bit words, the last of which may straddle the end)
+    cudaError_t e = pool ? cudaMallocFromPoolAsync(&q, n * sizeof(T) + 16, pool, stream) : cudaMallocAsync(&q, n * sizeof(T) + 16, stream);
     if (e != cudaSuccess) { set_error(std::string("cudaMallocAsync: ") + cudaGetErrorString(e)); return SBA_CUDA_ERROR; }
     allocs.push_back(q);
     *p = static_cast<T*>(q);
@@ -450,6 +453,20 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
       CUDA_TRY(cudaFuncSetAttribute(k_fused_chunk<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fused_smem, 1024)));
       CUDA_TRY(cudaFuncSetAttribute((k_fused_chunk<4, false, 128>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fused_smem, 1024)));
       h->fused_nt = (H.max_chunk_obs <= 128 && H.max_chunk_pts <= 128 && !std::getenv("SBA_FUSED_NT256")) ? 128 : 256;
+      // persistent variant: every chunk must fit its fixed input buffers
+      h->persist_ok = H.long_chunks.empty() && H.max_slots <= kFPSlots && H.max_chunk_obs <= 255 && !std::getenv("SBA_NO_PERSIST") && h->fused_nt == 256;
+      for (size_t ch = 0; h->persist_ok && ch < H.pchunk_begin.size(); ++ch) {
+        const int32_t* D = H.cdesc.data() + ch * 16;
+        if (D[8] > kFPLb || D[10] > kFPPairs || (int64_t)D[10] * 4 > (int64_t)D[3] * 72) h->persist_ok = false;
+      }
+      if (h->persist_ok) {
+        CUDA_TRY(cudaFuncSetAttribute(k_fused_persist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->fused_smem, 1024)));
+        int per_sm = 0, sms = 0;
+        CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fused_persist, kFusedThreads, h->fused_smem));
+        h->persist_grid = per_sm * sms;
+        if (per_sm < 1) h->persist_ok = false;
+      }
     }
   }
   {
@@ -642,7 +659,8 @@ int sba_get_state(sba_handle h, double* poses, double* points) {
 // the fused K1-K3 chunk kernel: 128-thread CTAs (4 per SM) when every regular chunk has at most 128 observations
 static void launch_fused(sba_handle h) {
   const Dev& d = h->d; const DevParams& P = h->P;
-  if (h->fused_nt == 128) k_fused_chunk<4, false, 128><<<d.npchunk, 128, h->fused_smem, h->stream>>>(d, P);
+  if (h->persist_ok) k_fused_persist<<<std::min(h->persist_grid, (int)d.npchunk), kFusedThreads, h->fused_smem, h->stream>>>(d, P);
+  else if (h->fused_nt == 128) k_fused_chunk<4, false, 128><<<d.npchunk, 128, h->fused_smem, h->stream>>>(d, P);
   else if (h->fused_occ == 3) k_fused_chunk<3><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
   else k_fused_chunk<2><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
   h->launches++;

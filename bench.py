@@ -292,7 +292,7 @@ def run_ours(args):
     # bytes / flops of BOTH stages, SURVEY 8(d), although W never comes back from HBM); without it k_lin_chunk does
     # K1/K2 and k_schur_chunk K3, each charged its own stage
     if t_fu is not None:
-        dom, t_dom, B_dom, F_dom = "k_fused_chunk", t_fu, B_lin + B_schur, F_lin + F_schur
+        dom, t_dom, B_dom, F_dom = (sv.fused_kernel or "k_fused_chunk"), t_fu, B_lin + B_schur, F_lin + F_schur
     elif t_sp >= t_lp:
         dom, t_dom, B_dom, F_dom = "k_schur_chunk", t_sp, B_schur, F_schur
     else:
@@ -375,7 +375,7 @@ def run_ours(args):
                          "fp64": {"achieved": F_dom / (t_dom * 1e-3) / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
                                   "frac": F_dom / (t_dom * 1e-3) / 1e12 / fp64_peak if fp64_peak > 0 else None,
                                   "algorithmic_flops": F_dom, "peak_source": "measured here (sba_measure_fp64_peak: register-only DFMA chains)"}},
-            "stages_us": {"k_fused_chunk": None if t_fu is None else 1e3 * t_fu, "k_lin_chunk": 1e3 * t_lp, "k_schur_chunk": 1e3 * t_sp,
+            "stages_us": {"fused (" + str(sv.fused_kernel) + ")": None if t_fu is None else 1e3 * t_fu, "k_lin_chunk": 1e3 * t_lp, "k_schur_chunk": 1e3 * t_sp,
                           "linearize_unfused": 1e3 * t_lin, "schur_unfused": 1e3 * t_sch},
             "stage_roofline": {"linearize_GBs": B_lin / (t_lin * 1e-3) / 1e9, "schur_GBs": B_schur / (t_sch * 1e-3) / 1e9,
                                "linearize_frac": B_lin / (t_lin * 1e-3) / 1e9 / peak, "schur_frac": B_schur / (t_sch * 1e-3) / 1e9 / peak,

@@ -182,6 +182,10 @@ int sba_get_factor_symbolic(sba_handle h, int64_t info[5], int32_t* perm, int32_
 int32_t sba_num_free_cameras(sba_handle h);
 /* number of kernels launched by this handle so far (bench.py's gpu_launches) */
 int64_t sba_launch_count(sba_handle h);
+/* which kernel runs K1-K3 of the chunks after the first linearisation of the current structure (diagnostics: bench.py names
+ * its dominant kernel with it): 0 the two-kernel path (k_lin_chunk + k_schur_chunk), 1 k_fused_chunk (256 threads),
+ * 2 k_fused_chunk (128 threads), 3 k_fused_persist */
+int32_t sba_fused_kernel_variant(sba_handle h);
 
 /* ---- multi-GPU (NCCL over NVLink) -------------------------------------------------------------- */
 /* id: 128-byte ncclUniqueId made by rank 0 with sba_comm_unique_id and broadcast by the caller. */

@@ -22,7 +22,7 @@ SYMBOLS = [
     "sba_time_stage", "sba_invert_pose", "sba_normalize_pose", "sba_compose_pose", "sba_get_factor_symbolic", "sba_measure_fp64_peak",
     "sba_map_reset", "sba_map_append_frame", "sba_map_num_frames", "sba_map_num_points", "sba_map_optimize", "sba_map_get_poses",
     "sba_map_set_pose", "sba_map_get_points", "sba_map_set_points", "sba_map_last_window", "sba_pgo_optimize",
-    "sba_ransac_default_options", "sba_ransac_stereo", "sba_triangulate_stereo", "sba_ransac_stereo_noalloc",
+    "sba_ransac_default_options", "sba_ransac_stereo", "sba_triangulate_stereo", "sba_ransac_stereo_noalloc", "sba_fused_kernel_variant",
 ]
 
 SBA_OK, SBA_NO_CONVERGENCE, SBA_NUMERICAL_FAILURE, SBA_INVALID_ARGUMENT, SBA_CUDA_ERROR, SBA_NCCL_ERROR = range(6)

@@ -1496,6 +1496,10 @@ int sba_measure_fp64_peak(sba_handle h, double* tflops) {
 
 int32_t sba_num_free_cameras(sba_handle h) { return (h && h->has_structure) ? h->H.Nf : -1; }
 int64_t sba_launch_count(sba_handle h) { return h ? h->launches : -1; }
+int32_t sba_fused_kernel_variant(sba_handle h) {
+  if (!h || !h->has_structure || !h->fused_ok) return 0;
+  return h->persist_ok ? 3 : (h->fused_nt == 128 ? 2 : 1);
+}
 
 // ---- device-resident map -------------------------------------------------------------
 extern "C++" {

@@ -214,5 +214,10 @@ class Solver:
         return int(self._L.sba_num_free_cameras(self._h))
 
     @property
+    def fused_kernel(self):
+        """Name of the kernel that runs K1-K3 of the chunks for the current structure (None: the two-kernel path)."""
+        return {0: None, 1: "k_fused_chunk", 2: "k_fused_chunk", 3: "k_fused_persist"}[int(self._L.sba_fused_kernel_variant(self._h))]
+
+    @property
     def launch_count(self):
         return int(self._L.sba_launch_count(self._h))

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libsba.so")
+LIB_PATH = os.environ.get("SBA_LIB_PATH") or os.path.join(_HERE, "lib", "libsba.so")      # the override is a tuning aid (build variants)
 
 # every symbol include/sba.h declares (tests check the header against this list and the .so)
 SYMBOLS = [

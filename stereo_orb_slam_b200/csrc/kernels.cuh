@@ -2650,7 +2650,11 @@ __global__ void __launch_bounds__(kThreads) k_pcg_coop(Dev d, DevParams P, int m
 // chunk partials: g.dp, dp^T D dp, |x|^2, max|dp|
 constexpr int kBackObs = 256;       // observations of a regular chunk (<= 240, structure.cpp)
 constexpr int kBackSlots = 64;      // camera slots staged; chunks with more read the camera steps through L2
-__device__ __forceinline__ void dev_backsub(const Dev& d, const DevParams& P, int chunk) {
+// TMA = true (k_backsub, one CTA per chunk): the chunk's rows of W (contiguous: n x 144 bytes) come to shared memory by
+// ONE cp.async.bulk issued by thread 0 before anything else — no load instructions, no staging registers, the copy
+// engine keeps HBM busy while the CTA fetches its indices; Ws / bar are the CTA's dynamic buffer and mbarrier.
+template <bool TMA = false>
+__device__ __forceinline__ void dev_backsub(const Dev& d, const DevParams& P, int chunk, double* Ws = nullptr, uint64_t* bar = nullptr) {
   __shared__ double sm[4 * 3];
   __shared__ double smx[4];
   __shared__ double sobs[kBackObs * 3];
@@ -2659,6 +2663,9 @@ __device__ __forceinline__ void dev_backsub(const Dev& d, const DevParams& P, in
   const int p0 = cd0.x, np = cd0.y, e0 = cd0.z, n = cd0.w, w = cd1.x, cs0 = cd1.y, ns = cd1.z;
   const bool regular = n <= kBackObs;
   const bool staged = regular && ns <= kBackSlots;
+  if constexpr (TMA) {
+    if (staged && n > 0 && threadIdx.x == 0) bulk_load(Ws, d.W + (size_t)e0 * 18, (uint32_t)n * 144u, bar);
+  }
   if (staged) {
     for (int i = threadIdx.x; i < ns * 6; i += kThreads) {
       const int sl = i / 6;
@@ -2683,23 +2690,33 @@ __device__ __forceinline__ void dev_backsub(const Dev& d, const DevParams& P, in
   double tl[3] = {0, 0, 0};          // long chunk (one point, thousands of observations): this thread's share
   if (staged) {
     // the rows of W first: independent loads, issued before the barrier the staged camera steps need
-    double Wr[2][18];
+    double Wr[TMA ? 1 : 2][18];
     int sl[2] = {0, 0};
     static_assert(kBackObs <= 2 * kThreads, "two observations per thread");
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
       const int i = threadIdx.x + k * kThreads;
-      if (i < n) { load_W(d.W, (size_t)(e0 + i), Wr[k]); sl[k] = d.oslot[e0 + i]; }
+      if (i < n) {
+        if constexpr (!TMA) load_W(d.W, (size_t)(e0 + i), Wr[k]);
+        sl[k] = d.oslot[e0 + i];
+      }
     }
     __syncthreads();
+    if constexpr (TMA) { if (n > 0) mbar_wait(bar, 0); }
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
       const int i = threadIdx.x + k * kThreads;
       if (i < n) {
         double s0 = 0.0, s1 = 0.0, s2 = 0.0;
         const double* dc = dcs + 6 * sl[k];
+        double (&Wk)[18] = Wr[TMA ? 0 : k];
+        if constexpr (TMA) {       // LDS.128 at a 144-byte stride: conflict-free per quarter-warp
+          const double2* src = reinterpret_cast<const double2*>(Ws + (size_t)i * 18);
 #pragma unroll
-        for (int q = 0; q < 6; ++q) { s0 += Wr[k][3 * q] * dc[q]; s1 += Wr[k][3 * q + 1] * dc[q]; s2 += Wr[k][3 * q + 2] * dc[q]; }
+          for (int q = 0; q < 9; ++q) { const double2 v = src[q]; Wk[2 * q] = v.x; Wk[2 * q + 1] = v.y; }
+        }
+#pragma unroll
+        for (int q = 0; q < 6; ++q) { s0 += Wk[3 * q] * dc[q]; s1 += Wk[3 * q + 1] * dc[q]; s2 += Wk[3 * q + 2] * dc[q]; }
         sobs[3 * i] = s0; sobs[3 * i + 1] = s1; sobs[3 * i + 2] = s2;
       }
     }
@@ -2749,7 +2766,16 @@ __device__ __forceinline__ void dev_backsub(const Dev& d, const DevParams& P, in
   if (threadIdx.x == 3) d.step_part[(size_t)chunk * 4 + 3] = mx;
 }
 
-__global__ void __launch_bounds__(kThreads) k_backsub(Dev d, DevParams P) { dev_backsub(d, P, blockIdx.x); }
+#ifndef SBA_BACKSUB_MIN_BLOCKS
+#define SBA_BACKSUB_MIN_BLOCKS 5
+#endif
+__global__ void __launch_bounds__(kThreads, SBA_BACKSUB_MIN_BLOCKS) k_backsub(Dev d, DevParams P) {
+  extern __shared__ __align__(16) double Ws[];             // [max regular chunk observations * 18]
+  __shared__ __align__(8) uint64_t bar;
+  if (threadIdx.x == 0) mbar_init(&bar, 1);
+  __syncthreads();
+  dev_backsub<true>(d, P, blockIdx.x, Ws, &bar);
+}
 
 // one CTA per window: the step scalars (cameras + point chunk partials) and the line-search start state.
 // (multi-GPU: camera terms are counted on rank 0 only; the scalars are all-reduced afterwards)
@@ -3227,7 +3253,7 @@ __device__ __forceinline__ void dev_ls_reduce_one(const Dev& d, int nb) {
 #ifndef SBA_STEP_MIN_BLOCKS
 #define SBA_STEP_MIN_BLOCKS 4
 #endif
-__global__ void __launch_bounds__(kThreads, SBA_STEP_MIN_BLOCKS) k_step_loop(Dev d, DevParams P, int fused_cams) {
+__global__ void __launch_bounds__(kThreads, SBA_STEP_MIN_BLOCKS) k_step_loop(Dev d, DevParams P, int fused_cams, int skip_backsub) {
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
   const int nb = gridDim.x;
   const bool one = d.nwin == 1 && d.npchunk > 4 * nb;      // one global window: two-level reductions
@@ -3235,7 +3261,7 @@ __global__ void __launch_bounds__(kThreads, SBA_STEP_MIN_BLOCKS) k_step_loop(Dev
   const bool prof = P.debug == 2 && blockIdx.x == 0 && threadIdx.x == 0;
   unsigned long long t0 = prof ? gtimer() : 0, tp[6] = {0, 0, 0, 0, 0, 0};
   auto lap = [&](int k) { if (prof) { const unsigned long long t = gtimer(); tp[k] += t - t0; t0 = t; } };
-  for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) { dev_backsub(d, P, ch); __syncthreads(); }
+  for (int ch = blockIdx.x; ch < d.npchunk && !skip_backsub; ch += nb) { dev_backsub<false>(d, P, ch); __syncthreads(); }
   if (blockIdx.x == 0 && threadIdx.x == 0) { d.counters[0] = 0; d.counters[2] = 0; d.counters[3] = 0; d.counters[5] = 0; }
   if (one) dev_step_partials_one(d, nb);
   grid.sync();

@@ -107,6 +107,7 @@ struct sba_handle_s {
   bool chol_band_ok = false; size_t chol_band_smem = 0; const int32_t* band_last = nullptr;   // banded windows: envelope in one CTA's shared memory (k_chol_band)
   size_t lin_smem = 0, schur_smem = 0;   // dynamic shared memory of the per-chunk kernels (largest chunk)
   size_t fused_smem = 0; bool fused_ok = false; int fused_occ = 2; int fused_nt = 256;
+  size_t backsub_smem = 0;     // k_backsub: W rows of the largest regular chunk
   bool persist_ok = false; int persist_grid = 0;      // k_fused_persist (persistent CTAs, inputs of the next chunk prefetched)   // k_fused_chunk (K1-K3 of a chunk in one CTA)
   bool schur_fresh = false;              // the last linearisation was fused: spart / rpart already hold this radius' Schur partials
   // ... and on a single GPU its camera-side assembly and finish are left to the next do_schur (one assemble kernel for
@@ -444,6 +445,8 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
     CUDA_TRY(cudaFuncSetAttribute(k_lin_chunk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->lin_smem, 1024)));
     CUDA_TRY(cudaFuncSetAttribute(k_schur_chunk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->schur_smem, 1024)));
     h->fused_smem = fused_smem_bytes(H.max_chunk_obs, H.max_chunk_pts, H.max_slots);
+    h->backsub_smem = (size_t)std::max(H.max_chunk_obs, 1) * 144;
+    CUDA_TRY(cudaFuncSetAttribute(k_backsub, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(h->backsub_smem, 1024)));
     h->fused_ok = h->fused_smem <= (size_t)220 * 1024 && !std::getenv("SBA_NO_FUSED");
     h->schur_fresh = false;
     if (h->fused_ok)
@@ -663,6 +666,14 @@ static void launch_fused(sba_handle h) {
   else if (h->fused_nt == 128) k_fused_chunk<4, false, 128><<<d.npchunk, 128, h->fused_smem, h->stream>>>(d, P);
   else if (h->fused_occ == 3) k_fused_chunk<3><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
   else k_fused_chunk<2><<<d.npchunk, kFusedThreads, h->fused_smem, h->stream>>>(d, P);
+  h->launches++;
+}
+
+// K5: one CTA per chunk, the chunk's rows of W by one bulk copy into its dynamic shared memory
+static void launch_backsub(sba_handle h) {
+  const Dev& d = h->d;
+  if (d.npchunk <= 0) return;
+  k_backsub<<<d.npchunk, kThreads, h->backsub_smem, h->stream>>>(d, h->P);
   h->launches++;
 }
 
@@ -928,7 +939,11 @@ static int do_step(sba_handle h, int* ls_rounds, bool defer = false) {
     if (const char* e = std::getenv("SBA_STEP_GRID")) grid = std::max(1, std::min(grid, std::atoi(e)));   // tuning aid
     Dev dd = d; DevParams pp = P;
     int fused_cams = (h->H.max_slots <= kTrialSlots && h->H.long_chunks.empty()) ? 1 : 0;
-    void* args[] = {&dd, &pp, &fused_cams};
+    // large problems: the back substitution as its own kernel (a CTA per chunk, W by bulk copy, more CTAs per SM than the
+    // register-heavy cooperative kernel allows); small ones keep it inside the cooperative launch
+    int skip_backsub = (d.npchunk >= 4 * grid && !std::getenv("SBA_BACKSUB_IN_LOOP")) ? 1 : 0;
+    if (skip_backsub) launch_backsub(h);
+    void* args[] = {&dd, &pp, &fused_cams, &skip_backsub};
     cudaEvent_t dbg[3] = {nullptr, nullptr, nullptr};
     const bool dbg_ev = P.debug == 2 && !defer;           // SBA_DEBUG_LS=2: where the step's wall time goes
     const auto th0 = std::chrono::steady_clock::now();
@@ -964,7 +979,7 @@ static int do_step(sba_handle h, int* ls_rounds, bool defer = false) {
   int rc;
   CUDA_TRY(cudaMemsetAsync(d.counters, 0, 4, h->stream));
   CUDA_TRY(cudaMemsetAsync(d.counters + 2, 0, 4, h->stream));
-  LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P);
+  launch_backsub(h);
   LAUNCH(h, k_cam_step, d.nwin, kThreads, d, rank);
   if (h->comm.active()) {
     std::string _err;   // w_gd, w_dDd, w_x2, w_dr and the max-norm slots are one contiguous block: one all-reduce
@@ -1133,11 +1148,11 @@ int sba_time_stage(sba_handle h, const sba_options* opt, double radius, int32_t 
           h->launches++;
         }
         break;
-      case 5: LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P); break;
+      case 5: launch_backsub(h); break;
       case 9: LAUNCH(h, k_assemble_cams, d.Nf, kAsmThreads, d); break;
       case 10: LAUNCH(h, k_lin_finish, d.nwin, kThreads, d, P, 0); break;
       case 6:      // one line-search evaluation of the full step (needs sba_schur + sba_pcg for a meaningful step)
-        LAUNCH(h, k_backsub, d.npchunk, kThreads, d, P);
+        launch_backsub(h);
         LAUNCH(h, k_cam_step, d.nwin, kThreads, d, 0);
         LAUNCH(h, k_trial_cams, cdiv(d.Nc, 128), 128, d);
         CUDA_TRY(cudaEventRecord(h->ev[6], h->stream));   // time the cost kernel alone

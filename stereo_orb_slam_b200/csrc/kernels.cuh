@@ -2874,7 +2874,10 @@ __global__ void k_trial_cams(Dev d) { dev_trial_cam(d, blockIdx.x * blockDim.x +
 //   d/ds cost = sum_obs  rho' (D^T r) . (G dw + dt + R dp)     evaluated at the trial point
 constexpr int kTrialSlots = 32;    // chunks with at most this many cameras compute their trial cameras in shared memory
 
-__device__ __forceinline__ void dev_trial_points(const Dev& d, const DevParams& P, int chunk) {
+// from_table: the trial cameras of the chunk's slots come from campre_new (written by dev_trial_cam for this trial) instead of
+// being recomputed here — the same bits; on a problem with dozens of chunks per CTA the sin / cos of every slot of
+// every chunk, by a handful of threads while the rest of the CTA waits, was the critical path of the trial evaluation.
+__device__ __forceinline__ void dev_trial_points(const Dev& d, const DevParams& P, int chunk, bool from_table = false) {
   __shared__ double sm[4 * 3];
   __shared__ double cps[kTrialSlots * 21];    // trial R / J_l / t of the chunk's cameras
   __shared__ double Xs[kPointChunk * 3];      // the chunk's trial points
@@ -2889,7 +2892,13 @@ __device__ __forceinline__ void dev_trial_points(const Dev& d, const DevParams& 
   // Trial cameras of the chunk, computed here exactly as dev_trial_cam does (same expression, same bits) instead of
   // read back from campre_new: no L2 round trip per observation, and no dependence on the trial-camera phase.
   const bool staged = ns <= kTrialSlots;
-  if (staged) {
+  if (staged && from_table) {
+    for (int k = threadIdx.x; k < ns * 21; k += kThreads) {
+      const int sl = k / 21;
+      cps[k] = __ldcg(reinterpret_cast<const double*>(d.campre_new + __ldg(d.cs_cam + cs0 + sl)) + (k - 21 * sl));
+    }
+    for (int sl = threadIdx.x; sl < ns; sl += kThreads) cfs[sl] = d.fc[__ldg(d.cs_cam + cs0 + sl)];
+  } else if (staged) {
     for (int sl = threadIdx.x; sl < ns; sl += kThreads) {
       const int c = d.cs_cam[cs0 + sl];
       const int f = d.fc[c];
@@ -2994,7 +3003,7 @@ __device__ __forceinline__ void dev_trial_points(const Dev& d, const DevParams& 
   if (threadIdx.x < 3) d.ls_part[(size_t)chunk * 3 + threadIdx.x] = tot;
 }
 
-__global__ void __launch_bounds__(kThreads) k_trial_points(Dev d, DevParams P) { dev_trial_points(d, P, blockIdx.x); }
+__global__ void __launch_bounds__(kThreads) k_trial_points(Dev d, DevParams P) { dev_trial_points(d, P, blockIdx.x, true); }   // k_trial_cams ran before
 
 // one CTA per searching window: raw sums (cost, directional derivative, |step|^2 incl. the cameras on rank 0)
 __device__ __forceinline__ void dev_ls_reduce(const Dev& d, int w, int rank) {
@@ -3284,7 +3293,7 @@ __global__ void __launch_bounds__(kThreads, SBA_STEP_MIN_BLOCKS) k_step_loop(Dev
     }
     if (!fused_cams) grid.sync();         // the chunks read campre_new only when one of them has too many cameras to stage
     lap(2);
-    for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) { dev_trial_points(d, P, ch); __syncthreads(); }
+    for (int ch = blockIdx.x; ch < d.npchunk; ch += nb) { dev_trial_points(d, P, ch, !fused_cams); __syncthreads(); }
     if (one) dev_ls_partials_one(d, nb, cam2);
     grid.sync();
     lap(3);

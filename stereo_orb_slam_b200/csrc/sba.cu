@@ -938,7 +938,9 @@ static int do_step(sba_handle h, int* ls_rounds, bool defer = false) {
     int grid = std::max(1, std::min(h->coop_blocks, want));
     if (const char* e = std::getenv("SBA_STEP_GRID")) grid = std::max(1, std::min(grid, std::atoi(e)));   // tuning aid
     Dev dd = d; DevParams pp = P;
-    int fused_cams = (h->H.max_slots <= kTrialSlots && h->H.long_chunks.empty()) ? 1 : 0;
+    // (small problems: every chunk computes its own trial cameras and the grid barrier behind the trial-camera phase is
+    // skipped; large ones read the table that phase writes)
+    int fused_cams = (h->H.max_slots <= kTrialSlots && h->H.long_chunks.empty() && d.npchunk < 4 * grid) ? 1 : 0;
     // large problems: the back substitution as its own kernel (a CTA per chunk, W by bulk copy, more CTAs per SM than the
     // register-heavy cooperative kernel allows); small ones keep it inside the cooperative launch
     int skip_backsub = (d.npchunk >= 4 * grid && !std::getenv("SBA_BACKSUB_IN_LOOP")) ? 1 : 0;

@@ -91,7 +91,7 @@ struct sba_handle_s {
   cudaGraphExec_t step_graph = nullptr;   // one K1-K3 step (stage 8) captured once per structure: a single launch per step
   int32_t* h_counters = nullptr;      // pinned
   unsigned long long* stamps = nullptr;   // SBA_DEBUG_LS=2
-  uint8_t* stage = nullptr; size_t stage_bytes = 0;   // pinned staging of sba_ransac_stereo (grown on demand)
+  uint8_t* stage = nullptr; size_t stage_bytes = 0; cudaEvent_t ev_stage = nullptr; bool stage_busy = false;   // (also the packed upload of sba_set_structure)   // pinned staging of sba_ransac_stereo (grown on demand)
   int64_t launches = 0;
   int64_t nobs_all = 0;
   sba::Comm comm;                     // NCCL (multi-GPU), inactive on 1 GPU
@@ -206,6 +206,7 @@ int sba_create(int device, sba_handle* out) {
     for (int i = 0; i < 12 && e == cudaSuccess; ++i) e = cudaEventCreate(&h->ev[i]);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_stage, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
     if (e == cudaSuccess && !std::getenv("SBA_NO_COOP")) {
       int coop = 0, per_sm = 0, sms = 0;
@@ -259,6 +260,7 @@ void sba_destroy(sba_handle h) {
     for (int i = 0; i < 12; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     if (h->h_counters) cudaFreeHost(h->h_counters);
     if (h->stage) cudaFreeHost(h->stage);
+    if (h->ev_stage) cudaEventDestroy(h->ev_stage);
     if (h->stamps) cudaFree(h->stamps);
     if (h->side) cudaStreamDestroy(h->side);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
@@ -381,17 +383,57 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
   d.nbu = (int32_t)H.blk_row.size(); d.npchunk = (int32_t)H.pchunk_begin.size();
   d.ncs = (int32_t)H.cs_cam.size(); d.nlb = (int32_t)H.lb_blk.size();
   int rc = 0;
-#define UP(field) if ((rc = h->upload(&d.field, H.field))) return rc;
+  // The ~45 index tables go up in ONE copy when they are small (windows: a few MB): they are packed into the handle's
+  // pinned staging buffer and land in one device allocation — a pageable cudaMemcpyAsync per table costs more than
+  // the bytes it moves, and the per-frame calls of the reference's pattern (src/slam.cpp:122-129) pay it every frame.
+  // Large structures (global BA: hundreds of MB) keep one copy per table straight from the host vectors.
+  struct UpItem { const void** dst; const void* src; size_t bytes, off; };
+  std::vector<UpItem> items;
+  size_t up_total = 0;
+  auto add = [&](auto** dst, const auto& vec) {
+    const size_t bytes = vec.size() * sizeof(vec[0]);
+    items.push_back({(const void**)dst, vec.data(), bytes, up_total});
+    up_total += (bytes + 16 + 255) & ~(size_t)255;        // (+16: see alloc)
+  };
+  const int32_t* cdesc_i32 = nullptr;
+#define UP(field) add(&d.field, H.field);
   UP(fc) UP(free2cam) UP(cam_win) UP(fcam_win) UP(win_cam_off) UP(win_fc_off) UP(win_pchunk_off)
   UP(pt_off) UP(perm_p) UP(pcam) UP(ppt)
   UP(pchunk_begin) UP(pchunk_end) UP(pchunk_win)
-  { const int32_t* cd = nullptr; if ((rc = h->upload(&cd, H.cdesc))) return rc; d.cdesc = reinterpret_cast<const int4*>(cd); }   // cudaMalloc'ed: 256-byte aligned
+  add(&cdesc_i32, H.cdesc);                                                       // slots are 256-byte aligned: int4 loads
   UP(slot_off) UP(cs_cam) UP(cs_obs_off) UP(lb_off) UP(lb_blk) UP(lb_pair_off) UP(pairs) UP(oslot) UP(lb_sa) UP(lb_sb) UP(sobs)
   UP(blk_row) UP(blk_col) UP(diag_blk) UP(blk_part_off) UP(blk_part) UP(cam_part_off) UP(cam_part)
   UP(row_ptr) UP(bsr_col) UP(bsr_blk) UP(lb_pos) UP(cs_pos)
   d.nlong = (int32_t)H.long_chunks.size();
   if (d.nlong > 0) { UP(long_chunks) UP(long_zoff) UP(long_lb_off) }
 #undef UP
+  if (up_total <= ((size_t)16 << 20) && !std::getenv("SBA_NO_PACKED_UPLOAD")) {
+    uint8_t* arena = nullptr;
+    if ((rc = h->alloc(&arena, up_total))) return rc;
+    if (h->stage_busy) { CUDA_TRY(cudaEventSynchronize(h->ev_stage)); h->stage_busy = false; }
+    if (h->stage_bytes < up_total) {
+      if (h->stage) cudaFreeHost(h->stage);
+      h->stage = nullptr; h->stage_bytes = 0;
+      const size_t want = std::max<size_t>(up_total * 2, (size_t)1 << 20);
+      CUDA_TRY(cudaMallocHost((void**)&h->stage, want));
+      h->stage_bytes = want;
+    }
+    for (const UpItem& it : items) {
+      if (it.bytes) std::memcpy(h->stage + it.off, it.src, it.bytes);
+      *it.dst = arena + it.off;
+    }
+    CUDA_TRY(cudaMemcpyAsync(arena, h->stage, up_total, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaEventRecord(h->ev_stage, h->stream));
+    h->stage_busy = true;
+  } else {
+    for (const UpItem& it : items) {
+      uint8_t* p = nullptr;
+      if ((rc = h->alloc(&p, it.bytes))) return rc;
+      if (it.bytes) CUDA_TRY(cudaMemcpyAsync(p, it.src, it.bytes, cudaMemcpyHostToDevice, h->stream));
+      *it.dst = p;
+    }
+  }
+  d.cdesc = reinterpret_cast<const int4*>(cdesc_i32);
   const size_t nobs = (size_t)H.Nobs, nc = (size_t)H.Nc, np = (size_t)H.Np, nf = (size_t)H.Nf, nw = (size_t)H.nwin;
 #define AL(ptr, n) if ((rc = h->alloc(&ptr, (n)))) return rc;
   float4* uvp;
@@ -1886,9 +1928,9 @@ static int ransac_run(sba_handle h, int32_t nprob, const int64_t* off, const flo
   const size_t w_src = in_bytes + out_bytes, w_dst = w_src + (size_t)n * 16, w_T = w_dst + (size_t)n * 16, total = w_T + nh * 48;
   uint8_t* arena = nullptr;
   if ((rc = h->alloc(&arena, total))) return rc;
+  if (h->stage_busy) { CUDA_TRY(cudaEventSynchronize(h->ev_stage)); h->stage_busy = false; }      // the buffer is shared with sba_set_structure
   if (h->stage_bytes < std::max(in_bytes, out_bytes)) {
     if (h->stage) cudaFreeHost(h->stage);
-    if (h->stamps) cudaFree(h->stamps);
     h->stage = nullptr; h->stage_bytes = 0;
     const size_t want = std::max<size_t>(std::max(in_bytes, out_bytes) * 2, 1 << 16);
     CUDA_TRY(cudaMallocHost((void**)&h->stage, want));

@@ -4,11 +4,18 @@
 // 26-29).  For the global BA calls (src/slam.cpp:156, src/pose_graph_optimizer.cpp:95: thousands of free cameras,
 // banded co-visibility + loop-closure blocks) the whole solve S x = rhs is ONE cooperative launch:
 //   0  scatter the blocks of S into the (nested-dissection ordered) pattern of L
-//   1  elimination-tree levels, leaves first, one grid barrier per level; a CTA per block column j (left-looking):
-//        every block (i, j) gathers its static list of products  L_ik L_jk^T  on the FP64 tensor cores (two m8n8k4
-//        MMAs per product, operands straight from L2), the right-hand side gathers  sum_k L_jk y_k  alongside;
-//        then the 6x6 diagonal factor + its inverse, the panel  L_ij = A_ij Linv_jj^T  and  y_j = Linv_jj t_j
-//   2  the same levels downwards, a warp per column:  x_j = Linv_jj^T (y_j - sum_i L_ij^T x_i)
+//   1  elimination-tree levels, leaves first; the unit of work is a CHAIN (a run of columns each the only child of the
+//      next: the separators and the top of the tree).  Per level:
+//        phase A, whole grid   a warp per block / column of the level's chains gathers what comes from OUTSIDE its
+//                              chain — finished columns of lower levels, through L2: the static list of products
+//                              L_ik L_jk^T on the FP64 tensor cores (two m8n8k4 MMAs per product), and the
+//                              right-hand-side terms  sum_k L_jk y_k  — and subtracts it in place;  grid barrier
+//        phase B, CTA / chain  the chain's panel comes to shared memory and is factored column by column: in-chain
+//                              products from the panel, 6x6 diagonal factor + inverse, panel  L_ij = A_ij Linv_jj^T,
+//                              y_j = Linv_jj t_j;  written back;  grid barrier
+//      (chains too large for the panel buffer go column by column through L2)
+//   2  the same levels downwards:  x_j = Linv_jj^T (y_j - sum_i L_ij^T x_i); a chain first takes the contribution of
+//      the rows outside it for all its columns at once, then one warp walks its columns
 // One writer per block, every sum in list order: bit-reproducible, no atomics.  Symbolic phase: sparse_chol.cpp.
 #pragma once
 #include <cooperative_groups.h>

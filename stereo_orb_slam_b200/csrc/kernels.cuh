@@ -1217,14 +1217,17 @@ __global__ void __launch_bounds__(kAsmThreads) k_assemble_schur(Dev d, int mode,
   __shared__ double sm[kAsmWarps * 36];
   __shared__ double sM[36];
   __shared__ double sU[28];
-  if ((int)blockIdx.x < d.nbu) {
-    const int b = blockIdx.x;
+  // mode bit 16 (point-sharded ranks): the grid covers only the blocks / cameras this rank has partials for (asm_ids);
+  // the rest of U | gc | S | rsum was zeroed by the caller
+  const int bid = (mode & 16) ? __ldg(d.asm_ids + blockIdx.x) : (int)blockIdx.x;
+  if (bid < d.nbu) {
+    const int b = bid;
     if (prepare && d.blk_row[b] == d.blk_col[b]) return;     // diagonal blocks belong to the camera CTAs
     const double tot = cta_gather<36, 9>(d.spart, d.blk_part_off[b], d.blk_part_off[b + 1], sm);
     if (threadIdx.x < 36) d.Su[(size_t)b * 36 + threadIdx.x] = -tot;
     return;
   }
-  const int f = blockIdx.x - d.nbu;
+  const int f = bid - d.nbu;
   if (f >= d.Nf) {
     // mode bit 8: one more CTA per window sums the window's chunk costs and gradient maxima while the camera CTAs work
     const int ww = f - d.Nf;

@@ -113,6 +113,7 @@ struct sba_handle_s {
   bool schur_fresh = false;              // the last linearisation was fused: spart / rpart already hold this radius' Schur partials
   // ... and on a single GPU its camera-side assembly and finish are left to the next do_schur (one assemble kernel for
   // U / gc / S / rhs; cost + gradient test on the side stream while the solve runs)
+  std::vector<int32_t> asm_ids_host;
   bool every_window_free = false;     // every window has at least one free camera (k_assemble_schur can finish the windows itself)
   bool cams_pending = false; bool pend_keep_cost = false; int pend_lm_begin = -1; double pend_radius = 0.0;
   // exact block-sparse Cholesky of the reduced system for windows of more than kCholMaxCams free cameras (k_spchol)
@@ -434,6 +435,16 @@ int sba_set_structure(sba_handle h, int32_t Nc, int32_t Np, int64_t Nobs, const 
     }
   }
   d.cdesc = reinterpret_cast<const int4*>(cdesc_i32);
+  {
+    // point-sharded ranks assemble only what they have partials for (a rank of 8 touches about an eighth of a
+    // trajectory's cameras); built always, used on the sharded path
+    std::vector<int32_t>& ids = h->asm_ids_host;          // (a member: the copy may read it after this function returns)
+    ids.clear();
+    for (int32_t b = 0; b < d.nbu; ++b) if (H.blk_part_off[b + 1] > H.blk_part_off[b]) ids.push_back(b);
+    for (int32_t f = 0; f < d.Nf; ++f) { const int32_t c = H.free2cam[f]; if (H.cam_part_off[c + 1] > H.cam_part_off[c]) ids.push_back(d.nbu + f); }
+    d.n_asm = (int32_t)ids.size();
+    if ((rc = h->upload(&d.asm_ids, ids))) return rc;
+  }
   const size_t nobs = (size_t)H.Nobs, nc = (size_t)H.Nc, np = (size_t)H.Np, nf = (size_t)H.Nf, nw = (size_t)H.nwin;
 #define AL(ptr, n) if ((rc = h->alloc(&ptr, (n)))) return rc;
   float4* uvp;
@@ -815,7 +826,12 @@ static int do_schur(sba_handle h, bool exact_solver = false) {
       // point-sharded: this rank's share of U | gc | S | rsum by ONE assemble kernel, its cost and gradient maximum,
       // then ONE all-reduce over the whole block instead of one per linearisation plus one per Schur step
       const int world = h->comm.world;
-      LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 2, h->P, 0, 0);
+      if (!std::getenv("SBA_NO_COMPACT_ASM")) {
+        CUDA_TRY(cudaMemsetAsync(d.U, 0, (size_t)((d.rsum + (size_t)d.Nf * 6) - d.U) * sizeof(double), h->stream));
+        LAUNCH(h, k_assemble_schur, d.n_asm, kAsmThreads, d, 2 | 16, h->P, 0, 0);
+      } else {
+        LAUNCH(h, k_assemble_schur, d.nbu + d.Nf, kAsmThreads, d, 2, h->P, 0, 0);
+      }
       LAUNCH(h, k_lin_finish_local, d.nwin, kThreads, d, h->comm.rank, world);
       std::string _err;
       if (!h->comm.allreduce(d.U, (size_t)((d.rsum + (size_t)d.Nf * 6) - d.U), false, h->stream, &_err)) { set_error(_err); return SBA_NCCL_ERROR; }

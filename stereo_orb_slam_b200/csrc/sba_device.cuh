@@ -68,6 +68,7 @@ struct Dev {
   double *step_part;             // [npchunk*4]  g.dp, dp D dp, |x|^2, max|dp|
   double *ls_part;               // [npchunk*3]  trial cost, directional derivative, |x_trial - x|^2
   double *win_part;              // [nwin*2] cost and gradient maximum over a window's chunks (k_assemble_schur's window CTAs)
+  const int32_t *asm_ids; int32_t n_asm;   // blocks (< nbu) and cameras (nbu + f) with a non-empty partial list on this rank
   int32_t *win_done;             // [nwin] tickets of k_assemble_schur's camera CTAs (zero between launches)
   double *cta_part;              // [step-loop CTAs * 16] one global window: per-CTA partials of the rows above and of the
                                  //   camera terms, so that the window's reductions sum a few hundred rows, not 10^5
